@@ -1,0 +1,78 @@
+/* srb.h — C ABI of libsrb.so, the B200 (sm_100a) implementation of the HybridSuperResolutionModel hot path.
+ *
+ * The reference (GDev96/SuperResolution) is pure Python and has no FFI of its own; its only seam for this path is
+ * the nn.Module surface of src/architecture.py:30-82 plus the small functions next to it.  Every entry point below
+ * names the reference interface it replaces.  A maintainer binds it with ctypes.
+ *
+ * Conventions: plain pointers and sizes, no torch types.  All pointers are DEVICE pointers unless a name ends in
+ * _host.  Every function returns 0 (SRB_OK) or a negative SRB_E_* code; srb_last_error() gives the message
+ * (thread-local).  Work is enqueued on the given cudaStream_t (passed as void*), no internal synchronisation, no
+ * hidden allocation: the caller owns outputs and the workspace.
+ */
+#ifndef SRB_H_
+#define SRB_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRB_OK 0
+#define SRB_E_SHAPE (-1)     /* unsupported geometry (H, W must be multiples of 16; stage-1 output of 8) */
+#define SRB_E_DTYPE (-2)
+#define SRB_E_WORKSPACE (-3) /* workspace / packed-weight buffer too small */
+#define SRB_E_CUDA (-4)      /* CUDA runtime / driver error, text in srb_last_error() */
+#define SRB_E_ARG (-5)
+
+/* element types of host/device image buffers */
+#define SRB_F32 0
+#define SRB_BF16 1
+#define SRB_U16 2
+
+/* smoothing modes of AntiCheckerboardLayer (reference src/architecture.py:9-27,67-72) */
+#define SRB_SMOOTH_NONE 0
+#define SRB_SMOOTH_LIGHT 1    /* 3x3 /16   */
+#define SRB_SMOOTH_BALANCED 2 /* 5x5 /256  */
+#define SRB_SMOOTH_STRONG 3   /* 7x7 /1600 */
+
+int srb_version(void);
+const char* srb_last_error(void);
+
+/* ---- model weights -------------------------------------------------------------------------------------------
+ * Replaces: nn.Module parameter storage of HybridSuperResolutionModel (state_dict contract).
+ * params: array of n device pointers in the canonical order returned by srb_param_name(i) (fp32 tensors, contiguous,
+ * PyTorch layout) followed by the two int64 index buffers.  packed receives bf16 / fp32 kernel-ready copies. */
+int srb_param_count(void);
+const char* srb_param_name(int i);       /* state-dict key, e.g. "stage1.conv_first.weight" */
+int64_t srb_param_numel(int i);
+size_t srb_packed_bytes(void);
+int srb_pack_weights(const void* const* params, int n, void* packed, size_t packed_bytes, void* stream);
+
+/* ---- forward --------------------------------------------------------------------------------------------------
+ * Replaces: HybridSuperResolutionModel.forward (src/architecture.py:74-82): stage1 (RRDBNet) -> s1 -> stage2 (HAT)
+ * -> s2 -> sf.  x: [B,1,H,W] (x_dtype F32 in [0,1], or U16 which is divided by 65535 like src/dataset.py:34).
+ * y: [B,1,4H,4W] F32 (or U16: clip, *65535, truncate like scripts/Modello_5.py:29-33).
+ * stage_mask: bit0 run stage 1, bit1 run stage 2 (both set = full model). */
+size_t srb_workspace_bytes(int B, int H, int W);
+int srb_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
+                void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream);
+/* number of kernels one srb_forward enqueues for this geometry (for bench "gpu_launches") */
+int srb_forward_launch_count(int B, int H, int W, int smoothing, int stage_mask);
+
+/* ---- granular ops (tests / building blocks) -------------------------------------------------------------------
+ * 3x3 (taps=9) or 1x1 (taps=1) NHWC bf16 implicit-GEMM convolution on tcgen05 with the fused epilogue
+ *   v = acc + bias; v = act(v); v = v*alpha1 + res1; v = v*alpha2 + res2*res2_cs
+ * Replaces: nn.Conv2d(…,3,1,1) / nn.Linear call sites inside RRDBNet / HAT. */
+int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const float* bias, void* out_bf16,
+                       int out_pitch, float* out_f32, int out32_pitch, int B, int H, int W, int Cin, int Cout,
+                       int taps, int act, float slope, float alpha1, const void* res1, int res1_f32, int res1_pitch,
+                       float alpha2, const void* res2, int res2_f32, int res2_pitch, const float* res2_cs,
+                       int pixel_shuffle, void* stream);
+/* fp32 [Cout,Cin,kh,kw] (PyTorch) -> bf16 [kh*kw][Cout][Cin] */
+int srb_pack_conv_weight(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRB_H_ */

@@ -1,0 +1,59 @@
+"""ctypes binding of libsrb.so (include/srb.h).  Fails loudly: there is no CPU / PyTorch fallback."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libsrb.so')
+
+SRB_F32, SRB_BF16, SRB_U16 = 0, 1, 2
+SMOOTHING = {'none': 0, 'light': 1, 'balanced': 2, 'strong': 3}
+ACT_NONE, ACT_LRELU, ACT_GELU = 0, 1, 2
+
+_lib = None
+
+_vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+
+_PROTOS = {
+    'srb_version': (C.c_int, []),
+    'srb_last_error': (C.c_char_p, []),
+    'srb_pack_conv_weight': (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    'srb_conv_nhwc_bf16': (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _i, _i,
+                                _f, _vp, _i, _i, _vp, _i, _vp]),
+}
+
+
+def register(name, restype, argtypes):
+    _PROTOS[name] = (restype, argtypes)
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.restype, fn.argtypes = restype, argtypes
+
+
+def lib():
+    """Load libsrb.so (built by __graft_entry__.build()).  Raises if it is missing: no fallback path exists."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f'{LIB_PATH} not built: run `python -c "import __graft_entry__ as g; g.build()"` '
+                               f'(or `make -C superresolution_b200/csrc`). There is no CPU fallback.')
+        _lib = C.CDLL(LIB_PATH)
+        for name, (restype, argtypes) in _PROTOS.items():
+            fn = getattr(_lib, name)
+            fn.restype, fn.argtypes = restype, argtypes
+    return _lib
+
+
+def check(rc, what=''):
+    if rc != 0:
+        msg = lib().srb_last_error().decode('utf-8', 'replace')
+        raise RuntimeError(f'libsrb {what} failed (code {rc}): {msg}')
+
+
+def ptr(t):
+    """device pointer of a torch tensor (or None)."""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def current_stream():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,79 @@
+// extern "C" surface of libsrb.so (declared in include/srb.h).  Thin: argument checks + launches.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.h"
+
+namespace srb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return SRB_E_CUDA;
+}
+
+// fp32 [Cout][Cin][taps] (PyTorch conv weight, taps = kh*kw contiguous) -> bf16 [taps][Cout][Cin]
+__global__ void pack_conv_weight_kernel(const float* __restrict__ w, bf16* __restrict__ o, int Cout, int Cin,
+                                        int taps) {
+    const int n = Cout * Cin * taps;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int ci = i % Cin, co = (i / Cin) % Cout, t = i / (Cin * Cout);
+        o[i] = __float2bfloat16_rn(w[((size_t)co * Cin + ci) * taps + t]);
+    }
+}
+
+int pack_conv_weight(const float* w, bf16* o, int Cout, int Cin, int taps, cudaStream_t s) {
+    const int n = Cout * Cin * taps;
+    pack_conv_weight_kernel<<<(n + 255) / 256, 256, 0, s>>>(w, o, Cout, Cin, taps);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+}  // namespace srb
+
+using namespace srb;
+
+extern "C" {
+
+int srb_version(void) { return 100; }
+const char* srb_last_error(void) { return g_err; }
+
+int srb_pack_conv_weight(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream) {
+    if (!w || !w_packed || Cout <= 0 || Cin <= 0 || taps <= 0) {
+        set_error("pack_conv_weight: bad args");
+        return SRB_E_ARG;
+    }
+    return pack_conv_weight(w, (bf16*)w_packed, Cout, Cin, taps, (cudaStream_t)stream);
+}
+
+int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const float* bias, void* out_bf16,
+                       int out_pitch, float* out_f32, int out32_pitch, int B, int H, int W, int Cin, int Cout,
+                       int taps, int act, float slope, float alpha1, const void* res1, int res1_f32, int res1_pitch,
+                       float alpha2, const void* res2, int res2_f32, int res2_pitch, const float* res2_cs,
+                       int pixel_shuffle, void* stream) {
+    if (!in || !w_packed || (!out_bf16 && !out_f32) || B <= 0) {
+        set_error("conv: bad args");
+        return SRB_E_ARG;
+    }
+    ConvArgs a;
+    memset(&a, 0, sizeof(a));
+    a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout; a.taps = taps;
+    a.in = (const bf16*)in; a.in_pitch = in_pitch; a.w = (const bf16*)w_packed; a.bias = bias;
+    a.act = act; a.slope = slope;
+    a.alpha1 = alpha1; a.res1 = res1; a.res1_f32 = res1_f32; a.res1_pitch = res1_pitch;
+    a.alpha2 = alpha2; a.res2 = res2; a.res2_f32 = res2_f32; a.res2_pitch = res2_pitch; a.res2_cs = res2_cs;
+    a.out = (bf16*)out_bf16; a.out_pitch = out_pitch; a.out32 = out_f32; a.out32_pitch = out32_pitch;
+    a.pixel_shuffle = pixel_shuffle;
+    return conv_tc_launch(a, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,57 @@
+// Shared host-side declarations for the srb CUDA library (error convention, launch parameter structs).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "../../include/srb.h"
+
+namespace srb {
+
+typedef __nv_bfloat16 bf16;
+
+// thread-local error string behind srb_last_error()
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);  // records the message, returns SRB_E_CUDA
+
+#define SRB_CUDA(x)                                          \
+    do {                                                     \
+        cudaError_t e__ = (x);                               \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #x);   \
+    } while (0)
+#define SRB_TRY(x)                \
+    do {                          \
+        int r__ = (x);            \
+        if (r__ != SRB_OK) return r__; \
+    } while (0)
+
+enum Act : int { ACT_NONE = 0, ACT_LRELU = 1, ACT_GELU = 2 };
+
+// One tensor-core conv / linear launch.  All activation tensors are NHWC ("pixel-major") with an explicit channel
+// pitch so that a layer can read / write a channel slice of a wider buffer (dense-block concatenation is free).
+//   v = acc + bias[c]; v = act(v); v = v*alpha1 + res1; v = v*alpha2 + res2 * (res2_cs ? res2_cs[b,c] : 1)
+struct ConvArgs {
+    int B, H, W;      // output (= input) spatial size; stride 1, zero "same" padding
+    int Cin, Cout;    // reduction channels / output channels
+    int taps;         // 9 (3x3) or 1 (1x1 == token-wise linear)
+    const bf16* in;   // input base already offset to the first input channel
+    int in_pitch;     // channels per pixel in the input buffer
+    const bf16* w;    // packed weights [taps][Cout][Cin] bf16
+    const float* bias;  // [Cout] or null
+    int act;
+    float slope;      // LeakyReLU slope
+    float alpha1;
+    const void* res1; int res1_f32; int res1_pitch;   // per pixel, channel index = output channel
+    float alpha2;
+    const void* res2; int res2_f32; int res2_pitch;
+    const float* res2_cs;                             // optional [B][Cout] scale on res2
+    bf16* out; int out_pitch;                         // bf16 output (base offset to first out channel) or null
+    float* out32; int out32_pitch;                    // fp32 output or null
+    int pixel_shuffle;                                // 1: out is [B,2H,2W,Cout/4] (PixelShuffle(2) fused in the store)
+    const float* ln_stats;                            // reserved (folded LayerNorm); null
+};
+
+int conv_tc_launch(const ConvArgs& a, cudaStream_t stream);
+
+}  // namespace srb

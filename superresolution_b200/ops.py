@@ -1,0 +1,37 @@
+"""Granular operator wrappers over the C ABI (used by the parity tests; the model forward uses srb_forward)."""
+import torch
+
+from . import _lib as L
+
+
+def pack_conv_weight(w):
+    """fp32 [Cout,Cin,kh,kw] (or Linear [Cout,Cin]) CUDA tensor -> bf16 [taps][Cout][Cin]."""
+    w = w.detach().float().contiguous()
+    cout, cin = w.shape[0], w.shape[1]
+    taps = w.numel() // (cout * cin)
+    out = torch.empty(taps, cout, cin, dtype=torch.bfloat16, device=w.device)
+    L.check(L.lib().srb_pack_conv_weight(L.ptr(w), L.ptr(out), cout, cin, taps, L.current_stream()), 'pack_conv_weight')
+    return out
+
+
+def conv_nhwc(x, cin, w_packed, bias=None, out=None, out32=None, act=L.ACT_NONE, slope=0.2, alpha1=1.0, res1=None,
+              alpha2=1.0, res2=None, res2_cs=None, pixel_shuffle=False):
+    """x: bf16 [B,H,W,Cpitch] (possibly a channel-offset view of a wider buffer); reads channels [0,cin).
+
+    out / out32 / res1 / res2: NHWC tensors (views allowed; last-dim stride must be 1); pitch = stride(2).
+    """
+    B, H, W = x.shape[:3]
+    taps, cout = w_packed.shape[0], w_packed.shape[1]
+    assert w_packed.shape[2] == cin
+
+    def pitch(t):
+        return 0 if t is None else t.stride(2)
+
+    def isf32(t):
+        return int(t is not None and t.dtype == torch.float32)
+
+    rc = L.lib().srb_conv_nhwc_bf16(
+        L.ptr(x), x.stride(2), L.ptr(w_packed), L.ptr(bias), L.ptr(out), pitch(out), L.ptr(out32), pitch(out32),
+        B, H, W, cin, cout, taps, act, slope, alpha1, L.ptr(res1), isf32(res1), pitch(res1), alpha2, L.ptr(res2),
+        isf32(res2), pitch(res2), L.ptr(res2_cs), int(pixel_shuffle), L.current_stream())
+    L.check(rc, 'conv_nhwc_bf16')
