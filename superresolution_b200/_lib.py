@@ -17,6 +17,14 @@ _PROTOS = {
     'srb_version': (C.c_int, []),
     'srb_last_error': (C.c_char_p, []),
     'srb_pack_conv_weight': (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    'srb_param_count': (_i, []),
+    'srb_param_name': (C.c_char_p, [_i]),
+    'srb_param_numel': (C.c_int64, [_i]),
+    'srb_packed_bytes': (_sz, []),
+    'srb_pack_weights': (_i, [_vp, _i, _vp, _sz, _vp]),
+    'srb_workspace_bytes': (_sz, [_i, _i, _i]),
+    'srb_forward': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _sz, _i, _i, _vp]),
+    'srb_forward_launch_count': (_i, [_i, _i, _i, _i, _i]),
     'srb_conv_nhwc_bf16': (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _i, _i,
                                 _f, _vp, _i, _i, _vp, _i, _vp]),
 }

@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "common.h"
+#include "ops.h"
 
 namespace srb {
 
@@ -74,6 +75,30 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
     a.out = (bf16*)out_bf16; a.out_pitch = out_pitch; a.out32 = out_f32; a.out32_pitch = out32_pitch;
     a.pixel_shuffle = pixel_shuffle;
     return conv_tc_launch(a, (cudaStream_t)stream);
+}
+
+int srb_param_count(void) { return model_param_count(); }
+const char* srb_param_name(int i) { return model_param_name(i); }
+int64_t srb_param_numel(int i) { return model_param_numel(i); }
+size_t srb_packed_bytes(void) { return model_packed_bytes(); }
+int srb_pack_weights(const void* const* params, int n, void* packed, size_t packed_bytes, void* stream) {
+    if (!params || !packed) { set_error("pack_weights: null pointer"); return SRB_E_ARG; }
+    return model_pack(params, n, packed, packed_bytes, (cudaStream_t)stream);
+}
+size_t srb_workspace_bytes(int B, int H, int W) {
+    if (B <= 0 || H <= 0 || W <= 0) return 0;
+    return model_workspace_bytes(B, H, W);
+}
+int srb_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
+                void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream) {
+    return model_forward(x, x_dtype, y, y_dtype, B, H, W, packed, workspace, workspace_bytes, smoothing, stage_mask,
+                         (cudaStream_t)stream, false, nullptr);
+}
+int srb_forward_launch_count(int B, int H, int W, int smoothing, int stage_mask) {
+    int n = 0;
+    int rc = model_forward(nullptr, SRB_F32, nullptr, SRB_F32, B, H, W, nullptr, nullptr, 0, smoothing, stage_mask, 0,
+                           true, &n);
+    return rc == SRB_OK ? n : rc;
 }
 
 }  // extern "C"

@@ -415,13 +415,13 @@ int conv_tc_launch(const ConvArgs& a, cudaStream_t stream) {
     }
     if (a.pixel_shuffle && (a.Cout % 128 || !a.out)) { set_error("conv_tc: pixel_shuffle needs Cout%%128==0"); return SRB_E_ARG; }
     if (a.taps == 9) {
-        if (a.Cout == 32) return launch_cfg<ConvCfg<32, 4, 9>>(a, stream);
-        if (a.Cout == 64) return launch_cfg<ConvCfg<64, 4, 9>>(a, stream);
+        if (a.Cout == 32) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<32, 4, 9>>(a, stream) : launch_cfg<ConvCfg<32, 2, 9>>(a, stream);
+        if (a.Cout == 64) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<64, 4, 9>>(a, stream) : launch_cfg<ConvCfg<64, 2, 9>>(a, stream);
         if (a.Cout % 128 == 0) return launch_cfg<ConvCfg<128, 2, 9>>(a, stream);
         if (a.Cout % 96 == 0) return launch_cfg<ConvCfg<96, 2, 9>>(a, stream);
     } else {
         if (a.Cout % 96 == 0) return launch_cfg<ConvCfg<96, 2, 1>>(a, stream);
-        if (a.Cout % 64 == 0) return launch_cfg<ConvCfg<64, 4, 1>>(a, stream);
+        if (a.Cout % 64 == 0) return launch_cfg<ConvCfg<64, 2, 1>>(a, stream);
     }
     set_error("conv_tc: no kernel instance for Cout=%d taps=%d", a.Cout, a.taps);
     return SRB_E_SHAPE;

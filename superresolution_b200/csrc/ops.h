@@ -1,0 +1,47 @@
+// Internal (C++) declarations of every kernel launcher in libsrb.so.
+#pragma once
+#include "common.h"
+
+namespace srb {
+
+// api.cu
+int pack_conv_weight(const float* w, bf16* o, int Cout, int Cin, int taps, cudaStream_t s);
+
+// small_ops.cu
+int rrdb_conv_first(const void* x, int x_dtype, const float* w, const float* bias, bf16* out, int out_pitch,
+                    float* trunk, float* feat, int B, int h, int w_, cudaStream_t s);
+int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, float* out, int B, int H, int W,
+               cudaStream_t s);
+int blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int W, cudaStream_t s);
+int convert_out(const float* in, void* out, int out_dtype, size_t n, cudaStream_t s);
+
+// small_ops2.cu
+int hat_conv_first_ln(const float* img, const float* w, const float* bias, const float* gamma, const float* beta,
+                      bf16* f0, bf16* xn, int B, int H, int W, cudaStream_t s);
+int layernorm96(const bf16* in, const float* gamma, const float* beta, bf16* out, size_t ntok, cudaStream_t s);
+int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cudaStream_t s);
+int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const float* w1, const float* b1,
+                          const float* w2, const float* b2, float conv_scale, int B, int HW, cudaStream_t s);
+
+// attn.cu
+// qkv: bf16 [B,H,W,288] = [q(96) | k(96) | v(96)], head h = channels [16h,16h+16) of each part.
+// bias: fp32 [6][64][NK] relative-position bias already gathered from the table.
+// shift: 0 or 4 (HAB cyclic shift, mask -100 across region borders).  out: bf16 [B,H,W,96].
+int window_attention(const bf16* qkv, const float* bias, bf16* out, int B, int H, int W, int shift, cudaStream_t s);
+// OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.
+int ocab_attention(const bf16* qkv, const float* bias, bf16* out, int B, int H, int W, cudaStream_t s);
+// table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> bias fp32 [6][64][NK]
+int expand_rel_bias(const float* table, int T, const int64_t* index, int NK, float* bias, cudaStream_t s);
+
+// forward.cu
+int model_param_count();
+const char* model_param_name(int i);
+int64_t model_param_numel(int i);
+size_t model_packed_bytes();
+int model_pack(const void* const* params, int n, void* packed, size_t packed_bytes, cudaStream_t s);
+size_t model_workspace_bytes(int B, int H, int W);
+int model_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
+                  void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, cudaStream_t s, bool dry,
+                  int* launches);
+
+}  // namespace srb

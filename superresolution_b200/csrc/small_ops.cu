@@ -1,0 +1,200 @@
+// HBM-bound / CUDA-core kernels around the tensor-core convs: input scaling + pixel-unshuffle + conv_first(4->64),
+// HAT conv_first(1->96)+LayerNorm, 64->1 convs, binomial blur, nearest x2, LayerNorm(96), CAB channel attention.
+// Each cites the reference call site it replaces.
+#include "common.h"
+#include "ops.h"
+
+namespace srb {
+
+__device__ __forceinline__ float load_pix(const void* x, int dtype, size_t i) {
+    // K1: src/dataset.py:31-34 (u16 / 65535.0) fused into the first conv's loads
+    if (dtype == SRB_U16) return (float)((const uint16_t*)x)[i] / 65535.0f;
+    if (dtype == SRB_BF16) return __bfloat162float(((const bf16*)x)[i]);
+    return ((const float*)x)[i];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K2: pixel_unshuffle(2) + conv_first (4->64, 3x3, pad 1) of RRDBNet (App. A.1).  One thread = one output pixel x 8
+// output channels.  Writes bf16 into channels [0,64) of the dense-block buffer and the fp32 trunk (two copies: the
+// running trunk and the long-skip "feat").
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+rrdb_conv_first_kernel(const void* __restrict__ x, int x_dtype, const float* __restrict__ w /*[64][4][3][3]*/,
+                       const float* __restrict__ bias, bf16* __restrict__ out, int out_pitch,
+                       float* __restrict__ trunk, float* __restrict__ feat, int B, int h, int w_) {
+    __shared__ float sw[64 * 36];
+    __shared__ float sb[64];
+    for (int i = threadIdx.x; i < 64 * 36; i += blockDim.x) sw[i] = w[i];
+    if (threadIdx.x < 64) sb[threadIdx.x] = bias[threadIdx.x];
+    __syncthreads();
+    const size_t total = (size_t)B * h * w_ * 8;
+    const int W = 2 * w_, H = 2 * h;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int cg = idx & 7;
+        const size_t pix = idx >> 3;
+        const int xo = pix % w_, yo = (pix / w_) % h, b = pix / ((size_t)w_ * h);
+        float in[36];
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                for (int kx = 0; kx < 3; ++kx) {
+                    const int yy = yo + ky - 1, xx = xo + kx - 1;
+                    float v = 0.f;
+                    if (yy >= 0 && yy < h && xx >= 0 && xx < w_)
+                        v = load_pix(x, x_dtype, ((size_t)b * H + 2 * yy + (c >> 1)) * W + 2 * xx + (c & 1));
+                    in[c * 9 + ky * 3 + kx] = v;
+                }
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float* wr = sw + (cg * 8 + j) * 36;
+            float s = sb[cg * 8 + j];
+#pragma unroll
+            for (int k = 0; k < 36; ++k) s = fmaf(in[k], wr[k], s);
+            acc[j] = s;
+        }
+        uint4 o;
+        __nv_bfloat162* hh = (__nv_bfloat162*)&o;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) hh[k] = __floats2bfloat162_rn(acc[2 * k], acc[2 * k + 1]);
+        *(uint4*)(out + pix * out_pitch + cg * 8) = o;
+        float4* tp = (float4*)(trunk + pix * 64 + cg * 8);
+        tp[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        tp[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+        float4* fp = (float4*)(feat + pix * 64 + cg * 8);
+        fp[0] = tp[0];
+        fp[1] = tp[1];
+    }
+}
+
+int rrdb_conv_first(const void* x, int x_dtype, const float* w, const float* bias, bf16* out, int out_pitch,
+                    float* trunk, float* feat, int B, int h, int w_, cudaStream_t s) {
+    const size_t total = (size_t)B * h * w_ * 8;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 8) grid = 148 * 8;
+    rrdb_conv_first_kernel<<<grid, 256, 0, s>>>(x, x_dtype, w, bias, out, out_pitch, trunk, feat, B, h, w_);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K7/K17: 3x3 conv with ONE output channel (conv_last of both stages), NHWC bf16 [B,H,W,64] -> fp32 [B,H,W].
+// 8 lanes per pixel, each owning 8 input channels (16-byte loads, 4 pixels = 512 contiguous bytes per warp load).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restrict__ w /*[1][64][3][3]*/,
+                  const float* __restrict__ bias, float* __restrict__ out, int B, int H, int W) {
+    const int sub = threadIdx.x & 7;
+    float wr[72];  // [tap][8 channels of this lane]
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) wr[t * 8 + j] = __ldg(w + (sub * 8 + j) * 9 + t);
+    const float b0 = bias[0];
+    const size_t npix = (size_t)B * H * W;
+    for (size_t pix = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 3; pix < npix;
+         pix += ((size_t)gridDim.x * blockDim.x) >> 3) {
+        const int x = pix % W, y = (pix / W) % H;
+        const size_t b = pix / ((size_t)W * H);
+        float s = 0.f;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
+            if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+                const uint4 v = __ldg((const uint4*)(in + ((b * H + yy) * W + xx) * pitch + sub * 8));
+                const __nv_bfloat162* h2 = (const __nv_bfloat162*)&v;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h2[k]);
+                    s = fmaf(f.x, wr[t * 8 + 2 * k], s);
+                    s = fmaf(f.y, wr[t * 8 + 2 * k + 1], s);
+                }
+            }
+        }
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        if (sub == 0) out[pix] = s + b0;
+    }
+}
+
+int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, float* out, int B, int H, int W,
+               cudaStream_t s) {
+    const size_t threads = (size_t)B * H * W * 8;
+    int grid = (int)((threads + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    conv_cout1_kernel<<<grid, 256, 0, s>>>(in, pitch, w, bias, out, B, H, W);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K8: AntiCheckerboardLayer (src/architecture.py:9-27): depthwise binomial k x k blur, zero padding, on fp32 [B,H,W].
+// Optional fused output conversion to u16 (scripts/Modello_5.py:29-33: clip, *65535, truncate).
+// ---------------------------------------------------------------------------------------------------------------
+template <int K>
+__global__ void __launch_bounds__(256)
+blur_kernel(const float* __restrict__ in, void* __restrict__ out, int out_dtype, int B, int H, int W) {
+    constexpr int R = K / 2;
+    // binomial rows: 3:[1,2,1]/4  5:[1,4,6,4,1]/16  7:[1,6,15,20,15,6,1]/64 ; the reference divides the integer
+    // outer product by 16 / 256 / 1600 — note 7x7 uses 1600, not 4096 (src/architecture.py:13).
+    const float row[7] = {K == 3 ? 1.f : K == 5 ? 1.f : 1.f, K == 3 ? 2.f : K == 5 ? 4.f : 6.f,
+                          K == 3 ? 1.f : K == 5 ? 6.f : 15.f, K == 5 ? 4.f : 20.f, K == 5 ? 1.f : 15.f, 6.f, 1.f};
+    const float norm = K == 3 ? 16.f : K == 5 ? 256.f : 1600.f;
+    const size_t n = (size_t)B * H * W;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int x = i % W, y = (i / W) % H;
+        const size_t base = i - (size_t)y * W - x;
+        float s = 0.f;
+#pragma unroll
+        for (int dy = -R; dy <= R; ++dy) {
+            const int yy = y + dy;
+            if (yy < 0 || yy >= H) continue;
+#pragma unroll
+            for (int dx = -R; dx <= R; ++dx) {
+                const int xx = x + dx;
+                if (xx < 0 || xx >= W) continue;
+                s = fmaf(in[base + (size_t)yy * W + xx], (row[dy + R] * row[dx + R]) / norm, s);
+            }
+        }
+        if (out_dtype == SRB_U16) {
+            const float c = fminf(fmaxf(s, 0.f), 1.f) * 65535.f;
+            ((uint16_t*)out)[i] = (uint16_t)c;
+        } else {
+            ((float*)out)[i] = s;
+        }
+    }
+}
+
+int blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int W, cudaStream_t s) {
+    const size_t n = (size_t)B * H * W;
+    int grid = (int)((n + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    if (mode == SRB_SMOOTH_LIGHT) blur_kernel<3><<<grid, 256, 0, s>>>(in, out, out_dtype, B, H, W);
+    else if (mode == SRB_SMOOTH_BALANCED) blur_kernel<5><<<grid, 256, 0, s>>>(in, out, out_dtype, B, H, W);
+    else if (mode == SRB_SMOOTH_STRONG) blur_kernel<7><<<grid, 256, 0, s>>>(in, out, out_dtype, B, H, W);
+    else { set_error("blur: bad mode %d", mode); return SRB_E_ARG; }
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+// fp32 [n] -> fp32 / u16 (used when smoothing == none and the caller wants u16 or a copy into y)
+__global__ void convert_out_kernel(const float* __restrict__ in, void* __restrict__ out, int out_dtype, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float v = in[i];
+        if (out_dtype == SRB_U16) ((uint16_t*)out)[i] = (uint16_t)(fminf(fmaxf(v, 0.f), 1.f) * 65535.f);
+        else ((float*)out)[i] = v;
+    }
+}
+
+int convert_out(const float* in, void* out, int out_dtype, size_t n, cudaStream_t s) {
+    int grid = (int)((n + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    convert_out_kernel<<<grid, 256, 0, s>>>(in, out, out_dtype, n);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+}  // namespace srb
