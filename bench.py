@@ -1,0 +1,275 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the hot path (BASELINE.json: "SR output Mpix/s at 1/2/4/8 B200 (bf16)").
+
+Workload (configs[1]): full HybridSuperResolutionModel (RRDBNet 2x + HAT 2x), bf16 tensor-core math with fp32
+accumulation, batch 16 of synthetic 128x128 single-channel 16-bit patches per GPU, smoothing='balanced',
+random-init weights (seed 0).  One "step" = one forward of the batch.  Multi-GPU = independent tile batches per rank
+(weak scaling, no data-path collective).
+
+  python bench.py --gpus N --steps K --warmup W          (torchrun launches it for N>1)
+  python bench.py --impl reference ...                   CPU arm: the oracle port of the reference on host cores
+
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = 'sr_output_mpix_per_s'
+UNIT = 'Mpix/s'
+BATCH, PATCH = 16, 128
+FLOP_PER_PATCH = 725.74e9  # 362.869 GMAC per 128x128 patch
+WORKLOAD = 'hybrid_rrdb23+hat96_bf16_infer_b16_128px'
+
+
+def load_peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d.get('bf16_tflops_sustained', 1400.0), d.get('hbm_gbs', 6650.0), 'measured (MEASURED_PEAKS.json, sustained)'
+    return 1400.0, 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def synthetic_batch(B, size, seed=1):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randint(0, 65536, (B, 1, size, size), generator=g).float() / 65535.0
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonSwPowerCap: 'sw_power_cap',
+                 nv.nvmlClocksThrottleReasonHwSlowdown: 'hw_slowdown',
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: 'sw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: 'hw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: 'hw_power_brake'}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {'sm_mhz': s[len(s) // 2] if s else None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons)}
+
+
+def visible_gpu_index(local_rank):
+    vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+    if vis:
+        try:
+            return int(vis.split(',')[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+def cpu_oracle_throughput(steps, warmup, size=64):
+    """Reference arm / cpu_baseline: the oracle port of the reference model (fp32, eager, no_grad) on all host cores,
+    on a bounded sample: ONE size x size patch per step (per-pixel cost is size-independent: convs + local windows)."""
+    from oracle.hybrid import HybridSuperResolutionModel as Oracle
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    o = Oracle(output_size=4 * size, smoothing='balanced').eval()
+    x = synthetic_batch(1, size)
+    with torch.no_grad():
+        for _ in range(warmup):
+            o(x)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            o(x)
+        dt = time.perf_counter() - t0
+    mpix = steps * (4 * size) ** 2 / 1e6
+    return mpix / dt, dt / steps * 1e3, cores, f'{steps} x one {size}x{size} patch (fp32 oracle port, torch eager)'
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    v, ms, cores, sample = cpu_oracle_throughput(args.steps, args.warmup)
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': WORKLOAD, 'note': 'reference model cannot be imported (BasicSR/HAT not vendored): '
+                                                 'oracle port on host cores'},
+        'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu(args):
+    import torch.distributed as dist
+    from superresolution_b200.architecture import HybridSuperResolutionModel
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py needs a CUDA device: libsrb has no CPU path')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    torch.manual_seed(0)
+    model = HybridSuperResolutionModel(output_size=4 * PATCH, smoothing='balanced').to(dev).eval()
+    x_host = synthetic_batch(BATCH, PATCH, seed=1 + rank).pin_memory()
+    x_dev = x_host.to(dev)
+    out_mpix = BATCH * (4 * PATCH) ** 2 / 1e6
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.no_grad():
+        model.pack_weights()
+        y = model(x_dev)  # first call: workspace allocation
+        torch.cuda.synchronize()
+        # ---- capture the forward in a CUDA graph (stream-ordered, allocation-free inside libsrb) ----
+        graph = None
+        if not args.no_graph:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                model(x_dev)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                y_graph = model(x_dev)
+
+        def step():
+            if graph is not None:
+                graph.replay()
+                return y_graph
+            return model(x_dev)
+
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+        for _ in range(max(args.warmup, 3)):
+            step()
+        barrier()
+        sampler = ClockSampler(visible_gpu_index(local_rank))
+        sampler.start()
+        # ---- value: device-resident inputs, one CUDA-event pair per step, L2 flushed between steps ----
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        for e0, e1 in evs:
+            flush.zero_()
+            e0.record()
+            step()
+            e1.record()
+        torch.cuda.synchronize()
+        dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
+        # ---- e2e: public API with host buffers, H2D + forward + D2H inside the timed region ----
+        y_host = torch.empty(BATCH, 1, 4 * PATCH, 4 * PATCH, dtype=torch.float32).pin_memory()
+        x_in = torch.empty_like(x_dev)
+        for _ in range(2):
+            x_in.copy_(x_host, non_blocking=True)
+            y_host.copy_(model(x_in), non_blocking=True)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            x_in.copy_(x_host, non_blocking=True)
+            y_host.copy_(model(x_in), non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        e2e_ms = e0.elapsed_time(e1)
+        clocks = sampler.stop()
+        # ---- roofline of the dominant kernel family (tcgen05 implicit-GEMM conv/linear), per-launch CUDA events ----
+        prof = model.profile(x_dev)
+
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = t.tolist()
+    if rank == 0:
+        peak_tf, peak_hbm, peak_src = load_peaks()
+        tc_ms = prof['conv3x3_tcgen05'][0] + prof['linear_tcgen05'][0]
+        tc_flops = prof['conv3x3_tcgen05'][1] + prof['linear_tcgen05'][1]
+        tc_n = prof['conv3x3_tcgen05'][2] + prof['linear_tcgen05'][2]
+        total_prof_ms = sum(v[0] for v in prof.values())
+        achieved = tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+        launches = model.launch_count(BATCH, PATCH, PATCH)
+        line = {
+            'metric': METRIC, 'value': world * out_mpix * args.steps / (dev_ms * 1e-3), 'unit': UNIT,
+            'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': dev_ms / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+            'config': {'workload': WORKLOAD, 'batch_per_gpu': BATCH, 'patch': PATCH, 'smoothing': 'balanced',
+                       'weights': 'random-init seed 0', 'cuda_graph': graph is not None,
+                       'l2': 'flushed between timed steps (256 MiB write)', 'patches_per_s':
+                           world * BATCH * args.steps / (dev_ms * 1e-3),
+                       'model_tflops': world * BATCH * FLOP_PER_PATCH * args.steps / (dev_ms * 1e-3) / 1e12},
+            'clocks': clocks,
+            'e2e': {'value': world * out_mpix * args.steps / (e2e_ms * 1e-3), 'unit': UNIT,
+                    'h2d_bytes_per_step': x_host.numel() * 4, 'd2h_bytes_per_step': y_host.numel() * 4},
+            'gpu_launches': launches * args.steps,
+            'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s',
+                         'frac': achieved / peak_tf, 'traffic': None, 'peak_source': peak_src,
+                         'kernel': 'conv_tc_kernel (tcgen05 implicit GEMM, 3x3 + 1x1)', 'launches_per_step': tc_n,
+                         'kernel_ms_per_step': tc_ms, 'share_of_step': tc_ms / total_prof_ms if total_prof_ms else None,
+                         'by_class_ms': {k: round(v[0], 4) for k, v in prof.items()}},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, ms, cores, sample = cpu_oracle_throughput(2, 1)
+            line['cpu_baseline'] = {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='srb', choices=['srb', 'reference'])
+    ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == '__main__':
+    main()

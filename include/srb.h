@@ -57,6 +57,13 @@ int srb_pack_weights(const void* const* params, int n, void* packed, size_t pack
 size_t srb_workspace_bytes(int B, int H, int W);
 int srb_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                 void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream);
+/* Profiling variant (bench only): same work, but every launch is bracketed by CUDA events on `stream`; the call
+ * synchronises the stream and returns per-class totals.  Classes: 0 conv3x3 (tcgen05), 1 linear (tcgen05),
+ * 2 attention, 3 layernorm, 4 other.  class_flops = algorithmic FLOPs (2*MACs) of the launches in the class. */
+#define SRB_PROF_CLASSES 5
+int srb_forward_profile(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
+                        void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream,
+                        double* class_ms, double* class_flops, int* class_launches);
 /* number of kernels one srb_forward enqueues for this geometry (for bench "gpu_launches") */
 int srb_forward_launch_count(int B, int H, int W, int smoothing, int stage_mask);
 
@@ -71,6 +78,27 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
                        int pixel_shuffle, void* stream);
 /* fp32 [Cout,Cin,kh,kw] (PyTorch) -> bf16 [kh*kw][Cout][Cin] */
 int srb_pack_conv_weight(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream);
+
+/* ---- loss / metrics / normalisation / stitching --------------------------------------------------------------
+ * srb_weighted_l1   replaces CombinedLoss.forward (src/losses.py:9-21): loss[0] = mean(|p-t| * (t>0.02 ? 500 : 1)).
+ *                   grad (optional, may be NULL) = dLoss/dpred = sign(p-t)*w/n.  scratch: srb_loss_scratch_bytes().
+ * srb_psnr_ssim     replaces Metrics.update / ssim_torch (src/metrics.py:5-32) for fp32 [B,1,H,W] pairs:
+ *                   out2[0] = sum_b 10*log10(1/(mse_b+1e-8)) after clamp[0,1];  out2[1] = SSIM batch mean * B.
+ * srb_log_normalize_u16 replaces the per-pixel transform of scripts/Dataset_step4_normalization.py:161-179:
+ *                   u16(clip((log1p(max(nan_to_num(x),0)) - gmin)/denom, 0, 1)*65535), denom = f32(gmax-gmin+1e-8).
+ * srb_blend_tiles / srb_blend_finalize: halo-blend stitch of tile outputs into rows [row0,row1) of a frame
+ *                   (whole-field tiled inference; no reference counterpart: Modello_5 iterates patches).
+ *                   acc/wsum: fp32 [(row1-row0) x FW], zeroed by the caller.  oy/ox: device int32 tile origins. */
+size_t srb_loss_scratch_bytes(void);
+int srb_weighted_l1(const float* pred, const float* target, size_t n, float* loss, float* grad, void* scratch,
+                    void* stream);
+size_t srb_psnr_ssim_scratch_bytes(int B, int H, int W);
+int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, void* scratch,
+                  void* stream);
+int srb_log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, void* stream);
+int srb_blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int overlap, float* acc,
+                    float* wsum, int FH, int FW, int row0, int row1, void* stream);
+int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, void* stream);
 
 #ifdef __cplusplus
 }

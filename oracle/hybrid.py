@@ -10,6 +10,7 @@ from .rrdbnet import RRDBNet
 from .hat import HAT
 
 _BINOMIAL = {3: [1, 2, 1], 5: [1, 4, 6, 4, 1], 7: [1, 6, 15, 20, 15, 6, 1]}
+_DIVISOR = {3: 16.0, 5: 256.0, 7: 1600.0}  # the reference's literal divisors (7x7 sums to 2.56, :13)
 
 
 class AntiCheckerboardLayer(nn.Module):
@@ -20,7 +21,7 @@ class AntiCheckerboardLayer(nn.Module):
         k = 7 if mode == 'strong' else 5 if mode == 'balanced' else 3
         row = torch.tensor(_BINOMIAL[k], dtype=torch.float32)
         # the reference divides the integer outer product by 1600 / 256 / 16
-        kernel = torch.outer(row, row) / float(row.sum() ** 2)
+        kernel = torch.outer(row, row) / _DIVISOR[k]
         self.register_buffer('weight', kernel.unsqueeze(0).unsqueeze(0))
         self.padding = k // 2
 

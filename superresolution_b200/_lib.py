@@ -24,7 +24,15 @@ _PROTOS = {
     'srb_pack_weights': (_i, [_vp, _i, _vp, _sz, _vp]),
     'srb_workspace_bytes': (_sz, [_i, _i, _i]),
     'srb_forward': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _sz, _i, _i, _vp]),
+    'srb_forward_profile': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _sz, _i, _i, _vp, _vp, _vp, _vp]),
     'srb_forward_launch_count': (_i, [_i, _i, _i, _i, _i]),
+    'srb_loss_scratch_bytes': (_sz, []),
+    'srb_weighted_l1': (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
+    'srb_psnr_ssim_scratch_bytes': (_sz, [_i, _i, _i]),
+    'srb_psnr_ssim': (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    'srb_log_normalize_u16': (_i, [_vp, _vp, _sz, _f, _f, _vp]),
+    'srb_blend_tiles': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _vp]),
+    'srb_blend_finalize': (_i, [_vp, _vp, _vp, _i, _sz, _vp]),
     'srb_conv_nhwc_bf16': (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _i, _i,
                                 _f, _vp, _i, _i, _vp, _i, _vp]),
 }

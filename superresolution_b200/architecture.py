@@ -14,6 +14,7 @@ import torch.nn as nn
 from . import _lib as L
 
 _BINOMIAL = {3: [1, 2, 1], 5: [1, 4, 6, 4, 1], 7: [1, 6, 15, 20, 15, 6, 1]}
+_DIVISOR = {3: 16.0, 5: 256.0, 7: 1600.0}  # the reference's literal divisors (7x7 sums to 2.56, :13)
 
 
 def _conv(cin, cout, k=3):
@@ -212,7 +213,7 @@ class AntiCheckerboardLayer(nn.Module):
         k = 7 if mode == 'strong' else 5 if mode == 'balanced' else 3
         self.mode = 'strong' if k == 7 else 'balanced' if k == 5 else 'light'
         row = torch.tensor(_BINOMIAL[k], dtype=torch.float32)
-        self.register_buffer('weight', (torch.outer(row, row) / float(row.sum() ** 2)).unsqueeze(0).unsqueeze(0))
+        self.register_buffer('weight', (torch.outer(row, row) / _DIVISOR[k]).unsqueeze(0).unsqueeze(0))
         self.padding = k // 2
 
     forward = _no_direct_forward
@@ -315,6 +316,29 @@ class HybridSuperResolutionModel(nn.Module):
             L.check(lib.srb_forward(L.ptr(x), xd, L.ptr(y), yd, B, H, W, L.ptr(packed), L.ptr(ws), ws.numel(),
                                     self._smoothing, stage_mask, L.current_stream()), 'forward')
         return y
+
+    PROFILE_CLASSES = ('conv3x3_tcgen05', 'linear_tcgen05', 'attention', 'layernorm', 'other')
+
+    def profile(self, x, stage_mask=3):
+        """bench helper: one forward with every launch bracketed by CUDA events on the launching stream.
+        Returns {class: (ms, algorithmic_flops, launches)}; synchronises."""
+        lib = L.lib()
+        x = x.float().contiguous()
+        B, _, H, W = x.shape
+        scale = 4 if stage_mask == 3 else 2
+        n = len(self.PROFILE_CLASSES)
+        ms, fl, cnt = (C.c_double * n)(), (C.c_double * n)(), (C.c_int * n)()
+        with torch.cuda.device(x.device):
+            packed = self.pack_weights()
+            ws = self._workspace(B, H, W, x.device)
+            y = torch.empty(B, 1, scale * H, scale * W, dtype=torch.float32, device=x.device)
+            L.check(lib.srb_forward_profile(L.ptr(x), L.SRB_F32, L.ptr(y), L.SRB_F32, B, H, W, L.ptr(packed),
+                                            L.ptr(ws), ws.numel(), self._smoothing, stage_mask, L.current_stream(),
+                                            ms, fl, cnt), 'forward_profile')
+        return {k: (ms[i], fl[i], cnt[i]) for i, k in enumerate(self.PROFILE_CLASSES)}
+
+    def launch_count(self, B, H, W, stage_mask=3):
+        return L.lib().srb_forward_launch_count(B, H, W, self._smoothing, stage_mask)
 
     def forward(self, x):
         y = self.run(x, 3)

@@ -94,11 +94,45 @@ int srb_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, 
     return model_forward(x, x_dtype, y, y_dtype, B, H, W, packed, workspace, workspace_bytes, smoothing, stage_mask,
                          (cudaStream_t)stream, false, nullptr);
 }
+int srb_forward_profile(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
+                        void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream,
+                        double* class_ms, double* class_flops, int* class_launches) {
+    if (!class_ms || !class_flops || !class_launches) { set_error("forward_profile: null output"); return SRB_E_ARG; }
+    return model_forward(x, x_dtype, y, y_dtype, B, H, W, packed, workspace, workspace_bytes, smoothing, stage_mask,
+                         (cudaStream_t)stream, false, nullptr, class_ms, class_flops, class_launches);
+}
 int srb_forward_launch_count(int B, int H, int W, int smoothing, int stage_mask) {
     int n = 0;
     int rc = model_forward(nullptr, SRB_F32, nullptr, SRB_F32, B, H, W, nullptr, nullptr, 0, smoothing, stage_mask, 0,
                            true, &n);
     return rc == SRB_OK ? n : rc;
+}
+
+size_t srb_loss_scratch_bytes(void) { return reduce_scratch_bytes(); }
+int srb_weighted_l1(const float* pred, const float* target, size_t n, float* loss, float* grad, void* scratch,
+                    void* stream) {
+    if (!pred || !target || !loss || !scratch || n == 0) { set_error("weighted_l1: bad args"); return SRB_E_ARG; }
+    return weighted_l1(pred, target, n, loss, grad, (float*)scratch, (cudaStream_t)stream);
+}
+size_t srb_psnr_ssim_scratch_bytes(int B, int H, int W) { return psnr_ssim_scratch_bytes(B, H, W); }
+int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, void* scratch,
+                  void* stream) {
+    if (!pred || !target || !out2 || !scratch || B <= 0) { set_error("psnr_ssim: bad args"); return SRB_E_ARG; }
+    return psnr_ssim(pred, target, B, H, W, out2, (float*)scratch, (cudaStream_t)stream);
+}
+int srb_log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, void* stream) {
+    if (n == 0) return SRB_OK;  // empty input is legal (reference: empty array in, empty array out)
+    if (!x || !out) { set_error("log_normalize: null pointer"); return SRB_E_ARG; }
+    return log_normalize_u16(x, out, n, gmin, denom, (cudaStream_t)stream);
+}
+int srb_blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int overlap, float* acc,
+                    float* wsum, int FH, int FW, int row0, int row1, void* stream) {
+    if (!tiles || !oy || !ox || !acc || !wsum || T <= 0) { set_error("blend_tiles: bad args"); return SRB_E_ARG; }
+    return blend_tiles(tiles, oy, ox, T, th, tw, overlap, acc, wsum, FH, FW, row0, row1, (cudaStream_t)stream);
+}
+int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, void* stream) {
+    if (!acc || !wsum || !out) { set_error("blend_finalize: null pointer"); return SRB_E_ARG; }
+    return blend_finalize(acc, wsum, out, out_dtype, n, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -247,7 +247,15 @@ size_t model_workspace_bytes(int B, int H, int W) {
 // ------------------------------------------------------------------------------------------------------------------
 // forward schedule
 // ------------------------------------------------------------------------------------------------------------------
+enum ProfClass { PC_CONV3 = 0, PC_LINEAR = 1, PC_ATTN = 2, PC_LN = 3, PC_OTHER = 4, PC_COUNT = 5 };
+struct ProfRec {
+    int cls;
+    double flops;
+    cudaEvent_t e0, e1;
+};
+
 struct Ctx {
+    std::vector<ProfRec>* prof = nullptr;  // per-launch CUDA events on the launching stream (profile mode only)
     const ModelDesc* m;
     const uint8_t* packed;
     cudaStream_t s;
@@ -257,6 +265,20 @@ struct Ctx {
     const float* F(const std::string& name) const { return (const float*)P(name); }
     const bf16* Wt(const std::string& name) const { return (const bf16*)P(name); }
 };
+
+static void prof_begin(Ctx& c, int cls, double flops) {
+    if (!c.prof || c.dry) return;
+    ProfRec r;
+    r.cls = cls; r.flops = flops;
+    cudaEventCreate(&r.e0);
+    cudaEventCreate(&r.e1);
+    cudaEventRecord(r.e0, c.s);
+    c.prof->push_back(r);
+}
+static void prof_end(Ctx& c) {
+    if (!c.prof || c.dry) return;
+    cudaEventRecord(c.prof->back().e1, c.s);
+}
 
 // one tensor-core conv / linear layer named by its state-dict prefix
 static int tc_layer(Ctx& c, const std::string& name, const bf16* in, int in_pitch, int B, int H, int W, int act,
@@ -278,19 +300,27 @@ static int tc_layer(Ctx& c, const std::string& name, const bf16* in, int in_pitc
     a.alpha2 = alpha2; a.res2 = res2; a.res2_f32 = res2_f32; a.res2_pitch = res2_pitch; a.res2_cs = res2_cs;
     a.out = out; a.out_pitch = out_pitch; a.out32 = out32; a.out32_pitch = 64;
     a.pixel_shuffle = pixel_shuffle;
-    return conv_tc_launch(a, c.s);
+    prof_begin(c, p.taps == 9 ? PC_CONV3 : PC_LINEAR, 2.0 * B * H * W * (double)p.cout * p.cin * p.taps);
+    const int rc = conv_tc_launch(a, c.s);
+    prof_end(c);
+    return rc;
 }
 
-#define LAUNCH(c, expr)             \
-    do {                            \
-        ++(c).launches;             \
-        if (!(c).dry) SRB_TRY(expr); \
+#define LAUNCH(c, cls, flops, expr)     \
+    do {                                \
+        ++(c).launches;                 \
+        if (!(c).dry) {                 \
+            prof_begin(c, cls, flops);  \
+            const int rc__ = (expr);    \
+            prof_end(c);                \
+            if (rc__ != SRB_OK) return rc__; \
+        }                               \
     } while (0)
 
 // RRDBNet.forward (App. A.1): x [B,1,H,W] -> s1a fp32 [B,2H,2W]
 static int run_stage1(Ctx& c, Workspace& w, const void* x, int x_dtype, int B, int H, int W) {
     const int h = H / 2, ww = W / 2;
-    LAUNCH(c, rrdb_conv_first(x, x_dtype, c.F("stage1.conv_first.weight"), c.F("stage1.conv_first.bias"), w.cb[0], 192,
+    LAUNCH(c, PC_OTHER, 0.0, rrdb_conv_first(x, x_dtype, c.F("stage1.conv_first.weight"), c.F("stage1.conv_first.bias"), w.cb[0], 192,
                               w.t[0], w.f0, B, h, ww, c.s));
     int cur = 0;
     char buf[96];
@@ -316,19 +346,19 @@ static int run_stage1(Ctx& c, Workspace& w, const void* x, int x_dtype, int B, i
     }
     // feat = feat + conv_body(body(feat))
     SRB_TRY(tc_layer(c, "stage1.conv_body", w.cb[cur], 192, B, h, ww, ACT_NONE, 0.f, w.fe, 64, nullptr, 1.f, w.f0, 1, 64));
-    LAUNCH(c, upsample2x(w.fe, 64, w.u1, B, h, ww, c.s));
+    LAUNCH(c, PC_OTHER, 0.0, upsample2x(w.fe, 64, w.u1, B, h, ww, c.s));
     SRB_TRY(tc_layer(c, "stage1.conv_up1", w.u1, 64, B, H, W, ACT_LRELU, 0.2f, w.v1, 64));
-    LAUNCH(c, upsample2x(w.v1, 64, w.u2, B, H, W, c.s));
+    LAUNCH(c, PC_OTHER, 0.0, upsample2x(w.v1, 64, w.u2, B, H, W, c.s));
     SRB_TRY(tc_layer(c, "stage1.conv_up2", w.u2, 64, B, 2 * H, 2 * W, ACT_LRELU, 0.2f, w.v2, 64));
     SRB_TRY(tc_layer(c, "stage1.conv_hr", w.v2, 64, B, 2 * H, 2 * W, ACT_LRELU, 0.2f, w.v3, 64));
-    LAUNCH(c, conv_cout1(w.v3, 64, c.F("stage1.conv_last.weight"), c.F("stage1.conv_last.bias"), w.s1a, B, 2 * H, 2 * W, c.s));
+    LAUNCH(c, PC_OTHER, 0.0, conv_cout1(w.v3, 64, c.F("stage1.conv_last.weight"), c.F("stage1.conv_last.bias"), w.s1a, B, 2 * H, 2 * W, c.s));
     return SRB_OK;
 }
 
 // token-wise MLP shared by HAB and OCAB: x += fc2(gelu(fc1(LN(x))))  (in place on x)
 static int run_mlp(Ctx& c, Workspace& w, const std::string& b, int B, int R, int Rw) {
     const size_t ntok = (size_t)B * R * Rw;
-    LAUNCH(c, layernorm96(w.y, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), w.xn, ntok, c.s));
+    LAUNCH(c, PC_LN, 0.0, layernorm96(w.y, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), w.xn, ntok, c.s));
     SRB_TRY(tc_layer(c, b + "mlp.fc1", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.hd, 192));
     SRB_TRY(tc_layer(c, b + "mlp.fc2", w.hd, 192, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
     return SRB_OK;
@@ -338,7 +368,7 @@ static int run_mlp(Ctx& c, Workspace& w, const std::string& b, int B, int R, int
 static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int Rw) {
     const size_t ntok = (size_t)B * R * Rw;
     const uint8_t* pk = c.packed;
-    LAUNCH(c, hat_conv_first_ln(img, c.F("stage2.conv_first.weight"), c.F("stage2.conv_first.bias"),
+    LAUNCH(c, PC_OTHER, 0.0, hat_conv_first_ln(img, c.F("stage2.conv_first.weight"), c.F("stage2.conv_first.bias"),
                                 c.F("stage2.patch_embed.norm.weight"), c.F("stage2.patch_embed.norm.bias"), w.f0h, w.g,
                                 B, R, Rw, c.s));
     char buf[128];
@@ -347,15 +377,15 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
             snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.", l, j);
             const std::string b = buf;
             const bf16* xin = (j == 0) ? w.g : w.y;  // token stream entering this block (= shortcut)
-            LAUNCH(c, layernorm96(xin, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
+            LAUNCH(c, PC_LN, 0.0, layernorm96(xin, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
             SRB_TRY(tc_layer(c, b + "attn.qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
-            LAUNCH(c, window_attention(w.qkv, (const float*)(pk + c.m->bias_sa_off[l * 6 + j]), w.ao, B, R, Rw,
+            LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 64 * 16 * 6 * ((double)B * R * Rw / 64), window_attention(w.qkv, (const float*)(pk + c.m->bias_sa_off[l * 6 + j]), w.ao, B, R, Rw,
                                        (j & 1) ? 4 : 0, c.s));
             // CAB on the normalised tensor: conv 96->32, GELU, conv 32->96, channel attention
             SRB_TRY(tc_layer(c, b + "conv_block.cab.0", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.c1, 32));
             SRB_TRY(tc_layer(c, b + "conv_block.cab.2", w.c1, 32, B, R, Rw, ACT_NONE, 0.f, w.c2, 96));
             c.launches += 2;  // memset + partial sums (counted with the finisher below)
-            LAUNCH(c, cab_channel_attention(w.c2, w.pool, w.cs, c.F(b + "conv_block.cab.3.attention.1.weight"),
+            LAUNCH(c, PC_OTHER, 0.0, cab_channel_attention(w.c2, w.pool, w.cs, c.F(b + "conv_block.cab.3.attention.1.weight"),
                                             c.F(b + "conv_block.cab.3.attention.1.bias"),
                                             c.F(b + "conv_block.cab.3.attention.3.weight"),
                                             c.F(b + "conv_block.cab.3.attention.3.bias"), 0.01f, B, R * Rw, c.s));
@@ -366,21 +396,21 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", l);
         const std::string b = buf;
-        LAUNCH(c, layernorm96(w.y, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
+        LAUNCH(c, PC_LN, 0.0, layernorm96(w.y, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
         SRB_TRY(tc_layer(c, b + "qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
-        LAUNCH(c, ocab_attention(w.qkv, (const float*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
+        LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const float*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
         SRB_TRY(tc_layer(c, b + "proj", w.ao, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
         SRB_TRY(run_mlp(c, w, b, B, R, Rw));
         // RHAG tail: g = conv(y) + g
         snprintf(buf, sizeof(buf), "stage2.layers.%d.conv", l);
         SRB_TRY(tc_layer(c, buf, w.y, 96, B, R, Rw, ACT_NONE, 0.f, w.g, 96, nullptr, 1.f, w.g, 0, 96));
     }
-    LAUNCH(c, layernorm96(w.g, c.F("stage2.norm.weight"), c.F("stage2.norm.bias"), w.xn, ntok, c.s));
+    LAUNCH(c, PC_LN, 0.0, layernorm96(w.g, c.F("stage2.norm.weight"), c.F("stage2.norm.bias"), w.xn, ntok, c.s));
     SRB_TRY(tc_layer(c, "stage2.conv_after_body", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.f0h, 0, 96));
     SRB_TRY(tc_layer(c, "stage2.conv_before_upsample.0", w.y, 96, B, R, Rw, ACT_LRELU, 0.01f, w.d1, 64));
     SRB_TRY(tc_layer(c, "stage2.upsample.0", w.d1, 64, B, R, Rw, ACT_NONE, 0.f, w.d2, 64, nullptr, 1.f, nullptr, 0, 0, 1.f,
                      nullptr, 0, 0, nullptr, 1));
-    LAUNCH(c, conv_cout1(w.d2, 64, c.F("stage2.conv_last.weight"), c.F("stage2.conv_last.bias"), w.o1, B, 2 * R, 2 * Rw, c.s));
+    LAUNCH(c, PC_OTHER, 0.0, conv_cout1(w.d2, 64, c.F("stage2.conv_last.weight"), c.F("stage2.conv_last.bias"), w.o1, B, 2 * R, 2 * Rw, c.s));
     return SRB_OK;
 }
 
@@ -392,35 +422,35 @@ static int run_forward(Ctx& c, const void* x, int x_dtype, void* y, int y_dtype,
     else carve(w, (uint8_t*)workspace, B, H, W);
     if (stage_mask == 1) {  // RRDBNet only: y = stage-1 image [B,1,2H,2W]
         SRB_TRY(run_stage1(c, w, x, x_dtype, B, H, W));
-        LAUNCH(c, convert_out(w.s1a, y, y_dtype, (size_t)B * 4 * H * W, c.s));
+        LAUNCH(c, PC_OTHER, 0.0, convert_out(w.s1a, y, y_dtype, (size_t)B * 4 * H * W, c.s));
         return SRB_OK;
     }
     if (stage_mask == 2) {  // HAT only: x fp32 [B,1,H,W] -> y [B,1,2H,2W]
         if (x_dtype != SRB_F32) { set_error("forward(stage 2 only) needs fp32 input"); return SRB_E_DTYPE; }
         SRB_TRY(run_stage2(c, w, (const float*)x, B, H, W));
-        LAUNCH(c, convert_out(w.o1, y, y_dtype, (size_t)B * 4 * H * W, c.s));
+        LAUNCH(c, PC_OTHER, 0.0, convert_out(w.o1, y, y_dtype, (size_t)B * 4 * H * W, c.s));
         return SRB_OK;
     }
     SRB_TRY(run_stage1(c, w, x, x_dtype, B, H, W));
     const float* img = w.s1a;
     if (smoothing != SRB_SMOOTH_NONE) {
-        LAUNCH(c, blur(w.s1a, w.s1b, SRB_F32, smoothing, B, 2 * H, 2 * W, c.s));
+        LAUNCH(c, PC_OTHER, 0.0, blur(w.s1a, w.s1b, SRB_F32, smoothing, B, 2 * H, 2 * W, c.s));
         img = w.s1b;
     }
     SRB_TRY(run_stage2(c, w, img, B, 2 * H, 2 * W));
     const size_t nout = (size_t)B * 16 * H * W;
     if (smoothing != SRB_SMOOTH_NONE) {
-        LAUNCH(c, blur(w.o1, w.o2, SRB_F32, smoothing, B, 4 * H, 4 * W, c.s));
-        LAUNCH(c, blur(w.o2, y, y_dtype, SRB_SMOOTH_LIGHT, B, 4 * H, 4 * W, c.s));
+        LAUNCH(c, PC_OTHER, 0.0, blur(w.o1, w.o2, SRB_F32, smoothing, B, 4 * H, 4 * W, c.s));
+        LAUNCH(c, PC_OTHER, 0.0, blur(w.o2, y, y_dtype, SRB_SMOOTH_LIGHT, B, 4 * H, 4 * W, c.s));
     } else {
-        LAUNCH(c, convert_out(w.o1, y, y_dtype, nout, c.s));
+        LAUNCH(c, PC_OTHER, 0.0, convert_out(w.o1, y, y_dtype, nout, c.s));
     }
     return SRB_OK;
 }
 
 int model_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                   void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, cudaStream_t s, bool dry,
-                  int* launches) {
+                  int* launches, double* prof_ms, double* prof_flops, int* prof_counts) {
     if (stage_mask < 1 || stage_mask > 3) { set_error("forward: stage_mask must be 1, 2 or 3"); return SRB_E_ARG; }
     if (smoothing < 0 || smoothing > 3) { set_error("forward: bad smoothing mode %d", smoothing); return SRB_E_ARG; }
     if (y_dtype != SRB_F32 && y_dtype != SRB_U16) { set_error("forward: y dtype must be F32 or U16"); return SRB_E_DTYPE; }
@@ -433,8 +463,24 @@ int model_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H
     }
     Ctx c;
     c.m = &desc(); c.packed = (const uint8_t*)packed; c.s = s; c.dry = dry; c.launches = 0;
+    std::vector<ProfRec> recs;
+    if (prof_ms && !dry) c.prof = &recs;
     int rc = run_forward(c, x, x_dtype, y, y_dtype, B, H, W, workspace, smoothing, stage_mask);
     if (launches) *launches = c.launches;
+    if (c.prof) {
+        // profile mode only: wait for the stream, then fold the per-launch event times into per-class totals
+        for (int i = 0; i < PC_COUNT; ++i) { prof_ms[i] = 0; prof_flops[i] = 0; prof_counts[i] = 0; }
+        cudaError_t e = cudaStreamSynchronize(s);
+        for (ProfRec& r : recs) {
+            float ms = 0.f;
+            if (e == cudaSuccess && cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+                prof_ms[r.cls] += ms; prof_flops[r.cls] += r.flops; prof_counts[r.cls] += 1;
+            }
+            cudaEventDestroy(r.e0);
+            cudaEventDestroy(r.e1);
+        }
+        if (e != cudaSuccess && rc == SRB_OK) rc = cuda_fail(e, "cudaStreamSynchronize(profile)");
+    }
     return rc;
 }
 

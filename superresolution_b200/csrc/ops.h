@@ -33,6 +33,20 @@ int ocab_attention(const bf16* qkv, const float* bias, bf16* out, int B, int H, 
 // table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> bias fp32 [6][64][NK]
 int expand_rel_bias(const float* table, int T, const int64_t* index, int NK, float* bias, cudaStream_t s);
 
+// metrics.cu
+size_t reduce_scratch_bytes();
+int weighted_l1(const float* pred, const float* target, size_t n, float* loss, float* grad, float* scratch,
+                cudaStream_t s);
+size_t psnr_ssim_scratch_bytes(int B, int H, int W);
+int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, float* scratch,
+              cudaStream_t s);
+int log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, cudaStream_t s);
+
+// blend.cu
+int blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int ov, float* acc,
+                float* wsum, int FH, int FW, int row0, int row1, cudaStream_t s);
+int blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, cudaStream_t s);
+
 // forward.cu
 int model_param_count();
 const char* model_param_name(int i);
@@ -42,6 +56,6 @@ int model_pack(const void* const* params, int n, void* packed, size_t packed_byt
 size_t model_workspace_bytes(int B, int H, int W);
 int model_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                   void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, cudaStream_t s, bool dry,
-                  int* launches);
+                  int* launches, double* prof_ms = nullptr, double* prof_flops = nullptr, int* prof_counts = nullptr);
 
 }  // namespace srb

@@ -1,0 +1,70 @@
+"""Host logic of tiled whole-field inference: tile plan coverage, band sharding, and the N>1 path on CPU with a
+world_size-2 gloo group (each rank blends its band with the oracle blend; the gathered frame equals the 1-rank one)."""
+import os
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def test_plan_covers_frame():
+    from superresolution_b200 import tiling
+    from oracle import tiling as otil
+    for size, tile, stride in ((4096, 128, 96), (160, 32, 24), (128, 128, 96), (100, 32, 32)):
+        xs = tiling.tile_origins(size, tile, stride)
+        assert xs == otil.tile_origins(size, tile, stride)
+        cov = np.zeros(size, bool)
+        for x in xs:
+            assert 0 <= x and x + tile <= max(size, tile)
+            cov[x:x + tile] = True
+        assert cov.all()
+    assert len(tiling.plan(4096, 4096)) == 43 * 43  # BASELINE config 3 / SURVEY.md §8d
+
+
+def test_bands_partition_rows():
+    from superresolution_b200 import tiling
+    for world in (1, 2, 3, 8):
+        rows = [tiling.band(r, world, 16384) for r in range(world)]
+        assert rows[0][0] == 0 and rows[-1][1] == 16384
+        assert all(rows[i][1] == rows[i + 1][0] for i in range(world - 1))
+
+
+def _worker(rank, world, port, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from superresolution_b200 import tiling
+    from oracle import tiling as otil
+    H = W = 80
+    tile, stride, scale = 32, 24, 4
+    rng = np.random.default_rng(0)
+    origins = tiling.plan(H, W, tile, stride)
+    outs = [rng.random((scale * tile, scale * tile), dtype=np.float32) for _ in origins]  # stand-in tile outputs
+    FH = FW = scale * H
+    r0, r1 = tiling.band(rank, world, FH)
+    mine = [(o, t) for o, t in zip(origins, outs) if scale * o[0] < r1 and scale * o[0] + scale * tile > r0]
+    full = otil.blend([t for _, t in mine], [(scale * o[0], scale * o[1]) for o, _ in mine], FH, FW,
+                      scale * (tile - stride))
+    band = torch.from_numpy(full[r0:r1].copy())
+    gathered = [torch.empty(tiling.band(r, world, FH)[1] - tiling.band(r, world, FH)[0], FW) for r in range(world)]
+    dist.all_gather(gathered, band) if len({g.shape for g in gathered}) == 1 else None
+    if rank == 0:
+        ref = otil.blend(outs, [(scale * o[0], scale * o[1]) for o in origins], FH, FW, scale * (tile - stride))
+        q.put(float(np.abs(torch.cat(gathered).numpy() - ref).max()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_band_sharding_matches_single_rank():
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    err = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert err < 1e-6
