@@ -10,15 +10,23 @@
 //    consecutive pixels (one 8-pixel row segment per group) with stride-byte-offset = patch row pitch, and the tap
 //    shift is a 128-byte-granular start-address offset (validated on B200, profiles/r01_umma_probe.log).
 //    L2->SMEM activation traffic is therefore ~1.2x the tensor instead of 9x.
-//  * Weights stream per (chunk, tap) as [N_TILE x 64] K-major tiles through their own TMA ring.
+//  * Weights: 3x3 -> [N_TILE x 64] K-major tiles per (chunk, tap) through a 4-deep TMA ring; 1x1 (linears) -> all
+//    tiles resident in shared memory for the whole kernel.  When Cout spans several N tiles the patch stays resident
+//    across them (activations are read from L2 once per layer).
 //  * Accumulators live in TMEM (MT tiles x N_TILE fp32 columns, double buffered when they fit) so the epilogue of
-//    tile i overlaps the MMAs of tile i+1.  Persistent CTAs, warp-specialised:
-//      warp 0 patch TMA | warp 1 MMA issue | warp 2 weight TMA | warp 3 TMEM alloc | warps 4-7 epilogue.
-//  * Epilogue (TMEM -> registers): bias, LeakyReLU / exact GELU, two scaled residuals (fp32 or bf16), bf16 and/or
-//    fp32 stores into a channel slice of a wider NHWC buffer (dense-block concat is free), optional PixelShuffle(2).
+//    tile i overlaps the MMAs of tile i+1.  Persistent CTAs, warp-specialised (384 threads):
+//      warp 0 patch TMA | warp 1 MMA issue | warp 2 weight TMA | warp 3 TMEM alloc | warps 4-11 epilogue (2 groups
+//      of 4 warps, each group covering the 128 TMEM lanes and taking every other 128x32 accumulator block).
+//  * Epilogue (TMEM -> registers): bias, LeakyReLU / exact GELU, two scaled residuals (fp32 or bf16), then bf16 tiles
+//    are staged in 64B-swizzled shared memory and written with TMA stores into a channel slice of a wider NHWC buffer
+//    (dense-block concat is free, stores are fully coalesced); fp32 trunk / PixelShuffle(2) outputs use direct stores.
+//  * Programmatic dependent launch: barrier init, TMEM allocation, tensor-map prefetch and the weight loads of layer
+//    i+1 overlap the tail of layer i (griddepcontrol.wait sits in front of the first activation access).
 #include <cuda.h>
-#include <mutex>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
 
 #include "common.h"
 #include "ptx.cuh"
@@ -34,256 +42,341 @@ struct ConvCfg {
     static constexpr int PATCH_BYTES = PH * PW * 128;
     static constexpr int PATCH_STRIDE = (PATCH_BYTES + 1023) / 1024 * 1024;
     static constexpr int W_BYTES = N_TILE * 128;
-    static constexpr int WS = 4;
-    static constexpr int PS_MAX = (200 * 1024 - WS * W_BYTES) / PATCH_STRIDE;
-    static constexpr int PS = PS_MAX >= 4 ? 4 : (PS_MAX >= 3 ? 3 : 2);
+    static constexpr int W_RING = 4;
     static constexpr int ACC_STAGES = (2 * MT * N_TILE <= 512) ? 2 : 1;
     static constexpr int ACC_COLS = ACC_STAGES * MT * N_TILE;
     static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128
                                      : ACC_COLS <= 256 ? 256 : 512;
-    static constexpr int SMEM_BYTES = PS * PATCH_STRIDE + WS * W_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int UNITS = MT * (N_TILE / 32);  // 128x32 accumulator blocks per tile
     static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
     static_assert(N_TILE % 32 == 0 && N_TILE >= 32 && N_TILE <= 256, "N_TILE");
     static_assert(W_BYTES % 1024 == 0, "weight tile must keep 1024B alignment");
-    static_assert(PS >= 2 && SMEM_BYTES <= 227 * 1024, "smem budget");
+    static_assert(UNITS % 2 == 0, "two epilogue groups split the units evenly");
 };
 
-struct ConvTiles {
-    int tiles_x, tiles_y, n_tiles_n, total, nchunks;
+constexpr int kThreads = 384;
+constexpr int kStageBytes = 8192;               // one 128 x 32 bf16 block, 64B-swizzled
+constexpr int kStagingBytes = 4 * kStageBytes;  // 2 epilogue groups x 2 buffers
+constexpr int kBarrierBytes = 512;
+constexpr int kSmemLimit = 227 * 1024;
+constexpr int kMaxPS = 4;
+
+struct ConvLaunch {
+    int tiles_x, tiles_y, n_tiles_n, n_spatial, nchunks;
+    int ps;         // patch ring stages
+    int wslots;     // weight slots (ring depth for 3x3, resident tile count for 1x1)
+    int reuse;      // patch chunks stay resident across the N tiles of one spatial tile
+    int tma_store;  // bf16 output through smem staging + TMA store
 };
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7, i.e. fp32-exact for a bf16 result): exact-GELU semantics of
+// nn.GELU() without the branchy erff().
+__device__ __forceinline__ float gelu_erf(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    const float e = 1.0f - p * t * __expf(-z * z);  // erf(|x|/sqrt2)
+    return 0.5f * x * (1.0f + copysignf(e, x));
+}
+
+// bias + activation + residuals on one 32-channel slice of one pixel (all indices compile-time after unrolling)
+__device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a, size_t pix, int cb, int b) {
+    if (a.bias) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            const float4 bb = __ldg((const float4*)(a.bias + cb + j));
+            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+        }
+    }
+    if (a.act == ACT_LRELU) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * a.slope;
+    } else if (a.act == ACT_GELU) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+    }
+    if (a.res1) {
+        if (a.res1_f32) {
+            const float4* rp = (const float4*)((const float*)a.res1 + pix * a.res1_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 rr = rp[j];
+                v[4 * j] = fmaf(v[4 * j], a.alpha1, rr.x);
+                v[4 * j + 1] = fmaf(v[4 * j + 1], a.alpha1, rr.y);
+                v[4 * j + 2] = fmaf(v[4 * j + 2], a.alpha1, rr.z);
+                v[4 * j + 3] = fmaf(v[4 * j + 3], a.alpha1, rr.w);
+            }
+        } else {
+            const uint4* rp = (const uint4*)((const bf16*)a.res1 + pix * a.res1_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 rr = rp[j];
+                const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h[k]);
+                    v[8 * j + 2 * k] = fmaf(v[8 * j + 2 * k], a.alpha1, f.x);
+                    v[8 * j + 2 * k + 1] = fmaf(v[8 * j + 2 * k + 1], a.alpha1, f.y);
+                }
+            }
+        }
+    }
+    if (a.res2) {
+        if (a.res2_f32) {
+            const float4* rp = (const float4*)((const float*)a.res2 + pix * a.res2_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 rr = rp[j];
+                float4 c4 = make_float4(1.f, 1.f, 1.f, 1.f);
+                if (a.res2_cs) c4 = __ldg((const float4*)(a.res2_cs + (size_t)b * a.Cout + cb + 4 * j));
+                v[4 * j] = fmaf(v[4 * j], a.alpha2, rr.x * c4.x);
+                v[4 * j + 1] = fmaf(v[4 * j + 1], a.alpha2, rr.y * c4.y);
+                v[4 * j + 2] = fmaf(v[4 * j + 2], a.alpha2, rr.z * c4.z);
+                v[4 * j + 3] = fmaf(v[4 * j + 3], a.alpha2, rr.w * c4.w);
+            }
+        } else {
+            const uint4* rp = (const uint4*)((const bf16*)a.res2 + pix * a.res2_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 rr = rp[j];
+                const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
+                float4 c0 = make_float4(1.f, 1.f, 1.f, 1.f), c1 = c0;
+                if (a.res2_cs) {
+                    c0 = __ldg((const float4*)(a.res2_cs + (size_t)b * a.Cout + cb + 8 * j));
+                    c1 = __ldg((const float4*)(a.res2_cs + (size_t)b * a.Cout + cb + 8 * j + 4));
+                }
+                const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h[k]);
+                    v[8 * j + 2 * k] = fmaf(v[8 * j + 2 * k], a.alpha2, f.x * cs[2 * k]);
+                    v[8 * j + 2 * k + 1] = fmaf(v[8 * j + 2 * k + 1], a.alpha2, f.y * cs[2 * k + 1]);
+                }
+            }
+        }
+    }
+}
 
 template <class Cfg>
-__global__ void __launch_bounds__(256, 1)
-conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const ConvArgs a,
-               const ConvTiles t) {
-    constexpr int N_TILE = Cfg::N_TILE, MT = Cfg::MT, TAPS = Cfg::TAPS;
-    constexpr int PS = Cfg::PS, WS = Cfg::WS, AS = Cfg::ACC_STAGES;
+__global__ void __launch_bounds__(kThreads, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+               const __grid_constant__ CUtensorMap tmO, const ConvArgs a, const ConvLaunch t) {
+    constexpr int N_TILE = Cfg::N_TILE, MT = Cfg::MT, TAPS = Cfg::TAPS, AS = Cfg::ACC_STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* patch0 = smem;
-    uint8_t* wt0 = smem + PS * Cfg::PATCH_STRIDE;
-    uint64_t* bars = (uint64_t*)(wt0 + WS * Cfg::W_BYTES);
-    uint64_t* full_p = bars;            // [PS]
-    uint64_t* empty_p = full_p + PS;    // [PS]
-    uint64_t* full_w = empty_p + PS;    // [WS]
-    uint64_t* empty_w = full_w + WS;    // [WS]
-    uint64_t* acc_full = empty_w + WS;  // [AS]
-    uint64_t* acc_empty = acc_full + AS;  // [AS]
-    uint32_t* tmem_slot = (uint32_t*)(acc_empty + AS);
+    uint8_t* wt0 = patch0 + t.ps * Cfg::PATCH_STRIDE;
+    uint8_t* stg0 = wt0 + t.wslots * Cfg::W_BYTES;
+    uint64_t* bars = (uint64_t*)(stg0 + kStagingBytes);
+    uint64_t* full_p = bars;                 // [kMaxPS]
+    uint64_t* empty_p = full_p + kMaxPS;     // [kMaxPS]
+    uint64_t* full_w = empty_p + kMaxPS;     // [W_RING]  (3x3: ring; 1x1: full_w[0] = all resident tiles landed)
+    uint64_t* empty_w = full_w + Cfg::W_RING;  // [W_RING]
+    uint64_t* acc_full = empty_w + Cfg::W_RING;  // [2]
+    uint64_t* acc_empty = acc_full + 2;          // [2]
+    uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < PS; ++i) { mbar_init(&full_p[i], 1); mbar_init(&empty_p[i], 1); }
-        for (int i = 0; i < WS; ++i) { mbar_init(&full_w[i], 1); mbar_init(&empty_w[i], 1); }
-        for (int i = 0; i < AS; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+        for (int i = 0; i < kMaxPS; ++i) { mbar_init(&full_p[i], 1); mbar_init(&empty_p[i], 1); }
+        for (int i = 0; i < Cfg::W_RING; ++i) { mbar_init(&full_w[i], 1); mbar_init(&empty_w[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 256); }
         fence_barrier_init();
     }
-    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW); }
+    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmO); }
     if (warp == 3) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) pdl_launch_dependents();  // the next layer may begin its own prologue
 
     const int per_img = t.tiles_x * t.tiles_y;
+    const int nreps = t.reuse ? 1 : t.n_tiles_n;  // patch (re)loads per spatial tile
 
     if (warp == 0) {
-        // ===================== patch TMA producer =====================
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < t.total; tile += gridDim.x) {
-                const int s = tile / t.n_tiles_n;
-                const int b = s / per_img, r = s % per_img;
-                const int ty = r / t.tiles_x, tx = r % t.tiles_x;
+        // ===================== patch TMA producer (warp-uniform control flow, one elected lane issues) ==========
+        pdl_wait();  // activations come from the previous kernel in the stream
+        uint32_t it = 0;
+        for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
+            const int b = st / per_img, r = st % per_img;
+            const int ty = r / t.tiles_x, tx = r % t.tiles_x;
+            for (int rep = 0; rep < nreps; ++rep) {
                 for (int ch = 0; ch < t.nchunks; ++ch, ++it) {
-                    const uint32_t st = it % PS;
-                    mbar_wait(&empty_p[st], ((it / PS) & 1) ^ 1);
-                    mbar_arrive_expect_tx(&full_p[st], Cfg::PATCH_BYTES);
-                    tma_load_4d(patch0 + st * Cfg::PATCH_STRIDE, &tmA, &full_p[st], ch * 64, tx * Cfg::TW - Cfg::HALO,
-                                ty * Cfg::TH - Cfg::HALO, b);
-                }
-            }
-        }
-        __syncwarp();
-    } else if (warp == 2) {
-        // ===================== weight TMA producer =====================
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < t.total; tile += gridDim.x) {
-                const int nt = tile % t.n_tiles_n;
-                for (int ch = 0; ch < t.nchunks; ++ch) {
-                    for (int tap = 0; tap < TAPS; ++tap, ++it) {
-                        const uint32_t st = it % WS;
-                        mbar_wait(&empty_w[st], ((it / WS) & 1) ^ 1);
-                        mbar_arrive_expect_tx(&full_w[st], Cfg::W_BYTES);
-                        tma_load_3d(wt0 + st * Cfg::W_BYTES, &tmW, &full_w[st], ch * 64, nt * N_TILE, tap);
+                    const uint32_t s = it % t.ps;
+                    mbar_wait(&empty_p[s], ((it / t.ps) & 1) ^ 1);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(&full_p[s], Cfg::PATCH_BYTES);
+                        tma_load_4d(patch0 + s * Cfg::PATCH_STRIDE, &tmA, &full_p[s], ch * 64,
+                                    tx * Cfg::TW - Cfg::HALO, ty * Cfg::TH - Cfg::HALO, b);
                     }
+                    __syncwarp();
                 }
             }
         }
-        __syncwarp();
+    } else if (warp == 2) {
+        // ===================== weight TMA producer (weights are constants: no dependency wait) =====================
+        if (TAPS == 1) {
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&full_w[0], (uint32_t)(t.wslots * Cfg::W_BYTES));
+                for (int nt = 0; nt < t.n_tiles_n; ++nt)
+                    for (int ch = 0; ch < t.nchunks; ++ch)
+                        tma_load_3d(wt0 + (nt * t.nchunks + ch) * Cfg::W_BYTES, &tmW, &full_w[0], ch * 64,
+                                    nt * N_TILE, 0);
+            }
+            __syncwarp();
+        } else {
+            uint32_t it = 0;
+            for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x)
+                for (int nt = 0; nt < t.n_tiles_n; ++nt)
+                    for (int ch = 0; ch < t.nchunks; ++ch)
+                        for (int tap = 0; tap < TAPS; ++tap, ++it) {
+                            const uint32_t s = it % Cfg::W_RING;
+                            mbar_wait(&empty_w[s], ((it / Cfg::W_RING) & 1) ^ 1);
+                            if (elect_one()) {
+                                mbar_arrive_expect_tx(&full_w[s], Cfg::W_BYTES);
+                                tma_load_3d(wt0 + s * Cfg::W_BYTES, &tmW, &full_w[s], ch * 64, nt * N_TILE, tap);
+                            }
+                            __syncwarp();
+                        }
+        }
     } else if (warp == 1) {
-        // ===================== MMA issuer (single thread) =====================
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16_f32(128, N_TILE);
-            const uint32_t p_u32 = smem_u32(patch0), w_u32 = smem_u32(wt0);
-            uint32_t it_p = 0, it_w = 0, it_a = 0;
-            for (int tile = blockIdx.x; tile < t.total; tile += gridDim.x, ++it_a) {
+        // ===================== MMA issuer: warp-uniform loops, one elected lane issues =====================
+        // Everything that feeds a descriptor is computed in uniform control flow so that it lives in uniform
+        // registers; an N=32 MMA is only 16-40 tensor cycles, so the issue path must be a handful of instructions.
+        const uint32_t idesc = umma_idesc_bf16_f32(128, N_TILE);
+        const uint32_t p_u32 = smem_u32(patch0), w_u32 = smem_u32(wt0);
+        uint32_t it_p = 0, it_w = 0, it_a = 0;
+        if (TAPS == 1) { mbar_wait(&full_w[0], 0); tc_fence_after(); }
+        for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
+            for (int nt = 0; nt < t.n_tiles_n; ++nt, ++it_a) {
                 const uint32_t as = it_a % AS;
                 mbar_wait(&acc_empty[as], ((it_a / AS) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t d_base = tmem_base + as * (MT * N_TILE);
-                for (int ch = 0; ch < t.nchunks; ++ch, ++it_p) {
-                    const uint32_t ps = it_p % PS;
-                    mbar_wait(&full_p[ps], (it_p / PS) & 1);
-                    const uint32_t pbase = p_u32 + ps * Cfg::PATCH_STRIDE;
-                    int kv = (a.Cin - ch * 64) / 16;
-                    kv = kv > 4 ? 4 : kv;
-                    for (int tap = 0; tap < TAPS; ++tap, ++it_w) {
-                        const uint32_t ws = it_w % WS;
-                        mbar_wait(&full_w[ws], (it_w / WS) & 1);
-                        tc_fence_after();
-                        const uint32_t wbase = w_u32 + ws * Cfg::W_BYTES;
-                        const uint32_t arow = (TAPS == 9) ? (uint32_t)((tap / 3) * Cfg::PW + (tap % 3)) : 0u;
+                for (int ch = 0; ch < t.nchunks; ++ch) {
+                    const uint32_t pi = it_p + ch;
+                    const uint32_t ps = pi % t.ps;
+                    mbar_wait(&full_p[ps], (pi / t.ps) & 1);  // immediate when the chunk is already resident
+                    tc_fence_after();
+                    const uint64_t ad0 = umma_smem_desc(p_u32 + ps * Cfg::PATCH_STRIDE, 16, Cfg::PW * 128, UMMA_SW_128B);
+                    const bool full_chunk = (a.Cin - ch * 64) >= 64;  // else 32 valid channels (2 k-steps)
+                    const uint32_t acc0 = (ch != 0);
+#pragma unroll
+                    for (int tap = 0; tap < TAPS; ++tap) {
+                        uint32_t wbase;
+                        uint32_t ws = 0;
+                        if (TAPS == 1) {
+                            wbase = w_u32 + (nt * t.nchunks + ch) * Cfg::W_BYTES;
+                        } else {
+                            ws = it_w % Cfg::W_RING;
+                            mbar_wait(&full_w[ws], (it_w / Cfg::W_RING) & 1);
+                            tc_fence_after();
+                            wbase = w_u32 + ws * Cfg::W_BYTES;
+                        }
+                        const uint64_t bd0 = umma_smem_desc(wbase, 16, 1024, UMMA_SW_128B);
+                        constexpr int kRowStep = 128 >> 4;  // one patch row in descriptor address units
+                        const int arow = (TAPS == 9) ? ((tap / 3) * Cfg::PW + (tap % 3)) : 0;
+                        const uint64_t ad_tap = ad0 + (uint64_t)(arow * kRowStep);
+                        const bool leader = elect_one();
 #pragma unroll
                         for (int mt = 0; mt < MT; ++mt) {
-                            for (int ks = 0; ks < kv; ++ks) {
-                                const uint64_t ad = umma_smem_desc(pbase + (arow + 8 * mt) * 128 + ks * 32, 16,
-                                                                   Cfg::PW * 128, UMMA_SW_128B);
-                                const uint64_t bd = umma_smem_desc(wbase + ks * 32, 16, 1024, UMMA_SW_128B);
-                                umma_bf16_ss(d_base + mt * N_TILE, ad, bd, idesc, (uint32_t)((ch | tap | ks) != 0));
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks) {
+                                if (leader && (ks < 2 || full_chunk))
+                                    umma_bf16_ss(d_base + mt * N_TILE, ad_tap + (uint64_t)(mt * 8 * kRowStep + ks * 2),
+                                                 bd0 + (uint64_t)(ks * 2), idesc, (tap == 0 && ks == 0) ? acc0 : 1u);
                             }
                         }
-                        umma_commit(&empty_w[ws]);
+                        if (TAPS != 1) {
+                            if (leader) umma_commit(&empty_w[ws]);
+                            ++it_w;
+                        }
+                        __syncwarp();
                     }
-                    umma_commit(&empty_p[ps]);
+                    if (!t.reuse || nt == t.n_tiles_n - 1) {
+                        if (elect_one()) umma_commit(&empty_p[ps]);
+                        __syncwarp();
+                    }
                 }
-                umma_commit(&acc_full[as]);
+                if (elect_one()) umma_commit(&acc_full[as]);
+                __syncwarp();
+                if (!t.reuse) it_p += t.nchunks;
             }
+            if (t.reuse) it_p += t.nchunks;
         }
-        __syncwarp();
     } else if (warp >= 4) {
-        // ===================== epilogue (4 warps, one TMEM lane quarter each) =====================
+        // ===================== epilogue: 2 groups x 4 warps, each group = all 128 TMEM lanes =====================
+        pdl_wait();  // residual reads / output writes must not overtake the previous kernel
+        const int eg = (warp - 4) >> 2;
         const int q = warp & 3;
         const int row = q * 32 + lane;  // M row inside the 128-row UMMA tile
-        uint32_t it_a = 0;
-        for (int tile = blockIdx.x; tile < t.total; tile += gridDim.x, ++it_a) {
-            const int nt = tile % t.n_tiles_n;
-            const int s = tile / t.n_tiles_n;
-            const int b = s / per_img, r = s % per_img;
+        const bool issuer = (q == 0 && lane == 0);
+        uint8_t* stg = stg0 + eg * 2 * kStageBytes;
+        uint32_t it_a = 0, it_s = 0;
+        for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
+            const int b = st / per_img, r = st % per_img;
             const int ty = r / t.tiles_x, tx = r % t.tiles_x;
-            const uint32_t as = it_a % AS;
-            mbar_wait(&acc_full[as], (it_a / AS) & 1);
-            tc_fence_after();
+            for (int nt = 0; nt < t.n_tiles_n; ++nt, ++it_a) {
+                const uint32_t as = it_a % AS;
+                mbar_wait(&acc_full[as], (it_a / AS) & 1);
+                tc_fence_after();
 #pragma unroll 1
-            for (int mt = 0; mt < MT; ++mt) {
-                const int y = ty * Cfg::TH + (row >> 3);
-                const int x = tx * Cfg::TW + 8 * mt + (row & 7);
-                const size_t pix = ((size_t)b * a.H + y) * a.W + x;
-#pragma unroll 1
-                for (int c0 = 0; c0 < N_TILE; c0 += 32) {
+                for (int u = eg; u < Cfg::UNITS; u += 2) {
+                    const int mt = u / (N_TILE / 32), c0 = (u % (N_TILE / 32)) * 32;
+                    const int y = ty * Cfg::TH + (row >> 3);
+                    const int x = tx * Cfg::TW + 8 * mt + (row & 7);
+                    const size_t pix = ((size_t)b * a.H + y) * a.W + x;
+                    const int cb = nt * N_TILE + c0;  // first output channel of this 32-wide block
                     uint32_t acc[32];
                     tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (MT * N_TILE) + mt * N_TILE + c0,
                                        acc);
                     tmem_ld_wait();
-                    const int cb = nt * N_TILE + c0;  // first output channel of this 32-wide chunk
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
-                    if (a.bias) {
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            const float4 bb = __ldg((const float4*)(a.bias + cb + j));
-                            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
-                        }
-                    }
-                    if (a.act == ACT_LRELU) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * a.slope;
-                    } else if (a.act == ACT_GELU) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-                    }
-                    if (a.res1) {
-                        if (a.res1_f32) {
-                            const float4* rp = (const float4*)((const float*)a.res1 + pix * a.res1_pitch + cb);
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const float4 rr = rp[j];
-                                v[4 * j] = v[4 * j] * a.alpha1 + rr.x;
-                                v[4 * j + 1] = v[4 * j + 1] * a.alpha1 + rr.y;
-                                v[4 * j + 2] = v[4 * j + 2] * a.alpha1 + rr.z;
-                                v[4 * j + 3] = v[4 * j + 3] * a.alpha1 + rr.w;
-                            }
-                        } else {
-                            const uint4* rp = (const uint4*)((const bf16*)a.res1 + pix * a.res1_pitch + cb);
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const uint4 rr = rp[j];
-                                const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    const float2 f = __bfloat1622float2(h[k]);
-                                    v[8 * j + 2 * k] = v[8 * j + 2 * k] * a.alpha1 + f.x;
-                                    v[8 * j + 2 * k + 1] = v[8 * j + 2 * k + 1] * a.alpha1 + f.y;
-                                }
-                            }
-                        }
-                    }
-                    if (a.res2) {
-                        float cs[32];
-                        if (a.res2_cs) {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 4) {
-                                const float4 c4 = __ldg((const float4*)(a.res2_cs + (size_t)b * a.Cout + cb + j));
-                                cs[j] = c4.x; cs[j + 1] = c4.y; cs[j + 2] = c4.z; cs[j + 3] = c4.w;
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) cs[j] = 1.f;
-                        }
-                        if (a.res2_f32) {
-                            const float4* rp = (const float4*)((const float*)a.res2 + pix * a.res2_pitch + cb);
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const float4 rr = rp[j];
-                                v[4 * j] = v[4 * j] * a.alpha2 + rr.x * cs[4 * j];
-                                v[4 * j + 1] = v[4 * j + 1] * a.alpha2 + rr.y * cs[4 * j + 1];
-                                v[4 * j + 2] = v[4 * j + 2] * a.alpha2 + rr.z * cs[4 * j + 2];
-                                v[4 * j + 3] = v[4 * j + 3] * a.alpha2 + rr.w * cs[4 * j + 3];
-                            }
-                        } else {
-                            const uint4* rp = (const uint4*)((const bf16*)a.res2 + pix * a.res2_pitch + cb);
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const uint4 rr = rp[j];
-                                const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    const float2 f = __bfloat1622float2(h[k]);
-                                    v[8 * j + 2 * k] = v[8 * j + 2 * k] * a.alpha2 + f.x * cs[8 * j + 2 * k];
-                                    v[8 * j + 2 * k + 1] = v[8 * j + 2 * k + 1] * a.alpha2 + f.y * cs[8 * j + 2 * k + 1];
-                                }
-                            }
-                        }
-                    }
+                    epilogue_math(v, a, pix, cb, b);
                     if (a.out32) {
                         float4* op = (float4*)(a.out32 + pix * a.out32_pitch + cb);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) op[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                     }
                     if (a.out) {
-                        if (!a.pixel_shuffle) {
+                        if (t.tma_store) {
+                            // stage the 128 x 32 bf16 block (64-byte rows, SWIZZLE_64B) and hand it to TMA
+                            uint8_t* sb = stg + (it_s & 1) * kStageBytes;
+                            if (issuer) bulk_wait_group_read<1>();  // the store that last used this buffer has read it
+                            named_bar_sync(1 + eg, 128);
+                            const uint32_t sw = (row >> 1) & 3;
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                uint4 o;
+                                __nv_bfloat162* h = (__nv_bfloat162*)&o;
+#pragma unroll
+                                for (int k = 0; k < 4; ++k)
+                                    h[k] = __floats2bfloat162_rn(v[8 * j + 2 * k], v[8 * j + 2 * k + 1]);
+                                *(uint4*)(sb + row * 64 + ((j ^ sw) << 4)) = o;
+                            }
+                            fence_proxy_async_smem();
+                            named_bar_sync(1 + eg, 128);
+                            if (issuer) {
+                                tma_store_4d(&tmO, sb, cb, tx * Cfg::TW + 8 * mt, ty * Cfg::TH, b);
+                                bulk_commit_group();
+                            }
+                            ++it_s;
+                        } else if (!a.pixel_shuffle) {
                             uint4* op = (uint4*)(a.out + pix * a.out_pitch + cb);
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
                                 uint4 o;
                                 __nv_bfloat162* h = (__nv_bfloat162*)&o;
 #pragma unroll
-                                for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[8 * j + 2 * k], v[8 * j + 2 * k + 1]);
+                                for (int k = 0; k < 4; ++k)
+                                    h[k] = __floats2bfloat162_rn(v[8 * j + 2 * k], v[8 * j + 2 * k + 1]);
                                 op[j] = o;
                             }
                         } else {
@@ -301,10 +394,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         }
                     }
                 }
+                tc_fence_before();
+                mbar_arrive(&acc_empty[as]);
             }
-            tc_fence_before();
-            mbar_arrive(&acc_empty[as]);
         }
+        if (issuer) bulk_wait_group<0>();  // all TMA stores of this group have completed
     }
 
     tc_fence_before();
@@ -334,7 +428,7 @@ static EncodeTiledFn get_encode() {
 }
 
 static int encode_bf16_map(CUtensorMap* m, const void* ptr, int rank, const cuuint64_t* dims,
-                           const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+                           const cuuint64_t* strides_bytes, const cuuint32_t* box, CUtensorMapSwizzle swz) {
     EncodeTiledFn enc = get_encode();
     if (!enc) {
         set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
@@ -342,8 +436,8 @@ static int encode_bf16_map(CUtensorMap* m, const void* ptr, int rank, const cuui
     }
     cuuint32_t es[5] = {1, 1, 1, 1, 1};
     CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), dims,
-                     strides_bytes, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                     strides_bytes, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled failed (CUresult %d): rank %d dims [%llu,%llu,%llu,%llu] box [%u,%u,%u,%u]",
                   (int)r, rank, (unsigned long long)dims[0], (unsigned long long)dims[1],
@@ -367,41 +461,79 @@ static int num_sms() {
     return g_num_sms;
 }
 
+static bool env_flag(const char* name, bool dflt) {
+    const char* v = getenv(name);
+    if (!v || !*v) return dflt;
+    return v[0] != '0';
+}
+
 template <class Cfg>
 static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     if (a.H % Cfg::TH || a.W % Cfg::TW) {
         set_error("conv_tc: H=%d W=%d not divisible by tile %dx%d", a.H, a.W, Cfg::TH, Cfg::TW);
         return SRB_E_SHAPE;
     }
-    CUtensorMap tmA, tmW;
+    ConvLaunch t;
+    t.tiles_x = a.W / Cfg::TW;
+    t.tiles_y = a.H / Cfg::TH;
+    t.n_tiles_n = a.Cout / Cfg::N_TILE;
+    t.n_spatial = a.B * t.tiles_x * t.tiles_y;
+    t.nchunks = (a.Cin + 63) / 64;
+    t.wslots = (Cfg::TAPS == 1) ? t.n_tiles_n * t.nchunks : Cfg::W_RING;
+    const int fixed = t.wslots * Cfg::W_BYTES + kStagingBytes + kBarrierBytes + 1024;
+    t.ps = (kSmemLimit - fixed) / Cfg::PATCH_STRIDE;
+    if (t.ps > kMaxPS) t.ps = kMaxPS;
+    if (t.ps < 2) {
+        set_error("conv_tc: layer does not fit shared memory (Cin=%d Cout=%d taps=%d)", a.Cin, a.Cout, Cfg::TAPS);
+        return SRB_E_SHAPE;
+    }
+    t.reuse = (t.n_tiles_n > 1 && t.nchunks <= t.ps) ? 1 : 0;
+    static const bool use_tma_store = env_flag("SRB_TMA_STORE", true);
+    static const bool use_pdl = env_flag("SRB_PDL", true);
+    t.tma_store = (a.out && !a.pixel_shuffle && use_tma_store && (((uintptr_t)a.out & 15) == 0) &&
+                   (a.out_pitch % 8 == 0)) ? 1 : 0;
+    const int smem = t.ps * Cfg::PATCH_STRIDE + fixed;
+
+    CUtensorMap tmA, tmW, tmO;
     {
         cuuint64_t dims[4] = {(cuuint64_t)a.Cin, (cuuint64_t)a.W, (cuuint64_t)a.H, (cuuint64_t)a.B};
         cuuint64_t str[3] = {(cuuint64_t)a.in_pitch * 2, (cuuint64_t)a.W * a.in_pitch * 2,
                              (cuuint64_t)a.H * a.W * a.in_pitch * 2};
         cuuint32_t box[4] = {64, (cuuint32_t)Cfg::PW, (cuuint32_t)Cfg::PH, 1};
-        SRB_TRY(encode_bf16_map(&tmA, a.in, 4, dims, str, box));
+        SRB_TRY(encode_bf16_map(&tmA, a.in, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B));
     }
     {
         cuuint64_t dims[3] = {(cuuint64_t)a.Cin, (cuuint64_t)a.Cout, (cuuint64_t)Cfg::TAPS};
         cuuint64_t str[2] = {(cuuint64_t)a.Cin * 2, (cuuint64_t)a.Cout * a.Cin * 2};
         cuuint32_t box[3] = {64, (cuuint32_t)Cfg::N_TILE, 1};
-        SRB_TRY(encode_bf16_map(&tmW, a.w, 3, dims, str, box));
+        SRB_TRY(encode_bf16_map(&tmW, a.w, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B));
     }
-    ConvTiles t;
-    t.tiles_x = a.W / Cfg::TW;
-    t.tiles_y = a.H / Cfg::TH;
-    t.n_tiles_n = a.Cout / Cfg::N_TILE;
-    t.total = a.B * t.tiles_x * t.tiles_y * t.n_tiles_n;
-    t.nchunks = (a.Cin + 63) / 64;
-    static bool attr_set = false;  // per template instantiation
-    if (!attr_set) {
-        SRB_CUDA(cudaFuncSetAttribute(conv_tc_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      Cfg::SMEM_BYTES));
-        attr_set = true;
+    if (t.tma_store) {
+        cuuint64_t dims[4] = {(cuuint64_t)a.Cout, (cuuint64_t)a.W, (cuuint64_t)a.H, (cuuint64_t)a.B};
+        cuuint64_t str[3] = {(cuuint64_t)a.out_pitch * 2, (cuuint64_t)a.W * a.out_pitch * 2,
+                             (cuuint64_t)a.H * a.W * a.out_pitch * 2};
+        cuuint32_t box[4] = {32, 8, 16, 1};
+        SRB_TRY(encode_bf16_map(&tmO, a.out, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B));
+    } else {
+        tmO = tmA;  // unused
     }
-    int grid = t.total < num_sms() ? t.total : num_sms();
-    conv_tc_kernel<Cfg><<<grid, 256, Cfg::SMEM_BYTES, stream>>>(tmA, tmW, a, t);
-    SRB_CUDA(cudaGetLastError());
+    static int smem_set = 0;  // per template instantiation
+    if (smem_set < smem) {
+        SRB_CUDA(cudaFuncSetAttribute(conv_tc_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
+        smem_set = kSmemLimit;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(t.n_spatial < num_sms() ? t.n_spatial : num_sms());
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = use_pdl ? 1 : 0;
+    SRB_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<Cfg>, tmA, tmW, tmO, a, t));
     return SRB_OK;
 }
 

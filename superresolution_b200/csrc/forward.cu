@@ -109,7 +109,7 @@ static void build_desc(ModelDesc& m) {
     conv_tc("stage2.upsample.0", 256, 64, 9);
     conv_f32("stage2.conv_last", 1, 64, 9);
     // ---- derived: gathered relative-position bias tables ----
-    for (int i = 0; i < 24; ++i) { m.bias_sa_off[i] = off; off = align256(off + 6 * 64 * 64 * 4); }
+    for (int i = 0; i < 24; ++i) { m.bias_sa_off[i] = off; off = align256(off + 6 * 64 * 64 * 2); }  // bf16, fragment order
     for (int i = 0; i < 4; ++i) { m.bias_oca_off[i] = off; off = align256(off + 6 * 64 * 144 * 4); }
     m.packed_bytes = off;
 }
@@ -153,11 +153,11 @@ int model_pack(const void* const* params, int n, void* packed, size_t packed_byt
         for (int j = 0; j < 6; ++j) {
             snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.attn.relative_position_bias_table", l, j);
             const float* tab = (const float*)(base + m.params[m.index.at(buf)].off);
-            SRB_TRY(expand_rel_bias(tab, 225, idx_sa, 64, (float*)(base + m.bias_sa_off[l * 6 + j]), s));
+            SRB_TRY(expand_rel_bias_bf16(tab, 225, idx_sa, 64, (bf16*)(base + m.bias_sa_off[l * 6 + j]), s));
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.relative_position_bias_table", l);
         const float* tab = (const float*)(base + m.params[m.index.at(buf)].off);
-        SRB_TRY(expand_rel_bias(tab, 361, idx_oca, 144, (float*)(base + m.bias_oca_off[l]), s));
+        SRB_TRY(expand_rel_bias_f32(tab, 361, idx_oca, 144, (float*)(base + m.bias_oca_off[l]), s));
     }
     return SRB_OK;
 }
@@ -379,7 +379,7 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
             const bf16* xin = (j == 0) ? w.g : w.y;  // token stream entering this block (= shortcut)
             LAUNCH(c, PC_LN, 0.0, layernorm96(xin, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
             SRB_TRY(tc_layer(c, b + "attn.qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
-            LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 64 * 16 * 6 * ((double)B * R * Rw / 64), window_attention(w.qkv, (const float*)(pk + c.m->bias_sa_off[l * 6 + j]), w.ao, B, R, Rw,
+            LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 64 * 16 * 6 * ((double)B * R * Rw / 64), window_attention(w.qkv, (const bf16*)(pk + c.m->bias_sa_off[l * 6 + j]), w.ao, B, R, Rw,
                                        (j & 1) ? 4 : 0, c.s));
             // CAB on the normalised tensor: conv 96->32, GELU, conv 32->96, channel attention
             SRB_TRY(tc_layer(c, b + "conv_block.cab.0", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.c1, 32));

@@ -25,13 +25,16 @@ int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const flo
 
 // attn.cu
 // qkv: bf16 [B,H,W,288] = [q(96) | k(96) | v(96)], head h = channels [16h,16h+16) of each part.
-// bias: fp32 [6][64][NK] relative-position bias already gathered from the table.
-// shift: 0 or 4 (HAB cyclic shift, mask -100 across region borders).  out: bf16 [B,H,W,96].
-int window_attention(const bf16* qkv, const float* bias, bf16* out, int B, int H, int W, int shift, cudaStream_t s);
+// bias_frag: relative-position bias gathered into MMA C-fragment order (expand_rel_bias_*), bf16 for HAB (staged in
+// shared memory), fp32 for OCAB.  shift: 0 or 4 (HAB cyclic shift, mask -100 across region borders).
+// out: bf16 [B,H,W,96].
+int window_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, int shift,
+                     cudaStream_t s);
 // OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.
-int ocab_attention(const bf16* qkv, const float* bias, bf16* out, int B, int H, int W, cudaStream_t s);
-// table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> bias fp32 [6][64][NK]
-int expand_rel_bias(const float* table, int T, const int64_t* index, int NK, float* bias, cudaStream_t s);
+int ocab_attention(const bf16* qkv, const float* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s);
+// table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> fragment-ordered bias [6*64*NK]
+int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, cudaStream_t s);
+int expand_rel_bias_f32(const float* table, int T, const int64_t* index, int NK, float* out, cudaStream_t s);
 
 // metrics.cu
 size_t reduce_scratch_bytes();
