@@ -38,31 +38,52 @@ __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+// A fragment (16 rows x 16 k) of a row-major [rows][AP] bf16 tile: r = {a0,a1,a2,a3}
+__device__ __forceinline__ void load_a_frag(uint32_t (&r)[4], const bf16* tile, int row0, int k0, int lane) {
+    ldsm_x4(r, tile + (row0 + (lane & 7) + ((lane >> 3) & 1) * 8) * AP + k0 + (lane >> 4) * 8);
+}
+// B fragments of TWO adjacent n-tiles (n0..n0+15) x 16 k from a [n][AP] (k contiguous) tile:
+// r = {b0,b1 of n-tile 0, b0,b1 of n-tile 1}
+__device__ __forceinline__ void load_b_frag2(uint32_t (&r)[4], const bf16* tile, int n0, int k0, int lane) {
+    ldsm_x4(r, tile + (n0 + (lane & 7) + (lane >> 4) * 8) * AP + k0 + ((lane >> 3) & 1) * 8);
+}
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-// One (window, head) attention for the calling warp.  sQ/sK/sV: [rows][AP] bf16 tiles of this window.
-// BIAS_T = bf16 (shared, fragment order, 4 values / lane / (mt, j)) or float (global, fragment order).
-// The normalised output overwrites this head's 16 columns of sQ (only this warp reads them).
+// One (window, head) attention for the calling warp over query m-tiles [mt_lo, mt_hi).  sQ/sK/sV: [rows][AP] bf16
+// tiles of this window.  BIAS_T = bf16 (shared, fragment order, 4 values / lane / (mt, j)) or float (global, fragment
+// order).  The normalised output overwrites this head's 16 columns of the processed Q rows (only this warp reads
+// them).  All operand fragments come from ldmatrix (V through .trans).
 template <int NK, typename BIAS_T>
 __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16* sV, const BIAS_T* bias_h,
-                                            const int* srid, bool masked, int h, int lane) {
+                                            const int* srid, bool masked, int h, int lane, int mt_lo = 0,
+                                            int mt_hi = 4) {
     const int g = lane >> 2, t = lane & 3;
     constexpr int NT = NK / 8;   // S n-tiles
     constexpr int KT = NK / 16;  // PV k-tiles
 #pragma unroll 1
-    for (int mt = 0; mt < 4; ++mt) {
+    for (int mt = mt_lo; mt < mt_hi; ++mt) {
         const int r0 = 16 * mt + g, r1 = r0 + 8;
-        const uint32_t a0 = *(const uint32_t*)(sQ + r0 * AP + h * 16 + 2 * t);
-        const uint32_t a1 = *(const uint32_t*)(sQ + r1 * AP + h * 16 + 2 * t);
-        const uint32_t a2 = *(const uint32_t*)(sQ + r0 * AP + h * 16 + 2 * t + 8);
-        const uint32_t a3 = *(const uint32_t*)(sQ + r1 * AP + h * 16 + 2 * t + 8);
+        uint32_t qa[4];
+        load_a_frag(qa, sQ, 16 * mt, h * 16, lane);
         float s[NT][4];
 #pragma unroll
-        for (int j = 0; j < NT; ++j) {
+        for (int j = 0; j < NT; j += 2) {
+            uint32_t kb[4];
+            load_b_frag2(kb, sK, 8 * j, h * 16, lane);
             s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
-            const uint32_t b0 = *(const uint32_t*)(sK + (8 * j + g) * AP + h * 16 + 2 * t);
-            const uint32_t b1 = *(const uint32_t*)(sK + (8 * j + g) * AP + h * 16 + 2 * t + 8);
-            mma_bf16_16816(s[j], a0, a1, a2, a3, b0, b1);
+            s[j + 1][0] = s[j + 1][1] = s[j + 1][2] = s[j + 1][3] = 0.f;
+            mma_bf16_16816(s[j], qa[0], qa[1], qa[2], qa[3], kb[0], kb[1]);
+            mma_bf16_16816(s[j + 1], qa[0], qa[1], qa[2], qa[3], kb[2], kb[3]);
         }
         // scale (head_dim^-0.5 = 0.25), relative position bias, shift mask (-100 across region borders)
         int rid0 = 0, rid1 = 0;
@@ -120,13 +141,11 @@ __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16
             const uint32_t p1 = pack_bf16(s[2 * kt][2], s[2 * kt][3]);
             const uint32_t p2 = pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]);
             const uint32_t p3 = pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3]);
-#pragma unroll
-            for (int nt = 0; nt < 2; ++nt) {
-                const bf16* vp = sV + (16 * kt + 2 * t) * AP + h * 16 + 8 * nt + g;
-                const uint32_t b0 = pack_raw(vp[0], vp[AP]);
-                const uint32_t b1 = pack_raw(vp[8 * AP], vp[9 * AP]);
-                mma_bf16_16816(o[nt], p0, p1, p2, p3, b0, b1);
-            }
+            // V^T fragments: {b0,b1 of dims 0-7, b0,b1 of dims 8-15} for keys [16kt, 16kt+16)
+            uint32_t vb[4];
+            ldsm_x4_trans(vb, sV + (16 * kt + (lane & 7) + ((lane >> 3) & 1) * 8) * AP + h * 16 + (lane >> 4) * 8);
+            mma_bf16_16816(o[0], p0, p1, p2, p3, vb[0], vb[1]);
+            mma_bf16_16816(o[1], p0, p1, p2, p3, vb[2], vb[3]);
         }
         const float i0 = 1.f / l0, i1 = 1.f / l1;
         __syncwarp();  // every lane has read its Q fragments of this m-tile before they are overwritten
@@ -309,6 +328,253 @@ int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK
 int expand_rel_bias_f32(const float* table, int T, const int64_t* index, int NK, float* out, cudaStream_t s) {
     const int n = 6 * 64 * NK;
     expand_rel_bias_kernel<float><<<(n + 255) / 256, 256, 0, s>>>(table, T, index, NK, out);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+}  // namespace srb
+
+namespace srb {
+
+// ---------------------------------------------------------------------------------------------------------------
+// Fused HAB attention branch (App. A.2.4):  t = x + proj( W-MSA( LN1(x) ) ),  and  xn = LN1(x)  for the CAB branch.
+// One persistent CTA (6 warps = 6 heads) walks over windows; weights (qkv 288x96, proj 96x96, bf16), the layer's
+// relative-position bias (fragment order) and the LayerNorm affine live in shared memory for the whole kernel.
+// Per window: cp.async gather of the 64 tokens (cyclic shift = index math, next window prefetched) -> LayerNorm in
+// fp32 -> qkv GEMM -> per-head attention -> proj GEMM + bias + shortcut -> coalesced scatter.  Nothing but x is read
+// from HBM and only xn and t are written: the qkv / attention-output round trips (1.6 GB per block at B=16) are gone.
+// The three small GEMMs (K = 96) run on warp-level mma.sync next to the softmax/LN CUDA-core work of the same warps.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int FA_WQKV = 288 * AP, FA_WPROJ = 96 * AP, FA_TILE = 64 * AP;
+constexpr int FA_SMEM = (FA_WQKV + FA_WPROJ + HAB_BIAS + 2 * FA_TILE /*x*/ + FA_TILE /*xn*/ + 3 * FA_TILE /*qkv*/) * 2 +
+                        2 * 128 * 4 /*meta*/ + (288 + 96 + 96 + 96) * 4;
+
+struct FusedAttnArgs {
+    const bf16* x;        // [B,H,W,96] token stream (shortcut)
+    const float *ln_g, *ln_b;
+    const bf16* wqkv;     // [288][96]
+    const float* bqkv;    // [288]
+    const bf16* bias_frag;
+    const bf16* wproj;    // [96][96]
+    const float* bproj;   // [96]
+    bf16* xn;             // [B,H,W,96] LN1(x)
+    bf16* t;              // [B,H,W,96] x + proj(attn)
+    int B, H, W, shift;
+};
+
+constexpr int FA_THREADS = 384;  // 12 warps: (m-half, head / column group)
+
+__global__ void __launch_bounds__(FA_THREADS, 1)
+hab_fused_attn_kernel(const FusedAttnArgs a) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    bf16* sWq = (bf16*)smem_raw;
+    bf16* sWp = sWq + FA_WQKV;
+    bf16* sBias = sWp + FA_WPROJ;
+    bf16* sX = sBias + HAB_BIAS;        // [2][64][AP]
+    bf16* sXN = sX + 2 * FA_TILE;       // [64][AP]
+    bf16* sQKV = sXN + FA_TILE;         // [3][64][AP]
+    int* meta = (int*)(sQKV + 3 * FA_TILE);  // [2][128]
+    float* sbq = (float*)(meta + 256);
+    float* sbp = sbq + 288;
+    float* sg = sbp + 96;
+    float* sb = sg + 96;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, tq = lane & 3;
+    const int mh = warp / 6, ng = warp % 6;  // m-half (m-tiles 2mh, 2mh+1) and column group / head
+    const int H = a.H, W = a.W, shift = a.shift;
+    const int nwx = W / 8, nwy = H / 8, nwin = a.B * nwx * nwy;
+
+    // ---- one-time: weights, bias tables, affine parameters ----
+    for (int i = tid; i < 288 * 12; i += FA_THREADS) *(uint4*)(sWq + (i / 12) * AP + (i % 12) * 8) = __ldg((const uint4*)a.wqkv + i);
+    for (int i = tid; i < 96 * 12; i += FA_THREADS) *(uint4*)(sWp + (i / 12) * AP + (i % 12) * 8) = __ldg((const uint4*)a.wproj + i);
+    for (int i = tid; i < HAB_BIAS / 8; i += FA_THREADS) ((uint4*)sBias)[i] = __ldg((const uint4*)a.bias_frag + i);
+    if (tid < 288) sbq[tid] = a.bqkv[tid];
+    if (tid < 96) { sbp[tid] = a.bproj[tid]; sg[tid] = a.ln_g[tid]; sb[tid] = a.ln_b[tid]; }
+
+    auto issue_load = [&](int win, int buf) {
+        bf16* dst = sX + buf * FA_TILE;
+        int* mt_ = meta + buf * 128;
+        const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
+        const size_t img = (size_t)b * H * W;
+        for (int i = tid; i < 64 * 12; i += FA_THREADS) {
+            const int n = i / 12, ck = i % 12;
+            const int ys = wy * 8 + (n >> 3), xs = wx * 8 + (n & 7);  // rolled-image coordinates
+            const int y = (ys + shift) % H, x = (xs + shift) % W;     // torch.roll(-shift)
+            const size_t pix = img + (size_t)y * W + x;
+            cp_async16(dst + n * AP + ck * 8, a.x + pix * 96 + ck * 8);
+            if (ck == 0) {
+                mt_[n] = (int)(pix - img);
+                const int rh = ys < H - 8 ? 0 : (ys < H - 4 ? 1 : 2);
+                const int rw = xs < W - 8 ? 0 : (xs < W - 4 ? 1 : 2);
+                mt_[64 + n] = rh * 3 + rw;
+            }
+        }
+    };
+
+    int win = blockIdx.x;
+    if (win < nwin) issue_load(win, 0);
+    cp_async_commit();
+    int it = 0;
+    for (; win < nwin; win += gridDim.x, ++it) {
+        const int buf = it & 1;
+        if (win + (int)gridDim.x < nwin) issue_load(win + gridDim.x, buf ^ 1);
+        cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        bf16* x_t = sX + buf * FA_TILE;
+        const int* mt_ = meta + buf * 128;
+        const size_t img = (size_t)(win / (nwx * nwy)) * H * W;
+
+        // ---- LayerNorm (fp32, eps 1e-5): 4 lanes per token, 24 channels each ----
+        if (tid < 256) {
+            const int n = tid >> 2, part = tid & 3;
+            float v[24];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const uint4 raw = *(const uint4*)(x_t + n * AP + part * 24 + c * 8);
+                const __nv_bfloat162* h2 = (const __nv_bfloat162*)&raw;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h2[k]);
+                    v[c * 8 + 2 * k] = f.x;
+                    v[c * 8 + 2 * k + 1] = f.y;
+                }
+            }
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 24; ++j) s += v[j];
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            const float mean = s * (1.f / 96.f);
+            float q = 0.f;
+#pragma unroll
+            for (int j = 0; j < 24; ++j) q += (v[j] - mean) * (v[j] - mean);
+            q += __shfl_xor_sync(0xffffffffu, q, 1);
+            q += __shfl_xor_sync(0xffffffffu, q, 2);
+            const float rstd = rsqrtf(q * (1.f / 96.f) + 1e-5f);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                uint4 o;
+                __nv_bfloat162* h2 = (__nv_bfloat162*)&o;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int ch = part * 24 + c * 8 + 2 * k;
+                    h2[k] = __floats2bfloat162_rn((v[c * 8 + 2 * k] - mean) * rstd * sg[ch] + sb[ch],
+                                                  (v[c * 8 + 2 * k + 1] - mean) * rstd * sg[ch + 1] + sb[ch + 1]);
+                }
+                *(uint4*)(sXN + n * AP + part * 24 + c * 8) = o;
+            }
+        }
+        __syncthreads();
+        // xn -> HBM for the CAB branch (coalesced 16-byte chunks)
+        for (int i = tid; i < 64 * 12; i += FA_THREADS) {
+            const int n = i / 12, c = i % 12;
+            *(uint4*)(a.xn + (img + mt_[n]) * 96 + c * 8) = *(const uint4*)(sXN + n * AP + c * 8);
+        }
+
+        // ---- qkv = xn @ Wqkv^T + b : warp (mh, ng) owns rows [32mh, 32mh+32) x columns [48ng, 48ng+48) ----
+        {
+            float acc[2][6][4];
+#pragma unroll
+            for (int m = 0; m < 2; ++m)
+#pragma unroll
+                for (int n = 0; n < 6; ++n) acc[m][n][0] = acc[m][n][1] = acc[m][n][2] = acc[m][n][3] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 6; ++ks) {
+                uint32_t af[2][4], bfr[3][4];
+                load_a_frag(af[0], sXN, 32 * mh, 16 * ks, lane);
+                load_a_frag(af[1], sXN, 32 * mh + 16, 16 * ks, lane);
+#pragma unroll
+                for (int n2 = 0; n2 < 3; ++n2) load_b_frag2(bfr[n2], sWq, 48 * ng + 16 * n2, 16 * ks, lane);
+#pragma unroll
+                for (int m = 0; m < 2; ++m)
+#pragma unroll
+                    for (int n2 = 0; n2 < 3; ++n2) {
+                        mma_bf16_16816(acc[m][2 * n2], af[m][0], af[m][1], af[m][2], af[m][3], bfr[n2][0], bfr[n2][1]);
+                        mma_bf16_16816(acc[m][2 * n2 + 1], af[m][0], af[m][1], af[m][2], af[m][3], bfr[n2][2], bfr[n2][3]);
+                    }
+            }
+#pragma unroll
+            for (int m = 0; m < 2; ++m) {
+                const int r0 = 32 * mh + 16 * m + g, r1 = r0 + 8;
+#pragma unroll
+                for (int n = 0; n < 6; ++n) {
+                    const int c = 48 * ng + 8 * n + 2 * tq;  // output column in [0,288)
+                    const int part = c / 96, cc = c % 96;
+                    const float b0 = sbq[c], b1 = sbq[c + 1];
+                    bf16* dst = sQKV + part * FA_TILE + cc;
+                    *(uint32_t*)(dst + r0 * AP) = pack_bf16(acc[m][n][0] + b0, acc[m][n][1] + b1);
+                    *(uint32_t*)(dst + r1 * AP) = pack_bf16(acc[m][n][2] + b0, acc[m][n][3] + b1);
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- per-head attention (head ng, query rows of m-half mh); output overwrites the Q tile ----
+        attend_head<64, bf16>(sQKV, sQKV + FA_TILE, sQKV + 2 * FA_TILE, sBias + ng * (4 * 8 * 32 * 4), mt_ + 64,
+                              shift > 0, ng, lane, 2 * mh, 2 * mh + 2);
+        __syncthreads();
+
+        // ---- t = x + attn @ Wproj^T + b : warp (mh, ng) owns rows [32mh, +32) x columns [16ng, +16) ----
+        {
+            float acc[2][2][4];
+#pragma unroll
+            for (int m = 0; m < 2; ++m)
+#pragma unroll
+                for (int n = 0; n < 2; ++n) acc[m][n][0] = acc[m][n][1] = acc[m][n][2] = acc[m][n][3] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 6; ++ks) {
+                uint32_t af[2][4], bfr[4];
+                load_a_frag(af[0], sQKV, 32 * mh, 16 * ks, lane);
+                load_a_frag(af[1], sQKV, 32 * mh + 16, 16 * ks, lane);
+                load_b_frag2(bfr, sWp, 16 * ng, 16 * ks, lane);
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    mma_bf16_16816(acc[m][0], af[m][0], af[m][1], af[m][2], af[m][3], bfr[0], bfr[1]);
+                    mma_bf16_16816(acc[m][1], af[m][0], af[m][1], af[m][2], af[m][3], bfr[2], bfr[3]);
+                }
+            }
+#pragma unroll
+            for (int m = 0; m < 2; ++m) {
+                const int r0 = 32 * mh + 16 * m + g, r1 = r0 + 8;
+#pragma unroll
+                for (int n = 0; n < 2; ++n) {
+                    const int c = 16 * ng + 8 * n + 2 * tq;
+                    const float b0 = sbp[c], b1 = sbp[c + 1];
+                    bf16* p0 = x_t + r0 * AP + c;
+                    bf16* p1 = x_t + r1 * AP + c;
+                    const float2 x0 = __bfloat1622float2(*(const __nv_bfloat162*)p0);
+                    const float2 x1 = __bfloat1622float2(*(const __nv_bfloat162*)p1);
+                    *(uint32_t*)p0 = pack_bf16(acc[m][n][0] + b0 + x0.x, acc[m][n][1] + b1 + x0.y);
+                    *(uint32_t*)p1 = pack_bf16(acc[m][n][2] + b0 + x1.x, acc[m][n][3] + b1 + x1.y);
+                }
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < 64 * 12; i += FA_THREADS) {
+            const int n = i / 12, c = i % 12;
+            *(uint4*)(a.t + (img + mt_[n]) * 96 + c * 8) = *(const uint4*)(x_t + n * AP + c * 8);
+        }
+        __syncthreads();  // x tile / meta / xn / qkv tiles free for the next window
+    }
+    cp_async_wait<0>();
+}
+
+int hab_fused_attention(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
+                        const bf16* bias_frag, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
+                        int W, int shift, cudaStream_t s) {
+    if (H % 8 || W % 8) { set_error("attention: H=%d W=%d must be multiples of the window size 8", H, W); return SRB_E_SHAPE; }
+    static bool attr = false;
+    if (!attr) {
+        SRB_CUDA(cudaFuncSetAttribute(hab_fused_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
+        attr = true;
+    }
+    FusedAttnArgs a;
+    a.x = x; a.ln_g = ln_g; a.ln_b = ln_b; a.wqkv = wqkv; a.bqkv = bqkv; a.bias_frag = bias_frag; a.wproj = wproj;
+    a.bproj = bproj; a.xn = xn; a.t = t; a.B = B; a.H = H; a.W = W; a.shift = shift;
+    const int nwin = B * (H / 8) * (W / 8);
+    hab_fused_attn_kernel<<<nwin < 148 ? nwin : 148, FA_THREADS, FA_SMEM, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

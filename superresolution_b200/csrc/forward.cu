@@ -216,7 +216,7 @@ static size_t carve(Workspace& w, uint8_t* base, int B, int H, int W) {
     w.c1 = (bf16*)take(ntok * 32 * 2);
     w.qkv = (bf16*)take(ntok * 288 * 2);
     w.hd = (bf16*)take(ntok * 192 * 2);
-    w.pool = (float*)take((size_t)B * 96 * 4);
+    w.pool = (float*)take((size_t)B * cab_pool_slabs((int)(4 * H * W)) * 96 * 4);  // per-slab partial sums
     w.cs = (float*)take((size_t)B * 96 * 4);
     w.d1 = (bf16*)take(ntok * 64 * 2);
     w.d2 = (bf16*)take(p4 * 64 * 2);
@@ -377,22 +377,25 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
             snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.", l, j);
             const std::string b = buf;
             const bf16* xin = (j == 0) ? w.g : w.y;  // token stream entering this block (= shortcut)
-            LAUNCH(c, PC_LN, 0.0, layernorm96(xin, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
-            SRB_TRY(tc_layer(c, b + "attn.qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
-            LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 64 * 16 * 6 * ((double)B * R * Rw / 64), window_attention(w.qkv, (const bf16*)(pk + c.m->bias_sa_off[l * 6 + j]), w.ao, B, R, Rw,
+            // fused attention branch: xn = LN1(x), ao = x + proj(W-MSA(xn))   (LN1, qkv, attention, proj in one kernel)
+            LAUNCH(c, PC_ATTN, 2.0 * (27648 + 12288 + 9216) * (double)ntok,
+                   hab_fused_attention(xin, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), c.Wt(b + "attn.qkv.weight"),
+                                       c.F(b + "attn.qkv.bias"), (const bf16*)(pk + c.m->bias_sa_off[l * 6 + j]),
+                                       c.Wt(b + "attn.proj.weight"), c.F(b + "attn.proj.bias"), w.xn, w.ao, B, R, Rw,
                                        (j & 1) ? 4 : 0, c.s));
             // CAB on the normalised tensor: conv 96->32, GELU, conv 32->96, channel attention
             SRB_TRY(tc_layer(c, b + "conv_block.cab.0", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.c1, 32));
             SRB_TRY(tc_layer(c, b + "conv_block.cab.2", w.c1, 32, B, R, Rw, ACT_NONE, 0.f, w.c2, 96));
-            c.launches += 2;  // memset + partial sums (counted with the finisher below)
+            c.launches += 1;  // partial sums (counted with the finisher below)
             LAUNCH(c, PC_OTHER, 0.0, cab_channel_attention(w.c2, w.pool, w.cs, c.F(b + "conv_block.cab.3.attention.1.weight"),
                                             c.F(b + "conv_block.cab.3.attention.1.bias"),
                                             c.F(b + "conv_block.cab.3.attention.3.weight"),
                                             c.F(b + "conv_block.cab.3.attention.3.bias"), 0.01f, B, R * Rw, c.s));
-            // x = shortcut + proj(attn) + cab * (sigmoid(..) * conv_scale)
-            SRB_TRY(tc_layer(c, b + "attn.proj", w.ao, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, xin, 0, 96,
-                             1.f, w.c2, 0, 96, w.cs));
-            SRB_TRY(run_mlp(c, w, b, B, R, Rw));
+            // y = ao + cab * (sigmoid(..) * conv_scale);  xn = LN2(y)
+            LAUNCH(c, PC_LN, 0.0, combine_ln96(w.ao, w.c2, w.cs, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), w.y, w.xn,
+                                              ntok, (size_t)R * Rw, c.s));
+            SRB_TRY(tc_layer(c, b + "mlp.fc1", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.hd, 192));
+            SRB_TRY(tc_layer(c, b + "mlp.fc2", w.hd, 192, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", l);
         const std::string b = buf;

@@ -19,7 +19,10 @@ int convert_out(const float* in, void* out, int out_dtype, size_t n, cudaStream_
 int hat_conv_first_ln(const float* img, const float* w, const float* bias, const float* gamma, const float* beta,
                       bf16* f0, bf16* xn, int B, int H, int W, cudaStream_t s);
 int layernorm96(const bf16* in, const float* gamma, const float* beta, bf16* out, size_t ntok, cudaStream_t s);
+int combine_ln96(const bf16* t, const bf16* cab, const float* cs, const float* gamma, const float* beta, bf16* y,
+                 bf16* xn, size_t ntok, size_t tok_per_img, cudaStream_t s);
 int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cudaStream_t s);
+int cab_pool_slabs(int HW);  // pool scratch = B * slabs * 96 floats
 int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const float* w1, const float* b1,
                           const float* w2, const float* b2, float conv_scale, int B, int HW, cudaStream_t s);
 
@@ -30,6 +33,10 @@ int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const flo
 // out: bf16 [B,H,W,96].
 int window_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, int shift,
                      cudaStream_t s);
+// fused HAB attention branch: xn = LN1(x); t = x + proj(W-MSA(xn)) + bproj   (one pass over x)
+int hab_fused_attention(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
+                        const bf16* bias_frag, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
+                        int W, int shift, cudaStream_t s);
 // OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.
 int ocab_attention(const bf16* qkv, const float* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s);
 // table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> fragment-ordered bias [6*64*NK]

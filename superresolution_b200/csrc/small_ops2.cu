@@ -146,6 +146,78 @@ layernorm96_kernel(const bf16* __restrict__ in, const float* __restrict__ gamma,
     }
 }
 
+// HAB combine + norm2 in one pass:  y = t + cab * cs[b,:]  (cs = sigmoid(...) * conv_scale from the CAB channel
+// attention),  xn = LayerNorm(y).  Replaces the add/mul elementwise kernels and the norm2 LayerNorm of the reference.
+__global__ void __launch_bounds__(256)
+combine_ln96_kernel(const bf16* __restrict__ t, const bf16* __restrict__ cab, const float* __restrict__ cs,
+                    const float* __restrict__ gamma, const float* __restrict__ beta, bf16* __restrict__ y,
+                    bf16* __restrict__ xn, size_t ntok, size_t tok_per_img) {
+    const int sub = threadIdx.x & 15;
+    const bool act = sub < 12;
+    const int c0 = (act ? sub : 0) * 8;
+    float gr[8], br[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        gr[j] = __ldg(gamma + c0 + j);
+        br[j] = __ldg(beta + c0 + j);
+    }
+    const size_t stride = ((size_t)gridDim.x * blockDim.x) >> 4;
+    for (size_t t0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 4; t0 < ntok + stride; t0 += stride) {
+        const bool valid = t0 < ntok;
+        const size_t tok = valid ? t0 : 0;
+        const size_t b = tok / tok_per_img;
+        float v[8];
+        {
+            const uint4 ra = *(const uint4*)(t + tok * 96 + c0);
+            const uint4 rb = *(const uint4*)(cab + tok * 96 + c0);
+            const float4 s0 = __ldg((const float4*)(cs + b * 96 + c0));
+            const float4 s1 = __ldg((const float4*)(cs + b * 96 + c0 + 4));
+            const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+            const __nv_bfloat162* ha = (const __nv_bfloat162*)&ra;
+            const __nv_bfloat162* hb = (const __nv_bfloat162*)&rb;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 fa = __bfloat1622float2(ha[k]), fb = __bfloat1622float2(hb[k]);
+                v[2 * k] = fmaf(fb.x, sc[2 * k], fa.x);
+                v[2 * k + 1] = fmaf(fb.y, sc[2 * k + 1], fa.y);
+            }
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[j];
+        s = group16_sum(act ? s : 0.f);
+        const float mean = s * (1.f / 96.f);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) q += (v[j] - mean) * (v[j] - mean);
+        q = group16_sum(act ? q : 0.f);
+        const float rstd = rsqrtf(q * (1.f / 96.f) + 1e-5f);
+        if (valid && act) {
+            uint4 o0, o1;
+            __nv_bfloat162* h0 = (__nv_bfloat162*)&o0;
+            __nv_bfloat162* h1 = (__nv_bfloat162*)&o1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                h0[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+                h1[k] = __floats2bfloat162_rn((v[2 * k] - mean) * rstd * gr[2 * k] + br[2 * k],
+                                              (v[2 * k + 1] - mean) * rstd * gr[2 * k + 1] + br[2 * k + 1]);
+            }
+            *(uint4*)(y + tok * 96 + c0) = o0;
+            *(uint4*)(xn + tok * 96 + c0) = o1;
+        }
+    }
+}
+
+int combine_ln96(const bf16* t, const bf16* cab, const float* cs, const float* gamma, const float* beta, bf16* y,
+                 bf16* xn, size_t ntok, size_t tok_per_img, cudaStream_t s) {
+    const size_t threads = ntok * 16;
+    int grid = (int)((threads + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    combine_ln96_kernel<<<grid, 256, 0, s>>>(t, cab, cs, gamma, beta, y, xn, ntok, tok_per_img);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
 int layernorm96(const bf16* in, const float* gamma, const float* beta, bf16* out, size_t ntok, cudaStream_t s) {
     const size_t threads = ntok * 16;
     int grid = (int)((threads + 255) / 256);
@@ -186,8 +258,8 @@ int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cud
 // Stage B: the tiny MLP; emits cs[b][c] = sigmoid(...) * conv_scale so the HAB combine is a single FMA.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(192)
-chan_sum96_kernel(const bf16* __restrict__ in, float* __restrict__ pool, int HW, int slab) {
-    // block = 192 threads = 16 pixel-lanes x 12 channel-groups; grid = (ceil(HW/slab), B)
+chan_sum96_kernel(const bf16* __restrict__ in, float* __restrict__ partial, int HW, int slab) {
+    // block = 192 threads = 16 pixel-lanes x 12 channel-groups; grid = (nslab, B); partial[b][slab][96]
     const int cgp = threadIdx.x % 12, pl = threadIdx.x / 12;
     const int b = blockIdx.y;
     const int p0 = blockIdx.x * slab;
@@ -211,18 +283,20 @@ chan_sum96_kernel(const bf16* __restrict__ in, float* __restrict__ pool, int HW,
         float s = 0.f;
 #pragma unroll
         for (int i = 0; i < 16; ++i) s += sm[i][threadIdx.x];
-        atomicAdd(pool + b * 96 + threadIdx.x, s);
+        partial[((size_t)b * gridDim.x + blockIdx.x) * 96 + threadIdx.x] = s;  // fixed order: deterministic
     }
 }
 
 __global__ void __launch_bounds__(96)
-cab_finish_kernel(const float* __restrict__ pool, float inv_hw, const float* __restrict__ w1 /*[3][96]*/,
+cab_finish_kernel(const float* __restrict__ partial, int nslab, float inv_hw, const float* __restrict__ w1 /*[3][96]*/,
                   const float* __restrict__ b1, const float* __restrict__ w2 /*[96][3]*/,
                   const float* __restrict__ b2, float conv_scale, float* __restrict__ cs) {
     __shared__ float mean[96];
     __shared__ float hid[3];
     const int b = blockIdx.x, c = threadIdx.x;
-    mean[c] = pool[b * 96 + c] * inv_hw;
+    float tot = 0.f;
+    for (int i = 0; i < nslab; ++i) tot += partial[((size_t)b * nslab + i) * 96 + c];
+    mean[c] = tot * inv_hw;
     __syncthreads();
     if (c < 3) {
         float s = b1[c];
@@ -236,14 +310,16 @@ cab_finish_kernel(const float* __restrict__ pool, float inv_hw, const float* __r
     cs[b * 96 + c] = conv_scale / (1.f + expf(-s));
 }
 
+int cab_pool_slabs(int HW) { return (HW + 1023) / 1024; }
+
 int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const float* w1, const float* b1,
                           const float* w2, const float* b2, float conv_scale, int B, int HW, cudaStream_t s) {
-    SRB_CUDA(cudaMemsetAsync(pool, 0, (size_t)B * 96 * sizeof(float), s));
     const int slab = 1024;
-    dim3 grid((HW + slab - 1) / slab, B);
+    const int nslab = cab_pool_slabs(HW);
+    dim3 grid(nslab, B);
     chan_sum96_kernel<<<grid, 192, 0, s>>>(cab_out, pool, HW, slab);
     SRB_CUDA(cudaGetLastError());
-    cab_finish_kernel<<<B, 96, 0, s>>>(pool, 1.f / (float)HW, w1, b1, w2, b2, conv_scale, cs);
+    cab_finish_kernel<<<B, 96, 0, s>>>(pool, nslab, 1.f / (float)HW, w1, b1, w2, b2, conv_scale, cs);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
