@@ -355,15 +355,6 @@ static int run_stage1(Ctx& c, Workspace& w, const void* x, int x_dtype, int B, i
     return SRB_OK;
 }
 
-// token-wise MLP shared by HAB and OCAB: x += fc2(gelu(fc1(LN(x))))  (in place on x)
-static int run_mlp(Ctx& c, Workspace& w, const std::string& b, int B, int R, int Rw) {
-    const size_t ntok = (size_t)B * R * Rw;
-    LAUNCH(c, PC_LN, 0.0, layernorm96(w.y, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), w.xn, ntok, c.s));
-    SRB_TRY(tc_layer(c, b + "mlp.fc1", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.hd, 192));
-    SRB_TRY(tc_layer(c, b + "mlp.fc2", w.hd, 192, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
-    return SRB_OK;
-}
-
 // HAT.forward (App. A.2): img fp32 [B,R,Rw] -> o1 fp32 [B,2R,2Rw]
 static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int Rw) {
     const size_t ntok = (size_t)B * R * Rw;
@@ -391,11 +382,11 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
                                             c.F(b + "conv_block.cab.3.attention.1.bias"),
                                             c.F(b + "conv_block.cab.3.attention.3.weight"),
                                             c.F(b + "conv_block.cab.3.attention.3.bias"), 0.01f, B, R * Rw, c.s));
-            // y = ao + cab * (sigmoid(..) * conv_scale);  xn = LN2(y)
-            LAUNCH(c, PC_LN, 0.0, combine_ln96(w.ao, w.c2, w.cs, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), w.y, w.xn,
-                                              ntok, (size_t)R * Rw, c.s));
-            SRB_TRY(tc_layer(c, b + "mlp.fc1", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.hd, 192));
-            SRB_TRY(tc_layer(c, b + "mlp.fc2", w.hd, 192, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
+            // y = (ao + cab * sigmoid(..) * conv_scale) + fc2(GELU(fc1(LN2(.))))  — combine, norm2 and the MLP in one kernel
+            LAUNCH(c, PC_LINEAR, 2.0 * 36864 * (double)ntok,
+                   mlp_fused(w.ao, w.c2, w.cs, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), c.Wt(b + "mlp.fc1.weight"),
+                             c.F(b + "mlp.fc1.bias"), c.Wt(b + "mlp.fc2.weight"), c.F(b + "mlp.fc2.bias"), w.y, ntok,
+                             (size_t)R * Rw, c.s));
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", l);
         const std::string b = buf;
@@ -403,7 +394,10 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
         SRB_TRY(tc_layer(c, b + "qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
         LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const float*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
         SRB_TRY(tc_layer(c, b + "proj", w.ao, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
-        SRB_TRY(run_mlp(c, w, b, B, R, Rw));
+        LAUNCH(c, PC_LINEAR, 2.0 * 36864 * (double)ntok,
+               mlp_fused(w.y, nullptr, nullptr, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), c.Wt(b + "mlp.fc1.weight"),
+                         c.F(b + "mlp.fc1.bias"), c.Wt(b + "mlp.fc2.weight"), c.F(b + "mlp.fc2.bias"), w.y, ntok,
+                         (size_t)R * Rw, c.s));
         // RHAG tail: g = conv(y) + g
         snprintf(buf, sizeof(buf), "stage2.layers.%d.conv", l);
         SRB_TRY(tc_layer(c, buf, w.y, 96, B, R, Rw, ACT_NONE, 0.f, w.g, 96, nullptr, 1.f, w.g, 0, 96));
