@@ -42,6 +42,7 @@ int pack_conv_weight(const float* w, bf16* o, int Cout, int Cin, int taps, cudaS
 }  // namespace srb
 
 using namespace srb;
+namespace srb { extern long long* g_fa_dbg; }
 
 extern "C" {
 
@@ -134,5 +135,9 @@ int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_d
     if (!acc || !wsum || !out) { set_error("blend_finalize: null pointer"); return SRB_E_ARG; }
     return blend_finalize(acc, wsum, out, out_dtype, n, (cudaStream_t)stream);
 }
+
+/* development aid (not in include/srb.h): device buffer [148][8] receiving per-phase cycle totals of the fused
+ * attention kernel; pass NULL to switch off */
+void srb_debug_set_phase_buffer(long long* dev_buf) { g_fa_dbg = dev_buf; }
 
 }  // extern "C"

@@ -19,7 +19,7 @@ constexpr int AP = 104;  // smem row pitch in bf16 (96 + 8): 52 words -> conflic
 
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                                uint32_t b0, uint32_t b1) {
-    asm volatile(
+    asm(
         "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
         : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
@@ -157,6 +157,114 @@ __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16
     }
 }
 
+// Two query m-tiles (rows [32*mh, 32*mh+32)) of one (window, head) at once: the S-MMAs, softmax and PV-MMAs of both
+// tiles are interleaved stage by stage so that the tensor pipe, the MUFU (exp) and the FMA pipe overlap inside one
+// warp.  bias fragments live in shared memory (bf16, fragment order).  `masked` is warp-uniform.
+__device__ __forceinline__ void attend_head_pair(bf16* sQ, const bf16* sK, const bf16* sV, const bf16* bias_h,
+                                                 const int* srid, bool masked, int h, int lane, int mh) {
+    const int g = lane >> 2, t = lane & 3;
+    uint32_t qa[2][4];
+    load_a_frag(qa[0], sQ, 32 * mh, h * 16, lane);
+    load_a_frag(qa[1], sQ, 32 * mh + 16, h * 16, lane);
+    float s[2][8][4];
+#pragma unroll
+    for (int j = 0; j < 8; j += 2) {
+        uint32_t kb[4];
+        load_b_frag2(kb, sK, 8 * j, h * 16, lane);
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+            s[m][j][0] = s[m][j][1] = s[m][j][2] = s[m][j][3] = 0.f;
+            s[m][j + 1][0] = s[m][j + 1][1] = s[m][j + 1][2] = s[m][j + 1][3] = 0.f;
+            mma_bf16_16816(s[m][j], qa[m][0], qa[m][1], qa[m][2], qa[m][3], kb[0], kb[1]);
+            mma_bf16_16816(s[m][j + 1], qa[m][0], qa[m][1], qa[m][2], qa[m][3], kb[2], kb[3]);
+        }
+    }
+    float mx[2][2], l[2][2];
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+        const int mt = 2 * mh + m;
+        mx[m][0] = mx[m][1] = -1e30f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint2 raw = *(const uint2*)(bias_h + ((mt * 8 + j) * 32 + lane) * 4);
+            const float2 lo = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
+            const float2 hi = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
+            s[m][j][0] = fmaf(s[m][j][0], 0.25f, lo.x);
+            s[m][j][1] = fmaf(s[m][j][1], 0.25f, lo.y);
+            s[m][j][2] = fmaf(s[m][j][2], 0.25f, hi.x);
+            s[m][j][3] = fmaf(s[m][j][3], 0.25f, hi.y);
+        }
+        if (masked) {  // shift mask (-100 across region borders): only windows touching the last window row / column
+            const int rid0 = srid[16 * mt + g], rid1 = srid[16 * mt + g + 8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int rc0 = srid[8 * j + 2 * t], rc1 = srid[8 * j + 2 * t + 1];
+                if (rc0 != rid0) s[m][j][0] -= 100.f;
+                if (rc1 != rid0) s[m][j][1] -= 100.f;
+                if (rc0 != rid1) s[m][j][2] -= 100.f;
+                if (rc1 != rid1) s[m][j][3] -= 100.f;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            mx[m][0] = fmaxf(mx[m][0], fmaxf(s[m][j][0], s[m][j][1]));
+            mx[m][1] = fmaxf(mx[m][1], fmaxf(s[m][j][2], s[m][j][3]));
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            mx[m][e] = fmaxf(mx[m][e], __shfl_xor_sync(0xffffffffu, mx[m][e], 1));
+            mx[m][e] = fmaxf(mx[m][e], __shfl_xor_sync(0xffffffffu, mx[m][e], 2));
+            l[m][e] = 0.f;
+        }
+    float o[2][2][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) o[m][nt][0] = o[m][nt][1] = o[m][nt][2] = o[m][nt][3] = 0.f;
+#pragma unroll
+    for (int kt = 0; kt < 4; ++kt) {
+        uint32_t vb[4];
+        ldsm_x4_trans(vb, sV + (16 * kt + (lane & 7) + ((lane >> 3) & 1) * 8) * AP + h * 16 + (lane >> 4) * 8);
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+            float e[2][4];
+#pragma unroll
+            for (int jj = 0; jj < 2; ++jj) {
+                const int j = 2 * kt + jj;
+                e[jj][0] = __expf(s[m][j][0] - mx[m][0]);
+                e[jj][1] = __expf(s[m][j][1] - mx[m][0]);
+                e[jj][2] = __expf(s[m][j][2] - mx[m][1]);
+                e[jj][3] = __expf(s[m][j][3] - mx[m][1]);
+                l[m][0] += e[jj][0] + e[jj][1];
+                l[m][1] += e[jj][2] + e[jj][3];
+            }
+            const uint32_t p0 = pack_bf16(e[0][0], e[0][1]), p1 = pack_bf16(e[0][2], e[0][3]);
+            const uint32_t p2 = pack_bf16(e[1][0], e[1][1]), p3 = pack_bf16(e[1][2], e[1][3]);
+            mma_bf16_16816(o[m][0], p0, p1, p2, p3, vb[0], vb[1]);
+            mma_bf16_16816(o[m][1], p0, p1, p2, p3, vb[2], vb[3]);
+        }
+    }
+    __syncwarp();  // every lane has read its Q fragments before they are overwritten
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+        float l0 = l[m][0], l1 = l[m][1];
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        const float i0 = 1.f / l0, i1 = 1.f / l1;
+        const int r0 = 32 * mh + 16 * m + g, r1 = r0 + 8;
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+            *(uint32_t*)(sQ + r0 * AP + h * 16 + 8 * nt + 2 * t) = pack_bf16(o[m][nt][0] * i0, o[m][nt][1] * i0);
+            *(uint32_t*)(sQ + r1 * AP + h * 16 + 8 * nt + 2 * t) = pack_bf16(o[m][nt][2] * i1, o[m][nt][3] * i1);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // HAB: persistent, 2 window slots x 6 warps
 // ---------------------------------------------------------------------------------------------------------------
@@ -249,7 +357,7 @@ int window_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, i
 constexpr int OCA_SMEM = (64 + 2 * 144) * AP * 2 + 64 * 4;
 
 __global__ void __launch_bounds__(192)
-ocab_attn_kernel(const bf16* __restrict__ qkv, const float* __restrict__ bias_frag, bf16* __restrict__ out, int H,
+ocab_attn_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ bias_frag, bf16* __restrict__ out, int H,
                  int W) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     bf16* sQ = (bf16*)smem_raw;
@@ -277,7 +385,7 @@ ocab_attn_kernel(const bf16* __restrict__ qkv, const float* __restrict__ bias_fr
     }
     __syncthreads();
     const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    attend_head<144, float>(sQ, sK, sV, bias_frag + (size_t)h * (4 * 18 * 32 * 4), nullptr, false, h, lane);
+    attend_head<144, bf16>(sQ, sK, sV, bias_frag + (size_t)h * (4 * 18 * 32 * 4), nullptr, false, h, lane);
     __syncthreads();
     for (int i = threadIdx.x; i < 64 * 12; i += 192) {
         const int n = i / 12, c = i % 12;
@@ -285,7 +393,7 @@ ocab_attn_kernel(const bf16* __restrict__ qkv, const float* __restrict__ bias_fr
     }
 }
 
-int ocab_attention(const bf16* qkv, const float* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s) {
+int ocab_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s) {
     if (H % 8 || W % 8) { set_error("attention: H=%d W=%d must be multiples of the window size 8", H, W); return SRB_E_SHAPE; }
     static bool attr = false;
     if (!attr) {
@@ -360,6 +468,7 @@ struct FusedAttnArgs {
     bf16* xn;             // [B,H,W,96] LN1(x)
     bf16* t;              // [B,H,W,96] x + proj(attn)
     int B, H, W, shift;
+    long long* dbg;  // optional [grid][8] per-phase cycle totals (development aid)
 };
 
 constexpr int FA_THREADS = 384;  // 12 warps: (m-half, head / column group)
@@ -392,19 +501,24 @@ hab_fused_attn_kernel(const FusedAttnArgs a) {
     if (tid < 288) sbq[tid] = a.bqkv[tid];
     if (tid < 96) { sbp[tid] = a.bproj[tid]; sg[tid] = a.ln_g[tid]; sb[tid] = a.ln_b[tid]; }
 
+    // each thread always moves the same two 16-byte chunks of a window tile: (token n, chunk ck) fixed per thread
+    const int ld_n0 = tid / 12, ld_c0 = tid % 12, ld_n1 = (tid + FA_THREADS) / 12, ld_c1 = (tid + FA_THREADS) % 12;
     auto issue_load = [&](int win, int buf) {
         bf16* dst = sX + buf * FA_TILE;
         int* mt_ = meta + buf * 128;
         const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
         const size_t img = (size_t)b * H * W;
-        for (int i = tid; i < 64 * 12; i += FA_THREADS) {
-            const int n = i / 12, ck = i % 12;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int n = k ? ld_n1 : ld_n0, ck = k ? ld_c1 : ld_c0;
             const int ys = wy * 8 + (n >> 3), xs = wx * 8 + (n & 7);  // rolled-image coordinates
-            const int y = (ys + shift) % H, x = (xs + shift) % W;     // torch.roll(-shift)
-            const size_t pix = img + (size_t)y * W + x;
-            cp_async16(dst + n * AP + ck * 8, a.x + pix * 96 + ck * 8);
+            int y = ys + shift, x = xs + shift;                       // torch.roll(-shift): rolled[i] = orig[i+shift]
+            if (y >= H) y -= H;
+            if (x >= W) x -= W;
+            const int pix = y * W + x;
+            cp_async16(dst + n * AP + ck * 8, a.x + (img + pix) * 96 + ck * 8);
             if (ck == 0) {
-                mt_[n] = (int)(pix - img);
+                mt_[n] = pix;
                 const int rh = ys < H - 8 ? 0 : (ys < H - 4 ? 1 : 2);
                 const int rw = xs < W - 8 ? 0 : (xs < W - 4 ? 1 : 2);
                 mt_[64 + n] = rh * 3 + rw;
@@ -416,12 +530,16 @@ hab_fused_attn_kernel(const FusedAttnArgs a) {
     if (win < nwin) issue_load(win, 0);
     cp_async_commit();
     int it = 0;
+    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tprev = clock64();
+#define SRB_PHASE(i) do { if (a.dbg && tid == 0) { const long long tn = clock64(); ph[i] += tn - tprev; tprev = tn; } } while (0)
     for (; win < nwin; win += gridDim.x, ++it) {
         const int buf = it & 1;
         if (win + (int)gridDim.x < nwin) issue_load(win + gridDim.x, buf ^ 1);
         cp_async_commit();
         cp_async_wait<1>();
         __syncthreads();
+        SRB_PHASE(0);
         bf16* x_t = sX + buf * FA_TILE;
         const int* mt_ = meta + buf * 128;
         const size_t img = (size_t)(win / (nwx * nwy)) * H * W;
@@ -467,6 +585,7 @@ hab_fused_attn_kernel(const FusedAttnArgs a) {
             }
         }
         __syncthreads();
+        SRB_PHASE(1);
         // xn -> HBM for the CAB branch (coalesced 16-byte chunks)
         for (int i = tid; i < 64 * 12; i += FA_THREADS) {
             const int n = i / 12, c = i % 12;
@@ -510,11 +629,17 @@ hab_fused_attn_kernel(const FusedAttnArgs a) {
             }
         }
         __syncthreads();
+        SRB_PHASE(2);
 
         // ---- per-head attention (head ng, query rows of m-half mh); output overwrites the Q tile ----
-        attend_head<64, bf16>(sQKV, sQKV + FA_TILE, sQKV + 2 * FA_TILE, sBias + ng * (4 * 8 * 32 * 4), mt_ + 64,
-                              shift > 0, ng, lane, 2 * mh, 2 * mh + 2);
+        {
+            const int wxx = win % nwx, wyy = (win / nwx) % nwy;
+            const bool masked = shift > 0 && (wxx == nwx - 1 || wyy == nwy - 1);  // other windows: one region, no mask
+            attend_head_pair(sQKV, sQKV + FA_TILE, sQKV + 2 * FA_TILE, sBias + ng * (4 * 8 * 32 * 4), mt_ + 64, masked,
+                             ng, lane, mh);
+        }
         __syncthreads();
+        SRB_PHASE(3);
 
         // ---- t = x + attn @ Wproj^T + b : warp (mh, ng) owns rows [32mh, +32) x columns [16ng, +16) ----
         {
@@ -552,14 +677,21 @@ hab_fused_attn_kernel(const FusedAttnArgs a) {
             }
         }
         __syncthreads();
+        SRB_PHASE(4);
         for (int i = tid; i < 64 * 12; i += FA_THREADS) {
             const int n = i / 12, c = i % 12;
             *(uint4*)(a.t + (img + mt_[n]) * 96 + c * 8) = *(const uint4*)(x_t + n * AP + c * 8);
         }
         __syncthreads();  // x tile / meta / xn / qkv tiles free for the next window
+        SRB_PHASE(5);
     }
     cp_async_wait<0>();
+    if (a.dbg && tid == 0)
+        for (int i = 0; i < 8; ++i) a.dbg[blockIdx.x * 8 + i] = ph[i];
+#undef SRB_PHASE
 }
+
+long long* g_fa_dbg = nullptr;  // set through srb_debug_set_phase_buffer (development aid)
 
 int hab_fused_attention(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
                         const bf16* bias_frag, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
@@ -573,6 +705,7 @@ int hab_fused_attention(const bf16* x, const float* ln_g, const float* ln_b, con
     FusedAttnArgs a;
     a.x = x; a.ln_g = ln_g; a.ln_b = ln_b; a.wqkv = wqkv; a.bqkv = bqkv; a.bias_frag = bias_frag; a.wproj = wproj;
     a.bproj = bproj; a.xn = xn; a.t = t; a.B = B; a.H = H; a.W = W; a.shift = shift;
+    a.dbg = g_fa_dbg;
     const int nwin = B * (H / 8) * (W / 8);
     hab_fused_attn_kernel<<<nwin < 148 ? nwin : 148, FA_THREADS, FA_SMEM, s>>>(a);
     SRB_CUDA(cudaGetLastError());

@@ -157,7 +157,7 @@ int model_pack(const void* const* params, int n, void* packed, size_t packed_byt
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.relative_position_bias_table", l);
         const float* tab = (const float*)(base + m.params[m.index.at(buf)].off);
-        SRB_TRY(expand_rel_bias_f32(tab, 361, idx_oca, 144, (float*)(base + m.bias_oca_off[l]), s));
+        SRB_TRY(expand_rel_bias_bf16(tab, 361, idx_oca, 144, (bf16*)(base + m.bias_oca_off[l]), s));
     }
     return SRB_OK;
 }
@@ -392,7 +392,7 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
         const std::string b = buf;
         LAUNCH(c, PC_LN, 0.0, layernorm96(w.y, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
         SRB_TRY(tc_layer(c, b + "qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
-        LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const float*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
+        LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const bf16*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
         SRB_TRY(tc_layer(c, b + "proj", w.ao, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
         LAUNCH(c, PC_LINEAR, 2.0 * 36864 * (double)ntok,
                mlp_fused(w.y, nullptr, nullptr, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), c.Wt(b + "mlp.fc1.weight"),

@@ -83,9 +83,17 @@ int rrdb_conv_first(const void* x, int x_dtype, const float* w, const float* bia
 // K7/K17: 3x3 conv with ONE output channel (conv_last of both stages), NHWC bf16 [B,H,W,64] -> fp32 [B,H,W].
 // 8 lanes per pixel, each owning 8 input channels (16-byte loads, 4 pixels = 512 contiguous bytes per warp load).
 // ---------------------------------------------------------------------------------------------------------------
+constexpr int C1_TH = 8, C1_TW = 32;                          // output tile
+constexpr int C1_PH = C1_TH + 2, C1_PW = C1_TW + 2;           // input patch with halo
+constexpr int C1_SMEM = C1_PH * C1_PW * 128;                  // 64 bf16 channels per pixel
+
 __global__ void __launch_bounds__(256)
 conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restrict__ w /*[1][64][3][3]*/,
                   const float* __restrict__ bias, float* __restrict__ out, int B, int H, int W) {
+    // The 3x3 x 64-channel dot product re-reads every input pixel 9 times: stage the haloed patch in shared memory once
+    // (coalesced 16-byte chunks, zero fill = conv padding) and let 8 lanes per output pixel (8 channels each) read it
+    // back conflict-free (4 pixels x 128 contiguous bytes per warp load).
+    extern __shared__ __align__(16) uint8_t c1_smem[];
     const int sub = threadIdx.x & 7;
     float wr[72];  // [tap][8 channels of this lane]
 #pragma unroll
@@ -93,17 +101,29 @@ conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restric
 #pragma unroll
         for (int j = 0; j < 8; ++j) wr[t * 8 + j] = __ldg(w + (sub * 8 + j) * 9 + t);
     const float b0 = bias[0];
-    const size_t npix = (size_t)B * H * W;
-    for (size_t pix = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 3; pix < npix;
-         pix += ((size_t)gridDim.x * blockDim.x) >> 3) {
-        const int x = pix % W, y = (pix / W) % H;
-        const size_t b = pix / ((size_t)W * H);
-        float s = 0.f;
+    const int tiles_x = W / C1_TW, tiles_y = H / C1_TH;
+    const int ntiles = B * tiles_x * tiles_y;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, b = tile / (tiles_x * tiles_y);
+        const int y0 = ty * C1_TH - 1, x0 = tx * C1_TW - 1;
+        __syncthreads();  // previous tile fully consumed
+        for (int i = threadIdx.x; i < C1_PH * C1_PW * 8; i += 256) {
+            const int ck = i & 7, p = i >> 3;
+            const int py = p / C1_PW, px = p % C1_PW;
+            const int y = y0 + py, x = x0 + px;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (y >= 0 && y < H && x >= 0 && x < W)
+                v = __ldg((const uint4*)(in + (((size_t)b * H + y) * W + x) * pitch) + ck);
+            *(uint4*)(c1_smem + p * 128 + ck * 16) = v;
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (int pass = 0; pass < C1_TH; ++pass) {  // 32 pixels (one tile row) per pass
+            const int oy = pass, ox = threadIdx.x >> 3;
+            float s = 0.f;
 #pragma unroll
-        for (int t = 0; t < 9; ++t) {
-            const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
-            if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-                const uint4 v = __ldg((const uint4*)(in + ((b * H + yy) * W + xx) * pitch + sub * 8));
+            for (int t = 0; t < 9; ++t) {
+                const uint4 v = *(const uint4*)(c1_smem + ((oy + t / 3) * C1_PW + ox + t % 3) * 128 + sub * 16);
                 const __nv_bfloat162* h2 = (const __nv_bfloat162*)&v;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
@@ -112,20 +132,25 @@ conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restric
                     s = fmaf(f.y, wr[t * 8 + 2 * k + 1], s);
                 }
             }
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            s += __shfl_xor_sync(0xffffffffu, s, 4);
+            if (sub == 0) out[((size_t)b * H + ty * C1_TH + oy) * W + tx * C1_TW + ox] = s + b0;
         }
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        if (sub == 0) out[pix] = s + b0;
     }
 }
 
 int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, float* out, int B, int H, int W,
                cudaStream_t s) {
-    const size_t threads = (size_t)B * H * W * 8;
-    int grid = (int)((threads + 255) / 256);
-    if (grid > 148 * 16) grid = 148 * 16;
-    conv_cout1_kernel<<<grid, 256, 0, s>>>(in, pitch, w, bias, out, B, H, W);
+    if (H % C1_TH || W % C1_TW) { set_error("conv_cout1: H=%d W=%d must be multiples of %dx%d", H, W, C1_TH, C1_TW); return SRB_E_SHAPE; }
+    static bool attr = false;
+    if (!attr) {
+        SRB_CUDA(cudaFuncSetAttribute(conv_cout1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C1_SMEM));
+        attr = true;
+    }
+    const int ntiles = B * (H / C1_TH) * (W / C1_TW);
+    int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;
+    conv_cout1_kernel<<<grid, 256, C1_SMEM, s>>>(in, pitch, w, bias, out, B, H, W);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
