@@ -76,6 +76,17 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
                        int taps, int act, float slope, float alpha1, const void* res1, int res1_f32, int res1_pitch,
                        float alpha2, const void* res2, int res2_f32, int res2_pitch, const float* res2_cs,
                        int pixel_shuffle, void* stream);
+/* Token-wise MLP branch of a HAT block (HAB / OCAB; upstream hat_arch.py `x = x + mlp(norm2(x))`, reached from
+ * src/architecture.py:78) as ONE tcgen05 kernel:   y0 = t + cab*cs[b,:] (cab/cs may be NULL: y0 = t);
+ *   y = y0 + fc2(GELU(fc1(LayerNorm(y0)))).   t, cab, y: bf16 [ntok,96] (y may alias t); cs: fp32 [B,96];
+ * w1_folded bf16 [192][96] / b1_folded fp32 [192]: fc1 with the LayerNorm affine folded in (srb_fold_ln_linear);
+ * w2_packed bf16 [96][192] (srb_pack_conv_weight, taps=1); ntok and tok_per_img must be multiples of 128.
+ * srb_fold_ln_linear: W'[n][k] = W[n][k]*gamma[k] (bf16), b'[n] = b[n] + sum_k W[n][k]*beta[k]; fp32 device inputs,
+ * W [N][K] as stored by nn.Linear. */
+int srb_fold_ln_linear(const float* w, const float* b, const float* gamma, const float* beta, void* w_folded,
+                       float* b_folded, int N, int K, void* stream);
+int srb_mlp_branch(const void* t, const void* cab, const float* cs, const void* w1_folded, const float* b1_folded,
+                   const void* w2_packed, const float* b2, void* y, size_t ntok, size_t tok_per_img, void* stream);
 /* fp32 [Cout,Cin,kh,kw] (PyTorch) -> bf16 [kh*kw][Cout][Cin] */
 int srb_pack_conv_weight(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream);
 

@@ -78,6 +78,25 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
     return conv_tc_launch(a, (cudaStream_t)stream);
 }
 
+int srb_fold_ln_linear(const float* w, const float* b, const float* gamma, const float* beta, void* w_folded,
+                       float* b_folded, int N, int K, void* stream) {
+    if (!w || !b || !gamma || !beta || !w_folded || !b_folded || N <= 0 || K <= 0) {
+        set_error("fold_ln_linear: bad args");
+        return SRB_E_ARG;
+    }
+    return fold_ln_linear(w, b, gamma, beta, (bf16*)w_folded, b_folded, N, K, (cudaStream_t)stream);
+}
+
+int srb_mlp_branch(const void* t, const void* cab, const float* cs, const void* w1_folded, const float* b1_folded,
+                   const void* w2_packed, const float* b2, void* y, size_t ntok, size_t tok_per_img, void* stream) {
+    if (!t || !w1_folded || !b1_folded || !w2_packed || !b2 || !y || ntok == 0 || (cab && !cs)) {
+        set_error("mlp_branch: bad args");
+        return SRB_E_ARG;
+    }
+    return mlp_fused((const bf16*)t, (const bf16*)cab, cs, (const bf16*)w1_folded, b1_folded, (const bf16*)w2_packed,
+                     b2, (bf16*)y, ntok, tok_per_img, (cudaStream_t)stream);
+}
+
 int srb_param_count(void) { return model_param_count(); }
 const char* srb_param_name(int i) { return model_param_name(i); }
 int64_t srb_param_numel(int i) { return model_param_numel(i); }

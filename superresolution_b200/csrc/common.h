@@ -53,5 +53,6 @@ struct ConvArgs {
 };
 
 int conv_tc_launch(const ConvArgs& a, cudaStream_t stream);
+int num_sms();  // SM count of the current device (cached)
 
 }  // namespace srb

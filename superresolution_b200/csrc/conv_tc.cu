@@ -449,7 +449,7 @@ static int encode_bf16_map(CUtensorMap* m, const void* ptr, int rank, const cuui
 }
 
 static int g_num_sms = 0;
-static int num_sms() {
+int num_sms() {
     if (g_num_sms == 0) {
         int dev = 0, n = 0;
         if (cudaGetDevice(&dev) == cudaSuccess &&

@@ -28,6 +28,7 @@ struct ModelDesc {
     std::unordered_map<std::string, int> index;
     size_t bias_sa_off[24];
     size_t bias_oca_off[4];
+    size_t mlp_w1f_off[28], mlp_b1f_off[28];  // norm2-folded fc1 (24 HAB then 4 OCAB), see fold_ln_linear
     size_t packed_bytes;
 };
 
@@ -111,6 +112,10 @@ static void build_desc(ModelDesc& m) {
     // ---- derived: gathered relative-position bias tables ----
     for (int i = 0; i < 24; ++i) { m.bias_sa_off[i] = off; off = align256(off + 6 * 64 * 64 * 2); }  // bf16, fragment order
     for (int i = 0; i < 4; ++i) { m.bias_oca_off[i] = off; off = align256(off + 6 * 64 * 144 * 4); }
+    for (int i = 0; i < 28; ++i) {
+        m.mlp_w1f_off[i] = off; off = align256(off + 192 * 96 * 2);
+        m.mlp_b1f_off[i] = off; off = align256(off + 192 * 4);
+    }
     m.packed_bytes = off;
 }
 
@@ -158,6 +163,16 @@ int model_pack(const void* const* params, int n, void* packed, size_t packed_byt
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.relative_position_bias_table", l);
         const float* tab = (const float*)(base + m.params[m.index.at(buf)].off);
         SRB_TRY(expand_rel_bias_bf16(tab, 361, idx_oca, 144, (bf16*)(base + m.bias_oca_off[l]), s));
+    }
+    // norm2 folded into mlp.fc1 (from the fp32 originals: one bf16 rounding)
+    auto src = [&](const std::string& name) { return (const float*)params[m.index.at(name)]; };
+    for (int i = 0; i < 28; ++i) {
+        if (i < 24) snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.", i / 6, i % 6);
+        else snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", i - 24);
+        const std::string b = buf;
+        SRB_TRY(fold_ln_linear(src(b + "mlp.fc1.weight"), src(b + "mlp.fc1.bias"), src(b + "norm2.weight"),
+                               src(b + "norm2.bias"), (bf16*)(base + m.mlp_w1f_off[i]),
+                               (float*)(base + m.mlp_b1f_off[i]), 192, 96, s));
     }
     return SRB_OK;
 }
@@ -384,9 +399,9 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
                                             c.F(b + "conv_block.cab.3.attention.3.bias"), 0.01f, B, R * Rw, c.s));
             // y = (ao + cab * sigmoid(..) * conv_scale) + fc2(GELU(fc1(LN2(.))))  — combine, norm2 and the MLP in one kernel
             LAUNCH(c, PC_LINEAR, 2.0 * 36864 * (double)ntok,
-                   mlp_fused(w.ao, w.c2, w.cs, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), c.Wt(b + "mlp.fc1.weight"),
-                             c.F(b + "mlp.fc1.bias"), c.Wt(b + "mlp.fc2.weight"), c.F(b + "mlp.fc2.bias"), w.y, ntok,
-                             (size_t)R * Rw, c.s));
+                   mlp_fused(w.ao, w.c2, w.cs, (const bf16*)(pk + c.m->mlp_w1f_off[l * 6 + j]),
+                             (const float*)(pk + c.m->mlp_b1f_off[l * 6 + j]), c.Wt(b + "mlp.fc2.weight"),
+                             c.F(b + "mlp.fc2.bias"), w.y, ntok, (size_t)R * Rw, c.s));
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", l);
         const std::string b = buf;
@@ -395,9 +410,9 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
         LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const bf16*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
         SRB_TRY(tc_layer(c, b + "proj", w.ao, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
         LAUNCH(c, PC_LINEAR, 2.0 * 36864 * (double)ntok,
-               mlp_fused(w.y, nullptr, nullptr, c.F(b + "norm2.weight"), c.F(b + "norm2.bias"), c.Wt(b + "mlp.fc1.weight"),
-                         c.F(b + "mlp.fc1.bias"), c.Wt(b + "mlp.fc2.weight"), c.F(b + "mlp.fc2.bias"), w.y, ntok,
-                         (size_t)R * Rw, c.s));
+               mlp_fused(w.y, nullptr, nullptr, (const bf16*)(pk + c.m->mlp_w1f_off[24 + l]),
+                         (const float*)(pk + c.m->mlp_b1f_off[24 + l]), c.Wt(b + "mlp.fc2.weight"),
+                         c.F(b + "mlp.fc2.bias"), w.y, ntok, (size_t)R * Rw, c.s));
         // RHAG tail: g = conv(y) + g
         snprintf(buf, sizeof(buf), "stage2.layers.%d.conv", l);
         SRB_TRY(tc_layer(c, buf, w.y, 96, B, R, Rw, ACT_NONE, 0.f, w.g, 96, nullptr, 1.f, w.g, 0, 96));

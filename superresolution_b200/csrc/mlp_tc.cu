@@ -1,0 +1,396 @@
+// Fused token-wise MLP branch of HAB / OCAB on tcgen05 (sm_100a):
+//     y0 = t + cab * cs[b,:]          (HAB: attention branch + CAB * sigmoid(...) * conv_scale; OCAB: y0 = t)
+//     y  = y0 + fc2( GELU( fc1( LayerNorm(y0) ) ) )
+// Replaces norm2 / mlp.fc1 / act / mlp.fc2 / residual of the un-vendored HAT blocks (call site src/architecture.py:78).
+//
+// One persistent CTA per SM walks 128-token tiles.  Both GEMMs run on the 5th-gen tensor cores with the accumulators
+// in TMEM; the 192-wide hidden activation never leaves the SM.  16 ALU warps + 1 MMA warp + 1 TMEM-allocator warp:
+//   LN(i+1):  4 lanes per token (coalesced 64-byte row segments), t (+cab*cs) -> fp32 statistics by quad shuffles ->
+//             (v - mean) * rstd as the bf16 A operand of fc1 (the LayerNorm affine is folded into fc1 at pack time:
+//             W1' = W1 diag(gamma), b1' = b1 + W1 beta), y0 (bf16) parked in the output staging buffer
+//   GELU(i):  D1 (TMEM 128x192 fp32) -> GELU -> bf16 A operand of fc2; thread = TMEM lane (row), 48 columns
+//   EPI(i):   D2 (TMEM 128x96 fp32) + y0 (smem, in place) -> one 24 KB bulk store per tile
+//   biases ride in the GEMMs: the A operands carry two constant 1.0 columns in an extra k-step and the weight planes
+//   hold bias_hi / bias_lo (bf16 split, ~16 mantissa bits) there, so no epilogue touches a bias vector.
+// ALU order GELU(i) -> LN(i+1) -> EPI(i) hides both MMAs behind ALU work and makes every buffer hazard implicit.
+// Operand layout: un-swizzled K-major "planes" [k/8][row][8 bf16] (core matrix = 8 rows x 16 B contiguous; LBO = plane
+// pitch, SBO = 128 B; validated on B200 by tools/probe_umma.cu "nosw planes"): 16-byte row writes are bank-conflict
+// free and K = 96 / 192 need no padding.  Weights (fc1 192x96, fc2 96x192) stay resident in smem.
+#include <cstring>
+
+#include "act.cuh"
+#include "common.h"
+#include "ops.h"
+#include "ptx.cuh"
+
+namespace srb {
+
+namespace {
+
+constexpr int kAluWarps = 16;
+constexpr int kAluThreads = kAluWarps * 32;
+constexpr int kMlpThreads = kAluThreads + 64;
+constexpr int A1_PITCH = 128 * 16 + 32;  // plane pitch; the 32-byte skew makes the 4-lanes-per-row LN stores conflict free
+constexpr int A1_PLANES = 12 + 2;        // + one k-step carrying the constant-one columns (bias)
+constexpr int A2_PITCH = 128 * 16;
+constexpr int A2_PLANES = 24 + 2;
+constexpr int W1_PITCH = 192 * 16;
+constexpr int W2_PITCH = 96 * 16;
+constexpr int Y_BYTES = 128 * 96 * 2;    // dense token tile (= its global layout)
+constexpr int OFF_A1 = 0;
+constexpr int OFF_A2 = OFF_A1 + A1_PLANES * A1_PITCH;
+constexpr int OFF_W1 = OFF_A2 + A2_PLANES * A2_PITCH;
+constexpr int OFF_W2 = OFF_W1 + A1_PLANES * W1_PITCH;
+constexpr int OFF_Y = OFF_W2 + A2_PLANES * W2_PITCH;
+constexpr int OFF_BAR = OFF_Y + 2 * Y_BYTES;
+constexpr int MLP_TC_SMEM = OFF_BAR + 64;
+constexpr uint32_t D1_COL = 0, D2_COL = 192, MLP_TMEM_COLS = 512;
+static_assert(MLP_TC_SMEM <= 227 * 1024, "shared memory budget");
+static_assert(OFF_A2 % 16 == 0 && OFF_W1 % 16 == 0 && OFF_W2 % 16 == 0 && OFF_Y % 16 == 0 && OFF_BAR % 8 == 0, "align");
+
+struct MlpArgs {
+    const bf16* t;
+    const bf16* cab;   // nullable
+    const float* cs;   // [B][96], nullable with cab
+    const bf16* w1;    // [192][96]  LayerNorm-folded fc1 weight
+    const float* b1;   // [192]      LayerNorm-folded fc1 bias
+    const bf16* w2;    // [96][192]
+    const float* b2;
+    bf16* y;
+    uint32_t ntiles, tiles_per_img;
+};
+
+__device__ __forceinline__ uint32_t packbf(float lo, float hi) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *(uint32_t*)&h;
+}
+__device__ __forceinline__ float2 unpackbf(uint32_t v) { return __bfloat1622float2(*(const __nv_bfloat162*)&v); }
+// {bias_hi, bias_lo, 0 x 6} as one 16-byte k-group
+__device__ __forceinline__ uint4 bias_split(float b) {
+    const bf16 hi = __float2bfloat16_rn(b);
+    const bf16 lo = __float2bfloat16_rn(b - __bfloat162float(hi));
+    return make_uint4((uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16), 0u, 0u, 0u);
+}
+
+__global__ void __launch_bounds__(kMlpThreads, 1)
+mlp_tc_kernel(const MlpArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sA1 = smem + OFF_A1;
+    uint8_t* sA2 = smem + OFF_A2;
+    uint8_t* sW1 = smem + OFF_W1;
+    uint8_t* sW2 = smem + OFF_W2;
+    uint8_t* sY = smem + OFF_Y;
+    uint64_t* bars = (uint64_t*)(smem + OFF_BAR);
+    uint64_t* bar_a1 = bars + 0;  // A1 (normalised tokens) written          count kAluThreads
+    uint64_t* bar_a2 = bars + 1;  // A2 (GELU hidden) written                 count kAluThreads
+    uint64_t* bar_d1 = bars + 2;  // fc1 accumulator complete                 count 1 (tcgen05.commit)
+    uint64_t* bar_d2 = bars + 3;  // fc2 accumulator complete                 count 1
+    uint32_t* tmem_slot = (uint32_t*)(bars + 4);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        mbar_init(bar_a1, kAluThreads); mbar_init(bar_a2, kAluThreads); mbar_init(bar_d1, 1); mbar_init(bar_d2, 1);
+        fence_barrier_init();
+    }
+    if (warp == kAluWarps + 1) { tmem_alloc(tmem_slot, MLP_TMEM_COLS); tmem_relinquish(); }
+    // weights are constants of the launch: stage them before waiting on the producer kernel (PDL prologue overlap)
+    for (int i = tid; i < 12 * 192; i += kMlpThreads) {
+        const int kg = i / 192, n = i % 192;
+        *(uint4*)(sW1 + kg * W1_PITCH + n * 16) = __ldg((const uint4*)a.w1 + n * 12 + kg);
+    }
+    for (int i = tid; i < 24 * 96; i += kMlpThreads) {
+        const int kg = i / 96, n = i % 96;
+        *(uint4*)(sW2 + kg * W2_PITCH + n * 16) = __ldg((const uint4*)a.w2 + n * 24 + kg);
+    }
+    const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+    const uint4 ones4 = make_uint4(0x3F803F80u, 0u, 0u, 0u);  // {1.0, 1.0, 0, 0, 0, 0, 0, 0} bf16
+    if (tid < 192) {
+        *(uint4*)(sW1 + 12 * W1_PITCH + tid * 16) = bias_split(a.b1[tid]);
+        *(uint4*)(sW1 + 13 * W1_PITCH + tid * 16) = zero4;
+    }
+    if (tid < 96) {
+        *(uint4*)(sW2 + 24 * W2_PITCH + tid * 16) = bias_split(a.b2[tid]);
+        *(uint4*)(sW2 + 25 * W2_PITCH + tid * 16) = zero4;
+    }
+    if (tid < 128) {
+        *(uint4*)(sA1 + 12 * A1_PITCH + tid * 16) = ones4;
+        *(uint4*)(sA1 + 13 * A1_PITCH + tid * 16) = zero4;
+        *(uint4*)(sA2 + 24 * A2_PITCH + tid * 16) = ones4;
+        *(uint4*)(sA2 + 25 * A2_PITCH + tid * 16) = zero4;
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (tid == 0) pdl_launch_dependents();
+    pdl_wait();  // t / cab / cs come from the previous kernels in the stream
+
+    const uint32_t first = blockIdx.x, step = gridDim.x;
+    const uint32_t n_my = (a.ntiles > first) ? (a.ntiles - first + step - 1) / step : 0;
+
+    if (warp == kAluWarps) {
+        // ===================== MMA issuer =====================
+        const uint32_t idesc1 = umma_idesc_bf16_f32(128, 192), idesc2 = umma_idesc_bf16_f32(128, 96);
+        const uint32_t a1 = smem_u32(sA1), a2 = smem_u32(sA2), w1 = smem_u32(sW1), w2 = smem_u32(sW2);
+        for (uint32_t i = 0; i < n_my; ++i) {
+            mbar_wait(bar_a1, i & 1);
+            tc_fence_after();
+            if (elect_one()) {
+#pragma unroll
+                for (int ks = 0; ks < A1_PLANES / 2; ++ks)
+                    umma_bf16_ss(tmem_base + D1_COL,
+                                 umma_smem_desc(a1 + ks * 2 * A1_PITCH, A1_PITCH, 128, UMMA_SW_NONE),
+                                 umma_smem_desc(w1 + ks * 2 * W1_PITCH, W1_PITCH, 128, UMMA_SW_NONE), idesc1, ks > 0);
+                umma_commit(bar_d1);
+            }
+            __syncwarp();
+            mbar_wait(bar_a2, i & 1);
+            tc_fence_after();
+            if (elect_one()) {
+#pragma unroll
+                for (int ks = 0; ks < A2_PLANES / 2; ++ks)
+                    umma_bf16_ss(tmem_base + D2_COL,
+                                 umma_smem_desc(a2 + ks * 2 * A2_PITCH, A2_PITCH, 128, UMMA_SW_NONE),
+                                 umma_smem_desc(w2 + ks * 2 * W2_PITCH, W2_PITCH, 128, UMMA_SW_NONE), idesc2, ks > 0);
+                umma_commit(bar_d2);
+            }
+            __syncwarp();
+        }
+    } else if (warp < kAluWarps) {
+        // ===================== ALU warps =====================
+        const int q = warp & 3, h4 = warp >> 2;
+        const int r = q * 32 + lane;                 // GELU / EPI: token row inside the tile == TMEM lane
+        const uint32_t tm_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+        const int ln_row = warp * 8 + (lane >> 2);   // LN: 4 lanes per token, lane j owns 16-byte units j, j+4, j+8
+        const int ln_j = lane & 3;
+        const bool issuer = (tid == 0);
+        const int rot = (lane >> 1) % 3;             // EPI staging rotation (2-way instead of 4-way bank conflicts)
+
+        uint4 pt[3], pc[3];                          // prefetched row thirds of t and cab
+
+        auto issue_loads = [&](uint32_t tile) {
+            const size_t row = (size_t)tile * 128 + ln_row;
+            const uint4* tp = (const uint4*)(a.t + row * 96) + ln_j;
+#pragma unroll
+            for (int m = 0; m < 3; ++m) pt[m] = tp[4 * m];  // plain loads: y may alias t (OCAB runs in place)
+            if (a.cab) {
+                const uint4* cp = (const uint4*)(a.cab + row * 96) + ln_j;
+#pragma unroll
+                for (int m = 0; m < 3; ++m) pc[m] = __ldg(cp + 4 * m);
+            }
+        };
+
+        // combine + LayerNorm (no affine) of the prefetched tile -> A1; residual y0 -> Y staging buffer
+        auto layer_norm = [&](uint32_t tile, uint32_t it) {
+            float v[24];
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                const uint32_t* w = (const uint32_t*)&pt[m];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = unpackbf(w[k]);
+                    v[8 * m + 2 * k] = f.x; v[8 * m + 2 * k + 1] = f.y;
+                }
+            }
+            if (a.cab) {
+                const float4* cs = (const float4*)(a.cs + (size_t)(tile / a.tiles_per_img) * 96) + 2 * ln_j;
+#pragma unroll
+                for (int m = 0; m < 3; ++m) {
+                    const uint32_t* w = (const uint32_t*)&pc[m];
+                    const float4 s0 = __ldg(cs + 8 * m), s1 = __ldg(cs + 8 * m + 1);
+                    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float2 f = unpackbf(w[k]);
+                        v[8 * m + 2 * k] = fmaf(f.x, sc[2 * k], v[8 * m + 2 * k]);
+                        v[8 * m + 2 * k + 1] = fmaf(f.y, sc[2 * k + 1], v[8 * m + 2 * k + 1]);
+                    }
+                }
+            }
+            uint8_t* yb = sY + (it & 1) * Y_BYTES + ln_row * 192;
+#pragma unroll
+            for (int m = 0; m < 3; ++m)
+                *(uint4*)(yb + 16 * (ln_j + 4 * m)) =
+                    make_uint4(packbf(v[8 * m], v[8 * m + 1]), packbf(v[8 * m + 2], v[8 * m + 3]),
+                               packbf(v[8 * m + 4], v[8 * m + 5]), packbf(v[8 * m + 6], v[8 * m + 7]));
+            float s = 0.f;
+#pragma unroll
+            for (int k = 0; k < 24; ++k) s += v[k];
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            const float mean = s * (1.f / 96.f);
+            float m2 = 0.f;
+#pragma unroll
+            for (int k = 0; k < 24; ++k) { v[k] -= mean; m2 = fmaf(v[k], v[k], m2); }
+            m2 += __shfl_xor_sync(0xffffffffu, m2, 1);
+            m2 += __shfl_xor_sync(0xffffffffu, m2, 2);
+            const float rs = rsqrtf(m2 * (1.f / 96.f) + 1e-5f);
+#pragma unroll
+            for (int m = 0; m < 3; ++m)
+                *(uint4*)(sA1 + (ln_j + 4 * m) * A1_PITCH + ln_row * 16) =
+                    make_uint4(packbf(v[8 * m] * rs, v[8 * m + 1] * rs), packbf(v[8 * m + 2] * rs, v[8 * m + 3] * rs),
+                               packbf(v[8 * m + 4] * rs, v[8 * m + 5] * rs), packbf(v[8 * m + 6] * rs, v[8 * m + 7] * rs));
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(bar_a1);
+        };
+
+        if (n_my > 0) {
+            issue_loads(first);
+            layer_norm(first, 0);
+            if (n_my > 1) issue_loads(first + step);
+            named_bar_sync(1, kAluThreads);  // y0(0) visible to the EPI threads even when this CTA has a single tile
+        }
+        for (uint32_t i = 0; i < n_my; ++i) {
+            const uint32_t tile = first + i * step;
+            // ---- (a) GELU(i): D1 -> A2 ----
+            mbar_wait(bar_d1, i & 1);
+            tc_fence_after();
+            {
+                uint32_t acc[48];
+                {
+                    uint32_t lo[32], hi[16];
+                    tmem_ld_32x32b_x32(tm_lane + D1_COL + 48 * h4, lo);
+                    tmem_ld_32x32b_x16(tm_lane + D1_COL + 48 * h4 + 32, hi);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) acc[k] = lo[k];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) acc[32 + k] = hi[k];
+                }
+#pragma unroll
+                for (int u = 0; u < 6; ++u) {
+                    uint4 o4;
+                    uint32_t* ow = (uint32_t*)&o4;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        ow[k] = packbf(gelu_fast(__uint_as_float(acc[8 * u + 2 * k])),
+                                       gelu_fast(__uint_as_float(acc[8 * u + 2 * k + 1])));
+                    *(uint4*)(sA2 + (6 * h4 + u) * A2_PITCH + r * 16) = o4;
+                }
+            }
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(bar_a2);
+            // ---- (b) LN(i+1) -> A1 (fc1(i) has completed: bar_d1 was waited), prefetch tile i+2 ----
+            if (i + 1 < n_my) {
+                // the staging buffer about to receive y0(i+1) was the source of tile i-1's bulk store
+                if (issuer) bulk_wait_group_read<0>();
+                named_bar_sync(1, kAluThreads);
+                layer_norm(tile + step, i + 1);
+                if (i + 2 < n_my) issue_loads(tile + 2 * step);
+            }
+            // ---- (c) EPI(i): D2 + y0 -> Y staging (in place) -> bulk store ----
+            mbar_wait(bar_d2, i & 1);
+            tc_fence_after();
+            {
+                uint32_t acc[24];
+                {
+                    uint32_t lo[16], hi[8];
+                    tmem_ld_32x32b_x16(tm_lane + D2_COL + 24 * h4, lo);
+                    tmem_ld_32x32b_x8(tm_lane + D2_COL + 24 * h4 + 16, hi);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) acc[k] = lo[k];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[16 + k] = hi[k];
+                }
+                uint8_t* yb = sY + (i & 1) * Y_BYTES + r * 192 + 48 * h4;
+                // unit visited at step s is (s + rot) % 3; the data registers are selected, not indexed
+#pragma unroll
+                for (int s3 = 0; s3 < 3; ++s3) {
+                    const int u = (s3 + rot) % 3;
+                    uint4 yy = *(const uint4*)(yb + 16 * u);
+                    const uint32_t* yw = (const uint32_t*)&yy;
+                    uint4 o4;
+                    uint32_t* ow = (uint32_t*)&o4;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float2 f = unpackbf(yw[k]);
+                        const float c0 = u == 0 ? __uint_as_float(acc[2 * k]) : u == 1 ? __uint_as_float(acc[8 + 2 * k])
+                                                                                        : __uint_as_float(acc[16 + 2 * k]);
+                        const float c1 = u == 0 ? __uint_as_float(acc[2 * k + 1]) : u == 1 ? __uint_as_float(acc[9 + 2 * k])
+                                                                                            : __uint_as_float(acc[17 + 2 * k]);
+                        ow[k] = packbf(c0 + f.x, c1 + f.y);
+                    }
+                    *(uint4*)(yb + 16 * u) = o4;
+                }
+            }
+            fence_proxy_async_smem();
+            named_bar_sync(2, kAluThreads);
+            if (issuer) {
+                bulk_store_1d(a.y + (size_t)tile * 128 * 96, sY + (i & 1) * Y_BYTES, Y_BYTES);
+                bulk_commit_group();
+            }
+        }
+        if (issuer) bulk_wait_group<0>();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kAluWarps + 1) tmem_dealloc(tmem_base, MLP_TMEM_COLS);
+}
+
+// W'[n][k] = W[n][k] * gamma[k] (bf16), b'[n] = b[n] + sum_k W[n][k] * beta[k]: LayerNorm affine folded into the
+// following Linear (fp32 inputs, one rounding).  grid = N blocks of 128 threads.
+__global__ void fold_ln_linear_kernel(const float* __restrict__ w, const float* __restrict__ b,
+                                      const float* __restrict__ gamma, const float* __restrict__ beta,
+                                      bf16* __restrict__ w_out, float* __restrict__ b_out, int K) {
+    __shared__ float red[4];
+    const int n = blockIdx.x;
+    float acc = 0.f;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const float wv = w[(size_t)n * K + k];
+        w_out[(size_t)n * K + k] = __float2bfloat16_rn(wv * gamma[k]);
+        acc = fmaf(wv, beta[k], acc);
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) b_out[n] = b[n] + red[0] + red[1] + red[2] + red[3];
+}
+
+}  // namespace
+
+int fold_ln_linear(const float* w, const float* b, const float* gamma, const float* beta, bf16* w_out, float* b_out,
+                   int N, int K, cudaStream_t s) {
+    fold_ln_linear_kernel<<<N, 128, 0, s>>>(w, b, gamma, beta, w_out, b_out, K);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, const float* b1f, const bf16* w2,
+              const float* b2, bf16* y, size_t ntok, size_t tok_per_img, cudaStream_t s) {
+    if (ntok % 128 || tok_per_img % 128) { set_error("mlp_fused: token counts must be multiples of 128"); return SRB_E_SHAPE; }
+    if (((uintptr_t)t | (uintptr_t)y | (uintptr_t)cab | (uintptr_t)w1f | (uintptr_t)w2) & 15) {
+        set_error("mlp_fused: pointers must be 16-byte aligned");
+        return SRB_E_ARG;
+    }
+    static bool attr = false;
+    if (!attr) {
+        SRB_CUDA(cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MLP_TC_SMEM));
+        attr = true;
+    }
+    MlpArgs a;
+    a.t = t; a.cab = cab; a.cs = cs; a.w1 = w1f; a.b1 = b1f; a.w2 = w2; a.b2 = b2; a.y = y;
+    a.ntiles = (uint32_t)(ntok / 128);
+    a.tiles_per_img = (uint32_t)(tok_per_img / 128);
+    const int sms = num_sms();
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(a.ntiles < (uint32_t)sms ? a.ntiles : sms);
+    cfg.blockDim = dim3(kMlpThreads);
+    cfg.dynamicSmemBytes = MLP_TC_SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute attrs[1];
+    attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = 1;
+    SRB_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, a));
+    return SRB_OK;
+}
+
+}  // namespace srb

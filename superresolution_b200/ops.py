@@ -35,3 +35,28 @@ def conv_nhwc(x, cin, w_packed, bias=None, out=None, out32=None, act=L.ACT_NONE,
         B, H, W, cin, cout, taps, act, slope, alpha1, L.ptr(res1), isf32(res1), pitch(res1), alpha2, L.ptr(res2),
         isf32(res2), pitch(res2), L.ptr(res2_cs), int(pixel_shuffle), L.current_stream())
     L.check(rc, 'conv_nhwc_bf16')
+
+
+def fold_ln_linear(w, b, gamma, beta):
+    """LayerNorm affine folded into the following Linear: returns (bf16 [N,K] weight, fp32 [N] bias)."""
+    w = w.detach().float().contiguous()
+    n, k = w.shape
+    wf = torch.empty(n, k, dtype=torch.bfloat16, device=w.device)
+    bf = torch.empty(n, dtype=torch.float32, device=w.device)
+    L.check(L.lib().srb_fold_ln_linear(L.ptr(w), L.ptr(b.float().contiguous()), L.ptr(gamma.float().contiguous()),
+                                       L.ptr(beta.float().contiguous()), L.ptr(wf), L.ptr(bf), n, k,
+                                       L.current_stream()), 'fold_ln_linear')
+    return wf, bf
+
+
+def mlp_branch(t, w1_folded, b1_folded, w2_packed, b2, cab=None, cs=None, out=None, tok_per_img=None):
+    """y = y0 + fc2(GELU(fc1(LN(y0)))), y0 = t + cab*cs[b].  t/cab/out: bf16 [ntok,96]; cs fp32 [B,96]."""
+    ntok = t.shape[0]
+    if out is None:
+        out = torch.empty_like(t)
+    if tok_per_img is None:
+        tok_per_img = ntok if cs is None else ntok // cs.shape[0]
+    rc = L.lib().srb_mlp_branch(L.ptr(t), L.ptr(cab), L.ptr(cs), L.ptr(w1_folded), L.ptr(b1_folded), L.ptr(w2_packed),
+                                L.ptr(b2), L.ptr(out), ntok, tok_per_img, L.current_stream())
+    L.check(rc, 'mlp_branch')
+    return out
