@@ -36,13 +36,16 @@ constexpr int A2_PITCH = 128 * 16;
 constexpr int A2_PLANES = 24 + 2;
 constexpr int W1_PITCH = 192 * 16;
 constexpr int W2_PITCH = 96 * 16;
-constexpr int Y_BYTES = 128 * 96 * 2;    // dense token tile (= its global layout)
+constexpr int YP_PITCH = 128 * 16 + 32;  // y0 / output tile as k-group planes (same skew as A1)
+constexpr int YP_BYTES = 12 * YP_PITCH;
+constexpr int kMaxImg = 64;              // images per launch (bf16 channel-attention table in smem)
 constexpr int OFF_A1 = 0;
 constexpr int OFF_A2 = OFF_A1 + A1_PLANES * A1_PITCH;
 constexpr int OFF_W1 = OFF_A2 + A2_PLANES * A2_PITCH;
 constexpr int OFF_W2 = OFF_W1 + A1_PLANES * W1_PITCH;
 constexpr int OFF_Y = OFF_W2 + A2_PLANES * W2_PITCH;
-constexpr int OFF_BAR = OFF_Y + 2 * Y_BYTES;
+constexpr int OFF_CS = OFF_Y + 2 * YP_BYTES;
+constexpr int OFF_BAR = OFF_CS + kMaxImg * 192;
 constexpr int MLP_TC_SMEM = OFF_BAR + 64;
 constexpr uint32_t D1_COL = 0, D2_COL = 192, MLP_TMEM_COLS = 512;
 static_assert(MLP_TC_SMEM <= 227 * 1024, "shared memory budget");
@@ -58,6 +61,8 @@ struct MlpArgs {
     const float* b2;
     bf16* y;
     uint32_t ntiles, tiles_per_img;
+    uint32_t nimg;  // images covered by this launch (cs table rows)
+    long long* dbg;  // optional [grid][8] per-phase cycle totals of thread 0 (development aid)
 };
 
 __device__ __forceinline__ uint32_t packbf(float lo, float hi) {
@@ -79,7 +84,8 @@ mlp_tc_kernel(const MlpArgs a) {
     uint8_t* sA2 = smem + OFF_A2;
     uint8_t* sW1 = smem + OFF_W1;
     uint8_t* sW2 = smem + OFF_W2;
-    uint8_t* sY = smem + OFF_Y;
+    uint8_t* sYP = smem + OFF_Y;
+    uint8_t* sCS = smem + OFF_CS;
     uint64_t* bars = (uint64_t*)(smem + OFF_BAR);
     uint64_t* bar_a1 = bars + 0;  // A1 (normalised tokens) written          count kAluThreads
     uint64_t* bar_a2 = bars + 1;  // A2 (GELU hidden) written                 count kAluThreads
@@ -163,12 +169,20 @@ mlp_tc_kernel(const MlpArgs a) {
         const int q = warp & 3, h4 = warp >> 2;
         const int r = q * 32 + lane;                 // GELU / EPI: token row inside the tile == TMEM lane
         const uint32_t tm_lane = tmem_base + ((uint32_t)(q * 32) << 16);
-        const int ln_row = warp * 8 + (lane >> 2);   // LN: 4 lanes per token, lane j owns 16-byte units j, j+4, j+8
+        const int ln_row = warp * 8 + (lane >> 2);   // LN / copy-out: 4 lanes per token, lane j owns 16-byte units j, j+4, j+8
         const int ln_j = lane & 3;
-        const bool issuer = (tid == 0);
-        const int rot = (lane >> 1) % 3;             // EPI staging rotation (2-way instead of 4-way bank conflicts)
 
         uint4 pt[3], pc[3];                          // prefetched row thirds of t and cab
+        uint4 csr[3];                                // channel-attention scales (packed bf16) of image cs_img
+        uint32_t cs_img = 0xffffffffu;
+#ifdef SRB_MLP_PHASES
+        long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+#endif
+#ifdef SRB_MLP_PHASES
+#define SRB_PHASE(k) do { if (a.dbg && tid == 0) { const long long tn = clock64(); ph[k] += tn - tprev; tprev = tn; } } while (0)
+#else
+#define SRB_PHASE(k) do { } while (0)
+#endif
 
         auto issue_loads = [&](uint32_t tile) {
             const size_t row = (size_t)tile * 128 + ln_row;
@@ -182,8 +196,31 @@ mlp_tc_kernel(const MlpArgs a) {
             }
         };
 
-        // combine + LayerNorm (no affine) of the prefetched tile -> A1; residual y0 -> Y staging buffer
+        // combine + LayerNorm (no affine) of the prefetched tile -> A1; residual y0 (bf16) -> plane buffer YP[it & 1]
         auto layer_norm = [&](uint32_t tile, uint32_t it) {
+            if (a.cab) {
+                // y0 = t + cab * cs in packed bf16 (one rounding: exactly the value the residual stream stores)
+                const uint32_t img = tile / a.tiles_per_img;
+                if (img != cs_img) {  // warp-uniform; a CTA changes image every few tiles
+                    const uint4* csp = (const uint4*)(sCS + img * 192) + ln_j;
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) csr[m] = csp[4 * m];
+                    cs_img = img;
+                }
+#pragma unroll
+                for (int m = 0; m < 3; ++m) {
+                    const uint4 s4 = csr[m];
+                    __nv_bfloat162* tv = (__nv_bfloat162*)&pt[m];
+                    const __nv_bfloat162* cv = (const __nv_bfloat162*)&pc[m];
+                    const __nv_bfloat162* sv = (const __nv_bfloat162*)&s4;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) tv[k] = __hfma2(cv[k], sv[k], tv[k]);
+                }
+            }
+            uint8_t* yp = sYP + (it & 1) * YP_BYTES + ln_row * 16;
+#pragma unroll
+            for (int m = 0; m < 3; ++m) *(uint4*)(yp + (ln_j + 4 * m) * YP_PITCH) = pt[m];
+            SRB_PHASE(2);
             float v[24];
 #pragma unroll
             for (int m = 0; m < 3; ++m) {
@@ -194,27 +231,6 @@ mlp_tc_kernel(const MlpArgs a) {
                     v[8 * m + 2 * k] = f.x; v[8 * m + 2 * k + 1] = f.y;
                 }
             }
-            if (a.cab) {
-                const float4* cs = (const float4*)(a.cs + (size_t)(tile / a.tiles_per_img) * 96) + 2 * ln_j;
-#pragma unroll
-                for (int m = 0; m < 3; ++m) {
-                    const uint32_t* w = (const uint32_t*)&pc[m];
-                    const float4 s0 = __ldg(cs + 8 * m), s1 = __ldg(cs + 8 * m + 1);
-                    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float2 f = unpackbf(w[k]);
-                        v[8 * m + 2 * k] = fmaf(f.x, sc[2 * k], v[8 * m + 2 * k]);
-                        v[8 * m + 2 * k + 1] = fmaf(f.y, sc[2 * k + 1], v[8 * m + 2 * k + 1]);
-                    }
-                }
-            }
-            uint8_t* yb = sY + (it & 1) * Y_BYTES + ln_row * 192;
-#pragma unroll
-            for (int m = 0; m < 3; ++m)
-                *(uint4*)(yb + 16 * (ln_j + 4 * m)) =
-                    make_uint4(packbf(v[8 * m], v[8 * m + 1]), packbf(v[8 * m + 2], v[8 * m + 3]),
-                               packbf(v[8 * m + 4], v[8 * m + 5]), packbf(v[8 * m + 6], v[8 * m + 7]));
             float s = 0.f;
 #pragma unroll
             for (int k = 0; k < 24; ++k) s += v[k];
@@ -232,22 +248,30 @@ mlp_tc_kernel(const MlpArgs a) {
                 *(uint4*)(sA1 + (ln_j + 4 * m) * A1_PITCH + ln_row * 16) =
                     make_uint4(packbf(v[8 * m] * rs, v[8 * m + 1] * rs), packbf(v[8 * m + 2] * rs, v[8 * m + 3] * rs),
                                packbf(v[8 * m + 4] * rs, v[8 * m + 5] * rs), packbf(v[8 * m + 6] * rs, v[8 * m + 7] * rs));
+            SRB_PHASE(3);
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(bar_a1);
+            SRB_PHASE(4);
         };
 
+        // per-image channel-attention scales of this launch -> packed bf16 table (read by every LN)
+        if (a.cab)
+            for (int i = tid; i < (int)a.nimg * 96; i += kAluThreads)
+                ((bf16*)sCS)[i] = __float2bfloat16_rn(a.cs[i]);
+        named_bar_sync(1, kAluThreads);
         if (n_my > 0) {
             issue_loads(first);
             layer_norm(first, 0);
             if (n_my > 1) issue_loads(first + step);
-            named_bar_sync(1, kAluThreads);  // y0(0) visible to the EPI threads even when this CTA has a single tile
         }
         for (uint32_t i = 0; i < n_my; ++i) {
             const uint32_t tile = first + i * step;
             // ---- (a) GELU(i): D1 -> A2 ----
+            SRB_PHASE(7);
             mbar_wait(bar_d1, i & 1);
             tc_fence_after();
+            SRB_PHASE(0);
             {
                 uint32_t acc[48];
                 {
@@ -274,58 +298,57 @@ mlp_tc_kernel(const MlpArgs a) {
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(bar_a2);
+            SRB_PHASE(1);
             // ---- (b) LN(i+1) -> A1 (fc1(i) has completed: bar_d1 was waited), prefetch tile i+2 ----
+            // the barrier orders copy-out(i-1) (last readers of YP[(i+1)&1]) before the y0(i+1) stores
+            named_bar_sync(1, kAluThreads);
+            SRB_PHASE(1);
             if (i + 1 < n_my) {
-                // the staging buffer about to receive y0(i+1) was the source of tile i-1's bulk store
-                if (issuer) bulk_wait_group_read<0>();
-                named_bar_sync(1, kAluThreads);
                 layer_norm(tile + step, i + 1);
-                if (i + 2 < n_my) issue_loads(tile + 2 * step);
             }
-            // ---- (c) EPI(i): D2 + y0 -> Y staging (in place) -> bulk store ----
+            SRB_PHASE(5);
+            // ---- (c) EPI(i): D2 + y0 -> YP[i&1] in place (row per lane: conflict free) ----
             mbar_wait(bar_d2, i & 1);
             tc_fence_after();
             {
-                uint32_t acc[24];
-                {
-                    uint32_t lo[16], hi[8];
-                    tmem_ld_32x32b_x16(tm_lane + D2_COL + 24 * h4, lo);
-                    tmem_ld_32x32b_x8(tm_lane + D2_COL + 24 * h4 + 16, hi);
-                    tmem_ld_wait();
+                uint32_t lo[16], hi[8];
+                tmem_ld_32x32b_x16(tm_lane + D2_COL + 24 * h4, lo);
+                tmem_ld_32x32b_x8(tm_lane + D2_COL + 24 * h4 + 16, hi);
+                tmem_ld_wait();
+                uint8_t* yp = sYP + (i & 1) * YP_BYTES + (3 * h4) * YP_PITCH + r * 16;
 #pragma unroll
-                    for (int k = 0; k < 16; ++k) acc[k] = lo[k];
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) acc[16 + k] = hi[k];
-                }
-                uint8_t* yb = sY + (i & 1) * Y_BYTES + r * 192 + 48 * h4;
-                // unit visited at step s is (s + rot) % 3; the data registers are selected, not indexed
-#pragma unroll
-                for (int s3 = 0; s3 < 3; ++s3) {
-                    const int u = (s3 + rot) % 3;
-                    uint4 yy = *(const uint4*)(yb + 16 * u);
+                for (int u = 0; u < 3; ++u) {
+                    const uint4 yy = *(const uint4*)(yp + u * YP_PITCH);
                     const uint32_t* yw = (const uint32_t*)&yy;
                     uint4 o4;
                     uint32_t* ow = (uint32_t*)&o4;
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
                         const float2 f = unpackbf(yw[k]);
-                        const float c0 = u == 0 ? __uint_as_float(acc[2 * k]) : u == 1 ? __uint_as_float(acc[8 + 2 * k])
-                                                                                        : __uint_as_float(acc[16 + 2 * k]);
-                        const float c1 = u == 0 ? __uint_as_float(acc[2 * k + 1]) : u == 1 ? __uint_as_float(acc[9 + 2 * k])
-                                                                                            : __uint_as_float(acc[17 + 2 * k]);
-                        ow[k] = packbf(c0 + f.x, c1 + f.y);
+                        const uint32_t c0 = u < 2 ? lo[8 * u + 2 * k] : hi[2 * k];
+                        const uint32_t c1 = u < 2 ? lo[8 * u + 2 * k + 1] : hi[2 * k + 1];
+                        ow[k] = packbf(__uint_as_float(c0) + f.x, __uint_as_float(c1) + f.y);
                     }
-                    *(uint4*)(yb + 16 * u) = o4;
+                    *(uint4*)(yp + u * YP_PITCH) = o4;
                 }
             }
-            fence_proxy_async_smem();
+            tc_fence_before();
+            SRB_PHASE(6);
             named_bar_sync(2, kAluThreads);
-            if (issuer) {
-                bulk_store_1d(a.y + (size_t)tile * 128 * 96, sY + (i & 1) * Y_BYTES, Y_BYTES);
-                bulk_commit_group();
+            // ---- (d) copy-out(i): 4 lanes per token, 64-byte row segments -> fully coalesced 16-byte stores ----
+            {
+                const uint8_t* yp = sYP + (i & 1) * YP_BYTES + ln_row * 16;
+                uint4* gp = (uint4*)(a.y + ((size_t)tile * 128 + ln_row) * 96) + ln_j;
+#pragma unroll
+                for (int m = 0; m < 3; ++m) gp[4 * m] = *(const uint4*)(yp + (ln_j + 4 * m) * YP_PITCH);
             }
+            if (i + 2 < n_my) issue_loads(tile + 2 * step);
         }
-        if (issuer) bulk_wait_group<0>();
+#ifdef SRB_MLP_PHASES
+        if (a.dbg && tid == 0)
+            for (int k = 0; k < 8; ++k) a.dbg[blockIdx.x * 8 + k] = ph[k];
+#endif
+#undef SRB_PHASE
     }
 
     tc_fence_before();
@@ -354,6 +377,8 @@ __global__ void fold_ln_linear_kernel(const float* __restrict__ w, const float* 
 
 }  // namespace
 
+extern long long* g_fa_dbg;  // attn.cu (srb_debug_set_phase_buffer)
+
 int fold_ln_linear(const float* w, const float* b, const float* gamma, const float* beta, bf16* w_out, float* b_out,
                    int N, int K, cudaStream_t s) {
     fold_ln_linear_kernel<<<N, 128, 0, s>>>(w, b, gamma, beta, w_out, b_out, K);
@@ -373,23 +398,32 @@ int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, 
         SRB_CUDA(cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MLP_TC_SMEM));
         attr = true;
     }
-    MlpArgs a;
-    a.t = t; a.cab = cab; a.cs = cs; a.w1 = w1f; a.b1 = b1f; a.w2 = w2; a.b2 = b2; a.y = y;
-    a.ntiles = (uint32_t)(ntok / 128);
-    a.tiles_per_img = (uint32_t)(tok_per_img / 128);
+    const size_t nimg_total = ntok / tok_per_img;
+    if (ntok % tok_per_img) { set_error("mlp_fused: ntok must be a multiple of tok_per_img"); return SRB_E_SHAPE; }
     const int sms = num_sms();
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3(a.ntiles < (uint32_t)sms ? a.ntiles : sms);
-    cfg.blockDim = dim3(kMlpThreads);
-    cfg.dynamicSmemBytes = MLP_TC_SMEM;
-    cfg.stream = s;
-    cudaLaunchAttribute attrs[1];
-    attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attrs[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attrs;
-    cfg.numAttrs = 1;
-    SRB_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, a));
+    for (size_t img = 0; img < nimg_total; img += kMaxImg) {  // the smem cs table holds kMaxImg images per launch
+        const size_t nimg = nimg_total - img < (size_t)kMaxImg ? nimg_total - img : (size_t)kMaxImg;
+        const size_t tok0 = img * tok_per_img;
+        MlpArgs a;
+        a.t = t + tok0 * 96; a.cab = cab ? cab + tok0 * 96 : nullptr; a.cs = cs ? cs + img * 96 : nullptr;
+        a.w1 = w1f; a.b1 = b1f; a.w2 = w2; a.b2 = b2; a.y = y + tok0 * 96;
+        a.ntiles = (uint32_t)(nimg * tok_per_img / 128);
+        a.tiles_per_img = (uint32_t)(tok_per_img / 128);
+        a.nimg = (uint32_t)nimg;
+        a.dbg = g_fa_dbg;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(a.ntiles < (uint32_t)sms ? a.ntiles : sms);
+        cfg.blockDim = dim3(kMlpThreads);
+        cfg.dynamicSmemBytes = MLP_TC_SMEM;
+        cfg.stream = s;
+        cudaLaunchAttribute attrs[1];
+        attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attrs[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attrs;
+        cfg.numAttrs = 1;
+        SRB_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, a));
+    }
     return SRB_OK;
 }
 

@@ -20,7 +20,7 @@ def _ref(t, cab, cs, g, b, w1, b1, w2, b2, tok_per_img):
 
 @pytest.mark.parametrize('ntok,B,with_cab,inplace', [(128, 1, False, False), (4096, 2, True, False),
                                                      (148 * 128 * 3 + 128 * 5, 1, True, False),
-                                                     (65536, 4, True, True), (8192, 2, False, True)])
+                                                     (65536, 4, True, True), (8192, 2, False, True), (128 * 70, 70, True, False)])
 def test_mlp_branch(cuda, ntok, B, with_cab, inplace):
     from superresolution_b200 import ops
     g = torch.Generator().manual_seed(ntok + B)

@@ -22,3 +22,19 @@ for _ in range(10):
     ops.mlp_branch(t, w1, b1, w2, b2, cab=cab, cs=cs, out=out, tok_per_img=ntok // B)
 e1.record(); torch.cuda.synchronize()
 print('mlp_branch us/launch', e0.elapsed_time(e1) * 100)
+
+import ctypes as C
+from superresolution_b200 import _lib as L
+lib = L.lib()
+buf = torch.zeros(148 * 8, dtype=torch.int64, device='cuda')
+lib.srb_debug_set_phase_buffer.argtypes = [C.c_void_p]; lib.srb_debug_set_phase_buffer.restype = None
+lib.srb_debug_set_phase_buffer(C.c_void_p(buf.data_ptr()))
+ops.mlp_branch(t, w1, b1, w2, b2, cab=cab, cs=cs, out=out, tok_per_img=ntok // B)
+torch.cuda.synchronize()
+lib.srb_debug_set_phase_buffer(None)
+p = buf.view(148, 8).double().mean(0)
+names = ['wait_d1', 'gelu+bar', 'ln_combine', 'ln_stats+A1', 'ln_fence', 'issue_loads', 'wait_d2+epi', 'epi_bar+copyout']
+tot = p.sum().item()
+for n, v in zip(names, p):
+    print(f'{n:12s} {v.item() / 55.35:8.0f} cyc/tile {100 * v.item() / tot:5.1f}%')
+print('total cyc/tile', tot / 55.35)
