@@ -413,7 +413,7 @@ int ocab_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int
 // ---------------------------------------------------------------------------------------------------------------
 template <typename OUT_T>
 __global__ void expand_rel_bias_kernel(const float* __restrict__ table, int T, const int64_t* __restrict__ index,
-                                       int NK, OUT_T* __restrict__ out) {
+                                       int NK, OUT_T* __restrict__ out, float scale) {
     const int NT = NK / 8;
     const int n = 6 * 4 * NT * 32 * 4;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -423,19 +423,20 @@ __global__ void expand_rel_bias_kernel(const float* __restrict__ table, int T, c
         const int c = 8 * j + 2 * (lane & 3) + (e & 1);
         long long idx = index[r * NK + c] % T;
         if (idx < 0) idx += T;
-        out[i] = (OUT_T)table[idx * 6 + h];
+        out[i] = (OUT_T)(table[idx * 6 + h] * scale);
     }
 }
 
-int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, cudaStream_t s) {
+int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, float scale,
+                         cudaStream_t s) {
     const int n = 6 * 64 * NK;
-    expand_rel_bias_kernel<bf16><<<(n + 255) / 256, 256, 0, s>>>(table, T, index, NK, out);
+    expand_rel_bias_kernel<bf16><<<(n + 255) / 256, 256, 0, s>>>(table, T, index, NK, out, scale);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
 int expand_rel_bias_f32(const float* table, int T, const int64_t* index, int NK, float* out, cudaStream_t s) {
     const int n = 6 * 64 * NK;
-    expand_rel_bias_kernel<float><<<(n + 255) / 256, 256, 0, s>>>(table, T, index, NK, out);
+    expand_rel_bias_kernel<float><<<(n + 255) / 256, 256, 0, s>>>(table, T, index, NK, out, 1.f);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -53,6 +53,9 @@ struct ConvArgs {
 };
 
 int conv_tc_launch(const ConvArgs& a, cudaStream_t stream);
+// chain of dependent 3x3 convs (Cout 32 / 64, common B/H/W) in one persistent kernel with grid barriers (conv_chain.cu)
+int conv_chain_launch(const ConvArgs* layers, int n, unsigned int* counters, cudaStream_t stream);
+int conv_chain_max_layers();
 int num_sms();  // SM count of the current device (cached)
 
 }  // namespace srb

@@ -1,0 +1,98 @@
+// Fused epilogue arithmetic shared by the tensor-core conv kernels (conv_tc.cu, conv_chain.cu).
+#pragma once
+#include "common.h"
+
+namespace srb {
+
+// erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7, i.e. fp32-exact for a bf16 result): exact-GELU semantics of
+// nn.GELU() without the branchy erff().
+__device__ __forceinline__ float gelu_erf(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    const float e = 1.0f - p * t * __expf(-z * z);  // erf(|x|/sqrt2)
+    return 0.5f * x * (1.0f + copysignf(e, x));
+}
+
+// bias + activation + residuals on one 32-channel slice of one pixel (all indices compile-time after unrolling)
+__device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a, size_t pix, int cb, int b) {
+    if (a.bias) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            const float4 bb = __ldg((const float4*)(a.bias + cb + j));
+            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+        }
+    }
+    if (a.act == ACT_LRELU) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * a.slope;
+    } else if (a.act == ACT_GELU) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+    }
+    if (a.res1) {
+        if (a.res1_f32) {
+            const float4* rp = (const float4*)((const float*)a.res1 + pix * a.res1_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 rr = rp[j];
+                v[4 * j] = fmaf(v[4 * j], a.alpha1, rr.x);
+                v[4 * j + 1] = fmaf(v[4 * j + 1], a.alpha1, rr.y);
+                v[4 * j + 2] = fmaf(v[4 * j + 2], a.alpha1, rr.z);
+                v[4 * j + 3] = fmaf(v[4 * j + 3], a.alpha1, rr.w);
+            }
+        } else {
+            const uint4* rp = (const uint4*)((const bf16*)a.res1 + pix * a.res1_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 rr = rp[j];
+                const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h[k]);
+                    v[8 * j + 2 * k] = fmaf(v[8 * j + 2 * k], a.alpha1, f.x);
+                    v[8 * j + 2 * k + 1] = fmaf(v[8 * j + 2 * k + 1], a.alpha1, f.y);
+                }
+            }
+        }
+    }
+    if (a.res2) {
+        if (a.res2_f32) {
+            const float4* rp = (const float4*)((const float*)a.res2 + pix * a.res2_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 rr = rp[j];
+                float4 c4 = make_float4(1.f, 1.f, 1.f, 1.f);
+                if (a.res2_cs) c4 = __ldg((const float4*)(a.res2_cs + (size_t)b * a.Cout + cb + 4 * j));
+                v[4 * j] = fmaf(v[4 * j], a.alpha2, rr.x * c4.x);
+                v[4 * j + 1] = fmaf(v[4 * j + 1], a.alpha2, rr.y * c4.y);
+                v[4 * j + 2] = fmaf(v[4 * j + 2], a.alpha2, rr.z * c4.z);
+                v[4 * j + 3] = fmaf(v[4 * j + 3], a.alpha2, rr.w * c4.w);
+            }
+        } else {
+            const uint4* rp = (const uint4*)((const bf16*)a.res2 + pix * a.res2_pitch + cb);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 rr = rp[j];
+                const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
+                float4 c0 = make_float4(1.f, 1.f, 1.f, 1.f), c1 = c0;
+                if (a.res2_cs) {
+                    c0 = __ldg((const float4*)(a.res2_cs + (size_t)b * a.Cout + cb + 8 * j));
+                    c1 = __ldg((const float4*)(a.res2_cs + (size_t)b * a.Cout + cb + 8 * j + 4));
+                }
+                const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h[k]);
+                    v[8 * j + 2 * k] = fmaf(v[8 * j + 2 * k], a.alpha2, f.x * cs[2 * k]);
+                    v[8 * j + 2 * k + 1] = fmaf(v[8 * j + 2 * k + 1], a.alpha2, f.y * cs[2 * k + 1]);
+                }
+            }
+        }
+    }
+}
+
+}  // namespace srb

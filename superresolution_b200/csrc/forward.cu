@@ -158,11 +158,11 @@ int model_pack(const void* const* params, int n, void* packed, size_t packed_byt
         for (int j = 0; j < 6; ++j) {
             snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.attn.relative_position_bias_table", l, j);
             const float* tab = (const float*)(base + m.params[m.index.at(buf)].off);
-            SRB_TRY(expand_rel_bias_bf16(tab, 225, idx_sa, 64, (bf16*)(base + m.bias_sa_off[l * 6 + j]), s));
+            SRB_TRY(expand_rel_bias_bf16(tab, 225, idx_sa, 64, (bf16*)(base + m.bias_sa_off[l * 6 + j]), 1.4426950408889634f, s));
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.relative_position_bias_table", l);
         const float* tab = (const float*)(base + m.params[m.index.at(buf)].off);
-        SRB_TRY(expand_rel_bias_bf16(tab, 361, idx_oca, 144, (bf16*)(base + m.bias_oca_off[l]), s));
+        SRB_TRY(expand_rel_bias_bf16(tab, 361, idx_oca, 144, (bf16*)(base + m.bias_oca_off[l]), 1.f, s));
     }
     // norm2 folded into mlp.fc1 (from the fp32 originals: one bf16 rounding)
     auto src = [&](const std::string& name) { return (const float*)params[m.index.at(name)]; };
@@ -198,6 +198,7 @@ struct Workspace {
     bf16* d1;       // [ntok,64]
     bf16* d2;       // [4*ntok,64]
     float *o1, *o2; // [B,4H,4W] fp32
+    unsigned int* chain_ctr;  // [23][16] grid-barrier counters of the RRDB chain kernels (zeroed per forward)
 };
 
 static size_t carve(Workspace& w, uint8_t* base, int B, int H, int W) {
@@ -237,6 +238,7 @@ static size_t carve(Workspace& w, uint8_t* base, int B, int H, int W) {
     w.d2 = (bf16*)take(p4 * 64 * 2);
     w.o1 = (float*)take(p4 * 4);
     w.o2 = (float*)take(p4 * 4);
+    w.chain_ctr = (unsigned int*)take(23 * 16 * sizeof(unsigned int));
     return off;
 }
 
@@ -296,13 +298,11 @@ static void prof_end(Ctx& c) {
 }
 
 // one tensor-core conv / linear layer named by its state-dict prefix
-static int tc_layer(Ctx& c, const std::string& name, const bf16* in, int in_pitch, int B, int H, int W, int act,
-                    float slope, bf16* out, int out_pitch, float* out32 = nullptr, float alpha1 = 1.f,
-                    const void* res1 = nullptr, int res1_f32 = 0, int res1_pitch = 0, float alpha2 = 1.f,
-                    const void* res2 = nullptr, int res2_f32 = 0, int res2_pitch = 0, const float* res2_cs = nullptr,
-                    int pixel_shuffle = 0) {
-    ++c.launches;
-    if (c.dry) return SRB_OK;
+static ConvArgs make_layer(const Ctx& c, const std::string& name, const bf16* in, int in_pitch, int B, int H, int W, int act,
+                           float slope, bf16* out, int out_pitch, float* out32 = nullptr, float alpha1 = 1.f,
+                           const void* res1 = nullptr, int res1_f32 = 0, int res1_pitch = 0, float alpha2 = 1.f,
+                           const void* res2 = nullptr, int res2_f32 = 0, int res2_pitch = 0,
+                           const float* res2_cs = nullptr, int pixel_shuffle = 0) {
     const Param& p = c.m->params[c.m->index.at(name + ".weight")];
     ConvArgs a;
     memset(&a, 0, sizeof(a));
@@ -315,7 +315,20 @@ static int tc_layer(Ctx& c, const std::string& name, const bf16* in, int in_pitc
     a.alpha2 = alpha2; a.res2 = res2; a.res2_f32 = res2_f32; a.res2_pitch = res2_pitch; a.res2_cs = res2_cs;
     a.out = out; a.out_pitch = out_pitch; a.out32 = out32; a.out32_pitch = 64;
     a.pixel_shuffle = pixel_shuffle;
-    prof_begin(c, p.taps == 9 ? PC_CONV3 : PC_LINEAR, 2.0 * B * H * W * (double)p.cout * p.cin * p.taps);
+    return a;
+}
+static double layer_flops(const ConvArgs& a) { return 2.0 * a.B * a.H * a.W * (double)a.Cout * a.Cin * a.taps; }
+
+static int tc_layer(Ctx& c, const std::string& name, const bf16* in, int in_pitch, int B, int H, int W, int act,
+                    float slope, bf16* out, int out_pitch, float* out32 = nullptr, float alpha1 = 1.f,
+                    const void* res1 = nullptr, int res1_f32 = 0, int res1_pitch = 0, float alpha2 = 1.f,
+                    const void* res2 = nullptr, int res2_f32 = 0, int res2_pitch = 0, const float* res2_cs = nullptr,
+                    int pixel_shuffle = 0) {
+    ++c.launches;
+    if (c.dry) return SRB_OK;
+    const ConvArgs a = make_layer(c, name, in, in_pitch, B, H, W, act, slope, out, out_pitch, out32, alpha1, res1,
+                                  res1_f32, res1_pitch, alpha2, res2, res2_f32, res2_pitch, res2_cs, pixel_shuffle);
+    prof_begin(c, a.taps == 9 ? PC_CONV3 : PC_LINEAR, layer_flops(a));
     const int rc = conv_tc_launch(a, c.s);
     prof_end(c);
     return rc;
@@ -339,24 +352,51 @@ static int run_stage1(Ctx& c, Workspace& w, const void* x, int x_dtype, int B, i
                               w.t[0], w.f0, B, h, ww, c.s));
     int cur = 0;
     char buf[96];
+    // One RRDB (15 dependent convs) = one persistent chain kernel when the trunk tiles as 16 x 32 (conv_chain.cu);
+    // narrower trunks fall back to one launch per conv.
+    const bool chain = (h % 16 == 0) && (ww % 32 == 0) && conv_chain_max_layers() >= 15;
+    if (chain && !c.dry) SRB_CUDA(cudaMemsetAsync(w.chain_ctr, 0, 23 * 16 * sizeof(unsigned int), c.s));
     for (int i = 0; i < 23; ++i) {
+        ConvArgs la[15];
+        int nl = 0;
         for (int j = 1; j <= 3; ++j) {
             bf16* cb = w.cb[cur];
-            for (int k = 1; k <= 4; ++k) {
-                snprintf(buf, sizeof(buf), "stage1.body.%d.rdb%d.conv%d", i, j, k);
-                SRB_TRY(tc_layer(c, buf, cb, 192, B, h, ww, ACT_LRELU, 0.2f, cb + 64 + 32 * (k - 1), 192));
-            }
-            snprintf(buf, sizeof(buf), "stage1.body.%d.rdb%d.conv5", i, j);
             bf16* nxt = w.cb[cur ^ 1];
-            // fp32 trunk: t[0] holds the RRDB input, t[1] the running RDB output
-            if (j == 1)
-                SRB_TRY(tc_layer(c, buf, cb, 192, B, h, ww, ACT_NONE, 0.f, nxt, 192, w.t[1], 0.2f, w.t[0], 1, 64));
-            else if (j == 2)
-                SRB_TRY(tc_layer(c, buf, cb, 192, B, h, ww, ACT_NONE, 0.f, nxt, 192, w.t[1], 0.2f, w.t[1], 1, 64));
-            else  // (x5*0.2 + x_rdb3)*0.2 + x_rrdb
-                SRB_TRY(tc_layer(c, buf, cb, 192, B, h, ww, ACT_NONE, 0.f, nxt, 192, w.t[0], 0.2f, w.t[1], 1, 64, 0.2f,
-                                 w.t[0], 1, 64));
+            for (int k = 1; k <= 5; ++k) {
+                snprintf(buf, sizeof(buf), "stage1.body.%d.rdb%d.conv%d", i, j, k);
+                if (c.dry) { ++nl; continue; }
+                if (k < 5)
+                    la[nl++] = make_layer(c, buf, cb, 192, B, h, ww, ACT_LRELU, 0.2f, cb + 64 + 32 * (k - 1), 192);
+                // fp32 trunk: t[0] holds the RRDB input, t[1] the running RDB output
+                else if (j == 1)
+                    la[nl++] = make_layer(c, buf, cb, 192, B, h, ww, ACT_NONE, 0.f, nxt, 192, w.t[1], 0.2f, w.t[0], 1, 64);
+                else if (j == 2)
+                    la[nl++] = make_layer(c, buf, cb, 192, B, h, ww, ACT_NONE, 0.f, nxt, 192, w.t[1], 0.2f, w.t[1], 1, 64);
+                else  // (x5*0.2 + x_rdb3)*0.2 + x_rrdb
+                    la[nl++] = make_layer(c, buf, cb, 192, B, h, ww, ACT_NONE, 0.f, nxt, 192, w.t[0], 0.2f, w.t[1], 1, 64,
+                                          0.2f, w.t[0], 1, 64);
+            }
             cur ^= 1;
+        }
+        if (chain) {
+            ++c.launches;
+            if (!c.dry) {
+                double fl = 0;
+                for (int q = 0; q < nl; ++q) fl += layer_flops(la[q]);
+                prof_begin(c, PC_CONV3, fl);
+                const int rc = conv_chain_launch(la, nl, w.chain_ctr + 16 * i, c.s);
+                prof_end(c);
+                if (rc != SRB_OK) return rc;
+            }
+        } else {
+            c.launches += nl;
+            if (!c.dry)
+                for (int q = 0; q < nl; ++q) {
+                    prof_begin(c, PC_CONV3, layer_flops(la[q]));
+                    const int rc = conv_tc_launch(la[q], c.s);
+                    prof_end(c);
+                    if (rc != SRB_OK) return rc;
+                }
         }
     }
     // feat = feat + conv_body(body(feat))
@@ -385,7 +425,7 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
             const bf16* xin = (j == 0) ? w.g : w.y;  // token stream entering this block (= shortcut)
             // fused attention branch: xn = LN1(x), ao = x + proj(W-MSA(xn))   (LN1, qkv, attention, proj in one kernel)
             LAUNCH(c, PC_ATTN, 2.0 * (27648 + 12288 + 9216) * (double)ntok,
-                   hab_fused_attention(xin, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), c.Wt(b + "attn.qkv.weight"),
+                   hab_attention_tc(xin, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), c.Wt(b + "attn.qkv.weight"),
                                        c.F(b + "attn.qkv.bias"), (const bf16*)(pk + c.m->bias_sa_off[l * 6 + j]),
                                        c.Wt(b + "attn.proj.weight"), c.F(b + "attn.proj.bias"), w.xn, w.ao, B, R, Rw,
                                        (j & 1) ? 4 : 0, c.s));

@@ -37,10 +37,16 @@ int window_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, i
 int hab_fused_attention(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
                         const bf16* bias_frag, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
                         int W, int shift, cudaStream_t s);
+// hab_tc.cu — the same branch with the qkv / proj GEMMs on tcgen05 (TMEM accumulators) over 128-token tiles;
+// bias_frag_log2e: expand_rel_bias_bf16(..., scale = log2(e))
+int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
+                     const bf16* bias_frag_log2e, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
+                     int W, int shift, cudaStream_t s);
 // OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.
 int ocab_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s);
 // table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> fragment-ordered bias [6*64*NK]
-int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, cudaStream_t s);
+int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, float scale,
+                         cudaStream_t s);  // out = table[index] * scale
 int expand_rel_bias_f32(const float* table, int T, const int64_t* index, int NK, float* out, cudaStream_t s);
 
 // mlp_tc.cu:  y0 = t + cab*cs (cab may be null);  y = y0 + fc2(GELU(fc1(LayerNorm(y0))))   (y may alias t)
