@@ -9,7 +9,8 @@
 //   operand layout: un-swizzled K-major planes [k/8][row][8 bf16] (core matrix = 8 rows x 16 B contiguous, LBO =
 //   plane pitch, SBO = 128 B) -> a plane row segment of 8 tokens is exactly one ldmatrix 8x8 tile, and a thread that
 //   owns one token row writes 16-byte units without bank conflicts.
-// 12 compute warps (TMEM lane quadrant = warp & 3, channel third = warp >> 2) + 1 MMA/TMEM warp:
+// 12 warps (TMEM lane quadrant = warp & 3, channel third = warp >> 2; 3 warps per SM sub-partition so that a thread
+// may use up to 168 registers); warp 0 also allocates TMEM and issues the tcgen05 MMAs:
 //   LN      thread = (token row, 32 channels): x from HBM -> registers (kept for the shortcut), statistics merged
 //           across the three channel thirds through shared memory, xn -> HBM (CAB branch) and -> A1 planes
 //   qkv     3 x 6 tcgen05.mma (q | k | v parts, one commit each) -> TMEM columns [0, 288)
@@ -30,8 +31,9 @@ namespace {
 
 constexpr int kComputeWarps = 12;
 constexpr int kComputeThreads = kComputeWarps * 32;
-constexpr int kHabThreads = kComputeThreads + 32;
-constexpr int PP = 128 * 16;             // activation plane pitch (bytes): 128 token rows x 16 B
+constexpr int kHabThreads = kComputeThreads;  // 3 warps per SM sub-partition -> up to 168 registers per thread
+constexpr int PP = 128 * 16 + 16;        // activation plane pitch (bytes): 128 token rows x 16 B + a 16-byte skew that
+                                         // spreads the 6-lanes-per-token global I/O pattern over the banks
 constexpr int WQ_PITCH = 288 * 16;       // qkv weight plane pitch
 constexpr int WP_PITCH = 96 * 16;        // proj weight plane pitch
 constexpr int BIAS_ELEMS = 6 * 4 * 8 * 32 * 4;  // bf16, MMA C-fragment order per head (expand_rel_bias_bf16)
@@ -62,6 +64,7 @@ struct HabArgs {
     bf16* t;              // [B,H,W,96] x + proj(attn)
     int B, H, W, shift;
     int ntiles;           // window pairs
+    long long* dbg;       // optional [grid][8] per-phase cycle totals of thread 0 (development aid)
 };
 
 __device__ __forceinline__ uint32_t packbf(float lo, float hi) {
@@ -238,7 +241,7 @@ hab_tc_kernel(const HabArgs a) {
         mbar_init(bar_t, 1);
         fence_barrier_init();
     }
-    if (warp == kComputeWarps) { tmem_alloc(tmem_slot, HAB_TMEM_COLS); tmem_relinquish(); }
+    if (warp == 0) { tmem_alloc(tmem_slot, HAB_TMEM_COLS); tmem_relinquish(); }
     // constants of the launch
     for (int i = tid; i < 12 * 288; i += kHabThreads) {
         const int kg = i / 288, n = i % 288;
@@ -262,46 +265,21 @@ hab_tc_kernel(const HabArgs a) {
     const int first = blockIdx.x, step = gridDim.x;
     const int n_my = (a.ntiles > first) ? (a.ntiles - first + step - 1) / step : 0;
 
-    if (warp == kComputeWarps) {
-        // ===================== MMA issuer =====================
-        const uint32_t idesc = umma_idesc_bf16_f32(128, 96);
-        const uint32_t a1 = smem_u32(sA1), q_ = smem_u32(sQ), wq = smem_u32(sWq), wp = smem_u32(sWp);
-        for (int i = 0; i < n_my; ++i) {
-            mbar_wait(bar_a1, i & 1);
-            tc_fence_after();
-            if (elect_one()) {
-#pragma unroll
-                for (int part = 0; part < 3; ++part) {
-#pragma unroll
-                    for (int ks = 0; ks < 6; ++ks)
-                        umma_bf16_ss(tmem_base + COL_QKV + 96 * part, umma_smem_desc(a1 + ks * 2 * PP, PP, 128, UMMA_SW_NONE),
-                                     umma_smem_desc(wq + part * 96 * 16 + ks * 2 * WQ_PITCH, WQ_PITCH, 128, UMMA_SW_NONE),
-                                     idesc, ks > 0);
-                    umma_commit(bar_qkv + part);
-                }
-            }
-            __syncwarp();
-            mbar_wait(bar_o, i & 1);
-            tc_fence_after();
-            if (elect_one()) {
-#pragma unroll
-                for (int ks = 0; ks < 6; ++ks)
-                    umma_bf16_ss(tmem_base + COL_T, umma_smem_desc(q_ + ks * 2 * PP, PP, 128, UMMA_SW_NONE),
-                                 umma_smem_desc(wp + ks * 2 * WP_PITCH, WP_PITCH, 128, UMMA_SW_NONE), idesc, ks > 0);
-                umma_commit(bar_t);
-            }
-            __syncwarp();
-        }
-    } else {
-        // ===================== compute warps =====================
+    {
+        // ===================== all 12 warps (warp 0 also issues the tcgen05 MMAs) =====================
         const int q = warp & 3, c3 = warp >> 2;
         const int r = q * 32 + lane;  // token row of the tile == TMEM lane;  window r >> 6, token r & 63
         const uint32_t tm_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         const int un_w = warp / 6, un_h = warp % 6;  // attention unit of this warp: (window of the pair, head)
+        // Global I/O mapping ("G"): 6 lanes per token, lane j moves the 16-byte units j and j + 6 -> every request
+        // covers 96 contiguous bytes per token (full 32-byte sectors); 2 passes of 384 threads = 128 tokens x 6.
+        int g_row[2], g_j[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) { g_row[p] = (p * kComputeThreads + tid) / 6; g_j[p] = (p * kComputeThreads + tid) % 6; }
 
-        // token -> pixel index of this thread's row for a tile (cyclic shift = index math), and its region id
-        auto token_pix = [&](int tile, int& rid) -> size_t {
-            const int win = 2 * tile + (r >> 6), n = r & 63;
+        // pixel index (cyclic shift = index math) and shift-mask region id of tile row `row`
+        auto token_pix = [&](int tile, int row, int& rid) -> size_t {
+            const int win = 2 * tile + (row >> 6), n = row & 63;
             const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
             const int ys = wy * 8 + (n >> 3), xs = wx * 8 + (n & 7);  // rolled-image coordinates
             int y = ys + shift, x = xs + shift;                       // torch.roll(-shift): rolled[i] = orig[i + shift]
@@ -313,21 +291,56 @@ hab_tc_kernel(const HabArgs a) {
             return ((size_t)b * H + y) * W + x;
         };
 
-        uint4 xc[4], xnx[4];  // this tile's / the next tile's 32 channels of x (bf16)
-        int rid_c = 0, rid_n = 0;
-        size_t pix_c = 0, pix_n = 0;
-        if (n_my > 0) {
-            pix_n = token_pix(first, rid_n);
-            const uint4* xp = (const uint4*)(a.x + pix_n * 96 + 32 * c3);
+        uint4 xc[4];        // this tile's 32 channels of x of row r (bf16): LayerNorm input and shortcut
+        uint4 xg[2][2];     // next tile's x in the G mapping (in flight from HBM)
+        size_t gp_c[2] = {0, 0}, gp_n[2] = {0, 0};  // pixel index of this thread's G rows: current / next tile
+        int grid_n[2] = {0, 0};
+        const uint32_t idesc = umma_idesc_bf16_f32(128, 96);
+        const uint32_t a1_u = smem_u32(sA1), q_u = smem_u32(sQ), wq_u = smem_u32(sWq), wp_u = smem_u32(sWp);
+#ifdef SRB_HAB_PHASES
+        long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+#define SRB_PHASE(k) do { if (a.dbg && tid == 0) { const long long tn = clock64(); ph[k] += tn - tprev; tprev = tn; } } while (0)
+#else
+#define SRB_PHASE(k) do { } while (0)
+#endif
+        auto load_x = [&](int tile) {  // HBM -> registers, G mapping
 #pragma unroll
-            for (int u = 0; u < 4; ++u) xnx[u] = __ldg(xp + u);
+            for (int p = 0; p < 2; ++p) {
+                gp_n[p] = token_pix(tile, g_row[p], grid_n[p]);
+                const uint4* xp = (const uint4*)(a.x + gp_n[p] * 96) + g_j[p];
+                xg[p][0] = __ldg(xp);
+                xg[p][1] = __ldg(xp + 6);
+            }
+        };
+        auto park_x = [&]() {  // registers -> V planes (free between attention(i) and the qkv epilogue of tile i+1)
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                *(uint4*)(sV + g_j[p] * PP + g_row[p] * 16) = xg[p][0];
+                *(uint4*)(sV + (g_j[p] + 6) * PP + g_row[p] * 16) = xg[p][1];
+                if (g_j[p] == 0) sRid[g_row[p]] = grid_n[p];
+                gp_c[p] = gp_n[p];
+            }
+        };
+        auto copy_out = [&](const uint8_t* planes, bf16* dst) {  // planes -> HBM, G mapping
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                uint4* op = (uint4*)(dst + gp_c[p] * 96) + g_j[p];
+                op[0] = *(const uint4*)(planes + g_j[p] * PP + g_row[p] * 16);
+                op[6] = *(const uint4*)(planes + (g_j[p] + 6) * PP + g_row[p] * 16);
+            }
+        };
+
+        if (n_my > 0) {
+            load_x(first);
+            park_x();
+            if (n_my > 1) load_x(first + step);
         }
+        named_bar_sync(1, kComputeThreads);
         for (int i = 0; i < n_my; ++i) {
             const int tile = first + i * step;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) xc[u] = xnx[u];
-            pix_c = pix_n; rid_c = rid_n;
             // ---- LayerNorm: local two-pass statistics over 32 channels, Chan merge of the three thirds ----
+#pragma unroll
+            for (int u = 0; u < 4; ++u) xc[u] = *(const uint4*)(sV + (4 * c3 + u) * PP + r * 16);
             float v[32];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -346,41 +359,50 @@ hab_tc_kernel(const HabArgs a) {
 #pragma unroll
             for (int k = 0; k < 32; ++k) { const float d = v[k] - mloc; m2 = fmaf(d, d, m2); }
             sEx[c3 * 128 + r] = make_float2(mloc, m2);
-            if (c3 == 0) sRid[r] = rid_c;
             named_bar_sync(1, kComputeThreads);
             const float2 e0 = sEx[r], e1 = sEx[128 + r], e2 = sEx[256 + r];
             const float mean = (e0.x + e1.x + e2.x) * (1.f / 3.f);
             const float d0 = e0.x - mean, d1 = e1.x - mean, d2 = e2.x - mean;
             const float var = (e0.y + e1.y + e2.y + 32.f * (d0 * d0 + d1 * d1 + d2 * d2)) * (1.f / 96.f);
             const float rs = rsqrtf(var + 1e-5f);
-            {
-                uint4* xnp = (uint4*)(a.xn + pix_c * 96 + 32 * c3);
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const float4 g0 = *(const float4*)(sg + 32 * c3 + 8 * u), g1 = *(const float4*)(sg + 32 * c3 + 8 * u + 4);
-                    const float4 b0 = *(const float4*)(sbeta + 32 * c3 + 8 * u), b1 = *(const float4*)(sbeta + 32 * c3 + 8 * u + 4);
-                    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-                    uint4 o4;
-                    uint32_t* ow = (uint32_t*)&o4;
+            for (int u = 0; u < 4; ++u) {
+                const float4 g0 = *(const float4*)(sg + 32 * c3 + 8 * u), g1 = *(const float4*)(sg + 32 * c3 + 8 * u + 4);
+                const float4 b0 = *(const float4*)(sbeta + 32 * c3 + 8 * u), b1 = *(const float4*)(sbeta + 32 * c3 + 8 * u + 4);
+                const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                uint4 o4;
+                uint32_t* ow = (uint32_t*)&o4;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        ow[k] = packbf(fmaf((v[8 * u + 2 * k] - mean) * rs, gg[2 * k], bb[2 * k]),
-                                       fmaf((v[8 * u + 2 * k + 1] - mean) * rs, gg[2 * k + 1], bb[2 * k + 1]));
-                    *(uint4*)(sA1 + (4 * c3 + u) * PP + r * 16) = o4;
-                    xnp[u] = o4;
-                }
+                for (int k = 0; k < 4; ++k)
+                    ow[k] = packbf(fmaf((v[8 * u + 2 * k] - mean) * rs, gg[2 * k], bb[2 * k]),
+                                   fmaf((v[8 * u + 2 * k + 1] - mean) * rs, gg[2 * k + 1], bb[2 * k + 1]));
+                *(uint4*)(sA1 + (4 * c3 + u) * PP + r * 16) = o4;
             }
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(bar_a1);
-            // prefetch the next tile's x while the tensor core runs the qkv GEMM
-            if (i + 1 < n_my) {
-                pix_n = token_pix(tile + step, rid_n);
-                const uint4* xp = (const uint4*)(a.x + pix_n * 96 + 32 * c3);
+            SRB_PHASE(0);
+            mbar_wait(bar_a1, i & 1);  // every thread: A1 (= xn) is complete
+            if (warp == 0) {           // qkv GEMM: q | k | v parts, one commit each
+                tc_fence_after();
+                if (elect_one()) {
 #pragma unroll
-                for (int u = 0; u < 4; ++u) xnx[u] = __ldg(xp + u);
+                    for (int part = 0; part < 3; ++part) {
+#pragma unroll
+                        for (int ks = 0; ks < 6; ++ks)
+                            umma_bf16_ss(tmem_base + COL_QKV + 96 * part,
+                                         umma_smem_desc(a1_u + ks * 2 * PP, PP, 128, UMMA_SW_NONE),
+                                         umma_smem_desc(wq_u + part * 96 * 16 + ks * 2 * WQ_PITCH, WQ_PITCH, 128, UMMA_SW_NONE),
+                                         idesc, ks > 0);
+                        umma_commit(bar_qkv + part);
+                    }
+                }
+                __syncwarp();
             }
+            // xn -> HBM for the CAB branch while the tensor core works (A1 is only read from here on)
+            copy_out(sA1, a.xn);
+            SRB_PHASE(1);
             // ---- qkv epilogue: this warp's 32 rows x the 96 columns of part c3 -> Q / K / V planes ----
             mbar_wait(bar_qkv + c3, i & 1);
             tc_fence_after();
@@ -408,7 +430,9 @@ hab_tc_kernel(const HabArgs a) {
                 }
             }
             tc_fence_before();
+            SRB_PHASE(2);
             named_bar_sync(1, kComputeThreads);  // Q / K / V planes complete
+            SRB_PHASE(3);
             // ---- attention: warp = (window un_w, head un_h), 64 query rows in two 32-row passes ----
             {
                 const int win = 2 * tile + un_w;
@@ -423,14 +447,27 @@ hab_tc_kernel(const HabArgs a) {
             }
             fence_proxy_async_smem();
             mbar_arrive(bar_o);
-            // ---- proj epilogue: t = x + attn @ Wproj^T + b : this thread's row x channels [32 c3, +32) ----
+            SRB_PHASE(4);
+            mbar_wait(bar_o, i & 1);  // every warp has left the attention: K / V planes and sRid are free
+            if (warp == 0) {          // proj GEMM
+                tc_fence_after();
+                if (elect_one()) {
+#pragma unroll
+                    for (int ks = 0; ks < 6; ++ks)
+                        umma_bf16_ss(tmem_base + COL_T, umma_smem_desc(q_u + ks * 2 * PP, PP, 128, UMMA_SW_NONE),
+                                     umma_smem_desc(wp_u + ks * 2 * WP_PITCH, WP_PITCH, 128, UMMA_SW_NONE), idesc, ks > 0);
+                    umma_commit(bar_t);
+                }
+                __syncwarp();
+            }
+            SRB_PHASE(5);
+            // ---- proj epilogue: t = x + attn @ Wproj^T + b : this thread's row x channels [32 c3, +32) -> K planes ----
             mbar_wait(bar_t, i & 1);
             tc_fence_after();
             {
                 uint32_t acc[32];
                 tmem_ld_32x32b_x32(tm_lane + COL_T + 32 * c3, acc);
                 tmem_ld_wait();
-                uint4* tp = (uint4*)(a.t + pix_c * 96 + 32 * c3);
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const float4 b0 = *(const float4*)(sbp + 32 * c3 + 8 * u), b1 = *(const float4*)(sbp + 32 * c3 + 8 * u + 4);
@@ -444,19 +481,34 @@ hab_tc_kernel(const HabArgs a) {
                         ow[k] = packbf(__uint_as_float(acc[8 * u + 2 * k]) + bb[2 * k] + xf.x,
                                        __uint_as_float(acc[8 * u + 2 * k + 1]) + bb[2 * k + 1] + xf.y);
                     }
-                    tp[u] = o4;
+                    *(uint4*)(sK + (4 * c3 + u) * PP + r * 16) = o4;
                 }
             }
             tc_fence_before();
+            named_bar_sync(1, kComputeThreads);  // t staged in the K planes
+            copy_out(sK, a.t);                   // (uses the current tile's pixel indices)
+            if (i + 1 < n_my) {
+                park_x();                        // x(i+1) -> V planes, region ids, pixel indices become "current"
+                if (i + 2 < n_my) load_x(tile + 2 * step);
+            }
+            named_bar_sync(1, kComputeThreads);  // x(i+1) parked; K planes read out
+            SRB_PHASE(6);
         }
+#ifdef SRB_HAB_PHASES
+        if (a.dbg && tid == 0)
+            for (int k = 0; k < 8; ++k) a.dbg[blockIdx.x * 8 + k] = ph[k];
+#endif
+#undef SRB_PHASE
     }
 
     tc_fence_before();
     __syncthreads();
-    if (warp == kComputeWarps) tmem_dealloc(tmem_base, HAB_TMEM_COLS);
+    if (warp == 0) tmem_dealloc(tmem_base, HAB_TMEM_COLS);
 }
 
 }  // namespace
+
+extern long long* g_fa_dbg;  // attn.cu (srb_debug_set_phase_buffer)
 
 int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
                      const bf16* bias_frag_log2e, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
@@ -471,6 +523,7 @@ int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const 
     a.x = x; a.ln_g = ln_g; a.ln_b = ln_b; a.wqkv = wqkv; a.bqkv = bqkv; a.bias_frag = bias_frag_log2e; a.wproj = wproj;
     a.bproj = bproj; a.xn = xn; a.t = t; a.B = B; a.H = H; a.W = W; a.shift = shift;
     a.ntiles = B * (H / 8) * (W / 8) / 2;
+    a.dbg = g_fa_dbg;
     const int sms = num_sms();
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));

@@ -14,7 +14,7 @@ with torch.no_grad():
     m(x); torch.cuda.synchronize()
     lib.srb_debug_set_phase_buffer(None)
 p = buf.view(148,8).double().mean(0)
-names=['wait_load','layernorm','xn_store+qkv','attention','proj','t_store']
-tot=p[:6].sum()
-for n,v in zip(names,p[:6]): print(f'{n:14s} {v.item()/1e3:9.1f} kcyc {100*v.item()/tot.item():5.1f}%')
-print('total kcycles per CTA', tot.item()/1e3, 'windows per CTA ~', 16384/148)
+names=['layernorm','wait_qkv','qkv_epi','qkv_barrier','attention','wait_proj','proj_epi']
+tot=p[:7].sum()
+for n,v in zip(names,p[:7]): print(f'{n:14s} {v.item()/1e3:9.1f} kcyc {100*v.item()/tot.item():5.1f}%')
+print('total kcycles per CTA', tot.item()/1e3, 'tiles per CTA ~', 8192/148, 'cycles per 128-token tile', tot.item()/(8192/148))
