@@ -58,9 +58,10 @@ size_t srb_workspace_bytes(int B, int H, int W);
 int srb_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                 void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream);
 /* Profiling variant (bench only): same work, but every launch is bracketed by CUDA events on `stream`; the call
- * synchronises the stream and returns per-class totals.  Classes: 0 conv3x3 (tcgen05), 1 linear (tcgen05),
- * 2 attention, 3 layernorm, 4 other.  class_flops = algorithmic FLOPs (2*MACs) of the launches in the class. */
-#define SRB_PROF_CLASSES 5
+ * synchronises the stream and returns per-class totals.  Classes: 0 conv3x3 (tcgen05 implicit GEMM, incl. the RRDB
+ * chain kernel), 1 linear (tcgen05), 2 HAB attention branch (LN + qkv + W-MSA + proj, tcgen05 + mma.sync),
+ * 3 layernorm, 4 other, 5 MLP branch (tcgen05), 6 OCAB attention core.  class_flops = algorithmic FLOPs (2*MACs). */
+#define SRB_PROF_CLASSES 7
 int srb_forward_profile(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                         void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream,
                         double* class_ms, double* class_flops, int* class_launches);

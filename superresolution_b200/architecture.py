@@ -317,7 +317,8 @@ class HybridSuperResolutionModel(nn.Module):
                                     self._smoothing, stage_mask, L.current_stream()), 'forward')
         return y
 
-    PROFILE_CLASSES = ('conv3x3_tcgen05', 'linear_tcgen05', 'attention', 'layernorm', 'other')
+    PROFILE_CLASSES = ('conv3x3_tcgen05', 'linear_tcgen05', 'hab_attention_tcgen05', 'layernorm', 'other',
+                       'mlp_tcgen05', 'ocab_attention')
 
     def profile(self, x, stage_mask=3):
         """bench helper: one forward with every launch bracketed by CUDA events on the launching stream.

@@ -264,7 +264,8 @@ size_t model_workspace_bytes(int B, int H, int W) {
 // ------------------------------------------------------------------------------------------------------------------
 // forward schedule
 // ------------------------------------------------------------------------------------------------------------------
-enum ProfClass { PC_CONV3 = 0, PC_LINEAR = 1, PC_ATTN = 2, PC_LN = 3, PC_OTHER = 4, PC_COUNT = 5 };
+enum ProfClass { PC_CONV3 = 0, PC_LINEAR = 1, PC_ATTN = 2, PC_LN = 3, PC_OTHER = 4, PC_MLP = 5, PC_OCAB = 6, PC_COUNT = 7 };
+static_assert(PC_COUNT == SRB_PROF_CLASSES, "profile classes");
 struct ProfRec {
     int cls;
     double flops;
@@ -438,7 +439,7 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
                                             c.F(b + "conv_block.cab.3.attention.3.weight"),
                                             c.F(b + "conv_block.cab.3.attention.3.bias"), 0.01f, B, R * Rw, c.s));
             // y = (ao + cab * sigmoid(..) * conv_scale) + fc2(GELU(fc1(LN2(.))))  — combine, norm2 and the MLP in one kernel
-            LAUNCH(c, PC_LINEAR, 2.0 * 36864 * (double)ntok,
+            LAUNCH(c, PC_MLP, 2.0 * 36864 * (double)ntok,
                    mlp_fused(w.ao, w.c2, w.cs, (const bf16*)(pk + c.m->mlp_w1f_off[l * 6 + j]),
                              (const float*)(pk + c.m->mlp_b1f_off[l * 6 + j]), c.Wt(b + "mlp.fc2.weight"),
                              c.F(b + "mlp.fc2.bias"), w.y, ntok, (size_t)R * Rw, c.s));
@@ -447,9 +448,9 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
         const std::string b = buf;
         LAUNCH(c, PC_LN, 0.0, layernorm96(w.y, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
         SRB_TRY(tc_layer(c, b + "qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
-        LAUNCH(c, PC_ATTN, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const bf16*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
+        LAUNCH(c, PC_OCAB, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const bf16*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
         SRB_TRY(tc_layer(c, b + "proj", w.ao, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));
-        LAUNCH(c, PC_LINEAR, 2.0 * 36864 * (double)ntok,
+        LAUNCH(c, PC_MLP, 2.0 * 36864 * (double)ntok,
                mlp_fused(w.y, nullptr, nullptr, (const bf16*)(pk + c.m->mlp_w1f_off[24 + l]),
                          (const float*)(pk + c.m->mlp_b1f_off[24 + l]), c.Wt(b + "mlp.fc2.weight"),
                          c.F(b + "mlp.fc2.bias"), w.y, ntok, (size_t)R * Rw, c.s));
