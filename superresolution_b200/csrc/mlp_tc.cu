@@ -231,15 +231,17 @@ mlp_tc_kernel(const MlpArgs a) {
                     v[8 * m + 2 * k] = f.x; v[8 * m + 2 * k + 1] = f.y;
                 }
             }
-            float s = 0.f;
+            float s4[4] = {0.f, 0.f, 0.f, 0.f};  // four independent chains instead of one 24-deep one
 #pragma unroll
-            for (int k = 0; k < 24; ++k) s += v[k];
+            for (int k = 0; k < 24; ++k) s4[k & 3] += v[k];
+            float s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
             s += __shfl_xor_sync(0xffffffffu, s, 1);
             s += __shfl_xor_sync(0xffffffffu, s, 2);
             const float mean = s * (1.f / 96.f);
-            float m2 = 0.f;
+            float q4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int k = 0; k < 24; ++k) { v[k] -= mean; m2 = fmaf(v[k], v[k], m2); }
+            for (int k = 0; k < 24; ++k) { v[k] -= mean; q4[k & 3] = fmaf(v[k], v[k], q4[k & 3]); }
+            float m2 = (q4[0] + q4[1]) + (q4[2] + q4[3]);
             m2 += __shfl_xor_sync(0xffffffffu, m2, 1);
             m2 += __shfl_xor_sync(0xffffffffu, m2, 2);
             const float rs = rsqrtf(m2 * (1.f / 96.f) + 1e-5f);

@@ -34,7 +34,7 @@ torch.cuda.synchronize()
 lib.srb_debug_set_phase_buffer(None)
 p = buf.view(148, 8).double().mean(0)
 names = ['wait_d1', 'gelu+bar', 'ln_combine', 'ln_stats+A1', 'ln_fence', 'issue_loads', 'wait_d2+epi', 'epi_bar+copyout']
-tot = p.sum().item()
+tot = p.sum().item() or 1.0  # all zero unless libsrb was built with EXTRA=-DSRB_MLP_PHASES
 for n, v in zip(names, p):
     print(f'{n:12s} {v.item() / 55.35:8.0f} cyc/tile {100 * v.item() / tot:5.1f}%')
 print('total cyc/tile', tot / 55.35)
