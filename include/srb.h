@@ -77,6 +77,19 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
                        int taps, int act, float slope, float alpha1, const void* res1, int res1_f32, int res1_pitch,
                        float alpha2, const void* res2, int res2_f32, int res2_pitch, const float* res2_cs,
                        int pixel_shuffle, void* stream);
+/* Attention branch of a HAB block (upstream hat_arch.py HAB.forward: norm1 -> (shifted) window_partition -> qkv ->
+ * softmax(q k^T * head_dim^-0.5 + relative_position_bias + shift mask) v -> proj -> window_reverse -> + shortcut;
+ * reached from src/architecture.py:78) as ONE kernel over tokens x: bf16 [B,H,W,96]:
+ *   xn = LayerNorm(x) (needed by the parallel CAB branch),  t = x + proj(W-MSA(xn)).
+ * window 8, 6 heads, shift 0 or 4 (cyclic shift + the -100 region mask of calculate_mask); H % 8 == 0, W % 16 == 0.
+ * wqkv_packed bf16 [288][96], wproj_packed bf16 [96][96] (srb_pack_conv_weight, taps = 1).
+ * bias_frag_log2e = srb_expand_rel_bias(table [225][6] fp32, index int64 [64*64] (relative_position_index_SA),
+ * NK = 64, scale = log2(e)): the gathered bias in tensor-core fragment order (NK = 144, scale 1 for OCAB). */
+int srb_expand_rel_bias(const float* table, int T, const int64_t* index, int NK, void* out_bf16, float scale,
+                        void* stream);
+int srb_hab_attention(const void* x, const float* ln_g, const float* ln_b, const void* wqkv_packed, const float* bqkv,
+                      const void* bias_frag_log2e, const void* wproj_packed, const float* bproj, void* xn, void* t,
+                      int B, int H, int W, int shift, void* stream);
 /* Token-wise MLP branch of a HAT block (HAB / OCAB; upstream hat_arch.py `x = x + mlp(norm2(x))`, reached from
  * src/architecture.py:78) as ONE tcgen05 kernel:   y0 = t + cab*cs[b,:] (cab/cs may be NULL: y0 = t);
  *   y = y0 + fc2(GELU(fc1(LayerNorm(y0)))).   t, cab, y: bf16 [ntok,96] (y may alias t); cs: fp32 [B,96];

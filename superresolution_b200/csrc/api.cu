@@ -78,6 +78,27 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
     return conv_tc_launch(a, (cudaStream_t)stream);
 }
 
+int srb_expand_rel_bias(const float* table, int T, const int64_t* index, int NK, void* out_bf16, float scale,
+                        void* stream) {
+    if (!table || !index || !out_bf16 || T <= 0 || (NK != 64 && NK != 144)) {
+        set_error("expand_rel_bias: bad args (NK must be 64 or 144)");
+        return SRB_E_ARG;
+    }
+    return expand_rel_bias_bf16(table, T, index, NK, (bf16*)out_bf16, scale, (cudaStream_t)stream);
+}
+
+int srb_hab_attention(const void* x, const float* ln_g, const float* ln_b, const void* wqkv_packed, const float* bqkv,
+                      const void* bias_frag_log2e, const void* wproj_packed, const float* bproj, void* xn, void* t,
+                      int B, int H, int W, int shift, void* stream) {
+    if (!x || !ln_g || !ln_b || !wqkv_packed || !bqkv || !bias_frag_log2e || !wproj_packed || !bproj || !xn || !t ||
+        B <= 0 || (shift != 0 && shift != 4)) {
+        set_error("hab_attention: bad args (shift must be 0 or 4)");
+        return SRB_E_ARG;
+    }
+    return hab_attention_tc((const bf16*)x, ln_g, ln_b, (const bf16*)wqkv_packed, bqkv, (const bf16*)bias_frag_log2e,
+                            (const bf16*)wproj_packed, bproj, (bf16*)xn, (bf16*)t, B, H, W, shift, (cudaStream_t)stream);
+}
+
 int srb_fold_ln_linear(const float* w, const float* b, const float* gamma, const float* beta, void* w_folded,
                        float* b_folded, int N, int K, void* stream) {
     if (!w || !b || !gamma || !beta || !w_folded || !b_folded || N <= 0 || K <= 0) {

@@ -1,15 +1,10 @@
-// Window self-attention of HAB ((S)W-MSA, 8x8 windows, 6 heads x 16) and overlapping cross-attention of OCAB
-// (8x8 queries x 12x12 zero-padded keys).  SURVEY.md §2.2 rows K12, K15; App. A.2.4-7.
+// Overlapping cross-attention core of OCAB (8x8 query windows x 12x12 zero-padded key/value windows, 6 heads x 16)
+// and the relative-position-bias expansion shared with the HAB branch (hab_tc.cu).  SURVEY.md §2.2 K15; App. A.2.6-7.
 //
-// The cyclic shift (torch.roll), window partition/reverse and nn.Unfold are pure index math in the loads/stores:
-// nothing is materialised.  One warp per (window, head): S = QK^T and O = PV run on the tensor cores through
-// warp-level mma.sync (head_dim 16 == one k-step); softmax (fp32, max-subtracted) lives in registers, P feeds the
-// second MMA straight from the accumulator fragments (flash-style).
-//  * HAB kernel: persistent CTAs (12 warps = 2 window slots x 6 heads), the relative-position bias of the layer sits in
-//    shared memory in MMA-fragment order (bf16, 48 KB, conflict-free 8-byte reads), qkv tiles are double buffered
-//    with cp.async, outputs are written back through shared memory as coalesced 16-byte stores.
-//  * OCAB kernel: one CTA per window (6 warps), fragment-ordered fp32 bias read straight from L2 (coalesced).
-// Attention proper is 7% of the model FLOPs; the tcgen05 budget goes to the convs/linears (conv_tc.cu).
+// nn.Unfold is pure index math in the loads: the 0.9 GB unfolded key/value buffer of the reference never exists, the
+// zero-padded keys stay in the softmax with logit = bias.  One CTA per window, one warp per head: S = QK^T and O = PV
+// run on warp-level mma.sync (head_dim 16 == one k-step); softmax (fp32, max-subtracted) lives in registers, P feeds
+// the second MMA straight from the accumulator fragments (flash-style); fragment-ordered bf16 bias is read from L2.
 #include "common.h"
 #include "ops.h"
 
@@ -157,199 +152,6 @@ __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16
     }
 }
 
-// Two query m-tiles (rows [32*mh, 32*mh+32)) of one (window, head) at once: the S-MMAs, softmax and PV-MMAs of both
-// tiles are interleaved stage by stage so that the tensor pipe, the MUFU (exp) and the FMA pipe overlap inside one
-// warp.  bias fragments live in shared memory (bf16, fragment order).  `masked` is warp-uniform.
-__device__ __forceinline__ void attend_head_pair(bf16* sQ, const bf16* sK, const bf16* sV, const bf16* bias_h,
-                                                 const int* srid, bool masked, int h, int lane, int mh) {
-    const int g = lane >> 2, t = lane & 3;
-    uint32_t qa[2][4];
-    load_a_frag(qa[0], sQ, 32 * mh, h * 16, lane);
-    load_a_frag(qa[1], sQ, 32 * mh + 16, h * 16, lane);
-    float s[2][8][4];
-#pragma unroll
-    for (int j = 0; j < 8; j += 2) {
-        uint32_t kb[4];
-        load_b_frag2(kb, sK, 8 * j, h * 16, lane);
-#pragma unroll
-        for (int m = 0; m < 2; ++m) {
-            s[m][j][0] = s[m][j][1] = s[m][j][2] = s[m][j][3] = 0.f;
-            s[m][j + 1][0] = s[m][j + 1][1] = s[m][j + 1][2] = s[m][j + 1][3] = 0.f;
-            mma_bf16_16816(s[m][j], qa[m][0], qa[m][1], qa[m][2], qa[m][3], kb[0], kb[1]);
-            mma_bf16_16816(s[m][j + 1], qa[m][0], qa[m][1], qa[m][2], qa[m][3], kb[2], kb[3]);
-        }
-    }
-    float mx[2][2], l[2][2];
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-        const int mt = 2 * mh + m;
-        mx[m][0] = mx[m][1] = -1e30f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const uint2 raw = *(const uint2*)(bias_h + ((mt * 8 + j) * 32 + lane) * 4);
-            const float2 lo = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
-            const float2 hi = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
-            s[m][j][0] = fmaf(s[m][j][0], 0.25f, lo.x);
-            s[m][j][1] = fmaf(s[m][j][1], 0.25f, lo.y);
-            s[m][j][2] = fmaf(s[m][j][2], 0.25f, hi.x);
-            s[m][j][3] = fmaf(s[m][j][3], 0.25f, hi.y);
-        }
-        if (masked) {  // shift mask (-100 across region borders): only windows touching the last window row / column
-            const int rid0 = srid[16 * mt + g], rid1 = srid[16 * mt + g + 8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int rc0 = srid[8 * j + 2 * t], rc1 = srid[8 * j + 2 * t + 1];
-                if (rc0 != rid0) s[m][j][0] -= 100.f;
-                if (rc1 != rid0) s[m][j][1] -= 100.f;
-                if (rc0 != rid1) s[m][j][2] -= 100.f;
-                if (rc1 != rid1) s[m][j][3] -= 100.f;
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            mx[m][0] = fmaxf(mx[m][0], fmaxf(s[m][j][0], s[m][j][1]));
-            mx[m][1] = fmaxf(mx[m][1], fmaxf(s[m][j][2], s[m][j][3]));
-        }
-    }
-#pragma unroll
-    for (int m = 0; m < 2; ++m)
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            mx[m][e] = fmaxf(mx[m][e], __shfl_xor_sync(0xffffffffu, mx[m][e], 1));
-            mx[m][e] = fmaxf(mx[m][e], __shfl_xor_sync(0xffffffffu, mx[m][e], 2));
-            l[m][e] = 0.f;
-        }
-    float o[2][2][4];
-#pragma unroll
-    for (int m = 0; m < 2; ++m)
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) o[m][nt][0] = o[m][nt][1] = o[m][nt][2] = o[m][nt][3] = 0.f;
-#pragma unroll
-    for (int kt = 0; kt < 4; ++kt) {
-        uint32_t vb[4];
-        ldsm_x4_trans(vb, sV + (16 * kt + (lane & 7) + ((lane >> 3) & 1) * 8) * AP + h * 16 + (lane >> 4) * 8);
-#pragma unroll
-        for (int m = 0; m < 2; ++m) {
-            float e[2][4];
-#pragma unroll
-            for (int jj = 0; jj < 2; ++jj) {
-                const int j = 2 * kt + jj;
-                e[jj][0] = __expf(s[m][j][0] - mx[m][0]);
-                e[jj][1] = __expf(s[m][j][1] - mx[m][0]);
-                e[jj][2] = __expf(s[m][j][2] - mx[m][1]);
-                e[jj][3] = __expf(s[m][j][3] - mx[m][1]);
-                l[m][0] += e[jj][0] + e[jj][1];
-                l[m][1] += e[jj][2] + e[jj][3];
-            }
-            const uint32_t p0 = pack_bf16(e[0][0], e[0][1]), p1 = pack_bf16(e[0][2], e[0][3]);
-            const uint32_t p2 = pack_bf16(e[1][0], e[1][1]), p3 = pack_bf16(e[1][2], e[1][3]);
-            mma_bf16_16816(o[m][0], p0, p1, p2, p3, vb[0], vb[1]);
-            mma_bf16_16816(o[m][1], p0, p1, p2, p3, vb[2], vb[3]);
-        }
-    }
-    __syncwarp();  // every lane has read its Q fragments before they are overwritten
-#pragma unroll
-    for (int m = 0; m < 2; ++m) {
-        float l0 = l[m][0], l1 = l[m][1];
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-        const float i0 = 1.f / l0, i1 = 1.f / l1;
-        const int r0 = 32 * mh + 16 * m + g, r1 = r0 + 8;
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-            *(uint32_t*)(sQ + r0 * AP + h * 16 + 8 * nt + 2 * t) = pack_bf16(o[m][nt][0] * i0, o[m][nt][1] * i0);
-            *(uint32_t*)(sQ + r1 * AP + h * 16 + 8 * nt + 2 * t) = pack_bf16(o[m][nt][2] * i1, o[m][nt][3] * i1);
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// HAB: persistent, 2 window slots x 6 warps
-// ---------------------------------------------------------------------------------------------------------------
-constexpr int HAB_TILE = 3 * 64 * AP;                   // bf16 elements of one window's q|k|v tile
-constexpr int HAB_BIAS = 6 * 4 * 8 * 32 * 4;            // bf16 elements (fragment order)
-constexpr int HAB_SMEM = HAB_BIAS * 2 + 4 * HAB_TILE * 2 + 2 * 2 * 128 * 4;
-
-__global__ void __launch_bounds__(384, 1)
-hab_attn_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ bias_frag, bf16* __restrict__ out, int B,
-                int H, int W, int shift) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    bf16* sbias = (bf16*)smem_raw;
-    bf16* tiles = sbias + HAB_BIAS;                 // [slot][buf][q|k|v][64][AP]
-    int* meta = (int*)(tiles + 4 * HAB_TILE);       // [slot][buf][128]: pixel index, region id
-    const int slot = threadIdx.x / 192, tl = threadIdx.x % 192;
-    const int nwx = W / 8, nwy = H / 8, nwin = B * nwx * nwy;
-
-    for (int i = threadIdx.x; i < HAB_BIAS / 8; i += 384) ((uint4*)sbias)[i] = __ldg((const uint4*)bias_frag + i);
-
-    auto issue_load = [&](int win, int buf) {
-        bf16* tq = tiles + (slot * 2 + buf) * HAB_TILE;
-        int* mt_ = meta + (slot * 2 + buf) * 128;
-        const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
-        const size_t img = (size_t)b * H * W;
-        for (int i = tl; i < 64 * 36; i += 192) {
-            const int n = i / 36, ck = i % 36;  // 36 x 16 B per token: q(12) k(12) v(12)
-            const int ys = wy * 8 + (n >> 3), xs = wx * 8 + (n & 7);  // coordinates in the rolled image
-            const int y = (ys + shift) % H, x = (xs + shift) % W;     // torch.roll(-shift): rolled[i] = orig[i+shift]
-            const size_t pix = img + (size_t)y * W + x;
-            const int part = ck / 12, c = ck % 12;
-            cp_async16(tq + part * 64 * AP + n * AP + c * 8, qkv + pix * 288 + ck * 8);
-            if (ck == 0) {
-                mt_[n] = (int)(pix - img);
-                const int rh = ys < H - 8 ? 0 : (ys < H - 4 ? 1 : 2);
-                const int rw = xs < W - 8 ? 0 : (xs < W - 4 ? 1 : 2);
-                mt_[64 + n] = rh * 3 + rw;
-            }
-        }
-    };
-
-    const int stride = gridDim.x * 2;
-    int win = blockIdx.x * 2 + slot;
-    if (win < nwin) issue_load(win, 0);
-    cp_async_commit();
-    __syncthreads();  // bias resident
-    int it = 0;
-    for (; win < nwin; win += stride, ++it) {
-        const int buf = it & 1;
-        if (win + stride < nwin) issue_load(win + stride, buf ^ 1);
-        cp_async_commit();
-        cp_async_wait<1>();
-        bar_sync(1 + slot, 192);
-        bf16* tq = tiles + (slot * 2 + buf) * HAB_TILE;
-        const int* mt_ = meta + (slot * 2 + buf) * 128;
-        const int h = tl >> 5, lane = tl & 31;
-        attend_head<64, bf16>(tq, tq + 64 * AP, tq + 128 * AP, sbias + h * (4 * 8 * 32 * 4), mt_ + 64, shift > 0, h, lane);
-        bar_sync(1 + slot, 192);
-        // coalesced write-back of the 64 x 96 output tile (now sitting in the Q tile)
-        const int b = win / (nwx * nwy);
-        const size_t img = (size_t)b * H * W;
-        for (int i = tl; i < 64 * 12; i += 192) {
-            const int n = i / 12, c = i % 12;
-            *(uint4*)(out + (img + mt_[n]) * 96 + c * 8) = *(const uint4*)(tq + n * AP + c * 8);
-        }
-        bar_sync(1 + slot, 192);  // tile + meta free before the next prefetch overwrites them
-    }
-    cp_async_wait<0>();
-}
-
-int window_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, int shift,
-                     cudaStream_t s) {
-    if (H % 8 || W % 8) { set_error("attention: H=%d W=%d must be multiples of the window size 8", H, W); return SRB_E_SHAPE; }
-    static bool attr = false;
-    if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(hab_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HAB_SMEM));
-        attr = true;
-    }
-    const int nwin = B * (H / 8) * (W / 8);
-    int grid = (nwin + 1) / 2;
-    if (grid > 148) grid = 148;
-    hab_attn_kernel<<<grid, 384, HAB_SMEM, s>>>(qkv, bias_frag, out, B, H, W, shift);
-    SRB_CUDA(cudaGetLastError());
-    return SRB_OK;
-}
-
 // ---------------------------------------------------------------------------------------------------------------
 // OCAB: one CTA per window, 6 warps; keys/values = 12x12 neighbourhood with ZERO vectors outside the image that
 // still take part in the softmax (nn.Unfold pads the projected K/V maps; logit = bias only).  App. A.2.6.
@@ -441,276 +243,6 @@ int expand_rel_bias_f32(const float* table, int T, const int64_t* index, int NK,
     return SRB_OK;
 }
 
-}  // namespace srb
-
-namespace srb {
-
-// ---------------------------------------------------------------------------------------------------------------
-// Fused HAB attention branch (App. A.2.4):  t = x + proj( W-MSA( LN1(x) ) ),  and  xn = LN1(x)  for the CAB branch.
-// One persistent CTA (6 warps = 6 heads) walks over windows; weights (qkv 288x96, proj 96x96, bf16), the layer's
-// relative-position bias (fragment order) and the LayerNorm affine live in shared memory for the whole kernel.
-// Per window: cp.async gather of the 64 tokens (cyclic shift = index math, next window prefetched) -> LayerNorm in
-// fp32 -> qkv GEMM -> per-head attention -> proj GEMM + bias + shortcut -> coalesced scatter.  Nothing but x is read
-// from HBM and only xn and t are written: the qkv / attention-output round trips (1.6 GB per block at B=16) are gone.
-// The three small GEMMs (K = 96) run on warp-level mma.sync next to the softmax/LN CUDA-core work of the same warps.
-// ---------------------------------------------------------------------------------------------------------------
-constexpr int FA_WQKV = 288 * AP, FA_WPROJ = 96 * AP, FA_TILE = 64 * AP;
-constexpr int FA_SMEM = (FA_WQKV + FA_WPROJ + HAB_BIAS + 2 * FA_TILE /*x*/ + FA_TILE /*xn*/ + 3 * FA_TILE /*qkv*/) * 2 +
-                        2 * 128 * 4 /*meta*/ + (288 + 96 + 96 + 96) * 4;
-
-struct FusedAttnArgs {
-    const bf16* x;        // [B,H,W,96] token stream (shortcut)
-    const float *ln_g, *ln_b;
-    const bf16* wqkv;     // [288][96]
-    const float* bqkv;    // [288]
-    const bf16* bias_frag;
-    const bf16* wproj;    // [96][96]
-    const float* bproj;   // [96]
-    bf16* xn;             // [B,H,W,96] LN1(x)
-    bf16* t;              // [B,H,W,96] x + proj(attn)
-    int B, H, W, shift;
-    long long* dbg;  // optional [grid][8] per-phase cycle totals (development aid)
-};
-
-constexpr int FA_THREADS = 384;  // 12 warps: (m-half, head / column group)
-
-__global__ void __launch_bounds__(FA_THREADS, 1)
-hab_fused_attn_kernel(const FusedAttnArgs a) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    bf16* sWq = (bf16*)smem_raw;
-    bf16* sWp = sWq + FA_WQKV;
-    bf16* sBias = sWp + FA_WPROJ;
-    bf16* sX = sBias + HAB_BIAS;        // [2][64][AP]
-    bf16* sXN = sX + 2 * FA_TILE;       // [64][AP]
-    bf16* sQKV = sXN + FA_TILE;         // [3][64][AP]
-    int* meta = (int*)(sQKV + 3 * FA_TILE);  // [2][128]
-    float* sbq = (float*)(meta + 256);
-    float* sbp = sbq + 288;
-    float* sg = sbp + 96;
-    float* sb = sg + 96;
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int g = lane >> 2, tq = lane & 3;
-    const int mh = warp / 6, ng = warp % 6;  // m-half (m-tiles 2mh, 2mh+1) and column group / head
-    const int H = a.H, W = a.W, shift = a.shift;
-    const int nwx = W / 8, nwy = H / 8, nwin = a.B * nwx * nwy;
-
-    // ---- one-time: weights, bias tables, affine parameters ----
-    for (int i = tid; i < 288 * 12; i += FA_THREADS) *(uint4*)(sWq + (i / 12) * AP + (i % 12) * 8) = __ldg((const uint4*)a.wqkv + i);
-    for (int i = tid; i < 96 * 12; i += FA_THREADS) *(uint4*)(sWp + (i / 12) * AP + (i % 12) * 8) = __ldg((const uint4*)a.wproj + i);
-    for (int i = tid; i < HAB_BIAS / 8; i += FA_THREADS) ((uint4*)sBias)[i] = __ldg((const uint4*)a.bias_frag + i);
-    if (tid < 288) sbq[tid] = a.bqkv[tid];
-    if (tid < 96) { sbp[tid] = a.bproj[tid]; sg[tid] = a.ln_g[tid]; sb[tid] = a.ln_b[tid]; }
-
-    // each thread always moves the same two 16-byte chunks of a window tile: (token n, chunk ck) fixed per thread
-    const int ld_n0 = tid / 12, ld_c0 = tid % 12, ld_n1 = (tid + FA_THREADS) / 12, ld_c1 = (tid + FA_THREADS) % 12;
-    auto issue_load = [&](int win, int buf) {
-        bf16* dst = sX + buf * FA_TILE;
-        int* mt_ = meta + buf * 128;
-        const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
-        const size_t img = (size_t)b * H * W;
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const int n = k ? ld_n1 : ld_n0, ck = k ? ld_c1 : ld_c0;
-            const int ys = wy * 8 + (n >> 3), xs = wx * 8 + (n & 7);  // rolled-image coordinates
-            int y = ys + shift, x = xs + shift;                       // torch.roll(-shift): rolled[i] = orig[i+shift]
-            if (y >= H) y -= H;
-            if (x >= W) x -= W;
-            const int pix = y * W + x;
-            cp_async16(dst + n * AP + ck * 8, a.x + (img + pix) * 96 + ck * 8);
-            if (ck == 0) {
-                mt_[n] = pix;
-                const int rh = ys < H - 8 ? 0 : (ys < H - 4 ? 1 : 2);
-                const int rw = xs < W - 8 ? 0 : (xs < W - 4 ? 1 : 2);
-                mt_[64 + n] = rh * 3 + rw;
-            }
-        }
-    };
-
-    int win = blockIdx.x;
-    if (win < nwin) issue_load(win, 0);
-    cp_async_commit();
-    int it = 0;
-    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    long long tprev = clock64();
-#define SRB_PHASE(i) do { if (a.dbg && tid == 0) { const long long tn = clock64(); ph[i] += tn - tprev; tprev = tn; } } while (0)
-    for (; win < nwin; win += gridDim.x, ++it) {
-        const int buf = it & 1;
-        if (win + (int)gridDim.x < nwin) issue_load(win + gridDim.x, buf ^ 1);
-        cp_async_commit();
-        cp_async_wait<1>();
-        __syncthreads();
-        SRB_PHASE(0);
-        bf16* x_t = sX + buf * FA_TILE;
-        const int* mt_ = meta + buf * 128;
-        const size_t img = (size_t)(win / (nwx * nwy)) * H * W;
-
-        // ---- LayerNorm (fp32, eps 1e-5): 4 lanes per token, 24 channels each ----
-        if (tid < 256) {
-            const int n = tid >> 2, part = tid & 3;
-            float v[24];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const uint4 raw = *(const uint4*)(x_t + n * AP + part * 24 + c * 8);
-                const __nv_bfloat162* h2 = (const __nv_bfloat162*)&raw;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float2 f = __bfloat1622float2(h2[k]);
-                    v[c * 8 + 2 * k] = f.x;
-                    v[c * 8 + 2 * k + 1] = f.y;
-                }
-            }
-            float s = 0.f;
-#pragma unroll
-            for (int j = 0; j < 24; ++j) s += v[j];
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            const float mean = s * (1.f / 96.f);
-            float q = 0.f;
-#pragma unroll
-            for (int j = 0; j < 24; ++j) q += (v[j] - mean) * (v[j] - mean);
-            q += __shfl_xor_sync(0xffffffffu, q, 1);
-            q += __shfl_xor_sync(0xffffffffu, q, 2);
-            const float rstd = rsqrtf(q * (1.f / 96.f) + 1e-5f);
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                uint4 o;
-                __nv_bfloat162* h2 = (__nv_bfloat162*)&o;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int ch = part * 24 + c * 8 + 2 * k;
-                    h2[k] = __floats2bfloat162_rn((v[c * 8 + 2 * k] - mean) * rstd * sg[ch] + sb[ch],
-                                                  (v[c * 8 + 2 * k + 1] - mean) * rstd * sg[ch + 1] + sb[ch + 1]);
-                }
-                *(uint4*)(sXN + n * AP + part * 24 + c * 8) = o;
-            }
-        }
-        __syncthreads();
-        SRB_PHASE(1);
-        // xn -> HBM for the CAB branch (coalesced 16-byte chunks)
-        for (int i = tid; i < 64 * 12; i += FA_THREADS) {
-            const int n = i / 12, c = i % 12;
-            *(uint4*)(a.xn + (img + mt_[n]) * 96 + c * 8) = *(const uint4*)(sXN + n * AP + c * 8);
-        }
-
-        // ---- qkv = xn @ Wqkv^T + b : warp (mh, ng) owns rows [32mh, 32mh+32) x columns [48ng, 48ng+48) ----
-        {
-            float acc[2][6][4];
-#pragma unroll
-            for (int m = 0; m < 2; ++m)
-#pragma unroll
-                for (int n = 0; n < 6; ++n) acc[m][n][0] = acc[m][n][1] = acc[m][n][2] = acc[m][n][3] = 0.f;
-#pragma unroll
-            for (int ks = 0; ks < 6; ++ks) {
-                uint32_t af[2][4], bfr[3][4];
-                load_a_frag(af[0], sXN, 32 * mh, 16 * ks, lane);
-                load_a_frag(af[1], sXN, 32 * mh + 16, 16 * ks, lane);
-#pragma unroll
-                for (int n2 = 0; n2 < 3; ++n2) load_b_frag2(bfr[n2], sWq, 48 * ng + 16 * n2, 16 * ks, lane);
-#pragma unroll
-                for (int m = 0; m < 2; ++m)
-#pragma unroll
-                    for (int n2 = 0; n2 < 3; ++n2) {
-                        mma_bf16_16816(acc[m][2 * n2], af[m][0], af[m][1], af[m][2], af[m][3], bfr[n2][0], bfr[n2][1]);
-                        mma_bf16_16816(acc[m][2 * n2 + 1], af[m][0], af[m][1], af[m][2], af[m][3], bfr[n2][2], bfr[n2][3]);
-                    }
-            }
-#pragma unroll
-            for (int m = 0; m < 2; ++m) {
-                const int r0 = 32 * mh + 16 * m + g, r1 = r0 + 8;
-#pragma unroll
-                for (int n = 0; n < 6; ++n) {
-                    const int c = 48 * ng + 8 * n + 2 * tq;  // output column in [0,288)
-                    const int part = c / 96, cc = c % 96;
-                    const float b0 = sbq[c], b1 = sbq[c + 1];
-                    bf16* dst = sQKV + part * FA_TILE + cc;
-                    *(uint32_t*)(dst + r0 * AP) = pack_bf16(acc[m][n][0] + b0, acc[m][n][1] + b1);
-                    *(uint32_t*)(dst + r1 * AP) = pack_bf16(acc[m][n][2] + b0, acc[m][n][3] + b1);
-                }
-            }
-        }
-        __syncthreads();
-        SRB_PHASE(2);
-
-        // ---- per-head attention (head ng, query rows of m-half mh); output overwrites the Q tile ----
-        {
-            const int wxx = win % nwx, wyy = (win / nwx) % nwy;
-            const bool masked = shift > 0 && (wxx == nwx - 1 || wyy == nwy - 1);  // other windows: one region, no mask
-            attend_head_pair(sQKV, sQKV + FA_TILE, sQKV + 2 * FA_TILE, sBias + ng * (4 * 8 * 32 * 4), mt_ + 64, masked,
-                             ng, lane, mh);
-        }
-        __syncthreads();
-        SRB_PHASE(3);
-
-        // ---- t = x + attn @ Wproj^T + b : warp (mh, ng) owns rows [32mh, +32) x columns [16ng, +16) ----
-        {
-            float acc[2][2][4];
-#pragma unroll
-            for (int m = 0; m < 2; ++m)
-#pragma unroll
-                for (int n = 0; n < 2; ++n) acc[m][n][0] = acc[m][n][1] = acc[m][n][2] = acc[m][n][3] = 0.f;
-#pragma unroll
-            for (int ks = 0; ks < 6; ++ks) {
-                uint32_t af[2][4], bfr[4];
-                load_a_frag(af[0], sQKV, 32 * mh, 16 * ks, lane);
-                load_a_frag(af[1], sQKV, 32 * mh + 16, 16 * ks, lane);
-                load_b_frag2(bfr, sWp, 16 * ng, 16 * ks, lane);
-#pragma unroll
-                for (int m = 0; m < 2; ++m) {
-                    mma_bf16_16816(acc[m][0], af[m][0], af[m][1], af[m][2], af[m][3], bfr[0], bfr[1]);
-                    mma_bf16_16816(acc[m][1], af[m][0], af[m][1], af[m][2], af[m][3], bfr[2], bfr[3]);
-                }
-            }
-#pragma unroll
-            for (int m = 0; m < 2; ++m) {
-                const int r0 = 32 * mh + 16 * m + g, r1 = r0 + 8;
-#pragma unroll
-                for (int n = 0; n < 2; ++n) {
-                    const int c = 16 * ng + 8 * n + 2 * tq;
-                    const float b0 = sbp[c], b1 = sbp[c + 1];
-                    bf16* p0 = x_t + r0 * AP + c;
-                    bf16* p1 = x_t + r1 * AP + c;
-                    const float2 x0 = __bfloat1622float2(*(const __nv_bfloat162*)p0);
-                    const float2 x1 = __bfloat1622float2(*(const __nv_bfloat162*)p1);
-                    *(uint32_t*)p0 = pack_bf16(acc[m][n][0] + b0 + x0.x, acc[m][n][1] + b1 + x0.y);
-                    *(uint32_t*)p1 = pack_bf16(acc[m][n][2] + b0 + x1.x, acc[m][n][3] + b1 + x1.y);
-                }
-            }
-        }
-        __syncthreads();
-        SRB_PHASE(4);
-        for (int i = tid; i < 64 * 12; i += FA_THREADS) {
-            const int n = i / 12, c = i % 12;
-            *(uint4*)(a.t + (img + mt_[n]) * 96 + c * 8) = *(const uint4*)(x_t + n * AP + c * 8);
-        }
-        __syncthreads();  // x tile / meta / xn / qkv tiles free for the next window
-        SRB_PHASE(5);
-    }
-    cp_async_wait<0>();
-    if (a.dbg && tid == 0)
-        for (int i = 0; i < 8; ++i) a.dbg[blockIdx.x * 8 + i] = ph[i];
-#undef SRB_PHASE
-}
-
-long long* g_fa_dbg = nullptr;  // set through srb_debug_set_phase_buffer (development aid)
-
-int hab_fused_attention(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
-                        const bf16* bias_frag, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
-                        int W, int shift, cudaStream_t s) {
-    if (H % 8 || W % 8) { set_error("attention: H=%d W=%d must be multiples of the window size 8", H, W); return SRB_E_SHAPE; }
-    static bool attr = false;
-    if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(hab_fused_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
-        attr = true;
-    }
-    FusedAttnArgs a;
-    a.x = x; a.ln_g = ln_g; a.ln_b = ln_b; a.wqkv = wqkv; a.bqkv = bqkv; a.bias_frag = bias_frag; a.wproj = wproj;
-    a.bproj = bproj; a.xn = xn; a.t = t; a.B = B; a.H = H; a.W = W; a.shift = shift;
-    a.dbg = g_fa_dbg;
-    const int nwin = B * (H / 8) * (W / 8);
-    hab_fused_attn_kernel<<<nwin < 148 ? nwin : 148, FA_THREADS, FA_SMEM, s>>>(a);
-    SRB_CUDA(cudaGetLastError());
-    return SRB_OK;
-}
+long long* g_fa_dbg = nullptr;  // set through srb_debug_set_phase_buffer (development aid: per-phase cycle buffers)
 
 }  // namespace srb

@@ -26,23 +26,12 @@ int cab_pool_slabs(int HW);  // pool scratch = B * slabs * 96 floats
 int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const float* w1, const float* b1,
                           const float* w2, const float* b2, float conv_scale, int B, int HW, cudaStream_t s);
 
-// attn.cu
-// qkv: bf16 [B,H,W,288] = [q(96) | k(96) | v(96)], head h = channels [16h,16h+16) of each part.
-// bias_frag: relative-position bias gathered into MMA C-fragment order (expand_rel_bias_*), bf16 for HAB (staged in
-// shared memory), fp32 for OCAB.  shift: 0 or 4 (HAB cyclic shift, mask -100 across region borders).
-// out: bf16 [B,H,W,96].
-int window_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, int shift,
-                     cudaStream_t s);
-// fused HAB attention branch: xn = LN1(x); t = x + proj(W-MSA(xn)) + bproj   (one pass over x)
-int hab_fused_attention(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
-                        const bf16* bias_frag, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
-                        int W, int shift, cudaStream_t s);
-// hab_tc.cu — the same branch with the qkv / proj GEMMs on tcgen05 (TMEM accumulators) over 128-token tiles;
-// bias_frag_log2e: expand_rel_bias_bf16(..., scale = log2(e))
+// hab_tc.cu — fused HAB attention branch: xn = LN1(x); t = x + proj((S)W-MSA(xn)) + bproj (one pass over x), the qkv /
+// proj GEMMs on tcgen05 (TMEM accumulators) over 128-token tiles; bias_frag_log2e: expand_rel_bias_bf16(..., scale = log2(e))
 int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
                      const bf16* bias_frag_log2e, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
                      int W, int shift, cudaStream_t s);
-// OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.
+// attn.cu — OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.
 int ocab_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s);
 // table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> fragment-ordered bias [6*64*NK]
 int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, float scale,

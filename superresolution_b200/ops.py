@@ -60,3 +60,21 @@ def mlp_branch(t, w1_folded, b1_folded, w2_packed, b2, cab=None, cs=None, out=No
                                 L.ptr(b2), L.ptr(out), ntok, tok_per_img, L.current_stream())
     L.check(rc, 'mlp_branch')
     return out
+
+
+def expand_rel_bias(table, index, nk, scale=1.0):
+    """table fp32 [T,6], index int64 [64,nk] -> bf16 bias in MMA fragment order [6*64*nk] (times `scale`)."""
+    out = torch.empty(6 * 64 * nk, dtype=torch.bfloat16, device=table.device)
+    L.check(L.lib().srb_expand_rel_bias(L.ptr(table.float().contiguous()), table.shape[0], L.ptr(index.contiguous()),
+                                        nk, L.ptr(out), scale, L.current_stream()), 'expand_rel_bias')
+    return out
+
+
+def hab_attention(x, ln_g, ln_b, wqkv_packed, bqkv, bias_frag_log2e, wproj_packed, bproj, shift):
+    """x: bf16 [B,H,W,96] -> (xn, t): LayerNorm(x) and x + proj(window attention(xn))."""
+    B, H, W, _ = x.shape
+    xn, t = torch.empty_like(x), torch.empty_like(x)
+    L.check(L.lib().srb_hab_attention(L.ptr(x), L.ptr(ln_g), L.ptr(ln_b), L.ptr(wqkv_packed), L.ptr(bqkv),
+                                      L.ptr(bias_frag_log2e), L.ptr(wproj_packed), L.ptr(bproj), L.ptr(xn), L.ptr(t),
+                                      B, H, W, shift, L.current_stream()), 'hab_attention')
+    return xn, t
