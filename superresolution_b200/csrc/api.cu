@@ -39,6 +39,24 @@ int pack_conv_weight(const float* w, bf16* o, int Cout, int Cin, int taps, cudaS
     return SRB_OK;
 }
 
+__global__ void pack_linear_scaled_kernel(const float* __restrict__ w, const float* __restrict__ b, bf16* __restrict__ wo,
+                                          float* __restrict__ bo, int Cout, int Cin, int nrows, float scale) {
+    const int n = Cout * Cin;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int co = i / Cin;
+        wo[i] = __float2bfloat16_rn(co < nrows ? w[i] * scale : w[i]);
+        if (i < Cout) bo[i] = i < nrows ? b[i] * scale : b[i];
+    }
+}
+
+int pack_linear_scaled(const float* w, const float* b, bf16* w_out, float* b_out, int Cout, int Cin, int nrows, float scale,
+                       cudaStream_t s) {
+    const int n = Cout * Cin;
+    pack_linear_scaled_kernel<<<(n + 255) / 256, 256, 0, s>>>(w, b, w_out, b_out, Cout, Cin, nrows, scale);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
 }  // namespace srb
 
 using namespace srb;

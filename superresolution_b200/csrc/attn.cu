@@ -54,58 +54,46 @@ __device__ __forceinline__ void load_b_frag2(uint32_t (&r)[4], const bf16* tile,
 }
 __device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-// One (window, head) attention for the calling warp over query m-tiles [mt_lo, mt_hi).  sQ/sK/sV: [rows][AP] bf16
-// tiles of this window.  BIAS_T = bf16 (shared, fragment order, 4 values / lane / (mt, j)) or float (global, fragment
-// order).  The normalised output overwrites this head's 16 columns of the processed Q rows (only this warp reads
-// them).  All operand fragments come from ldmatrix (V through .trans).
-template <int NK, typename BIAS_T>
-__device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16* sV, const BIAS_T* bias_h,
-                                            const int* srid, bool masked, int h, int lane, int mt_lo = 0,
-                                            int mt_hi = 4) {
+__device__ __forceinline__ float ex2f(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// One (window, head) attention for the calling warp over the 64 query rows.  sQ/sK/sV: [rows][AP] bf16 tiles of this
+// window.  The logits arrive in the log2 domain: q was scaled by head_dim^-0.5 * log2(e) inside the qkv linear (folded
+// into its weights at pack time) and bias_h (global, MMA C-fragment order, 4 values / lane / (mt, j)) holds
+// bias * log2(e); the bias is the accumulator initialiser of the S MMAs.  The normalised output overwrites this head's
+// 16 columns of the Q rows (only this warp reads them).  All operand fragments come from ldmatrix (V through .trans).
+template <int NK>
+__device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16* sV, const bf16* bias_h, int h,
+                                            int lane) {
     const int g = lane >> 2, t = lane & 3;
     constexpr int NT = NK / 8;   // S n-tiles
     constexpr int KT = NK / 16;  // PV k-tiles
 #pragma unroll 1
-    for (int mt = mt_lo; mt < mt_hi; ++mt) {
+    for (int mt = 0; mt < 4; ++mt) {
         const int r0 = 16 * mt + g, r1 = r0 + 8;
         uint32_t qa[4];
         load_a_frag(qa, sQ, 16 * mt, h * 16, lane);
         float s[NT][4];
 #pragma unroll
+        for (int j = 0; j < NT; ++j) {
+            const uint2 raw = __ldg((const uint2*)(bias_h + ((mt * NT + j) * 32 + lane) * 4));
+            const float2 lo = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
+            const float2 hi = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
+            s[j][0] = lo.x; s[j][1] = lo.y; s[j][2] = hi.x; s[j][3] = hi.y;
+        }
+#pragma unroll
         for (int j = 0; j < NT; j += 2) {
             uint32_t kb[4];
             load_b_frag2(kb, sK, 8 * j, h * 16, lane);
-            s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
-            s[j + 1][0] = s[j + 1][1] = s[j + 1][2] = s[j + 1][3] = 0.f;
             mma_bf16_16816(s[j], qa[0], qa[1], qa[2], qa[3], kb[0], kb[1]);
             mma_bf16_16816(s[j + 1], qa[0], qa[1], qa[2], qa[3], kb[2], kb[3]);
         }
-        // scale (head_dim^-0.5 = 0.25), relative position bias, shift mask (-100 across region borders)
-        int rid0 = 0, rid1 = 0;
-        if (masked) { rid0 = srid[r0]; rid1 = srid[r1]; }
         float m0 = -1e30f, m1 = -1e30f;
 #pragma unroll
         for (int j = 0; j < NT; ++j) {
-            float bb[4];
-            if (sizeof(BIAS_T) == 2) {
-                const uint2 raw = *(const uint2*)((const bf16*)bias_h + ((mt * NT + j) * 32 + lane) * 4);
-                const float2 lo = __bfloat1622float2(*(const __nv_bfloat162*)&raw.x);
-                const float2 hi = __bfloat1622float2(*(const __nv_bfloat162*)&raw.y);
-                bb[0] = lo.x; bb[1] = lo.y; bb[2] = hi.x; bb[3] = hi.y;
-            } else {
-                const float4 raw = __ldg((const float4*)((const float*)bias_h + ((mt * NT + j) * 32 + lane) * 4));
-                bb[0] = raw.x; bb[1] = raw.y; bb[2] = raw.z; bb[3] = raw.w;
-            }
-#pragma unroll
-            for (int e = 0; e < 4; ++e) s[j][e] = fmaf(s[j][e], 0.25f, bb[e]);
-            if (masked) {
-                const int c = 8 * j + 2 * t;
-                const int rc0 = srid[c], rc1 = srid[c + 1];
-                if (rc0 != rid0) s[j][0] -= 100.f;
-                if (rc1 != rid0) s[j][1] -= 100.f;
-                if (rc0 != rid1) s[j][2] -= 100.f;
-                if (rc1 != rid1) s[j][3] -= 100.f;
-            }
             m0 = fmaxf(m0, fmaxf(s[j][0], s[j][1]));
             m1 = fmaxf(m1, fmaxf(s[j][2], s[j][3]));
         }
@@ -114,35 +102,35 @@ __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16
         m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
         m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
         float l0 = 0.f, l1 = 0.f;
-#pragma unroll
-        for (int j = 0; j < NT; ++j) {
-            s[j][0] = __expf(s[j][0] - m0);
-            s[j][1] = __expf(s[j][1] - m0);
-            s[j][2] = __expf(s[j][2] - m1);
-            s[j][3] = __expf(s[j][3] - m1);
-            l0 += s[j][0] + s[j][1];
-            l1 += s[j][2] + s[j][3];
-        }
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
         float o[2][4];
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
 #pragma unroll
         for (int kt = 0; kt < KT; ++kt) {
-            const uint32_t p0 = pack_bf16(s[2 * kt][0], s[2 * kt][1]);
-            const uint32_t p1 = pack_bf16(s[2 * kt][2], s[2 * kt][3]);
-            const uint32_t p2 = pack_bf16(s[2 * kt + 1][0], s[2 * kt + 1][1]);
-            const uint32_t p3 = pack_bf16(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+            float e[2][4];
+#pragma unroll
+            for (int jj = 0; jj < 2; ++jj) {
+                const int j = 2 * kt + jj;
+                e[jj][0] = ex2f(s[j][0] - m0);
+                e[jj][1] = ex2f(s[j][1] - m0);
+                e[jj][2] = ex2f(s[j][2] - m1);
+                e[jj][3] = ex2f(s[j][3] - m1);
+                l0 += e[jj][0] + e[jj][1];
+                l1 += e[jj][2] + e[jj][3];
+            }
+            const uint32_t p0 = pack_bf16(e[0][0], e[0][1]), p1 = pack_bf16(e[0][2], e[0][3]);
+            const uint32_t p2 = pack_bf16(e[1][0], e[1][1]), p3 = pack_bf16(e[1][2], e[1][3]);
             // V^T fragments: {b0,b1 of dims 0-7, b0,b1 of dims 8-15} for keys [16kt, 16kt+16)
             uint32_t vb[4];
             ldsm_x4_trans(vb, sV + (16 * kt + (lane & 7) + ((lane >> 3) & 1) * 8) * AP + h * 16 + (lane >> 4) * 8);
             mma_bf16_16816(o[0], p0, p1, p2, p3, vb[0], vb[1]);
             mma_bf16_16816(o[1], p0, p1, p2, p3, vb[2], vb[3]);
         }
-        const float i0 = 1.f / l0, i1 = 1.f / l1;
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        const float i0 = __fdividef(1.f, l0), i1 = __fdividef(1.f, l1);
         __syncwarp();  // every lane has read its Q fragments of this m-tile before they are overwritten
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) {
@@ -170,24 +158,27 @@ ocab_attn_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ bias_fra
     const int win = blockIdx.x;
     const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
     const size_t img = (size_t)b * H * W;
+    // every 16-byte chunk of the window is one cp.async: all loads of the CTA are in flight at once
     for (int i = threadIdx.x; i < 64 * 12; i += 192) {
         const int n = i / 12, ck = i % 12;
         const size_t pix = img + (size_t)(wy * 8 + (n >> 3)) * W + wx * 8 + (n & 7);
-        *(uint4*)(sQ + n * AP + ck * 8) = __ldg((const uint4*)(qkv + pix * 288) + ck);
+        cp_async16(sQ + n * AP + ck * 8, (const uint4*)(qkv + pix * 288) + ck);
         if (ck == 0) spix[n] = (int)(pix - img);
     }
     for (int i = threadIdx.x; i < 144 * 24; i += 192) {
         const int m = i / 24, ck = i % 24;
         const int y = wy * 8 - 2 + m / 12, x = wx * 8 - 2 + m % 12;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (y >= 0 && y < H && x >= 0 && x < W)
-            v = __ldg((const uint4*)(qkv + (img + (size_t)y * W + x) * 288 + 96) + ck);
         bf16* dst = (ck < 12) ? (sK + m * AP + ck * 8) : (sV + m * AP + (ck - 12) * 8);
-        *(uint4*)dst = v;
+        if (y >= 0 && y < H && x >= 0 && x < W)
+            cp_async16(dst, (const uint4*)(qkv + (img + (size_t)y * W + x) * 288 + 96) + ck);
+        else
+            *(uint4*)dst = make_uint4(0, 0, 0, 0);  // nn.Unfold zero padding of the projected K / V maps
     }
+    cp_async_commit();
+    cp_async_wait<0>();
     __syncthreads();
     const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    attend_head<144, bf16>(sQ, sK, sV, bias_frag + (size_t)h * (4 * 18 * 32 * 4), nullptr, false, h, lane);
+    attend_head<144>(sQ, sK, sV, bias_frag + (size_t)h * (4 * 18 * 32 * 4), h, lane);
     __syncthreads();
     for (int i = threadIdx.x; i < 64 * 12; i += 192) {
         const int n = i / 12, c = i % 12;

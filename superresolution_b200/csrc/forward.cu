@@ -162,10 +162,18 @@ int model_pack(const void* const* params, int n, void* packed, size_t packed_byt
         }
         snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.relative_position_bias_table", l);
         const float* tab = (const float*)(base + m.params[m.index.at(buf)].off);
-        SRB_TRY(expand_rel_bias_bf16(tab, 361, idx_oca, 144, (bf16*)(base + m.bias_oca_off[l]), 1.f, s));
+        SRB_TRY(expand_rel_bias_bf16(tab, 361, idx_oca, 144, (bf16*)(base + m.bias_oca_off[l]), 1.4426950408889634f, s));
+    }
+    auto src = [&](const std::string& name) { return (const float*)params[m.index.at(name)]; };
+    // OCAB: the q rows of qkv carry head_dim^-0.5 * log2(e) (the attention core works in the log2 domain)
+    for (int l = 0; l < 4; ++l) {
+        snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.qkv", l);
+        const std::string b = buf;
+        SRB_TRY(pack_linear_scaled(src(b + ".weight"), src(b + ".bias"), (bf16*)(base + m.params[m.index.at(b + ".weight")].off),
+                                   (float*)(base + m.params[m.index.at(b + ".bias")].off), 288, 96, 96,
+                                   0.25f * 1.4426950408889634f, s));
     }
     // norm2 folded into mlp.fc1 (from the fp32 originals: one bf16 rounding)
-    auto src = [&](const std::string& name) { return (const float*)params[m.index.at(name)]; };
     for (int i = 0; i < 28; ++i) {
         if (i < 24) snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.", i / 6, i % 6);
         else snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", i - 24);

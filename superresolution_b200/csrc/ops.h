@@ -6,6 +6,9 @@ namespace srb {
 
 // api.cu
 int pack_conv_weight(const float* w, bf16* o, int Cout, int Cin, int taps, cudaStream_t s);
+// fp32 [Cout][Cin] linear weight -> bf16 with rows [0, nrows) multiplied by `scale` before the rounding; bias likewise
+int pack_linear_scaled(const float* w, const float* b, bf16* w_out, float* b_out, int Cout, int Cin, int nrows, float scale,
+                       cudaStream_t s);
 
 // small_ops.cu
 int rrdb_conv_first(const void* x, int x_dtype, const float* w, const float* bias, bf16* out, int out_pitch,
@@ -31,7 +34,8 @@ int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const flo
 int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
                      const bf16* bias_frag_log2e, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
                      int W, int shift, cudaStream_t s);
-// attn.cu — OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.
+// attn.cu — OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.  Log2 domain:
+// the q part of qkv arrives scaled by head_dim^-0.5 * log2(e) (scale_rows at pack time), bias_frag holds bias * log2(e).
 int ocab_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s);
 // table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> fragment-ordered bias [6*64*NK]
 int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, float scale,
