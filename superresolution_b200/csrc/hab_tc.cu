@@ -72,9 +72,10 @@ __device__ __forceinline__ uint32_t packbf(float lo, float hi) {
     return *(uint32_t*)&h;
 }
 __device__ __forceinline__ float2 unpackbf(uint32_t v) { return __bfloat1622float2(*(const __nv_bfloat162*)&v); }
-__device__ __forceinline__ float ex2f(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+// two exp2 per MUFU op on packed bf16 (input and result are bf16x2)
+__device__ __forceinline__ uint32_t ex2_bf16x2(uint32_t x) {
+    uint32_t y;
+    asm("ex2.approx.ftz.bf16x2 %0, %1;" : "=r"(y) : "r"(x));
     return y;
 }
 __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
@@ -129,7 +130,7 @@ __device__ __forceinline__ void attend_pair(uint32_t q_u32, uint32_t k_u32, uint
             mma16816(s[m][j + 1], qa[m], kb[2], kb[3]);
         }
     }
-    float mx[2][2], l[2][2];
+    float mx[2][2];
 #pragma unroll
     for (int m = 0; m < 2; ++m) {
         const int mt = 2 * mh + m;
@@ -154,50 +155,43 @@ __device__ __forceinline__ void attend_pair(uint32_t q_u32, uint32_t k_u32, uint
         for (int e = 0; e < 2; ++e) {
             mx[m][e] = fmaxf(mx[m][e], __shfl_xor_sync(0xffffffffu, mx[m][e], 1));
             mx[m][e] = fmaxf(mx[m][e], __shfl_xor_sync(0xffffffffu, mx[m][e], 2));
-            l[m][e] = 0.f;
         }
     }
-    float o[2][2][4];
+    // P = exp2(s - max) as packed bf16 pairs: one MUFU.EX2 per two logits (ex2.approx.ftz.bf16x2) and the result is
+    // already the A fragment of the PV MMA.  The row sums come out of the tensor core too: a third n-tile whose B
+    // fragment is all ones accumulates sum_k P[row][k] (c0 -> row g, c2 -> row g + 8), from the same bf16 P that
+    // multiplies V.
+    float o[2][3][4];
 #pragma unroll
     for (int m = 0; m < 2; ++m)
 #pragma unroll
-        for (int nt = 0; nt < 2; ++nt) o[m][nt][0] = o[m][nt][1] = o[m][nt][2] = o[m][nt][3] = 0.f;
+        for (int nt = 0; nt < 3; ++nt) o[m][nt][0] = o[m][nt][1] = o[m][nt][2] = o[m][nt][3] = 0.f;
     // V^T fragments through ldmatrix.trans: matrices (keys 0-7, dims 0-7) (keys 8-15, dims 0-7) (keys 0-7, dims 8-15)
     // (keys 8-15, dims 8-15) of the 16 keys of k-tile kt
     const uint32_t v_off = (uint32_t)((lane >> 4) * PP + ((lane & 7) + ((lane >> 3) & 1) * 8) * 16);
+    constexpr uint32_t kOnes = 0x3F803F80u;  // {1.0, 1.0} bf16
 #pragma unroll
     for (int kt = 0; kt < 4; ++kt) {
         uint32_t vb[4];
         ldsm4_trans(vb, v_u32 + (16 * kt) * 16 + v_off);
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
-            float e[2][4];
+            uint32_t p[4];
 #pragma unroll
             for (int jj = 0; jj < 2; ++jj) {
                 const int j = 2 * kt + jj;
-                e[jj][0] = ex2f(s[m][j][0] - mx[m][0]);
-                e[jj][1] = ex2f(s[m][j][1] - mx[m][0]);
-                e[jj][2] = ex2f(s[m][j][2] - mx[m][1]);
-                e[jj][3] = ex2f(s[m][j][3] - mx[m][1]);
-                l[m][0] += e[jj][0] + e[jj][1];
-                l[m][1] += e[jj][2] + e[jj][3];
+                p[2 * jj] = ex2_bf16x2(packbf(s[m][j][0] - mx[m][0], s[m][j][1] - mx[m][0]));
+                p[2 * jj + 1] = ex2_bf16x2(packbf(s[m][j][2] - mx[m][1], s[m][j][3] - mx[m][1]));
             }
-            uint32_t p[4];
-            p[0] = packbf(e[0][0], e[0][1]); p[1] = packbf(e[0][2], e[0][3]);
-            p[2] = packbf(e[1][0], e[1][1]); p[3] = packbf(e[1][2], e[1][3]);
             mma16816(o[m][0], p, vb[0], vb[1]);
             mma16816(o[m][1], p, vb[2], vb[3]);
+            mma16816(o[m][2], p, kOnes, kOnes);
         }
     }
     __syncwarp();  // every lane has read its Q fragments before the rows are overwritten
 #pragma unroll
     for (int m = 0; m < 2; ++m) {
-        float l0 = l[m][0], l1 = l[m][1];
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-        const float i0 = __fdividef(1.f, l0), i1 = __fdividef(1.f, l1);
+        const float i0 = __fdividef(1.f, o[m][2][0]), i1 = __fdividef(1.f, o[m][2][2]);
         const int r0 = 32 * mh + 16 * m + g, r1 = r0 + 8;
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) {  // head dims 8nt + 2t, +1  -> plane (2h + nt), byte 4t of the row's 16 B
@@ -351,13 +345,14 @@ hab_tc_kernel(const HabArgs a) {
                     v[8 * u + 2 * k] = f.x; v[8 * u + 2 * k + 1] = f.y;
                 }
             }
-            float sm = 0.f;
+            float s4[4] = {0.f, 0.f, 0.f, 0.f};  // four independent chains instead of one 32-deep one
 #pragma unroll
-            for (int k = 0; k < 32; ++k) sm += v[k];
-            const float mloc = sm * (1.f / 32.f);
-            float m2 = 0.f;
+            for (int k = 0; k < 32; ++k) s4[k & 3] += v[k];
+            const float mloc = ((s4[0] + s4[1]) + (s4[2] + s4[3])) * (1.f / 32.f);
+            float q4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int k = 0; k < 32; ++k) { const float d = v[k] - mloc; m2 = fmaf(d, d, m2); }
+            for (int k = 0; k < 32; ++k) { const float d = v[k] - mloc; q4[k & 3] = fmaf(d, d, q4[k & 3]); }
+            const float m2 = (q4[0] + q4[1]) + (q4[2] + q4[3]);
             sEx[c3 * 128 + r] = make_float2(mloc, m2);
             named_bar_sync(1, kComputeThreads);
             const float2 e0 = sEx[r], e1 = sEx[128 + r], e2 = sEx[256 + r];
@@ -409,11 +404,12 @@ hab_tc_kernel(const HabArgs a) {
             {
                 uint8_t* dst = (c3 == 0 ? sQ : c3 == 1 ? sK : sV) + r * 16;
                 const float scale = (c3 == 0) ? 0.25f * kLog2e : 1.f;
-#pragma unroll 1
+                uint32_t acc[2][32];
+                tmem_ld_32x32b_x32(tm_lane + COL_QKV + 96 * c3, acc[0]);
+#pragma unroll
                 for (int j = 0; j < 3; ++j) {
-                    uint32_t acc[32];
-                    tmem_ld_32x32b_x32(tm_lane + COL_QKV + 96 * c3 + 32 * j, acc);
-                    tmem_ld_wait();
+                    tmem_ld_wait();  // chunk j is in registers; fetch chunk j+1 while it is converted
+                    if (j < 2) tmem_ld_32x32b_x32(tm_lane + COL_QKV + 96 * c3 + 32 * (j + 1), acc[(j + 1) & 1]);
                     const float* bp = sbq + 96 * c3 + 32 * j;
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
@@ -423,8 +419,8 @@ hab_tc_kernel(const HabArgs a) {
                         uint32_t* ow = (uint32_t*)&o4;
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            ow[k] = packbf((__uint_as_float(acc[8 * u + 2 * k]) + bb[2 * k]) * scale,
-                                           (__uint_as_float(acc[8 * u + 2 * k + 1]) + bb[2 * k + 1]) * scale);
+                            ow[k] = packbf((__uint_as_float(acc[j & 1][8 * u + 2 * k]) + bb[2 * k]) * scale,
+                                           (__uint_as_float(acc[j & 1][8 * u + 2 * k + 1]) + bb[2 * k + 1]) * scale);
                         *(uint4*)(dst + (4 * j + u) * PP) = o4;
                     }
                 }
