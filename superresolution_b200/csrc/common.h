@@ -49,7 +49,8 @@ struct ConvArgs {
     bf16* out; int out_pitch;                         // bf16 output (base offset to first out channel) or null
     float* out32; int out32_pitch;                    // fp32 output or null
     int pixel_shuffle;                                // 1: out is [B,2H,2W,Cout/4] (PixelShuffle(2) fused in the store)
-    const float* ln_stats;                            // reserved (folded LayerNorm); null
+    float* colsum;                                    // optional [B * tiles_per_image][Cout] fp32: per-tile channel sums of the
+                                                      // epilogue result (CAB average pool fused into cab.2; needs Cout == N tile)
 };
 
 int conv_tc_launch(const ConvArgs& a, cudaStream_t stream);

@@ -60,6 +60,7 @@ constexpr int kThreads = 384;
 constexpr int kStageBytes = 8192;               // one 128 x 32 bf16 block, 64B-swizzled
 constexpr int kStagingBytes = 4 * kStageBytes;  // 2 epilogue groups x 2 buffers
 constexpr int kBarrierBytes = 512;
+constexpr int kColsumBytes = 2 * 16 * 128 * 4;  // [2 tiles][MT * 4 row groups <= 16][N_TILE <= 128] fp32 partial channel sums
 constexpr int kSmemLimit = 227 * 1024;
 constexpr int kMaxPS = 4;
 
@@ -69,7 +70,23 @@ struct ConvLaunch {
     int wslots;     // weight slots (ring depth for 3x3, resident tile count for 1x1)
     int reuse;      // patch chunks stay resident across the N tiles of one spatial tile
     int tma_store;  // bf16 output through smem staging + TMA store
+    int colsum_bytes;  // shared-memory bytes of the per-tile channel-sum scratch (0 unless a.colsum)
 };
+
+// Sum of v[c] over the 32 lanes of the warp, returned in lane c (recursive halving: 31 shuffles). Destroys v.
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float send = up ? v[i] : v[i + off];
+            const float keep = up ? v[i + off] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
 
 template <class Cfg>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -81,7 +98,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t* patch0 = smem;
     uint8_t* wt0 = patch0 + t.ps * Cfg::PATCH_STRIDE;
     uint8_t* stg0 = wt0 + t.wslots * Cfg::W_BYTES;
-    uint64_t* bars = (uint64_t*)(stg0 + kStagingBytes);
+    float* scol = (float*)(stg0 + kStagingBytes);  // only carved when a.colsum (t.colsum_bytes)
+    uint64_t* bars = (uint64_t*)(stg0 + kStagingBytes + t.colsum_bytes);
     uint64_t* full_p = bars;                 // [kMaxPS]
     uint64_t* empty_p = full_p + kMaxPS;     // [kMaxPS]
     uint64_t* full_w = empty_p + kMaxPS;     // [W_RING]  (3x3: ring; 1x1: full_w[0] = all resident tiles landed)
@@ -304,9 +322,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             }
                         }
                     }
+                    if (a.colsum) {  // channel sums of this unit over the warp's 32 pixels (v is dead from here on)
+                        const float cs_ = warp_colsum32(v, lane);
+                        scol[((it_a & 1) * 16 + mt * 4 + q) * N_TILE + c0 + lane] = cs_;
+                    }
                 }
                 tc_fence_before();
                 mbar_arrive(&acc_empty[as]);
+                if (a.colsum) {  // both epilogue groups: fixed-order sum of the MT*4 row-group partials -> colsum[st][c]
+                    named_bar_sync(3, 256);
+                    const int c = threadIdx.x - 128;
+                    if (c < N_TILE) {
+                        float tot = 0.f;
+#pragma unroll
+                        for (int g8 = 0; g8 < MT * 4; ++g8) tot += scol[((it_a & 1) * 16 + g8) * N_TILE + c];
+                        a.colsum[(size_t)st * a.Cout + c] = tot;
+                    }
+                }
             }
         }
         if (issuer) bulk_wait_group<0>();  // all TMA stores of this group have completed
@@ -391,7 +423,12 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     t.n_spatial = a.B * t.tiles_x * t.tiles_y;
     t.nchunks = (a.Cin + 63) / 64;
     t.wslots = (Cfg::TAPS == 1) ? t.n_tiles_n * t.nchunks : Cfg::W_RING;
-    const int fixed = t.wslots * Cfg::W_BYTES + kStagingBytes + kBarrierBytes + 1024;
+    t.colsum_bytes = a.colsum ? kColsumBytes : 0;
+    if (a.colsum && (t.n_tiles_n != 1 || Cfg::MT * 4 > 16 || Cfg::N_TILE > 128)) {
+        set_error("conv_tc: colsum needs Cout == N tile (Cout=%d)", a.Cout);
+        return SRB_E_ARG;
+    }
+    const int fixed = t.wslots * Cfg::W_BYTES + kStagingBytes + t.colsum_bytes + kBarrierBytes + 1024;
     t.ps = (kSmemLimit - fixed) / Cfg::PATCH_STRIDE;
     if (t.ps > kMaxPS) t.ps = kMaxPS;
     if (t.ps < 2) {

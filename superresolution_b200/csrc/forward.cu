@@ -240,7 +240,7 @@ static size_t carve(Workspace& w, uint8_t* base, int B, int H, int W) {
     w.c1 = (bf16*)take(ntok * 32 * 2);
     w.qkv = (bf16*)take(ntok * 288 * 2);
     w.hd = (bf16*)take(ntok * 192 * 2);
-    w.pool = (float*)take((size_t)B * cab_pool_slabs((int)(4 * H * W)) * 96 * 4);  // per-slab partial sums
+    w.pool = (float*)take((size_t)B * cab_pool_slabs((int)(4 * H * W)) * 96 * 4);  // per-tile partial sums
     w.cs = (float*)take((size_t)B * 96 * 4);
     w.d1 = (bf16*)take(ntok * 64 * 2);
     w.d2 = (bf16*)take(p4 * 64 * 2);
@@ -332,11 +332,12 @@ static int tc_layer(Ctx& c, const std::string& name, const bf16* in, int in_pitc
                     float slope, bf16* out, int out_pitch, float* out32 = nullptr, float alpha1 = 1.f,
                     const void* res1 = nullptr, int res1_f32 = 0, int res1_pitch = 0, float alpha2 = 1.f,
                     const void* res2 = nullptr, int res2_f32 = 0, int res2_pitch = 0, const float* res2_cs = nullptr,
-                    int pixel_shuffle = 0) {
+                    int pixel_shuffle = 0, float* colsum = nullptr) {
     ++c.launches;
     if (c.dry) return SRB_OK;
-    const ConvArgs a = make_layer(c, name, in, in_pitch, B, H, W, act, slope, out, out_pitch, out32, alpha1, res1,
+    ConvArgs a = make_layer(c, name, in, in_pitch, B, H, W, act, slope, out, out_pitch, out32, alpha1, res1,
                                   res1_f32, res1_pitch, alpha2, res2, res2_f32, res2_pitch, res2_cs, pixel_shuffle);
+    a.colsum = colsum;
     prof_begin(c, a.taps == 9 ? PC_CONV3 : PC_LINEAR, layer_flops(a));
     const int rc = conv_tc_launch(a, c.s);
     prof_end(c);
@@ -440,9 +441,11 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
                                        (j & 1) ? 4 : 0, c.s));
             // CAB on the normalised tensor: conv 96->32, GELU, conv 32->96, channel attention
             SRB_TRY(tc_layer(c, b + "conv_block.cab.0", w.xn, 96, B, R, Rw, ACT_GELU, 0.f, w.c1, 32));
-            SRB_TRY(tc_layer(c, b + "conv_block.cab.2", w.c1, 32, B, R, Rw, ACT_NONE, 0.f, w.c2, 96));
-            c.launches += 1;  // partial sums (counted with the finisher below)
-            LAUNCH(c, PC_OTHER, 0.0, cab_channel_attention(w.c2, w.pool, w.cs, c.F(b + "conv_block.cab.3.attention.1.weight"),
+            // cab.2 also leaves per-tile channel sums in w.pool (the average pool of the channel attention, fused)
+            SRB_TRY(tc_layer(c, b + "conv_block.cab.2", w.c1, 32, B, R, Rw, ACT_NONE, 0.f, w.c2, 96, nullptr, 1.f, nullptr,
+                             0, 0, 1.f, nullptr, 0, 0, nullptr, 0, w.pool));
+            LAUNCH(c, PC_OTHER, 0.0, cab_channel_scale(w.pool, cab_pool_slabs(R * Rw), w.cs,
+                                            c.F(b + "conv_block.cab.3.attention.1.weight"),
                                             c.F(b + "conv_block.cab.3.attention.1.bias"),
                                             c.F(b + "conv_block.cab.3.attention.3.weight"),
                                             c.F(b + "conv_block.cab.3.attention.3.bias"), 0.01f, B, R * Rw, c.s));

@@ -315,10 +315,10 @@ hab_tc_kernel(const HabArgs a) {
                 gp_c[p] = gp_n[p];
             }
         };
-        auto copy_out = [&](const uint8_t* planes, bf16* dst) {  // planes -> HBM, G mapping
+        auto copy_out = [&](const uint8_t* planes, bf16* dst, const size_t (&gp)[2]) {  // planes -> HBM, G mapping
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
-                uint4* op = (uint4*)(dst + gp_c[p] * 96) + g_j[p];
+                uint4* op = (uint4*)(dst + gp[p] * 96) + g_j[p];
                 op[0] = *(const uint4*)(planes + g_j[p] * PP + g_row[p] * 16);
                 op[6] = *(const uint4*)(planes + (g_j[p] + 6) * PP + g_row[p] * 16);
             }
@@ -396,7 +396,7 @@ hab_tc_kernel(const HabArgs a) {
                 __syncwarp();
             }
             // xn -> HBM for the CAB branch while the tensor core works (A1 is only read from here on)
-            copy_out(sA1, a.xn);
+            copy_out(sA1, a.xn, gp_c);
             SRB_PHASE(1);
             // ---- qkv epilogue: this warp's 32 rows x the 96 columns of part c3 -> Q / K / V planes ----
             mbar_wait(bar_qkv + c3, i & 1);
@@ -456,6 +456,12 @@ hab_tc_kernel(const HabArgs a) {
                 }
                 __syncwarp();
             }
+            // while the proj GEMM runs: x(i+1) -> V planes (free since every warp has left the attention)
+            size_t gp_t[2] = {gp_c[0], gp_c[1]};  // this tile's pixel indices for the t copy-out below
+            if (i + 1 < n_my) {
+                park_x();
+                if (i + 2 < n_my) load_x(tile + 2 * step);
+            }
             SRB_PHASE(5);
             // ---- proj epilogue: t = x + attn @ Wproj^T + b : this thread's row x channels [32 c3, +32) -> K planes ----
             mbar_wait(bar_t, i & 1);
@@ -482,11 +488,7 @@ hab_tc_kernel(const HabArgs a) {
             }
             tc_fence_before();
             named_bar_sync(1, kComputeThreads);  // t staged in the K planes
-            copy_out(sK, a.t);                   // (uses the current tile's pixel indices)
-            if (i + 1 < n_my) {
-                park_x();                        // x(i+1) -> V planes, region ids, pixel indices become "current"
-                if (i + 2 < n_my) load_x(tile + 2 * step);
-            }
+            copy_out(sK, a.t, gp_t);
             named_bar_sync(1, kComputeThreads);  // x(i+1) parked; K planes read out
             SRB_PHASE(6);
         }

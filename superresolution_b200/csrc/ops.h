@@ -26,8 +26,8 @@ int combine_ln96(const bf16* t, const bf16* cab, const float* cs, const float* g
                  bf16* xn, size_t ntok, size_t tok_per_img, cudaStream_t s);
 int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cudaStream_t s);
 int cab_pool_slabs(int HW);  // pool scratch = B * slabs * 96 floats
-int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const float* w1, const float* b1,
-                          const float* w2, const float* b2, float conv_scale, int B, int HW, cudaStream_t s);
+int cab_channel_scale(const float* pool, int nslab, float* cs, const float* w1, const float* b1, const float* w2,
+                      const float* b2, float conv_scale, int B, int HW, cudaStream_t s);
 
 // hab_tc.cu — fused HAB attention branch: xn = LN1(x); t = x + proj((S)W-MSA(xn)) + bproj (one pass over x), the qkv /
 // proj GEMMs on tcgen05 (TMEM accumulators) over 128-token tiles; bias_frag_log2e: expand_rel_bias_bf16(..., scale = log2(e))

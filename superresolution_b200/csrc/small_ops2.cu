@@ -253,40 +253,11 @@ int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cud
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// K13: ChannelAttention of CAB: AdaptiveAvgPool2d(1) over [B,HW,96] (bf16), then 1x1 96->3, ReLU, 1x1 3->96, sigmoid.
-// Stage A: per-(image, slab) partial channel sums, atomically added into pool[B][96] (fp32, pre-zeroed).
-// Stage B: the tiny MLP; emits cs[b][c] = sigmoid(...) * conv_scale so the HAB combine is a single FMA.
+// K13: ChannelAttention of CAB: AdaptiveAvgPool2d(1) over [B,HW,96], then 1x1 96->3, ReLU, 1x1 3->96, sigmoid.
+// Stage A lives in the cab.2 conv epilogue (conv_tc.cu, ConvArgs::colsum): fp32 channel sums per 16 x 16 output tile,
+// partial[b][tile][96]. Stage B (here): fixed-order sum of the tiles, the tiny MLP, and cs[b][c] = sigmoid(...) *
+// conv_scale so the HAB combine is a single FMA.
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(192)
-chan_sum96_kernel(const bf16* __restrict__ in, float* __restrict__ partial, int HW, int slab) {
-    // block = 192 threads = 16 pixel-lanes x 12 channel-groups; grid = (nslab, B); partial[b][slab][96]
-    const int cgp = threadIdx.x % 12, pl = threadIdx.x / 12;
-    const int b = blockIdx.y;
-    const int p0 = blockIdx.x * slab;
-    const int p1 = min(HW, p0 + slab);
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int p = p0 + pl; p < p1; p += 16) {
-        const uint4 raw = __ldg((const uint4*)(in + ((size_t)b * HW + p) * 96 + cgp * 8));
-        const __nv_bfloat162* h = (const __nv_bfloat162*)&raw;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float2 f = __bfloat1622float2(h[k]);
-            acc[2 * k] += f.x;
-            acc[2 * k + 1] += f.y;
-        }
-    }
-    __shared__ float sm[16][96];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sm[pl][cgp * 8 + j] = acc[j];
-    __syncthreads();
-    if (threadIdx.x < 96) {
-        float s = 0.f;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) s += sm[i][threadIdx.x];
-        partial[((size_t)b * gridDim.x + blockIdx.x) * 96 + threadIdx.x] = s;  // fixed order: deterministic
-    }
-}
-
 __global__ void __launch_bounds__(96)
 cab_finish_kernel(const float* __restrict__ partial, int nslab, float inv_hw, const float* __restrict__ w1 /*[3][96]*/,
                   const float* __restrict__ b1, const float* __restrict__ w2 /*[96][3]*/,
@@ -294,9 +265,9 @@ cab_finish_kernel(const float* __restrict__ partial, int nslab, float inv_hw, co
     __shared__ float mean[96];
     __shared__ float hid[3];
     const int b = blockIdx.x, c = threadIdx.x;
-    float tot = 0.f;
-    for (int i = 0; i < nslab; ++i) tot += partial[((size_t)b * nslab + i) * 96 + c];
-    mean[c] = tot * inv_hw;
+    float t4[4] = {0.f, 0.f, 0.f, 0.f};  // four interleaved chains, fixed order
+    for (int i = 0; i < nslab; ++i) t4[i & 3] += partial[((size_t)b * nslab + i) * 96 + c];
+    mean[c] = ((t4[0] + t4[1]) + (t4[2] + t4[3])) * inv_hw;
     __syncthreads();
     if (c < 3) {
         float s = b1[c];
@@ -310,15 +281,11 @@ cab_finish_kernel(const float* __restrict__ partial, int nslab, float inv_hw, co
     cs[b * 96 + c] = conv_scale / (1.f + expf(-s));
 }
 
-int cab_pool_slabs(int HW) { return (HW + 1023) / 1024; }
+// One slab = one 16 x 16 output tile of the cab.2 conv (conv_tc <96,2,9>), which writes the per-tile sums itself.
+int cab_pool_slabs(int HW) { return (HW + 255) / 256; }
 
-int cab_channel_attention(const bf16* cab_out, float* pool, float* cs, const float* w1, const float* b1,
-                          const float* w2, const float* b2, float conv_scale, int B, int HW, cudaStream_t s) {
-    const int slab = 1024;
-    const int nslab = cab_pool_slabs(HW);
-    dim3 grid(nslab, B);
-    chan_sum96_kernel<<<grid, 192, 0, s>>>(cab_out, pool, HW, slab);
-    SRB_CUDA(cudaGetLastError());
+int cab_channel_scale(const float* pool, int nslab, float* cs, const float* w1, const float* b1, const float* w2,
+                      const float* b2, float conv_scale, int B, int HW, cudaStream_t s) {
     cab_finish_kernel<<<B, 96, 0, s>>>(pool, nslab, 1.f / (float)HW, w1, b1, w2, b2, conv_scale, cs);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
