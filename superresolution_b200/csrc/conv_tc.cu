@@ -487,8 +487,6 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
 
 int conv_tc_launch(const ConvArgs& a_in, cudaStream_t stream) {
     ConvArgs a = a_in;
-    static const bool dbg_nores = env_flag("SRB_DEBUG_NORES", false);  // timing experiment only (wrong results)
-    if (dbg_nores) { a.res1 = nullptr; a.res2 = nullptr; }
     if (a.taps != 9 && a.taps != 1) { set_error("conv_tc: taps must be 9 or 1"); return SRB_E_ARG; }
     if (a.Cin % 16 || a.Cin < 16) { set_error("conv_tc: Cin=%d must be a multiple of 16", a.Cin); return SRB_E_SHAPE; }
     if (a.Cout % 32) { set_error("conv_tc: Cout=%d must be a multiple of 32", a.Cout); return SRB_E_SHAPE; }

@@ -93,68 +93,122 @@ int weighted_l1(const float* pred, const float* target, size_t n, float* loss, f
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// PSNR + SSIM.  One block = 32x32 tile: per-image squared-error partial over the tile's own pixels, and the SSIM
-// map (11x11 Gaussian sigma 1.5, *valid* convolution, C1=0.01^2, C2=0.03^2) over the tile's valid outputs, computed
-// separably from a 42x42 clamped input patch in shared memory.
+// PSNR + SSIM (11x11 Gaussian sigma 1.5, *valid* convolution, C1 = 0.01^2, C2 = 0.03^2; inputs clamped to [0,1]).
+// One block = 64 x 32 output tile.  Pass A (horizontal): each thread filters 4 adjacent outputs of one input row from
+// 16 clamped inputs read straight from global (float4, L1 absorbs the overlap), forms a^2, c^2, ac once per input and
+// leaves the 5 filtered rows in shared memory; the squared error of the tile's own pixels rides along.  Pass B
+// (vertical): each thread owns one column and 8 consecutive output rows, so every shared-memory value feeds up to 8
+// accumulators from registers (statically unrolled taps), then evaluates the SSIM map entry.  FP32-FMA bound
+// (~113 FMA per pixel), not HBM bound.
 // ---------------------------------------------------------------------------------------------------------------
 struct GaussWin { float g[11]; };
 
-__global__ void __launch_bounds__(256)
+constexpr int kSsimTX = 64, kSsimTY = 32, kSsimRows = kSsimTY + 10;
+constexpr int kSsimSmem = 5 * kSsimRows * kSsimTX * (int)sizeof(float);
+
+// four clamped pixels of one row starting at column x (x % 4 == 0); zeros beyond the image
+__device__ __forceinline__ float4 load4_sat(const float* __restrict__ row, int x, int W, bool row_ok, bool vec_ok) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row_ok) {
+        if (vec_ok && x + 3 < W) {
+            v = __ldg((const float4*)(row + x));
+        } else {
+            if (x < W) v.x = row[x];
+            if (x + 1 < W) v.y = row[x + 1];
+            if (x + 2 < W) v.z = row[x + 2];
+            if (x + 3 < W) v.w = row[x + 3];
+        }
+    }
+    return make_float4(__saturatef(v.x), __saturatef(v.y), __saturatef(v.z), __saturatef(v.w));
+}
+
+__global__ void __launch_bounds__(256, 3)
 psnr_ssim_tile_kernel(const float* __restrict__ p, const float* __restrict__ t, int H, int W, GaussWin win,
                       float* __restrict__ part_se, float* __restrict__ part_ssim) {
-    __shared__ float sp[42][43], st[42][43];
-    __shared__ float hz[5][42][32];
+    extern __shared__ float hz[];  // [5][kSsimRows][kSsimTX]
     __shared__ float sh[32];
-    const int bx = blockIdx.x * 32, by = blockIdx.y * 32, b = blockIdx.z;
+    const int bx = blockIdx.x * kSsimTX, by = blockIdx.y * kSsimTY, b = blockIdx.z;
     const float* pb = p + (size_t)b * H * W;
     const float* tb = t + (size_t)b * H * W;
+    const bool vec_ok = (W & 3) == 0 && (((uintptr_t)p | (uintptr_t)t) & 15) == 0;
     float se = 0.f;
-    for (int i = threadIdx.x; i < 42 * 42; i += 256) {
-        const int ly = i / 42, lx = i % 42;
-        const int y = by + ly, x = bx + lx;
-        float a = 0.f, c = 0.f;
-        if (y < H && x < W) {
-            a = fminf(fmaxf(pb[(size_t)y * W + x], 0.f), 1.f);
-            c = fminf(fmaxf(tb[(size_t)y * W + x], 0.f), 1.f);
-            if (ly < 32 && lx < 32) se += (a - c) * (a - c);
-        }
-        sp[ly][lx] = a;
-        st[ly][lx] = c;
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < 42 * 32; i += 256) {
-        const int ly = i / 32, ox = i % 32;
-        float m1 = 0.f, m2 = 0.f, s11 = 0.f, s22 = 0.f, s12 = 0.f;
+    // ---- pass A: 42 rows x 16 groups of 4 outputs
+    for (int i = threadIdx.x; i < kSsimRows * (kSsimTX / 4); i += 256) {
+        const int ly = i >> 4, gx = (i & 15) * 4;
+        const int y = by + ly, x = bx + gx;
+        const bool row_ok = y < H;
+        const float* pr = pb + (size_t)y * W;
+        const float* tr = tb + (size_t)y * W;
+        float a[16], c[16];
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
-            const float a = sp[ly][ox + k], c = st[ly][ox + k], g = win.g[k];
-            m1 = fmaf(g, a, m1);
-            m2 = fmaf(g, c, m2);
-            s11 = fmaf(g, a * a, s11);
-            s22 = fmaf(g, c * c, s22);
-            s12 = fmaf(g, a * c, s12);
+        for (int j = 0; j < 4; ++j) {
+            const float4 va = load4_sat(pr, x + 4 * j, W, row_ok, vec_ok);
+            const float4 vc = load4_sat(tr, x + 4 * j, W, row_ok, vec_ok);
+            a[4 * j] = va.x; a[4 * j + 1] = va.y; a[4 * j + 2] = va.z; a[4 * j + 3] = va.w;
+            c[4 * j] = vc.x; c[4 * j + 1] = vc.y; c[4 * j + 2] = vc.z; c[4 * j + 3] = vc.w;
         }
-        hz[0][ly][ox] = m1; hz[1][ly][ox] = m2; hz[2][ly][ox] = s11; hz[3][ly][ox] = s22; hz[4][ly][ox] = s12;
+        if (ly < kSsimTY) {  // squared error over the tile's own pixels (out-of-image pixels are 0 - 0)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) se = fmaf(a[j] - c[j], a[j] - c[j], se);
+        }
+        float o[5][4];
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o[q][j] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 14; ++k) {
+            const float aa = a[k] * a[k], cc = c[k] * c[k], ac = a[k] * c[k];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (k - j >= 0 && k - j < 11) {
+                    const float g = win.g[k - j];
+                    o[0][j] = fmaf(g, a[k], o[0][j]);
+                    o[1][j] = fmaf(g, c[k], o[1][j]);
+                    o[2][j] = fmaf(g, aa, o[2][j]);
+                    o[3][j] = fmaf(g, cc, o[3][j]);
+                    o[4][j] = fmaf(g, ac, o[4][j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+            *(float4*)(hz + (q * kSsimRows + ly) * kSsimTX + gx) = make_float4(o[q][0], o[q][1], o[q][2], o[q][3]);
     }
     __syncthreads();
-    float ss = 0.f;
+    // ---- pass B: column ox, output rows oy0 .. oy0 + 7
+    const int ox = threadIdx.x & 63, oy0 = (threadIdx.x >> 6) * 8;
     const int OH = H - 10, OW = W - 10;
-    for (int i = threadIdx.x; i < 32 * 32; i += 256) {
-        const int oy = i / 32, ox = i % 32;
-        if (by + oy >= OH || bx + ox >= OW) continue;
-        float m1 = 0.f, m2 = 0.f, s11 = 0.f, s22 = 0.f, s12 = 0.f;
+    float acc[8][5];
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
-            const float g = win.g[k];
-            m1 = fmaf(g, hz[0][oy + k][ox], m1);
-            m2 = fmaf(g, hz[1][oy + k][ox], m2);
-            s11 = fmaf(g, hz[2][oy + k][ox], s11);
-            s22 = fmaf(g, hz[3][oy + k][ox], s22);
-            s12 = fmaf(g, hz[4][oy + k][ox], s12);
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int q = 0; q < 5; ++q) acc[j][q] = 0.f;
+#pragma unroll
+    for (int r = 0; r < 18; ++r) {
+        float v[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) v[q] = hz[(q * kSsimRows + oy0 + r) * kSsimTX + ox];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (r - j >= 0 && r - j < 11) {
+                const float g = win.g[r - j];
+#pragma unroll
+                for (int q = 0; q < 5; ++q) acc[j][q] = fmaf(g, v[q], acc[j][q]);
+            }
         }
-        const float v1 = s11 - m1 * m1, v2 = s22 - m2 * m2, cv = s12 - m1 * m2;
-        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-        ss += ((2.f * m1 * m2 + C1) * (2.f * cv + C2)) / ((m1 * m1 + m2 * m2 + C1) * (v1 + v2 + C2));
+    }
+    float ss = 0.f;
+    if (bx + ox < OW) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (by + oy0 + j < OH) {
+                const float m1 = acc[j][0], m2 = acc[j][1];
+                const float v1 = acc[j][2] - m1 * m1, v2 = acc[j][3] - m2 * m2, cv = acc[j][4] - m1 * m2;
+                const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+                ss += __fdividef((2.f * m1 * m2 + C1) * (2.f * cv + C2), (m1 * m1 + m2 * m2 + C1) * (v1 + v2 + C2));
+            }
+        }
     }
     const float se_b = block_sum(se, sh);
     const float ss_b = block_sum(ss, sh);
@@ -165,59 +219,78 @@ psnr_ssim_tile_kernel(const float* __restrict__ p, const float* __restrict__ t, 
     }
 }
 
-// out[0] = sum_b 10*log10(1/(mse_b + 1e-8)) ; out[1] = (sum of all SSIM map values / (B*OH*OW)) * B
-__global__ void __launch_bounds__(256)
-psnr_ssim_final_kernel(const float* __restrict__ part_se, const float* __restrict__ part_ssim, int B, int tiles,
-                       double inv_hw, double inv_ohw, float* __restrict__ out) {
-    __shared__ double sh[256];
-    double psnr = 0.0, ssim = 0.0;
-    for (int b = 0; b < B; ++b) {
-        double a = 0.0, c = 0.0;
-        for (int i = threadIdx.x; i < tiles; i += 256) {
-            a += (double)part_se[(size_t)b * tiles + i];
-            c += (double)part_ssim[(size_t)b * tiles + i];
-        }
-        sh[threadIdx.x] = a;
+// per image: fixed-order sums of its tile partials -> img[b] = {10*log10(1/(mse_b + 1e-8)), sum of its SSIM map}
+__global__ void __launch_bounds__(128)
+psnr_ssim_image_kernel(const float* __restrict__ part_se, const float* __restrict__ part_ssim, int tiles,
+                       double inv_hw, double* __restrict__ img) {
+    __shared__ double sa[128], sc[128];
+    const int b = blockIdx.x;
+    double a = 0.0, c = 0.0;
+    for (int i = threadIdx.x; i < tiles; i += 128) {
+        a += (double)part_se[(size_t)b * tiles + i];
+        c += (double)part_ssim[(size_t)b * tiles + i];
+    }
+    sa[threadIdx.x] = a;
+    sc[threadIdx.x] = c;
+    __syncthreads();
+    for (int s = 64; s > 0; s >>= 1) {
+        if (threadIdx.x < s) { sa[threadIdx.x] += sa[threadIdx.x + s]; sc[threadIdx.x] += sc[threadIdx.x + s]; }
         __syncthreads();
-        for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s]; __syncthreads(); }
-        const double se = sh[0];
-        __syncthreads();
-        sh[threadIdx.x] = c;
-        __syncthreads();
-        for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s]; __syncthreads(); }
-        const double sv = sh[0];
-        __syncthreads();
-        const float mse = (float)(se * inv_hw);
-        psnr += (double)(10.f * log10f(1.0f / (mse + 1e-8f)));
-        ssim += sv;
     }
     if (threadIdx.x == 0) {
-        out[0] = (float)psnr;
-        out[1] = (float)(ssim * inv_ohw);  // == mean over [B,1,OH,OW] times B
+        const float mse = (float)(sa[0] * inv_hw);
+        img[2 * b] = (double)(10.f * log10f(1.0f / (mse + 1e-8f)));
+        img[2 * b + 1] = sc[0];
     }
 }
 
+// out[0] = sum_b psnr_b ; out[1] = (sum of all SSIM map values / (B*OH*OW)) * B
+__global__ void __launch_bounds__(256)
+psnr_ssim_final_kernel(const double* __restrict__ img, int B, double inv_ohw, float* __restrict__ out) {
+    __shared__ double sa[256], sc[256];
+    double a = 0.0, c = 0.0;
+    for (int b = threadIdx.x; b < B; b += 256) { a += img[2 * b]; c += img[2 * b + 1]; }
+    sa[threadIdx.x] = a;
+    sc[threadIdx.x] = c;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) { sa[threadIdx.x] += sa[threadIdx.x + s]; sc[threadIdx.x] += sc[threadIdx.x + s]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        out[0] = (float)sa[0];
+        out[1] = (float)(sc[0] * inv_ohw);  // == mean over [B,1,OH,OW] times B
+    }
+}
+
+static size_t ssim_tiles(int H, int W) { return (size_t)((H + kSsimTY - 1) / kSsimTY) * ((W + kSsimTX - 1) / kSsimTX); }
+
 size_t psnr_ssim_scratch_bytes(int B, int H, int W) {
-    return (size_t)B * ((H + 31) / 32) * ((W + 31) / 32) * 2 * sizeof(float);
+    return (size_t)B * 2 * sizeof(double) + (size_t)B * ssim_tiles(H, W) * 2 * sizeof(float);
 }
 
 int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, float* scratch,
               cudaStream_t s) {
     if (H < 11 || W < 11) { set_error("psnr_ssim: image smaller than the 11x11 SSIM window"); return SRB_E_SHAPE; }
+    if ((uintptr_t)scratch & 7) { set_error("psnr_ssim: scratch must be 8-byte aligned"); return SRB_E_ARG; }
     GaussWin win;
     {   // reference: gauss = exp(-(x-5)^2 / (2*1.5^2)), normalised in fp32 (src/metrics.py:11-12)
         float g[11], sum = 0.f;
         for (int i = 0; i < 11; ++i) { g[i] = (float)exp(-(double)((i - 5) * (i - 5)) / (2.0 * 1.5 * 1.5)); sum += g[i]; }
         for (int i = 0; i < 11; ++i) win.g[i] = g[i] / sum;
     }
-    dim3 grid((W + 31) / 32, (H + 31) / 32, B);
+    // per call: the attribute is per device, and a process may drive several (DataParallel-style threads)
+    SRB_CUDA(cudaFuncSetAttribute(psnr_ssim_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSsimSmem));
+    dim3 grid((W + kSsimTX - 1) / kSsimTX, (H + kSsimTY - 1) / kSsimTY, B);
     const int tiles = grid.x * grid.y;
-    float* part_se = scratch;
-    float* part_ssim = scratch + (size_t)B * tiles;
-    psnr_ssim_tile_kernel<<<grid, 256, 0, s>>>(pred, target, H, W, win, part_se, part_ssim);
+    double* img = (double*)scratch;
+    float* part_se = (float*)(img + 2 * (size_t)B);
+    float* part_ssim = part_se + (size_t)B * tiles;
+    psnr_ssim_tile_kernel<<<grid, 256, kSsimSmem, s>>>(pred, target, H, W, win, part_se, part_ssim);
     SRB_CUDA(cudaGetLastError());
-    psnr_ssim_final_kernel<<<1, 256, 0, s>>>(part_se, part_ssim, B, tiles, 1.0 / ((double)H * W),
-                                             1.0 / ((double)(H - 10) * (W - 10)), out2);
+    psnr_ssim_image_kernel<<<B, 128, 0, s>>>(part_se, part_ssim, tiles, 1.0 / ((double)H * W), img);
+    SRB_CUDA(cudaGetLastError());
+    psnr_ssim_final_kernel<<<1, 256, 0, s>>>(img, B, 1.0 / ((double)(H - 10) * (W - 10)), out2);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
@@ -226,30 +299,36 @@ int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float
 // LOG normalisation: u16( clip((log1p(max(nan_to_num(x),0)) - gmin) / denom, 0, 1) * 65535 )   (truncating cast)
 // denom = float32(gmax - gmin + 1e-8) is formed by the caller exactly as numpy does.
 // ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint16_t lognorm1(float x, float gmin, float denom) {
-    if (isnan(x)) x = 0.f;
-    else if (isinf(x)) x = x > 0.f ? FLT_MAX : -FLT_MAX;
-    float d = log1pf(fmaxf(x, 0.f));
-    d = __fdiv_rn(d - gmin, denom);
+// x -> nan_to_num -> max(.,0): fmaxf(NaN, 0) = 0 and -inf -> 0 already; +inf -> FLT_MAX as np.nan_to_num does.
+// The IEEE quotient (d - gmin) / denom is formed without the divide slow path: with rcp = RN(1/denom),
+// q0 = RN(a*rcp), r = a - q0*denom (exact in one FMA), q = RN(q0 + r*rcp) is the correctly rounded a/denom
+// (Markstein's theorem; no overflow/underflow at these magnitudes), so the result equals numpy's division bit for bit.
+__device__ __forceinline__ uint32_t lognorm1(float x, float gmin, float denom, float rcp) {
+    x = fminf(fmaxf(x, 0.f), FLT_MAX);
+    const float a = log1pf(x) - gmin;
+    const float q0 = a * rcp;
+    const float r = fmaf(-q0, denom, a);
+    float d = fmaf(r, rcp, q0);
     d = fminf(fmaxf(d, 0.f), 1.f);
-    return (uint16_t)(d * 65535.f);
+    return (uint32_t)(d * 65535.f);
 }
 
 __global__ void __launch_bounds__(256)
-log_normalize_kernel(const float* __restrict__ x, uint16_t* __restrict__ out, size_t n, float gmin, float denom) {
+log_normalize_kernel(const float* __restrict__ x, uint16_t* __restrict__ out, size_t n, float gmin, float denom,
+                     float rcp) {
     const size_t n8 = n / 8;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
         const float4 a = __ldcs((const float4*)x + 2 * i), b = __ldcs((const float4*)x + 2 * i + 1);
         uint4 o;
-        o.x = lognorm1(a.x, gmin, denom) | ((uint32_t)lognorm1(a.y, gmin, denom) << 16);
-        o.y = lognorm1(a.z, gmin, denom) | ((uint32_t)lognorm1(a.w, gmin, denom) << 16);
-        o.z = lognorm1(b.x, gmin, denom) | ((uint32_t)lognorm1(b.y, gmin, denom) << 16);
-        o.w = lognorm1(b.z, gmin, denom) | ((uint32_t)lognorm1(b.w, gmin, denom) << 16);
+        o.x = lognorm1(a.x, gmin, denom, rcp) | (lognorm1(a.y, gmin, denom, rcp) << 16);
+        o.y = lognorm1(a.z, gmin, denom, rcp) | (lognorm1(a.w, gmin, denom, rcp) << 16);
+        o.z = lognorm1(b.x, gmin, denom, rcp) | (lognorm1(b.y, gmin, denom, rcp) << 16);
+        o.w = lognorm1(b.z, gmin, denom, rcp) | (lognorm1(b.w, gmin, denom, rcp) << 16);
         __stcs((uint4*)out + i, o);
     }
     if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
         const size_t i = n8 * 8 + threadIdx.x;
-        out[i] = lognorm1(x[i], gmin, denom);
+        out[i] = (uint16_t)lognorm1(x[i], gmin, denom, rcp);
     }
 }
 
@@ -258,7 +337,8 @@ int log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float
     int grid = (int)((n / 8 + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;
     if (grid < 1) grid = 1;
-    log_normalize_kernel<<<grid, 256, 0, s>>>(x, out, n, gmin, denom);
+    const float rcp = (float)(1.0 / (double)denom);  // correctly rounded reciprocal
+    log_normalize_kernel<<<grid, 256, 0, s>>>(x, out, n, gmin, denom, rcp);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
