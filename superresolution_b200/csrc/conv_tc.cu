@@ -71,6 +71,7 @@ struct ConvLaunch {
     int reuse;      // patch chunks stay resident across the N tiles of one spatial tile
     int tma_store;  // bf16 output through smem staging + TMA store
     int colsum_bytes;  // shared-memory bytes of the per-tile channel-sum scratch (0 unless a.colsum)
+    long long* dbg;    // development aid (-DSRB_CONV_PHASES): [grid][8] cycle totals of the MMA / epilogue warps
 };
 
 // Sum of v[c] over the 32 lanes of the warp, returned in lane c (recursive halving: 31 shuffles). Destroys v.
@@ -180,17 +181,29 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t idesc = umma_idesc_bf16_f32(128, N_TILE);
         const uint32_t p_u32 = smem_u32(patch0), w_u32 = smem_u32(wt0);
         uint32_t it_p = 0, it_w = 0, it_a = 0;
+#ifdef SRB_CONV_PHASES
+        long long ph_acc = 0, ph_patch = 0, ph_w = 0, ph_t0 = clock64(), ph_c;
+#define PH_BEGIN() ph_c = clock64()
+#define PH_END(x) x += clock64() - ph_c
+#else
+#define PH_BEGIN()
+#define PH_END(x)
+#endif
         if (TAPS == 1) { mbar_wait(&full_w[0], 0); tc_fence_after(); }
         for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
             for (int nt = 0; nt < t.n_tiles_n; ++nt, ++it_a) {
                 const uint32_t as = it_a % AS;
+                PH_BEGIN();
                 mbar_wait(&acc_empty[as], ((it_a / AS) & 1) ^ 1);
+                PH_END(ph_acc);
                 tc_fence_after();
                 const uint32_t d_base = tmem_base + as * (MT * N_TILE);
                 for (int ch = 0; ch < t.nchunks; ++ch) {
                     const uint32_t pi = it_p + ch;
                     const uint32_t ps = pi % t.ps;
+                    PH_BEGIN();
                     mbar_wait(&full_p[ps], (pi / t.ps) & 1);  // immediate when the chunk is already resident
+                    PH_END(ph_patch);
                     tc_fence_after();
                     const uint64_t ad0 = umma_smem_desc(p_u32 + ps * Cfg::PATCH_STRIDE, 16, Cfg::PW * 128, UMMA_SW_128B);
                     const bool full_chunk = (a.Cin - ch * 64) >= 64;  // else 32 valid channels (2 k-steps)
@@ -203,7 +216,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             wbase = w_u32 + (nt * t.nchunks + ch) * Cfg::W_BYTES;
                         } else {
                             ws = it_w % Cfg::W_RING;
+                            PH_BEGIN();
                             mbar_wait(&full_w[ws], (it_w / Cfg::W_RING) & 1);
+                            PH_END(ph_w);
                             tc_fence_after();
                             wbase = w_u32 + ws * Cfg::W_BYTES;
                         }
@@ -238,6 +253,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             if (t.reuse) it_p += t.nchunks;
         }
+#ifdef SRB_CONV_PHASES
+        if (t.dbg && lane == 0) {
+            long long* d = t.dbg + blockIdx.x * 8;
+            d[0] = clock64() - ph_t0; d[1] = ph_acc; d[2] = ph_patch; d[3] = ph_w;
+        }
+#endif
     } else if (warp >= 4) {
         // ===================== epilogue: 2 groups x 4 warps, each group = all 128 TMEM lanes =====================
         pdl_wait();  // residual reads / output writes must not overtake the previous kernel
@@ -247,12 +268,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool issuer = (q == 0 && lane == 0);
         uint8_t* stg = stg0 + eg * 2 * kStageBytes;
         uint32_t it_a = 0, it_s = 0;
+#ifdef SRB_CONV_PHASES
+        long long ph_full = 0, ph_e0 = clock64(), ph_c;
+#endif
         for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
             const int b = st / per_img, r = st % per_img;
             const int ty = r / t.tiles_x, tx = r % t.tiles_x;
             for (int nt = 0; nt < t.n_tiles_n; ++nt, ++it_a) {
                 const uint32_t as = it_a % AS;
+                PH_BEGIN();
                 mbar_wait(&acc_full[as], (it_a / AS) & 1);
+                PH_END(ph_full);
                 tc_fence_after();
 #pragma unroll 1
                 for (int u = eg; u < Cfg::UNITS; u += 2) {
@@ -342,6 +368,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
         if (issuer) bulk_wait_group<0>();  // all TMA stores of this group have completed
+#ifdef SRB_CONV_PHASES
+        if (t.dbg && warp == 4 && lane == 0) {
+            long long* d = t.dbg + blockIdx.x * 8;
+            d[4] = clock64() - ph_e0; d[5] = ph_full;
+        }
+#endif
     }
 
     tc_fence_before();
@@ -356,6 +388,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+extern long long* g_fa_dbg;  // attn.cu (srb_debug_set_phase_buffer)
 static EncodeTiledFn g_encode = nullptr;
 static std::once_flag g_encode_once;
 
@@ -441,6 +474,7 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     t.tma_store = (a.out && !a.pixel_shuffle && use_tma_store && (((uintptr_t)a.out & 15) == 0) &&
                    (a.out_pitch % 8 == 0)) ? 1 : 0;
     const int smem = t.ps * Cfg::PATCH_STRIDE + fixed;
+    t.dbg = g_fa_dbg;
 
     CUtensorMap tmA, tmW, tmO;
     {
