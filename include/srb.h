@@ -125,6 +125,24 @@ int srb_blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int
                     float* wsum, int FH, int FW, int row0, int row1, void* stream);
 int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, void* stream);
 
+
+/* ---- optimizer half of the training step ------------------------------------------------
+ * Replaces GradScaler.unscale_ + clip_grad_norm_(1.0) + torch.optim.AdamW.step of scripts/Modello_supporto.py:107,
+ * 133-141 on FLAT fp32 buffers (all parameters / gradients / moments of the model back to back).
+ * srb_grad_sumsq   info2[0] = sum of squares of grad[0..n), info2[1] = 1 if any element is inf/nan else 0
+ *                  (deterministic two-level reduction; scratch: srb_grad_norm_scratch_bytes()).
+ * srb_adamw_step   g = grad * coef, coef = inv_scale * min(1, max_norm / (sqrt(info2[0]) * inv_scale + 1e-6))
+ *                  (no clipping when max_norm <= 0 or info2 == NULL); the step is skipped when info2[1] != 0;
+ *                  then torch.optim.AdamW: p *= 1 - lr*wd; m = lerp(m, g, 1-beta1); v = beta2*v + (1-beta2)*g*g;
+ *                  p -= lr/(1-beta1^step) * m / (sqrt(v)/sqrt(1-beta2^step) + eps).  step counts from 1.
+ *                  shadow_bf16 (optional): bf16 copy of the updated parameters written in the same pass.
+ *                  No host synchronisation; the multi-rank gradient mean is folded into inv_scale (1/world). */
+size_t srb_grad_norm_scratch_bytes(void);
+int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream);
+int srb_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, int step, float inv_scale, float max_norm,
+                   const float* info2, void* shadow_bf16, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

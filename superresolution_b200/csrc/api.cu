@@ -179,6 +179,18 @@ int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, f
     if (!pred || !target || !out2 || !scratch || B <= 0) { set_error("psnr_ssim: bad args"); return SRB_E_ARG; }
     return psnr_ssim(pred, target, B, H, W, out2, (float*)scratch, (cudaStream_t)stream);
 }
+size_t srb_grad_norm_scratch_bytes(void) { return grad_norm_scratch_bytes(); }
+int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream) {
+    if (!grad || !info2 || !scratch || n == 0) { set_error("grad_sumsq: bad args"); return SRB_E_ARG; }
+    return grad_sumsq(grad, n, info2, scratch, (cudaStream_t)stream);
+}
+int srb_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, size_t n, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, int step, float inv_scale, float max_norm,
+                   const float* info2, void* shadow_bf16, void* stream) {
+    if (!param || !grad || !exp_avg || !exp_avg_sq || n == 0) { set_error("adamw_step: bad args"); return SRB_E_ARG; }
+    return adamw_step(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, inv_scale,
+                      max_norm, info2, shadow_bf16, (cudaStream_t)stream);
+}
 int srb_log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, void* stream) {
     if (n == 0) return SRB_OK;  // empty input is legal (reference: empty array in, empty array out)
     if (!x || !out) { set_error("log_normalize: null pointer"); return SRB_E_ARG; }

@@ -59,6 +59,13 @@ int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float
               cudaStream_t s);
 int log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, cudaStream_t s);
 
+// optim.cu
+size_t grad_norm_scratch_bytes();
+int grad_sumsq(const float* g, size_t n, float* info, void* scratch, cudaStream_t s);
+int adamw_step(float* p, const float* g, float* m, float* v, size_t n, float lr, float beta1, float beta2, float eps,
+               float weight_decay, int step, float inv_scale, float max_norm, const float* info, void* shadow_bf16,
+               cudaStream_t s);
+
 // blend.cu
 int blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int ov, float* acc,
                 float* wsum, int FH, int FW, int row0, int row1, cudaStream_t s);

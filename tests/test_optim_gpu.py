@@ -1,0 +1,103 @@
+"""Optimizer half of the training step: libsrb FusedAdamW against torch.optim.AdamW +
+GradScaler.unscale_ + clip_grad_norm_ (the sequence of reference scripts/Modello_supporto.py:133-141) on the same
+seeded parameters and gradients.  fp32 arithmetic: tolerance 2e-6 absolute on O(1) parameters."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(64, 4, 3, 3), (64,), (32, 64, 3, 3), (96, 96), (3,), (225, 6), (1, 64, 3, 3), (5,)]
+
+
+def _make(cuda, seed):
+    g = torch.Generator().manual_seed(seed)
+    return [torch.nn.Parameter(torch.randn(s, generator=g).to(cuda)) for s in SHAPES]
+
+
+def _grads(seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return [torch.randn(s, generator=g) * scale for s in SHAPES]
+
+
+def test_plain_step_matches_torch_adamw(cuda):
+    from superresolution_b200.optim import FusedAdamW
+    a, b = _make(cuda, 0), _make(cuda, 0)
+    ref = torch.optim.AdamW(a, lr=5e-4, weight_decay=0.01)
+    opt = FusedAdamW(b, lr=5e-4, weight_decay=0.01)
+    for it in range(6):
+        for p, q, g in zip(a, b, _grads(10 + it)):
+            p.grad = g.to(cuda)
+            q.grad.copy_(g.to(cuda))
+        ref.step()
+        opt.step()
+        ref.zero_grad()
+        opt.zero_grad()
+    for p, q in zip(a, b):
+        assert torch.allclose(p, q, rtol=0, atol=2e-6), (p - q).abs().max().item()
+        assert q.grad is not None and q.grad.abs().max().item() == 0.0  # views survive zero_grad
+
+
+def test_fused_unscale_clip_step_matches_reference_sequence(cuda):
+    from superresolution_b200.optim import FusedAdamW
+    a, b = _make(cuda, 1), _make(cuda, 1)
+    ref = torch.optim.AdamW(a, lr=5e-4, weight_decay=0.0)
+    opt = FusedAdamW(b, lr=5e-4, weight_decay=0.0, bf16_shadow=True)
+    scale = 1024.0
+    for it in range(4):
+        gs = _grads(20 + it, scale=scale * (3.0 if it % 2 else 0.01))  # clipped and unclipped steps
+        for p, q, g in zip(a, b, gs):
+            p.grad = g.to(cuda) / scale  # what scaler.unscale_ leaves
+            q.grad.copy_(g.to(cuda))
+        norm_ref = torch.nn.utils.clip_grad_norm_(a, 1.0)
+        norm = opt.grad_norm(grad_scale=scale)
+        assert abs(norm.item() - norm_ref.item()) <= 1e-5 * max(1.0, norm_ref.item())
+        ref.step()
+        opt.step(grad_scale=scale, max_norm=1.0)
+        assert opt.found_inf().item() == 0.0
+    for p, q in zip(a, b):
+        assert torch.allclose(p, q, rtol=0, atol=2e-6), (p - q).abs().max().item()
+    assert torch.equal(opt.shadow.float(), opt.flat_param.bfloat16().float())
+
+
+def test_nonfinite_gradient_skips_the_step(cuda):
+    from superresolution_b200.optim import FusedAdamW
+    b = _make(cuda, 2)
+    opt = FusedAdamW(b, lr=1e-3, weight_decay=0.0)
+    before = opt.flat_param.clone()
+    for q, g in zip(b, _grads(30)):
+        q.grad.copy_(g.to(cuda))
+    b[3].grad[5, 7] = float('inf')
+    opt.step(grad_scale=65536.0, max_norm=1.0)
+    assert opt.found_inf().item() == 1.0
+    assert torch.equal(opt.flat_param, before) and opt.exp_avg.abs().max().item() == 0.0
+    b[3].grad[5, 7] = float('nan')
+    opt.step(grad_scale=65536.0, max_norm=1.0)
+    assert opt.found_inf().item() == 1.0 and torch.equal(opt.flat_param, before)
+
+
+def test_drives_model_parameters_and_repack(cuda):
+    """The optimizer re-homes the model's parameters into its flat buffer; state_dict keys/values are unchanged and
+    the model's packed-weight cache notices the update (version counters are bumped)."""
+    from superresolution_b200.architecture import HybridSuperResolutionModel
+    from superresolution_b200.losses import CombinedLoss
+    from superresolution_b200.optim import FusedAdamW
+    torch.manual_seed(0)
+    m = HybridSuperResolutionModel(output_size=128, smoothing='none').to(cuda).eval()
+    sd0 = {k: v.clone() for k, v in m.state_dict().items()}
+    opt = FusedAdamW(m.parameters(), lr=5e-4, weight_decay=0.0)
+    assert list(m.state_dict().keys()) == list(sd0.keys())
+    assert all(torch.equal(v, sd0[k]) for k, v in m.state_dict().items())
+    x = torch.rand(1, 1, 32, 32, device=cuda)
+    with torch.no_grad():
+        y0 = m(x)
+    # gradient on one tensor only (the model backward is not built): d loss / d conv_last.bias through the loss kernel
+    t = torch.rand_like(y0)
+    bias = m.stage2.conv_last.bias
+    loss, _ = CombinedLoss()(y0 + bias.view(1, 1, 1, 1) * 0 + (bias - bias.detach()).view(1, 1, 1, 1), t)
+    loss.backward()
+    assert bias.grad.abs().sum().item() > 0
+    opt.step(grad_scale=1.0, max_norm=1.0)
+    with torch.no_grad():
+        y1 = m(x)
+    assert not torch.equal(y0, y1)  # repacked with the updated bias
+    assert (m.stage2.conv_last.bias - sd0['stage2.conv_last.bias']).abs().max().item() > 0

@@ -68,3 +68,38 @@ def test_two_rank_band_sharding_matches_single_rank():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert err < 1e-6
+
+
+def _allreduce_worker(rank, world, port, q):
+    import os
+    import torch
+    import torch.distributed as dist
+    from superresolution_b200.optim import allreduce_gradients
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    g = torch.Generator().manual_seed(100 + rank)
+    flat = torch.randn(100_003, generator=g)
+    allreduce_gradients(flat, bucket_bytes=64 << 10)  # 7 buckets, the last one ragged
+    q.put((rank, flat[:5].tolist(), float(flat.double().sum())))
+    dist.destroy_process_group()
+
+
+def test_bucketed_gradient_allreduce_world2():
+    """N>1 path of the training step's exchange (replaces DataParallel's reduce-add): gloo, world 2, on CPU."""
+    import torch
+    import torch.multiprocessing as mp
+    from superresolution_b200.optim import bucket_ranges
+    assert bucket_ranges(10, 4) == [(0, 4), (4, 8), (8, 10)]
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    ps = [ctx.Process(target=_allreduce_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in ps)
+    for p in ps:
+        p.join(60)
+    want = sum(torch.randn(100_003, generator=torch.Generator().manual_seed(100 + r)) for r in range(2))
+    for _, head, tot in res:
+        assert head == want[:5].tolist()
+        assert abs(tot - float(want.double().sum())) < 1e-6
