@@ -27,12 +27,13 @@ rrdb_conv_first_kernel(const void* __restrict__ x, int x_dtype, const float* __r
     for (int i = threadIdx.x; i < 64 * 36; i += blockDim.x) sw[i] = w[i];
     if (threadIdx.x < 64) sb[threadIdx.x] = bias[threadIdx.x];
     __syncthreads();
-    const size_t total = (size_t)B * h * w_ * 8;
+    const unsigned total = (unsigned)B * h * w_ * 8;  // host checks < 2^31
     const int W = 2 * w_, H = 2 * h;
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
         const int cg = idx & 7;
-        const size_t pix = idx >> 3;
-        const int xo = pix % w_, yo = (pix / w_) % h, b = pix / ((size_t)w_ * h);
+        const unsigned pix = idx >> 3;
+        const unsigned rowi = pix / (unsigned)w_;
+        const int xo = (int)(pix - rowi * w_), yo = (int)(rowi % (unsigned)h), b = (int)(rowi / (unsigned)h);
         float in[36];
 #pragma unroll
         for (int c = 0; c < 4; ++c)
@@ -59,11 +60,11 @@ rrdb_conv_first_kernel(const void* __restrict__ x, int x_dtype, const float* __r
         __nv_bfloat162* hh = (__nv_bfloat162*)&o;
 #pragma unroll
         for (int k = 0; k < 4; ++k) hh[k] = __floats2bfloat162_rn(acc[2 * k], acc[2 * k + 1]);
-        *(uint4*)(out + pix * out_pitch + cg * 8) = o;
-        float4* tp = (float4*)(trunk + pix * 64 + cg * 8);
+        *(uint4*)(out + (size_t)pix * out_pitch + cg * 8) = o;
+        float4* tp = (float4*)(trunk + (size_t)pix * 64 + cg * 8);
         tp[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
         tp[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-        float4* fp = (float4*)(feat + pix * 64 + cg * 8);
+        float4* fp = (float4*)(feat + (size_t)pix * 64 + cg * 8);
         fp[0] = tp[0];
         fp[1] = tp[1];
     }
@@ -72,6 +73,7 @@ rrdb_conv_first_kernel(const void* __restrict__ x, int x_dtype, const float* __r
 int rrdb_conv_first(const void* x, int x_dtype, const float* w, const float* bias, bf16* out, int out_pitch,
                     float* trunk, float* feat, int B, int h, int w_, cudaStream_t s) {
     const size_t total = (size_t)B * h * w_ * 8;
+    if (total >= ((size_t)1 << 31)) { set_error("rrdb_conv_first: tensor too large for 32-bit indexing"); return SRB_E_SHAPE; }
     int grid = (int)((total + 255) / 256);
     if (grid > 148 * 8) grid = 148 * 8;
     rrdb_conv_first_kernel<<<grid, 256, 0, s>>>(x, x_dtype, w, bias, out, out_pitch, trunk, feat, B, h, w_);
@@ -168,10 +170,11 @@ blur_kernel(const float* __restrict__ in, void* __restrict__ out, int out_dtype,
     const float row[7] = {K == 3 ? 1.f : K == 5 ? 1.f : 1.f, K == 3 ? 2.f : K == 5 ? 4.f : 6.f,
                           K == 3 ? 1.f : K == 5 ? 6.f : 15.f, K == 5 ? 4.f : 20.f, K == 5 ? 1.f : 15.f, 6.f, 1.f};
     const float norm = K == 3 ? 16.f : K == 5 ? 256.f : 1600.f;
-    const size_t n = (size_t)B * H * W;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const int x = i % W, y = (i / W) % H;
-        const size_t base = i - (size_t)y * W - x;
+    const unsigned n = (unsigned)B * H * W;  // host checks < 2^31
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned rowi = i / (unsigned)W;
+        const int x = (int)(i - rowi * W), y = (int)(rowi % (unsigned)H);
+        const size_t base = (size_t)i - (size_t)y * W - x;
         float s = 0.f;
 #pragma unroll
         for (int dy = -R; dy <= R; ++dy) {
@@ -195,6 +198,7 @@ blur_kernel(const float* __restrict__ in, void* __restrict__ out, int out_dtype,
 
 int blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int W, cudaStream_t s) {
     const size_t n = (size_t)B * H * W;
+    if (n >= ((size_t)1 << 31)) { set_error("blur: tensor too large for 32-bit indexing"); return SRB_E_SHAPE; }
     int grid = (int)((n + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;
     if (mode == SRB_SMOOTH_LIGHT) blur_kernel<3><<<grid, 256, 0, s>>>(in, out, out_dtype, B, H, W);

@@ -6,11 +6,14 @@
 namespace srb {
 
 // 16-lane group reduction (groups are aligned halves of a warp)
+// sum over the 16 lanes of a half-warp; the mask names only that half, so the two groups of a warp may leave their
+// grid-stride loops on different iterations
 __device__ __forceinline__ float group16_sum(float v) {
-    v += __shfl_xor_sync(0xffffffffu, v, 8);
-    v += __shfl_xor_sync(0xffffffffu, v, 4);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    const unsigned m = 0xffffu << (threadIdx.x & 16);
+    v += __shfl_xor_sync(m, v, 8);
+    v += __shfl_xor_sync(m, v, 4);
+    v += __shfl_xor_sync(m, v, 2);
+    v += __shfl_xor_sync(m, v, 1);
     return v;
 }
 
@@ -36,19 +39,21 @@ hat_conv_first_ln_kernel(const float* __restrict__ img, const float* __restrict_
         gr[j] = __ldg(gamma + c0 + j);
         ber[j] = __ldg(beta + c0 + j);
     }
-    const size_t npix = (size_t)B * H * W;
-    const size_t stride = ((size_t)gridDim.x * blockDim.x) >> 4;
+    // 32-bit pixel indices (host checks B*H*W < 2^31): 64-bit div/mod per pixel used to dominate this kernel
+    const unsigned npix = (unsigned)B * H * W;
+    const unsigned stride = (gridDim.x * blockDim.x) >> 4;
     // all 16 lanes of a group iterate together (npix is a multiple of the per-iteration pixel count or guarded)
-    for (size_t pix0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 4; pix0 < npix + stride; pix0 += stride) {
+    for (unsigned pix0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 4; pix0 < npix + stride; pix0 += stride) {
         const bool valid = pix0 < npix;
-        const size_t pix = valid ? pix0 : 0;
-        const int x = pix % W, y = (pix / W) % H;
-        const size_t b = pix / ((size_t)W * H);
+        const unsigned pix = valid ? pix0 : 0;
+        const unsigned rowi = pix / (unsigned)W;
+        const int x = (int)(pix - rowi * W), y = (int)(rowi % (unsigned)H);
+        const unsigned b = rowi / (unsigned)H;
         float in[9];
 #pragma unroll
         for (int t = 0; t < 9; ++t) {
             const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
-            in[t] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(img + (b * H + yy) * W + xx) : 0.f;
+            in[t] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(img + ((size_t)b * H + yy) * W + xx) : 0.f;
         }
         float v[8];
         float s = 0.f;
@@ -77,8 +82,8 @@ hat_conv_first_ln_kernel(const float* __restrict__ img, const float* __restrict_
                 h1[k] = __floats2bfloat162_rn((v[2 * k] - mean) * rstd * gr[2 * k] + ber[2 * k],
                                               (v[2 * k + 1] - mean) * rstd * gr[2 * k + 1] + ber[2 * k + 1]);
             }
-            *(uint4*)(f0 + pix * 96 + c0) = o0;
-            *(uint4*)(xn + pix * 96 + c0) = o1;
+            *(uint4*)(f0 + (size_t)pix * 96 + c0) = o0;
+            *(uint4*)(xn + (size_t)pix * 96 + c0) = o1;
         }
     }
 }
@@ -86,6 +91,7 @@ hat_conv_first_ln_kernel(const float* __restrict__ img, const float* __restrict_
 int hat_conv_first_ln(const float* img, const float* w, const float* bias, const float* gamma, const float* beta,
                       bf16* f0, bf16* xn, int B, int H, int W, cudaStream_t s) {
     const size_t threads = (size_t)B * H * W * 16;
+    if (threads >= ((size_t)1 << 31)) { set_error("hat_conv_first_ln: B*H*W too large for 32-bit indexing"); return SRB_E_SHAPE; }
     int grid = (int)((threads + 255) / 256);
     if (grid > 148 * 8) grid = 148 * 8;
     hat_conv_first_ln_kernel<<<grid, 256, 0, s>>>(img, w, bias, gamma, beta, f0, xn, B, H, W);
@@ -109,39 +115,46 @@ layernorm96_kernel(const bf16* __restrict__ in, const float* __restrict__ gamma,
         gr[j] = __ldg(gamma + c0 + j);
         br[j] = __ldg(beta + c0 + j);
     }
+    constexpr int U = 4;  // tokens in flight per 16-lane group (HBM-bound: keep several 16-byte loads outstanding)
     const size_t stride = ((size_t)gridDim.x * blockDim.x) >> 4;
-    for (size_t t0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 4; t0 < ntok + stride; t0 += stride) {
-        const bool valid = t0 < ntok;
-        const size_t tok = valid ? t0 : 0;
-        float v[8];
-        {
-            const uint4 raw = *(const uint4*)(in + tok * 96 + c0);
-            const __nv_bfloat162* h = (const __nv_bfloat162*)&raw;
+    for (size_t t0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 4; t0 < ntok + stride * U; t0 += stride * U) {
+        uint4 raw[U];
+        bool valid[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t tk = t0 + u * stride;
+            valid[u] = tk < ntok;
+            raw[u] = valid[u] ? __ldcs((const uint4*)(in + tk * 96 + c0)) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float v[8];
+            const __nv_bfloat162* h = (const __nv_bfloat162*)&raw[u];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float2 f = __bfloat1622float2(h[k]);
                 v[2 * k] = f.x;
                 v[2 * k + 1] = f.y;
             }
-        }
-        float s = 0.f;
+            float s = 0.f;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s += v[j];
-        s = group16_sum(act ? s : 0.f);
-        const float mean = s * (1.f / 96.f);
-        float q = 0.f;
+            for (int j = 0; j < 8; ++j) s += v[j];
+            s = group16_sum(act ? s : 0.f);
+            const float mean = s * (1.f / 96.f);
+            float q = 0.f;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) q += (v[j] - mean) * (v[j] - mean);
-        q = group16_sum(act ? q : 0.f);
-        const float rstd = rsqrtf(q * (1.f / 96.f) + 1e-5f);
-        if (valid && act) {
-            uint4 o;
-            __nv_bfloat162* h = (__nv_bfloat162*)&o;
+            for (int j = 0; j < 8; ++j) q += (v[j] - mean) * (v[j] - mean);
+            q = group16_sum(act ? q : 0.f);
+            const float rstd = rsqrtf(q * (1.f / 96.f) + 1e-5f);
+            if (valid[u] && act) {
+                uint4 o;
+                __nv_bfloat162* ho = (__nv_bfloat162*)&o;
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                h[k] = __floats2bfloat162_rn((v[2 * k] - mean) * rstd * gr[2 * k] + br[2 * k],
-                                             (v[2 * k + 1] - mean) * rstd * gr[2 * k + 1] + br[2 * k + 1]);
-            *(uint4*)(out + tok * 96 + c0) = o;
+                for (int k = 0; k < 4; ++k)
+                    ho[k] = __floats2bfloat162_rn((v[2 * k] - mean) * rstd * gr[2 * k] + br[2 * k],
+                                                  (v[2 * k + 1] - mean) * rstd * gr[2 * k + 1] + br[2 * k + 1]);
+                *(uint4*)(out + (t0 + u * stride) * 96 + c0) = o;
+            }
         }
     }
 }
@@ -232,19 +245,20 @@ int layernorm96(const bf16* in, const float* gamma, const float* beta, bf16* out
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 upsample2x_kernel(const bf16* __restrict__ in, int in_pitch, bf16* __restrict__ out, int B, int h, int w) {
-    const size_t n = (size_t)B * (2 * h) * (2 * w) * 8;  // 16-byte chunks, 8 per pixel
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const unsigned n = (unsigned)B * (2 * h) * (2 * w) * 8;  // 16-byte chunks, 8 per pixel (host checks < 2^31)
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const int ck = i & 7;
-        const size_t pix = i >> 3;
-        const int x = pix % (2 * w), y = (pix / (2 * w)) % (2 * h);
-        const size_t b = pix / ((size_t)4 * w * h);
-        *(uint4*)(out + pix * 64 + ck * 8) =
-            __ldg((const uint4*)(in + ((b * h + (y >> 1)) * w + (x >> 1)) * in_pitch + ck * 8));
+        const unsigned pix = i >> 3;
+        const unsigned rowi = pix / (unsigned)(2 * w);
+        const unsigned x = pix - rowi * (2 * w), y = rowi % (unsigned)(2 * h), b = rowi / (unsigned)(2 * h);
+        *(uint4*)(out + (size_t)pix * 64 + ck * 8) =
+            __ldg((const uint4*)(in + (((size_t)b * h + (y >> 1)) * w + (x >> 1)) * in_pitch + ck * 8));
     }
 }
 
 int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cudaStream_t s) {
     const size_t n = (size_t)B * 4 * h * w * 8;
+    if (n >= ((size_t)1 << 31)) { set_error("upsample2x: tensor too large for 32-bit indexing"); return SRB_E_SHAPE; }
     int grid = (int)((n + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;
     upsample2x_kernel<<<grid, 256, 0, s>>>(in, in_pitch, out, B, h, w);
@@ -258,27 +272,45 @@ int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cud
 // partial[b][tile][96]. Stage B (here): fixed-order sum of the tiles, the tiny MLP, and cs[b][c] = sigmoid(...) *
 // conv_scale so the HAB combine is a single FMA.
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(96)
+__global__ void __launch_bounds__(768)
 cab_finish_kernel(const float* __restrict__ partial, int nslab, float inv_hw, const float* __restrict__ w1 /*[3][96]*/,
                   const float* __restrict__ b1, const float* __restrict__ w2 /*[96][3]*/,
                   const float* __restrict__ b2, float conv_scale, float* __restrict__ cs) {
+    // 8 slab groups x 96 channels: group g sums slabs g, g+8, ... (independent loads, unrolled), then the 8 group
+    // sums are added in fixed order -> deterministic, and the 256-slab sum is 32 loads deep instead of 256
+    __shared__ float part[8][96];
     __shared__ float mean[96];
     __shared__ float hid[3];
-    const int b = blockIdx.x, c = threadIdx.x;
-    float t4[4] = {0.f, 0.f, 0.f, 0.f};  // four interleaved chains, fixed order
-    for (int i = 0; i < nslab; ++i) t4[i & 3] += partial[((size_t)b * nslab + i) * 96 + c];
-    mean[c] = ((t4[0] + t4[1]) + (t4[2] + t4[3])) * inv_hw;
+    const int b = blockIdx.x, c = threadIdx.x % 96, g = threadIdx.x / 96;
+    float tot = 0.f;
+    const float* src = partial + (size_t)b * nslab * 96 + c;
+#pragma unroll 8
+    for (int i = g; i < nslab; i += 8) tot += __ldg(src + (size_t)i * 96);
+    part[g][c] = tot;
     __syncthreads();
-    if (c < 3) {
-        float s = b1[c];
-        for (int k = 0; k < 96; ++k) s = fmaf(w1[c * 96 + k], mean[k], s);
-        hid[c] = fmaxf(s, 0.f);
+    if (threadIdx.x < 96) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += part[k][c];
+        mean[c] = t * inv_hw;
     }
     __syncthreads();
-    float s = b2[c];
+    if (threadIdx.x < 96) {  // warp w computes hidden unit w: 3 products per lane, fixed-order butterfly
+        const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+        float s = w1[w * 96 + l] * mean[l];
+        s = fmaf(w1[w * 96 + l + 32], mean[l + 32], s);
+        s = fmaf(w1[w * 96 + l + 64], mean[l + 64], s);
 #pragma unroll
-    for (int k = 0; k < 3; ++k) s = fmaf(w2[c * 3 + k], hid[k], s);
-    cs[b * 96 + c] = conv_scale / (1.f + expf(-s));
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (l == 0) hid[w] = fmaxf(s + b1[w], 0.f);
+    }
+    __syncthreads();
+    if (threadIdx.x < 96) {
+        float s = b2[c];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) s = fmaf(w2[c * 3 + k], hid[k], s);
+        cs[b * 96 + c] = conv_scale / (1.f + expf(-s));
+    }
 }
 
 // One slab = one 16 x 16 output tile of the cab.2 conv (conv_tc <96,2,9>), which writes the per-tile sums itself.
@@ -286,7 +318,7 @@ int cab_pool_slabs(int HW) { return (HW + 255) / 256; }
 
 int cab_channel_scale(const float* pool, int nslab, float* cs, const float* w1, const float* b1, const float* w2,
                       const float* b2, float conv_scale, int B, int HW, cudaStream_t s) {
-    cab_finish_kernel<<<B, 96, 0, s>>>(pool, nslab, 1.f / (float)HW, w1, b1, w2, b2, conv_scale, cs);
+    cab_finish_kernel<<<B, 768, 0, s>>>(pool, nslab, 1.f / (float)HW, w1, b1, w2, b2, conv_scale, cs);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
