@@ -33,7 +33,8 @@ constexpr int kStage = 8192;      // one 128 x 32 bf16 block, 64B-swizzled
 constexpr int OFF_W = PS * PATCH_STRIDE;
 constexpr int OFF_STG = OFF_W + W_RING * W_SLOT;
 constexpr int OFF_BAR = OFF_STG + 4 * kStage;
-constexpr int CHAIN_SMEM = OFF_BAR + 256 + 1024;
+constexpr int OFF_BIAS = OFF_BAR + 256;  // [kMaxChain][64] fp32: every layer's bias, staged once
+constexpr int CHAIN_SMEM = OFF_BIAS + kMaxChain * 64 * 4 + 1024;
 static_assert(CHAIN_SMEM <= 227 * 1024, "shared memory budget");
 
 struct alignas(64) ChainLayer {
@@ -74,8 +75,14 @@ conv_chain_kernel(const __grid_constant__ ChainParams P) {
     uint64_t* acc_full = empty_w + W_RING;  // [2]
     uint64_t* acc_empty = acc_full + 2;     // [2]
     uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
+    float* sbias = (float*)(smem + OFF_BIAS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    for (int i = threadIdx.x; i < P.nlayers * 64; i += kChainThreads) {  // biases are constants: no dependency wait
+        const ConvArgs& la = P.L[i >> 6].a;
+        sbias[i] = (la.bias && (i & 63) < la.Cout) ? __ldg(la.bias + (i & 63)) : 0.f;
+    }
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < PS; ++i) { mbar_init(&full_p[i], 1); mbar_init(&empty_p[i], 1); }
@@ -247,7 +254,7 @@ conv_chain_kernel(const __grid_constant__ ChainParams P) {
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
-                    epilogue_math(v, a, pix, c0, b);
+                    epilogue_math(v, a, pix, c0, b, sbias + l * 64);
                     if (a.out32) {
                         float4* op = (float4*)(a.out32 + pix * a.out32_pitch + c0);
 #pragma unroll

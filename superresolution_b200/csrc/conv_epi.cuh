@@ -18,8 +18,17 @@ __device__ __forceinline__ float gelu_erf(float x) {
 }
 
 // bias + activation + residuals on one 32-channel slice of one pixel (all indices compile-time after unrolling)
-__device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a, size_t pix, int cb, int b) {
-    if (a.bias) {
+// sbias: the layer's bias staged in shared memory by the kernel prologue (zeros when the layer has none); a global
+// __ldg per unit sat on the epilogue's critical path (~500 cycles per 128 x 32 block).
+__device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a, size_t pix, int cb, int b,
+                                              const float* sbias = nullptr) {
+    if (sbias) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            const float4 bb = *(const float4*)(sbias + cb + j);
+            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+        }
+    } else if (a.bias) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
             const float4 bb = __ldg((const float4*)(a.bias + cb + j));

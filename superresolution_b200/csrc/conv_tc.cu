@@ -60,6 +60,7 @@ constexpr int kThreads = 384;
 constexpr int kStageBytes = 8192;               // one 128 x 32 bf16 block, 64B-swizzled
 constexpr int kStagingBytes = 4 * kStageBytes;  // 2 epilogue groups x 2 buffers
 constexpr int kBarrierBytes = 512;
+constexpr int kBiasBytes = 2048;   // the layer's bias in shared memory (Cout <= 512 floats)
 constexpr int kColsumBytes = 2 * 16 * 128 * 4;  // [2 tiles][MT * 4 row groups <= 16][N_TILE <= 128] fp32 partial channel sums
 constexpr int kSmemLimit = 227 * 1024;
 constexpr int kMaxPS = 4;
@@ -71,7 +72,7 @@ struct ConvLaunch {
     int reuse;      // patch chunks stay resident across the N tiles of one spatial tile
     int tma_store;  // bf16 output through smem staging + TMA store
     int colsum_bytes;  // shared-memory bytes of the per-tile channel-sum scratch (0 unless a.colsum)
-    long long* dbg;    // development aid (-DSRB_CONV_PHASES): [grid][8] cycle totals of the MMA / epilogue warps
+    long long* dbg;    // development aid (-DSRB_CONV_PHASES): [grid][16] cycle totals of the MMA / epilogue warps
 };
 
 // Sum of v[c] over the 32 lanes of the warp, returned in lane c (recursive halving: 31 shuffles). Destroys v.
@@ -100,7 +101,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t* wt0 = patch0 + t.ps * Cfg::PATCH_STRIDE;
     uint8_t* stg0 = wt0 + t.wslots * Cfg::W_BYTES;
     float* scol = (float*)(stg0 + kStagingBytes);  // only carved when a.colsum (t.colsum_bytes)
-    uint64_t* bars = (uint64_t*)(stg0 + kStagingBytes + t.colsum_bytes);
+    float* sbias = (float*)(stg0 + kStagingBytes + t.colsum_bytes);
+    uint64_t* bars = (uint64_t*)(stg0 + kStagingBytes + t.colsum_bytes + kBiasBytes);
     uint64_t* full_p = bars;                 // [kMaxPS]
     uint64_t* empty_p = full_p + kMaxPS;     // [kMaxPS]
     uint64_t* full_w = empty_p + kMaxPS;     // [W_RING]  (3x3: ring; 1x1: full_w[0] = all resident tiles landed)
@@ -117,6 +119,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 256); }
         fence_barrier_init();
     }
+    for (int i = threadIdx.x; i < a.Cout; i += kThreads) sbias[i] = a.bias ? __ldg(a.bias + i) : 0.f;  // constants
     if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmO); }
     if (warp == 3) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
     tc_fence_before();
@@ -255,7 +258,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
 #ifdef SRB_CONV_PHASES
         if (t.dbg && lane == 0) {
-            long long* d = t.dbg + blockIdx.x * 8;
+            long long* d = t.dbg + blockIdx.x * 16;
             d[0] = clock64() - ph_t0; d[1] = ph_acc; d[2] = ph_patch; d[3] = ph_w;
         }
 #endif
@@ -269,7 +272,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint8_t* stg = stg0 + eg * 2 * kStageBytes;
         uint32_t it_a = 0, it_s = 0;
 #ifdef SRB_CONV_PHASES
-        long long ph_full = 0, ph_e0 = clock64(), ph_c;
+        long long ph_full = 0, ph_e0 = clock64(), ph_c, ph_ld = 0, ph_math = 0, ph_b1 = 0, ph_st = 0, ph_b2 = 0;
 #endif
         for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
             const int b = st / per_img, r = st % per_img;
@@ -288,13 +291,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const size_t pix = ((size_t)b * a.H + y) * a.W + x;
                     const int cb = nt * N_TILE + c0;  // first output channel of this 32-wide block
                     uint32_t acc[32];
+                    PH_BEGIN();
                     tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (MT * N_TILE) + mt * N_TILE + c0,
                                        acc);
                     tmem_ld_wait();
+                    PH_END(ph_ld);
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
-                    epilogue_math(v, a, pix, cb, b);
+                    PH_BEGIN();
+                    epilogue_math(v, a, pix, cb, b, sbias);
+                    PH_END(ph_math);
                     if (a.out32) {
                         float4* op = (float4*)(a.out32 + pix * a.out32_pitch + cb);
 #pragma unroll
@@ -304,8 +311,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         if (t.tma_store) {
                             // stage the 128 x 32 bf16 block (64-byte rows, SWIZZLE_64B) and hand it to TMA
                             uint8_t* sb = stg + (it_s & 1) * kStageBytes;
+                            PH_BEGIN();
                             if (issuer) bulk_wait_group_read<1>();  // the store that last used this buffer has read it
                             named_bar_sync(1 + eg, 128);
+                            PH_END(ph_b1);
+                            PH_BEGIN();
                             const uint32_t sw = (row >> 1) & 3;
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
@@ -317,7 +327,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                 *(uint4*)(sb + row * 64 + ((j ^ sw) << 4)) = o;
                             }
                             fence_proxy_async_smem();
+                            PH_END(ph_st);
+                            PH_BEGIN();
                             named_bar_sync(1 + eg, 128);
+                            PH_END(ph_b2);
                             if (issuer) {
                                 tma_store_4d(&tmO, sb, cb, tx * Cfg::TW + 8 * mt, ty * Cfg::TH, b);
                                 bulk_commit_group();
@@ -370,8 +383,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (issuer) bulk_wait_group<0>();  // all TMA stores of this group have completed
 #ifdef SRB_CONV_PHASES
         if (t.dbg && warp == 4 && lane == 0) {
-            long long* d = t.dbg + blockIdx.x * 8;
-            d[4] = clock64() - ph_e0; d[5] = ph_full;
+            long long* d = t.dbg + blockIdx.x * 16;
+            d[4] = clock64() - ph_e0; d[5] = ph_full; d[6] = ph_ld; d[7] = ph_math; d[8] = ph_b1; d[9] = ph_st; d[10] = ph_b2;
         }
 #endif
     }
@@ -461,7 +474,7 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
         set_error("conv_tc: colsum needs Cout == N tile (Cout=%d)", a.Cout);
         return SRB_E_ARG;
     }
-    const int fixed = t.wslots * Cfg::W_BYTES + kStagingBytes + t.colsum_bytes + kBarrierBytes + 1024;
+    const int fixed = t.wslots * Cfg::W_BYTES + kStagingBytes + t.colsum_bytes + kBiasBytes + kBarrierBytes + 1024;
     t.ps = (kSmemLimit - fixed) / Cfg::PATCH_STRIDE;
     if (t.ps > kMaxPS) t.ps = kMaxPS;
     if (t.ps < 2) {
@@ -523,7 +536,7 @@ int conv_tc_launch(const ConvArgs& a_in, cudaStream_t stream) {
     ConvArgs a = a_in;
     if (a.taps != 9 && a.taps != 1) { set_error("conv_tc: taps must be 9 or 1"); return SRB_E_ARG; }
     if (a.Cin % 16 || a.Cin < 16) { set_error("conv_tc: Cin=%d must be a multiple of 16", a.Cin); return SRB_E_SHAPE; }
-    if (a.Cout % 32) { set_error("conv_tc: Cout=%d must be a multiple of 32", a.Cout); return SRB_E_SHAPE; }
+    if (a.Cout % 32 || a.Cout > kBiasBytes / 4) { set_error("conv_tc: Cout=%d must be a multiple of 32, at most %d", a.Cout, kBiasBytes / 4); return SRB_E_SHAPE; }
     if (a.in_pitch % 8 || ((uintptr_t)a.in & 15) || ((uintptr_t)a.w & 15)) {
         set_error("conv_tc: input pitch / pointers must be 16-byte aligned");
         return SRB_E_ARG;

@@ -16,7 +16,7 @@ bias = torch.zeros(cout, device='cuda')
 out = torch.empty(B, R, R, cout, device='cuda', dtype=torch.bfloat16)
 lib = L.lib()
 lib.srb_debug_set_phase_buffer.argtypes = [C.c_void_p]; lib.srb_debug_set_phase_buffer.restype = None
-buf = torch.zeros(148 * 8, dtype=torch.int64, device='cuda')
+buf = torch.zeros(148 * 16, dtype=torch.int64, device='cuda')
 for _ in range(3):
     ops.conv_nhwc(x, cin, w, bias, out=out, act=act)
 torch.cuda.synchronize()
@@ -30,10 +30,11 @@ lib.srb_debug_set_phase_buffer(C.c_void_p(buf.data_ptr()))
 ops.conv_nhwc(x, cin, w, bias, out=out, act=act)
 torch.cuda.synchronize()
 lib.srb_debug_set_phase_buffer(None)
-p = buf.view(148, 8).double().mean(0)
+p = buf.view(148, 16).double().mean(0)
 fl = 2.0 * B * R * R * cin * cout * taps
 print(f'conv {cin}->{cout} taps {taps} act {act} B {B} R {R}: {us:.1f} us/launch (warm L2, back to back), {fl / us / 1e6:.0f} TFLOP/s')
-names = ['mma_total', 'wait_acc_empty', 'wait_patch', 'wait_weight', 'epi_total', 'epi_wait_acc_full']
-for n, v in zip(names, p[:6]):
+names = ['mma_total', 'wait_acc_empty', 'wait_patch', 'wait_weight', 'epi_total', 'epi_wait_acc_full', 'epi_tmem_ld',
+         'epi_math', 'epi_bar1(+read wait)', 'epi_pack+sts+fence', 'epi_bar2']
+for n, v in zip(names, p[:11]):
     print(f'  {n:18s} {v.item() / 1e3:9.1f} kcyc')
 print(f'  mma issue+other    {(p[0] - p[1] - p[2] - p[3]).item() / 1e3:9.1f} kcyc;  epilogue work {(p[4] - p[5]).item() / 1e3:9.1f} kcyc')
