@@ -22,9 +22,11 @@ __global__ void __launch_bounds__(256)
 rrdb_conv_first_kernel(const void* __restrict__ x, int x_dtype, const float* __restrict__ w /*[64][4][3][3]*/,
                        const float* __restrict__ bias, bf16* __restrict__ out, int out_pitch,
                        float* __restrict__ trunk, float* __restrict__ feat, int B, int h, int w_) {
-    __shared__ float sw[64 * 36];
+    // weights transposed to [k = cin*9 + tap][64 cout]: a lane reads its 8 output channels of one k as two 16-byte
+    // loads (the [cout][k] order put all 8 channel groups of a warp on one bank: 8-way conflicts on every load)
+    __shared__ __align__(16) float sw[36 * 64];
     __shared__ float sb[64];
-    for (int i = threadIdx.x; i < 64 * 36; i += blockDim.x) sw[i] = w[i];
+    for (int i = threadIdx.x; i < 64 * 36; i += blockDim.x) sw[(i % 36) * 64 + i / 36] = w[i];
     if (threadIdx.x < 64) sb[threadIdx.x] = bias[threadIdx.x];
     __syncthreads();
     const unsigned total = (unsigned)B * h * w_ * 8;  // host checks < 2^31
@@ -49,12 +51,14 @@ rrdb_conv_first_kernel(const void* __restrict__ x, int x_dtype, const float* __r
                 }
         float acc[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float* wr = sw + (cg * 8 + j) * 36;
-            float s = sb[cg * 8 + j];
+        for (int j = 0; j < 8; ++j) acc[j] = sb[cg * 8 + j];
 #pragma unroll
-            for (int k = 0; k < 36; ++k) s = fmaf(in[k], wr[k], s);
-            acc[j] = s;
+        for (int k = 0; k < 36; ++k) {
+            const float4 w0 = *(const float4*)(sw + k * 64 + cg * 8), w1 = *(const float4*)(sw + k * 64 + cg * 8 + 4);
+            acc[0] = fmaf(in[k], w0.x, acc[0]); acc[1] = fmaf(in[k], w0.y, acc[1]);
+            acc[2] = fmaf(in[k], w0.z, acc[2]); acc[3] = fmaf(in[k], w0.w, acc[3]);
+            acc[4] = fmaf(in[k], w1.x, acc[4]); acc[5] = fmaf(in[k], w1.y, acc[5]);
+            acc[6] = fmaf(in[k], w1.z, acc[6]); acc[7] = fmaf(in[k], w1.w, acc[7]);
         }
         uint4 o;
         __nv_bfloat162* hh = (__nv_bfloat162*)&o;

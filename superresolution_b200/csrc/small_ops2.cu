@@ -22,7 +22,7 @@ __device__ __forceinline__ float group16_sum(float v) {
 // 16 lanes per pixel, lanes 0..11 own 8 channels each.  Writes f0 (long skip, pre-norm) and x = LN(f0), both bf16
 // [B,H,W,96].  LayerNorm statistics in fp32 over the fp32 conv result (eps 1e-5, biased variance).
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 hat_conv_first_ln_kernel(const float* __restrict__ img, const float* __restrict__ w /*[96][1][3][3]*/,
                          const float* __restrict__ bias, const float* __restrict__ gamma,
                          const float* __restrict__ beta, bf16* __restrict__ f0, bf16* __restrict__ xn, int B, int H,
@@ -39,51 +39,70 @@ hat_conv_first_ln_kernel(const float* __restrict__ img, const float* __restrict_
         gr[j] = __ldg(gamma + c0 + j);
         ber[j] = __ldg(beta + c0 + j);
     }
-    // 32-bit pixel indices (host checks B*H*W < 2^31): 64-bit div/mod per pixel used to dominate this kernel
-    const unsigned npix = (unsigned)B * H * W;
+    // Each 16-lane group walks a run of 8 consecutive pixels of one row with a sliding 3x3 window: 3 new loads per
+    // pixel instead of 9, index arithmetic once per run (32-bit; host checks B*H*W < 2^31 and W % 8 == 0).
+    const unsigned segs_per_row = (unsigned)W >> 3;
+    const unsigned nseg = (unsigned)B * H * segs_per_row;
     const unsigned stride = (gridDim.x * blockDim.x) >> 4;
-    // all 16 lanes of a group iterate together (npix is a multiple of the per-iteration pixel count or guarded)
-    for (unsigned pix0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 4; pix0 < npix + stride; pix0 += stride) {
-        const bool valid = pix0 < npix;
-        const unsigned pix = valid ? pix0 : 0;
-        const unsigned rowi = pix / (unsigned)W;
-        const int x = (int)(pix - rowi * W), y = (int)(rowi % (unsigned)H);
+    for (unsigned seg = (blockIdx.x * blockDim.x + threadIdx.x) >> 4; seg < nseg; seg += stride) {
+        const unsigned rowi = seg / segs_per_row;
+        const int xs = (int)(seg - rowi * segs_per_row) * 8, y = (int)(rowi % (unsigned)H);
         const unsigned b = rowi / (unsigned)H;
-        float in[9];
-#pragma unroll
-        for (int t = 0; t < 9; ++t) {
-            const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
-            in[t] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(img + ((size_t)b * H + yy) * W + xx) : 0.f;
+        const float* r1 = img + ((size_t)b * H + y) * W;
+        const float* r0 = r1 - W;
+        const float* r2 = r1 + W;
+        const bool up = y > 0, dn = y + 1 < H;
+        float in[9];  // in[3 * row + col]
+        in[0] = in[3] = in[6] = 0.f;
+        if (xs > 0) {
+            in[0] = up ? __ldg(r0 + xs - 1) : 0.f;
+            in[3] = __ldg(r1 + xs - 1);
+            in[6] = dn ? __ldg(r2 + xs - 1) : 0.f;
         }
-        float v[8];
-        float s = 0.f;
+        in[1] = up ? __ldg(r0 + xs) : 0.f;
+        in[4] = __ldg(r1 + xs);
+        in[7] = dn ? __ldg(r2 + xs) : 0.f;
+#pragma unroll 1
+        for (int i = 0; i < 8; ++i) {
+            const int x = xs + i;
+            const bool rt = x + 1 < W;
+            in[2] = (rt && up) ? __ldg(r0 + x + 1) : 0.f;
+            in[5] = rt ? __ldg(r1 + x + 1) : 0.f;
+            in[8] = (rt && dn) ? __ldg(r2 + x + 1) : 0.f;
+            float v[8];
+            float s = 0.f;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            float a = br[j];
+            for (int j = 0; j < 8; ++j) {
+                float a = br[j];
 #pragma unroll
-            for (int t = 0; t < 9; ++t) a = fmaf(in[t], wr[j * 9 + t], a);
-            v[j] = a;
-            s += a;
-        }
-        s = group16_sum(act ? s : 0.f);
-        const float mean = s * (1.f / 96.f);
-        float q = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) q += (v[j] - mean) * (v[j] - mean);
-        q = group16_sum(act ? q : 0.f);
-        const float rstd = rsqrtf(q * (1.f / 96.f) + 1e-5f);
-        if (valid && act) {
-            uint4 o0, o1;
-            __nv_bfloat162* h0 = (__nv_bfloat162*)&o0;
-            __nv_bfloat162* h1 = (__nv_bfloat162*)&o1;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                h0[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
-                h1[k] = __floats2bfloat162_rn((v[2 * k] - mean) * rstd * gr[2 * k] + ber[2 * k],
-                                              (v[2 * k + 1] - mean) * rstd * gr[2 * k + 1] + ber[2 * k + 1]);
+                for (int t = 0; t < 9; ++t) a = fmaf(in[t], wr[j * 9 + t], a);
+                v[j] = a;
+                s += a;
             }
-            *(uint4*)(f0 + (size_t)pix * 96 + c0) = o0;
-            *(uint4*)(xn + (size_t)pix * 96 + c0) = o1;
+            s = group16_sum(act ? s : 0.f);
+            const float mean = s * (1.f / 96.f);
+            float q = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) q += (v[j] - mean) * (v[j] - mean);
+            q = group16_sum(act ? q : 0.f);
+            const float rstd = rsqrtf(q * (1.f / 96.f) + 1e-5f);
+            if (act) {
+                uint4 o0, o1;
+                __nv_bfloat162* h0 = (__nv_bfloat162*)&o0;
+                __nv_bfloat162* h1 = (__nv_bfloat162*)&o1;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    h0[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+                    h1[k] = __floats2bfloat162_rn((v[2 * k] - mean) * rstd * gr[2 * k] + ber[2 * k],
+                                                  (v[2 * k + 1] - mean) * rstd * gr[2 * k + 1] + ber[2 * k + 1]);
+                }
+                const size_t pix = ((size_t)b * H + y) * W + x;
+                *(uint4*)(f0 + pix * 96 + c0) = o0;
+                *(uint4*)(xn + pix * 96 + c0) = o1;
+            }
+            in[0] = in[1]; in[1] = in[2];
+            in[3] = in[4]; in[4] = in[5];
+            in[6] = in[7]; in[7] = in[8];
         }
     }
 }
@@ -92,7 +111,8 @@ int hat_conv_first_ln(const float* img, const float* w, const float* bias, const
                       bf16* f0, bf16* xn, int B, int H, int W, cudaStream_t s) {
     const size_t threads = (size_t)B * H * W * 16;
     if (threads >= ((size_t)1 << 31)) { set_error("hat_conv_first_ln: B*H*W too large for 32-bit indexing"); return SRB_E_SHAPE; }
-    int grid = (int)((threads + 255) / 256);
+    if (W % 8) { set_error("hat_conv_first_ln: W=%d must be a multiple of 8 (the HAT window)", W); return SRB_E_SHAPE; }
+    int grid = (int)((threads / 8 + 255) / 256);
     if (grid > 148 * 8) grid = 148 * 8;
     hat_conv_first_ln_kernel<<<grid, 256, 0, s>>>(img, w, bias, gamma, beta, f0, xn, B, H, W);
     SRB_CUDA(cudaGetLastError());
