@@ -101,6 +101,11 @@ int srb_fold_ln_linear(const float* w, const float* b, const float* gamma, const
                        float* b_folded, int N, int K, void* stream);
 int srb_mlp_branch(const void* t, const void* cab, const float* cs, const void* w1_folded, const float* b1_folded,
                    const void* w2_packed, const float* b2, void* y, size_t ntok, size_t tok_per_img, void* stream);
+/* srb_mlp_branch plus a second output xn_out = LayerNorm(y) * ln_g + ln_b (bf16 [ntok,96]): the norm1 of the block that
+ * follows (OCAB.norm1 after the last HAB of a residual group), computed from the output rows while they are stored. */
+int srb_mlp_branch_ln(const void* t, const void* cab, const float* cs, const void* w1_folded, const float* b1_folded,
+                      const void* w2_packed, const float* b2, void* y, const float* ln_g, const float* ln_b,
+                      void* xn_out, size_t ntok, size_t tok_per_img, void* stream);
 /* fp32 [Cout,Cin,kh,kw] (PyTorch) -> bf16 [kh*kw][Cout][Cin] */
 int srb_pack_conv_weight(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream);
 

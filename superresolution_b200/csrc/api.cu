@@ -135,6 +135,17 @@ int srb_mlp_branch(const void* t, const void* cab, const float* cs, const void* 
     return mlp_fused((const bf16*)t, (const bf16*)cab, cs, (const bf16*)w1_folded, b1_folded, (const bf16*)w2_packed,
                      b2, (bf16*)y, ntok, tok_per_img, (cudaStream_t)stream);
 }
+int srb_mlp_branch_ln(const void* t, const void* cab, const float* cs, const void* w1_folded, const float* b1_folded,
+                      const void* w2_packed, const float* b2, void* y, const float* ln_g, const float* ln_b,
+                      void* xn_out, size_t ntok, size_t tok_per_img, void* stream) {
+    if (!t || !w1_folded || !b1_folded || !w2_packed || !b2 || !y || ntok == 0 || (cab && !cs) || !ln_g || !ln_b ||
+        !xn_out) {
+        set_error("mlp_branch_ln: bad args");
+        return SRB_E_ARG;
+    }
+    return mlp_fused((const bf16*)t, (const bf16*)cab, cs, (const bf16*)w1_folded, b1_folded, (const bf16*)w2_packed,
+                     b2, (bf16*)y, ntok, tok_per_img, (cudaStream_t)stream, ln_g, ln_b, (bf16*)xn_out);
+}
 
 int srb_param_count(void) { return model_param_count(); }
 const char* srb_param_name(int i) { return model_param_name(i); }

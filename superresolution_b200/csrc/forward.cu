@@ -77,6 +77,8 @@ static void build_desc(ModelDesc& m) {
     conv_f32("stage2.conv_first", 96, 1, 9);
     ln("stage2.patch_embed.norm");
     for (int l = 0; l < 4; ++l) {
+        snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", l);
+        const std::string oca = buf;
         for (int j = 0; j < 6; ++j) {
             snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.", l, j);
             const std::string b = buf;
@@ -429,6 +431,8 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
                                 B, R, Rw, c.s));
     char buf[128];
     for (int l = 0; l < 4; ++l) {
+        snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", l);
+        const std::string oca = buf;
         for (int j = 0; j < 6; ++j) {
             snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.blocks.%d.", l, j);
             const std::string b = buf;
@@ -453,11 +457,12 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
             LAUNCH(c, PC_MLP, 2.0 * 36864 * (double)ntok,
                    mlp_fused(w.ao, w.c2, w.cs, (const bf16*)(pk + c.m->mlp_w1f_off[l * 6 + j]),
                              (const float*)(pk + c.m->mlp_b1f_off[l * 6 + j]), c.Wt(b + "mlp.fc2.weight"),
-                             c.F(b + "mlp.fc2.bias"), w.y, ntok, (size_t)R * Rw, c.s));
+                             c.F(b + "mlp.fc2.bias"), w.y, ntok, (size_t)R * Rw, c.s,
+                             // the last HAB of a group also emits xn = OCAB.norm1(y) from its copy-out
+                             j == 5 ? c.F(oca + "norm1.weight") : nullptr, j == 5 ? c.F(oca + "norm1.bias") : nullptr,
+                             j == 5 ? w.xn : nullptr));
         }
-        snprintf(buf, sizeof(buf), "stage2.layers.%d.residual_group.overlap_attn.", l);
-        const std::string b = buf;
-        LAUNCH(c, PC_LN, 0.0, layernorm96(w.y, c.F(b + "norm1.weight"), c.F(b + "norm1.bias"), w.xn, ntok, c.s));
+        const std::string b = oca;
         SRB_TRY(tc_layer(c, b + "qkv", w.xn, 96, B, R, Rw, ACT_NONE, 0.f, w.qkv, 288));
         LAUNCH(c, PC_OCAB, 2.0 * 2 * 64 * 144 * 16 * 6 * ((double)B * R * Rw / 64), ocab_attention(w.qkv, (const bf16*)(pk + c.m->bias_oca_off[l]), w.ao, B, R, Rw, c.s));
         SRB_TRY(tc_layer(c, b + "proj", w.ao, 96, B, R, Rw, ACT_NONE, 0.f, w.y, 96, nullptr, 1.f, w.y, 0, 96));

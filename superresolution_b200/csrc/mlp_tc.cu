@@ -46,7 +46,8 @@ constexpr int OFF_W2 = OFF_W1 + A1_PLANES * W1_PITCH;
 constexpr int OFF_Y = OFF_W2 + A2_PLANES * W2_PITCH;
 constexpr int OFF_CS = OFF_Y + 2 * YP_BYTES;
 constexpr int OFF_BAR = OFF_CS + kMaxImg * 192;
-constexpr int MLP_TC_SMEM = OFF_BAR + 64;
+constexpr int OFF_LN2 = OFF_BAR + 64;  // [2][96] fp32: affine of the optional second LayerNorm output
+constexpr int MLP_TC_SMEM = OFF_LN2 + 2 * 96 * 4;
 constexpr uint32_t D1_COL = 0, D2_COL = 192, MLP_TMEM_COLS = 512;
 static_assert(MLP_TC_SMEM <= 227 * 1024, "shared memory budget");
 static_assert(OFF_A2 % 16 == 0 && OFF_W1 % 16 == 0 && OFF_W2 % 16 == 0 && OFF_Y % 16 == 0 && OFF_BAR % 8 == 0, "align");
@@ -60,6 +61,9 @@ struct MlpArgs {
     const bf16* w2;    // [96][192]
     const float* b2;
     bf16* y;
+    const float* ln2_g;  // optional second output xn2 = LayerNorm(y) * ln2_g + ln2_b (the next block's norm1,
+    const float* ln2_b;  // fused into the copy-out: OCAB's norm1 after the last HAB of a group)
+    bf16* xn2;
     uint32_t ntiles, tiles_per_img;
     uint32_t nimg;  // images covered by this launch (cs table rows)
     long long* dbg;  // optional [grid][8] per-phase cycle totals of thread 0 (development aid)
@@ -77,6 +81,7 @@ __device__ __forceinline__ uint4 bias_split(float b) {
     return make_uint4((uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16), 0u, 0u, 0u);
 }
 
+template <bool LN2>
 __global__ void __launch_bounds__(kMlpThreads, 1)
 mlp_tc_kernel(const MlpArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -87,6 +92,7 @@ mlp_tc_kernel(const MlpArgs a) {
     uint8_t* sYP = smem + OFF_Y;
     uint8_t* sCS = smem + OFF_CS;
     uint64_t* bars = (uint64_t*)(smem + OFF_BAR);
+    float* sLN2 = (float*)(smem + OFF_LN2);
     uint64_t* bar_a1 = bars + 0;  // A1 (normalised tokens) written          count kAluThreads
     uint64_t* bar_a2 = bars + 1;  // A2 (GELU hidden) written                 count kAluThreads
     uint64_t* bar_d1 = bars + 2;  // fc1 accumulator complete                 count 1 (tcgen05.commit)
@@ -109,6 +115,7 @@ mlp_tc_kernel(const MlpArgs a) {
         const int kg = i / 96, n = i % 96;
         *(uint4*)(sW2 + kg * W2_PITCH + n * 16) = __ldg((const uint4*)a.w2 + n * 24 + kg);
     }
+    if (LN2 && tid < 192) sLN2[tid] = tid < 96 ? __ldg(a.ln2_g + tid) : __ldg(a.ln2_b + tid - 96);
     const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
     const uint4 ones4 = make_uint4(0x3F803F80u, 0u, 0u, 0u);  // {1.0, 1.0, 0, 0, 0, 0, 0, 0} bf16
     if (tid < 192) {
@@ -341,8 +348,55 @@ mlp_tc_kernel(const MlpArgs a) {
             {
                 const uint8_t* yp = sYP + (i & 1) * YP_BYTES + ln_row * 16;
                 uint4* gp = (uint4*)(a.y + ((size_t)tile * 128 + ln_row) * 96) + ln_j;
+                uint4 o[3];
 #pragma unroll
-                for (int m = 0; m < 3; ++m) gp[4 * m] = *(const uint4*)(yp + (ln_j + 4 * m) * YP_PITCH);
+                for (int m = 0; m < 3; ++m) {
+                    o[m] = *(const uint4*)(yp + (ln_j + 4 * m) * YP_PITCH);
+                    gp[4 * m] = o[m];
+                }
+                if (LN2) {  // xn2 = LayerNorm(y) of the bf16 row just written (4 lanes per token: two shuffles per sum)
+                    float v[24];
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) {
+                        const uint32_t* w = (const uint32_t*)&o[m];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 f = unpackbf(w[k]);
+                            v[8 * m + 2 * k] = f.x;
+                            v[8 * m + 2 * k + 1] = f.y;
+                        }
+                    }
+                    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { s0 += v[k]; s1 += v[8 + k]; s2 += v[16 + k]; }
+                    float sm = (s0 + s1) + s2;
+                    sm += __shfl_xor_sync(0xffffffffu, sm, 1);
+                    sm += __shfl_xor_sync(0xffffffffu, sm, 2);
+                    const float mean = sm * (1.f / 96.f);
+                    float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        q0 = fmaf(v[k] - mean, v[k] - mean, q0);
+                        q1 = fmaf(v[8 + k] - mean, v[8 + k] - mean, q1);
+                        q2 = fmaf(v[16 + k] - mean, v[16 + k] - mean, q2);
+                    }
+                    float qq = (q0 + q1) + q2;
+                    qq += __shfl_xor_sync(0xffffffffu, qq, 1);
+                    qq += __shfl_xor_sync(0xffffffffu, qq, 2);
+                    const float rstd = rsqrtf(qq * (1.f / 96.f) + 1e-5f);
+                    uint4* xp = (uint4*)(a.xn2 + ((size_t)tile * 128 + ln_row) * 96) + ln_j;
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) {
+                        const float* gg = sLN2 + (ln_j + 4 * m) * 8;
+                        uint4 x4;
+                        uint32_t* xw = (uint32_t*)&x4;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            xw[k] = packbf(fmaf((v[8 * m + 2 * k] - mean) * rstd, gg[2 * k], gg[96 + 2 * k]),
+                                           fmaf((v[8 * m + 2 * k + 1] - mean) * rstd, gg[2 * k + 1], gg[96 + 2 * k + 1]));
+                        xp[4 * m] = x4;
+                    }
+                }
             }
             if (i + 2 < n_my) issue_loads(tile + 2 * step);
         }
@@ -389,15 +443,18 @@ int fold_ln_linear(const float* w, const float* b, const float* gamma, const flo
 }
 
 int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, const float* b1f, const bf16* w2,
-              const float* b2, bf16* y, size_t ntok, size_t tok_per_img, cudaStream_t s) {
+              const float* b2, bf16* y, size_t ntok, size_t tok_per_img, cudaStream_t s, const float* ln2_g,
+              const float* ln2_b, bf16* xn2) {
     if (ntok % 128 || tok_per_img % 128) { set_error("mlp_fused: token counts must be multiples of 128"); return SRB_E_SHAPE; }
     if (((uintptr_t)t | (uintptr_t)y | (uintptr_t)cab | (uintptr_t)w1f | (uintptr_t)w2) & 15) {
         set_error("mlp_fused: pointers must be 16-byte aligned");
         return SRB_E_ARG;
     }
+    if (xn2 && (!ln2_g || !ln2_b || ((uintptr_t)xn2 & 15))) { set_error("mlp_fused: xn2 needs ln2_g / ln2_b and 16-byte alignment"); return SRB_E_ARG; }
     static bool attr = false;
     if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MLP_TC_SMEM));
+        SRB_CUDA(cudaFuncSetAttribute(mlp_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MLP_TC_SMEM));
+        SRB_CUDA(cudaFuncSetAttribute(mlp_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MLP_TC_SMEM));
         attr = true;
     }
     const size_t nimg_total = ntok / tok_per_img;
@@ -409,6 +466,7 @@ int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, 
         MlpArgs a;
         a.t = t + tok0 * 96; a.cab = cab ? cab + tok0 * 96 : nullptr; a.cs = cs ? cs + img * 96 : nullptr;
         a.w1 = w1f; a.b1 = b1f; a.w2 = w2; a.b2 = b2; a.y = y + tok0 * 96;
+        a.ln2_g = ln2_g; a.ln2_b = ln2_b; a.xn2 = xn2 ? xn2 + tok0 * 96 : nullptr;
         a.ntiles = (uint32_t)(nimg * tok_per_img / 128);
         a.tiles_per_img = (uint32_t)(tok_per_img / 128);
         a.nimg = (uint32_t)nimg;
@@ -424,7 +482,8 @@ int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, 
         attrs[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attrs;
         cfg.numAttrs = 1;
-        SRB_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, a));
+        if (xn2) SRB_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel<true>, a));
+        else SRB_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel<false>, a));
     }
     return SRB_OK;
 }

@@ -45,7 +45,8 @@ int expand_rel_bias_f32(const float* table, int T, const int64_t* index, int NK,
 // mlp_tc.cu:  y0 = t + cab*cs (cab may be null);  y = y0 + fc2(GELU(fc1(LayerNorm(y0))))   (y may alias t)
 // w1f / b1f: fc1 with the LayerNorm affine folded in (fold_ln_linear)
 int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, const float* b1f, const bf16* w2,
-              const float* b2, bf16* y, size_t ntok, size_t tok_per_img, cudaStream_t s);
+              const float* b2, bf16* y, size_t ntok, size_t tok_per_img, cudaStream_t s,
+              const float* ln2_g = nullptr, const float* ln2_b = nullptr, bf16* xn2 = nullptr);
 // W'[n][k] = W[n][k]*gamma[k] -> bf16, b'[n] = b[n] + sum_k W[n][k]*beta[k]   (fp32 inputs)
 int fold_ln_linear(const float* w, const float* b, const float* gamma, const float* beta, bf16* w_out, float* b_out,
                    int N, int K, cudaStream_t s);

@@ -49,13 +49,21 @@ def fold_ln_linear(w, b, gamma, beta):
     return wf, bf
 
 
-def mlp_branch(t, w1_folded, b1_folded, w2_packed, b2, cab=None, cs=None, out=None, tok_per_img=None):
-    """y = y0 + fc2(GELU(fc1(LN(y0)))), y0 = t + cab*cs[b].  t/cab/out: bf16 [ntok,96]; cs fp32 [B,96]."""
+def mlp_branch(t, w1_folded, b1_folded, w2_packed, b2, cab=None, cs=None, out=None, tok_per_img=None, next_ln=None):
+    """y = y0 + fc2(GELU(fc1(LN(y0)))), y0 = t + cab*cs[b].  t/cab/out: bf16 [ntok,96]; cs fp32 [B,96].
+    next_ln=(gamma, beta): also returns xn = LayerNorm(y)*gamma + beta (bf16), the fused norm1 of the next block."""
     ntok = t.shape[0]
     if out is None:
         out = torch.empty_like(t)
     if tok_per_img is None:
         tok_per_img = ntok if cs is None else ntok // cs.shape[0]
+    if next_ln is not None:
+        xn = torch.empty_like(t)
+        rc = L.lib().srb_mlp_branch_ln(L.ptr(t), L.ptr(cab), L.ptr(cs), L.ptr(w1_folded), L.ptr(b1_folded),
+                                       L.ptr(w2_packed), L.ptr(b2), L.ptr(out), L.ptr(next_ln[0]), L.ptr(next_ln[1]),
+                                       L.ptr(xn), ntok, tok_per_img, L.current_stream())
+        L.check(rc, 'mlp_branch_ln')
+        return out, xn
     rc = L.lib().srb_mlp_branch(L.ptr(t), L.ptr(cab), L.ptr(cs), L.ptr(w1_folded), L.ptr(b1_folded), L.ptr(w2_packed),
                                 L.ptr(b2), L.ptr(out), ntok, tok_per_img, L.current_stream())
     L.check(rc, 'mlp_branch')

@@ -44,3 +44,25 @@ def test_mlp_branch(cuda, ntok, B, with_cab, inplace):
     bad = (err > tol).sum().item()
     assert bad == 0, f'{bad} mismatches, max err {err.max().item():.4g}, ref absmax {ref.abs().max().item():.4g}'
     assert err.mean().item() < 6e-3, err.mean().item()
+
+
+def test_mlp_branch_with_fused_next_layernorm(cuda):
+    """The last HAB of a group also emits OCAB.norm1(y): must equal LayerNorm of the kernel's own bf16 output."""
+    from superresolution_b200 import ops
+    ntok, B = 152 * 128, 2
+    g = torch.Generator().manual_seed(7)
+    t = (torch.randn(ntok, 96, generator=g) * 1.5 + 0.3).to(cuda).to(torch.bfloat16)
+    cab = (torch.randn(ntok, 96, generator=g) * 3).to(cuda).to(torch.bfloat16)
+    cs = (torch.rand(B, 96, generator=g) * 0.02).to(cuda)
+    mk = lambda *s, k=1.0: (k * torch.randn(*s, generator=g)).to(cuda)
+    ln_g, ln_b = 1 + mk(96, k=0.2), mk(96, k=0.1)
+    w1, b1, w2, b2 = mk(192, 96, k=96 ** -0.5), mk(192, k=0.3), mk(96, 192, k=192 ** -0.5), mk(96, k=0.3)
+    g2, be2 = 1 + mk(96, k=0.3), mk(96, k=0.2)
+    (w1f, b1f), w2p = ops.fold_ln_linear(w1, b1, ln_g, ln_b), ops.pack_conv_weight(w2)
+    plain = ops.mlp_branch(t, w1f, b1f, w2p, b2, cab=cab, cs=cs, tok_per_img=ntok // B)
+    out, xn = ops.mlp_branch(t, w1f, b1f, w2p, b2, cab=cab, cs=cs, tok_per_img=ntok // B, next_ln=(g2, be2))
+    torch.cuda.synchronize()
+    assert torch.equal(out, plain)
+    want = F.layer_norm(out.float(), (96,), g2, be2, 1e-5)
+    err = (xn.float() - want).abs()
+    assert (err <= 8e-3 * want.abs() + 1e-2).all(), err.max().item()  # one bf16 rounding of the result
