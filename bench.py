@@ -238,6 +238,7 @@ def run_gpu(args):
         tc_ms = sum(prof[k][0] for k in fam)
         tc_flops = sum(prof[k][1] for k in fam)
         launches = model.launch_count(BATCH, PATCH, PATCH)
+        traffic, traffic_src = family_traffic(dom)
         line = {
             'metric': METRIC, 'value': world * out_mpix * args.steps / (dev_ms * 1e-3), 'unit': UNIT,
             'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': dev_ms / args.steps,
@@ -252,7 +253,8 @@ def run_gpu(args):
                     'h2d_bytes_per_step': x_host.numel() * 4, 'd2h_bytes_per_step': y_host.numel() * 4},
             'gpu_launches': launches * args.steps,
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s',
-                         'frac': achieved / peak_tf, 'traffic': None, 'peak_source': peak_src,
+                         'frac': achieved / peak_tf, 'traffic': traffic, 'traffic_source': traffic_src,
+                         'peak_source': peak_src,
                          'kernel': fam[dom], 'launches_per_step': d_n, 'kernel_ms_per_step': d_ms,
                          'share_of_step': d_ms / total_prof_ms if total_prof_ms else None,
                          'all_tensor_kernels': {'achieved': tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms else 0.0,
@@ -269,6 +271,29 @@ def run_gpu(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+# kernel-name substrings of each tensor-core family in the committed ncu capture (profiles/r01_kernel_traffic.json)
+FAMILY_KERNELS = {'conv3x3_tcgen05': ('conv_chain_kernel', ', 9>>'), 'linear_tcgen05': (', 1>>',),
+                  'hab_attention_tcgen05': ('hab_tc_kernel',), 'mlp_tcgen05': ('mlp_tc_kernel',),
+                  'ocab_attention': ('ocab_attn_kernel',)}
+
+
+def family_traffic(family):
+    """DRAM bytes (read + write) per launch of the family's kernels, averaged over its launches in one forward, from
+    the committed ncu capture of tools/run_forward_once.py (dram__bytes_read.sum + dram__bytes_write.sum per launch;
+    tools/ncu_metrics_table.py --json).  None when the file is absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r01_kernel_traffic.json')
+    try:
+        tab = json.load(open(path))
+    except Exception:
+        return None, None
+    tot = n = 0
+    for name, row in tab.items():
+        if any(k in name for k in FAMILY_KERNELS.get(family, ())):
+            tot += row['dram_bytes_per_launch'] * row['launches']
+            n += row['launches']
+    return (tot / n if n else None), 'profiles/r01_kernel_traffic.json (ncu dram__bytes_read+write per launch, one forward)'
 
 
 def main():
