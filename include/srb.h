@@ -131,6 +131,20 @@ int srb_blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int
 int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, void* stream);
 
 
+/* ---- backward of the conv / linear layers (autograd of nn.Conv2d(..,3,1,1) / nn.Linear inside
+ * RRDBNet / HAT, reached from scripts/Modello_supporto.py:133) -------------------------------------------------------
+ * data gradient:   dX = srb_conv_nhwc_bf16(dY, w = srb_pack_conv_weight_dgrad(W), Cin' = Cout, Cout' = Cin); accumulate
+ *                  into an existing gradient with res1 = out (in place).
+ * srb_pack_conv_weight_dgrad  fp32 [Cout,Cin,kh,kw] -> bf16 [kh*kw][Cin][Cout] with the taps reversed.
+ * srb_conv_wgrad   dW[Cout,Cin,kh,kw] (fp32, PyTorch layout) = sum_px dY[px,co] * X[px+tap,ci]  (+= when accumulate);
+ *                  db[Cout] = sum_px dY (optional).  x / dy: bf16 NHWC with channel pitches; W % 32 == 0;
+ *                  Cin, Cout multiples of 8.  Deterministic (split-K partials reduced in fixed order).
+ *                  scratch: srb_conv_wgrad_scratch_bytes(...) (0 = unsupported geometry). */
+int srb_pack_conv_weight_dgrad(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream);
+size_t srb_conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps);
+int srb_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
+                   int H, int W, int Cin, int Cout, int taps, int accumulate, void* stream);
+
 /* ---- optimizer half of the training step ------------------------------------------------
  * Replaces GradScaler.unscale_ + clip_grad_norm_(1.0) + torch.optim.AdamW.step of scripts/Modello_supporto.py:107,
  * 133-141 on FLAT fp32 buffers (all parameters / gradients / moments of the model back to back).

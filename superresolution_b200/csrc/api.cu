@@ -190,6 +190,19 @@ int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, f
     if (!pred || !target || !out2 || !scratch || B <= 0) { set_error("psnr_ssim: bad args"); return SRB_E_ARG; }
     return psnr_ssim(pred, target, B, H, W, out2, (float*)scratch, (cudaStream_t)stream);
 }
+int srb_pack_conv_weight_dgrad(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream) {
+    if (!w || !w_packed || Cout <= 0 || Cin <= 0 || (taps != 9 && taps != 1)) { set_error("pack_conv_weight_dgrad: bad args"); return SRB_E_ARG; }
+    return pack_conv_weight_dgrad(w, (bf16*)w_packed, Cout, Cin, taps, (cudaStream_t)stream);
+}
+size_t srb_conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps) {
+    return conv_wgrad_scratch_bytes(B, H, W, Cin, Cout, taps);
+}
+int srb_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
+                   int H, int W, int Cin, int Cout, int taps, int accumulate, void* stream) {
+    if (!x || !dy || !dw || !scratch || B <= 0 || H <= 0 || W <= 0) { set_error("conv_wgrad: bad args"); return SRB_E_ARG; }
+    return conv_wgrad((const bf16*)x, x_pitch, (const bf16*)dy, dy_pitch, dw, db, scratch, B, H, W, Cin, Cout, taps,
+                      accumulate, (cudaStream_t)stream);
+}
 size_t srb_grad_norm_scratch_bytes(void) { return grad_norm_scratch_bytes(); }
 int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream) {
     if (!grad || !info2 || !scratch || n == 0) { set_error("grad_sumsq: bad args"); return SRB_E_ARG; }

@@ -1,0 +1,286 @@
+// Backward building blocks of the conv / linear layers (93 % of the model's FLOPs are
+// 3x3 convs and linears, so these two operators carry the same share of the backward pass).  Reference: autograd of
+// nn.Conv2d(.., 3, 1, 1) / nn.Linear inside BasicSR RRDBNet and HAT, reached from scripts/Modello_supporto.py:133.
+//
+//   data gradient    dX = conv3x3(dY, W') with W'[ci][co][ky][kx] = W[co][ci][2-ky][2-kx]  (stride 1, pad 1): the forward
+//                    tcgen05 kernel (conv_tc.cu) on a flipped / transposed weight image -> pack_conv_weight_dgrad.
+//                    Accumulating into a gradient slice of a dense block is the forward epilogue's `+ res1` in place.
+//   weight gradient  dW[co][ci][tap] = sum_px dY[px][co] * X[px + tap][ci]: a GEMM whose contraction runs over pixels, both
+//                    operands channel-contiguous (= "MN-major").  conv_wgrad_kernel: split-K over pixel chunks, 64 x 64
+//                    (co x ci) CTA tiles per tap, mma.sync.m16n8k16 with ldmatrix.trans fragments from XOR-swizzled
+//                    shared memory, fp32 partials + fixed-order reduction (deterministic, no atomics).
+//   bias gradient    db[co] = sum_px dY[px][co]: two-level column sum.
+#include <cuda_bf16.h>
+
+#include "common.h"
+#include "ops.h"
+#include "ptx.cuh"
+
+namespace srb {
+
+namespace {
+
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// 16-byte async copy; !valid -> the destination is zero-filled (src-size 0), nothing is read
+__device__ __forceinline__ void cp_async16_zfill(void* dst, const void* src, bool valid) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)),
+                 "l"(src), "r"(valid ? 16 : 0)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(addr));
+}
+
+// fp32 [Cout][Cin][taps] -> bf16 [taps][Cin][Cout] with the taps reversed: the weight image of the data-gradient conv
+__global__ void pack_conv_weight_dgrad_kernel(const float* __restrict__ w, bf16* __restrict__ o, int Cout, int Cin,
+                                              int taps) {
+    const int n = Cout * Cin * taps;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int co = i % Cout, ci = (i / Cout) % Cin, t = i / (Cin * Cout);
+        o[i] = __float2bfloat16_rn(w[((size_t)co * Cin + ci) * taps + (taps - 1 - t)]);
+    }
+}
+
+constexpr int WG_KC = 32;        // pixels per k-chunk (two m16n8k16 k-steps): one row segment of the image
+constexpr int WG_TILE = 64;      // co x ci tile of a CTA
+constexpr int WG_THREADS = 256;  // 8 warps = 2 (co) x 4 (ci); warp tile 32 x 16
+constexpr int WG_STAGES = 3;
+
+struct WgradArgs {
+    const bf16* x;   // [B,H,W,x_pitch]  layer input (channels [0,Cin))
+    const bf16* dy;  // [B,H,W,dy_pitch] gradient of the layer output (channels [0,Cout))
+    float* partial;  // [ksplit][taps][Cout][Cin]
+    int x_pitch, dy_pitch, B, H, W, Cin, Cout, taps;
+    int nchunks, chunks_per_split;
+};
+
+// One k-chunk = WG_KC consecutive pixels of one image row.  Stage layout: dY tile [32 px][64 co], X tile [32 px][64 ci],
+// 128 B per pixel row, 16-byte units XOR-swizzled with (px & 7) so that ldmatrix (8 rows, one unit column) is
+// conflict free.
+__device__ __forceinline__ void wg_load_chunk(const WgradArgs& a, int chunk, int co0, int ci0, int dyo, int dxo,
+                                              uint8_t* s_dy, uint8_t* s_x, int tid) {
+    const int segs = a.W / WG_KC;
+    const int row = chunk / segs, x0 = (chunk % segs) * WG_KC;
+    const int b = row / a.H, y = row % a.H;
+    // 32 px x 8 units per operand = 256 x 16 B each: one unit per thread and operand
+    const int px = tid >> 3, u = tid & 7;
+    {
+        const bool ok = co0 + u * 8 < a.Cout;
+        const bf16* src = a.dy + (((size_t)b * a.H + y) * a.W + x0 + px) * a.dy_pitch + co0 + u * 8;
+        cp_async16_zfill(s_dy + px * 128 + ((u ^ (px & 7)) << 4), src, ok);
+    }
+    {
+        const int yy = y + dyo, xx = x0 + px + dxo;
+        const bool ok = (ci0 + u * 8 < a.Cin) && yy >= 0 && yy < a.H && xx >= 0 && xx < a.W;
+        const bf16* src = a.x + (((size_t)b * a.H + (ok ? yy : 0)) * a.W + (ok ? xx : 0)) * a.x_pitch + ci0 + u * 8;
+        cp_async16_zfill(s_x + px * 128 + ((u ^ (px & 7)) << 4), src, ok);
+    }
+}
+
+__global__ void __launch_bounds__(WG_THREADS)
+conv_wgrad_kernel(const WgradArgs a) {
+    __shared__ __align__(128) uint8_t smem[WG_STAGES][2][WG_KC * 128];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp >> 2, wn = warp & 3;  // warp tile: co [32 wm, +32), ci [16 wn, +16)
+    const int nci = (a.Cin + WG_TILE - 1) / WG_TILE;
+    const int tile = blockIdx.x;  // (tap, co block, ci block)
+    const int tap = tile / (nci * ((a.Cout + WG_TILE - 1) / WG_TILE));
+    const int rem = tile % (nci * ((a.Cout + WG_TILE - 1) / WG_TILE));
+    const int co0 = (rem / nci) * WG_TILE, ci0 = (rem % nci) * WG_TILE;
+    const int dyo = a.taps == 9 ? tap / 3 - 1 : 0, dxo = a.taps == 9 ? tap % 3 - 1 : 0;
+    const int c_begin = blockIdx.y * a.chunks_per_split;
+    const int c_end = min(a.nchunks, c_begin + a.chunks_per_split);
+
+    float acc[2][2][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc[i][j][k] = 0.f;
+
+    // prologue: WG_STAGES - 1 chunks in flight
+#pragma unroll
+    for (int s = 0; s < WG_STAGES - 1; ++s) {
+        if (c_begin + s < c_end) wg_load_chunk(a, c_begin + s, co0, ci0, dyo, dxo, smem[s][0], smem[s][1], tid);
+        cp_async_commit();
+    }
+    for (int c = c_begin; c < c_end; ++c) {
+        const int st = (c - c_begin) % WG_STAGES;
+        cp_async_wait<WG_STAGES - 2>();
+        __syncthreads();  // chunk c landed for every thread; the stage refilled below was consumed in iteration c-1
+        {
+            const int cn = c + WG_STAGES - 1;
+            const int sn = (cn - c_begin) % WG_STAGES;
+            if (cn < c_end) wg_load_chunk(a, cn, co0, ci0, dyo, dxo, smem[sn][0], smem[sn][1], tid);
+            cp_async_commit();
+        }
+        const uint32_t s_dy = smem_u32(smem[st][0]), s_x = smem_u32(smem[st][1]);
+#pragma unroll
+        for (int ks = 0; ks < WG_KC / 16; ++ks) {
+            // A = dY^T [co 16][px 16] per m-tile: memory is [px][co] -> ldmatrix.trans; matrices ordered
+            // (co 0-7, px 0-7), (co 8-15, px 0-7), (co 0-7, px 8-15), (co 8-15, px 8-15) = a0..a3
+            uint32_t af[2][4];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                const int px = ks * 16 + (lane & 7) + ((lane >> 4) << 3);
+                const int unit = ((wm * 32 + mt * 16) >> 3) + ((lane >> 3) & 1);
+                ldmatrix_x4_trans(s_dy + px * 128 + ((unit ^ (px & 7)) << 4), af[mt][0], af[mt][1], af[mt][2], af[mt][3]);
+            }
+            // B = X [px 16][ci 8] per n-tile: matrices (px 0-7, ci 0-7), (px 8-15, ci 0-7) = b0, b1 of n-tile 0, then n-tile 1
+            uint32_t bfr[4];
+            {
+                const int px = ks * 16 + (lane & 7) + (((lane >> 3) & 1) << 3);
+                const int unit = ((wn * 16) >> 3) + (lane >> 4);
+                ldmatrix_x4_trans(s_x + px * 128 + ((unit ^ (px & 7)) << 4), bfr[0], bfr[1], bfr[2], bfr[3]);
+            }
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 2; ++nt)
+                    mma_bf16_16816(acc[mt][nt], af[mt], bfr[2 * nt], bfr[2 * nt + 1]);
+        }
+    }
+    cp_async_wait<0>();
+    // partial[split][tap][co][ci]
+    float* dst = a.partial + ((size_t)blockIdx.y * a.taps + tap) * a.Cout * a.Cin;
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int co = co0 + wm * 32 + mt * 16 + g + 8 * h;
+                const int ci = ci0 + wn * 16 + nt * 8 + 2 * t;
+                if (co < a.Cout && ci < a.Cin)
+                    *(float2*)(dst + (size_t)co * a.Cin + ci) = make_float2(acc[mt][nt][2 * h], acc[mt][nt][2 * h + 1]);
+            }
+}
+
+// dW[co][ci][tap] (PyTorch layout) = (accumulate ? dW : 0) + sum_split partial[split][tap][co][ci], fixed order
+__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int ksplit, int taps,
+                                    int Cout, int Cin, int accumulate) {
+    const int n = taps * Cout * Cin;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < ksplit; ++k) s += partial[(size_t)k * n + i];
+        const int ci = i % Cin, co = (i / Cin) % Cout, tap = i / (Cin * Cout);
+        float* o = dw + ((size_t)co * Cin + ci) * taps + tap;
+        *o = accumulate ? *o + s : s;
+    }
+}
+
+constexpr int BG_ROWS = 1024;  // pixels per block of the bias-gradient column sum
+
+// partial[blk][c] = sum over the block's pixels of dy[px][c]  (c < C <= 512, 8 channels per thread)
+__global__ void __launch_bounds__(256)
+bias_grad_partial_kernel(const bf16* __restrict__ dy, int pitch, size_t npx, int C, float* __restrict__ partial) {
+    __shared__ float sm[256 * 8];
+    const int cg = C / 8;               // 16-byte channel groups
+    const int lanes_px = 256 / cg;      // pixel lanes (threads beyond cg * lanes_px idle)
+    const int g = threadIdx.x % cg, pl = threadIdx.x / cg;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const size_t p0 = (size_t)blockIdx.x * BG_ROWS;
+    const size_t p1 = p0 + BG_ROWS < npx ? p0 + BG_ROWS : npx;
+    if (pl < lanes_px) {
+        for (size_t p = p0 + pl; p < p1; p += lanes_px) {
+            const uint4 raw = __ldg((const uint4*)(dy + p * pitch + g * 8));
+            const __nv_bfloat162* h = (const __nv_bfloat162*)&raw;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 f = __bfloat1622float2(h[k]);
+                acc[2 * k] += f.x;
+                acc[2 * k + 1] += f.y;
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sm[threadIdx.x * 8 + j] = acc[j];
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += 256) {
+        float s = 0.f;
+        for (int l = 0; l < lanes_px; ++l) s += sm[(l * cg + c / 8) * 8 + (c & 7)];
+        partial[(size_t)blockIdx.x * C + c] = s;
+    }
+}
+
+__global__ void bias_grad_final_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ db,
+                                       int accumulate) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double s = 0.0;
+    for (int i = 0; i < nblk; ++i) s += (double)partial[(size_t)i * C + c];
+    db[c] = accumulate ? db[c] + (float)s : (float)s;
+}
+
+int wgrad_ksplit(int Cin, int Cout, int taps, int nchunks) {
+    const int tiles = taps * ((Cout + WG_TILE - 1) / WG_TILE) * ((Cin + WG_TILE - 1) / WG_TILE);
+    int ks = (num_sms() * 4 + tiles - 1) / tiles;  // ~4 CTAs per SM (33 KB smem, 256 threads each)
+    if (ks > nchunks) ks = nchunks;
+    if (ks < 1) ks = 1;
+    return ks;
+}
+
+}  // namespace
+
+int pack_conv_weight_dgrad(const float* w, bf16* o, int Cout, int Cin, int taps, cudaStream_t s) {
+    const int n = Cout * Cin * taps;
+    pack_conv_weight_dgrad_kernel<<<(n + 255) / 256, 256, 0, s>>>(w, o, Cout, Cin, taps);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+size_t conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps) {
+    if (W % WG_KC) return 0;
+    const int nchunks = B * H * (W / WG_KC);
+    const size_t npx = (size_t)B * H * W;
+    const size_t wpart = (size_t)wgrad_ksplit(Cin, Cout, taps, nchunks) * taps * Cout * Cin * sizeof(float);
+    const size_t bpart = ((npx + BG_ROWS - 1) / BG_ROWS) * Cout * sizeof(float);
+    return wpart + bpart;
+}
+
+int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
+               int H, int W, int Cin, int Cout, int taps, int accumulate, cudaStream_t s) {
+    if (taps != 9 && taps != 1) { set_error("conv_wgrad: taps must be 9 or 1"); return SRB_E_ARG; }
+    if (W % WG_KC) { set_error("conv_wgrad: W=%d must be a multiple of %d", W, WG_KC); return SRB_E_SHAPE; }
+    if (Cin % 8 || Cout % 8 || Cout > 512) { set_error("conv_wgrad: Cin=%d Cout=%d must be multiples of 8 (Cout <= 512)", Cin, Cout); return SRB_E_SHAPE; }
+    if (x_pitch % 8 || dy_pitch % 8 || (((uintptr_t)x | (uintptr_t)dy) & 15) || ((uintptr_t)scratch & 15)) {
+        set_error("conv_wgrad: pitches / pointers must be 16-byte aligned");
+        return SRB_E_ARG;
+    }
+    WgradArgs a;
+    a.x = x; a.dy = dy; a.partial = (float*)scratch;
+    a.x_pitch = x_pitch; a.dy_pitch = dy_pitch; a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout; a.taps = taps;
+    a.nchunks = B * H * (W / WG_KC);
+    const int ksplit = wgrad_ksplit(Cin, Cout, taps, a.nchunks);
+    a.chunks_per_split = (a.nchunks + ksplit - 1) / ksplit;
+    const int tiles = taps * ((Cout + WG_TILE - 1) / WG_TILE) * ((Cin + WG_TILE - 1) / WG_TILE);
+    conv_wgrad_kernel<<<dim3(tiles, ksplit), WG_THREADS, 0, s>>>(a);
+    SRB_CUDA(cudaGetLastError());
+    const int n = taps * Cout * Cin;
+    wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(a.partial, dw, ksplit, taps, Cout, Cin, accumulate);
+    SRB_CUDA(cudaGetLastError());
+    if (db) {
+        const size_t npx = (size_t)B * H * W;
+        float* bpart = a.partial + (size_t)ksplit * n;
+        const int nblk = (int)((npx + BG_ROWS - 1) / BG_ROWS);
+        if (256 / (Cout / 8) < 1) { set_error("conv_wgrad: Cout too large for the bias gradient"); return SRB_E_SHAPE; }
+        bias_grad_partial_kernel<<<nblk, 256, 0, s>>>(dy, dy_pitch, npx, Cout, bpart);
+        SRB_CUDA(cudaGetLastError());
+        bias_grad_final_kernel<<<(Cout + 127) / 128, 128, 0, s>>>(bpart, nblk, Cout, db, accumulate);
+        SRB_CUDA(cudaGetLastError());
+    }
+    return SRB_OK;
+}
+
+}  // namespace srb

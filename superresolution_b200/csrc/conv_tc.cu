@@ -547,6 +547,8 @@ int conv_tc_launch(const ConvArgs& a_in, cudaStream_t stream) {
         if (a.Cout == 64) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<64, 4, 9>>(a, stream) : launch_cfg<ConvCfg<64, 2, 9>>(a, stream);
         if (a.Cout % 128 == 0) return launch_cfg<ConvCfg<128, 2, 9>>(a, stream);
         if (a.Cout % 96 == 0) return launch_cfg<ConvCfg<96, 2, 9>>(a, stream);
+        // any other multiple of 32 (e.g. the 160-channel data gradient of a dense-block conv4): N tiles of 32
+        return (a.W % 32 == 0) ? launch_cfg<ConvCfg<32, 4, 9>>(a, stream) : launch_cfg<ConvCfg<32, 2, 9>>(a, stream);
     } else {
         if (a.Cout % 96 == 0) return launch_cfg<ConvCfg<96, 2, 1>>(a, stream);
         if (a.Cout % 64 == 0) return launch_cfg<ConvCfg<64, 2, 1>>(a, stream);

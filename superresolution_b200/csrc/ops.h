@@ -60,6 +60,12 @@ int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float
               cudaStream_t s);
 int log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, cudaStream_t s);
 
+// conv_bwd.cu
+int pack_conv_weight_dgrad(const float* w, bf16* o, int Cout, int Cin, int taps, cudaStream_t s);
+size_t conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps);
+int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
+               int H, int W, int Cin, int Cout, int taps, int accumulate, cudaStream_t s);
+
 // optim.cu
 size_t grad_norm_scratch_bytes();
 int grad_sumsq(const float* g, size_t n, float* info, void* scratch, cudaStream_t s);

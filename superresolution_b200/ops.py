@@ -86,3 +86,34 @@ def hab_attention(x, ln_g, ln_b, wqkv_packed, bqkv, bias_frag_log2e, wproj_packe
                                       L.ptr(bias_frag_log2e), L.ptr(wproj_packed), L.ptr(bproj), L.ptr(xn), L.ptr(t),
                                       B, H, W, shift, L.current_stream()), 'hab_attention')
     return xn, t
+
+
+def pack_conv_weight_dgrad(w):
+    """fp32 [Cout,Cin,kh,kw] (or Linear [Cout,Cin]) -> bf16 [taps][Cin][Cout], taps reversed: weights of the
+    data-gradient conv  dX = conv_nhwc(dY, Cout, pack_conv_weight_dgrad(W))."""
+    w = w.detach().float().contiguous()
+    cout, cin = w.shape[0], w.shape[1]
+    taps = w.numel() // (cout * cin)
+    out = torch.empty(taps, cin, cout, dtype=torch.bfloat16, device=w.device)
+    L.check(L.lib().srb_pack_conv_weight_dgrad(L.ptr(w), L.ptr(out), cout, cin, taps, L.current_stream()),
+            'pack_conv_weight_dgrad')
+    return out
+
+
+def conv_wgrad(x, cin, dy, cout, taps, dw=None, db=None, accumulate=False, want_bias=True):
+    """x: bf16 [B,H,W,>=cin] layer input, dy: bf16 [B,H,W,>=cout] output gradient (channel-offset views allowed).
+    Returns (dW fp32 [cout,cin,k,k] or [cout,cin], db fp32 [cout] or None)."""
+    B, H, W = x.shape[:3]
+    k = 3 if taps == 9 else 1
+    if dw is None:
+        dw = torch.zeros((cout, cin, k, k) if taps == 9 else (cout, cin), dtype=torch.float32, device=x.device)
+    if db is None and want_bias:
+        db = torch.zeros(cout, dtype=torch.float32, device=x.device)
+    lib = L.lib()
+    nbytes = lib.srb_conv_wgrad_scratch_bytes(B, H, W, cin, cout, taps)
+    if nbytes == 0:
+        raise RuntimeError('conv_wgrad: unsupported geometry (W must be a multiple of 32)')
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    L.check(lib.srb_conv_wgrad(L.ptr(x), x.stride(2), L.ptr(dy), dy.stride(2), L.ptr(dw), L.ptr(db), L.ptr(scratch),
+                               B, H, W, cin, cout, taps, int(accumulate), L.current_stream()), 'conv_wgrad')
+    return dw, db
