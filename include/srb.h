@@ -145,6 +145,21 @@ size_t srb_conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int 
 int srb_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
                    int H, int W, int Cin, int Cout, int taps, int accumulate, void* stream);
 
+/* srb_upsample2x_nearest  F.interpolate(scale_factor=2, mode='nearest') of a 64-channel bf16 NHWC tensor
+ *                         ([B,h,w,in_pitch] -> dense [B,2h,2w,64]); RRDBNet.forward upsampling (rrdbnet_arch.py).
+ * srb_conv3x3_cout1       conv_last of both stages: bf16 [B,H,W,64] -> fp32 [B,H,W], w fp32 [1,64,3,3] (H % 8, W % 32). */
+int srb_upsample2x_nearest(const void* in, int in_pitch, void* out, int B, int h, int w, void* stream);
+int srb_conv3x3_cout1(const void* in, int in_pitch, const float* w, const float* bias, float* out, int B, int H, int W,
+                      void* stream);
+/* element-wise backward operators of the RRDBNet training path; tensors are NHWC slices [npx][C] with a channel pitch
+ * srb_lrelu_bwd       g *= (y > 0 ? 1 : slope) in place, y = the saved LeakyReLU OUTPUT (bf16 both; C % 8 == 0)
+ * srb_axpby           out = a*x + b*y (y may be NULL); each operand bf16 (f32 flag 0) or fp32 (1); out may alias x / y
+ * srb_upsample2x_bwd  backward of F.interpolate(scale_factor=2, mode='nearest'): out[b,y,x,:] = sum of the 2x2 block */
+int srb_lrelu_bwd(void* g, int g_pitch, const void* y, int y_pitch, size_t npx, int C, float slope, void* stream);
+int srb_axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b,
+              const void* y, int y_f32, int y_pitch, size_t npx, int C, void* stream);
+int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int B, int h, int w, int C, void* stream);
+
 /* ---- optimizer half of the training step ------------------------------------------------
  * Replaces GradScaler.unscale_ + clip_grad_norm_(1.0) + torch.optim.AdamW.step of scripts/Modello_supporto.py:107,
  * 133-141 on FLAT fp32 buffers (all parameters / gradients / moments of the model back to back).

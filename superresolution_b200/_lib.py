@@ -34,6 +34,11 @@ _PROTOS = {
     'srb_pack_conv_weight_dgrad': (_i, [_vp, _vp, _i, _i, _i, _vp]),
     'srb_conv_wgrad_scratch_bytes': (_sz, [_i] * 6),
     'srb_conv_wgrad': (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    'srb_upsample2x_nearest': (_i, [_vp, _i, _vp, _i, _i, _i, _vp]),
+    'srb_conv3x3_cout1': (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    'srb_lrelu_bwd': (_i, [_vp, _i, _vp, _i, _sz, _i, _f, _vp]),
+    'srb_axpby': (_i, [_vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _sz, _i, _vp]),
+    'srb_upsample2x_bwd': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
     'srb_grad_norm_scratch_bytes': (_sz, []),
     'srb_grad_sumsq': (_i, [_vp, _sz, _vp, _vp, _vp]),
     'srb_adamw_step': (_i, [_vp, _vp, _vp, _vp, _sz, _f, _f, _f, _f, _f, _i, _f, _f, _vp, _vp, _vp]),

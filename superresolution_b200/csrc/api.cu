@@ -203,6 +203,28 @@ int srb_conv_wgrad(const void* x, int x_pitch, const void* dy, int dy_pitch, flo
     return conv_wgrad((const bf16*)x, x_pitch, (const bf16*)dy, dy_pitch, dw, db, scratch, B, H, W, Cin, Cout, taps,
                       accumulate, (cudaStream_t)stream);
 }
+int srb_upsample2x_nearest(const void* in, int in_pitch, void* out, int B, int h, int w, void* stream) {
+    if (!in || !out || B <= 0 || h <= 0 || w <= 0 || in_pitch % 8) { set_error("upsample2x_nearest: bad args"); return SRB_E_ARG; }
+    return upsample2x((const bf16*)in, in_pitch, (bf16*)out, B, h, w, (cudaStream_t)stream);
+}
+int srb_conv3x3_cout1(const void* in, int in_pitch, const float* w, const float* bias, float* out, int B, int H, int W,
+                      void* stream) {
+    if (!in || !w || !bias || !out || B <= 0 || in_pitch % 8) { set_error("conv3x3_cout1: bad args"); return SRB_E_ARG; }
+    return conv_cout1((const bf16*)in, in_pitch, w, bias, out, B, H, W, (cudaStream_t)stream);
+}
+int srb_lrelu_bwd(void* g, int g_pitch, const void* y, int y_pitch, size_t npx, int C, float slope, void* stream) {
+    if (!g || !y || npx == 0 || C <= 0) { set_error("lrelu_bwd: bad args"); return SRB_E_ARG; }
+    return lrelu_bwd((bf16*)g, g_pitch, (const bf16*)y, y_pitch, npx, C, slope, (cudaStream_t)stream);
+}
+int srb_axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b,
+              const void* y, int y_f32, int y_pitch, size_t npx, int C, void* stream) {
+    if (!out || !x || npx == 0 || C <= 0) { set_error("axpby: bad args"); return SRB_E_ARG; }
+    return axpby(out, out_f32, out_pitch, a, x, x_f32, x_pitch, b, y, y_f32, y_pitch, npx, C, (cudaStream_t)stream);
+}
+int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int B, int h, int w, int C, void* stream) {
+    if (!g || !out || B <= 0 || h <= 0 || w <= 0) { set_error("upsample2x_bwd: bad args"); return SRB_E_ARG; }
+    return upsample2x_bwd((const bf16*)g, g_pitch, (bf16*)out, out_pitch, B, h, w, C, (cudaStream_t)stream);
+}
 size_t srb_grad_norm_scratch_bytes(void) { return grad_norm_scratch_bytes(); }
 int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream) {
     if (!grad || !info2 || !scratch || n == 0) { set_error("grad_sumsq: bad args"); return SRB_E_ARG; }

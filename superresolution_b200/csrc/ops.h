@@ -66,6 +66,12 @@ size_t conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps
 int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
                int H, int W, int Cin, int Cout, int taps, int accumulate, cudaStream_t s);
 
+// train_ops.cu
+int lrelu_bwd(bf16* g, int g_pitch, const bf16* y, int y_pitch, size_t npx, int C, float slope, cudaStream_t s);
+int axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b, const void* y,
+          int y_f32, int y_pitch, size_t npx, int C, cudaStream_t s);
+int upsample2x_bwd(const bf16* g, int g_pitch, bf16* out, int out_pitch, int B, int h, int w, int C, cudaStream_t s);
+
 // optim.cu
 size_t grad_norm_scratch_bytes();
 int grad_sumsq(const float* g, size_t n, float* info, void* scratch, cudaStream_t s);

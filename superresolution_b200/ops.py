@@ -117,3 +117,54 @@ def conv_wgrad(x, cin, dy, cout, taps, dw=None, db=None, accumulate=False, want_
     L.check(lib.srb_conv_wgrad(L.ptr(x), x.stride(2), L.ptr(dy), dy.stride(2), L.ptr(dw), L.ptr(db), L.ptr(scratch),
                                B, H, W, cin, cout, taps, int(accumulate), L.current_stream()), 'conv_wgrad')
     return dw, db
+
+
+def _npx(t):
+    return t.shape[0] * t.shape[1] * t.shape[2]
+
+
+def lrelu_bwd_(g, y, slope=0.2):
+    """g *= (y > 0 ? 1 : slope) in place; g, y: bf16 NHWC (channel-offset views allowed), y = saved activation output."""
+    L.check(L.lib().srb_lrelu_bwd(L.ptr(g), g.stride(2), L.ptr(y), y.stride(2), _npx(g), g.shape[3], slope,
+                                  L.current_stream()), 'lrelu_bwd')
+    return g
+
+
+def axpby(out, a, x, b=0.0, y=None):
+    """out = a*x + b*y on NHWC tensors / channel slices (bf16 or fp32 each); returns out."""
+    f32 = lambda t: int(t is not None and t.dtype == torch.float32)
+    L.check(L.lib().srb_axpby(L.ptr(out), f32(out), out.stride(2), float(a), L.ptr(x), f32(x), x.stride(2), float(b),
+                              L.ptr(y), f32(y), 0 if y is None else y.stride(2), _npx(out), out.shape[3],
+                              L.current_stream()), 'axpby')
+    return out
+
+
+def upsample2x_bwd(g, out=None):
+    """g: bf16 [B,2h,2w,C] -> bf16 [B,h,w,C], sum over each 2x2 block (backward of nearest 2x upsampling)."""
+    B, H2, W2, C = g.shape
+    if out is None:
+        out = torch.empty(B, H2 // 2, W2 // 2, C, dtype=torch.bfloat16, device=g.device)
+    L.check(L.lib().srb_upsample2x_bwd(L.ptr(g), g.stride(2), L.ptr(out), out.stride(2), B, H2 // 2, W2 // 2, C,
+                                       L.current_stream()), 'upsample2x_bwd')
+    return out
+
+
+def upsample2x_nearest(x, out=None):
+    """bf16 [B,h,w,64] (channel-offset view allowed) -> dense bf16 [B,2h,2w,64], nearest neighbour."""
+    B, h, w, C = x.shape
+    assert C == 64
+    if out is None:
+        out = torch.empty(B, 2 * h, 2 * w, 64, dtype=torch.bfloat16, device=x.device)
+    L.check(L.lib().srb_upsample2x_nearest(L.ptr(x), x.stride(2), L.ptr(out), B, h, w, L.current_stream()),
+            'upsample2x_nearest')
+    return out
+
+
+def conv3x3_cout1(x, w, bias):
+    """bf16 [B,H,W,64] -> fp32 [B,H,W]; w fp32 [1,64,3,3], bias fp32 [1]."""
+    B, H, W, _ = x.shape
+    out = torch.empty(B, H, W, dtype=torch.float32, device=x.device)
+    L.check(L.lib().srb_conv3x3_cout1(L.ptr(x), x.stride(2), L.ptr(w.detach().float().contiguous()),
+                                      L.ptr(bias.detach().float().contiguous()), L.ptr(out), B, H, W,
+                                      L.current_stream()), 'conv3x3_cout1')
+    return out
