@@ -6,9 +6,10 @@
 //                    tcgen05 kernel (conv_tc.cu) on a flipped / transposed weight image -> pack_conv_weight_dgrad.
 //                    Accumulating into a gradient slice of a dense block is the forward epilogue's `+ res1` in place.
 //   weight gradient  dW[co][ci][tap] = sum_px dY[px][co] * X[px + tap][ci]: a GEMM whose contraction runs over pixels, both
-//                    operands channel-contiguous (= "MN-major").  conv_wgrad_kernel: split-K over pixel chunks, 64 x 64
-//                    (co x ci) CTA tiles per tap, mma.sync.m16n8k16 with ldmatrix.trans fragments from XOR-swizzled
-//                    shared memory, fp32 partials + fixed-order reduction (deterministic, no atomics).
+//                    operands channel-contiguous (= "MN-major").  conv_wgrad_kernel: split-K over pixel chunks, one CTA
+//                    tile = (co block x ci block) x all taps from one haloed X tile, mma.sync.m16n8k16 with
+//                    ldmatrix.trans fragments from XOR-swizzled shared memory, fp32 partials + fixed-order
+//                    reduction (deterministic, no atomics).
 //   bias gradient    db[co] = sum_px dY[px][co]: two-level column sum.
 #include <cuda_bf16.h>
 
@@ -51,8 +52,7 @@ __global__ void pack_conv_weight_dgrad_kernel(const float* __restrict__ w, bf16*
 }
 
 constexpr int WG_KC = 32;        // pixels per k-chunk (two m16n8k16 k-steps): one row segment of the image
-constexpr int WG_TILE = 64;      // co x ci tile of a CTA
-constexpr int WG_THREADS = 256;  // 8 warps = 2 (co) x 4 (ci); warp tile 32 x 16
+constexpr int WG_THREADS = 256;  // 8 warps, warp tile 32 (co) x 16 (ci)
 constexpr int WG_STAGES = 3;
 
 struct WgradArgs {
@@ -63,55 +63,75 @@ struct WgradArgs {
     int nchunks, chunks_per_split;
 };
 
-// One k-chunk = WG_KC consecutive pixels of one image row.  Stage layout: dY tile [32 px][64 co], X tile [32 px][64 ci],
-// 128 B per pixel row, 16-byte units XOR-swizzled with (px & 7) so that ldmatrix (8 rows, one unit column) is
-// conflict free.
-__device__ __forceinline__ void wg_load_chunk(const WgradArgs& a, int chunk, int co0, int ci0, int dyo, int dxo,
-                                              uint8_t* s_dy, uint8_t* s_x, int tid) {
+// CTA tile: BM = 32 * WM output channels x BN = 8 * (8 / WM) input channels, ALL taps at once: the dY tile of a k-chunk
+// is loaded once and the haloed X tile (3 rows x 34 pixels) once, the nine taps are nine shifted ldmatrix views of it
+// (per-tap CTAs re-read both operands nine times and were L2-bandwidth bound).  WM = 1 (32 x 64) serves the Cout = 32
+// layers (4 of the 5 convs of every dense block) without multiplying zero rows; WM = 2 (64 x 32) everything else.
+// Warp tile 32 (co) x 8 (ci) x TAPS -> 72 fp32 accumulators per thread.
+template <int WM, int TAPS>
+struct WgTile {
+    static constexpr int BM = 32 * WM, BN = 8 * (8 / WM);
+    static constexpr int UM = BM / 8, UN = BN / 8;  // 16-byte units per pixel row
+    static constexpr int HALO = TAPS == 9 ? 1 : 0;
+    static constexpr int XR = 1 + 2 * HALO, XP = WG_KC + 2 * HALO;  // rows / pixels of the X tile
+    static constexpr int DY_BYTES = WG_KC * BM * 2, X_BYTES = XR * XP * BN * 2;
+    static constexpr int STAGE = (DY_BYTES + X_BYTES + 127) / 128 * 128;
+};
+
+// 16-byte unit swizzle of a [px][units] tile: any 8 consecutive pixels at one logical unit hit 8 different bank groups
+template <int UNITS>
+__device__ __forceinline__ int wg_swz(int px, int u) {
+    if (UNITS == 4) return u ^ ((px >> 1) & 3);  // 64-byte rows: two rows per 128 bytes
+    return u ^ (px & 7);                          // 128-byte rows
+}
+
+// One k-chunk = WG_KC consecutive pixels of one image row: dY tile [32 px][BM co], X tile [XR rows][XP px][BN ci]
+// (zero-filled outside the image / beyond the channel counts).
+template <int WM, int TAPS>
+__device__ __forceinline__ void wg_load_chunk(const WgradArgs& a, int chunk, int co0, int ci0, uint8_t* stage, int tid) {
+    using T = WgTile<WM, TAPS>;
     const int segs = a.W / WG_KC;
     const int row = chunk / segs, x0 = (chunk % segs) * WG_KC;
     const int b = row / a.H, y = row % a.H;
-    // 32 px x 8 units per operand = 256 x 16 B each: one unit per thread and operand
-    const int px = tid >> 3, u = tid & 7;
-    {
+    for (int i = tid; i < WG_KC * T::UM; i += WG_THREADS) {
+        const int px = i / T::UM, u = i % T::UM;
         const bool ok = co0 + u * 8 < a.Cout;
-        const bf16* src = a.dy + (((size_t)b * a.H + y) * a.W + x0 + px) * a.dy_pitch + co0 + u * 8;
-        cp_async16_zfill(s_dy + px * 128 + ((u ^ (px & 7)) << 4), src, ok);
+        const bf16* src = a.dy + (((size_t)b * a.H + y) * a.W + x0 + px) * a.dy_pitch + (ok ? co0 + u * 8 : 0);
+        cp_async16_zfill(stage + (px * T::UM + wg_swz<T::UM>(px, u)) * 16, src, ok);
     }
-    {
-        const int yy = y + dyo, xx = x0 + px + dxo;
+    for (int i = tid; i < T::XR * T::XP * T::UN; i += WG_THREADS) {
+        const int u = i % T::UN, p = (i / T::UN) % T::XP, r = i / (T::UN * T::XP);
+        const int yy = y + r - T::HALO, xx = x0 + p - T::HALO;
         const bool ok = (ci0 + u * 8 < a.Cin) && yy >= 0 && yy < a.H && xx >= 0 && xx < a.W;
-        const bf16* src = a.x + (((size_t)b * a.H + (ok ? yy : 0)) * a.W + (ok ? xx : 0)) * a.x_pitch + ci0 + u * 8;
-        cp_async16_zfill(s_x + px * 128 + ((u ^ (px & 7)) << 4), src, ok);
+        const bf16* src = a.x + (((size_t)b * a.H + (ok ? yy : 0)) * a.W + (ok ? xx : 0)) * a.x_pitch + (ok ? ci0 + u * 8 : 0);
+        cp_async16_zfill(stage + T::DY_BYTES + ((r * T::XP + p) * T::UN + wg_swz<T::UN>(p, u)) * 16, src, ok);
     }
 }
 
+template <int WM, int TAPS>
 __global__ void __launch_bounds__(WG_THREADS)
 conv_wgrad_kernel(const WgradArgs a) {
-    __shared__ __align__(128) uint8_t smem[WG_STAGES][2][WG_KC * 128];
+    using T = WgTile<WM, TAPS>;
+    extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int wm = warp >> 2, wn = warp & 3;  // warp tile: co [32 wm, +32), ci [16 wn, +16)
-    const int nci = (a.Cin + WG_TILE - 1) / WG_TILE;
-    const int tile = blockIdx.x;  // (tap, co block, ci block)
-    const int tap = tile / (nci * ((a.Cout + WG_TILE - 1) / WG_TILE));
-    const int rem = tile % (nci * ((a.Cout + WG_TILE - 1) / WG_TILE));
-    const int co0 = (rem / nci) * WG_TILE, ci0 = (rem % nci) * WG_TILE;
-    const int dyo = a.taps == 9 ? tap / 3 - 1 : 0, dxo = a.taps == 9 ? tap % 3 - 1 : 0;
+    const int wm = warp / (8 / WM), wn = warp % (8 / WM);  // warp tile: co [32 wm, +32), ci [8 wn, +8)
+    const int nci = (a.Cin + T::BN - 1) / T::BN;
+    const int co0 = (blockIdx.x / nci) * T::BM, ci0 = (blockIdx.x % nci) * T::BN;
     const int c_begin = blockIdx.y * a.chunks_per_split;
     const int c_end = min(a.nchunks, c_begin + a.chunks_per_split);
 
-    float acc[2][2][4];
+    float acc[TAPS][2][4];
 #pragma unroll
-    for (int i = 0; i < 2; ++i)
+    for (int t = 0; t < TAPS; ++t)
 #pragma unroll
         for (int j = 0; j < 2; ++j)
 #pragma unroll
-            for (int k = 0; k < 4; ++k) acc[i][j][k] = 0.f;
+            for (int k = 0; k < 4; ++k) acc[t][j][k] = 0.f;
 
     // prologue: WG_STAGES - 1 chunks in flight
 #pragma unroll
     for (int s = 0; s < WG_STAGES - 1; ++s) {
-        if (c_begin + s < c_end) wg_load_chunk(a, c_begin + s, co0, ci0, dyo, dxo, smem[s][0], smem[s][1], tid);
+        if (c_begin + s < c_end) wg_load_chunk<WM, TAPS>(a, c_begin + s, co0, ci0, smem + s * T::STAGE, tid);
         cp_async_commit();
     }
     for (int c = c_begin; c < c_end; ++c) {
@@ -121,50 +141,61 @@ conv_wgrad_kernel(const WgradArgs a) {
         {
             const int cn = c + WG_STAGES - 1;
             const int sn = (cn - c_begin) % WG_STAGES;
-            if (cn < c_end) wg_load_chunk(a, cn, co0, ci0, dyo, dxo, smem[sn][0], smem[sn][1], tid);
+            if (cn < c_end) wg_load_chunk<WM, TAPS>(a, cn, co0, ci0, smem + sn * T::STAGE, tid);
             cp_async_commit();
         }
-        const uint32_t s_dy = smem_u32(smem[st][0]), s_x = smem_u32(smem[st][1]);
+        const uint32_t s_dy = smem_u32(smem + st * T::STAGE), s_x = s_dy + T::DY_BYTES;
+        // A = dY^T [co 16][px 16] per (k-step, m-tile): memory is [px][co] -> ldmatrix.trans; matrices ordered
+        // (co 0-7, px 0-7), (co 8-15, px 0-7), (co 0-7, px 8-15), (co 8-15, px 8-15) = a0..a3.  Shared by all taps.
+        uint32_t af[2][2][4];
 #pragma unroll
-        for (int ks = 0; ks < WG_KC / 16; ++ks) {
-            // A = dY^T [co 16][px 16] per m-tile: memory is [px][co] -> ldmatrix.trans; matrices ordered
-            // (co 0-7, px 0-7), (co 8-15, px 0-7), (co 0-7, px 8-15), (co 8-15, px 8-15) = a0..a3
-            uint32_t af[2][4];
+        for (int ks = 0; ks < 2; ++ks)
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt) {
                 const int px = ks * 16 + (lane & 7) + ((lane >> 4) << 3);
                 const int unit = ((wm * 32 + mt * 16) >> 3) + ((lane >> 3) & 1);
-                ldmatrix_x4_trans(s_dy + px * 128 + ((unit ^ (px & 7)) << 4), af[mt][0], af[mt][1], af[mt][2], af[mt][3]);
+                ldmatrix_x4_trans(s_dy + (px * T::UM + wg_swz<T::UM>(px, unit)) * 16, af[ks][mt][0], af[ks][mt][1],
+                                  af[ks][mt][2], af[ks][mt][3]);
             }
-            // B = X [px 16][ci 8] per n-tile: matrices (px 0-7, ci 0-7), (px 8-15, ci 0-7) = b0, b1 of n-tile 0, then n-tile 1
+#pragma unroll
+        for (int t = 0; t < TAPS; ++t) {
+            // B = X [px 32][ci 8] of tap t: one x4.trans = {b0, b1} of k-step 0 and {b0, b1} of k-step 1 (lane = pixel)
+            const int r = TAPS == 9 ? t / 3 : 0, p = lane + (TAPS == 9 ? t % 3 : 0);
             uint32_t bfr[4];
-            {
-                const int px = ks * 16 + (lane & 7) + (((lane >> 3) & 1) << 3);
-                const int unit = ((wn * 16) >> 3) + (lane >> 4);
-                ldmatrix_x4_trans(s_x + px * 128 + ((unit ^ (px & 7)) << 4), bfr[0], bfr[1], bfr[2], bfr[3]);
+            ldmatrix_x4_trans(s_x + ((r * T::XP + p) * T::UN + wg_swz<T::UN>(p, wn)) * 16, bfr[0], bfr[1], bfr[2], bfr[3]);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                mma_bf16_16816(acc[t][mt], af[0][mt], bfr[0], bfr[1]);
+                mma_bf16_16816(acc[t][mt], af[1][mt], bfr[2], bfr[3]);
             }
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < 2; ++nt)
-                    mma_bf16_16816(acc[mt][nt], af[mt], bfr[2 * nt], bfr[2 * nt + 1]);
         }
     }
     cp_async_wait<0>();
     // partial[split][tap][co][ci]
-    float* dst = a.partial + ((size_t)blockIdx.y * a.taps + tap) * a.Cout * a.Cin;
-    const int g = lane >> 2, t = lane & 3;
+    const int g = lane >> 2, tq = lane & 3;
 #pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
+    for (int t = 0; t < TAPS; ++t) {
+        float* dst = a.partial + ((size_t)blockIdx.y * TAPS + t) * a.Cout * a.Cin;
 #pragma unroll
-        for (int nt = 0; nt < 2; ++nt)
+        for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int co = co0 + wm * 32 + mt * 16 + g + 8 * h;
-                const int ci = ci0 + wn * 16 + nt * 8 + 2 * t;
+                const int ci = ci0 + wn * 8 + 2 * tq;
                 if (co < a.Cout && ci < a.Cin)
-                    *(float2*)(dst + (size_t)co * a.Cin + ci) = make_float2(acc[mt][nt][2 * h], acc[mt][nt][2 * h + 1]);
+                    *(float2*)(dst + (size_t)co * a.Cin + ci) = make_float2(acc[t][mt][2 * h], acc[t][mt][2 * h + 1]);
             }
+    }
+}
+
+template <int WM, int TAPS>
+int launch_wgrad(const WgradArgs& a, int tiles, int ksplit, cudaStream_t s) {
+    using T = WgTile<WM, TAPS>;
+    const int smem = WG_STAGES * T::STAGE;
+    SRB_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<WM, TAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    conv_wgrad_kernel<WM, TAPS><<<dim3(tiles, ksplit), WG_THREADS, smem, s>>>(a);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
 }
 
 // dW[co][ci][tap] (PyTorch layout) = (accumulate ? dW : 0) + sum_split partial[split][tap][co][ci], fixed order
@@ -180,7 +211,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __
     }
 }
 
-constexpr int BG_ROWS = 1024;  // pixels per block of the bias-gradient column sum
+constexpr int BG_ROWS = 256;  // pixels per block of the bias-gradient column sum
 
 // partial[blk][c] = sum over the block's pixels of dy[px][c]  (c < C <= 512, 8 channels per thread)
 __global__ void __launch_bounds__(256)
@@ -214,18 +245,30 @@ bias_grad_partial_kernel(const bf16* __restrict__ dy, int pitch, size_t npx, int
     }
 }
 
-__global__ void bias_grad_final_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ db,
-                                       int accumulate) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+// db[c] = (accumulate ? db[c] : 0) + sum_blk partial[blk][c]; one block per channel, fixed-order tree (deterministic)
+__global__ void __launch_bounds__(128)
+bias_grad_final_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ db, int accumulate) {
+    __shared__ double sh[128];
+    const int c = blockIdx.x;
     double s = 0.0;
-    for (int i = 0; i < nblk; ++i) s += (double)partial[(size_t)i * C + c];
-    db[c] = accumulate ? db[c] + (float)s : (float)s;
+    for (int i = threadIdx.x; i < nblk; i += 128) s += (double)partial[(size_t)i * C + c];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int k = 64; k > 0; k >>= 1) {
+        if (threadIdx.x < k) sh[threadIdx.x] += sh[threadIdx.x + k];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) db[c] = accumulate ? db[c] + (float)sh[0] : (float)sh[0];
+}
+
+int wgrad_tiles(int Cin, int Cout) {
+    const int bm = Cout <= 32 ? 32 : 64, bn = Cout <= 32 ? 64 : 32;
+    return ((Cout + bm - 1) / bm) * ((Cin + bn - 1) / bn);
 }
 
 int wgrad_ksplit(int Cin, int Cout, int taps, int nchunks) {
-    const int tiles = taps * ((Cout + WG_TILE - 1) / WG_TILE) * ((Cin + WG_TILE - 1) / WG_TILE);
-    int ks = (num_sms() * 4 + tiles - 1) / tiles;  // ~4 CTAs per SM (33 KB smem, 256 threads each)
+    const int tiles = wgrad_tiles(Cin, Cout);
+    int ks = (num_sms() * 3 + tiles - 1) / tiles;  // ~3 CTAs per SM (<= 45 KB smem, 256 threads each)
     if (ks > nchunks) ks = nchunks;
     if (ks < 1) ks = 1;
     return ks;
@@ -264,9 +307,11 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
     a.nchunks = B * H * (W / WG_KC);
     const int ksplit = wgrad_ksplit(Cin, Cout, taps, a.nchunks);
     a.chunks_per_split = (a.nchunks + ksplit - 1) / ksplit;
-    const int tiles = taps * ((Cout + WG_TILE - 1) / WG_TILE) * ((Cin + WG_TILE - 1) / WG_TILE);
-    conv_wgrad_kernel<<<dim3(tiles, ksplit), WG_THREADS, 0, s>>>(a);
-    SRB_CUDA(cudaGetLastError());
+    const int tiles = wgrad_tiles(Cin, Cout);
+    int rc;
+    if (taps == 9) rc = Cout <= 32 ? launch_wgrad<1, 9>(a, tiles, ksplit, s) : launch_wgrad<2, 9>(a, tiles, ksplit, s);
+    else rc = Cout <= 32 ? launch_wgrad<1, 1>(a, tiles, ksplit, s) : launch_wgrad<2, 1>(a, tiles, ksplit, s);
+    if (rc != SRB_OK) return rc;
     const int n = taps * Cout * Cin;
     wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(a.partial, dw, ksplit, taps, Cout, Cin, accumulate);
     SRB_CUDA(cudaGetLastError());
@@ -277,7 +322,7 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
         if (256 / (Cout / 8) < 1) { set_error("conv_wgrad: Cout too large for the bias gradient"); return SRB_E_SHAPE; }
         bias_grad_partial_kernel<<<nblk, 256, 0, s>>>(dy, dy_pitch, npx, Cout, bpart);
         SRB_CUDA(cudaGetLastError());
-        bias_grad_final_kernel<<<(Cout + 127) / 128, 128, 0, s>>>(bpart, nblk, Cout, db, accumulate);
+        bias_grad_final_kernel<<<Cout, 128, 0, s>>>(bpart, nblk, Cout, db, accumulate);
         SRB_CUDA(cudaGetLastError());
     }
     return SRB_OK;

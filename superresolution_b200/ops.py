@@ -106,9 +106,11 @@ def conv_wgrad(x, cin, dy, cout, taps, dw=None, db=None, accumulate=False, want_
     B, H, W = x.shape[:3]
     k = 3 if taps == 9 else 1
     if dw is None:
-        dw = torch.zeros((cout, cin, k, k) if taps == 9 else (cout, cin), dtype=torch.float32, device=x.device)
+        assert not accumulate
+        dw = torch.empty((cout, cin, k, k) if taps == 9 else (cout, cin), dtype=torch.float32, device=x.device)
     if db is None and want_bias:
-        db = torch.zeros(cout, dtype=torch.float32, device=x.device)
+        assert not accumulate
+        db = torch.empty(cout, dtype=torch.float32, device=x.device)
     lib = L.lib()
     nbytes = lib.srb_conv_wgrad_scratch_bytes(B, H, W, cin, cout, taps)
     if nbytes == 0:

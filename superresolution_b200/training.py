@@ -44,6 +44,8 @@ def _pad_w(w, cout=None, cin=None):
 
 
 class _RRDBNetFn(torch.autograd.Function):
+    _direct = None  # set by rrdbnet_forward(accumulate_into_grad=True) for the call that follows
+
     @staticmethod
     def forward(ctx, x, *params):
         if x.device.type != 'cuda':
@@ -99,6 +101,8 @@ class _RRDBNetFn(torch.autograd.Function):
         y = ops.conv3x3_cout1(A3, P['conv_last'][0], P['conv_last'][1])  # fp32 [B,4h,4w]
         ctx.saved = (P, u16, D, body_out, U1, A1, U2, A2, A3)
         ctx.geom = (B, h, w)
+        ctx.direct = _RRDBNetFn._direct or {}
+        _RRDBNetFn._direct = None
         return y.unsqueeze(1)
 
     @staticmethod
@@ -110,8 +114,14 @@ class _RRDBNetFn(torch.autograd.Function):
         grads = {}
 
         def wgrad(name, x, cin, dy, cout, keep_out=None, keep_in=None):
+            tgt = ctx.direct.get(name) if not (keep_out or keep_in) else None
+            if tgt is not None:  # accumulate straight into the parameters' .grad buffers (no autograd add kernels)
+                ops.conv_wgrad(x, cin, dy, cout, 9, dw=tgt[0], db=tgt[1], accumulate=True)
+                grads[name] = (None, None)
+                return
             dw, db = ops.conv_wgrad(x, cin, dy, cout, 9)
-            grads[name] = (dw[:keep_out, :keep_in] if (keep_out or keep_in) else dw, db[:keep_out] if keep_out else db)
+            grads[name] = (dw[:keep_out, :keep_in].contiguous() if (keep_out or keep_in) else dw,
+                           db[:keep_out].contiguous() if keep_out else db)
 
         def dgrad(name, dy, cout, out, cin_rows=None, acc=False, pad_out=None):
             """out (+)= conv^T(dy) for the input channels [0, cin_rows) of conv `name`"""
@@ -179,16 +189,24 @@ class _RRDBNetFn(torch.autograd.Function):
         wgrad('conv_first', u16, 16, gf0b, 64, keep_in=4)
         out = [None]
         for n in CONV_NAMES:
-            dw, db = grads[n]
-            out += [dw.contiguous(), db.contiguous()]
+            out += list(grads[n])
         return tuple(out)
 
 
-def rrdbnet_forward(stage1, x):
+def rrdbnet_forward(stage1, x, accumulate_into_grad=False):
     """Differentiable RRDBNet forward on libsrb: x [B,1,H,W] float in [0,1] -> [B,1,2H,2W] fp32.
-    ``stage1``: the ``stage1`` sub-module of ``HybridSuperResolutionModel`` (parameter holder, BasicSR key layout)."""
+    ``stage1``: the ``stage1`` sub-module of ``HybridSuperResolutionModel`` (parameter holder, BasicSR key layout).
+    ``accumulate_into_grad``: the weight-gradient kernels add straight into existing fp32 ``p.grad`` buffers (e.g. the
+    flat-gradient views of ``FusedAdamW``) instead of returning tensors for autograd to add — same result, ~700 fewer
+    element-wise launches per step; parameters without a ``.grad`` buffer take the autograd route."""
     sd = dict(stage1.named_parameters())
     params = []
+    direct = {}
     for n in CONV_NAMES:
-        params += [sd[n + '.weight'], sd[n + '.bias']]
+        w, b = sd[n + '.weight'], sd[n + '.bias']
+        params += [w, b]
+        if accumulate_into_grad and w.grad is not None and b.grad is not None and w.grad.is_contiguous() \
+                and w.grad.dtype == torch.float32 and b.grad.dtype == torch.float32:
+            direct[n] = (w.grad, b.grad)
+    _RRDBNetFn._direct = direct
     return _RRDBNetFn.apply(x, *params)

@@ -107,7 +107,7 @@ def test_rrdbnet_training_step_reduces_loss(cuda):
     losses = []
     for _ in range(6):
         opt.zero_grad()
-        loss, _ = crit(rrdbnet_forward(m.stage1, x), t)
+        loss, _ = crit(rrdbnet_forward(m.stage1, x, accumulate_into_grad=True), t)
         loss.backward()
         opt.step(grad_scale=1.0, max_norm=1.0)
         losses.append(loss.item())
