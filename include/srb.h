@@ -160,6 +160,18 @@ int srb_axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int
               const void* y, int y_f32, int y_pitch, size_t npx, int C, void* stream);
 int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int B, int h, int w, int C, void* stream);
 
+/* HAT (stage 2) backward building blocks — tested operators, not yet assembled into a stage-2 training path:
+ * srb_layernorm96      y = LayerNorm(x)*gamma + beta over 96 channels, eps 1e-5 (nn.LayerNorm of HAT), bf16 [ntok,96]
+ * srb_layernorm96_bwd  dx = LN backward of g (+ res, bf16 or fp32, optional: the shortcut's gradient), dgamma / dbeta
+ *                      (+= when accumulate); deterministic two-level reduction; scratch: srb_layernorm96_bwd_scratch_bytes()
+ * srb_gelu             grad == NULL: out = GELU_erf(pre);  else out = grad * GELU_erf'(pre)  (out may alias grad) */
+size_t srb_layernorm96_bwd_scratch_bytes(void);
+int srb_layernorm96(const void* x, const float* gamma, const float* beta, void* y, size_t ntok, void* stream);
+int srb_layernorm96_bwd(const void* x, const void* g, const float* gamma, const void* res, int res_f32, void* dx,
+                        float* dgamma, float* dbeta, void* scratch, size_t ntok, int accumulate, void* stream);
+int srb_gelu(void* out, int out_pitch, const void* pre, int pre_pitch, const void* grad, int grad_pitch, size_t npx, int C,
+             void* stream);
+
 /* ---- optimizer half of the training step ------------------------------------------------
  * Replaces GradScaler.unscale_ + clip_grad_norm_(1.0) + torch.optim.AdamW.step of scripts/Modello_supporto.py:107,
  * 133-141 on FLAT fp32 buffers (all parameters / gradients / moments of the model back to back).

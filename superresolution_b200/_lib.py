@@ -39,6 +39,10 @@ _PROTOS = {
     'srb_lrelu_bwd': (_i, [_vp, _i, _vp, _i, _sz, _i, _f, _vp]),
     'srb_axpby': (_i, [_vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _sz, _i, _vp]),
     'srb_upsample2x_bwd': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    'srb_layernorm96_bwd_scratch_bytes': (_sz, []),
+    'srb_layernorm96': (_i, [_vp, _vp, _vp, _vp, _sz, _vp]),
+    'srb_layernorm96_bwd': (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _sz, _i, _vp]),
+    'srb_gelu': (_i, [_vp, _i, _vp, _i, _vp, _i, _sz, _i, _vp]),
     'srb_grad_norm_scratch_bytes': (_sz, []),
     'srb_grad_sumsq': (_i, [_vp, _sz, _vp, _vp, _vp]),
     'srb_adamw_step': (_i, [_vp, _vp, _vp, _vp, _sz, _f, _f, _f, _f, _f, _i, _f, _f, _vp, _vp, _vp]),

@@ -225,6 +225,23 @@ int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int
     if (!g || !out || B <= 0 || h <= 0 || w <= 0) { set_error("upsample2x_bwd: bad args"); return SRB_E_ARG; }
     return upsample2x_bwd((const bf16*)g, g_pitch, (bf16*)out, out_pitch, B, h, w, C, (cudaStream_t)stream);
 }
+size_t srb_layernorm96_bwd_scratch_bytes(void) { return layernorm96_bwd_scratch_bytes(); }
+int srb_layernorm96(const void* x, const float* gamma, const float* beta, void* y, size_t ntok, void* stream) {
+    if (!x || !gamma || !beta || !y || ntok == 0) { set_error("layernorm96: bad args"); return SRB_E_ARG; }
+    return layernorm96((const bf16*)x, gamma, beta, (bf16*)y, ntok, (cudaStream_t)stream);
+}
+int srb_layernorm96_bwd(const void* x, const void* g, const float* gamma, const void* res, int res_f32, void* dx,
+                        float* dgamma, float* dbeta, void* scratch, size_t ntok, int accumulate, void* stream) {
+    if (!x || !g || !gamma || !dx || !dgamma || !dbeta || !scratch || ntok == 0) { set_error("layernorm96_bwd: bad args"); return SRB_E_ARG; }
+    return layernorm96_bwd((const bf16*)x, (const bf16*)g, gamma, res, res_f32, (bf16*)dx, dgamma, dbeta, scratch, ntok,
+                           accumulate, (cudaStream_t)stream);
+}
+int srb_gelu(void* out, int out_pitch, const void* pre, int pre_pitch, const void* grad, int grad_pitch, size_t npx, int C,
+             void* stream) {
+    if (!out || !pre || npx == 0 || C <= 0) { set_error("gelu: bad args"); return SRB_E_ARG; }
+    return gelu_fwd_bwd((bf16*)out, out_pitch, (const bf16*)pre, pre_pitch, (const bf16*)grad, grad_pitch, npx, C,
+                        (cudaStream_t)stream);
+}
 size_t srb_grad_norm_scratch_bytes(void) { return grad_norm_scratch_bytes(); }
 int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream) {
     if (!grad || !info2 || !scratch || n == 0) { set_error("grad_sumsq: bad args"); return SRB_E_ARG; }

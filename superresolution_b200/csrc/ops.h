@@ -72,6 +72,12 @@ int axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f
           int y_f32, int y_pitch, size_t npx, int C, cudaStream_t s);
 int upsample2x_bwd(const bf16* g, int g_pitch, bf16* out, int out_pitch, int B, int h, int w, int C, cudaStream_t s);
 
+size_t layernorm96_bwd_scratch_bytes();
+int layernorm96_bwd(const bf16* x, const bf16* g, const float* gamma, const void* res, int res_f32, bf16* dx,
+                    float* dgamma, float* dbeta, void* scratch, size_t ntok, int accumulate, cudaStream_t s);
+int gelu_fwd_bwd(bf16* out, int out_pitch, const bf16* pre, int pre_pitch, const bf16* g, int g_pitch, size_t npx, int C,
+                 cudaStream_t s);
+
 // optim.cu
 size_t grad_norm_scratch_bytes();
 int grad_sumsq(const float* g, size_t n, float* info, void* scratch, cudaStream_t s);

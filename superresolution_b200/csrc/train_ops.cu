@@ -149,3 +149,195 @@ int upsample2x_bwd(const bf16* g, int g_pitch, bf16* out, int out_pitch, int B, 
 }
 
 }  // namespace srb
+
+// ---------------------------------------------------------------------------------------------------------------
+// HAT building blocks (stage-2 backward, not yet assembled): LayerNorm(96) backward and exact-erf GELU forward/backward
+// ---------------------------------------------------------------------------------------------------------------
+namespace srb {
+
+namespace {
+
+__device__ __forceinline__ float half16_sum(float v) {  // sum over the 16 lanes of a half-warp
+    const unsigned m = 0xffffu << (threadIdx.x & 16);
+    v += __shfl_xor_sync(m, v, 8);
+    v += __shfl_xor_sync(m, v, 4);
+    v += __shfl_xor_sync(m, v, 2);
+    v += __shfl_xor_sync(m, v, 1);
+    return v;
+}
+
+constexpr int LNB_BLOCKS = 148 * 4;
+
+// y = LayerNorm(x) * gamma + beta over 96 channels (eps 1e-5, biased variance), g = dL/dy:
+//   dx = (g*gamma - mean(g*gamma) - xhat * mean(g*gamma*xhat)) * rstd (+ res),  dgamma = sum_tok g*xhat,  dbeta = sum_tok g
+// 16 lanes per token (12 active, 8 channels each).  partial[blk][2][96]: per-block sums of dgamma / dbeta.
+__global__ void __launch_bounds__(256)
+layernorm96_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ g, const float* __restrict__ gamma,
+                       const void* __restrict__ res, int res_f32, bf16* __restrict__ dx, size_t ntok,
+                       float* __restrict__ partial) {
+    __shared__ float red[16][2][96];
+    const int sub = threadIdx.x & 15, grp = threadIdx.x >> 4;
+    const bool act = sub < 12;
+    const int c0 = (act ? sub : 0) * 8;
+    float gam[8], dg[8], db[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { gam[j] = __ldg(gamma + c0 + j); dg[j] = 0.f; db[j] = 0.f; }
+    const size_t stride = ((size_t)gridDim.x * blockDim.x) >> 4;
+    for (size_t tok = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 4; tok < ntok; tok += stride) {
+        float xv[8], gv[8];
+        {
+            const uint4 xr = __ldg((const uint4*)(x + tok * 96 + c0)), gr = __ldg((const uint4*)(g + tok * 96 + c0));
+            const __nv_bfloat162* xh = (const __nv_bfloat162*)&xr;
+            const __nv_bfloat162* gh = (const __nv_bfloat162*)&gr;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 a = __bfloat1622float2(xh[k]), b = __bfloat1622float2(gh[k]);
+                xv[2 * k] = a.x; xv[2 * k + 1] = a.y; gv[2 * k] = b.x; gv[2 * k + 1] = b.y;
+            }
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += xv[j];
+        const float mean = half16_sum(act ? s : 0.f) * (1.f / 96.f);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) q += (xv[j] - mean) * (xv[j] - mean);
+        const float rstd = rsqrtf(half16_sum(act ? q : 0.f) * (1.f / 96.f) + 1e-5f);
+        float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            xv[j] = (xv[j] - mean) * rstd;  // xhat
+            const float gg = gv[j] * gam[j];
+            m1 += gg;
+            m2 = fmaf(gg, xv[j], m2);
+            dg[j] = fmaf(gv[j], xv[j], dg[j]);
+            db[j] += gv[j];
+        }
+        m1 = half16_sum(act ? m1 : 0.f) * (1.f / 96.f);
+        m2 = half16_sum(act ? m2 : 0.f) * (1.f / 96.f);
+        if (act) {
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = (gv[j] * gam[j] - m1 - xv[j] * m2) * rstd;
+            if (res) {
+                if (res_f32) {
+                    const float4 r0 = *(const float4*)((const float*)res + tok * 96 + c0);
+                    const float4 r1 = *(const float4*)((const float*)res + tok * 96 + c0 + 4);
+                    o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w; o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+                } else {
+                    const uint4 rr = *(const uint4*)((const bf16*)res + tok * 96 + c0);
+                    const __nv_bfloat162* rh = (const __nv_bfloat162*)&rr;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float2 f = __bfloat1622float2(rh[k]);
+                        o[2 * k] += f.x; o[2 * k + 1] += f.y;
+                    }
+                }
+            }
+            uint4 ov;
+            __nv_bfloat162* oh = (__nv_bfloat162*)&ov;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) oh[k] = __floats2bfloat162_rn(o[2 * k], o[2 * k + 1]);
+            *(uint4*)(dx + tok * 96 + c0) = ov;
+        }
+    }
+    if (act) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { red[grp][0][c0 + j] = dg[j]; red[grp][1][c0 + j] = db[j]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 192) {
+        const int w = threadIdx.x / 96, c = threadIdx.x % 96;
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) s += red[k][w][c];
+        partial[((size_t)blockIdx.x * 2 + w) * 96 + c] = s;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+layernorm96_bwd_final_kernel(const float* __restrict__ partial, int nblk, float* __restrict__ dgamma,
+                             float* __restrict__ dbeta, int accumulate) {
+    __shared__ double sh[128];
+    const int w = blockIdx.x / 96, c = blockIdx.x % 96;
+    double s = 0.0;
+    for (int i = threadIdx.x; i < nblk; i += 128) s += (double)partial[((size_t)i * 2 + w) * 96 + c];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int k = 64; k > 0; k >>= 1) {
+        if (threadIdx.x < k) sh[threadIdx.x] += sh[threadIdx.x + k];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        float* o = (w == 0 ? dgamma : dbeta) + c;
+        *o = accumulate ? *o + (float)sh[0] : (float)sh[0];
+    }
+}
+
+__device__ __forceinline__ float gelu_exact(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_exact_grad(float x) {
+    return 0.5f * (1.f + erff(x * 0.70710678118654752f)) + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+}
+
+// mode 0: out = GELU(pre)      mode 1: out = g * GELU'(pre)   (out may alias g); [npx][C] slices with channel pitches
+__global__ void __launch_bounds__(256)
+gelu_kernel(bf16* __restrict__ out, int out_pitch, const bf16* __restrict__ pre, int pre_pitch, const bf16* g, int g_pitch,
+            size_t npx, int C, int mode) {
+    const int cg = C >> 3;
+    const size_t n = npx * cg;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t px = i / cg;
+        const int c = (int)(i - px * cg) * 8;
+        const uint4 pv = __ldg((const uint4*)(pre + px * pre_pitch + c));
+        uint4 gv = make_uint4(0, 0, 0, 0);
+        if (mode) gv = *(const uint4*)(g + px * g_pitch + c);
+        const __nv_bfloat162* ph = (const __nv_bfloat162*)&pv;
+        const __nv_bfloat162* gh = (const __nv_bfloat162*)&gv;
+        uint4 ov;
+        __nv_bfloat162* oh = (__nv_bfloat162*)&ov;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float2 p = __bfloat1622float2(ph[k]);
+            if (mode) {
+                const float2 gg = __bfloat1622float2(gh[k]);
+                oh[k] = __floats2bfloat162_rn(gg.x * gelu_exact_grad(p.x), gg.y * gelu_exact_grad(p.y));
+            } else {
+                oh[k] = __floats2bfloat162_rn(gelu_exact(p.x), gelu_exact(p.y));
+            }
+        }
+        *(uint4*)(out + px * out_pitch + c) = ov;
+    }
+}
+
+}  // namespace
+
+size_t layernorm96_bwd_scratch_bytes() { return (size_t)LNB_BLOCKS * 2 * 96 * sizeof(float); }
+
+int layernorm96_bwd(const bf16* x, const bf16* g, const float* gamma, const void* res, int res_f32, bf16* dx,
+                    float* dgamma, float* dbeta, void* scratch, size_t ntok, int accumulate, cudaStream_t s) {
+    if ((((uintptr_t)x | (uintptr_t)g | (uintptr_t)dx | (uintptr_t)res) & 15)) {
+        set_error("layernorm96_bwd: pointers must be 16-byte aligned");
+        return SRB_E_ARG;
+    }
+    size_t want = (ntok * 16 + 255) / 256;
+    const int grid = (int)(want < 1 ? 1 : (want > LNB_BLOCKS ? LNB_BLOCKS : want));
+    layernorm96_bwd_kernel<<<grid, 256, 0, s>>>(x, g, gamma, res, res_f32, dx, ntok, (float*)scratch);
+    SRB_CUDA(cudaGetLastError());
+    layernorm96_bwd_final_kernel<<<192, 128, 0, s>>>((const float*)scratch, grid, dgamma, dbeta, accumulate);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int gelu_fwd_bwd(bf16* out, int out_pitch, const bf16* pre, int pre_pitch, const bf16* g, int g_pitch, size_t npx, int C,
+                 cudaStream_t s) {
+    if (C % 8 || out_pitch % 8 || pre_pitch % 8 || (g && g_pitch % 8) ||
+        (((uintptr_t)out | (uintptr_t)pre | (uintptr_t)g) & 15)) {
+        set_error("gelu: C and pitches must be multiples of 8, pointers 16-byte aligned");
+        return SRB_E_ARG;
+    }
+    gelu_kernel<<<grid_for(npx * (C / 8)), 256, 0, s>>>(out, out_pitch, pre, pre_pitch, g, g_pitch, npx, C, g ? 1 : 0);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+}  // namespace srb

@@ -170,3 +170,36 @@ def conv3x3_cout1(x, w, bias):
                                       L.ptr(bias.detach().float().contiguous()), L.ptr(out), B, H, W,
                                       L.current_stream()), 'conv3x3_cout1')
     return out
+
+
+def layernorm96(x, gamma, beta):
+    """bf16 [ntok,96] -> bf16 [ntok,96], LayerNorm over the 96 channels (eps 1e-5)."""
+    y = torch.empty_like(x)
+    L.check(L.lib().srb_layernorm96(L.ptr(x), L.ptr(gamma), L.ptr(beta), L.ptr(y), x.shape[0], L.current_stream()),
+            'layernorm96')
+    return y
+
+
+def layernorm96_bwd(x, g, gamma, res=None):
+    """x, g: bf16 [ntok,96] (LN input, gradient of the LN output).  Returns (dx bf16 (+ res), dgamma fp32, dbeta fp32)."""
+    dx = torch.empty_like(x)
+    dg = torch.empty(96, dtype=torch.float32, device=x.device)
+    db = torch.empty(96, dtype=torch.float32, device=x.device)
+    lib = L.lib()
+    scratch = torch.empty(lib.srb_layernorm96_bwd_scratch_bytes(), dtype=torch.uint8, device=x.device)
+    L.check(lib.srb_layernorm96_bwd(L.ptr(x), L.ptr(g), L.ptr(gamma), L.ptr(res),
+                                    int(res is not None and res.dtype == torch.float32), L.ptr(dx), L.ptr(dg), L.ptr(db),
+                                    L.ptr(scratch), x.shape[0], 0, L.current_stream()), 'layernorm96_bwd')
+    return dx, dg, db
+
+
+def gelu(pre, grad=None, out=None):
+    """pre: bf16 [...,C] (last-dim-contiguous 2-D / NHWC slice).  grad None: GELU(pre); else grad * GELU'(pre)."""
+    p2 = pre.reshape(-1, pre.shape[-1]) if pre.is_contiguous() else pre
+    npx = pre.numel() // pre.shape[-1]
+    if out is None:
+        out = torch.empty(pre.shape, dtype=torch.bfloat16, device=pre.device)
+    pitch = lambda t: t.stride(-2)
+    L.check(L.lib().srb_gelu(L.ptr(out), pitch(out), L.ptr(pre), pitch(pre), L.ptr(grad),
+                             0 if grad is None else pitch(grad), npx, pre.shape[-1], L.current_stream()), 'gelu')
+    return out
