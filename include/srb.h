@@ -165,6 +165,14 @@ int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int
  * srb_layernorm96_bwd  dx = LN backward of g (+ res, bf16 or fp32, optional: the shortcut's gradient), dgamma / dbeta
  *                      (+= when accumulate); deterministic two-level reduction; scratch: srb_layernorm96_bwd_scratch_bytes()
  * srb_gelu             grad == NULL: out = GELU_erf(pre);  else out = grad * GELU_erf'(pre)  (out may alias grad) */
+/* srb_window_attention      (S)W-MSA core of HAB from a saved qkv tensor (bf16 [B,H,W,288] = q|k|v, 6 heads x 16):
+ *                           out[B,H,W,96] = softmax(q k^T / 4 + bias[h] (+ shift mask)) v per 8x8 window; shift 0 or 4;
+ *                           bias fp32 [6][64][64] = relative_position_bias_table gathered through the index buffer.
+ * srb_window_attention_bwd  dqkv[B,H,W,288] from dout[B,H,W,96] (P recomputed) and dtable[225][6] += gradient of the
+ *                           relative position bias TABLE (index: int32 [64][64]; atomicAdd: zero it first). */
+int srb_window_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, int shift, void* stream);
+int srb_window_attention_bwd(const void* qkv, const float* bias, const int* index, const void* dout, void* dqkv,
+                             float* dtable, int B, int H, int W, int shift, void* stream);
 size_t srb_layernorm96_bwd_scratch_bytes(void);
 int srb_layernorm96(const void* x, const float* gamma, const float* beta, void* y, size_t ntok, void* stream);
 int srb_layernorm96_bwd(const void* x, const void* g, const float* gamma, const void* res, int res_f32, void* dx,

@@ -242,6 +242,16 @@ int srb_gelu(void* out, int out_pitch, const void* pre, int pre_pitch, const voi
     return gelu_fwd_bwd((bf16*)out, out_pitch, (const bf16*)pre, pre_pitch, (const bf16*)grad, grad_pitch, npx, C,
                         (cudaStream_t)stream);
 }
+int srb_window_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, int shift, void* stream) {
+    if (!qkv || !bias || !out) { set_error("window_attention: bad args"); return SRB_E_ARG; }
+    return win_attn_fwd((const bf16*)qkv, bias, (bf16*)out, B, H, W, shift, (cudaStream_t)stream);
+}
+int srb_window_attention_bwd(const void* qkv, const float* bias, const int* index, const void* dout, void* dqkv,
+                             float* dtable, int B, int H, int W, int shift, void* stream) {
+    if (!qkv || !bias || !index || !dout || !dqkv || !dtable) { set_error("window_attention_bwd: bad args"); return SRB_E_ARG; }
+    return win_attn_bwd((const bf16*)qkv, bias, index, (const bf16*)dout, (bf16*)dqkv, dtable, B, H, W, shift,
+                        (cudaStream_t)stream);
+}
 size_t srb_grad_norm_scratch_bytes(void) { return grad_norm_scratch_bytes(); }
 int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream) {
     if (!grad || !info2 || !scratch || n == 0) { set_error("grad_sumsq: bad args"); return SRB_E_ARG; }

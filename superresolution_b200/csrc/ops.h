@@ -78,6 +78,11 @@ int layernorm96_bwd(const bf16* x, const bf16* g, const float* gamma, const void
 int gelu_fwd_bwd(bf16* out, int out_pitch, const bf16* pre, int pre_pitch, const bf16* g, int g_pitch, size_t npx, int C,
                  cudaStream_t s);
 
+// win_attn.cu
+int win_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, int W, int shift, cudaStream_t s);
+int win_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf16* dout, bf16* dqkv, float* dtable, int B,
+                 int H, int W, int shift, cudaStream_t s);
+
 // optim.cu
 size_t grad_norm_scratch_bytes();
 int grad_sumsq(const float* g, size_t n, float* info, void* scratch, cudaStream_t s);

@@ -203,3 +203,29 @@ def gelu(pre, grad=None, out=None):
     L.check(L.lib().srb_gelu(L.ptr(out), pitch(out), L.ptr(pre), pitch(pre), L.ptr(grad),
                              0 if grad is None else pitch(grad), npx, pre.shape[-1], L.current_stream()), 'gelu')
     return out
+
+
+def gather_rel_bias(table, index):
+    """relative_position_bias_table fp32 [225,6] + relative_position_index int64 [64,64] -> fp32 [6,64,64] (a gather)."""
+    return table.detach().float()[index.view(-1)].view(64, 64, 6).permute(2, 0, 1).contiguous()
+
+
+def window_attention(qkv, bias, shift):
+    """qkv bf16 [B,H,W,288], bias fp32 [6,64,64] -> bf16 [B,H,W,96] (attention output before proj)."""
+    B, H, W, _ = qkv.shape
+    out = torch.empty(B, H, W, 96, dtype=torch.bfloat16, device=qkv.device)
+    L.check(L.lib().srb_window_attention(L.ptr(qkv), L.ptr(bias), L.ptr(out), B, H, W, shift, L.current_stream()),
+            'window_attention')
+    return out
+
+
+def window_attention_bwd(qkv, bias, index, dout, shift, dtable=None):
+    """Returns (dqkv bf16 [B,H,W,288], dtable fp32 [225,6]); dtable is accumulated into when given."""
+    B, H, W, _ = qkv.shape
+    dqkv = torch.empty_like(qkv)
+    if dtable is None:
+        dtable = torch.zeros(225, 6, dtype=torch.float32, device=qkv.device)
+    idx = index.to(torch.int32).contiguous()
+    L.check(L.lib().srb_window_attention_bwd(L.ptr(qkv), L.ptr(bias), L.ptr(idx), L.ptr(dout), L.ptr(dqkv), L.ptr(dtable),
+                                             B, H, W, shift, L.current_stream()), 'window_attention_bwd')
+    return dqkv, dtable

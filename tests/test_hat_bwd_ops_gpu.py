@@ -53,3 +53,51 @@ def test_gelu_forward_backward(cuda):
     assert (err <= 1e-2 * pr.grad.abs() + 1e-2).all(), err.max().item()
     ops.gelu(pre, grad=gy, out=gy)  # in place on the gradient
     assert torch.equal(gy, d)
+
+
+def _ref_window_attention(qkv, table, index, shift):
+    """torch restatement of HAB's attention core (upstream hat_arch.py: roll, window_partition, WindowAttention without the
+    qkv / proj linears, window_reverse, roll back) on fp32 tensors; differentiable."""
+    B, H, W, _ = qkv.shape
+    x = torch.roll(qkv, (-shift, -shift), (1, 2)) if shift else qkv
+    xw = x.view(B, H // 8, 8, W // 8, 8, 288).permute(0, 1, 3, 2, 4, 5).reshape(-1, 64, 3, 6, 16).permute(2, 0, 3, 1, 4)
+    q, k, v = xw[0] * 0.25, xw[1], xw[2]                       # [nW, 6, 64, 16]
+    attn = q @ k.transpose(-2, -1) + table[index.view(-1)].view(64, 64, 6).permute(2, 0, 1).unsqueeze(0)
+    if shift:
+        img = torch.zeros(H, W, device=qkv.device)
+        cnt = 0
+        for hs in (slice(0, -8), slice(-8, -4), slice(-4, None)):
+            for ws in (slice(0, -8), slice(-8, -4), slice(-4, None)):
+                img[hs, ws] = cnt
+                cnt += 1
+        mw = img.view(H // 8, 8, W // 8, 8).permute(0, 2, 1, 3).reshape(-1, 64)
+        mask = (mw.unsqueeze(1) - mw.unsqueeze(2)).ne(0).float() * -100.0   # [nW_img, 64, 64]
+        attn = attn.view(B, -1, 6, 64, 64) + mask.view(1, -1, 1, 64, 64)
+        attn = attn.view(-1, 6, 64, 64)
+    o = (attn.softmax(-1) @ v).transpose(1, 2).reshape(-1, 8, 8, 96)
+    o = o.view(B, H // 8, W // 8, 8, 8, 96).permute(0, 1, 3, 2, 4, 5).reshape(B, H, W, 96)
+    return torch.roll(o, (shift, shift), (1, 2)) if shift else o
+
+
+@pytest.mark.parametrize('B,H,W,shift', [(1, 16, 16, 0), (2, 16, 32, 4), (1, 32, 24, 4), (3, 24, 16, 0)])
+def test_window_attention_forward_backward(cuda, B, H, W, shift):
+    from superresolution_b200 import ops
+    g = torch.Generator().manual_seed(B * 1000 + H + shift)
+    qkv = (torch.randn(B, H, W, 288, generator=g) * 1.2).to(cuda).bfloat16()
+    table = (torch.randn(225, 6, generator=g) * 0.5).to(cuda)
+    coords = torch.stack(torch.meshgrid(torch.arange(8), torch.arange(8), indexing='ij')).flatten(1)
+    rel = (coords[:, :, None] - coords[:, None, :]).permute(1, 2, 0) + 7
+    index = (rel[..., 0] * 15 + rel[..., 1]).to(cuda)          # relative_position_index of an 8x8 window
+    dout = torch.randn(B, H, W, 96, generator=g).to(cuda).bfloat16()
+    qr = qkv.float().requires_grad_(True)
+    tr = table.clone().requires_grad_(True)
+    ref = _ref_window_attention(qr, tr, index, shift)
+    ref.backward(dout.float())
+    bias = ops.gather_rel_bias(table, index)
+    out = ops.window_attention(qkv, bias, shift)
+    err = (out.float() - ref.detach()).abs()
+    assert (err <= 1e-2 * ref.detach().abs() + 2e-2).all(), err.max().item()
+    dqkv, dtab = ops.window_attention_bwd(qkv, bias, index, dout, shift)
+    err = (dqkv.float() - qr.grad).abs()
+    assert (err <= 2e-2 * qr.grad.abs() + 3e-2).all(), err.max().item()
+    assert (dtab - tr.grad).abs().max().item() <= 2e-2 * tr.grad.abs().max().item() + 1e-2
