@@ -173,6 +173,16 @@ int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int
 int srb_window_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, int shift, void* stream);
 int srb_window_attention_bwd(const void* qkv, const float* bias, const int* index, const void* dout, void* dqkv,
                              float* dtable, int B, int H, int W, int shift, void* stream);
+/* srb_channel_attention      ChannelAttention of CAB: out = y * sigmoid(W2 relu(W1 mean_px(y) + b1) + b2), y bf16 [B,HW,96],
+ *                            w1 fp32 [3,96], w2 fp32 [96,3]; saves pooled [B,96], hid [B,3], scale [B,96] for the backward.
+ * srb_channel_attention_bwd  dy (direct + pooled term) and dw1/db1/dw2/db2 (+= when accumulate); dpooled [B,96] scratch out.
+ *                            scratch: srb_channel_attention_scratch_bytes(B, HW).  Deterministic. */
+size_t srb_channel_attention_scratch_bytes(int B, int HW);
+int srb_channel_attention(const void* y, const float* w1, const float* b1, const float* w2, const float* b2, void* out,
+                          float* pooled, float* hid, float* scale, void* scratch, int B, int HW, void* stream);
+int srb_channel_attention_bwd(const void* y, const void* g, const float* w1, const float* w2, const float* pooled,
+                              const float* hid, const float* scale, void* dy, float* dw1, float* db1, float* dw2,
+                              float* db2, float* dpooled, void* scratch, int B, int HW, int accumulate, void* stream);
 size_t srb_layernorm96_bwd_scratch_bytes(void);
 int srb_layernorm96(const void* x, const float* gamma, const float* beta, void* y, size_t ntok, void* stream);
 int srb_layernorm96_bwd(const void* x, const void* g, const float* gamma, const void* res, int res_f32, void* dx,

@@ -252,6 +252,26 @@ int srb_window_attention_bwd(const void* qkv, const float* bias, const int* inde
     return win_attn_bwd((const bf16*)qkv, bias, index, (const bf16*)dout, (bf16*)dqkv, dtable, B, H, W, shift,
                         (cudaStream_t)stream);
 }
+size_t srb_channel_attention_scratch_bytes(int B, int HW) { return chan_attn_scratch_bytes(B, HW); }
+int srb_channel_attention(const void* y, const float* w1, const float* b1, const float* w2, const float* b2, void* out,
+                          float* pooled, float* hid, float* scale, void* scratch, int B, int HW, void* stream) {
+    if (!y || !w1 || !b1 || !w2 || !b2 || !out || !pooled || !hid || !scale || !scratch || B <= 0 || HW <= 0) {
+        set_error("channel_attention: bad args");
+        return SRB_E_ARG;
+    }
+    return chan_attn_fwd((const bf16*)y, w1, b1, w2, b2, (bf16*)out, pooled, hid, scale, scratch, B, HW, (cudaStream_t)stream);
+}
+int srb_channel_attention_bwd(const void* y, const void* g, const float* w1, const float* w2, const float* pooled,
+                              const float* hid, const float* scale, void* dy, float* dw1, float* db1, float* dw2,
+                              float* db2, float* dpooled, void* scratch, int B, int HW, int accumulate, void* stream) {
+    if (!y || !g || !w1 || !w2 || !pooled || !hid || !scale || !dy || !dw1 || !db1 || !dw2 || !db2 || !dpooled ||
+        !scratch || B <= 0 || HW <= 0) {
+        set_error("channel_attention_bwd: bad args");
+        return SRB_E_ARG;
+    }
+    return chan_attn_bwd((const bf16*)y, (const bf16*)g, w1, w2, pooled, hid, scale, (bf16*)dy, dw1, db1, dw2, db2, dpooled,
+                         scratch, B, HW, accumulate, (cudaStream_t)stream);
+}
 size_t srb_grad_norm_scratch_bytes(void) { return grad_norm_scratch_bytes(); }
 int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream) {
     if (!grad || !info2 || !scratch || n == 0) { set_error("grad_sumsq: bad args"); return SRB_E_ARG; }

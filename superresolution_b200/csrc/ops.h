@@ -83,6 +83,14 @@ int win_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, in
 int win_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf16* dout, bf16* dqkv, float* dtable, int B,
                  int H, int W, int shift, cudaStream_t s);
 
+// chan_attn.cu
+size_t chan_attn_scratch_bytes(int B, int HW);
+int chan_attn_fwd(const bf16* y, const float* w1, const float* b1, const float* w2, const float* b2, bf16* out,
+                  float* pooled, float* hid, float* s, void* scratch, int B, int HW, cudaStream_t st);
+int chan_attn_bwd(const bf16* y, const bf16* g, const float* w1, const float* w2, const float* pooled, const float* hid,
+                  const float* s, bf16* dy, float* dw1, float* db1, float* dw2, float* db2, float* dpooled,
+                  void* scratch, int B, int HW, int accumulate, cudaStream_t st);
+
 // optim.cu
 size_t grad_norm_scratch_bytes();
 int grad_sumsq(const float* g, size_t n, float* info, void* scratch, cudaStream_t s);

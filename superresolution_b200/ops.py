@@ -229,3 +229,38 @@ def window_attention_bwd(qkv, bias, index, dout, shift, dtable=None):
     L.check(L.lib().srb_window_attention_bwd(L.ptr(qkv), L.ptr(bias), L.ptr(idx), L.ptr(dout), L.ptr(dqkv), L.ptr(dtable),
                                              B, H, W, shift, L.current_stream()), 'window_attention_bwd')
     return dqkv, dtable
+
+
+def channel_attention(y, w1, b1, w2, b2):
+    """y bf16 [B,HW,96]; w1 [3,96(,1,1)], w2 [96,3(,1,1)] fp32.  Returns (out bf16, saved = (pooled, hid, scale))."""
+    B, HW, _ = y.shape
+    dev = y.device
+    out = torch.empty_like(y)
+    pooled = torch.empty(B, 96, dtype=torch.float32, device=dev)
+    hid = torch.empty(B, 3, dtype=torch.float32, device=dev)
+    scale = torch.empty(B, 96, dtype=torch.float32, device=dev)
+    lib = L.lib()
+    scratch = torch.empty(lib.srb_channel_attention_scratch_bytes(B, HW), dtype=torch.uint8, device=dev)
+    f = lambda t: t.detach().float().contiguous()
+    L.check(lib.srb_channel_attention(L.ptr(y), L.ptr(f(w1)), L.ptr(f(b1)), L.ptr(f(w2)), L.ptr(f(b2)), L.ptr(out),
+                                      L.ptr(pooled), L.ptr(hid), L.ptr(scale), L.ptr(scratch), B, HW,
+                                      L.current_stream()), 'channel_attention')
+    return out, (pooled, hid, scale)
+
+
+def channel_attention_bwd(y, g, w1, w2, saved):
+    """Returns (dy bf16 [B,HW,96], dw1 [3,96], db1 [3], dw2 [96,3], db2 [96])."""
+    B, HW, _ = y.shape
+    dev = y.device
+    pooled, hid, scale = saved
+    dy = torch.empty_like(y)
+    mk = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+    dw1, db1, dw2, db2, dpooled = mk(3, 96), mk(3), mk(96, 3), mk(96), mk(B, 96)
+    lib = L.lib()
+    scratch = torch.empty(lib.srb_channel_attention_scratch_bytes(B, HW), dtype=torch.uint8, device=dev)
+    f = lambda t: t.detach().float().contiguous()
+    L.check(lib.srb_channel_attention_bwd(L.ptr(y), L.ptr(g), L.ptr(f(w1)), L.ptr(f(w2)), L.ptr(pooled), L.ptr(hid),
+                                          L.ptr(scale), L.ptr(dy), L.ptr(dw1), L.ptr(db1), L.ptr(dw2), L.ptr(db2),
+                                          L.ptr(dpooled), L.ptr(scratch), B, HW, 0, L.current_stream()),
+            'channel_attention_bwd')
+    return dy, dw1, db1, dw2, db2

@@ -101,3 +101,29 @@ def test_window_attention_forward_backward(cuda, B, H, W, shift):
     err = (dqkv.float() - qr.grad).abs()
     assert (err <= 2e-2 * qr.grad.abs() + 3e-2).all(), err.max().item()
     assert (dtab - tr.grad).abs().max().item() <= 2e-2 * tr.grad.abs().max().item() + 1e-2
+
+
+@pytest.mark.parametrize('B,HW', [(1, 256), (3, 32 * 40), (2, 64 * 64 + 64)])
+def test_channel_attention_forward_backward(cuda, B, HW):
+    from superresolution_b200 import ops
+    g = torch.Generator().manual_seed(B * 7 + HW)
+    y = (torch.randn(B, HW, 96, generator=g) + 0.3).to(cuda).bfloat16()
+    gy = torch.randn(B, HW, 96, generator=g).to(cuda).bfloat16()
+    w1 = (torch.randn(3, 96, generator=g) * 0.3).to(cuda)
+    b1 = (torch.randn(3, generator=g) * 0.3 + 0.2).to(cuda)
+    w2 = (torch.randn(96, 3, generator=g) * 0.5).to(cuda)
+    b2 = (torch.randn(96, generator=g) * 0.3).to(cuda)
+    yr = y.float().requires_grad_(True)
+    P = [t.clone().requires_grad_(True) for t in (w1, b1, w2, b2)]
+    pooled = yr.mean(1)
+    sc = torch.sigmoid(torch.relu(pooled @ P[0].t() + P[1]) @ P[2].t() + P[3])
+    ref = yr * sc.unsqueeze(1)
+    ref.backward(gy.float())
+    out, saved = ops.channel_attention(y, w1, b1, w2, b2)
+    err = (out.float() - ref.detach()).abs()
+    assert (err <= 1e-2 * ref.detach().abs() + 1e-2).all(), err.max().item()
+    dy, dw1, db1, dw2, db2 = ops.channel_attention_bwd(y, gy, w1, w2, saved)
+    err = (dy.float() - yr.grad).abs()
+    assert (err <= 1e-2 * yr.grad.abs() + 1e-2).all(), err.max().item()
+    for got, want in ((dw1, P[0].grad), (db1, P[1].grad), (dw2, P[2].grad), (db2, P[3].grad)):
+        assert (got - want).abs().max().item() <= 1e-2 * want.abs().max().item() + 1e-3, (got - want).abs().max().item()
