@@ -173,6 +173,16 @@ int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int
 int srb_window_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, int shift, void* stream);
 int srb_window_attention_bwd(const void* qkv, const float* bias, const int* index, const void* dout, void* dqkv,
                              float* dtable, int B, int H, int W, int shift, void* stream);
+/* srb_overlap_attention      OCAB attention core from a saved qkv tensor (bf16 [B,H,W,288]): 8x8 query windows attend to the
+ *                            12x12 key/value window around them (zero vectors outside the image, still in the softmax);
+ *                            bias fp32 [6][64][144] = OCAB relative_position_bias_table gathered through its index buffer.
+ * srb_overlap_attention_bwd  dqkv[B,H,W,288] from dout[B,H,W,96]; dK/dV of overlapping windows summed per pixel in fixed
+ *                            order; dtable[361][6] += (index: int32 [64][144]; atomicAdd: zero it first).
+ *                            scratch: srb_overlap_attention_bwd_scratch_bytes(B, H, W). */
+size_t srb_overlap_attention_bwd_scratch_bytes(int B, int H, int W);
+int srb_overlap_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, void* stream);
+int srb_overlap_attention_bwd(const void* qkv, const float* bias, const int* index, const void* dout, void* dqkv,
+                              float* dtable, void* scratch, int B, int H, int W, void* stream);
 /* srb_channel_attention      ChannelAttention of CAB: out = y * sigmoid(W2 relu(W1 mean_px(y) + b1) + b2), y bf16 [B,HW,96],
  *                            w1 fp32 [3,96], w2 fp32 [96,3]; saves pooled [B,96], hid [B,3], scale [B,96] for the backward.
  * srb_channel_attention_bwd  dy (direct + pooled term) and dw1/db1/dw2/db2 (+= when accumulate); dpooled [B,96] scratch out.

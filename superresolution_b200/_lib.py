@@ -45,6 +45,9 @@ _PROTOS = {
     'srb_gelu': (_i, [_vp, _i, _vp, _i, _vp, _i, _sz, _i, _vp]),
     'srb_window_attention': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'srb_window_attention_bwd': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    'srb_overlap_attention_bwd_scratch_bytes': (_sz, [_i, _i, _i]),
+    'srb_overlap_attention': (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    'srb_overlap_attention_bwd': (_i, [_vp] * 7 + [_i, _i, _i, _vp]),
     'srb_channel_attention_scratch_bytes': (_sz, [_i, _i]),
     'srb_channel_attention': (_i, [_vp] * 10 + [_i, _i, _vp]),
     'srb_channel_attention_bwd': (_i, [_vp] * 14 + [_i, _i, _i, _vp]),

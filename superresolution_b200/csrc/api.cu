@@ -252,6 +252,17 @@ int srb_window_attention_bwd(const void* qkv, const float* bias, const int* inde
     return win_attn_bwd((const bf16*)qkv, bias, index, (const bf16*)dout, (bf16*)dqkv, dtable, B, H, W, shift,
                         (cudaStream_t)stream);
 }
+size_t srb_overlap_attention_bwd_scratch_bytes(int B, int H, int W) { return ocab_attn_bwd_scratch_bytes(B, H, W); }
+int srb_overlap_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, void* stream) {
+    if (!qkv || !bias || !out) { set_error("overlap_attention: bad args"); return SRB_E_ARG; }
+    return ocab_attn_fwd((const bf16*)qkv, bias, (bf16*)out, B, H, W, (cudaStream_t)stream);
+}
+int srb_overlap_attention_bwd(const void* qkv, const float* bias, const int* index, const void* dout, void* dqkv,
+                              float* dtable, void* scratch, int B, int H, int W, void* stream) {
+    if (!qkv || !bias || !index || !dout || !dqkv || !dtable || !scratch) { set_error("overlap_attention_bwd: bad args"); return SRB_E_ARG; }
+    return ocab_attn_bwd((const bf16*)qkv, bias, index, (const bf16*)dout, (bf16*)dqkv, dtable, scratch, B, H, W,
+                         (cudaStream_t)stream);
+}
 size_t srb_channel_attention_scratch_bytes(int B, int HW) { return chan_attn_scratch_bytes(B, HW); }
 int srb_channel_attention(const void* y, const float* w1, const float* b1, const float* w2, const float* b2, void* out,
                           float* pooled, float* hid, float* scale, void* scratch, int B, int HW, void* stream) {

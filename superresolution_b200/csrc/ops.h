@@ -83,6 +83,12 @@ int win_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, in
 int win_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf16* dout, bf16* dqkv, float* dtable, int B,
                  int H, int W, int shift, cudaStream_t s);
 
+// ocab_attn_train.cu
+size_t ocab_attn_bwd_scratch_bytes(int B, int H, int W);
+int ocab_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, int W, cudaStream_t s);
+int ocab_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf16* dout, bf16* dqkv, float* dtable,
+                  void* scratch, int B, int H, int W, cudaStream_t s);
+
 // chan_attn.cu
 size_t chan_attn_scratch_bytes(int B, int HW);
 int chan_attn_fwd(const bf16* y, const float* w1, const float* b1, const float* w2, const float* b2, bf16* out,

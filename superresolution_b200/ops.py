@@ -231,6 +231,35 @@ def window_attention_bwd(qkv, bias, index, dout, shift, dtable=None):
     return dqkv, dtable
 
 
+def gather_rel_bias_oca(table, index):
+    """OCAB: table fp32 [361,6] + index int64 [64,144] -> fp32 [6,64,144]."""
+    return table.detach().float()[index.view(-1)].view(64, 144, 6).permute(2, 0, 1).contiguous()
+
+
+def overlap_attention(qkv, bias):
+    """qkv bf16 [B,H,W,288], bias fp32 [6,64,144] -> bf16 [B,H,W,96] (OCAB attention output before proj)."""
+    B, H, W, _ = qkv.shape
+    out = torch.empty(B, H, W, 96, dtype=torch.bfloat16, device=qkv.device)
+    L.check(L.lib().srb_overlap_attention(L.ptr(qkv), L.ptr(bias), L.ptr(out), B, H, W, L.current_stream()),
+            'overlap_attention')
+    return out
+
+
+def overlap_attention_bwd(qkv, bias, index, dout, dtable=None):
+    """Returns (dqkv bf16 [B,H,W,288], dtable fp32 [361,6]); dtable is accumulated into when given."""
+    B, H, W, _ = qkv.shape
+    dqkv = torch.empty_like(qkv)
+    if dtable is None:
+        dtable = torch.zeros(361, 6, dtype=torch.float32, device=qkv.device)
+    # HAT.calculate_rpi_oca yields indices in [-200, 160]: negative ones address the table from its end (Python indexing)
+    idx = (index % 361).to(torch.int32).contiguous()
+    lib = L.lib()
+    scratch = torch.empty(lib.srb_overlap_attention_bwd_scratch_bytes(B, H, W), dtype=torch.uint8, device=qkv.device)
+    L.check(lib.srb_overlap_attention_bwd(L.ptr(qkv), L.ptr(bias), L.ptr(idx), L.ptr(dout), L.ptr(dqkv), L.ptr(dtable),
+                                          L.ptr(scratch), B, H, W, L.current_stream()), 'overlap_attention_bwd')
+    return dqkv, dtable
+
+
 def channel_attention(y, w1, b1, w2, b2):
     """y bf16 [B,HW,96]; w1 [3,96(,1,1)], w2 [96,3(,1,1)] fp32.  Returns (out bf16, saved = (pooled, hid, scale))."""
     B, HW, _ = y.shape

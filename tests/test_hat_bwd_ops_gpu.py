@@ -127,3 +127,48 @@ def test_channel_attention_forward_backward(cuda, B, HW):
     assert (err <= 1e-2 * yr.grad.abs() + 1e-2).all(), err.max().item()
     for got, want in ((dw1, P[0].grad), (db1, P[1].grad), (dw2, P[2].grad), (db2, P[3].grad)):
         assert (got - want).abs().max().item() <= 1e-2 * want.abs().max().item() + 1e-3, (got - want).abs().max().item()
+
+
+def _ref_overlap_attention(qkv, table, index):
+    """OCAB.forward's attention core (oracle/hat.py OCAB.forward) on a [B,H,W,288] qkv tensor, fp32."""
+    B, H, W, _ = qkv.shape
+    c, ws, ows = 96, 8, 12
+    q = qkv[..., :96]
+    kv = qkv[..., 96:].permute(0, 3, 1, 2)  # b, 2c, h, w
+    qw = q.view(B, H // ws, ws, W // ws, ws, c).permute(0, 1, 3, 2, 4, 5).reshape(-1, ws * ws, c)
+    kvw = torch.nn.functional.unfold(kv, kernel_size=ows, stride=ws, padding=2)
+    nw = kvw.shape[-1]
+    kvw = kvw.view(B, 2, c, ows, ows, nw).permute(1, 0, 5, 3, 4, 2).reshape(2, B * nw, ows * ows, c)
+    b_ = qw.shape[0]
+    qh = qw.reshape(b_, 64, 6, 16).permute(0, 2, 1, 3) * 0.25
+    kh = kvw[0].reshape(b_, 144, 6, 16).permute(0, 2, 1, 3)
+    vh = kvw[1].reshape(b_, 144, 6, 16).permute(0, 2, 1, 3)
+    bias = table[index.view(-1)].view(64, 144, 6).permute(2, 0, 1)
+    attn = torch.softmax(qh @ kh.transpose(-2, -1) + bias.unsqueeze(0), dim=-1)
+    o = (attn @ vh).transpose(1, 2).reshape(b_, 64, c)
+    return o.view(B, H // ws, W // ws, ws, ws, c).permute(0, 1, 3, 2, 4, 5).reshape(B, H, W, c)
+
+
+@pytest.mark.parametrize('B,H,W', [(1, 8, 8), (1, 16, 16), (2, 16, 32), (3, 24, 16)])
+def test_overlap_attention_forward_backward(cuda, B, H, W):
+    from superresolution_b200 import ops
+    g = torch.Generator().manual_seed(B * 1000 + H + W)
+    qkv = (torch.randn(B, H, W, 288, generator=g) * 1.2).to(cuda).bfloat16()
+    table = (torch.randn(361, 6, generator=g) * 0.5).to(cuda)
+    co = torch.stack(torch.meshgrid(torch.arange(8), torch.arange(8), indexing='ij')).flatten(1)
+    ce = torch.stack(torch.meshgrid(torch.arange(12), torch.arange(12), indexing='ij')).flatten(1)
+    rel = (ce[:, None, :] - co[:, :, None]).permute(1, 2, 0) + (8 - 12 + 1)   # HAT.calculate_rpi_oca
+    index = (rel[..., 0] * 19 + rel[..., 1]).to(cuda)
+    dout = torch.randn(B, H, W, 96, generator=g).to(cuda).bfloat16()
+    qr = qkv.float().requires_grad_(True)
+    tr = table.clone().requires_grad_(True)
+    ref = _ref_overlap_attention(qr, tr, index)
+    ref.backward(dout.float())
+    bias = ops.gather_rel_bias_oca(table, index)
+    out = ops.overlap_attention(qkv, bias)
+    err = (out.float() - ref.detach()).abs()
+    assert (err <= 1e-2 * ref.detach().abs() + 2e-2).all(), err.max().item()
+    dqkv, dtab = ops.overlap_attention_bwd(qkv, bias, index, dout)
+    err = (dqkv.float() - qr.grad).abs()
+    assert (err <= 2e-2 * qr.grad.abs() + 4e-2).all(), err.max().item()
+    assert (dtab - tr.grad).abs().max().item() <= 2e-2 * tr.grad.abs().max().item() + 1e-2
