@@ -53,7 +53,8 @@ int srb_pack_weights(const void* const* params, int n, void* packed, size_t pack
  * Replaces: HybridSuperResolutionModel.forward (src/architecture.py:74-82): stage1 (RRDBNet) -> s1 -> stage2 (HAT)
  * -> s2 -> sf.  x: [B,1,H,W] (x_dtype F32 in [0,1], or U16 which is divided by 65535 like src/dataset.py:34).
  * y: [B,1,4H,4W] F32 (or U16: clip, *65535, truncate like scripts/Modello_5.py:29-33).
- * stage_mask: bit0 run stage 1, bit1 run stage 2 (both set = full model). */
+ * stage_mask: bit0 run stage 1, bit1 run stage 2 (both set = full model); 7 = full model stopping after s2 (the caller
+ * then resizes with srb_resample_separable and applies sf with srb_blur: the output_size branch of :80-82). */
 size_t srb_workspace_bytes(int B, int H, int W);
 int srb_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                 void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream);
@@ -126,6 +127,13 @@ size_t srb_psnr_ssim_scratch_bytes(int B, int H, int W);
 int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, void* scratch,
                   void* stream);
 int srb_log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, void* stream);
+/* srb_robust_hist   one level of the exact percentile search behind calculate_robust_stats
+ *                   (scripts/Dataset_step4_normalization.py:55-91): over the valid pixels of x (finite, >= thresh > 0)
+ *                   ADD into hist (u64, zeroed by the caller) the counts of  level 0: bits[30:21] (1 x 2048 bins);
+ *                   level 1: bits[20:10] of the pixels with bits[31:21] == prefixes[j] (nprefix x 2048 bins);
+ *                   level 2: bits[9:0] of the pixels with bits[31:10] == prefixes[j].  x 16-byte aligned; 1..4 prefixes. */
+int srb_robust_hist(const float* x, size_t n, float thresh, int level, const uint32_t* prefixes, int nprefix,
+                    unsigned long long* hist, void* stream);
 int srb_blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int overlap, float* acc,
                     float* wsum, int FH, int FW, int row0, int row1, void* stream);
 int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, void* stream);
@@ -159,6 +167,18 @@ int srb_lrelu_bwd(void* g, int g_pitch, const void* y, int y_pitch, size_t npx, 
 int srb_axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b,
               const void* y, int y_f32, int y_pitch, size_t npx, int C, void* stream);
 int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int B, int h, int w, int C, void* stream);
+
+/* srb_blur               AntiCheckerboardLayer.forward (reference src/architecture.py:9-27): depthwise binomial blur with zero
+ *                        padding on fp32 [B,H,W]; mode = SRB_SMOOTH_LIGHT (3x3 /16) | BALANCED (5x5 /256) | STRONG (7x7 /1600).
+ *                        out_dtype SRB_F32, or SRB_U16 = clip[0,1]*65535 truncated (scripts/Modello_5.py:29-33).  The
+ *                        operator is symmetric, so its backward is the same call on the gradient.
+ * srb_resample_separable out[b,oy,ox] = sum_{i<K} sum_{j<K} wy[oy*K+i] * wx[ox*K+j] * in[b, iy[oy*K+i], ix[ox*K+j]]  (fp32):
+ *                        the bicubic resize branch F.interpolate(mode='bicubic', align_corners=False) of
+ *                        src/architecture.py:80-81 with K = 4 and the host-built tap tables, and its backward with the
+ *                        transposed tables (K = the largest number of outputs one input feeds).  K <= 64. */
+int srb_blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int W, void* stream);
+int srb_resample_separable(const float* in, float* out, int B, int Hi, int Wi, int Ho, int Wo, const int* iy,
+                           const float* wy, const int* ix, const float* wx, int K, void* stream);
 
 /* HAT (stage 2) backward building blocks — tested operators, not yet assembled into a stage-2 training path:
  * srb_layernorm96      y = LayerNorm(x)*gamma + beta over 96 channels, eps 1e-5 (nn.LayerNorm of HAT), bf16 [ntok,96]

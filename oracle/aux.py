@@ -76,3 +76,28 @@ def log_normalize_u16(data, gmin, gmax):
 
 def to_u16(t):
     return (np.clip(np.asarray(t, dtype=np.float32), 0, 1) * 65535).astype(np.uint16)
+
+
+def robust_stats(images, black_clip_percentile=3.0, num_samples_per_img=None, batch_size=32):
+    """calculate_robust_stats of scripts/Dataset_step4_normalization.py:55-91 on in-memory float32 images (the FITS read
+    of :42-51 — nan_to_num(nan, +-inf -> 0), cast to float32 — is applied here).  Batches of ``batch_size`` images are
+    stacked like the DataLoader does (images of one call must share a shape).  ``num_samples_per_img=None`` keeps EVERY
+    valid pixel instead of the reference's unseeded ``torch.randperm`` subsample of 4000 per image (:73-75): that is
+    the population value the reference's estimate scatters around, and the one the CUDA path computes exactly."""
+    import torch
+    sampled = []
+    for s in range(0, len(images), batch_size):
+        batch = torch.stack([torch.from_numpy(np.nan_to_num(np.asarray(im), nan=0.0, posinf=0.0, neginf=0.0)
+                                              .astype(np.float32)) for im in images[s:s + batch_size]])
+        batch = torch.log1p(torch.maximum(batch, torch.tensor(0.0)))
+        flat = batch.view(-1)
+        valid = flat[flat > 1e-5]
+        if valid.numel() > 0:
+            if num_samples_per_img is not None:
+                take = min(valid.numel(), num_samples_per_img * batch.shape[0])
+                valid = valid[torch.randperm(valid.numel())[:take]]
+            sampled.append(valid.numpy())
+    if not sampled:
+        return 0.0, 1.0
+    full = np.concatenate(sampled)
+    return np.percentile(full, black_clip_percentile), np.percentile(full, 99.99)

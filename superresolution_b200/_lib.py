@@ -36,6 +36,9 @@ _PROTOS = {
     'srb_conv_wgrad': (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     'srb_upsample2x_nearest': (_i, [_vp, _i, _vp, _i, _i, _i, _vp]),
     'srb_conv3x3_cout1': (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    'srb_robust_hist': (_i, [_vp, _sz, _f, _i, _vp, _i, _vp, _vp]),
+    'srb_blur': (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    'srb_resample_separable': (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     'srb_lrelu_bwd': (_i, [_vp, _i, _vp, _i, _sz, _i, _f, _vp]),
     'srb_axpby': (_i, [_vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _sz, _i, _vp]),
     'srb_upsample2x_bwd': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),

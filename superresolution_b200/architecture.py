@@ -295,8 +295,6 @@ class HybridSuperResolutionModel(nn.Module):
             raise ValueError(f'expected [B,1,H,W], got {tuple(x.shape)}')
         if x.device.type != 'cuda':
             raise RuntimeError('libsrb runs on CUDA only (no CPU fallback); move the input to the GPU')
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and self.training:
-            raise NotImplementedError('backward kernels are not built yet: call under torch.no_grad() / .eval()')
         if x.dtype == torch.uint16:
             xd = L.SRB_U16
         elif x.dtype == torch.bfloat16:
@@ -306,7 +304,7 @@ class HybridSuperResolutionModel(nn.Module):
             xd = L.SRB_F32
         x = x.contiguous()
         B, _, H, W = x.shape
-        scale = 4 if stage_mask == 3 else 2
+        scale = 4 if stage_mask in (3, 7) else 2
         yd = L.SRB_U16 if out_dtype == torch.uint16 else L.SRB_F32
         with torch.cuda.device(x.device):
             packed = self.pack_weights()
@@ -342,9 +340,14 @@ class HybridSuperResolutionModel(nn.Module):
         return L.lib().srb_forward_launch_count(B, H, W, self._smoothing, stage_mask)
 
     def forward(self, x):
-        y = self.run(x, 3)
-        if y.shape[-1] != self.output_size:
-            raise NotImplementedError(
-                f'output {y.shape[-1]} != output_size {self.output_size}: the bicubic resize branch '
-                '(src/architecture.py:80-81) is not built yet; construct with output_size=4*H')
-        return y
+        """src/architecture.py:74-82.  Inference (eval() or no_grad): one srb_forward call.  Training (train() mode with
+        grad enabled): the differentiable libsrb path of training.hybrid_forward."""
+        if torch.is_grad_enabled() and self.training and any(p.requires_grad for p in self.parameters()):
+            from .training import hybrid_forward
+            return hybrid_forward(self, x)
+        if 4 * x.shape[-1] == self.output_size:
+            return self.run(x, 3)
+        # resize branch (:80-81): stage1 -> s1 -> stage2 -> s2, bicubic to output_size x output_size, then sf
+        from . import ops
+        y = ops.bicubic_resize(self.run(x, 7), self.output_size, self.output_size)
+        return ops.blur(y, 'light') if self._smoothing else y

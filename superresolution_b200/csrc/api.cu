@@ -212,6 +212,24 @@ int srb_conv3x3_cout1(const void* in, int in_pitch, const float* w, const float*
     if (!in || !w || !bias || !out || B <= 0 || in_pitch % 8) { set_error("conv3x3_cout1: bad args"); return SRB_E_ARG; }
     return conv_cout1((const bf16*)in, in_pitch, w, bias, out, B, H, W, (cudaStream_t)stream);
 }
+int srb_robust_hist(const float* x, size_t n, float thresh, int level, const uint32_t* prefixes, int nprefix,
+                    unsigned long long* hist, void* stream) {
+    if (!x || !hist || n == 0) { set_error("robust_hist: bad args"); return SRB_E_ARG; }
+    return robust_hist(x, n, thresh, level, prefixes, nprefix, hist, (cudaStream_t)stream);
+}
+int srb_blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int W, void* stream) {
+    if (!in || !out || in == out || B <= 0 || H <= 0 || W <= 0) { set_error("blur: bad args"); return SRB_E_ARG; }
+    if (out_dtype != SRB_F32 && out_dtype != SRB_U16) { set_error("blur: out_dtype must be f32 or u16"); return SRB_E_DTYPE; }
+    return blur(in, out, out_dtype, mode, B, H, W, (cudaStream_t)stream);
+}
+int srb_resample_separable(const float* in, float* out, int B, int Hi, int Wi, int Ho, int Wo, const int* iy,
+                           const float* wy, const int* ix, const float* wx, int K, void* stream) {
+    if (!in || !out || !iy || !wy || !ix || !wx || B <= 0 || Hi <= 0 || Wi <= 0 || Ho <= 0 || Wo <= 0 || K <= 0 || K > 64) {
+        set_error("resample_separable: bad args");
+        return SRB_E_ARG;
+    }
+    return resample_separable(in, out, B, Hi, Wi, Ho, Wo, iy, wy, ix, wx, K, (cudaStream_t)stream);
+}
 int srb_lrelu_bwd(void* g, int g_pitch, const void* y, int y_pitch, size_t npx, int C, float slope, void* stream) {
     if (!g || !y || npx == 0 || C <= 0) { set_error("lrelu_bwd: bad args"); return SRB_E_ARG; }
     return lrelu_bwd((bf16*)g, g_pitch, (const bf16*)y, y_pitch, npx, C, slope, (cudaStream_t)stream);

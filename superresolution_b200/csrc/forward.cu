@@ -485,6 +485,8 @@ static int run_stage2(Ctx& c, Workspace& w, const float* img, int B, int R, int 
 
 static int run_forward(Ctx& c, const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, void* workspace,
                        int smoothing, int stage_mask) {
+    const bool stop_before_sf = stage_mask == 7;  // the caller resizes (src/architecture.py:80-81) and applies sf itself
+    if (stop_before_sf) stage_mask = 3;
     Workspace w;
     memset(&w, 0, sizeof(w));
     if (stage_mask == 2) carve(w, (uint8_t*)workspace, B, H / 2, W / 2);
@@ -508,7 +510,9 @@ static int run_forward(Ctx& c, const void* x, int x_dtype, void* y, int y_dtype,
     }
     SRB_TRY(run_stage2(c, w, img, B, 2 * H, 2 * W));
     const size_t nout = (size_t)B * 16 * H * W;
-    if (smoothing != SRB_SMOOTH_NONE) {
+    if (smoothing != SRB_SMOOTH_NONE && stop_before_sf) {
+        LAUNCH(c, PC_OTHER, 0.0, blur(w.o1, y, y_dtype, smoothing, B, 4 * H, 4 * W, c.s));
+    } else if (smoothing != SRB_SMOOTH_NONE) {
         LAUNCH(c, PC_OTHER, 0.0, blur(w.o1, w.o2, SRB_F32, smoothing, B, 4 * H, 4 * W, c.s));
         LAUNCH(c, PC_OTHER, 0.0, blur(w.o2, y, y_dtype, SRB_SMOOTH_LIGHT, B, 4 * H, 4 * W, c.s));
     } else {
@@ -520,7 +524,7 @@ static int run_forward(Ctx& c, const void* x, int x_dtype, void* y, int y_dtype,
 int model_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                   void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, cudaStream_t s, bool dry,
                   int* launches, double* prof_ms, double* prof_flops, int* prof_counts) {
-    if (stage_mask < 1 || stage_mask > 3) { set_error("forward: stage_mask must be 1, 2 or 3"); return SRB_E_ARG; }
+    if ((stage_mask < 1 || stage_mask > 3) && stage_mask != 7) { set_error("forward: stage_mask must be 1, 2, 3 or 7"); return SRB_E_ARG; }
     if (smoothing < 0 || smoothing > 3) { set_error("forward: bad smoothing mode %d", smoothing); return SRB_E_ARG; }
     if (y_dtype != SRB_F32 && y_dtype != SRB_U16) { set_error("forward: y dtype must be F32 or U16"); return SRB_E_DTYPE; }
     if (x_dtype != SRB_F32 && x_dtype != SRB_U16 && x_dtype != SRB_BF16) { set_error("forward: bad x dtype"); return SRB_E_DTYPE; }

@@ -16,7 +16,13 @@ int rrdb_conv_first(const void* x, int x_dtype, const float* w, const float* bia
 int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, float* out, int B, int H, int W,
                cudaStream_t s);
 int blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int W, cudaStream_t s);
+int resample_separable(const float* in, float* out, int B, int Hi, int Wi, int Ho, int Wo, const int* iy, const float* wy,
+                       const int* ix, const float* wx, int K, cudaStream_t s);
 int convert_out(const float* in, void* out, int out_dtype, size_t n, cudaStream_t s);
+
+// robust_stats.cu
+int robust_hist(const float* x, size_t n, float thresh, int level, const uint32_t* prefixes, int nprefix,
+                unsigned long long* hist, cudaStream_t s);
 
 // small_ops2.cu
 int hat_conv_first_ln(const float* img, const float* w, const float* bias, const float* gamma, const float* beta,

@@ -200,6 +200,47 @@ blur_kernel(const float* __restrict__ in, void* __restrict__ out, int out_dtype,
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// K8b: separable K-tap resample on fp32 [B,H,W] (bicubic resize branch of src/architecture.py:80-81 and its transpose).
+// One thread per output pixel; the x taps of a warp's 32 neighbouring outputs overlap, so the loads coalesce through L1.
+// Accumulation order matches ATen's upsample_bicubic2d: rows outer, columns inner (sum_i wy_i * (sum_j wx_j * in)).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+resample_kernel(const float* __restrict__ in, float* __restrict__ out, int B, int Hi, int Wi, int Ho, int Wo,
+                const int* __restrict__ iy, const float* __restrict__ wy, const int* __restrict__ ix,
+                const float* __restrict__ wx, int K) {
+    const unsigned n = (unsigned)B * Ho * Wo;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned r = i / (unsigned)Wo;
+        const int ox = (int)(i - r * Wo), oy = (int)(r % (unsigned)Ho), b = (int)(r / (unsigned)Ho);
+        const float* src = in + (size_t)b * Hi * Wi;
+        float acc = 0.f;
+        for (int a = 0; a < K; ++a) {
+            const float wa = wy[oy * K + a];
+            if (wa == 0.f) continue;
+            const float* row = src + (size_t)iy[oy * K + a] * Wi;
+            float s = 0.f;
+            for (int c = 0; c < K; ++c) s = fmaf(row[ix[ox * K + c]], wx[ox * K + c], s);
+            acc = fmaf(s, wa, acc);
+        }
+        out[i] = acc;
+    }
+}
+
+int resample_separable(const float* in, float* out, int B, int Hi, int Wi, int Ho, int Wo, const int* iy, const float* wy,
+                       const int* ix, const float* wx, int K, cudaStream_t s) {
+    const size_t n = (size_t)B * Ho * Wo;
+    if (n >= ((size_t)1 << 31) || (size_t)B * Hi * Wi >= ((size_t)1 << 31)) {
+        set_error("resample_separable: tensor too large for 32-bit indexing");
+        return SRB_E_SHAPE;
+    }
+    int grid = (int)((n + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    resample_kernel<<<grid, 256, 0, s>>>(in, out, B, Hi, Wi, Ho, Wo, iy, wy, ix, wx, K);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
 int blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int W, cudaStream_t s) {
     const size_t n = (size_t)B * H * W;
     if (n >= ((size_t)1 << 31)) { set_error("blur: tensor too large for 32-bit indexing"); return SRB_E_SHAPE; }

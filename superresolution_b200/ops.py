@@ -293,3 +293,89 @@ def channel_attention_bwd(y, g, w1, w2, saved):
                                           L.ptr(dpooled), L.ptr(scratch), B, HW, 0, L.current_stream()),
             'channel_attention_bwd')
     return dy, dw1, db1, dw2, db2
+
+
+def blur(x, mode, out_dtype=torch.float32):
+    """AntiCheckerboardLayer.forward (reference src/architecture.py:26-27) on fp32 [B,1,H,W] / [B,H,W]; mode 'light' |
+    'balanced' | 'strong'.  The zero-padded binomial operator is symmetric: its backward is the same call."""
+    x = x.contiguous()
+    if x.dtype != torch.float32:
+        raise TypeError('blur: fp32 input expected')
+    H, W = x.shape[-2:]
+    out = torch.empty(x.shape, dtype=out_dtype, device=x.device)
+    L.check(L.lib().srb_blur(L.ptr(x), L.ptr(out), L.SRB_U16 if out_dtype == torch.uint16 else L.SRB_F32,
+                             L.SMOOTHING[mode], x.numel() // (H * W), H, W, L.current_stream()), 'blur')
+    return out
+
+
+_BICUBIC_TABLES = {}
+
+
+def _cubic_taps(n_in, n_out):
+    """tap tables of ATen's upsample_bicubic2d (align_corners=False, A=-0.75, no scale_factor): source coordinate
+    (dst + 0.5) * n_in / n_out - 0.5 (not clamped), 4 taps at floor - 1 .. floor + 2 clamped to the image."""
+    A = -0.75
+    scale = torch.tensor(n_in / n_out, dtype=torch.float32)
+    real = scale * (torch.arange(n_out, dtype=torch.float32) + 0.5) - 0.5
+    fl = torch.floor(real)
+    t = real - fl
+    c1 = lambda v: ((A + 2) * v - (A + 3)) * v * v + 1
+    c2 = lambda v: ((A * v - 5 * A) * v + 8 * A) * v - 4 * A
+    w = torch.stack([c2(t + 1.0), c1(t), c1(1.0 - t), c2((1.0 - t) + 1.0)], 1).float()
+    idx = (fl.long()[:, None] + torch.arange(-1, 3)[None]).clamp_(0, n_in - 1).int()
+    return idx, w
+
+
+def _transpose_taps(idx, w, n_in):
+    """tables of the transposed operator: for every input position, the outputs it feeds and their weights (padded)"""
+    n_out, K = idx.shape
+    lists = [[] for _ in range(n_in)]
+    for o in range(n_out):
+        for k in range(K):
+            lists[int(idx[o, k])].append((o, float(w[o, k])))
+    Kt = max(len(l) for l in lists)
+    it = torch.zeros(n_in, Kt, dtype=torch.int32)
+    wt = torch.zeros(n_in, Kt, dtype=torch.float32)
+    for i, l in enumerate(lists):
+        for k, (o, v) in enumerate(l):
+            it[i, k], wt[i, k] = o, v
+    return it, wt
+
+
+def bicubic_tables(n_in, n_out, device, transpose=False):
+    key = (n_in, n_out, str(device), transpose)
+    if key not in _BICUBIC_TABLES:
+        idx, w = _cubic_taps(n_in, n_out)
+        if transpose:
+            idx, w = _transpose_taps(idx, w, n_in)
+            if idx.shape[1] > 64:
+                raise ValueError(f'bicubic backward {n_out} -> {n_in}: more than 64 outputs per input pixel')
+        _BICUBIC_TABLES[key] = (idx.contiguous().to(device), w.contiguous().to(device))
+    return _BICUBIC_TABLES[key]
+
+
+def resample_separable(x, Ho, Wo, ty, tx):
+    """fp32 [B,1,Hi,Wi] -> [B,1,Ho,Wo] through per-axis (index, weight) tap tables (see bicubic_tables)."""
+    x = x.contiguous()
+    B, Hi, Wi = x.numel() // (x.shape[-2] * x.shape[-1]), x.shape[-2], x.shape[-1]
+    out = torch.empty(*x.shape[:-2], Ho, Wo, dtype=torch.float32, device=x.device)
+    K = ty[0].shape[1]
+    assert tx[0].shape[1] == K and ty[0].shape[0] == Ho and tx[0].shape[0] == Wo
+    L.check(L.lib().srb_resample_separable(L.ptr(x), L.ptr(out), B, Hi, Wi, Ho, Wo, L.ptr(ty[0]), L.ptr(ty[1]),
+                                           L.ptr(tx[0]), L.ptr(tx[1]), K, L.current_stream()), 'resample_separable')
+    return out
+
+
+def bicubic_resize(x, Ho, Wo):
+    """F.interpolate(x, size=(Ho, Wo), mode='bicubic', align_corners=False) on fp32 [B,1,H,W] (src/architecture.py:80-81)."""
+    Hi, Wi = x.shape[-2:]
+    return resample_separable(x, Ho, Wo, bicubic_tables(Hi, Ho, x.device), bicubic_tables(Wi, Wo, x.device))
+
+
+def bicubic_resize_bwd(g, Hi, Wi):
+    """gradient of bicubic_resize w.r.t. its input: the transposed separable operator applied to g [B,1,Ho,Wo]."""
+    Ho, Wo = g.shape[-2:]
+    ty, tx = bicubic_tables(Hi, Ho, g.device, True), bicubic_tables(Wi, Wo, g.device, True)
+    K = max(ty[0].shape[1], tx[0].shape[1])
+    pad = lambda t: tuple(torch.nn.functional.pad(a, (0, K - a.shape[1])).contiguous() for a in t)
+    return resample_separable(g, Hi, Wi, pad(ty), pad(tx))

@@ -11,8 +11,12 @@ backward: it is the input of every conv of the block and the sign source of ever
 its gradient are fp32, the per-block gradient buffer ``G[B,h,w,192]`` is bf16 (dense-block concat backward = in-place
 accumulation into channel slices through the conv epilogue's ``+ res1``).
 
-Not built: the HAT (stage 2) backward.  ``HybridSuperResolutionModel`` therefore still refuses to run in training mode.
+``hybrid_forward(model, x)`` chains it with the blur layers, the stage-2 path (training_hat.py) and the bicubic resize
+branch into the differentiable forward of ``HybridSuperResolutionModel`` (src/architecture.py:74-82); ``train_step`` is
+the optimizer step of ``scripts/Modello_supporto.py:125-141`` over it.
 """
+import threading
+
 import torch
 import torch.nn.functional as F
 
@@ -44,7 +48,8 @@ def _pad_w(w, cout=None, cin=None):
 
 
 class _RRDBNetFn(torch.autograd.Function):
-    _direct = None  # set by rrdbnet_forward(accumulate_into_grad=True) for the call that follows
+    _tls = threading.local()  # .direct: set by rrdbnet_forward(accumulate_into_grad=True) for the call that follows
+                              # (thread-local: nn.DataParallel drives one replica per thread)
 
     @staticmethod
     def forward(ctx, x, *params):
@@ -101,8 +106,8 @@ class _RRDBNetFn(torch.autograd.Function):
         y = ops.conv3x3_cout1(A3, P['conv_last'][0], P['conv_last'][1])  # fp32 [B,4h,4w]
         ctx.saved = (P, u16, D, body_out, U1, A1, U2, A2, A3)
         ctx.geom = (B, h, w)
-        ctx.direct = _RRDBNetFn._direct or {}
-        _RRDBNetFn._direct = None
+        ctx.direct = getattr(_RRDBNetFn._tls, 'direct', None) or {}
+        _RRDBNetFn._tls.direct = None
         return y.unsqueeze(1)
 
     @staticmethod
@@ -208,5 +213,75 @@ def rrdbnet_forward(stage1, x, accumulate_into_grad=False):
         if accumulate_into_grad and w.grad is not None and b.grad is not None and w.grad.is_contiguous() \
                 and w.grad.dtype == torch.float32 and b.grad.dtype == torch.float32:
             direct[n] = (w.grad, b.grad)
-    _RRDBNetFn._direct = direct
+    _RRDBNetFn._tls.direct = direct
     return _RRDBNetFn.apply(x, *params)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Whole-model training path: reference src/architecture.py:74-82 made differentiable on libsrb operators.
+class _BlurFn(torch.autograd.Function):
+    """AntiCheckerboardLayer: zero-padded symmetric binomial operator -> its own transpose."""
+
+    @staticmethod
+    def forward(ctx, x, mode):
+        ctx.mode = mode
+        return ops.blur(x.detach().float(), mode)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.blur(g.float(), ctx.mode), None
+
+
+class _BicubicFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, Ho, Wo):
+        ctx.in_hw = tuple(x.shape[-2:])
+        return ops.bicubic_resize(x.detach().float(), Ho, Wo)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.bicubic_resize_bwd(g.float(), *ctx.in_hw), None, None
+
+
+def hybrid_forward(model, x, accumulate_into_grad=False, drop_path_rate=0.1):
+    """Differentiable ``HybridSuperResolutionModel.forward``: stage1 -> s1 -> stage2 -> s2 -> (bicubic resize to
+    output_size when the shape differs) -> sf, exactly the order of src/architecture.py:74-82.  x: [B,1,H,W] float in
+    [0,1] with H % 32 == 0 and W % 64 == 0.  Returns fp32 [B,1,output_size,output_size] (or [B,1,4H,4W])."""
+    from .training_hat import hat_forward
+    mode = getattr(model.s1, 'mode', None)  # nn.Identity when smoothing == 'none'
+    y = rrdbnet_forward(model.stage1, x, accumulate_into_grad=accumulate_into_grad)
+    if mode is not None:
+        y = _BlurFn.apply(y, mode)
+    y = hat_forward(model.stage2, y, drop_path_rate=drop_path_rate, training=model.training)
+    if mode is not None:
+        y = _BlurFn.apply(y, mode)
+    if y.shape[-1] != model.output_size:
+        y = _BicubicFn.apply(y, model.output_size, model.output_size)
+    if mode is not None:
+        y = _BlurFn.apply(y, 'light')
+    return y
+
+
+def train_step(model, optimizer, criterion, lr, hr, micro_batch=None, max_norm=1.0, world=1, group=None, grad_scale=1.0):
+    """One optimizer step of scripts/Modello_supporto.py:125-141 on libsrb: forward + loss + backward over the batch
+    (in ``micro_batch``-sized slices whose gradients accumulate in the optimizer's flat fp32 buffer: the saved
+    activations of HAT do not fit 180 GB at 32 patches, and without batch statistics the sum of slice gradients IS the
+    batch gradient), gradient SUM all-reduce over ``world`` ranks (mean folded into the update), global-norm clip at
+    ``max_norm`` and AdamW — the last three fused in ``FusedAdamW.step``.  ``model`` must be in train() mode, on CUDA;
+    ``optimizer`` a ``FusedAdamW`` over ``model.parameters()``.  Returns the batch loss (0-d tensor, no sync)."""
+    from .optim import allreduce_gradients
+    B = lr.shape[0]
+    mb = micro_batch or B
+    optimizer.zero_grad()
+    total = None
+    for s in range(0, B, mb):
+        e = min(B, s + mb)
+        pred = hybrid_forward(model, lr[s:e], accumulate_into_grad=True)
+        loss, _ = criterion(pred, hr[s:e])
+        part = loss * (grad_scale * (e - s) / B)  # mean over the whole batch = weighted sum of slice means
+        part.backward()
+        total = loss.detach() * ((e - s) / B) if total is None else total + loss.detach() * ((e - s) / B)
+    if world > 1:
+        allreduce_gradients(optimizer.flat_grad, group)
+    optimizer.step(grad_scale=grad_scale, max_norm=max_norm, world=world)
+    return total

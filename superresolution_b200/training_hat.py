@@ -15,6 +15,8 @@ Layout: NHWC bf16 activations and activation gradients ([B,H,W,C], tokens = pixe
 The un-fused operators are used on purpose: the fused inference kernels (hab_tc, mlp_tc) keep qkv / hidden activations
 on chip, the backward needs them in HBM.
 """
+import threading
+
 import torch
 
 from . import _lib as L
@@ -214,14 +216,14 @@ def _ocab_bwd(G, pre, saved, rpi, g2):
 # whole network
 # ---------------------------------------------------------------------------------------------------------------------
 class _HATFn(torch.autograd.Function):
-    _cfg = None  # (names, rpi_sa, rpi_oca, masks) for the call that follows
+    _tls = threading.local()  # .cfg = (names, rpi_sa, rpi_oca, masks, debug) for the call that follows
 
     @staticmethod
     def forward(ctx, x, *params):
         if x.device.type != 'cuda':
             raise RuntimeError('libsrb training path runs on CUDA only; no CPU fallback')
-        names, rpi_sa, rpi_oca, masks, debug = _HATFn._cfg
-        _HATFn._cfg = None
+        names, rpi_sa, rpi_oca, masks, debug = _HATFn._tls.cfg
+        _HATFn._tls.cfg = None
         P = {n: p.detach().float().contiguous() for n, p in zip(names, params)}
         B, _, H, W = x.shape
         if H % 16 or W % 32:
@@ -323,5 +325,5 @@ def hat_forward(stage2, x, drop_path_rate=0.1, training=None, masks=None, debug=
     rates = torch.linspace(0, drop_path_rate, 24).tolist()
     if masks is None:  # (attention-branch factors, MLP-branch factors) per HAB, each a list of B floats or None
         masks = [(drop_path_masks(B, rt, training, x.device), drop_path_masks(B, rt, training, x.device)) for rt in rates]
-    _HATFn._cfg = (names, stage2.relative_position_index_SA, stage2.relative_position_index_OCA, masks, debug)
+    _HATFn._tls.cfg = (names, stage2.relative_position_index_SA, stage2.relative_position_index_OCA, masks, debug)
     return _HATFn.apply(x, *[p for _, p in named])

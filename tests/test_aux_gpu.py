@@ -138,3 +138,44 @@ def test_model_matches_committed_golden(cuda):
         psnr = 10 * math.log10(1.0 / max(mse, 1e-20))
         print(k, f'{psnr:.2f} dB')
         assert psnr >= 50.0, (k, psnr)
+
+
+def _sky(g, n, shape):
+    """positive heavy-tailed 'astronomical counts' with NaN, inf, negatives and exact zeros mixed in"""
+    x = torch.expm1(torch.randn(n, *shape, generator=g) * 1.2 + 0.5).abs()
+    u = torch.rand(n, *shape, generator=g)
+    x[u < 0.01] = -x[u < 0.01]
+    x[(u >= 0.01) & (u < 0.011)] = float('nan')
+    x[(u >= 0.011) & (u < 0.0115)] = float('inf')
+    x[(u >= 0.0115) & (u < 0.012)] = float('-inf')
+    x[(u >= 0.012) & (u < 0.03)] = 0.0
+    x[(u >= 0.03) & (u < 0.035)] = 5e-6     # below the valid threshold
+    return x
+
+
+@pytest.mark.parametrize('n,shape,black', [(7, (128, 128), 3.0), (40, (64, 96), 15.0), (3, (33, 17), 5.0), (2, (512, 512), 3.0)])
+def test_robust_stats_equal_the_exact_population_percentiles(cuda, n, shape, black):
+    """srb_robust_hist radix select == np.percentile over every valid pixel (oracle/aux.py robust_stats without the
+    reference's random subsample), bit for bit; and the reference-style subsample estimate scatters around it."""
+    from oracle import aux
+    from superresolution_b200.normalization import robust_stats
+    g = torch.Generator().manual_seed(100 + n)
+    x = _sky(g, n, shape)
+    ref_min, ref_max = aux.robust_stats([im.numpy() for im in x], black)
+    chunks = [x[:n // 2].to(cuda), x[n // 2:].to(cuda)]          # uneven chunks, incl. sizes not divisible by 4
+    got_min, got_max = robust_stats(chunks, black)
+    assert got_min.dtype == np.float32 and got_max.dtype == np.float32
+    assert got_min == np.float32(ref_min) and got_max == np.float32(ref_max), (got_min, ref_min, got_max, ref_max)
+    got2 = robust_stats(lambda: iter([x.to(cuda).view(-1)]), black)  # streaming form, one flat batch
+    assert got2 == (got_min, got_max)
+    torch.manual_seed(0)
+    est_min, est_max = aux.robust_stats([im.numpy() for im in x], black, num_samples_per_img=4000)
+    assert abs(est_min - ref_min) <= 0.1 * (ref_max - ref_min)
+
+
+def test_robust_stats_without_valid_pixels_falls_back(cuda):
+    from superresolution_b200.normalization import robust_stats
+    x = torch.full((4, 32, 32), float('nan'))
+    x[0] = -3.0
+    x[1] = 0.0
+    assert robust_stats([x.to(cuda)]) == (np.float32(0.0), np.float32(1.0))

@@ -1,0 +1,147 @@
+"""Whole-model training path (SURVEY.md §8 a2 + a12): superresolution_b200.training.hybrid_forward / train_step and the
+operators that join the two stages (AntiCheckerboardLayer blur, bicubic resize branch of src/architecture.py:80-81) against
+the fp32 oracle (oracle/hybrid.py = the reference's forward over the re-derived RRDBNet / HAT) and PyTorch autograd.
+
+Bars: blur and bicubic are fp32 operators -> 1e-5 absolute against ATen.  The hybrid gradients run through ~400 bf16
+layers whose LeakyReLU sign patterns differ from an fp32 forward at ~0.05-0.3 % of the elements (see
+test_training_gpu.py / test_training_hat_gpu.py, where each stage is checked against a sign-matched reference to 2-4 %):
+here the composition is checked, so the bars are per-stage medians of the relative L2 error and the cosine of the whole
+flattened gradient."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return ((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30)).item()
+
+
+@pytest.mark.parametrize('mode', ['light', 'balanced', 'strong'])
+def test_blur_abi_matches_reference_layer_and_is_self_adjoint(cuda, mode):
+    from oracle.hybrid import AntiCheckerboardLayer as RefBlur
+    from superresolution_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(3, 1, 40, 72, generator=g)
+    ref = RefBlur(mode)(x)
+    got = ops.blur(x.to(cuda), mode)
+    assert (got.cpu() - ref).abs().max().item() <= 1e-6
+    # <blur(x), r> == <x, blur(r)>: the backward used by the training path
+    r = torch.rand(3, 1, 40, 72, generator=g)
+    lhs = (got.double() * r.to(cuda).double()).sum().item()
+    rhs = (x.to(cuda).double() * ops.blur(r.to(cuda), mode).double()).sum().item()
+    assert abs(lhs - rhs) <= 1e-6 * abs(lhs)
+    u16 = ops.blur(x.to(cuda), mode, out_dtype=torch.uint16)
+    exp = (ref.clamp(0, 1) * 65535.0).to(torch.int32)
+    assert (u16.cpu().to(torch.int32) - exp).abs().max().item() <= 1
+
+
+@pytest.mark.parametrize('hw_in,hw_out', [((128, 256), (192, 192)), ((64, 64), (512, 512)), ((96, 128), (37, 53))])
+def test_bicubic_resize_forward_backward_match_aten(cuda, hw_in, hw_out):
+    from superresolution_b200 import ops
+    g = torch.Generator().manual_seed(12)
+    x = torch.rand(2, 1, *hw_in, generator=g, requires_grad=True)
+    ref = F.interpolate(x, size=hw_out, mode='bicubic', align_corners=False)
+    r = torch.randn(ref.shape, generator=g)
+    (ref * r).sum().backward()
+    got = ops.bicubic_resize(x.detach().to(cuda), *hw_out)
+    assert got.shape == ref.shape
+    assert (got.cpu() - ref.detach()).abs().max().item() <= 1e-5
+    gx = ops.bicubic_resize_bwd(r.to(cuda), *hw_in)
+    assert (gx.cpu() - x.grad).abs().max().item() <= 1e-4 * max(1.0, x.grad.abs().max().item())
+
+
+def test_inference_resize_branch_matches_oracle(cuda):
+    """output_size != 4W: stage1 -> s1 -> stage2 -> s2 -> bicubic -> sf (src/architecture.py:74-82), bf16 bar 50 dB."""
+    from oracle.hybrid import HybridSuperResolutionModel as Oracle
+    from superresolution_b200.architecture import HybridSuperResolutionModel as Model
+    torch.manual_seed(0)
+    o = Oracle(output_size=96, smoothing='balanced').eval()
+    m = Model(output_size=96, smoothing='balanced')
+    m.load_state_dict(o.state_dict(), strict=True)
+    m = m.to(cuda).eval()
+    g = torch.Generator().manual_seed(1)
+    x = torch.randint(0, 65536, (1, 1, 32, 32), generator=g).float() / 65535.0
+    with torch.no_grad():
+        ref = o(x)
+        got = m(x.to(cuda)).cpu()
+    assert got.shape == ref.shape == (1, 1, 96, 96)
+    mse = (got.double() - ref.double()).pow(2).mean().item()
+    assert 10 * math.log10(1.0 / max(mse, 1e-20)) >= 50.0
+
+
+@pytest.mark.parametrize('smoothing,output_size', [('none', 256), ('balanced', 192)])
+def test_hybrid_forward_backward_matches_oracle_autograd(cuda, smoothing, output_size):
+    from oracle.hybrid import HybridSuperResolutionModel as Oracle
+    from superresolution_b200.architecture import HybridSuperResolutionModel as Model
+    from superresolution_b200.training import hybrid_forward
+    torch.manual_seed(2)
+    o = Oracle(output_size=output_size, smoothing=smoothing).eval()   # eval: DropPath off on both sides
+    m = Model(output_size=output_size, smoothing=smoothing)
+    m.load_state_dict(o.state_dict(), strict=True)
+    m = m.to(cuda).train()
+    g = torch.Generator().manual_seed(8)
+    x = torch.randint(0, 65536, (1, 1, 32, 64), generator=g).float() / 65535.0
+    yo = o(x)
+    R = torch.randn(yo.shape, generator=g)
+    (yo * R).sum().backward()
+    y = hybrid_forward(m, x.to(cuda), drop_path_rate=0.0)
+    assert y.shape == yo.shape and y.requires_grad
+    mse = (y.detach().cpu().double() - yo.detach().double()).pow(2).mean().item()
+    psnr = 10 * math.log10(1.0 / max(mse, 1e-20))
+    print(f'forward psnr vs fp32 oracle {psnr:.2f} dB')
+    assert psnr >= 50.0
+    (y * R.to(cuda)).sum().backward()
+    ref = dict(o.named_parameters())
+    for stage, med_bar, cos_bar in (('stage2.', 0.12, 0.99), ('stage1.', 0.20, 0.99)):
+        errs, a, b = [], [], []
+        for n, p in m.named_parameters():
+            if not n.startswith(stage):
+                continue
+            assert p.grad is not None and p.grad.shape == ref[n].grad.shape, n
+            errs.append(_rel(p.grad.cpu(), ref[n].grad))
+            a.append(p.grad.cpu().double().flatten())
+            b.append(ref[n].grad.double().flatten())
+        a, b = torch.cat(a), torch.cat(b)
+        cos = (a @ b / (a.norm() * b.norm())).item()
+        errs.sort()
+        print(f'{stage} {len(errs)} tensors: median rel err {errs[len(errs) // 2]:.4f}  p90 {errs[int(len(errs) * .9)]:.4f} '
+              f'max {errs[-1]:.4f}  cosine {cos:.5f}  |g| {a.norm():.4g} vs {b.norm():.4g}')
+        assert errs[len(errs) // 2] <= med_bar
+        assert cos >= cos_bar
+
+
+def test_train_step_micro_batches_equal_full_batch_and_reduce_loss(cuda):
+    """train_step = scripts/Modello_supporto.py:125-141: the gradient of a batch taken in micro-batches equals the
+    gradient of the batch taken at once (deterministic kernels: bit-equal is not required, 1e-3 relative is), and a few
+    steps lower the reference loss."""
+    from superresolution_b200.architecture import HybridSuperResolutionModel as Model
+    from superresolution_b200.losses import CombinedLoss
+    from superresolution_b200.optim import FusedAdamW
+    from superresolution_b200.training import hybrid_forward, train_step
+    torch.manual_seed(3)
+    m = Model(output_size=128, smoothing='none').to(cuda).train()
+    opt = FusedAdamW(m.parameters(), lr=2e-4, weight_decay=0.0)
+    crit = CombinedLoss()
+    g = torch.Generator().manual_seed(9)
+    x = (torch.randint(0, 65536, (2, 1, 32, 32 * 2), generator=g).float() / 65535.0).to(cuda)
+    t = F.interpolate(x, scale_factor=4, mode='bilinear', align_corners=False)
+    t[:, :, ::17, ::13] = 0.9  # bright "stars": the 500x branch of src/losses.py fires
+    m.output_size = t.shape[-1]
+    grads = []
+    for mb in (2, 1):
+        opt.zero_grad()
+        for s in range(0, 2, mb):
+            pred = hybrid_forward(m, x[s:s + mb], accumulate_into_grad=True, drop_path_rate=0.0)
+            loss, _ = crit(pred, t[s:s + mb])
+            (loss * (mb / 2)).backward()
+        grads.append(opt.flat_grad.clone())
+    err = _rel(grads[1], grads[0])
+    print(f'micro-batch vs full-batch gradient rel err {err:.2e}')
+    assert err <= 1e-3
+    losses = [train_step(m, opt, crit, x, t, micro_batch=1, max_norm=1.0).item() for _ in range(5)]
+    print('losses', [round(v, 4) for v in losses])
+    assert all(math.isfinite(v) for v in losses) and losses[-1] < losses[0]
