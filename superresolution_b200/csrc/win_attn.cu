@@ -5,10 +5,16 @@
 //   window = 8 x 8 tokens, 6 heads x 16 channels, logits = q.k * 0.25 + bias[h][i][j] (+ -100 across shift-mask regions),
 //   softmax over the 64 keys, out = P v.  torch.roll / window_partition / window_reverse are index arithmetic.
 //
-// Correctness-first CUDA-core implementation (fp32 math on bf16 operands): one CTA per window, one warp per head, a lane
-// owns query rows {lane, lane + 32}; the backward recomputes P, exchanges dS^T / P^T through shared memory (bf16, padded
-// rows) for the key-side sums, and accumulates the relative-position-bias TABLE gradient (225 x 6) in shared memory
-// across the windows of a persistent CTA (one global atomicAdd per entry and CTA).
+// One WARP per (window, head), one warp per CTA, persistent over items; every contraction is a warp-level
+// mma.sync.m16n8k16 (head_dim 16 = one k-step) on ldmatrix fragments of the head's 32-byte q / k / v / dO slices staged by
+// cp.async (rows padded to an odd number of 16-byte chunks: conflict-free).  No CTA-wide barrier exists; 8 (backward) to
+// 16 (forward) independent warps per SM overlap one another's load / MMA / store phases.
+//   forward : S = Q K^T (+bias, mask) -> softmax in registers -> O = P V with P taken straight from the accumulators.
+//   backward: per 16-row block: S, P recomputed; dP = dO V^T; dS = P (dP - rowsum(P dP)); dQ = dS K / 4;
+//             dK += dS^T Q / 4 and dV += P^T dO with the transposed A fragments produced by movmatrix (register
+//             accumulators over the 4 row blocks); the relative-position-bias gradient accumulates dS in a per-warp
+//             fp32 [64][64] shared-memory tile across all windows of the warp (each element owned by one lane: plain
+//             read-add-write), folded through the index buffer once at the end (one global atomicAdd per table entry).
 #include <cuda_bf16.h>
 
 #include "common.h"
@@ -18,12 +24,9 @@ namespace srb {
 
 namespace {
 
-constexpr int WA_THREADS = 192;
-constexpr int WA_QKV_BYTES = 64 * 288 * 2;
-constexpr int WA_DO_BYTES = 64 * 96 * 2;
-constexpr int WA_TP = 66;  // bf16 pitch of the transposed dS / P scratch rows (132 B: conflict-free row-per-lane reads)
-constexpr int WA_SCR_BYTES = 2 * 64 * WA_TP * 2;  // per warp: dS^T and P^T
-constexpr int WA_TAB = 225;
+constexpr int RP = 56;  // bf16 pitch of a staged token row: q16 | k16 | v16 | 8 pad = 112 B = 7 chunks (odd)
+constexpr int GP = 24;  // bf16 pitch of a staged dO row: 16 | 8 pad = 48 B = 3 chunks (odd)
+constexpr float LOG2E = 1.4426950408889634f;
 
 struct WinArgs {
     const bf16* qkv;    // [B,H,W,288]
@@ -35,25 +38,69 @@ struct WinArgs {
     int B, H, W, shift, nwin;
 };
 
-__device__ __forceinline__ void unpack8(const uint4& raw, float* f) {
-    const __nv_bfloat162* h = (const __nv_bfloat162*)&raw;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float2 v = __bfloat1622float2(h[k]);
-        f[2 * k] = v.x;
-        f[2 * k + 1] = v.y;
-    }
+__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
-__device__ __forceinline__ uint4 pack8(const float* f) {
-    uint4 raw;
-    __nv_bfloat162* h = (__nv_bfloat162*)&raw;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(f[2 * k], f[2 * k + 1]);
-    return raw;
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *(uint32_t*)&h;
+}
+__device__ __forceinline__ void cp16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_commit_wait() {
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+__device__ __forceinline__ void ldsm4(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+__device__ __forceinline__ void ldsm4t(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"((uint32_t)__cvta_generic_to_shared(p)));
+}
+// 8x8 b16 transpose across the warp: accumulator-layout block -> A-fragment block of the transposed matrix
+__device__ __forceinline__ uint32_t movt(uint32_t a) {
+    uint32_t d;
+    asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+    return d;
+}
+__device__ __forceinline__ float ex2f(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float quad_max(float v) {
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 1));
+    return fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 2));
+}
+__device__ __forceinline__ float quad_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    return v + __shfl_xor_sync(0xffffffffu, v, 2);
+}
+
+// A fragment: rows row0..row0+15, 16 k-columns starting at element col0 of a [rows][pitch] bf16 tile
+__device__ __forceinline__ void frag_a(uint32_t (&r)[4], const bf16* tile, int pitch, int row0, int col0, int lane) {
+    ldsm4(r, tile + (row0 + (lane & 7) + ((lane >> 3) & 1) * 8) * pitch + col0 + (lane >> 4) * 8);
+}
+// B fragments of two adjacent n-tiles (rows n0..n0+15 of the tile are the n index, k contiguous): {b0,b1 | b0,b1}
+__device__ __forceinline__ void frag_b_nk(uint32_t (&r)[4], const bf16* tile, int pitch, int n0, int col0, int lane) {
+    ldsm4(r, tile + (n0 + (lane & 7) + (lane >> 4) * 8) * pitch + col0 + ((lane >> 3) & 1) * 8);
+}
+// B fragments for k = rows k0..k0+15 of the tile, n = 16 columns from col0 (two n-tiles): {b0,b1 of n 0-7 | b0,b1 of n 8-15}
+__device__ __forceinline__ void frag_b_kn(uint32_t (&r)[4], const bf16* tile, int pitch, int k0, int col0, int lane) {
+    ldsm4t(r, tile + (k0 + (lane & 7) + ((lane >> 3) & 1) * 8) * pitch + col0 + (lane >> 4) * 8);
 }
 
 // pixel index of window token n (cyclic shift = index math) and its shift-mask region id
-__device__ __forceinline__ size_t win_token(const WinArgs& a, int win, int n, int& rid) {
+__device__ __forceinline__ int win_token(const WinArgs& a, int win, int n, int& rid) {
     const int nwx = a.W / 8, nwy = a.H / 8;
     const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
     const int ys = wy * 8 + (n >> 3), xs = wx * 8 + (n & 7);  // rolled-image coordinates
@@ -62,198 +109,272 @@ __device__ __forceinline__ size_t win_token(const WinArgs& a, int win, int n, in
     if (x >= a.W) x -= a.W;
     const int rh = ys < a.H - 8 ? 0 : (ys < a.H - 4 ? 1 : 2);
     const int rw = xs < a.W - 8 ? 0 : (xs < a.W - 4 ? 1 : 2);
-    rid = rh * 3 + rw;
-    return ((size_t)b * a.H + y) * a.W + x;
+    rid = a.shift > 0 ? rh * 3 + rw : 0;
+    return (b * a.H + y) * a.W + x;  // host checks B*H*W < 2^31
 }
 
-// stage the window's qkv rows (and optionally dOut rows) in shared memory; sPix / sRid per token
-__device__ __forceinline__ void load_window(const WinArgs& a, int win, uint8_t* sQKV, uint8_t* sDO, size_t* sPix, int* sRid) {
-    if (threadIdx.x < 64) {
-        int rid;
-        sPix[threadIdx.x] = win_token(a, win, threadIdx.x, rid);
-        sRid[threadIdx.x] = rid;
+// stage this (window, head): sT rows = q|k|v slices, optional sG rows = dO slice; returns true when the window crosses
+// shift-mask regions
+template <bool BWD>
+__device__ __forceinline__ bool stage(const WinArgs& a, int win, int h, bf16* sT, bf16* sG, int* sPix, uint8_t* sRid,
+                                      int lane) {
+    int r0, r1;
+    const int p0 = win_token(a, win, lane, r0), p1 = win_token(a, win, lane + 32, r1);
+    sPix[lane] = p0; sPix[lane + 32] = p1;
+    sRid[lane] = (uint8_t)r0; sRid[lane + 32] = (uint8_t)r1;
+    const int first = __shfl_sync(0xffffffffu, r0, 0);
+    const bool mixed = __any_sync(0xffffffffu, r0 != first || r1 != first);
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        const int i = lane + 32 * k, n = i / 6, c = i % 6;
+        cp16(sT + n * RP + c * 8, a.qkv + (size_t)sPix[n] * 288 + (c >> 1) * 96 + h * 16 + (c & 1) * 8);
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < 64 * 36; i += WA_THREADS) {
-        const int n = i / 36, u = i % 36;
-        *(uint4*)(sQKV + n * 576 + u * 16) = __ldg((const uint4*)(a.qkv + sPix[n] * 288) + u);
-    }
-    if (sDO) {
-        for (int i = threadIdx.x; i < 64 * 12; i += WA_THREADS) {
-            const int n = i / 12, u = i % 12;
-            *(uint4*)(sDO + n * 192 + u * 16) = __ldg((const uint4*)(a.dout + sPix[n] * 96) + u);
+    if (BWD) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = lane + 32 * k, n = i >> 1, c = i & 1;
+            cp16(sG + n * GP + c * 8, a.dout + (size_t)sPix[n] * 96 + h * 16 + c * 8);
         }
     }
-    __syncthreads();
+    cp_commit_wait();
+    __syncwarp();
+    return mixed;
 }
 
-// softmax probabilities of query row r of head h: p[64] (fp32 registers)
-__device__ __forceinline__ void attn_row(const WinArgs& a, const uint8_t* sQKV, const int* sRid, int h, int r, float* q,
-                                         float* p) {
-    unpack8(*(const uint4*)(sQKV + r * 576 + h * 32), q);
-    unpack8(*(const uint4*)(sQKV + r * 576 + h * 32 + 16), q + 8);
-    const float* brow = a.bias + ((size_t)h * 64 + r) * 64;
-    const int rid = sRid[r];
-    float mx = -1e30f;
+// softmax probabilities of the 16 query rows of block mt (fp32, accumulator layout: s[j][0..1] row g, s[j][2..3] row g+8)
+__device__ __forceinline__ void probs(const WinArgs& a, const bf16* sT, const uint8_t* sRid, bool mixed, int h, int mt,
+                                      int lane, float (&s)[8][4]) {
+    const int g = lane >> 2, t = lane & 3;
+    uint32_t qa[4];
+    frag_a(qa, sT, RP, 16 * mt, 0, lane);
 #pragma unroll
-    for (int j = 0; j < 64; ++j) {
-        float k[16];
-        unpack8(*(const uint4*)(sQKV + j * 576 + 192 + h * 32), k);
-        unpack8(*(const uint4*)(sQKV + j * 576 + 192 + h * 32 + 16), k + 8);
-        float s = 0.f;
+    for (int j = 0; j < 8; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
 #pragma unroll
-        for (int d = 0; d < 16; ++d) s = fmaf(q[d], k[d], s);
-        s = fmaf(s, 0.25f, __ldg(brow + j));
-        if (a.shift > 0 && sRid[j] != rid) s -= 100.f;
-        p[j] = s;
-        mx = fmaxf(mx, s);
+    for (int j = 0; j < 8; j += 2) {
+        uint32_t kb[4];
+        frag_b_nk(kb, sT, RP, 8 * j, 16, lane);
+        mma16816(s[j], qa[0], qa[1], qa[2], qa[3], kb[0], kb[1]);
+        mma16816(s[j + 1], qa[0], qa[1], qa[2], qa[3], kb[2], kb[3]);
     }
-    float sum = 0.f;
+    const int r0 = 16 * mt + g, r1 = r0 + 8;
+    const float* b0 = a.bias + ((size_t)h * 64 + r0) * 64 + 2 * t;
+    const float* b1 = b0 + 8 * 64;
 #pragma unroll
-    for (int j = 0; j < 64; ++j) {
-        p[j] = __expf(p[j] - mx);
-        sum += p[j];
+    for (int j = 0; j < 8; ++j) {
+        const float2 u = __ldg((const float2*)(b0 + 8 * j)), v = __ldg((const float2*)(b1 + 8 * j));
+        s[j][0] = fmaf(s[j][0], 0.25f, u.x); s[j][1] = fmaf(s[j][1], 0.25f, u.y);
+        s[j][2] = fmaf(s[j][2], 0.25f, v.x); s[j][3] = fmaf(s[j][3], 0.25f, v.y);
     }
-    const float inv = 1.f / sum;
+    if (mixed) {
+        const int q0 = sRid[r0], q1 = sRid[r1];
 #pragma unroll
-    for (int j = 0; j < 64; ++j) p[j] *= inv;
+        for (int j = 0; j < 8; ++j) {
+            const int c0 = sRid[8 * j + 2 * t], c1 = sRid[8 * j + 2 * t + 1];
+            if (c0 != q0) s[j][0] -= 100.f;
+            if (c1 != q0) s[j][1] -= 100.f;
+            if (c0 != q1) s[j][2] -= 100.f;
+            if (c1 != q1) s[j][3] -= 100.f;
+        }
+    }
+    float m0 = -1e30f, m1 = -1e30f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        m0 = fmaxf(m0, fmaxf(s[j][0], s[j][1]));
+        m1 = fmaxf(m1, fmaxf(s[j][2], s[j][3]));
+    }
+    m0 = quad_max(m0) * LOG2E; m1 = quad_max(m1) * LOG2E;
+    float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        s[j][0] = ex2f(fmaf(s[j][0], LOG2E, -m0)); s[j][1] = ex2f(fmaf(s[j][1], LOG2E, -m0));
+        s[j][2] = ex2f(fmaf(s[j][2], LOG2E, -m1)); s[j][3] = ex2f(fmaf(s[j][3], LOG2E, -m1));
+        l0 += s[j][0] + s[j][1];
+        l1 += s[j][2] + s[j][3];
+    }
+    const float i0 = 1.f / quad_sum(l0), i1 = 1.f / quad_sum(l1);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j][0] *= i0; s[j][1] *= i0; s[j][2] *= i1; s[j][3] *= i1; }
 }
 
-__global__ void __launch_bounds__(WA_THREADS)
+constexpr int FWD_SMEM = 64 * RP * 2 + 64 * 4 + 64;
+
+__global__ void __launch_bounds__(32)
 win_attn_fwd_kernel(const WinArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint8_t* sQKV = smem;
-    size_t* sPix = (size_t*)(smem + WA_QKV_BYTES);
-    int* sRid = (int*)(sPix + 64);
-    const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int win = blockIdx.x; win < a.nwin; win += gridDim.x) {
-        __syncthreads();  // previous window fully consumed
-        load_window(a, win, sQKV, nullptr, sPix, sRid);
-        for (int rr = 0; rr < 2; ++rr) {
-            const int r = lane + 32 * rr;
-            float q[16], p[64], o[16];
-            attn_row(a, sQKV, sRid, h, r, q, p);
+    bf16* sT = (bf16*)smem;
+    int* sPix = (int*)(smem + 64 * RP * 2);
+    uint8_t* sRid = (uint8_t*)(sPix + 64);
+    const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
+    for (int item = blockIdx.x; item < a.nwin * 6; item += gridDim.x) {
+        const int win = item / 6, h = item % 6;
+        const bool mixed = stage<false>(a, win, h, sT, nullptr, sPix, sRid, lane);
+#pragma unroll 1
+        for (int mt = 0; mt < 4; ++mt) {
+            float s[8][4];
+            probs(a, sT, sRid, mixed, h, mt, lane, s);
+            float o[2][4];
 #pragma unroll
-            for (int d = 0; d < 16; ++d) o[d] = 0.f;
+            for (int nt = 0; nt < 2; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
 #pragma unroll
-            for (int j = 0; j < 64; ++j) {
-                float v[16];
-                unpack8(*(const uint4*)(sQKV + j * 576 + 384 + h * 32), v);
-                unpack8(*(const uint4*)(sQKV + j * 576 + 384 + h * 32 + 16), v + 8);
-#pragma unroll
-                for (int d = 0; d < 16; ++d) o[d] = fmaf(p[j], v[d], o[d]);
+            for (int kt = 0; kt < 4; ++kt) {
+                uint32_t vb[4];
+                frag_b_kn(vb, sT, RP, 16 * kt, 32, lane);
+                const uint32_t p0 = pack2(s[2 * kt][0], s[2 * kt][1]), p1 = pack2(s[2 * kt][2], s[2 * kt][3]);
+                const uint32_t p2 = pack2(s[2 * kt + 1][0], s[2 * kt + 1][1]), p3 = pack2(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+                mma16816(o[0], p0, p1, p2, p3, vb[0], vb[1]);
+                mma16816(o[1], p0, p1, p2, p3, vb[2], vb[3]);
             }
-            uint4* op = (uint4*)(a.out + sPix[r] * 96 + h * 16);
-            op[0] = pack8(o);
-            op[1] = pack8(o + 8);
+            __syncwarp();  // every lane holds its Q fragments of this block before the rows are overwritten
+            const int r0 = 16 * mt + g, r1 = r0 + 8;
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                *(uint32_t*)(sT + r0 * RP + 8 * nt + 2 * t) = pack2(o[nt][0], o[nt][1]);
+                *(uint32_t*)(sT + r1 * RP + 8 * nt + 2 * t) = pack2(o[nt][2], o[nt][3]);
+            }
         }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = lane + 32 * k, n = i >> 1, c = i & 1;
+            *(uint4*)(a.out + (size_t)sPix[n] * 96 + h * 16 + c * 8) = *(const uint4*)(sT + n * RP + c * 8);
+        }
+        __syncwarp();  // the stage of the next item overwrites sT / sPix
     }
 }
 
-__global__ void __launch_bounds__(WA_THREADS)
+constexpr int BWD_SMEM = 64 * RP * 2 + 64 * GP * 2 + 64 * 64 * 4 + 64 * 4 + 64;
+
+__global__ void __launch_bounds__(32)
 win_attn_bwd_kernel(const WinArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint8_t* sQKV = smem;
-    uint8_t* sDO = sQKV + WA_QKV_BYTES;
-    uint8_t* sScr = sDO + WA_DO_BYTES;                       // [6 warps][dS^T | P^T]
-    float* sTab = (float*)(sScr + 6 * WA_SCR_BYTES);         // [6][225]
-    size_t* sPix = (size_t*)(sTab + 6 * WA_TAB + 2);         // (+2 floats keeps 8-byte alignment: 6*225 is even)
-    int* sRid = (int*)(sPix + 64);
-    const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    bf16* dsT = (bf16*)(sScr + h * WA_SCR_BYTES);
-    bf16* pT = dsT + 64 * WA_TP;
-    for (int i = threadIdx.x; i < 6 * WA_TAB; i += WA_THREADS) sTab[i] = 0.f;
-    for (int win = blockIdx.x; win < a.nwin; win += gridDim.x) {
-        __syncthreads();  // previous window fully consumed (and sTab zeroed on the first pass)
-        load_window(a, win, sQKV, sDO, sPix, sRid);
-        // ---- pass 1: query rows. P recomputed; dP = dO V^T; dS = P (dP - sum_j P dP); dQ = 0.25 dS K
-        for (int rr = 0; rr < 2; ++rr) {
-            const int r = lane + 32 * rr;
-            float q[16], p[64], go[16];
-            attn_row(a, sQKV, sRid, h, r, q, p);
-            unpack8(*(const uint4*)(sDO + r * 192 + h * 32), go);
-            unpack8(*(const uint4*)(sDO + r * 192 + h * 32 + 16), go + 8);
-            float ds[64];
-            float delta = 0.f;
+    bf16* sT = (bf16*)smem;
+    bf16* sG = sT + 64 * RP;
+    float* sAcc = (float*)(sG + 64 * GP);            // [64][64] sum over this warp's windows of dS (one head)
+    int* sPix = (int*)(sAcc + 64 * 64);
+    uint8_t* sRid = (uint8_t*)(sPix + 64);
+    const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
+    // a warp keeps ONE head for all its items (grid is a multiple of 6): its sAcc tile is a single-head sum
+    const int h = blockIdx.x % 6;
+    for (int i = lane; i < 64 * 64; i += 32) sAcc[i] = 0.f;
+    __syncwarp();
+    for (int win = blockIdx.x / 6; win < a.nwin; win += gridDim.x / 6) {
+        const bool mixed = stage<true>(a, win, h, sT, sG, sPix, sRid, lane);
+        float dk[4][2][4], dv[4][2][4];
 #pragma unroll
-            for (int j = 0; j < 64; ++j) {
-                float v[16];
-                unpack8(*(const uint4*)(sQKV + j * 576 + 384 + h * 32), v);
-                unpack8(*(const uint4*)(sQKV + j * 576 + 384 + h * 32 + 16), v + 8);
-                float dp = 0.f;
+        for (int kb = 0; kb < 4; ++kb)
 #pragma unroll
-                for (int d = 0; d < 16; ++d) dp = fmaf(go[d], v[d], dp);
-                ds[j] = dp;
-                delta = fmaf(p[j], dp, delta);
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) dk[kb][nt][e] = dv[kb][nt][e] = 0.f;
+#pragma unroll 1
+        for (int mt = 0; mt < 4; ++mt) {
+            float p[8][4], ds[8][4];
+            probs(a, sT, sRid, mixed, h, mt, lane, p);
+            // dP = dO V^T
+            uint32_t ga[4];
+            frag_a(ga, sG, GP, 16 * mt, 0, lane);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ds[j][0] = ds[j][1] = ds[j][2] = ds[j][3] = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+                uint32_t vb[4];
+                frag_b_nk(vb, sT, RP, 8 * j, 32, lane);
+                mma16816(ds[j], ga[0], ga[1], ga[2], ga[3], vb[0], vb[1]);
+                mma16816(ds[j + 1], ga[0], ga[1], ga[2], ga[3], vb[2], vb[3]);
             }
-            float dq[16];
+            float d0 = 0.f, d1 = 0.f;
 #pragma unroll
-            for (int d = 0; d < 16; ++d) dq[d] = 0.f;
-            const int* irow = a.index + r * 64;
-#pragma unroll
-            for (int j = 0; j < 64; ++j) {
-                const float s = p[j] * (ds[j] - delta);  // dS[r][j] = gradient of the logit (and of the bias entry)
-                float k[16];
-                unpack8(*(const uint4*)(sQKV + j * 576 + 192 + h * 32), k);
-                unpack8(*(const uint4*)(sQKV + j * 576 + 192 + h * 32 + 16), k + 8);
-#pragma unroll
-                for (int d = 0; d < 16; ++d) dq[d] = fmaf(s, k[d], dq[d]);
-                atomicAdd(&sTab[h * WA_TAB + __ldg(irow + j)], s);
-                dsT[j * WA_TP + r] = __float2bfloat16_rn(s);
-                pT[j * WA_TP + r] = __float2bfloat16_rn(p[j]);
+            for (int j = 0; j < 8; ++j) {
+                d0 = fmaf(p[j][0], ds[j][0], fmaf(p[j][1], ds[j][1], d0));
+                d1 = fmaf(p[j][2], ds[j][2], fmaf(p[j][3], ds[j][3], d1));
             }
+            d0 = quad_sum(d0); d1 = quad_sum(d1);
+            const int r0 = 16 * mt + g, r1 = r0 + 8;
+            uint32_t pp[8][2], sp[8][2];  // bf16 P and dS, accumulator-layout 8x8 blocks: [j][0] rows 0-7, [j][1] rows 8-15
 #pragma unroll
-            for (int d = 0; d < 16; ++d) dq[d] *= 0.25f;
-            uint4* op = (uint4*)(a.out + sPix[r] * 288 + h * 16);
-            op[0] = pack8(dq);
-            op[1] = pack8(dq + 8);
+            for (int j = 0; j < 8; ++j) {
+                ds[j][0] = p[j][0] * (ds[j][0] - d0); ds[j][1] = p[j][1] * (ds[j][1] - d0);
+                ds[j][2] = p[j][2] * (ds[j][2] - d1); ds[j][3] = p[j][3] * (ds[j][3] - d1);
+                // 8-float column groups XOR-swizzled by the row (r0 & 7 == r1 & 7 == g): the 8 rows of a request hit 8 groups
+                float2* q0 = (float2*)(sAcc + r0 * 64 + 8 * (j ^ g) + 2 * t);
+                float2* q1 = (float2*)(sAcc + r1 * 64 + 8 * (j ^ g) + 2 * t);
+                float2 u = *q0, v = *q1;
+                u.x += ds[j][0]; u.y += ds[j][1]; v.x += ds[j][2]; v.y += ds[j][3];
+                *q0 = u; *q1 = v;
+                pp[j][0] = pack2(p[j][0], p[j][1]); pp[j][1] = pack2(p[j][2], p[j][3]);
+                sp[j][0] = pack2(ds[j][0], ds[j][1]); sp[j][1] = pack2(ds[j][2], ds[j][3]);
+            }
+            // dQ = dS K / 4   (k = keys: 4 k-steps; B[k=key][n=d] = K rows through ldmatrix.trans)
+            float dq[2][4];
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) dq[nt][0] = dq[nt][1] = dq[nt][2] = dq[nt][3] = 0.f;
+#pragma unroll
+            for (int kt = 0; kt < 4; ++kt) {
+                uint32_t kb[4];
+                frag_b_kn(kb, sT, RP, 16 * kt, 16, lane);
+                mma16816(dq[0], sp[2 * kt][0], sp[2 * kt][1], sp[2 * kt + 1][0], sp[2 * kt + 1][1], kb[0], kb[1]);
+                mma16816(dq[1], sp[2 * kt][0], sp[2 * kt][1], sp[2 * kt + 1][0], sp[2 * kt + 1][1], kb[2], kb[3]);
+            }
+            // dK += dS^T Q / 4, dV += P^T dO   (k = the 16 query rows of this block; A = transposed blocks via movmatrix)
+            uint32_t qb[4], gb[4];
+            frag_b_kn(qb, sT, RP, 16 * mt, 0, lane);
+            frag_b_kn(gb, sG, GP, 16 * mt, 0, lane);
+#pragma unroll
+            for (int kb = 0; kb < 4; ++kb) {
+                const uint32_t s0 = movt(sp[2 * kb][0]), s1 = movt(sp[2 * kb + 1][0]);
+                const uint32_t s2 = movt(sp[2 * kb][1]), s3 = movt(sp[2 * kb + 1][1]);
+                mma16816(dk[kb][0], s0, s1, s2, s3, qb[0], qb[1]);
+                mma16816(dk[kb][1], s0, s1, s2, s3, qb[2], qb[3]);
+                const uint32_t t0 = movt(pp[2 * kb][0]), t1 = movt(pp[2 * kb + 1][0]);
+                const uint32_t t2 = movt(pp[2 * kb][1]), t3 = movt(pp[2 * kb + 1][1]);
+                mma16816(dv[kb][0], t0, t1, t2, t3, gb[0], gb[1]);
+                mma16816(dv[kb][1], t0, t1, t2, t3, gb[2], gb[3]);
+            }
+            __syncwarp();  // all lanes hold the Q fragments of this block: its rows now take dQ
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                *(uint32_t*)(sT + r0 * RP + 8 * nt + 2 * t) = pack2(dq[nt][0] * 0.25f, dq[nt][1] * 0.25f);
+                *(uint32_t*)(sT + r1 * RP + 8 * nt + 2 * t) = pack2(dq[nt][2] * 0.25f, dq[nt][3] * 0.25f);
+            }
         }
-        __syncwarp();  // dS^T / P^T of this head are complete (written and read by the same warp only)
-        // ---- pass 2: key rows. dK_j = 0.25 sum_r dS[r][j] q_r;  dV_j = sum_r P[r][j] dO_r
-        for (int jj = 0; jj < 2; ++jj) {
-            const int j = lane + 32 * jj;
-            float dk[16], dv[16];
+        __syncwarp();  // K / V no longer read: their slots take dK / dV
 #pragma unroll
-            for (int d = 0; d < 16; ++d) { dk[d] = 0.f; dv[d] = 0.f; }
-#pragma unroll 4
-            for (int r = 0; r < 64; ++r) {
-                const float s = __bfloat162float(dsT[j * WA_TP + r]), pp = __bfloat162float(pT[j * WA_TP + r]);
-                float q[16], go[16];
-                unpack8(*(const uint4*)(sQKV + r * 576 + h * 32), q);
-                unpack8(*(const uint4*)(sQKV + r * 576 + h * 32 + 16), q + 8);
-                unpack8(*(const uint4*)(sDO + r * 192 + h * 32), go);
-                unpack8(*(const uint4*)(sDO + r * 192 + h * 32 + 16), go + 8);
+        for (int kb = 0; kb < 4; ++kb)
 #pragma unroll
-                for (int d = 0; d < 16; ++d) {
-                    dk[d] = fmaf(s, q[d], dk[d]);
-                    dv[d] = fmaf(pp, go[d], dv[d]);
-                }
+            for (int nt = 0; nt < 2; ++nt) {
+                const int k0 = 16 * kb + g, k1 = k0 + 8, c = 8 * nt + 2 * t;
+                *(uint32_t*)(sT + k0 * RP + 16 + c) = pack2(dk[kb][nt][0] * 0.25f, dk[kb][nt][1] * 0.25f);
+                *(uint32_t*)(sT + k1 * RP + 16 + c) = pack2(dk[kb][nt][2] * 0.25f, dk[kb][nt][3] * 0.25f);
+                *(uint32_t*)(sT + k0 * RP + 32 + c) = pack2(dv[kb][nt][0], dv[kb][nt][1]);
+                *(uint32_t*)(sT + k1 * RP + 32 + c) = pack2(dv[kb][nt][2], dv[kb][nt][3]);
             }
+        __syncwarp();
 #pragma unroll
-            for (int d = 0; d < 16; ++d) dk[d] *= 0.25f;
-            uint4* ok = (uint4*)(a.out + sPix[j] * 288 + 96 + h * 16);
-            ok[0] = pack8(dk);
-            ok[1] = pack8(dk + 8);
-            uint4* ov = (uint4*)(a.out + sPix[j] * 288 + 192 + h * 16);
-            ov[0] = pack8(dv);
-            ov[1] = pack8(dv + 8);
+        for (int k = 0; k < 12; ++k) {
+            const int i = lane + 32 * k, n = i / 6, c = i % 6;
+            *(uint4*)(a.out + (size_t)sPix[n] * 288 + (c >> 1) * 96 + h * 16 + (c & 1) * 8) = *(const uint4*)(sT + n * RP + c * 8);
         }
+        __syncwarp();
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < 6 * WA_TAB; i += WA_THREADS) {
-        const int hh = i / WA_TAB, t = i % WA_TAB;
-        atomicAdd(a.dtable + t * 6 + hh, sTab[i]);
+    // fold the dS sums through the index buffer: table gradient [225][6].  sT is free: 225 floats of it hold the fold.
+    float* sTab = (float*)sT;
+    for (int i = lane; i < 225; i += 32) sTab[i] = 0.f;
+    __syncwarp();
+    for (int i = lane; i < 64 * 64; i += 32) {  // lanes of one step: one row, 32 consecutive columns -> distinct entries
+        const int r = i >> 6, c = i & 63;
+        atomicAdd(&sTab[__ldg(a.index + i)], sAcc[r * 64 + 8 * ((c >> 3) ^ (r & 7)) + (c & 7)]);
     }
+    __syncwarp();
+    for (int i = lane; i < 225; i += 32) atomicAdd(a.dtable + i * 6 + h, sTab[i]);
 }
-
-constexpr int WA_FWD_SMEM = WA_QKV_BYTES + 64 * 8 + 64 * 4;
-constexpr int WA_BWD_SMEM = WA_QKV_BYTES + WA_DO_BYTES + 6 * WA_SCR_BYTES + (6 * WA_TAB + 2) * 4 + 64 * 8 + 64 * 4;
 
 int check_geom(int B, int H, int W, int shift) {
     if (B <= 0 || H % 8 || W % 8 || H < 8 || W < 8 || (shift != 0 && shift != 4)) {
         set_error("win_attn: H=%d W=%d must be multiples of 8, shift=%d must be 0 or 4", H, W, shift);
         return SRB_E_SHAPE;
     }
+    if ((size_t)B * H * W >= ((size_t)1 << 31) / 288) { set_error("win_attn: tensor too large for 32-bit indexing"); return SRB_E_SHAPE; }
     return SRB_OK;
 }
 
@@ -264,8 +385,8 @@ int win_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, in
     WinArgs a;
     a.qkv = qkv; a.bias = bias; a.index = nullptr; a.dout = nullptr; a.out = out; a.dtable = nullptr;
     a.B = B; a.H = H; a.W = W; a.shift = shift; a.nwin = B * (H / 8) * (W / 8);
-    const int grid = a.nwin < num_sms() * 4 ? a.nwin : num_sms() * 4;
-    win_attn_fwd_kernel<<<grid, WA_THREADS, WA_FWD_SMEM, s>>>(a);
+    const int items = a.nwin * 6, cap = num_sms() * 16;
+    win_attn_fwd_kernel<<<items < cap ? items : cap, 32, FWD_SMEM, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
@@ -276,9 +397,9 @@ int win_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf1
     WinArgs a;
     a.qkv = qkv; a.bias = bias; a.index = index; a.dout = dout; a.out = dqkv; a.dtable = dtable;
     a.B = B; a.H = H; a.W = W; a.shift = shift; a.nwin = B * (H / 8) * (W / 8);
-    SRB_CUDA(cudaFuncSetAttribute(win_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WA_BWD_SMEM));
-    const int grid = a.nwin < num_sms() ? a.nwin : num_sms();
-    win_attn_bwd_kernel<<<grid, WA_THREADS, WA_BWD_SMEM, s>>>(a);
+    int warps_per_head = (num_sms() * 8) / 6;  // 8 resident single-warp CTAs per SM (registers and shared memory)
+    if (warps_per_head > a.nwin) warps_per_head = a.nwin;
+    win_attn_bwd_kernel<<<warps_per_head * 6, 32, BWD_SMEM, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
