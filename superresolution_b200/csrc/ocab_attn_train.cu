@@ -6,13 +6,21 @@
 //   PROJECTED k/v maps: keys outside the image are zero vectors that still take part in the softmax with logit = bias).
 //   6 heads x 16 channels, logits = q.k * 0.25 + bias[h][i][j], out = P v.
 //
-// One CTA per window, one warp per head.  Forward / backward pass 1: a lane owns query rows {lane, lane + 32} with the 144
-// probabilities in registers.  Backward pass 2 is key-owned (lane owns keys lane + 32 jj) and RECOMPUTES P from the saved
-// per-row log-sum-exp, so no 64 x 144 matrix is ever exchanged (flash-attention style).  Keys belong to up to four windows:
-// every window writes its dK/dV rows to a per-window scratch and a fold kernel sums them per pixel in fixed order
-// (deterministic); the relative-position-bias table gradient (361 x 6) is accumulated in shared memory per CTA.
+// One WARP per (window, head), one warp per CTA, persistent; all contractions on mma.sync.m16n8k16 (attn_mma.cuh), like
+// win_attn.cu.  With 144 keys the probabilities of a 16-row block do not fit the register file next to the dK / dV
+// accumulators, so the backward is two passes over the staged slices:
+//   pass A (per 16-row block): S over all 144 keys -> row max, 1 / row sum, O = P V -> delta = rowsum(dO . O)  (the
+//           flash-attention identity for rowsum(P . dP)); the three row statistics go to shared memory.
+//   pass B (per chunk of 48 keys, inner loop over the 4 row blocks): P and dP of the chunk recomputed, dS = P (dP - delta),
+//           dQ += dS K / 4 (register accumulators of all 4 blocks), dK / dV of the chunk accumulated over the blocks with
+//           movmatrix-transposed dS / P.  The bias-table gradient accumulates dS in a per-warp fp32 [64][144] shared-memory
+//           tile over all windows of the warp (rotated 8-float groups: conflict-free), folded through the index buffer
+//           at the end.
+// Keys belong to up to four windows: every (window, head) writes its dK / dV rows to a per-window scratch and a fold kernel
+// sums them per pixel in fixed order (deterministic).
 #include <cuda_bf16.h>
 
+#include "attn_mma.cuh"
 #include "common.h"
 #include "ops.h"
 
@@ -20,8 +28,11 @@ namespace srb {
 
 namespace {
 
-constexpr int OA_THREADS = 192, OA_NK = 144, OA_TAB = 361;
-constexpr int OA_Q_BYTES = 64 * 96 * 2, OA_KV_BYTES = OA_NK * 192 * 2, OA_DO_BYTES = 64 * 96 * 2;
+using namespace amma;
+
+constexpr int OA_NK = 144, OA_TAB = 361;
+constexpr int QP = 24;  // bf16 pitch of a staged q / dO row: 16 | 8 pad = 48 B (3 chunks, odd)
+constexpr int KP = 40;  // bf16 pitch of a staged key row: k16 | v16 | 8 pad = 80 B (5 chunks, odd)
 
 struct OcaArgs {
     const bf16* qkv;    // [B,H,W,288]
@@ -50,196 +61,298 @@ __device__ __forceinline__ uint4 oa_pack8(const float* f) {
     for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(f[2 * k], f[2 * k + 1]);
     return raw;
 }
-__device__ __forceinline__ void oa_load16(const uint8_t* p, float* f) {
-    oa_unpack8(*(const uint4*)p, f);
-    oa_unpack8(*(const uint4*)(p + 16), f + 8);
-}
 
-// stage q rows [64][96], k|v rows [144][192] (zero outside the image) and optionally dO rows [64][96]
-__device__ __forceinline__ void oa_load_window(const OcaArgs& a, int win, uint8_t* sQ, uint8_t* sKV, uint8_t* sDO) {
+// stage (window, head): sQ rows = q slice, sKV rows = k | v slices of the 12 x 12 neighbourhood (zero outside the image),
+// optional sG rows = dO slice; sPix = pixel of every query token
+template <bool BWD>
+__device__ __forceinline__ void oa_stage(const OcaArgs& a, int win, int h, bf16* sQ, bf16* sKV, bf16* sG, int* sPix, int lane) {
     const int nwx = a.W / 8, nwy = a.H / 8;
     const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
-    for (int i = threadIdx.x; i < 64 * 12; i += OA_THREADS) {
-        const int n = i / 12, u = i % 12;
-        const size_t pix = ((size_t)b * a.H + wy * 8 + (n >> 3)) * a.W + wx * 8 + (n & 7);
-        *(uint4*)(sQ + n * 192 + u * 16) = __ldg((const uint4*)(a.qkv + pix * 288) + u);
-        if (sDO) *(uint4*)(sDO + n * 192 + u * 16) = __ldg((const uint4*)(a.dout + pix * 96) + u);
+    const int img = b * a.H * a.W;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int n = lane + 32 * k;
+        sPix[n] = img + (wy * 8 + (n >> 3)) * a.W + wx * 8 + (n & 7);
     }
-    for (int i = threadIdx.x; i < OA_NK * 24; i += OA_THREADS) {
-        const int n = i / 24, u = i % 24;
-        const int y = wy * 8 - 2 + n / 12, x = wx * 8 - 2 + n % 12;
-        uint4 v = make_uint4(0, 0, 0, 0);
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int i = lane + 32 * k, n = i >> 1, c = i & 1;
+        cp16(sQ + n * QP + c * 8, a.qkv + (size_t)sPix[n] * 288 + h * 16 + c * 8);
+        if (BWD) cp16(sG + n * QP + c * 8, a.dout + (size_t)sPix[n] * 96 + h * 16 + c * 8);
+    }
+#pragma unroll
+    for (int k = 0; k < 18; ++k) {
+        const int i = lane + 32 * k, m = i >> 2, c = i & 3;  // c: k chunk 0/1, v chunk 0/1
+        const int y = wy * 8 - 2 + m / 12, x = wx * 8 - 2 + m % 12;
+        bf16* dst = sKV + m * KP + c * 8;
         if (y >= 0 && y < a.H && x >= 0 && x < a.W)
-            v = __ldg((const uint4*)(a.qkv + (((size_t)b * a.H + y) * a.W + x) * 288 + 96) + u);
-        *(uint4*)(sKV + n * 384 + u * 16) = v;
+            cp16(dst, a.qkv + (size_t)(img + y * a.W + x) * 288 + 96 + (c >> 1) * 96 + h * 16 + (c & 1) * 8);
+        else
+            *(uint4*)dst = make_uint4(0, 0, 0, 0);  // nn.Unfold zero padding of the projected K / V maps
     }
-    __syncthreads();
+    cp_commit_wait();
+    __syncwarp();
 }
 
-// softmax probabilities of query row r of head h: p[144]; returns the row's log-sum-exp
-__device__ __forceinline__ float oa_attn_row(const OcaArgs& a, const uint8_t* sQ, const uint8_t* sKV, int h, int r, float* p) {
-    float q[16];
-    oa_load16(sQ + r * 192 + h * 32, q);
-    const float* brow = a.bias + ((size_t)h * 64 + r) * OA_NK;
-    float mx = -1e30f;
+// logits of NT n-tiles (keys key0 ...) of row block mt: s = q.k / 4 + bias
+template <int NT>
+__device__ __forceinline__ void oa_logits(const OcaArgs& a, const bf16* sQ, const bf16* sKV, int h, int mt, int key0, int lane,
+                                          float (&s)[NT][4]) {
+    const int g = lane >> 2, t = lane & 3;
+    uint32_t qa[4];
+    frag_a(qa, sQ, QP, 16 * mt, 0, lane);
 #pragma unroll
-    for (int j = 0; j < OA_NK; ++j) {
-        float k[16];
-        oa_load16(sKV + j * 384 + h * 32, k);
-        float s = 0.f;
+    for (int j = 0; j < NT; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
 #pragma unroll
-        for (int d = 0; d < 16; ++d) s = fmaf(q[d], k[d], s);
-        s = fmaf(s, 0.25f, __ldg(brow + j));
-        p[j] = s;
-        mx = fmaxf(mx, s);
+    for (int j = 0; j < NT; j += 2) {
+        uint32_t kb[4];
+        frag_b_nk(kb, sKV, KP, key0 + 8 * j, 0, lane);
+        mma16816(s[j], qa[0], qa[1], qa[2], qa[3], kb[0], kb[1]);
+        mma16816(s[j + 1], qa[0], qa[1], qa[2], qa[3], kb[2], kb[3]);
     }
-    float sum = 0.f;
+    const float* b0 = a.bias + ((size_t)h * 64 + 16 * mt + g) * OA_NK + key0 + 2 * t;
+    const float* b1 = b0 + 8 * OA_NK;
 #pragma unroll
-    for (int j = 0; j < OA_NK; ++j) {
-        p[j] = __expf(p[j] - mx);
-        sum += p[j];
+    for (int j = 0; j < NT; ++j) {
+        const float2 u = __ldg((const float2*)(b0 + 8 * j)), v = __ldg((const float2*)(b1 + 8 * j));
+        s[j][0] = fmaf(s[j][0], 0.25f, u.x); s[j][1] = fmaf(s[j][1], 0.25f, u.y);
+        s[j][2] = fmaf(s[j][2], 0.25f, v.x); s[j][3] = fmaf(s[j][3], 0.25f, v.y);
     }
-    const float inv = 1.f / sum;
-#pragma unroll
-    for (int j = 0; j < OA_NK; ++j) p[j] *= inv;
-    return mx + __logf(sum);
 }
 
-__device__ __forceinline__ size_t oa_qpix(const OcaArgs& a, int win, int n) {
-    const int nwx = a.W / 8, nwy = a.H / 8;
-    const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
-    return ((size_t)b * a.H + wy * 8 + (n >> 3)) * a.W + wx * 8 + (n & 7);
+// full-row pass of block mt: un-normalised probabilities in s (18 n-tiles), row maxima (log2 domain) and 1 / row sums,
+// o = normalised P V
+__device__ __forceinline__ void oa_rows(const OcaArgs& a, const bf16* sQ, const bf16* sKV, int h, int mt, int lane,
+                                        float (&o)[2][4], float& m0, float& m1, float& i0, float& i1) {
+    float s[18][4];
+    oa_logits<18>(a, sQ, sKV, h, mt, 0, lane, s);
+    m0 = -1e30f; m1 = -1e30f;
+#pragma unroll
+    for (int j = 0; j < 18; ++j) {
+        m0 = fmaxf(m0, fmaxf(s[j][0], s[j][1]));
+        m1 = fmaxf(m1, fmaxf(s[j][2], s[j][3]));
+    }
+    m0 = quad_max(m0) * LOG2E; m1 = quad_max(m1) * LOG2E;
+    float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+#pragma unroll
+    for (int kt = 0; kt < 9; ++kt) {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int j = 2 * kt + jj;
+            s[j][0] = ex2f(fmaf(s[j][0], LOG2E, -m0)); s[j][1] = ex2f(fmaf(s[j][1], LOG2E, -m0));
+            s[j][2] = ex2f(fmaf(s[j][2], LOG2E, -m1)); s[j][3] = ex2f(fmaf(s[j][3], LOG2E, -m1));
+            l0 += s[j][0] + s[j][1];
+            l1 += s[j][2] + s[j][3];
+        }
+        uint32_t vb[4];
+        frag_b_kn(vb, sKV, KP, 16 * kt, 16, lane);
+        const uint32_t p0 = pack2(s[2 * kt][0], s[2 * kt][1]), p1 = pack2(s[2 * kt][2], s[2 * kt][3]);
+        const uint32_t p2 = pack2(s[2 * kt + 1][0], s[2 * kt + 1][1]), p3 = pack2(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+        mma16816(o[0], p0, p1, p2, p3, vb[0], vb[1]);
+        mma16816(o[1], p0, p1, p2, p3, vb[2], vb[3]);
+    }
+    i0 = 1.f / quad_sum(l0); i1 = 1.f / quad_sum(l1);
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) { o[nt][0] *= i0; o[nt][1] *= i0; o[nt][2] *= i1; o[nt][3] *= i1; }
 }
 
-__global__ void __launch_bounds__(OA_THREADS)
+constexpr int OA_FWD_SMEM = 64 * QP * 2 + OA_NK * KP * 2 + 64 * 4;
+
+__global__ void __launch_bounds__(32)
 ocab_attn_fwd_kernel(const OcaArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint8_t* sQ = smem;
-    uint8_t* sKV = sQ + OA_Q_BYTES;
-    const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int win = blockIdx.x; win < a.nwin; win += gridDim.x) {
-        __syncthreads();
-        oa_load_window(a, win, sQ, sKV, nullptr);
-        for (int rr = 0; rr < 2; ++rr) {
-            const int r = lane + 32 * rr;
-            float p[OA_NK], o[16];
-            oa_attn_row(a, sQ, sKV, h, r, p);
+    bf16* sQ = (bf16*)smem;
+    bf16* sKV = sQ + 64 * QP;
+    int* sPix = (int*)(sKV + OA_NK * KP);
+    const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
+    for (int item = blockIdx.x; item < a.nwin * 6; item += gridDim.x) {
+        const int win = item / 6, h = item % 6;
+        oa_stage<false>(a, win, h, sQ, sKV, nullptr, sPix, lane);
+#pragma unroll 1
+        for (int mt = 0; mt < 4; ++mt) {
+            float o[2][4], m0, m1, i0, i1;
+            oa_rows(a, sQ, sKV, h, mt, lane, o, m0, m1, i0, i1);
+            __syncwarp();  // every lane holds its Q fragments of this block before the rows are overwritten
+            const int r0 = 16 * mt + g, r1 = r0 + 8;
 #pragma unroll
-            for (int d = 0; d < 16; ++d) o[d] = 0.f;
-#pragma unroll
-            for (int j = 0; j < OA_NK; ++j) {
-                float v[16];
-                oa_load16(sKV + j * 384 + 192 + h * 32, v);
-#pragma unroll
-                for (int d = 0; d < 16; ++d) o[d] = fmaf(p[j], v[d], o[d]);
+            for (int nt = 0; nt < 2; ++nt) {
+                *(uint32_t*)(sQ + r0 * QP + 8 * nt + 2 * t) = pack2(o[nt][0], o[nt][1]);
+                *(uint32_t*)(sQ + r1 * QP + 8 * nt + 2 * t) = pack2(o[nt][2], o[nt][3]);
             }
-            uint4* op = (uint4*)(a.out + oa_qpix(a, win, r) * 96 + h * 16);
-            op[0] = oa_pack8(o);
-            op[1] = oa_pack8(o + 8);
         }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = lane + 32 * k, n = i >> 1, c = i & 1;
+            *(uint4*)(a.out + (size_t)sPix[n] * 96 + h * 16 + c * 8) = *(const uint4*)(sQ + n * QP + c * 8);
+        }
+        __syncwarp();
     }
 }
 
-__global__ void __launch_bounds__(OA_THREADS)
+constexpr int OA_BWD_SMEM = 64 * QP * 2 * 2 + OA_NK * KP * 2 + 64 * OA_NK * 4 + 64 * 4 * 4 + 64 * 4;
+
+__global__ void __launch_bounds__(32)
 ocab_attn_bwd_kernel(const OcaArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint8_t* sQ = smem;
-    uint8_t* sKV = sQ + OA_Q_BYTES;
-    uint8_t* sDO = sKV + OA_KV_BYTES;
-    float* sLse = (float*)(sDO + OA_DO_BYTES);  // [6][64]
-    float* sDelta = sLse + 6 * 64;              // [6][64]
-    float* sTab = sDelta + 6 * 64;              // [6][361]
-    const int h = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < 6 * OA_TAB; i += OA_THREADS) sTab[i] = 0.f;
-    for (int win = blockIdx.x; win < a.nwin; win += gridDim.x) {
-        __syncthreads();
-        oa_load_window(a, win, sQ, sKV, sDO);
-        // ---- pass 1 (query-owned): P, delta = sum_j P dP, dS = P (dP - delta), dQ = 0.25 dS K, bias-table gradient
-        for (int rr = 0; rr < 2; ++rr) {
-            const int r = lane + 32 * rr;
-            float p[OA_NK], go[16], dq[16];
-            const float lse = oa_attn_row(a, sQ, sKV, h, r, p);
-            oa_load16(sDO + r * 192 + h * 32, go);
-            float delta = 0.f;
+    bf16* sQ = (bf16*)smem;
+    bf16* sG = sQ + 64 * QP;
+    bf16* sKV = sG + 64 * QP;
+    float* sAcc = (float*)(sKV + OA_NK * KP);   // [64][144] sum of dS over this warp's windows (one head)
+    float4* sStat = (float4*)(sAcc + 64 * OA_NK);  // per query row: max (log2 domain), 1 / sum, delta
+    int* sPix = (int*)(sStat + 64);
+    const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
+    const int h = blockIdx.x % 6;  // a warp keeps one head for all its windows
+    for (int i = lane; i < 64 * OA_NK; i += 32) sAcc[i] = 0.f;
+    __syncwarp();
+    for (int win = blockIdx.x / 6; win < a.nwin; win += gridDim.x / 6) {
+        oa_stage<true>(a, win, h, sQ, sKV, sG, sPix, lane);
+        // ---- pass A: row statistics
+#pragma unroll 1
+        for (int mt = 0; mt < 4; ++mt) {
+            float o[2][4], m0, m1, i0, i1;
+            oa_rows(a, sQ, sKV, h, mt, lane, o, m0, m1, i0, i1);
+            const int r0 = 16 * mt + g, r1 = r0 + 8;
+            float d0 = 0.f, d1 = 0.f;
 #pragma unroll
-            for (int j = 0; j < OA_NK; ++j) {
-                float v[16];
-                oa_load16(sKV + j * 384 + 192 + h * 32, v);
-                float dp = 0.f;
-#pragma unroll
-                for (int d = 0; d < 16; ++d) dp = fmaf(go[d], v[d], dp);
-                delta = fmaf(p[j], dp, delta);
+            for (int nt = 0; nt < 2; ++nt) {
+                const float2 u = __bfloat1622float2(*(const __nv_bfloat162*)(sG + r0 * QP + 8 * nt + 2 * t));
+                const float2 v = __bfloat1622float2(*(const __nv_bfloat162*)(sG + r1 * QP + 8 * nt + 2 * t));
+                d0 = fmaf(o[nt][0], u.x, fmaf(o[nt][1], u.y, d0));
+                d1 = fmaf(o[nt][2], v.x, fmaf(o[nt][3], v.y, d1));
             }
-#pragma unroll
-            for (int d = 0; d < 16; ++d) dq[d] = 0.f;
-            const int* irow = a.index + r * OA_NK;
-#pragma unroll
-            for (int j = 0; j < OA_NK; ++j) {
-                float v[16], k[16];
-                oa_load16(sKV + j * 384 + 192 + h * 32, v);
-                oa_load16(sKV + j * 384 + h * 32, k);
-                float dp = 0.f;
-#pragma unroll
-                for (int d = 0; d < 16; ++d) dp = fmaf(go[d], v[d], dp);
-                const float s = p[j] * (dp - delta);
-#pragma unroll
-                for (int d = 0; d < 16; ++d) dq[d] = fmaf(s, k[d], dq[d]);
-                atomicAdd(&sTab[h * OA_TAB + __ldg(irow + j)], s);
+            d0 = quad_sum(d0); d1 = quad_sum(d1);
+            if (t == 0) {
+                sStat[r0] = make_float4(m0, i0, d0, 0.f);
+                sStat[r1] = make_float4(m1, i1, d1, 0.f);
             }
-#pragma unroll
-            for (int d = 0; d < 16; ++d) dq[d] *= 0.25f;
-            uint4* op = (uint4*)(a.out + oa_qpix(a, win, r) * 288 + h * 16);
-            op[0] = oa_pack8(dq);
-            op[1] = oa_pack8(dq + 8);
-            sLse[h * 64 + r] = lse;
-            sDelta[h * 64 + r] = delta;
         }
-        __syncwarp();  // lse / delta of this head are read by the same warp only
-        // ---- pass 2 (key-owned): P recomputed from lse; dK_j = 0.25 sum_r dS[r][j] q_r;  dV_j = sum_r P[r][j] dO_r
-        for (int jj = 0; jj < 5; ++jj) {
-            const int j = lane + 32 * jj;
-            if (j >= OA_NK) break;
-            float k[16], v[16], dk[16], dv[16];
-            oa_load16(sKV + j * 384 + h * 32, k);
-            oa_load16(sKV + j * 384 + 192 + h * 32, v);
+        __syncwarp();
+        // ---- pass B: key chunks of 48
+        float dq[4][2][4];
 #pragma unroll
-            for (int d = 0; d < 16; ++d) { dk[d] = 0.f; dv[d] = 0.f; }
-            const float* bcol = a.bias + (size_t)h * 64 * OA_NK + j;
-#pragma unroll 2
-            for (int r = 0; r < 64; ++r) {
-                float q[16], go[16];
-                oa_load16(sQ + r * 192 + h * 32, q);
-                oa_load16(sDO + r * 192 + h * 32, go);
-                float s = 0.f, dp = 0.f;
+        for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-                for (int d = 0; d < 16; ++d) {
-                    s = fmaf(q[d], k[d], s);
-                    dp = fmaf(go[d], v[d], dp);
+            for (int nt = 0; nt < 2; ++nt) dq[mt][nt][0] = dq[mt][nt][1] = dq[mt][nt][2] = dq[mt][nt][3] = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 3; ++c) {
+            const int key0 = 48 * c;
+            float dk[3][2][4], dv[3][2][4];
+#pragma unroll
+            for (int kb = 0; kb < 3; ++kb)
+#pragma unroll
+                for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) dk[kb][nt][e] = dv[kb][nt][e] = 0.f;
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt) {
+                const int r0 = 16 * mt + g, r1 = r0 + 8;
+                float p[6][4], ds[6][4];
+                oa_logits<6>(a, sQ, sKV, h, mt, key0, lane, p);
+                const float4 st0 = sStat[r0], st1 = sStat[r1];
+#pragma unroll
+                for (int j = 0; j < 6; ++j) {
+                    p[j][0] = ex2f(fmaf(p[j][0], LOG2E, -st0.x)) * st0.y; p[j][1] = ex2f(fmaf(p[j][1], LOG2E, -st0.x)) * st0.y;
+                    p[j][2] = ex2f(fmaf(p[j][2], LOG2E, -st1.x)) * st1.y; p[j][3] = ex2f(fmaf(p[j][3], LOG2E, -st1.x)) * st1.y;
+                    ds[j][0] = ds[j][1] = ds[j][2] = ds[j][3] = 0.f;
                 }
-                const float pp = __expf(fmaf(s, 0.25f, __ldg(bcol + r * OA_NK)) - sLse[h * 64 + r]);
-                const float ds = pp * (dp - sDelta[h * 64 + r]);
+                uint32_t ga[4];
+                frag_a(ga, sG, QP, 16 * mt, 0, lane);
 #pragma unroll
-                for (int d = 0; d < 16; ++d) {
-                    dk[d] = fmaf(ds, q[d], dk[d]);
-                    dv[d] = fmaf(pp, go[d], dv[d]);
+                for (int j = 0; j < 6; j += 2) {
+                    uint32_t vb[4];
+                    frag_b_nk(vb, sKV, KP, key0 + 8 * j, 16, lane);
+                    mma16816(ds[j], ga[0], ga[1], ga[2], ga[3], vb[0], vb[1]);
+                    mma16816(ds[j + 1], ga[0], ga[1], ga[2], ga[3], vb[2], vb[3]);
+                }
+                uint32_t pp[6][2], sp[6][2];
+#pragma unroll
+                for (int j = 0; j < 6; ++j) {
+                    ds[j][0] = p[j][0] * (ds[j][0] - st0.z); ds[j][1] = p[j][1] * (ds[j][1] - st0.z);
+                    ds[j][2] = p[j][2] * (ds[j][2] - st1.z); ds[j][3] = p[j][3] * (ds[j][3] - st1.z);
+                    int grp = 6 * c + j + g;  // 8-float groups rotated by the row (r0 & 7 == r1 & 7 == g): conflict-free
+                    if (grp >= 18) grp -= 18;
+                    float2* q0 = (float2*)(sAcc + r0 * OA_NK + 8 * grp + 2 * t);
+                    float2* q1 = (float2*)(sAcc + r1 * OA_NK + 8 * grp + 2 * t);
+                    float2 u = *q0, v = *q1;
+                    u.x += ds[j][0]; u.y += ds[j][1]; v.x += ds[j][2]; v.y += ds[j][3];
+                    *q0 = u; *q1 = v;
+                    pp[j][0] = pack2(p[j][0], p[j][1]); pp[j][1] = pack2(p[j][2], p[j][3]);
+                    sp[j][0] = pack2(ds[j][0], ds[j][1]); sp[j][1] = pack2(ds[j][2], ds[j][3]);
+                }
+#pragma unroll
+                for (int kt = 0; kt < 3; ++kt) {  // dQ += dS K
+                    uint32_t kb[4];
+                    frag_b_kn(kb, sKV, KP, key0 + 16 * kt, 0, lane);
+                    mma16816(dq[mt][0], sp[2 * kt][0], sp[2 * kt][1], sp[2 * kt + 1][0], sp[2 * kt + 1][1], kb[0], kb[1]);
+                    mma16816(dq[mt][1], sp[2 * kt][0], sp[2 * kt][1], sp[2 * kt + 1][0], sp[2 * kt + 1][1], kb[2], kb[3]);
+                }
+                uint32_t qb[4], gb[4];
+                frag_b_kn(qb, sQ, QP, 16 * mt, 0, lane);
+                frag_b_kn(gb, sG, QP, 16 * mt, 0, lane);
+#pragma unroll
+                for (int kb = 0; kb < 3; ++kb) {  // dK += dS^T Q, dV += P^T dO
+                    const uint32_t s0 = movt(sp[2 * kb][0]), s1 = movt(sp[2 * kb + 1][0]);
+                    const uint32_t s2 = movt(sp[2 * kb][1]), s3 = movt(sp[2 * kb + 1][1]);
+                    mma16816(dk[kb][0], s0, s1, s2, s3, qb[0], qb[1]);
+                    mma16816(dk[kb][1], s0, s1, s2, s3, qb[2], qb[3]);
+                    const uint32_t t0 = movt(pp[2 * kb][0]), t1 = movt(pp[2 * kb + 1][0]);
+                    const uint32_t t2 = movt(pp[2 * kb][1]), t3 = movt(pp[2 * kb + 1][1]);
+                    mma16816(dv[kb][0], t0, t1, t2, t3, gb[0], gb[1]);
+                    mma16816(dv[kb][1], t0, t1, t2, t3, gb[2], gb[3]);
                 }
             }
+            __syncwarp();  // the K / V rows of this chunk are not read again: they take dK / dV
 #pragma unroll
-            for (int d = 0; d < 16; ++d) dk[d] *= 0.25f;
-            bf16* row = a.dkv_win + ((size_t)win * OA_NK + j) * 192;
-            uint4* ok = (uint4*)(row + h * 16);
-            ok[0] = oa_pack8(dk);
-            ok[1] = oa_pack8(dk + 8);
-            uint4* ov = (uint4*)(row + 96 + h * 16);
-            ov[0] = oa_pack8(dv);
-            ov[1] = oa_pack8(dv + 8);
+            for (int kb = 0; kb < 3; ++kb)
+#pragma unroll
+                for (int nt = 0; nt < 2; ++nt) {
+                    const int k0 = key0 + 16 * kb + g, k1 = k0 + 8, cc = 8 * nt + 2 * t;
+                    *(uint32_t*)(sKV + k0 * KP + cc) = pack2(dk[kb][nt][0] * 0.25f, dk[kb][nt][1] * 0.25f);
+                    *(uint32_t*)(sKV + k1 * KP + cc) = pack2(dk[kb][nt][2] * 0.25f, dk[kb][nt][3] * 0.25f);
+                    *(uint32_t*)(sKV + k0 * KP + 16 + cc) = pack2(dv[kb][nt][0], dv[kb][nt][1]);
+                    *(uint32_t*)(sKV + k1 * KP + 16 + cc) = pack2(dv[kb][nt][2], dv[kb][nt][3]);
+                }
+            __syncwarp();
         }
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) {
+            const int r0 = 16 * mt + g, r1 = r0 + 8;
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) {
+                *(uint32_t*)(sQ + r0 * QP + 8 * nt + 2 * t) = pack2(dq[mt][nt][0] * 0.25f, dq[mt][nt][1] * 0.25f);
+                *(uint32_t*)(sQ + r1 * QP + 8 * nt + 2 * t) = pack2(dq[mt][nt][2] * 0.25f, dq[mt][nt][3] * 0.25f);
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = lane + 32 * k, n = i >> 1, cc = i & 1;
+            *(uint4*)(a.out + (size_t)sPix[n] * 288 + h * 16 + cc * 8) = *(const uint4*)(sQ + n * QP + cc * 8);
+        }
+#pragma unroll
+        for (int k = 0; k < 18; ++k) {
+            const int i = lane + 32 * k, m = i >> 2, cc = i & 3;
+            *(uint4*)(a.dkv_win + ((size_t)win * OA_NK + m) * 192 + (cc >> 1) * 96 + h * 16 + (cc & 1) * 8) =
+                *(const uint4*)(sKV + m * KP + cc * 8);
+        }
+        __syncwarp();
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < 6 * OA_TAB; i += OA_THREADS) {
-        const int hh = i / OA_TAB, t = i % OA_TAB;
-        atomicAdd(a.dtable + t * 6 + hh, sTab[i]);
+    // fold the dS sums through the index buffer: table gradient [361][6].  sKV is free: 361 floats of it hold the fold.
+    float* sTab = (float*)sKV;
+    for (int i = lane; i < OA_TAB; i += 32) sTab[i] = 0.f;
+    __syncwarp();
+    for (int i = lane; i < 64 * OA_NK; i += 32) {
+        const int r = i / OA_NK, cidx = i % OA_NK;
+        int grp = (cidx >> 3) + (r & 7);
+        if (grp >= 18) grp -= 18;
+        atomicAdd(&sTab[__ldg(a.index + i)], sAcc[r * OA_NK + 8 * grp + (cidx & 7)]);
     }
+    __syncwarp();
+    for (int i = lane; i < OA_TAB; i += 32) atomicAdd(a.dtable + i * 6 + h, sTab[i]);
 }
 
 // dqkv[pix][96 + c] = sum over the (up to 4) windows whose 12 x 12 key region holds the pixel, in (wy, wx) order
@@ -267,14 +380,13 @@ ocab_fold_kernel(const bf16* __restrict__ dkv_win, bf16* __restrict__ dqkv, int 
     }
 }
 
-constexpr int OA_FWD_SMEM = OA_Q_BYTES + OA_KV_BYTES;
-constexpr int OA_BWD_SMEM = OA_Q_BYTES + OA_KV_BYTES + OA_DO_BYTES + (2 * 6 * 64 + 6 * OA_TAB) * 4;
 
 int oa_check(int B, int H, int W) {
     if (B <= 0 || H % 8 || W % 8 || H < 8 || W < 8) {
         set_error("ocab_attn: H=%d W=%d must be multiples of 8", H, W);
         return SRB_E_SHAPE;
     }
+    if ((size_t)B * H * W >= ((size_t)1 << 31) / 288) { set_error("ocab_attn: tensor too large for 32-bit indexing"); return SRB_E_SHAPE; }
     return SRB_OK;
 }
 
@@ -286,9 +398,8 @@ int ocab_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, i
     SRB_TRY(oa_check(B, H, W));
     OcaArgs a{};
     a.qkv = qkv; a.bias = bias; a.out = out; a.B = B; a.H = H; a.W = W; a.nwin = B * (H / 8) * (W / 8);
-    SRB_CUDA(cudaFuncSetAttribute(ocab_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OA_FWD_SMEM));
-    const int grid = a.nwin < num_sms() * 3 ? a.nwin : num_sms() * 3;
-    ocab_attn_fwd_kernel<<<grid, OA_THREADS, OA_FWD_SMEM, s>>>(a);
+    const int items = a.nwin * 6, cap = num_sms() * 12;
+    ocab_attn_fwd_kernel<<<items < cap ? items : cap, 32, OA_FWD_SMEM, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
@@ -300,8 +411,9 @@ int ocab_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf
     a.qkv = qkv; a.bias = bias; a.index = index; a.dout = dout; a.out = dqkv; a.dkv_win = (bf16*)scratch; a.dtable = dtable;
     a.B = B; a.H = H; a.W = W; a.nwin = B * (H / 8) * (W / 8);
     SRB_CUDA(cudaFuncSetAttribute(ocab_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OA_BWD_SMEM));
-    const int grid = a.nwin < num_sms() * 2 ? a.nwin : num_sms() * 2;
-    ocab_attn_bwd_kernel<<<grid, OA_THREADS, OA_BWD_SMEM, s>>>(a);
+    int warps_per_head = (num_sms() * 4) / 6;  // 4 resident single-warp CTAs per SM (56 KB of shared memory each)
+    if (warps_per_head > a.nwin) warps_per_head = a.nwin;
+    ocab_attn_bwd_kernel<<<warps_per_head * 6, 32, OA_BWD_SMEM, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     const size_t n = (size_t)B * H * W * 24;
     size_t g = (n + 255) / 256;
