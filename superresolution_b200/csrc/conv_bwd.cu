@@ -198,6 +198,116 @@ int launch_wgrad(const WgradArgs& a, int tiles, int ksplit, cudaStream_t s) {
     return SRB_OK;
 }
 
+// ---- Linear layers (taps == 1) with Cout = 32 MT, Cin = 32 NT: ONE CTA tile covers the whole [Cout x Cin] gradient, so
+// every pixel of dY and X is read exactly once (the 64 x 32 tiles above re-read dY Cin/32 times and X Cout/64 times:
+// 700 MB of L2 traffic per qkv linear at 4 patches against 200 MB of operands).  8 warps = 2 (co) x 4 (ci), warp tile
+// 16 MT x 8 NT, fp32 accumulators in registers (108 for qkv 288 x 96), same split-K partial layout and reduce kernel.
+template <int MT, int NT>
+struct WgFull {
+    static constexpr int UM = 4 * MT, UN = 4 * NT;  // 16-byte units per pixel row of dY / X
+    static constexpr int DY_BYTES = WG_KC * UM * 16, X_BYTES = WG_KC * UN * 16;
+    static constexpr int STAGE = DY_BYTES + X_BYTES;
+};
+template <int UNITS>
+__device__ __forceinline__ int wgf_swz(int px, int u) {
+    if (UNITS % 8 == 0) return u ^ (px & 7);  // row = whole 128-byte lines
+    return u ^ ((px >> 1) & 3);               // row = odd number of 64-byte halves: two rows alternate halves
+}
+template <int MT, int NT>
+__device__ __forceinline__ void wgf_load_chunk(const WgradArgs& a, int chunk, uint8_t* stage, int tid) {
+    using T = WgFull<MT, NT>;
+    const size_t px0 = (size_t)chunk * WG_KC;  // chunks tile the flattened pixel index (W % 32 == 0)
+    for (int i = tid; i < WG_KC * T::UM; i += WG_THREADS) {
+        const int px = i / T::UM, u = i % T::UM;
+        cp_async16_zfill(stage + (px * T::UM + wgf_swz<T::UM>(px, u)) * 16, a.dy + (px0 + px) * a.dy_pitch + u * 8, true);
+    }
+    for (int i = tid; i < WG_KC * T::UN; i += WG_THREADS) {
+        const int px = i / T::UN, u = i % T::UN;
+        cp_async16_zfill(stage + T::DY_BYTES + (px * T::UN + wgf_swz<T::UN>(px, u)) * 16, a.x + (px0 + px) * a.x_pitch + u * 8,
+                         true);
+    }
+}
+
+template <int MT, int NT>
+__global__ void __launch_bounds__(WG_THREADS)
+linear_wgrad_full_kernel(const WgradArgs a) {
+    using T = WgFull<MT, NT>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp >> 2, wn = warp & 3;  // warp tile: co [16 MT wm, +16 MT), ci [8 NT wn, +8 NT)
+    const int c_begin = blockIdx.x * a.chunks_per_split;
+    const int c_end = min(a.nchunks, c_begin + a.chunks_per_split);
+    float acc[MT][NT][4];
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j) acc[i][j][0] = acc[i][j][1] = acc[i][j][2] = acc[i][j][3] = 0.f;
+#pragma unroll
+    for (int s = 0; s < WG_STAGES - 1; ++s) {
+        if (c_begin + s < c_end) wgf_load_chunk<MT, NT>(a, c_begin + s, smem + s * T::STAGE, tid);
+        cp_async_commit();
+    }
+    for (int c = c_begin; c < c_end; ++c) {
+        const int st = (c - c_begin) % WG_STAGES;
+        cp_async_wait<WG_STAGES - 2>();
+        __syncthreads();
+        {
+            const int cn = c + WG_STAGES - 1;
+            if (cn < c_end) wgf_load_chunk<MT, NT>(a, cn, smem + ((cn - c_begin) % WG_STAGES) * T::STAGE, tid);
+            cp_async_commit();
+        }
+        const uint32_t s_dy = smem_u32(smem + st * T::STAGE), s_x = s_dy + T::DY_BYTES;
+        uint32_t bfr[NT][4];  // {b0, b1} of k-step 0 and of k-step 1 per n-tile (lane = pixel)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+            ldmatrix_x4_trans(s_x + (lane * T::UN + wgf_swz<T::UN>(lane, wn * NT + j)) * 16, bfr[j][0], bfr[j][1], bfr[j][2],
+                              bfr[j][3]);
+#pragma unroll
+        for (int i = 0; i < MT; ++i) {
+            uint32_t af[2][4];
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) {
+                const int px = ks * 16 + (lane & 7) + ((lane >> 4) << 3);
+                const int unit = (wm * MT + i) * 2 + ((lane >> 3) & 1);
+                ldmatrix_x4_trans(s_dy + (px * T::UM + wgf_swz<T::UM>(px, unit)) * 16, af[ks][0], af[ks][1], af[ks][2], af[ks][3]);
+            }
+#pragma unroll
+            for (int j = 0; j < NT; ++j) {
+                mma_bf16_16816(acc[i][j], af[0], bfr[j][0], bfr[j][1]);
+                mma_bf16_16816(acc[i][j], af[1], bfr[j][2], bfr[j][3]);
+            }
+        }
+    }
+    cp_async_wait<0>();
+    const int g = lane >> 2, tq = lane & 3;
+    float* dst = a.partial + (size_t)blockIdx.x * a.Cout * a.Cin;
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int co = (wm * MT + i) * 16 + g + 8 * h, ci = (wn * NT + j) * 8 + 2 * tq;
+                *(float2*)(dst + (size_t)co * a.Cin + ci) = make_float2(acc[i][j][2 * h], acc[i][j][2 * h + 1]);
+            }
+}
+
+template <int MT, int NT>
+int launch_wgrad_full(const WgradArgs& a, int ksplit, cudaStream_t s) {
+    using T = WgFull<MT, NT>;
+    const int smem = WG_STAGES * T::STAGE;
+    SRB_CUDA(cudaFuncSetAttribute(linear_wgrad_full_kernel<MT, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    linear_wgrad_full_kernel<MT, NT><<<ksplit, WG_THREADS, smem, s>>>(a);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+// the linear shapes of HAT: qkv 96->288, fc1 96->192, fc2 192->96, proj 96->96
+bool wgrad_full_shape(int Cin, int Cout, int taps) {
+    return taps == 1 && ((Cout == 288 && Cin == 96) || (Cout == 192 && Cin == 96) || (Cout == 96 && Cin == 192) ||
+                         (Cout == 96 && Cin == 96));
+}
+
 // dW[co][ci][tap] (PyTorch layout) = (accumulate ? dW : 0) + sum_split partial[split][tap][co][ci], fixed order
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int ksplit, int taps,
                                     int Cout, int Cin, int accumulate) {
@@ -267,6 +377,10 @@ int wgrad_tiles(int Cin, int Cout) {
 }
 
 int wgrad_ksplit(int Cin, int Cout, int taps, int nchunks) {
+    if (wgrad_full_shape(Cin, Cout, taps)) {  // one CTA per split, 1 (qkv: 150 registers) or 2 CTAs per SM
+        const int ks = num_sms() * (Cout == 288 ? 1 : 2);
+        return ks < nchunks ? ks : (nchunks < 1 ? 1 : nchunks);
+    }
     const int tiles = wgrad_tiles(Cin, Cout);
     int ks = (num_sms() * 3 + tiles - 1) / tiles;  // ~3 CTAs per SM (<= 45 KB smem, 256 threads each)
     if (ks > nchunks) ks = nchunks;
@@ -309,7 +423,12 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
     a.chunks_per_split = (a.nchunks + ksplit - 1) / ksplit;
     const int tiles = wgrad_tiles(Cin, Cout);
     int rc;
-    if (taps == 9) rc = Cout <= 32 ? launch_wgrad<1, 9>(a, tiles, ksplit, s) : launch_wgrad<2, 9>(a, tiles, ksplit, s);
+    if (wgrad_full_shape(Cin, Cout, taps) && x_pitch >= Cin && dy_pitch >= Cout) {
+        rc = Cout == 288 ? launch_wgrad_full<9, 3>(a, ksplit, s)
+           : Cout == 192 ? launch_wgrad_full<6, 3>(a, ksplit, s)
+           : Cin == 192  ? launch_wgrad_full<3, 6>(a, ksplit, s)
+                         : launch_wgrad_full<3, 3>(a, ksplit, s);
+    } else if (taps == 9) rc = Cout <= 32 ? launch_wgrad<1, 9>(a, tiles, ksplit, s) : launch_wgrad<2, 9>(a, tiles, ksplit, s);
     else rc = Cout <= 32 ? launch_wgrad<1, 1>(a, tiles, ksplit, s) : launch_wgrad<2, 1>(a, tiles, ksplit, s);
     if (rc != SRB_OK) return rc;
     const int n = taps * Cout * Cin;

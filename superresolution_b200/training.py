@@ -243,15 +243,17 @@ class _BicubicFn(torch.autograd.Function):
         return ops.bicubic_resize_bwd(g.float(), *ctx.in_hw), None, None
 
 
-def hybrid_forward(model, x, accumulate_into_grad=False, drop_path_rate=0.1):
-    """Differentiable ``HybridSuperResolutionModel.forward``: stage1 -> s1 -> stage2 -> s2 -> (bicubic resize to
-    output_size when the shape differs) -> sf, exactly the order of src/architecture.py:74-82.  x: [B,1,H,W] float in
-    [0,1] with H % 32 == 0 and W % 64 == 0.  Returns fp32 [B,1,output_size,output_size] (or [B,1,4H,4W])."""
-    from .training_hat import hat_forward
-    mode = getattr(model.s1, 'mode', None)  # nn.Identity when smoothing == 'none'
+def _head(model, x, accumulate_into_grad):
+    """stage1 -> s1 (src/architecture.py:75-76)"""
     y = rrdbnet_forward(model.stage1, x, accumulate_into_grad=accumulate_into_grad)
-    if mode is not None:
-        y = _BlurFn.apply(y, mode)
+    mode = getattr(model.s1, 'mode', None)  # nn.Identity when smoothing == 'none'
+    return _BlurFn.apply(y, mode) if mode is not None else y
+
+
+def _tail(model, y, drop_path_rate):
+    """stage2 -> s2 -> bicubic resize when the shape differs -> sf (src/architecture.py:77-82)"""
+    from .training_hat import hat_forward
+    mode = getattr(model.s1, 'mode', None)
     y = hat_forward(model.stage2, y, drop_path_rate=drop_path_rate, training=model.training)
     if mode is not None:
         y = _BlurFn.apply(y, mode)
@@ -262,25 +264,41 @@ def hybrid_forward(model, x, accumulate_into_grad=False, drop_path_rate=0.1):
     return y
 
 
-def train_step(model, optimizer, criterion, lr, hr, micro_batch=None, max_norm=1.0, world=1, group=None, grad_scale=1.0):
-    """One optimizer step of scripts/Modello_supporto.py:125-141 on libsrb: forward + loss + backward over the batch
-    (in ``micro_batch``-sized slices whose gradients accumulate in the optimizer's flat fp32 buffer: the saved
-    activations of HAT do not fit 180 GB at 32 patches, and without batch statistics the sum of slice gradients IS the
-    batch gradient), gradient SUM all-reduce over ``world`` ranks (mean folded into the update), global-norm clip at
-    ``max_norm`` and AdamW — the last three fused in ``FusedAdamW.step``.  ``model`` must be in train() mode, on CUDA;
-    ``optimizer`` a ``FusedAdamW`` over ``model.parameters()``.  Returns the batch loss (0-d tensor, no sync)."""
+def hybrid_forward(model, x, accumulate_into_grad=False, drop_path_rate=0.1):
+    """Differentiable ``HybridSuperResolutionModel.forward``: stage1 -> s1 -> stage2 -> s2 -> (bicubic resize to
+    output_size when the shape differs) -> sf, exactly the order of src/architecture.py:74-82.  x: [B,1,H,W] float in
+    [0,1] with H % 32 == 0 and W % 64 == 0.  Returns fp32 [B,1,output_size,output_size] (or [B,1,4H,4W])."""
+    return _tail(model, _head(model, x, accumulate_into_grad), drop_path_rate)
+
+
+def train_step(model, optimizer, criterion, lr, hr, micro_batch=16, max_norm=1.0, world=1, group=None, grad_scale=1.0,
+               drop_path_rate=0.1):
+    """One optimizer step of scripts/Modello_supporto.py:125-141 on libsrb: forward + loss + backward over the batch,
+    gradient SUM all-reduce over ``world`` ranks (mean folded into the update), global-norm clip at ``max_norm`` and
+    AdamW — the last three fused in ``FusedAdamW.step``.
+
+    Memory plan: stage 1 (RRDBNet, ~0.11 GB of saved activations per patch) runs forward and backward on the WHOLE batch
+    — its 700 small launches are latency-bound below ~16 patches; stage 2 (HAT, ~4.3 GB per patch: it does not fit
+    180 GB at 32 patches) runs in ``micro_batch``-sized slices of the stage-1 output, each slice forward + loss +
+    backward at once, its input gradient collected into the stage-1 output gradient.  Without batch statistics the sum
+    of the slice gradients IS the batch gradient; parameter gradients accumulate in the optimizer's flat fp32 buffer.
+    ``model`` must be in train() mode, on CUDA; ``optimizer`` a ``FusedAdamW`` over ``model.parameters()``.
+    Returns the batch loss (0-d tensor, no sync)."""
     from .optim import allreduce_gradients
     B = lr.shape[0]
     mb = micro_batch or B
     optimizer.zero_grad()
+    y1 = _head(model, lr, True)
+    g1 = torch.empty_like(y1)
     total = None
     for s in range(0, B, mb):
         e = min(B, s + mb)
-        pred = hybrid_forward(model, lr[s:e], accumulate_into_grad=True)
-        loss, _ = criterion(pred, hr[s:e])
-        part = loss * (grad_scale * (e - s) / B)  # mean over the whole batch = weighted sum of slice means
-        part.backward()
+        ys = y1[s:e].detach().requires_grad_(True)
+        loss, _ = criterion(_tail(model, ys, drop_path_rate), hr[s:e])
+        (loss * (grad_scale * (e - s) / B)).backward()  # mean over the whole batch = weighted sum of slice means
+        g1[s:e] = ys.grad
         total = loss.detach() * ((e - s) / B) if total is None else total + loss.detach() * ((e - s) / B)
+    y1.backward(g1)
     if world > 1:
         allreduce_gradients(optimizer.flat_grad, group)
     optimizer.step(grad_scale=grad_scale, max_norm=max_norm, world=world)

@@ -10,7 +10,8 @@ pytestmark = pytest.mark.gpu
 # B, H, W, Cin, Cout, taps
 CASES = [(1, 32, 32, 64, 32, 9), (2, 32, 64, 96, 32, 9), (1, 64, 64, 160, 32, 9), (2, 32, 32, 192, 64, 9),
          (1, 32, 32, 32, 96, 9), (2, 64, 32, 96, 96, 9), (1, 64, 64, 64, 256, 9), (2, 32, 32, 96, 288, 1),
-         (1, 64, 64, 192, 96, 1), (3, 32, 32, 64, 64, 9)]
+         (1, 64, 64, 192, 96, 1), (3, 32, 32, 64, 64, 9), (1, 32, 64, 96, 192, 1), (2, 64, 64, 96, 96, 1),
+         (1, 16, 32, 96, 288, 1), (1, 32, 32, 64, 96, 1)]
 
 
 def _mk(B, H, W, Cin, Cout, taps, cuda, seed):

@@ -131,17 +131,18 @@ def test_train_step_micro_batches_equal_full_batch_and_reduce_loss(cuda):
     t = F.interpolate(x, scale_factor=4, mode='bilinear', align_corners=False)
     t[:, :, ::17, ::13] = 0.9  # bright "stars": the 500x branch of src/losses.py fires
     m.output_size = t.shape[-1]
-    grads = []
-    for mb in (2, 1):
-        opt.zero_grad()
-        for s in range(0, 2, mb):
-            pred = hybrid_forward(m, x[s:s + mb], accumulate_into_grad=True, drop_path_rate=0.0)
-            loss, _ = crit(pred, t[s:s + mb])
-            (loss * (mb / 2)).backward()
-        grads.append(opt.flat_grad.clone())
-    err = _rel(grads[1], grads[0])
-    print(f'micro-batch vs full-batch gradient rel err {err:.2e}')
-    assert err <= 1e-3
+    # (a) the whole batch through hybrid_forward at once; (b) train_step's plan (stage 1 on the batch, stage 2 in slices of
+    # one patch, input gradients collected) with a zero learning rate so that the parameters stay put
+    opt.zero_grad()
+    loss, _ = crit(hybrid_forward(m, x, accumulate_into_grad=True, drop_path_rate=0.0), t)
+    loss.backward()
+    g_full, l_full = opt.flat_grad.clone(), loss.item()
+    opt.param_groups[0]['lr'] = 0.0
+    l_step = train_step(m, opt, crit, x, t, micro_batch=1, max_norm=1.0, drop_path_rate=0.0).item()
+    opt.param_groups[0]['lr'] = 2e-4
+    err = _rel(opt.flat_grad, g_full)
+    print(f'train_step (micro-batch 1) vs full-batch gradient rel err {err:.2e}, loss {l_step:.6f} vs {l_full:.6f}')
+    assert err <= 1e-3 and abs(l_step - l_full) <= 1e-4 * abs(l_full)
     losses = [train_step(m, opt, crit, x, t, micro_batch=1, max_norm=1.0).item() for _ in range(5)]
     print('losses', [round(v, 4) for v in losses])
     assert all(math.isfinite(v) for v in losses) and losses[-1] < losses[0]
