@@ -166,6 +166,10 @@ int srb_conv3x3_cout1(const void* in, int in_pitch, const float* w, const float*
 int srb_lrelu_bwd(void* g, int g_pitch, const void* y, int y_pitch, size_t npx, int C, float slope, void* stream);
 int srb_axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b,
               const void* y, int y_f32, int y_pitch, size_t npx, int C, void* stream);
+/* srb_axpby_samples   out = a_samples[px / npx_per_sample] * x + b * y: the per-sample DropPath factor of a residual branch
+ *                     (upstream drop_path(): keep-mask / keep_prob per sample) fused with the residual add; a_samples on device */
+int srb_axpby_samples(void* out, int out_f32, int out_pitch, const float* a_samples, size_t npx_per_sample, const void* x,
+                      int x_f32, int x_pitch, float b, const void* y, int y_f32, int y_pitch, size_t npx, int C, void* stream);
 int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int B, int h, int w, int C, void* stream);
 
 /* srb_blur               AntiCheckerboardLayer.forward (reference src/architecture.py:9-27): depthwise binomial blur with zero

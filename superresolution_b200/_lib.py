@@ -41,6 +41,7 @@ _PROTOS = {
     'srb_resample_separable': (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     'srb_lrelu_bwd': (_i, [_vp, _i, _vp, _i, _sz, _i, _f, _vp]),
     'srb_axpby': (_i, [_vp, _i, _i, _f, _vp, _i, _i, _f, _vp, _i, _i, _sz, _i, _vp]),
+    'srb_axpby_samples': (_i, [_vp, _i, _i, _vp, _sz, _vp, _i, _i, _f, _vp, _i, _i, _sz, _i, _vp]),
     'srb_upsample2x_bwd': (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
     'srb_layernorm96_bwd_scratch_bytes': (_sz, []),
     'srb_layernorm96': (_i, [_vp, _vp, _vp, _vp, _sz, _vp]),

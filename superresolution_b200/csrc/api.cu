@@ -239,6 +239,12 @@ int srb_axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int
     if (!out || !x || npx == 0 || C <= 0) { set_error("axpby: bad args"); return SRB_E_ARG; }
     return axpby(out, out_f32, out_pitch, a, x, x_f32, x_pitch, b, y, y_f32, y_pitch, npx, C, (cudaStream_t)stream);
 }
+int srb_axpby_samples(void* out, int out_f32, int out_pitch, const float* a_samples, size_t npx_per_sample, const void* x,
+                      int x_f32, int x_pitch, float b, const void* y, int y_f32, int y_pitch, size_t npx, int C, void* stream) {
+    if (!out || !x || !a_samples || npx == 0 || C <= 0) { set_error("axpby_samples: bad args"); return SRB_E_ARG; }
+    return axpby(out, out_f32, out_pitch, 1.f, x, x_f32, x_pitch, b, y, y_f32, y_pitch, npx, C, (cudaStream_t)stream, a_samples,
+                 npx_per_sample);
+}
 int srb_upsample2x_bwd(const void* g, int g_pitch, void* out, int out_pitch, int B, int h, int w, int C, void* stream) {
     if (!g || !out || B <= 0 || h <= 0 || w <= 0) { set_error("upsample2x_bwd: bad args"); return SRB_E_ARG; }
     return upsample2x_bwd((const bf16*)g, g_pitch, (bf16*)out, out_pitch, B, h, w, C, (cudaStream_t)stream);

@@ -75,7 +75,8 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
 // train_ops.cu
 int lrelu_bwd(bf16* g, int g_pitch, const bf16* y, int y_pitch, size_t npx, int C, float slope, cudaStream_t s);
 int axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b, const void* y,
-          int y_f32, int y_pitch, size_t npx, int C, cudaStream_t s);
+          int y_f32, int y_pitch, size_t npx, int C, cudaStream_t s, const float* a_vec = nullptr,
+          size_t npx_per_sample = 0);
 int upsample2x_bwd(const bf16* g, int g_pitch, bf16* out, int out_pitch, int B, int h, int w, int C, cudaStream_t s);
 
 size_t layernorm96_bwd_scratch_bytes();

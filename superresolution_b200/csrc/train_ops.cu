@@ -54,13 +54,14 @@ __device__ __forceinline__ void store4(void* p, int f32, size_t idx, float4 v) {
 
 // out = a * x + b * y  (y optional); every operand bf16 or fp32 with its own channel pitch; out may alias x or y
 __global__ void __launch_bounds__(256)
-axpby_kernel(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b,
-             const void* y, int y_f32, int y_pitch, size_t npx, int C) {
+axpby_kernel(void* out, int out_f32, int out_pitch, float a0, const float* __restrict__ a_vec, size_t npx_per_sample,
+             const void* x, int x_f32, int x_pitch, float b, const void* y, int y_f32, int y_pitch, size_t npx, int C) {
     const int cg = C >> 2;
     const size_t n = npx * cg;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const size_t px = i / cg;
         const int c = (int)(i - px * cg) * 4;
+        const float a = a_vec ? a0 * __ldg(a_vec + px / npx_per_sample) : a0;  // per-sample factor (DropPath)
         float4 v = load4(x, x_f32, px * x_pitch + c);
         v.x *= a; v.y *= a; v.z *= a; v.w *= a;
         if (y) {
@@ -122,7 +123,8 @@ int lrelu_bwd(bf16* g, int g_pitch, const bf16* y, int y_pitch, size_t npx, int 
 }
 
 int axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f32, int x_pitch, float b, const void* y,
-          int y_f32, int y_pitch, size_t npx, int C, cudaStream_t s) {
+          int y_f32, int y_pitch, size_t npx, int C, cudaStream_t s, const float* a_vec, size_t npx_per_sample) {
+    if (a_vec && (npx_per_sample == 0 || npx % npx_per_sample)) { set_error("axpby: npx must be a multiple of npx_per_sample"); return SRB_E_ARG; }
     if (C % 4 || out_pitch % 4 || x_pitch % 4 || (y && y_pitch % 4) ||
         (((uintptr_t)out | (uintptr_t)x | (uintptr_t)y) & 7)) {
         set_error("axpby: C and pitches must be multiples of 4, pointers 8-byte aligned (16 for fp32)");
@@ -132,8 +134,8 @@ int axpby(void* out, int out_f32, int out_pitch, float a, const void* x, int x_f
         set_error("axpby: fp32 operands must be 16-byte aligned");
         return SRB_E_ARG;
     }
-    axpby_kernel<<<grid_for(npx * (C / 4)), 256, 0, s>>>(out, out_f32, out_pitch, a, x, x_f32, x_pitch, b, y, y_f32,
-                                                         y_pitch, npx, C);
+    axpby_kernel<<<grid_for(npx * (C / 4)), 256, 0, s>>>(out, out_f32, out_pitch, a, a_vec, npx_per_sample, x, x_f32, x_pitch,
+                                                         b, y, y_f32, y_pitch, npx, C);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -141,6 +141,16 @@ def axpby(out, a, x, b=0.0, y=None):
     return out
 
 
+def axpby_samples(out, a, x, b=0.0, y=None):
+    """out[n] = a[n] * x[n] + b * y[n] on NHWC tensors; a: fp32 device tensor [B] (per-sample DropPath factors)."""
+    f32 = lambda t: int(t is not None and t.dtype == torch.float32)
+    assert a.dtype == torch.float32 and a.numel() == out.shape[0] and a.is_cuda
+    L.check(L.lib().srb_axpby_samples(L.ptr(out), f32(out), out.stride(2), L.ptr(a), out.shape[1] * out.shape[2], L.ptr(x),
+                                      f32(x), x.stride(2), float(b), L.ptr(y), f32(y), 0 if y is None else y.stride(2),
+                                      _npx(out), out.shape[3], L.current_stream()), 'axpby_samples')
+    return out
+
+
 def upsample2x_bwd(g, out=None):
     """g: bf16 [B,2h,2w,C] -> bf16 [B,h,w,C], sum over each 2x2 block (backward of nearest 2x upsampling)."""
     B, H2, W2, C = g.shape

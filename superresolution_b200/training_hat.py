@@ -38,15 +38,13 @@ def drop_path_masks(B, rate, training, device):
     if not training or rate == 0.0:
         return None
     keep = 1.0 - rate
-    m = (keep + torch.rand(B, device=device)).floor_() / keep
-    return [float(v) for v in m.tolist()]
+    return (keep + torch.rand(B, device=device)).floor_() / keep  # stays on the device: no sync in the step
 
 
-def _scale_samples(t, m):
-    out = torch.empty_like(t)
-    for b, a in enumerate(m):
-        ops.axpby(out[b:b + 1], a, t[b:b + 1])
-    return out
+def _scale_samples(t, m, plus=None):
+    """m[b] * t[b] (+ plus[b]): one pass; m = per-sample factors (device tensor, or a list in tests)"""
+    a = torch.as_tensor(m, dtype=torch.float32).to(t.device)
+    return ops.axpby_samples(torch.empty_like(t), a, t, 0.0 if plus is None else 1.0, plus)
 
 
 class _Tape:
@@ -109,16 +107,14 @@ def _mlp_fwd(T, pre, x1, m):
     if m is None:
         x2 = T.conv(ha, 192, pre + 'mlp.fc2', res1=x1)
     else:
-        br = _scale_samples(T.conv(ha, 192, pre + 'mlp.fc2'), m)
-        x2 = ops.axpby(torch.empty_like(x1), 1.0, x1, 1.0, br)
-    return x2, (x1n, hp)
+        x2 = _scale_samples(T.conv(ha, 192, pre + 'mlp.fc2'), m, plus=x1)
+    return x2, (x1n, hp, ha)  # ha is kept: recomputing it costs a full HBM pass over [tokens, 192]
 
 
 def _mlp_bwd(G, pre, x1, saved, m, g2):
     """g2 = dL/dx2 -> dL/dx1 (identity path included)"""
-    x1n, hp = saved
+    x1n, hp, ha = saved
     gb = g2 if m is None else _scale_samples(g2, m)
-    ha = ops.gelu(hp)
     G.wgrad(pre + 'mlp.fc2', ha, 192, gb, 96, 1)
     dha = G.dgrad(pre + 'mlp.fc2', gb)
     dhp = ops.gelu(hp, dha, out=dha)
@@ -147,15 +143,14 @@ def _hab_fwd(T, pre, x, shift, rpi, m1, m2):
     if m1 is None:
         x1 = T.conv(ao, 96, pre + 'attn.proj', res1=tmp)
     else:
-        br = _scale_samples(T.conv(ao, 96, pre + 'attn.proj'), m1)
-        x1 = ops.axpby(tmp, 1.0, tmp, 1.0, br)
+        x1 = _scale_samples(T.conv(ao, 96, pre + 'attn.proj'), m1, plus=tmp)
     x2, mlp_saved = _mlp_fwd(T, pre, x1, m2)
-    return x2, (x, xn, qkv, bias, ao, c1p, c2, ca_saved, x1, mlp_saved)
+    return x2, (x, xn, qkv, bias, ao, c1p, c1, c2, ca_saved, x1, mlp_saved)
 
 
 def _hab_bwd(G, pre, saved, shift, rpi, m1, m2, g2):
     P = G.P
-    x, xn, qkv, bias, ao, c1p, c2, ca_saved, x1, mlp_saved = saved
+    x, xn, qkv, bias, ao, c1p, c1, c2, ca_saved, x1, mlp_saved = saved
     B, H, W, _ = x.shape
     g1 = _mlp_bwd(G, pre, x1, mlp_saved, m2, g2)                       # dL/dx1
     # ---- attention branch
@@ -177,7 +172,6 @@ def _hab_bwd(G, pre, saved, shift, rpi, m1, m2, g2):
     G.g[ca_pre + '3.weight'] = dw2.view(96, 3, 1, 1)
     G.g[ca_pre + '3.bias'] = db2
     dc2 = dc2.view(B, H, W, 96)
-    c1 = ops.gelu(c1p)
     G.wgrad(pre + 'conv_block.cab.2', c1, 32, dc2, 96, 9)
     dc1 = G.dgrad(pre + 'conv_block.cab.2', dc2)
     dc1p = ops.gelu(c1p, dc1, out=dc1)
