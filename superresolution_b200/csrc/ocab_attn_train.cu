@@ -100,6 +100,12 @@ template <int NT>
 __device__ __forceinline__ void oa_logits(const OcaArgs& a, const bf16* sQ, const bf16* sKV, int h, int mt, int key0, int lane,
                                           float (&s)[NT][4]) {
     const int g = lane >> 2, t = lane & 3;
+    // bias rows come from L2: issue the loads before the ldmatrix + MMA sequence that covers their latency
+    const float* b0 = a.bias + ((size_t)h * 64 + 16 * mt + g) * OA_NK + key0 + 2 * t;
+    const float* b1 = b0 + 8 * OA_NK;
+    float2 bu[NT], bv[NT];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) { bu[j] = __ldg((const float2*)(b0 + 8 * j)); bv[j] = __ldg((const float2*)(b1 + 8 * j)); }
     uint32_t qa[4];
     frag_a(qa, sQ, QP, 16 * mt, 0, lane);
 #pragma unroll
@@ -111,13 +117,10 @@ __device__ __forceinline__ void oa_logits(const OcaArgs& a, const bf16* sQ, cons
         mma16816(s[j], qa[0], qa[1], qa[2], qa[3], kb[0], kb[1]);
         mma16816(s[j + 1], qa[0], qa[1], qa[2], qa[3], kb[2], kb[3]);
     }
-    const float* b0 = a.bias + ((size_t)h * 64 + 16 * mt + g) * OA_NK + key0 + 2 * t;
-    const float* b1 = b0 + 8 * OA_NK;
 #pragma unroll
     for (int j = 0; j < NT; ++j) {
-        const float2 u = __ldg((const float2*)(b0 + 8 * j)), v = __ldg((const float2*)(b1 + 8 * j));
-        s[j][0] = fmaf(s[j][0], 0.25f, u.x); s[j][1] = fmaf(s[j][1], 0.25f, u.y);
-        s[j][2] = fmaf(s[j][2], 0.25f, v.x); s[j][3] = fmaf(s[j][3], 0.25f, v.y);
+        s[j][0] = fmaf(s[j][0], 0.25f, bu[j].x); s[j][1] = fmaf(s[j][1], 0.25f, bu[j].y);
+        s[j][2] = fmaf(s[j][2], 0.25f, bv[j].x); s[j][3] = fmaf(s[j][3], 0.25f, bv[j].y);
     }
 }
 

@@ -87,6 +87,14 @@ __device__ __forceinline__ bool stage(const WinArgs& a, int win, int h, bf16* sT
 __device__ __forceinline__ void probs(const WinArgs& a, const bf16* sT, const uint8_t* sRid, bool mixed, int h, int mt,
                                       int lane, float (&s)[8][4]) {
     const int g = lane >> 2, t = lane & 3;
+    // the bias rows come from L2 (the shared-memory carve-out leaves almost no L1): issue the loads first so that the
+    // ldmatrix + MMA sequence below covers their latency
+    const int r0 = 16 * mt + g, r1 = r0 + 8;
+    const float* b0 = a.bias + ((size_t)h * 64 + r0) * 64 + 2 * t;
+    const float* b1 = b0 + 8 * 64;
+    float2 bu[8], bv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { bu[j] = __ldg((const float2*)(b0 + 8 * j)); bv[j] = __ldg((const float2*)(b1 + 8 * j)); }
     uint32_t qa[4];
     frag_a(qa, sT, RP, 16 * mt, 0, lane);
 #pragma unroll
@@ -98,14 +106,10 @@ __device__ __forceinline__ void probs(const WinArgs& a, const bf16* sT, const ui
         mma16816(s[j], qa[0], qa[1], qa[2], qa[3], kb[0], kb[1]);
         mma16816(s[j + 1], qa[0], qa[1], qa[2], qa[3], kb[2], kb[3]);
     }
-    const int r0 = 16 * mt + g, r1 = r0 + 8;
-    const float* b0 = a.bias + ((size_t)h * 64 + r0) * 64 + 2 * t;
-    const float* b1 = b0 + 8 * 64;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const float2 u = __ldg((const float2*)(b0 + 8 * j)), v = __ldg((const float2*)(b1 + 8 * j));
-        s[j][0] = fmaf(s[j][0], 0.25f, u.x); s[j][1] = fmaf(s[j][1], 0.25f, u.y);
-        s[j][2] = fmaf(s[j][2], 0.25f, v.x); s[j][3] = fmaf(s[j][3], 0.25f, v.y);
+        s[j][0] = fmaf(s[j][0], 0.25f, bu[j].x); s[j][1] = fmaf(s[j][1], 0.25f, bu[j].y);
+        s[j][2] = fmaf(s[j][2], 0.25f, bv[j].x); s[j][3] = fmaf(s[j][3], 0.25f, bv[j].y);
     }
     if (mixed) {
         const int q0 = sRid[r0], q1 = sRid[r1];

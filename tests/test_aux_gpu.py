@@ -111,6 +111,22 @@ def test_tiled_frame_matches_oracle_blend(cuda):
     bands = [tiling.infer_frame(m, frame, tile, stride, batch=4, rank=r, world=2, out_dtype=torch.float32)[0]
              for r in range(2)]
     assert np.abs(torch.cat(bands).cpu().numpy() - ref).max() < 1e-5
+    # seams='p2p': every tile computed once, the overhanging partial sums handed to the next rank (here through an
+    # in-process stand-in for the isend / irecv pair; the real exchange is covered by the gloo test on CPU)
+    strips = {}
+
+    def handover(sums, plan_all, rank, group=None):
+        _, own0, own1, end = plan_all[rank]
+        if rank + 1 < len(plan_all) and end > own1:
+            strips[rank] = sums[:, own1 - own0:].clone()
+        if rank - 1 in strips:
+            sums[:, :strips[rank - 1].shape[1]] += strips[rank - 1]
+        return sums
+
+    parts = [tiling.infer_frame(m, frame, tile, stride, batch=4, rank=r, world=2, out_dtype=torch.float32, seams='p2p',
+                                _exchange=handover) for r in range(2)]
+    assert [p[1] for p in parts] == [(0, 96), (96, 320)] and strips[0].shape[1] == 32
+    assert np.abs(torch.cat([p[0] for p in parts]).cpu().numpy() - ref).max() < 1e-5
     u16, _ = tiling.infer_frame(m, frame, tile, stride, batch=16)
     want = (np.clip(out.cpu().numpy(), 0, 1) * 65535).astype(np.uint16)
     assert np.abs(u16.cpu().numpy().astype(np.int64) - want.astype(np.int64)).max() <= 1

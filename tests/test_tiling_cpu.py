@@ -103,3 +103,72 @@ def test_bucketed_gradient_allreduce_world2():
     for _, head, tot in res:
         assert head == want[:5].tolist()
         assert abs(tot - float(want.double().sum())) < 1e-6
+
+
+def _seam_worker(rank, world, port, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from superresolution_b200 import tiling
+    from oracle import tiling as otil
+    H, W = 128, 80
+    tile, stride, scale = 32, 24, 4
+    ov = scale * (tile - stride)
+    rng = np.random.default_rng(0)
+    origins = tiling.plan(H, W, tile, stride)
+    outs = {o: rng.random((scale * tile, scale * tile), dtype=np.float32) for o in origins}  # stand-in tile outputs
+    FH, FW = scale * H, scale * W
+    plan_all = tiling.seam_plan(H, tile, stride, scale, world)
+    rows, own0, own1, end = plan_all[rank]
+    sums = np.zeros((2, end - own0, FW), np.float32)
+    for (y, x), t in outs.items():
+        if y not in rows:
+            continue
+        w = np.outer(otil.ramp(scale * tile, ov), otil.ramp(scale * tile, ov)).astype(np.float32)
+        oy, ox = scale * y - own0, scale * x
+        sums[0, oy:oy + scale * tile, ox:ox + scale * tile] += w * t
+        sums[1, oy:oy + scale * tile, ox:ox + scale * tile] += w
+    sums = tiling.exchange_seams_planned(torch.from_numpy(sums), plan_all, rank).numpy()
+    mine = sums[0, :own1 - own0] / np.maximum(sums[1, :own1 - own0], 1e-30)
+    parts = [None] * world
+    dist.all_gather_object(parts, (own0, own1, mine))
+    if rank == 0:
+        ref = otil.blend(list(outs.values()), [(scale * y, scale * x) for (y, x) in outs], FH, FW, ov)
+        got = np.zeros_like(ref)
+        covered = np.zeros(FH, bool)
+        for a, b, m in parts:
+            got[a:b] = m
+            assert not covered[a:b].any()
+            covered[a:b] = True
+        q.put((bool(covered.all()), float(np.abs(got - ref).max()), [len(p[0]) for p in plan_all]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_three_rank_seam_exchange_matches_single_rank():
+    """seams='p2p': tile rows dealt out by count, every tile computed once, overhanging partial sums shipped to the next
+    rank point-to-point — the stitched frame equals the single-rank blend (fp32 addition order differs: 1e-6)."""
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_seam_worker, args=(r, 3, port, q)) for r in range(3)]
+    for p in procs:
+        p.start()
+    covered, err, counts = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert covered and err < 1e-6
+    assert sum(counts) == 5 and max(counts) - min(counts) <= 1  # 5 tile rows over 3 ranks, none computed twice
+
+
+def test_seam_plan_partitions_rows_and_tiles():
+    from superresolution_b200 import tiling
+    for world in (1, 2, 3, 8, 50):
+        pl = tiling.seam_plan(4096, 128, 96, 4, world)
+        rows = [y for p in pl for y in p[0]]
+        assert rows == tiling.tile_origins(4096, 128, 96)           # every tile row exactly once
+        edges = [(p[1], p[2]) for p in pl if p[0]]
+        assert edges[0][0] == 0 and edges[-1][1] == 16384
+        assert all(edges[i][1] == edges[i + 1][0] for i in range(len(edges) - 1))
+        assert all(p[3] - p[2] <= 4 * 128 for p in pl)               # a strip is at most one tile high

@@ -22,7 +22,7 @@ from superresolution_b200 import tiling  # noqa: E402
 from superresolution_b200.architecture import HybridSuperResolutionModel  # noqa: E402
 from superresolution_b200.losses import CombinedLoss  # noqa: E402
 from superresolution_b200.metrics import _psnr_ssim  # noqa: E402
-from superresolution_b200.normalization import log_normalize_u16  # noqa: E402
+from superresolution_b200.normalization import log_normalize_u16, robust_stats  # noqa: E402
 from superresolution_b200.optim import FusedAdamW  # noqa: E402
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -51,7 +51,7 @@ def timed(fn, warmup=2, iters=5):
     return ts[len(ts) // 2]
 
 
-def bench_frame(size, rank, world):
+def bench_frame(size, rank, world, seams='recompute'):
     dev = torch.device('cuda', torch.cuda.current_device())
     torch.manual_seed(0)
     model = HybridSuperResolutionModel(output_size=512).to(dev).eval()
@@ -61,7 +61,7 @@ def bench_frame(size, rank, world):
     out = {}
 
     def run():
-        out['y'], out['band'] = tiling.infer_frame(model, frame, rank=rank, world=world)
+        out['y'], out['band'] = tiling.infer_frame(model, frame, rank=rank, world=world, seams=seams)
 
     ms = timed(run, warmup=1, iters=3)
     if world > 1:
@@ -71,7 +71,7 @@ def bench_frame(size, rank, world):
     r0, r1 = out['band']
     if rank == 0:
         print(json.dumps({'workload': f'config3: {size}x{size} u16 frame, 128-px tiles stride 96, 4x output u16',
-                          'n_gpus': world, 'tiles': ntiles, 'frame_ms': round(ms, 2),
+                          'n_gpus': world, 'seams': seams, 'tiles': ntiles, 'frame_ms': round(ms, 2),
                           'output_mpix_per_s': round(16 * size * size / 1e6 / (ms / 1e3), 2),
                           'tiles_per_s': round(ntiles / (ms / 1e3), 1), 'band_rows_rank0': [r0, r1],
                           'timing': 'CUDA events around infer_frame (tile gather, forwards, blend, finalise); '
@@ -102,6 +102,23 @@ def bench_aux(pairs):
                       'ms': round(ms, 3), 'pairs_per_s': round(nchunks * chunk / (ms / 1e3)),
                       'roofline': {'bound': 'hbm', 'achieved': round(gbs, 1), 'peak': peak, 'unit': 'GB/s',
                                    'frac': round(gbs / peak, 3), 'algorithmic_bytes_per_px': 6, 'peak_source': src}}))
+
+    # the step before the normalisation: exact black / white percentiles of the HR population
+    stats = {}
+
+    def rstats():
+        stats['v'] = robust_stats([hr] * nchunks, 3.0)
+
+    ms = timed(rstats, warmup=1, iters=3)
+    px = nchunks * hr.numel()
+    gbs = px * 12 / 1e9 / (ms / 1e3)
+    print(json.dumps({'workload': f'config5c: robust stats (3rd / 99.99th percentile of log1p over the valid pixels) of '
+                                  f'{nchunks * chunk} HR[512,512] fp32 images, exact 3-level radix select',
+                      'ms': round(ms, 3), 'gmin_gmax': [float(stats['v'][0]), float(stats['v'][1])],
+                      'roofline': {'bound': 'hbm', 'achieved': round(gbs, 1), 'peak': peak, 'unit': 'GB/s',
+                                   'frac': round(gbs / peak, 3), 'algorithmic_bytes_per_px': 12,
+                                   'note': 'three 4-byte reads per pixel (one per radix level); includes 3 host syncs',
+                                   'peak_source': src}}))
     del hr, lr
 
     t = torch.rand(chunk, 1, 512, 512, device=dev, generator=g)
@@ -165,6 +182,7 @@ def main():
     ap.add_argument('what', nargs='*', default=['frame', 'aux'])
     ap.add_argument('--frame-size', type=int, default=4096)
     ap.add_argument('--pairs', type=int, default=10000)
+    ap.add_argument('--seams', default='recompute', choices=['recompute', 'p2p'])
     a = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
@@ -175,7 +193,7 @@ def main():
         bench_aux(a.pairs)
         bench_optim()
     if 'frame' in a.what:
-        bench_frame(a.frame_size, rank, world)
+        bench_frame(a.frame_size, rank, world, a.seams)
     if world > 1:
         torch.distributed.destroy_process_group()
 
