@@ -7,8 +7,8 @@
 //   level 0: histogram of bits[30:21]            (1024 bins)
 //   level 1: histogram of bits[20:10] where bits[31:21] == prefix  (2048 bins, up to 4 prefixes at once)
 //   level 2: histogram of bits[9:0]   where bits[31:10] == prefix  (1024 bins, up to 4 prefixes)
-// Per-block shared-memory histograms; intra-warp conflicts on the (heavily populated) sky-background bin are removed by
-// __match_any_sync aggregation; block partials are added to the 64-bit global bins at the end.
+// Per-block shared-memory histograms (native u32 atomics); a warp whose 32 pixels fall into one bin (the heavily populated
+// sky background) issues a single add of 32; block partials are added to the 64-bit global bins at the end.
 #include "common.h"
 #include "ops.h"
 
@@ -44,11 +44,18 @@ radix_hist_kernel(const float* __restrict__ x, size_t n, RsParams p, unsigned lo
             for (int j = 0; j < RS_MAXP; ++j)
                 if (j < p.nprefix && pre == p.prefix[j]) { ok = true; slot = j; break; }
         }
+        if (!__any_sync(0xFFFFFFFFu, ok)) return;  // levels 1 / 2: most warps hold no pixel of the wanted prefixes
         const uint32_t key = ok ? (uint32_t)slot * RS_BINS + ((b >> p.bin_shift) & p.bin_mask) : 0xFFFFFFFFu;
-        const unsigned peers = __match_any_sync(0xFFFFFFFFu, key);
-        if (ok && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&sh[key], (uint32_t)__popc(peers));
+        // sky background: the whole warp usually lands in one bin -> one add of 32; otherwise native shared-memory
+        // integer atomics (few lanes collide once the keys differ)
+        const uint32_t k0 = __shfl_sync(0xFFFFFFFFu, key, 0);
+        if (__all_sync(0xFFFFFFFFu, key == k0)) {
+            if ((threadIdx.x & 31) == 0) atomicAdd(&sh[key], 32u);
+        } else if (ok) {
+            atomicAdd(&sh[key], 1u);
+        }
     };
-    // every thread of a warp runs the same number of iterations (match_any needs the full warp)
+    // every thread of a warp runs the same number of iterations (the warp votes need the full warp)
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t iters = (n4 + stride - 1) / stride;
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
