@@ -127,6 +127,13 @@ size_t srb_psnr_ssim_scratch_bytes(int B, int H, int W);
 int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, void* scratch,
                   void* stream);
 int srb_log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, void* stream);
+/* srb_to_u16          save_as_tiff16's conversion (scripts/Modello_5.py:29-33): u16(clip(x, 0, 1) * 65535), truncating cast
+ * srb_preview_strip   the [LR | SR | HR] comparison strip of scripts/Modello_5.py:83-85 / Modello_supporto.py:187-190:
+ *                     cat(nearest-upsampled lr [B,h,w] -> [B,H,W], sr, hr; width).clamp(0,1) -> [B,H,3W]; out_u8 = 0: fp32,
+ *                     1: uint8 with torchvision save_image's rounding (x*255 + 0.5, clamp, truncate) */
+int srb_to_u16(const float* x, uint16_t* out, size_t n, void* stream);
+int srb_preview_strip(const float* lr, const float* sr, const float* hr, void* out, int out_u8, int B, int h, int w, int H,
+                      int W, void* stream);
 /* srb_robust_hist   one level of the exact percentile search behind calculate_robust_stats
  *                   (scripts/Dataset_step4_normalization.py:55-91): over the valid pixels of x (finite, >= thresh > 0)
  *                   ADD into hist (u64, zeroed by the caller) the counts of  level 0: bits[30:21] (1 x 2048 bins);

@@ -36,6 +36,8 @@ _PROTOS = {
     'srb_conv_wgrad': (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     'srb_upsample2x_nearest': (_i, [_vp, _i, _vp, _i, _i, _i, _vp]),
     'srb_conv3x3_cout1': (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    'srb_to_u16': (_i, [_vp, _vp, _sz, _vp]),
+    'srb_preview_strip': (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     'srb_robust_hist': (_i, [_vp, _sz, _f, _i, _vp, _i, _vp, _vp]),
     'srb_blur': (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     'srb_resample_separable': (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),

@@ -212,6 +212,15 @@ int srb_conv3x3_cout1(const void* in, int in_pitch, const float* w, const float*
     if (!in || !w || !bias || !out || B <= 0 || in_pitch % 8) { set_error("conv3x3_cout1: bad args"); return SRB_E_ARG; }
     return conv_cout1((const bf16*)in, in_pitch, w, bias, out, B, H, W, (cudaStream_t)stream);
 }
+int srb_to_u16(const float* x, uint16_t* out, size_t n, void* stream) {
+    if (!x || !out || n == 0) { set_error("to_u16: bad args"); return SRB_E_ARG; }
+    return convert_out(x, out, SRB_U16, n, (cudaStream_t)stream);
+}
+int srb_preview_strip(const float* lr, const float* sr, const float* hr, void* out, int out_u8, int B, int h, int w, int H,
+                      int W, void* stream) {
+    if (!lr || !sr || !hr || !out || B <= 0 || h <= 0 || w <= 0 || H <= 0 || W <= 0) { set_error("preview_strip: bad args"); return SRB_E_ARG; }
+    return preview_strip(lr, sr, hr, out, out_u8, B, h, w, H, W, (cudaStream_t)stream);
+}
 int srb_robust_hist(const float* x, size_t n, float thresh, int level, const uint32_t* prefixes, int nprefix,
                     unsigned long long* hist, void* stream) {
     if (!x || !hist || n == 0) { set_error("robust_hist: bad args"); return SRB_E_ARG; }

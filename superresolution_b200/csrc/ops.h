@@ -19,6 +19,8 @@ int blur(const float* in, void* out, int out_dtype, int mode, int B, int H, int 
 int resample_separable(const float* in, float* out, int B, int Hi, int Wi, int Ho, int Wo, const int* iy, const float* wy,
                        const int* ix, const float* wx, int K, cudaStream_t s);
 int convert_out(const float* in, void* out, int out_dtype, size_t n, cudaStream_t s);
+int preview_strip(const float* lr, const float* sr, const float* hr, void* out, int out_u8, int B, int h, int w, int H, int W,
+                  cudaStream_t s);
 
 // robust_stats.cu
 int robust_hist(const float* x, size_t n, float thresh, int level, const uint32_t* prefixes, int nprefix,

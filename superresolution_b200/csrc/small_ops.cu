@@ -263,6 +263,44 @@ __global__ void convert_out_kernel(const float* __restrict__ in, void* __restric
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// K8c: validation / preview strip of scripts/Modello_5.py:83-85 and Modello_supporto.py:187-190:
+//   comp = cat(F.interpolate(lr, size=(H, W), mode='nearest'), sr, hr, dim=3).clamp(0, 1)   -> [B, H, 3W]
+// out_dtype F32 = comp itself; U8 = torchvision save_image's quantisation (x * 255 + 0.5, clamp, truncate).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+preview_strip_kernel(const float* __restrict__ lr, const float* __restrict__ sr, const float* __restrict__ hr,
+                     void* __restrict__ out, int out_u8, int B, int h, int w, int H, int W, float sy, float sx) {
+    const unsigned n = (unsigned)B * H * 3 * W;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned row = i / (3u * W);
+        const int c = (int)(i - row * 3u * W), y = (int)(row % (unsigned)H), b = (int)(row / (unsigned)H);
+        float v;
+        if (c < W) {  // ATen nearest: src = min(floor(dst * in / out), in - 1), the ratio in fp32
+            const int yy = min((int)floorf(y * sy), h - 1), xx = min((int)floorf(c * sx), w - 1);
+            v = lr[((size_t)b * h + yy) * w + xx];
+        } else if (c < 2 * W) {
+            v = sr[((size_t)b * H + y) * W + c - W];
+        } else {
+            v = hr[((size_t)b * H + y) * W + c - 2 * W];
+        }
+        v = fminf(fmaxf(v, 0.f), 1.f);
+        if (out_u8) ((uint8_t*)out)[i] = (uint8_t)fminf(fmaxf(v * 255.f + 0.5f, 0.f), 255.f);
+        else ((float*)out)[i] = v;
+    }
+}
+
+int preview_strip(const float* lr, const float* sr, const float* hr, void* out, int out_u8, int B, int h, int w, int H, int W,
+                  cudaStream_t s) {
+    const size_t n = (size_t)B * H * 3 * W;
+    if (n >= ((size_t)1 << 31)) { set_error("preview_strip: tensor too large for 32-bit indexing"); return SRB_E_SHAPE; }
+    int grid = (int)((n + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    preview_strip_kernel<<<grid, 256, 0, s>>>(lr, sr, hr, out, out_u8, B, h, w, H, W, (float)h / (float)H, (float)w / (float)W);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
 int convert_out(const float* in, void* out, int out_dtype, size_t n, cudaStream_t s) {
     int grid = (int)((n + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;

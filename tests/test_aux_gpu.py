@@ -195,3 +195,28 @@ def test_robust_stats_without_valid_pixels_falls_back(cuda):
     x[0] = -3.0
     x[1] = 0.0
     assert robust_stats([x.to(cuda)]) == (np.float32(0.0), np.float32(1.0))
+
+
+def test_tiff16_and_preview_glue(cuda, tmp_path):
+    """save_as_tiff16 (Modello_5.py:29-33), the TIFF load of src/dataset.py:24-41 and the [LR|SR|HR] strip of
+    Modello_5.py:83-85 against their reference expressions (PIL / torch on the CPU)."""
+    from PIL import Image
+    from superresolution_b200 import io16
+    g = torch.Generator().manual_seed(21)
+    sr = torch.rand(1, 1, 64, 96, generator=g) * 1.2 - 0.1           # values outside [0,1] exercise the clip
+    io16.save_as_tiff16(sr.to(cuda), tmp_path / 'sr.tiff')
+    want = (np.clip(sr.squeeze().numpy(), 0, 1) * 65535).astype(np.uint16)
+    got = np.array(Image.open(tmp_path / 'sr.tiff'))
+    assert got.dtype == np.uint16 and np.array_equal(got, want)
+    back = io16.load_tiff_as_tensor(tmp_path / 'sr.tiff', cuda)
+    ref = torch.from_numpy(np.array(Image.open(tmp_path / 'sr.tiff'), dtype=np.float32) / 65535.0).unsqueeze(0)
+    assert back.dtype == torch.uint16 and torch.equal(back.cpu().float() / 65535.0, ref)
+    for (h, w), (H, W) in (((16, 24), (64, 96)), ((20, 30), (64, 96))):  # integer and fractional nearest ratios
+        lr = torch.rand(2, 1, h, w, generator=g)
+        s2 = torch.rand(2, 1, H, W, generator=g) * 1.2 - 0.1
+        hr = torch.rand(2, 1, H, W, generator=g)
+        comp = torch.cat((torch.nn.functional.interpolate(lr, size=(H, W), mode='nearest'), s2, hr), dim=3).clamp(0, 1)
+        out = io16.preview_strip(lr.to(cuda), s2.to(cuda), hr.to(cuda))
+        assert torch.equal(out.cpu(), comp)
+        q = io16.preview_strip(lr.to(cuda), s2.to(cuda), hr.to(cuda), quantize=True)
+        assert torch.equal(q.cpu(), comp.mul(255).add_(0.5).clamp_(0, 255).to(torch.uint8))  # torchvision save_image

@@ -68,3 +68,18 @@ def test_oracle_robust_stats_matches_reference_formula_on_a_tiny_case():
     v = np.log1p(np.array([1, 2, 3, 4], dtype=np.float32))
     assert lo == np.percentile(v, 3.0) and hi == np.percentile(v, 99.99)
     assert aux.robust_stats([np.zeros((2, 2), np.float32)]) == (0.0, 1.0)
+
+
+# ---- 16-bit TIFF container (host code, no kernel) -----------------------------------------------------------
+@pytest.mark.parametrize('shape', [(37, 53), (128, 128), (1, 7)])
+def test_tiff16_codec_round_trips_with_pil(tmp_path, shape):
+    import numpy as np
+    from PIL import Image
+    from superresolution_b200 import io16
+    a = np.random.default_rng(shape[0]).integers(0, 65536, shape, dtype=np.uint16)
+    io16.write_tiff16(a, tmp_path / 'ours.tiff')
+    pil = Image.open(tmp_path / 'ours.tiff')
+    assert pil.mode == 'I;16' and np.array_equal(np.array(pil), a)          # what src/dataset.py:28-31 would read
+    Image.fromarray(a).save(tmp_path / 'pil.tiff')                          # what Modello_5.save_as_tiff16 writes
+    assert np.array_equal(io16.read_tiff16(tmp_path / 'pil.tiff'), a)
+    assert np.array_equal(io16.read_tiff16(tmp_path / 'ours.tiff'), a)
