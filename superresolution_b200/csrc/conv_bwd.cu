@@ -10,7 +10,8 @@
 //                    tile = (co block x ci block) x all taps from one haloed X tile, mma.sync.m16n8k16 with
 //                    ldmatrix.trans fragments from XOR-swizzled shared memory, fp32 partials + fixed-order
 //                    reduction (deterministic, no atomics).
-//   bias gradient    db[co] = sum_px dY[px][co]: two-level column sum.
+//   bias gradient    db[co] = sum_px dY[px][co]: per-split column sums taken from the dY tiles the weight-gradient kernel
+//                    has staged in shared memory anyway, then a fixed-order sum over the splits.
 #include <cuda_bf16.h>
 
 #include "common.h"
@@ -59,6 +60,7 @@ struct WgradArgs {
     const bf16* x;   // [B,H,W,x_pitch]  layer input (channels [0,Cin))
     const bf16* dy;  // [B,H,W,dy_pitch] gradient of the layer output (channels [0,Cout))
     float* partial;  // [ksplit][taps][Cout][Cin]
+    float* bpartial; // [ksplit][Cout] column sums of dY per split (bias gradient), or nullptr
     int x_pitch, dy_pitch, B, H, W, Cin, Cout, taps;
     int nchunks, chunks_per_split;
 };
@@ -109,7 +111,7 @@ __device__ __forceinline__ void wg_load_chunk(const WgradArgs& a, int chunk, int
 }
 
 template <int WM, int TAPS>
-__global__ void __launch_bounds__(WG_THREADS)
+__global__ void __launch_bounds__(WG_THREADS, 2)
 conv_wgrad_kernel(const WgradArgs a) {
     using T = WgTile<WM, TAPS>;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -120,6 +122,14 @@ conv_wgrad_kernel(const WgradArgs a) {
     const int c_begin = blockIdx.y * a.chunks_per_split;
     const int c_end = min(a.nchunks, c_begin + a.chunks_per_split);
 
+    // bias gradient = column sums of dY: the dY tile is already in shared memory, so the CTAs of the first ci tile add
+    // their 32 pixels per chunk here (thread = one output channel) instead of a separate pass over dY
+    // thread = (16-byte unit of 8 channels, pixel slot): one 16-byte load per chunk, 8 register sums kept over all chunks,
+    // folded over the pixel slots once after the loop.
+    constexpr int BSLOTS = WG_THREADS / T::UM < WG_KC ? WG_THREADS / T::UM : WG_KC;  // 32 pixel slots (UM 4 or 8)
+    const int bu = tid % T::UM, bslot = tid / T::UM;
+    const bool do_bias = a.bpartial != nullptr && ci0 == 0 && bslot < BSLOTS;
+    float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float acc[TAPS][2][4];
 #pragma unroll
     for (int t = 0; t < TAPS; ++t)
@@ -143,6 +153,20 @@ conv_wgrad_kernel(const WgradArgs a) {
             const int sn = (cn - c_begin) % WG_STAGES;
             if (cn < c_end) wg_load_chunk<WM, TAPS>(a, cn, co0, ci0, smem + sn * T::STAGE, tid);
             cp_async_commit();
+        }
+        if (do_bias) {
+            const uint8_t* sd = smem + st * T::STAGE;
+#pragma unroll
+            for (int px = bslot; px < WG_KC; px += BSLOTS) {
+                const uint4 raw = *(const uint4*)(sd + (px * T::UM + wg_swz<T::UM>(px, bu)) * 16);
+                const __nv_bfloat162* h2 = (const __nv_bfloat162*)&raw;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h2[k]);
+                    bsum[2 * k] += f.x;
+                    bsum[2 * k + 1] += f.y;
+                }
+            }
         }
         const uint32_t s_dy = smem_u32(smem + st * T::STAGE), s_x = s_dy + T::DY_BYTES;
         // A = dY^T [co 16][px 16] per (k-step, m-tile): memory is [px][co] -> ldmatrix.trans; matrices ordered
@@ -171,6 +195,20 @@ conv_wgrad_kernel(const WgradArgs a) {
         }
     }
     cp_async_wait<0>();
+    if (a.bpartial != nullptr && ci0 == 0) {  // fold the pixel slots (CTA-uniform branch): smem [slot][BM] floats
+        __syncthreads();
+        float* red = (float*)smem;
+        if (do_bias) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) red[bslot * T::BM + bu * 8 + k] = bsum[k];
+        }
+        __syncthreads();
+        if (tid < T::BM && co0 + tid < a.Cout) {
+            float v = 0.f;
+            for (int sl = 0; sl < BSLOTS; ++sl) v += red[sl * T::BM + tid];
+            a.bpartial[(size_t)blockIdx.y * a.Cout + co0 + tid] = v;
+        }
+    }
     // partial[split][tap][co][ci]
     const int g = lane >> 2, tq = lane & 3;
 #pragma unroll
@@ -229,7 +267,7 @@ __device__ __forceinline__ void wgf_load_chunk(const WgradArgs& a, int chunk, ui
 }
 
 template <int MT, int NT>
-__global__ void __launch_bounds__(WG_THREADS)
+__global__ void __launch_bounds__(WG_THREADS, (MT * NT > 18) ? 1 : 2)
 linear_wgrad_full_kernel(const WgradArgs a) {
     using T = WgFull<MT, NT>;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -237,6 +275,11 @@ linear_wgrad_full_kernel(const WgradArgs a) {
     const int wm = warp >> 2, wn = warp & 3;  // warp tile: co [16 MT wm, +16 MT), ci [8 NT wn, +8 NT)
     const int c_begin = blockIdx.x * a.chunks_per_split;
     const int c_end = min(a.nchunks, c_begin + a.chunks_per_split);
+    // bias gradient: thread = (16-byte unit of 8 channels, pixel slot), 8 register sums over all chunks, folded at the end
+    constexpr int BSLOTS = WG_THREADS / T::UM;  // 7 (qkv), 10 or 21 pixel slots
+    const int bu = tid % T::UM, bslot = tid / T::UM;
+    const bool do_bias = a.bpartial != nullptr && bslot < BSLOTS;
+    float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float acc[MT][NT][4];
 #pragma unroll
     for (int i = 0; i < MT; ++i)
@@ -255,6 +298,19 @@ linear_wgrad_full_kernel(const WgradArgs a) {
             const int cn = c + WG_STAGES - 1;
             if (cn < c_end) wgf_load_chunk<MT, NT>(a, cn, smem + ((cn - c_begin) % WG_STAGES) * T::STAGE, tid);
             cp_async_commit();
+        }
+        if (do_bias) {
+            const uint8_t* sd = smem + st * T::STAGE;
+            for (int px = bslot; px < WG_KC; px += BSLOTS) {
+                const uint4 raw = *(const uint4*)(sd + (px * T::UM + wgf_swz<T::UM>(px, bu)) * 16);
+                const __nv_bfloat162* h2 = (const __nv_bfloat162*)&raw;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(h2[k]);
+                    bsum[2 * k] += f.x;
+                    bsum[2 * k + 1] += f.y;
+                }
+            }
         }
         const uint32_t s_dy = smem_u32(smem + st * T::STAGE), s_x = s_dy + T::DY_BYTES;
         uint32_t bfr[NT][4];  // {b0, b1} of k-step 0 and of k-step 1 per n-tile (lane = pixel)
@@ -279,6 +335,20 @@ linear_wgrad_full_kernel(const WgradArgs a) {
         }
     }
     cp_async_wait<0>();
+    if (a.bpartial) {  // fold the pixel slots: smem [slot][Cout] floats (<= 21 x 96 or 7 x 288)
+        __syncthreads();
+        float* red = (float*)smem;
+        if (do_bias) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) red[bslot * (32 * MT) + bu * 8 + k] = bsum[k];
+        }
+        __syncthreads();
+        for (int co = tid; co < 32 * MT; co += WG_THREADS) {
+            float v = 0.f;
+            for (int sl = 0; sl < BSLOTS; ++sl) v += red[sl * (32 * MT) + co];
+            a.bpartial[(size_t)blockIdx.x * a.Cout + co] = v;
+        }
+    }
     const int g = lane >> 2, tq = lane & 3;
     float* dst = a.partial + (size_t)blockIdx.x * a.Cout * a.Cin;
 #pragma unroll
@@ -321,39 +391,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __
     }
 }
 
-constexpr int BG_ROWS = 256;  // pixels per block of the bias-gradient column sum
-
-// partial[blk][c] = sum over the block's pixels of dy[px][c]  (c < C <= 512, 8 channels per thread)
-__global__ void __launch_bounds__(256)
-bias_grad_partial_kernel(const bf16* __restrict__ dy, int pitch, size_t npx, int C, float* __restrict__ partial) {
-    __shared__ float sm[256 * 8];
-    const int cg = C / 8;               // 16-byte channel groups
-    const int lanes_px = 256 / cg;      // pixel lanes (threads beyond cg * lanes_px idle)
-    const int g = threadIdx.x % cg, pl = threadIdx.x / cg;
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    const size_t p0 = (size_t)blockIdx.x * BG_ROWS;
-    const size_t p1 = p0 + BG_ROWS < npx ? p0 + BG_ROWS : npx;
-    if (pl < lanes_px) {
-        for (size_t p = p0 + pl; p < p1; p += lanes_px) {
-            const uint4 raw = __ldg((const uint4*)(dy + p * pitch + g * 8));
-            const __nv_bfloat162* h = (const __nv_bfloat162*)&raw;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float2 f = __bfloat1622float2(h[k]);
-                acc[2 * k] += f.x;
-                acc[2 * k + 1] += f.y;
-            }
-        }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sm[threadIdx.x * 8 + j] = acc[j];
-    __syncthreads();
-    for (int c = threadIdx.x; c < C; c += 256) {
-        float s = 0.f;
-        for (int l = 0; l < lanes_px; ++l) s += sm[(l * cg + c / 8) * 8 + (c & 7)];
-        partial[(size_t)blockIdx.x * C + c] = s;
-    }
-}
+constexpr int BG_ROWS = 256;  // (scratch sizing only: the column sums now come from the weight-gradient kernels)
 
 // db[c] = (accumulate ? db[c] : 0) + sum_blk partial[blk][c]; one block per channel, fixed-order tree (deterministic)
 __global__ void __launch_bounds__(128)
@@ -402,7 +440,9 @@ size_t conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps
     const int nchunks = B * H * (W / WG_KC);
     const size_t npx = (size_t)B * H * W;
     const size_t wpart = (size_t)wgrad_ksplit(Cin, Cout, taps, nchunks) * taps * Cout * Cin * sizeof(float);
-    const size_t bpart = ((npx + BG_ROWS - 1) / BG_ROWS) * Cout * sizeof(float);
+    const size_t nb = (npx + BG_ROWS - 1) / BG_ROWS;
+    const size_t ks = (size_t)wgrad_ksplit(Cin, Cout, taps, nchunks);
+    const size_t bpart = (nb > ks ? nb : ks) * Cout * sizeof(float);
     return wpart + bpart;
 }
 
@@ -416,12 +456,14 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
         return SRB_E_ARG;
     }
     WgradArgs a;
-    a.x = x; a.dy = dy; a.partial = (float*)scratch;
+    a.x = x; a.dy = dy; a.partial = (float*)scratch; a.bpartial = nullptr;
     a.x_pitch = x_pitch; a.dy_pitch = dy_pitch; a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout; a.taps = taps;
     a.nchunks = B * H * (W / WG_KC);
     const int ksplit = wgrad_ksplit(Cin, Cout, taps, a.nchunks);
     a.chunks_per_split = (a.nchunks + ksplit - 1) / ksplit;
     const int tiles = wgrad_tiles(Cin, Cout);
+    const int n = taps * Cout * Cin;
+    if (db) a.bpartial = a.partial + (size_t)ksplit * n;  // [ksplit][Cout], written by the weight-gradient kernel
     int rc;
     if (wgrad_full_shape(Cin, Cout, taps) && x_pitch >= Cin && dy_pitch >= Cout) {
         rc = Cout == 288 ? launch_wgrad_full<9, 3>(a, ksplit, s)
@@ -431,17 +473,10 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
     } else if (taps == 9) rc = Cout <= 32 ? launch_wgrad<1, 9>(a, tiles, ksplit, s) : launch_wgrad<2, 9>(a, tiles, ksplit, s);
     else rc = Cout <= 32 ? launch_wgrad<1, 1>(a, tiles, ksplit, s) : launch_wgrad<2, 1>(a, tiles, ksplit, s);
     if (rc != SRB_OK) return rc;
-    const int n = taps * Cout * Cin;
     wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(a.partial, dw, ksplit, taps, Cout, Cin, accumulate);
     SRB_CUDA(cudaGetLastError());
     if (db) {
-        const size_t npx = (size_t)B * H * W;
-        float* bpart = a.partial + (size_t)ksplit * n;
-        const int nblk = (int)((npx + BG_ROWS - 1) / BG_ROWS);
-        if (256 / (Cout / 8) < 1) { set_error("conv_wgrad: Cout too large for the bias gradient"); return SRB_E_SHAPE; }
-        bias_grad_partial_kernel<<<nblk, 256, 0, s>>>(dy, dy_pitch, npx, Cout, bpart);
-        SRB_CUDA(cudaGetLastError());
-        bias_grad_final_kernel<<<Cout, 128, 0, s>>>(bpart, nblk, Cout, db, accumulate);
+        bias_grad_final_kernel<<<Cout, 128, 0, s>>>(a.bpartial, ksplit, Cout, db, accumulate);
         SRB_CUDA(cudaGetLastError());
     }
     return SRB_OK;
