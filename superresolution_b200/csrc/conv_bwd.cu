@@ -420,7 +420,7 @@ int wgrad_ksplit(int Cin, int Cout, int taps, int nchunks) {
         return ks < nchunks ? ks : (nchunks < 1 ? 1 : nchunks);
     }
     const int tiles = wgrad_tiles(Cin, Cout);
-    int ks = (num_sms() * 3 + tiles - 1) / tiles;  // ~3 CTAs per SM (<= 45 KB smem, 256 threads each)
+    int ks = (num_sms() * 2 + tiles - 1) / tiles;  // one wave: 2 CTAs per SM are resident (128 registers x 256 threads)
     if (ks > nchunks) ks = nchunks;
     if (ks < 1) ks = 1;
     return ks;

@@ -39,7 +39,7 @@ def test_hat_forward_backward_matches_oracle_autograd(cuda, drop, monkeypatch):
         it = iter([half for mm in masks[1:] for half in mm])
 
         def fake_drop_path(t, p=0.0, training=False):
-            f = torch.tensor(next(it), dtype=t.dtype).view(-1, *([1] * (t.ndim - 1)))
+            f = torch.as_tensor(next(it), dtype=t.dtype).view(-1, *([1] * (t.ndim - 1)))
             return t * f
 
         monkeypatch.setattr(ohat, 'drop_path', fake_drop_path)
