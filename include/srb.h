@@ -191,7 +191,7 @@ int srb_blur(const float* in, void* out, int out_dtype, int mode, int B, int H, 
 int srb_resample_separable(const float* in, float* out, int B, int Hi, int Wi, int Ho, int Wo, const int* iy,
                            const float* wy, const int* ix, const float* wx, int K, void* stream);
 
-/* HAT (stage 2) backward building blocks — tested operators, not yet assembled into a stage-2 training path:
+/* HAT (stage 2) backward building blocks (assembled into the stage-2 training path by superresolution_b200/training_hat.py):
  * srb_layernorm96      y = LayerNorm(x)*gamma + beta over 96 channels, eps 1e-5 (nn.LayerNorm of HAT), bf16 [ntok,96]
  * srb_layernorm96_bwd  dx = LN backward of g (+ res, bf16 or fp32, optional: the shortcut's gradient), dgamma / dbeta
  *                      (+= when accumulate); deterministic two-level reduction; scratch: srb_layernorm96_bwd_scratch_bytes()

@@ -153,7 +153,7 @@ int upsample2x_bwd(const bf16* g, int g_pitch, bf16* out, int out_pitch, int B, 
 }  // namespace srb
 
 // ---------------------------------------------------------------------------------------------------------------
-// HAT building blocks (stage-2 backward, not yet assembled): LayerNorm(96) backward and exact-erf GELU forward/backward
+// HAT building blocks of the stage-2 training path (training_hat.py): LayerNorm(96) backward, exact-erf GELU forward/backward
 // ---------------------------------------------------------------------------------------------------------------
 namespace srb {
 

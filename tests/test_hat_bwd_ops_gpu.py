@@ -1,6 +1,6 @@
 """HAT (stage 2) backward building blocks against torch autograd in fp32 on the same bf16-rounded inputs:
 LayerNorm(96) forward / backward (+ fused shortcut gradient), exact-erf GELU forward / backward.
-(tested operators for the stage-2 training path, which is not assembled yet.)"""
+(the operators the stage-2 training path of training_hat.py is assembled from.)"""
 import pytest
 import torch
 import torch.nn.functional as F

@@ -90,7 +90,7 @@ def test_drives_model_parameters_and_repack(cuda):
     x = torch.rand(1, 1, 32, 32, device=cuda)
     with torch.no_grad():
         y0 = m(x)
-    # gradient on one tensor only (the model backward is not built): d loss / d conv_last.bias through the loss kernel
+    # gradient on one tensor only (this test is about the optimizer): d loss / d conv_last.bias through the loss kernel
     t = torch.rand_like(y0)
     bias = m.stage2.conv_last.bias
     loss, _ = CombinedLoss()(y0 + bias.view(1, 1, 1, 1) * 0 + (bias - bias.detach()).view(1, 1, 1, 1), t)

@@ -1,7 +1,7 @@
-"""Training-step measurement of what exists of BASELINE config 4: the STAGE-1 (RRDBNet) half of the hybrid model,
-batch 32 of 128x128 patches per GPU, loss = src/losses.py, gradient SUM all-reduce over the ranks (NCCL), fused
-unscale + clip(1.0) + AdamW(5e-4, wd 0).  The HAT backward is not built, so this is NOT the config-4 number; it is the
-measured cost of the built half: 3 x 146.7 GFLOP x 32 = 14.1 TFLOP per step and GPU.
+"""Training-step measurement of the STAGE-1 (RRDBNet) half of the hybrid model alone: batch 32 of 128x128 patches per GPU,
+loss = src/losses.py, gradient SUM all-reduce over the ranks (NCCL), fused unscale + clip(1.0) + AdamW(5e-4, wd 0).
+This is NOT the config-4 number (tools/bench_train.py measures the whole hybrid step); it isolates the cost of the first
+stage: 3 x 146.7 GFLOP x 32 = 14.1 TFLOP per step and GPU.
 
 usage: python tools/bench_train_stage1.py [--batch 32] [--steps 5] [--warmup 2]
        python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/bench_train_stage1.py"""
