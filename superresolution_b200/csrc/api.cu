@@ -96,6 +96,27 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
     return conv_tc_launch(a, (cudaStream_t)stream);
 }
 
+int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed, const float* bias, void* out_bf16,
+                             int out_pitch, int B, int H, int W, int Cin, int Cout, int taps, int act, float slope,
+                             const void* res1, int res1_f32, int res1_pitch, void* pre_out, int pre_pitch,
+                             const void* gelu_grad_of, int gelu_grad_pitch, void* stream) {
+    if (!in || !w_packed || !out_bf16 || B <= 0) { set_error("conv_train: bad args"); return SRB_E_ARG; }
+    if (Cout % 32 || ((uintptr_t)pre_out & 15) || ((uintptr_t)gelu_grad_of & 15) || pre_pitch % 8 || gelu_grad_pitch % 8) {
+        set_error("conv_train: Cout %% 32, 16-byte aligned pre_out / gelu_grad_of with pitches %% 8 required");
+        return SRB_E_ARG;
+    }
+    ConvArgs a;
+    memset(&a, 0, sizeof(a));
+    a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout; a.taps = taps;
+    a.in = (const bf16*)in; a.in_pitch = in_pitch; a.w = (const bf16*)w_packed; a.bias = bias;
+    a.act = act; a.slope = slope;
+    a.alpha1 = 1.f; a.res1 = res1; a.res1_f32 = res1_f32; a.res1_pitch = res1_pitch; a.alpha2 = 1.f;
+    a.out = (bf16*)out_bf16; a.out_pitch = out_pitch;
+    a.pre_out = (bf16*)pre_out; a.pre_pitch = pre_pitch;
+    a.gelu_grad_of = (const bf16*)gelu_grad_of; a.gelu_grad_pitch = gelu_grad_pitch;
+    return conv_tc_launch(a, (cudaStream_t)stream);
+}
+
 int srb_expand_rel_bias(const float* table, int T, const int64_t* index, int NK, void* out_bf16, float scale,
                         void* stream) {
     if (!table || !index || !out_bf16 || T <= 0 || (NK != 64 && NK != 144)) {

@@ -51,6 +51,10 @@ struct ConvArgs {
     int pixel_shuffle;                                // 1: out is [B,2H,2W,Cout/4] (PixelShuffle(2) fused in the store)
     float* colsum;                                    // optional [B * tiles_per_image][Cout] fp32: per-tile channel sums of the
                                                       // epilogue result (CAB average pool fused into cab.2; needs Cout == N tile)
+    // training path (both optional): pre_out keeps the pre-activation acc + bias (bf16) next to the activated output;
+    // gelu_grad_of multiplies the result by GELU'(x) of that saved pre-activation (the dgrad conv feeding a GELU)
+    bf16* pre_out; int pre_pitch;
+    const bf16* gelu_grad_of; int gelu_grad_pitch;
 };
 
 int conv_tc_launch(const ConvArgs& a, cudaStream_t stream);

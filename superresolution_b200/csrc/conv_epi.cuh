@@ -17,9 +17,23 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return 0.5f * x * (1.0f + copysignf(e, x));
 }
 
+// GELU'(x) = Phi(x) + x phi(x) with the same erf approximation
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    const float ex = __expf(-z * z);  // exp(-x^2 / 2)
+    const float e = 1.0f - p * t * ex;
+    return fmaf(x * 0.3989422804014327f, ex, 0.5f * (1.0f + copysignf(e, x)));
+}
+
 // bias + activation + residuals on one 32-channel slice of one pixel (all indices compile-time after unrolling)
 // sbias: the layer's bias staged in shared memory by the kernel prologue (zeros when the layer has none); a global
 // __ldg per unit sat on the epilogue's critical path (~500 cycles per 128 x 32 block).
+template <bool TRAIN = false>
 __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a, size_t pix, int cb, int b,
                                               const float* sbias = nullptr) {
     if (sbias) {
@@ -35,12 +49,37 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
             v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
         }
     }
+    if (TRAIN && a.pre_out) {
+        uint4* pp = (uint4*)(a.pre_out + pix * a.pre_pitch + cb);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint4 o;
+            __nv_bfloat162* h = (__nv_bfloat162*)&o;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[8 * j + 2 * k], v[8 * j + 2 * k + 1]);
+            pp[j] = o;
+        }
+    }
     if (a.act == ACT_LRELU) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * a.slope;
     } else if (a.act == ACT_GELU) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+    }
+    if (TRAIN && a.gelu_grad_of) {
+        const uint4* gp = (const uint4*)(a.gelu_grad_of + pix * a.gelu_grad_pitch + cb);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint4 rr = __ldg(gp + j);
+            const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 f = __bfloat1622float2(h[k]);
+                v[8 * j + 2 * k] *= gelu_erf_grad(f.x);
+                v[8 * j + 2 * k + 1] *= gelu_erf_grad(f.y);
+            }
+        }
     }
     if (a.res1) {
         if (a.res1_f32) {

@@ -35,9 +35,12 @@
 
 namespace srb {
 
-template <int N_TILE_, int MT_, int TAPS_>
+// TRAIN_: the epilogue also honours ConvArgs::pre_out / gelu_grad_of (training path).  A compile-time flag: the two
+// extra run-time tests in the inference epilogue cost 0.4 ms per batch-16 forward when they were unconditional.
+template <int N_TILE_, int MT_, int TAPS_, bool TRAIN_ = false>
 struct ConvCfg {
     static constexpr int N_TILE = N_TILE_, MT = MT_, TAPS = TAPS_;
+    static constexpr bool TRAIN = TRAIN_;
     static constexpr int HALO = (TAPS == 9) ? 1 : 0;
     static constexpr int TH = 16, TW = 8 * MT;
     static constexpr int PH = TH + 2 * HALO, PW = TW + 2 * HALO;
@@ -300,7 +303,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
                     PH_BEGIN();
-                    epilogue_math(v, a, pix, cb, b, sbias);
+                    epilogue_math<Cfg::TRAIN>(v, a, pix, cb, b, sbias);
                     PH_END(ph_math);
                     if (a.out32) {
                         float4* op = (float4*)(a.out32 + pix * a.out32_pitch + cb);
@@ -542,6 +545,12 @@ int conv_tc_launch(const ConvArgs& a_in, cudaStream_t stream) {
         return SRB_E_ARG;
     }
     if (a.pixel_shuffle && (a.Cout % 128 || !a.out)) { set_error("conv_tc: pixel_shuffle needs Cout%%128==0"); return SRB_E_ARG; }
+    if (a.pre_out || a.gelu_grad_of) {  // training-path epilogue: instantiated for the two shapes that use it
+        if (a.taps == 1 && a.Cout % 96 == 0) return launch_cfg<ConvCfg<96, 2, 1, true>>(a, stream);
+        if (a.taps == 9 && a.Cout == 32 && a.W % 32 == 0) return launch_cfg<ConvCfg<32, 4, 9, true>>(a, stream);
+        set_error("conv_tc: pre_out / gelu_grad_of need a linear with Cout %% 96 == 0 or a 3x3 conv with Cout == 32, W %% 32 == 0");
+        return SRB_E_SHAPE;
+    }
     if (a.taps == 9) {
         if (a.Cout == 32) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<32, 4, 9>>(a, stream) : launch_cfg<ConvCfg<32, 2, 9>>(a, stream);
         if (a.Cout == 64) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<64, 4, 9>>(a, stream) : launch_cfg<ConvCfg<64, 2, 9>>(a, stream);

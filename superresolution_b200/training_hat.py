@@ -62,6 +62,15 @@ class _Tape:
         return out
 
 
+    def conv_gelu(self, x, cin, name):
+        """(GELU(conv(x)), conv(x)): the activated output and the bf16 pre-activation the backward needs, one kernel"""
+        w, b = self.P[name + '.weight'], self.P[name + '.bias']
+        B, H, W = x.shape[:3]
+        pre = torch.empty(B, H, W, w.shape[0], dtype=torch.bfloat16, device=x.device)
+        act = ops.conv_nhwc_train(x, cin, ops.pack_conv_weight(w), b, act=L.ACT_GELU, pre_out=pre)
+        return act, pre
+
+
 class _Grads:
     def __init__(self, P):
         self.P = P
@@ -72,13 +81,17 @@ class _Grads:
         self.g[name + '.weight'] = dw
         self.g[name + '.bias'] = db
 
-    def dgrad(self, name, dy, out=None, acc=False):
-        """out (+)= conv^T(dy) through the weights of `name` (3x3 conv or Linear)"""
+    def dgrad(self, name, dy, out=None, acc=False, gelu_grad_of=None):
+        """out (+)= conv^T(dy) through the weights of `name` (3x3 conv or Linear); with ``gelu_grad_of`` (the saved
+        pre-activation that fed a GELU producing this layer's input) the result is multiplied by GELU' of it"""
         w = self.P[name + '.weight']
         cout, cin = w.shape[0], w.shape[1]
         if out is None:
             B, H, W = dy.shape[:3]
             out = torch.empty(B, H, W, cin, dtype=torch.bfloat16, device=dy.device)
+        if gelu_grad_of is not None:
+            assert not acc
+            return ops.conv_nhwc_train(dy, cout, ops.pack_conv_weight_dgrad(w), None, out=out, gelu_grad_of=gelu_grad_of)
         ops.conv_nhwc(dy, cout, ops.pack_conv_weight_dgrad(w), None, out=out, res1=out if acc else None)
         return out
 
@@ -102,8 +115,7 @@ def _ln(P, name, x):
 def _mlp_fwd(T, pre, x1, m):
     P = T.P
     x1n = _ln(P, pre + 'norm2', x1)
-    hp = T.conv(x1n, 96, pre + 'mlp.fc1')
-    ha = ops.gelu(hp)
+    ha, hp = T.conv_gelu(x1n, 96, pre + 'mlp.fc1')
     if m is None:
         x2 = T.conv(ha, 192, pre + 'mlp.fc2', res1=x1)
     else:
@@ -116,8 +128,7 @@ def _mlp_bwd(G, pre, x1, saved, m, g2):
     x1n, hp, ha = saved
     gb = g2 if m is None else _scale_samples(g2, m)
     G.wgrad(pre + 'mlp.fc2', ha, 192, gb, 96, 1)
-    dha = G.dgrad(pre + 'mlp.fc2', gb)
-    dhp = ops.gelu(hp, dha, out=dha)
+    dhp = G.dgrad(pre + 'mlp.fc2', gb, gelu_grad_of=hp)
     G.wgrad(pre + 'mlp.fc1', x1n, 96, dhp, 192, 1)
     dx1n = G.dgrad(pre + 'mlp.fc1', dhp)
     return G.ln_bwd(pre + 'norm2', x1, dx1n, res=g2)
@@ -133,8 +144,7 @@ def _hab_fwd(T, pre, x, shift, rpi, m1, m2):
     qkv = T.conv(xn, 96, pre + 'attn.qkv')
     bias = ops.gather_rel_bias(P[pre + 'attn.relative_position_bias_table'], rpi)
     ao = ops.window_attention(qkv, bias, shift)
-    c1p = T.conv(xn, 96, pre + 'conv_block.cab.0')
-    c1 = ops.gelu(c1p)
+    c1, c1p = T.conv_gelu(xn, 96, pre + 'conv_block.cab.0')
     c2 = T.conv(c1, 32, pre + 'conv_block.cab.2')
     ca_pre = pre + 'conv_block.cab.3.attention.'
     ca, ca_saved = ops.channel_attention(c2.view(B, H * W, 96), P[ca_pre + '1.weight'].view(3, 96), P[ca_pre + '1.bias'],
@@ -173,8 +183,7 @@ def _hab_bwd(G, pre, saved, shift, rpi, m1, m2, g2):
     G.g[ca_pre + '3.bias'] = db2
     dc2 = dc2.view(B, H, W, 96)
     G.wgrad(pre + 'conv_block.cab.2', c1, 32, dc2, 96, 9)
-    dc1 = G.dgrad(pre + 'conv_block.cab.2', dc2)
-    dc1p = ops.gelu(c1p, dc1, out=dc1)
+    dc1p = G.dgrad(pre + 'conv_block.cab.2', dc2, gelu_grad_of=c1p)
     G.wgrad(pre + 'conv_block.cab.0', xn, 96, dc1p, 32, 9)
     G.dgrad(pre + 'conv_block.cab.0', dc1p, out=dxn, acc=True)         # both consumers of norm1's output
     return G.ln_bwd(pre + 'norm1', x, dxn, res=g1)
