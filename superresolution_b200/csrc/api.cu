@@ -99,8 +99,9 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
 int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed, const float* bias, void* out_bf16,
                              int out_pitch, int B, int H, int W, int Cin, int Cout, int taps, int act, float slope,
                              const void* res1, int res1_f32, int res1_pitch, void* pre_out, int pre_pitch,
-                             const void* gelu_grad_of, int gelu_grad_pitch, void* stream) {
+                             const void* gelu_grad_of, int gelu_grad_pitch, const float* alpha1_samples, void* stream) {
     if (!in || !w_packed || !out_bf16 || B <= 0) { set_error("conv_train: bad args"); return SRB_E_ARG; }
+    if (alpha1_samples && !res1) { set_error("conv_train: alpha1_samples scales the conv result in front of res1"); return SRB_E_ARG; }
     if (Cout % 32 || ((uintptr_t)pre_out & 15) || ((uintptr_t)gelu_grad_of & 15) || pre_pitch % 8 || gelu_grad_pitch % 8) {
         set_error("conv_train: Cout %% 32, 16-byte aligned pre_out / gelu_grad_of with pitches %% 8 required");
         return SRB_E_ARG;
@@ -114,6 +115,7 @@ int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed,
     a.out = (bf16*)out_bf16; a.out_pitch = out_pitch;
     a.pre_out = (bf16*)pre_out; a.pre_pitch = pre_pitch;
     a.gelu_grad_of = (const bf16*)gelu_grad_of; a.gelu_grad_pitch = gelu_grad_pitch;
+    a.alpha1_samples = alpha1_samples;
     return conv_tc_launch(a, (cudaStream_t)stream);
 }
 

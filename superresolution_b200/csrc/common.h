@@ -55,6 +55,7 @@ struct ConvArgs {
     // gelu_grad_of multiplies the result by GELU'(x) of that saved pre-activation (the dgrad conv feeding a GELU)
     bf16* pre_out; int pre_pitch;
     const bf16* gelu_grad_of; int gelu_grad_pitch;
+    const float* alpha1_samples;                      // optional [B]: per-image alpha1 (DropPath factor of the branch)
 };
 
 int conv_tc_launch(const ConvArgs& a, cudaStream_t stream);

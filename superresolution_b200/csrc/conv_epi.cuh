@@ -82,15 +82,16 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
         }
     }
     if (a.res1) {
+        const float al = (TRAIN && a.alpha1_samples) ? __ldg(a.alpha1_samples + b) : a.alpha1;
         if (a.res1_f32) {
             const float4* rp = (const float4*)((const float*)a.res1 + pix * a.res1_pitch + cb);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const float4 rr = rp[j];
-                v[4 * j] = fmaf(v[4 * j], a.alpha1, rr.x);
-                v[4 * j + 1] = fmaf(v[4 * j + 1], a.alpha1, rr.y);
-                v[4 * j + 2] = fmaf(v[4 * j + 2], a.alpha1, rr.z);
-                v[4 * j + 3] = fmaf(v[4 * j + 3], a.alpha1, rr.w);
+                v[4 * j] = fmaf(v[4 * j], al, rr.x);
+                v[4 * j + 1] = fmaf(v[4 * j + 1], al, rr.y);
+                v[4 * j + 2] = fmaf(v[4 * j + 2], al, rr.z);
+                v[4 * j + 3] = fmaf(v[4 * j + 3], al, rr.w);
             }
         } else {
             const uint4* rp = (const uint4*)((const bf16*)a.res1 + pix * a.res1_pitch + cb);
@@ -101,8 +102,8 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float2 f = __bfloat1622float2(h[k]);
-                    v[8 * j + 2 * k] = fmaf(v[8 * j + 2 * k], a.alpha1, f.x);
-                    v[8 * j + 2 * k + 1] = fmaf(v[8 * j + 2 * k + 1], a.alpha1, f.y);
+                    v[8 * j + 2 * k] = fmaf(v[8 * j + 2 * k], al, f.x);
+                    v[8 * j + 2 * k + 1] = fmaf(v[8 * j + 2 * k + 1], al, f.y);
                 }
             }
         }

@@ -71,6 +71,13 @@ class _Tape:
         return act, pre
 
 
+    def conv_droppath(self, x, cin, name, m, res):
+        """res + m[image] * conv(x): the DropPath-scaled residual branch in the conv epilogue (no extra pass)"""
+        w, b = self.P[name + '.weight'], self.P[name + '.bias']
+        a = torch.as_tensor(m, dtype=torch.float32).to(x.device)
+        return ops.conv_nhwc_train(x, cin, ops.pack_conv_weight(w), b, res1=res, alpha1_samples=a)
+
+
 class _Grads:
     def __init__(self, P):
         self.P = P
@@ -119,7 +126,7 @@ def _mlp_fwd(T, pre, x1, m):
     if m is None:
         x2 = T.conv(ha, 192, pre + 'mlp.fc2', res1=x1)
     else:
-        x2 = _scale_samples(T.conv(ha, 192, pre + 'mlp.fc2'), m, plus=x1)
+        x2 = T.conv_droppath(ha, 192, pre + 'mlp.fc2', m, x1)
     return x2, (x1n, hp, ha)  # ha is kept: recomputing it costs a full HBM pass over [tokens, 192]
 
 
@@ -153,7 +160,7 @@ def _hab_fwd(T, pre, x, shift, rpi, m1, m2):
     if m1 is None:
         x1 = T.conv(ao, 96, pre + 'attn.proj', res1=tmp)
     else:
-        x1 = _scale_samples(T.conv(ao, 96, pre + 'attn.proj'), m1, plus=tmp)
+        x1 = T.conv_droppath(ao, 96, pre + 'attn.proj', m1, tmp)
     x2, mlp_saved = _mlp_fwd(T, pre, x1, m2)
     return x2, (x, xn, qkv, bias, ao, c1p, c1, c2, ca_saved, x1, mlp_saved)
 
