@@ -80,12 +80,14 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
                        int pixel_shuffle, void* stream);
 /* Training-path variant of the same kernel: v = acc + bias; pre_out (bf16, optional) = v; v = act(v) (ACT_GELU = exact-erf
  * GELU); v *= GELU'(gelu_grad_of) (optional: the data-gradient conv that feeds a GELU backward); v = v * alpha + res1 with
- * alpha = alpha1_samples[image] (optional fp32 [B] on the device: the DropPath factor of a residual branch) or 1.  Keeps
+ * alpha = alpha1_samples[image] (optional fp32 [B] on the device: the DropPath factor of a residual branch) or 1; then
+ * v += res2 * res2_cs[image][channel] (optional bf16 tensor and fp32 [B][Cout] scale: HAB's conv_scale * CAB term).  Keeps
  * the pre-activation the backward needs without a separate GELU pass over HBM in either direction.  Cout % 32 == 0. */
 int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed, const float* bias, void* out_bf16,
                              int out_pitch, int B, int H, int W, int Cin, int Cout, int taps, int act, float slope,
                              const void* res1, int res1_f32, int res1_pitch, void* pre_out, int pre_pitch,
-                             const void* gelu_grad_of, int gelu_grad_pitch, const float* alpha1_samples, void* stream);
+                             const void* gelu_grad_of, int gelu_grad_pitch, const float* alpha1_samples, const void* res2,
+                             int res2_pitch, const float* res2_cs, void* stream);
 /* Attention branch of a HAB block (upstream hat_arch.py HAB.forward: norm1 -> (shifted) window_partition -> qkv ->
  * softmax(q k^T * head_dim^-0.5 + relative_position_bias + shift mask) v -> proj -> window_reverse -> + shortcut;
  * reached from src/architecture.py:78) as ONE kernel over tokens x: bf16 [B,H,W,96]:

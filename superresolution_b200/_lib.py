@@ -68,7 +68,7 @@ _PROTOS = {
     'srb_mlp_branch_ln': (_i, [_vp] * 11 + [_sz, _sz, _vp]),
     'srb_fold_ln_linear': (_i, [_vp] * 6 + [_i, _i, _vp]),
     'srb_conv_nhwc_bf16_train': (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _i, _i, _vp, _i,
-                                      _vp, _i, _vp, _vp]),
+                                      _vp, _i, _vp, _vp, _i, _vp, _vp]),
     'srb_conv_nhwc_bf16': (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _f, _vp, _i, _i,
                                 _f, _vp, _i, _i, _vp, _i, _vp]),
 }

@@ -99,7 +99,8 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
 int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed, const float* bias, void* out_bf16,
                              int out_pitch, int B, int H, int W, int Cin, int Cout, int taps, int act, float slope,
                              const void* res1, int res1_f32, int res1_pitch, void* pre_out, int pre_pitch,
-                             const void* gelu_grad_of, int gelu_grad_pitch, const float* alpha1_samples, void* stream) {
+                             const void* gelu_grad_of, int gelu_grad_pitch, const float* alpha1_samples, const void* res2,
+                             int res2_pitch, const float* res2_cs, void* stream) {
     if (!in || !w_packed || !out_bf16 || B <= 0) { set_error("conv_train: bad args"); return SRB_E_ARG; }
     if (alpha1_samples && !res1) { set_error("conv_train: alpha1_samples scales the conv result in front of res1"); return SRB_E_ARG; }
     if (Cout % 32 || ((uintptr_t)pre_out & 15) || ((uintptr_t)gelu_grad_of & 15) || pre_pitch % 8 || gelu_grad_pitch % 8) {
@@ -116,6 +117,7 @@ int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed,
     a.pre_out = (bf16*)pre_out; a.pre_pitch = pre_pitch;
     a.gelu_grad_of = (const bf16*)gelu_grad_of; a.gelu_grad_pitch = gelu_grad_pitch;
     a.alpha1_samples = alpha1_samples;
+    a.res2 = res2; a.res2_f32 = 0; a.res2_pitch = res2_pitch; a.res2_cs = res2_cs;
     return conv_tc_launch(a, (cudaStream_t)stream);
 }
 

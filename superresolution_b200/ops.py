@@ -38,10 +38,11 @@ def conv_nhwc(x, cin, w_packed, bias=None, out=None, out32=None, act=L.ACT_NONE,
 
 
 def conv_nhwc_train(x, cin, w_packed, bias=None, out=None, act=L.ACT_NONE, slope=0.2, res1=None, pre_out=None,
-                    gelu_grad_of=None, alpha1_samples=None):
+                    gelu_grad_of=None, alpha1_samples=None, res2=None, res2_cs=None):
     """conv_nhwc for the training path: optional ``pre_out`` (bf16, receives acc + bias before the activation) and
     ``gelu_grad_of`` (bf16 saved pre-activation: the result is multiplied by GELU' of it); ``alpha1_samples`` (fp32 [B]
-    on the device): out = conv * alpha1_samples[image] + res1.  Returns out."""
+    on the device): out = conv * alpha1_samples[image] + res1; ``res2`` (bf16) with ``res2_cs`` (fp32 [B, Cout]):
+    out += res2 * res2_cs[image, channel].  Returns out."""
     B, H, W = x.shape[:3]
     taps, cout = w_packed.shape[0], w_packed.shape[1]
     assert w_packed.shape[2] == cin
@@ -51,7 +52,8 @@ def conv_nhwc_train(x, cin, w_packed, bias=None, out=None, act=L.ACT_NONE, slope
     L.check(L.lib().srb_conv_nhwc_bf16_train(
         L.ptr(x), x.stride(2), L.ptr(w_packed), L.ptr(bias), L.ptr(out), out.stride(2), B, H, W, cin, cout, taps, act,
         slope, L.ptr(res1), int(res1 is not None and res1.dtype == torch.float32), pitch(res1), L.ptr(pre_out),
-        pitch(pre_out), L.ptr(gelu_grad_of), pitch(gelu_grad_of), L.ptr(alpha1_samples), L.current_stream()),
+        pitch(pre_out), L.ptr(gelu_grad_of), pitch(gelu_grad_of), L.ptr(alpha1_samples), L.ptr(res2), pitch(res2),
+        L.ptr(res2_cs), L.current_stream()),
         'conv_nhwc_bf16_train')
     return out
 

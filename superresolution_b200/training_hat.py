@@ -71,11 +71,15 @@ class _Tape:
         return act, pre
 
 
-    def conv_droppath(self, x, cin, name, m, res):
-        """res + m[image] * conv(x): the DropPath-scaled residual branch in the conv epilogue (no extra pass)"""
+    def conv_droppath(self, x, cin, name, m, res, res2=None, res2_scale=None):
+        """res + m[image] * conv(x) (+ res2_scale * res2): the DropPath-scaled residual branch, and HAB's conv_scale * CAB
+        term, in the conv epilogue (no extra pass); m = None: factor 1"""
         w, b = self.P[name + '.weight'], self.P[name + '.bias']
-        a = torch.as_tensor(m, dtype=torch.float32).to(x.device)
-        return ops.conv_nhwc_train(x, cin, ops.pack_conv_weight(w), b, res1=res, alpha1_samples=a)
+        a = None if m is None else torch.as_tensor(m, dtype=torch.float32).to(x.device)
+        cs = None
+        if res2 is not None:
+            cs = torch.full((x.shape[0], w.shape[0]), float(res2_scale), dtype=torch.float32, device=x.device)
+        return ops.conv_nhwc_train(x, cin, ops.pack_conv_weight(w), b, res1=res, alpha1_samples=a, res2=res2, res2_cs=cs)
 
 
 class _Grads:
@@ -156,11 +160,8 @@ def _hab_fwd(T, pre, x, shift, rpi, m1, m2):
     ca_pre = pre + 'conv_block.cab.3.attention.'
     ca, ca_saved = ops.channel_attention(c2.view(B, H * W, 96), P[ca_pre + '1.weight'].view(3, 96), P[ca_pre + '1.bias'],
                                          P[ca_pre + '3.weight'].view(96, 3), P[ca_pre + '3.bias'])
-    tmp = ops.axpby(torch.empty_like(x), 1.0, x, _CONV_SCALE, ca.view(B, H, W, 96))  # shortcut + conv_x * conv_scale
-    if m1 is None:
-        x1 = T.conv(ao, 96, pre + 'attn.proj', res1=tmp)
-    else:
-        x1 = T.conv_droppath(ao, 96, pre + 'attn.proj', m1, tmp)
+    # x1 = shortcut + DropPath(proj(attention)) + conv_scale * CAB: all three terms in the proj epilogue
+    x1 = T.conv_droppath(ao, 96, pre + 'attn.proj', m1, x, res2=ca.view(B, H, W, 96), res2_scale=_CONV_SCALE)
     x2, mlp_saved = _mlp_fwd(T, pre, x1, m2)
     return x2, (x, xn, qkv, bias, ao, c1p, c1, c2, ca_saved, x1, mlp_saved)
 
