@@ -146,3 +146,53 @@ def test_train_step_micro_batches_equal_full_batch_and_reduce_loss(cuda):
     losses = [train_step(m, opt, crit, x, t, micro_batch=1, max_norm=1.0).item() for _ in range(5)]
     print('losses', [round(v, 4) for v in losses])
     assert all(math.isfinite(v) for v in losses) and losses[-1] < losses[0]
+
+
+def test_reference_training_loop_runs_unchanged(cuda):
+    """The loop body of scripts/Modello_supporto.py:125-141, verbatim (autocast, GradScaler, unscale_, clip_grad_norm_,
+    stock optim.AdamW, zero_grad), over the drop-in module and loss: forward and backward run on libsrb, parameters move,
+    the loss falls, and a state dict saved afterwards loads back strictly (:177-185)."""
+    from superresolution_b200.architecture import HybridSuperResolutionModel
+    from superresolution_b200.losses import CombinedLoss
+    torch.manual_seed(4)
+    device = cuda
+    model = HybridSuperResolutionModel(output_size=256, smoothing='none', device=device).to(device)
+    optimizer = torch.optim.AdamW(model.parameters(), lr=2e-4, weight_decay=0)
+    criterion = CombinedLoss().to(device)
+    scaler = torch.cuda.amp.GradScaler()
+    ACCUM_STEPS = 1
+    g = torch.Generator().manual_seed(10)
+    lr_img = torch.randint(0, 65536, (2, 1, 64, 64), generator=g).float() / 65535.0
+    hr_img = F.interpolate(lr_img, scale_factor=4, mode='bilinear', align_corners=False)
+    batch = {'lr': lr_img, 'hr': hr_img}
+    before = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    model.train()
+    optimizer.zero_grad()
+    losses = []
+    for i in range(4):
+        lr = batch['lr'].to(device, non_blocking=True)
+        hr = batch['hr'].to(device, non_blocking=True)
+        with torch.cuda.amp.autocast():
+            pred = model(lr)
+            loss, _ = criterion(pred, hr)
+            loss = loss / ACCUM_STEPS
+        scaler.scale(loss).backward()
+        if (i + 1) % ACCUM_STEPS == 0:
+            scaler.unscale_(optimizer)
+            gn = torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+            scaler.step(optimizer)
+            scaler.update()
+            optimizer.zero_grad()
+        assert math.isfinite(gn.item()) and gn.item() > 0
+        losses.append(loss.item() * ACCUM_STEPS)
+    print('losses', [round(v, 4) for v in losses])
+    assert losses[-1] < losses[0]
+    after = model.state_dict()
+    moved = sum(int(not torch.equal(before[k], after[k])) for k in before if before[k].is_floating_point())
+    assert moved >= 1200  # every weight / bias tensor of both stages received a gradient and a step
+    model.eval()
+    with torch.inference_mode(), torch.cuda.amp.autocast():
+        v_pred = model(batch['lr'].to(device))          # validation forward of :159-166: the fused inference path
+    assert v_pred.shape == (2, 1, 256, 256) and torch.isfinite(v_pred).all()
+    fresh = HybridSuperResolutionModel(output_size=256, smoothing='none')
+    fresh.load_state_dict({k: v.cpu() for k, v in after.items()}, strict=True)
