@@ -136,3 +136,19 @@ def test_abi_exports_every_declared_symbol():
     assert names == list(sd)  # the C parameter table is the state-dict, in order
     lib.srb_forward_launch_count.restype = ctypes.c_int
     assert lib.srb_forward_launch_count(1, 30, 32, 2, 3) == -1  # SRB_E_SHAPE, host-side check only
+
+
+def test_abi_argument_errors_need_no_gpu():
+    """Argument validation happens before any CUDA call: negative code + message, also on a machine without a GPU."""
+    import ctypes as C
+    from superresolution_b200 import _lib as L
+    lib = L.lib()
+    assert lib.srb_forward_launch_count(16, 128, 128, 2, 3) > 100
+    assert lib.srb_forward_launch_count(16, 100, 128, 2, 3) < 0 and lib.srb_last_error()      # H % 32
+    assert lib.srb_forward_launch_count(16, 128, 128, 2, 5) < 0 and b'stage_mask' in lib.srb_last_error()
+    assert lib.srb_forward_launch_count(16, 128, 128, 9, 3) < 0 and b'smoothing' in lib.srb_last_error()
+    rc = lib.srb_forward(None, L.SRB_F32, None, L.SRB_F32, 1, 32, 32, None, None, 0, 2, 3, None)
+    assert rc < 0 and b'null' in lib.srb_last_error()
+    assert lib.srb_blur(None, None, L.SRB_F32, 2, 1, 8, 8, None) < 0
+    assert lib.srb_robust_hist(None, 0, C.c_float(1e-5), 0, None, 0, None, None) < 0
+    assert lib.srb_workspace_bytes(16, 128, 128) > (1 << 30)
