@@ -1,5 +1,6 @@
 // Fused epilogue arithmetic shared by the tensor-core conv kernels (conv_tc.cu, conv_chain.cu).
 #pragma once
+#include "act.cuh"
 #include "common.h"
 
 namespace srb {
@@ -17,17 +18,17 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return 0.5f * x * (1.0f + copysignf(e, x));
 }
 
-// GELU'(x) = Phi(x) + x phi(x) with the same erf approximation
-__device__ __forceinline__ float gelu_erf_grad(float x) {
-    const float z = fabsf(x) * 0.70710678118654752f;
-    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-    float p = fmaf(1.061405429f, t, -1.453152027f);
-    p = fmaf(p, t, 1.421413741f);
-    p = fmaf(p, t, -0.284496736f);
-    p = fmaf(p, t, 0.254829592f);
-    const float ex = __expf(-z * z);  // exp(-x^2 / 2)
-    const float e = 1.0f - p * t * ex;
-    return fmaf(x * 0.3989422804014327f, ex, 0.5f * (1.0f + copysignf(e, x)));
+// GELU'(x) = Phi(x) + x phi(x) with Phi from the tanh fit of act.cuh (|error| ~1e-4, below the bf16 rounding of the
+// gradient it multiplies): 10 FP32-pipe operations + 2 MUFU.  The TRAIN epilogues are bound by this arithmetic (8 epilogue
+// warps per SM do the work a 64-warp element-wise kernel would), so the cheaper forms are used there.
+__device__ __forceinline__ float gelu_fast_grad(float x) {
+    const float xx = x * x;
+    const float x2 = fminf(xx, 64.f);
+    float p = fmaf(x2, -3.51516789e-4f, 3.70056460e-2f);
+    p = fmaf(p, x2, 7.97507884e-1f);
+    const float t = tanh_approx(x * p);
+    const float phi = 0.3989422804014327f * __expf(-0.5f * xx);
+    return fmaf(x, phi, fmaf(0.5f, t, 0.5f));
 }
 
 // bias + activation + residuals on one 32-channel slice of one pixel (all indices compile-time after unrolling)
@@ -65,7 +66,7 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
         for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * a.slope;
     } else if (a.act == ACT_GELU) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        for (int j = 0; j < 32; ++j) v[j] = TRAIN ? gelu_fast(v[j]) : gelu_erf(v[j]);
     }
     if (TRAIN && a.gelu_grad_of) {
         const uint4* gp = (const uint4*)(a.gelu_grad_of + pix * a.gelu_grad_pitch + cb);
@@ -76,8 +77,8 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const float2 f = __bfloat1622float2(h[k]);
-                v[8 * j + 2 * k] *= gelu_erf_grad(f.x);
-                v[8 * j + 2 * k + 1] *= gelu_erf_grad(f.y);
+                v[8 * j + 2 * k] *= gelu_fast_grad(f.x);
+                v[8 * j + 2 * k + 1] *= gelu_fast_grad(f.y);
             }
         }
     }
