@@ -11,7 +11,7 @@ __device__ __forceinline__ float tanh_approx(float x) {
 }
 
 // nn.GELU() (exact, erf form) evaluated as 0.5 x (1 + tanh(x (c0 + c1 x^2 + c2 x^4))): the odd polynomial is a
-// minimax fit of atanh(erf(x / sqrt 2)) (max |gelu_fast - gelu_erf| = 2.5e-5 over R in exact arithmetic, ~1e-4 with
+// minimax fit of atanh(erf(x / sqrt 2)) (max |gelu_fast - exact GELU| = 2.5e-5 over R in exact arithmetic, ~1e-4 with
 // the 2^-11 relative error of MUFU.TANH) — an order of magnitude below the bf16 rounding of the value that is stored.
 // 7 FP32-pipe operations + 1 MUFU per element instead of ~14 + 2 for the Abramowitz-Stegun erf.
 __device__ __forceinline__ float gelu_fast(float x) {

@@ -5,19 +5,6 @@
 
 namespace srb {
 
-// erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7, i.e. fp32-exact for a bf16 result): exact-GELU semantics of
-// nn.GELU() without the branchy erff().
-__device__ __forceinline__ float gelu_erf(float x) {
-    const float z = fabsf(x) * 0.70710678118654752f;
-    const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-    float p = fmaf(1.061405429f, t, -1.453152027f);
-    p = fmaf(p, t, 1.421413741f);
-    p = fmaf(p, t, -0.284496736f);
-    p = fmaf(p, t, 0.254829592f);
-    const float e = 1.0f - p * t * __expf(-z * z);  // erf(|x|/sqrt2)
-    return 0.5f * x * (1.0f + copysignf(e, x));
-}
-
 // GELU'(x) = Phi(x) + x phi(x) with Phi from the tanh fit of act.cuh (|error| ~1e-4, below the bf16 rounding of the
 // gradient it multiplies): 10 FP32-pipe operations + 2 MUFU.  The TRAIN epilogues are bound by this arithmetic (8 epilogue
 // warps per SM do the work a 64-warp element-wise kernel would), so the cheaper forms are used there.
@@ -66,7 +53,7 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
         for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : v[j] * a.slope;
     } else if (a.act == ACT_GELU) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = TRAIN ? gelu_fast(v[j]) : gelu_erf(v[j]);
+        for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);  // tanh fit of the exact (erf) GELU, see act.cuh
     }
     if (TRAIN && a.gelu_grad_of) {
         const uint4* gp = (const uint4*)(a.gelu_grad_of + pix * a.gelu_grad_pitch + cb);
