@@ -278,7 +278,7 @@ def train_step(model, optimizer, criterion, lr, hr, micro_batch=16, max_norm=1.0
     AdamW — the last three fused in ``FusedAdamW.step``.
 
     Memory plan: stage 1 (RRDBNet, ~0.11 GB of saved activations per patch) runs forward and backward on the WHOLE batch
-    — its 700 small launches are latency-bound below ~16 patches; stage 2 (HAT, ~4.3 GB per patch: it does not fit
+    — its 700 small launches are latency-bound below ~16 patches; stage 2 (HAT, ~5 GB per patch: it does not fit
     180 GB at 32 patches) runs in ``micro_batch``-sized slices of the stage-1 output, each slice forward + loss +
     backward at once, its input gradient collected into the stage-1 output gradient.  Without batch statistics the sum
     of the slice gradients IS the batch gradient; parameter gradients accumulate in the optimizer's flat fp32 buffer.
