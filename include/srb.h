@@ -220,6 +220,11 @@ int srb_window_attention_bwd(const void* qkv, const float* bias, const int* inde
  * srb_overlap_attention_bwd  dqkv[B,H,W,288] from dout[B,H,W,96]; dK/dV of overlapping windows summed per pixel in fixed
  *                            order; dtable[361][6] += (index: int32 [64][144]; atomicAdd: zero it first).
  *                            scratch: srb_overlap_attention_bwd_scratch_bytes(B, H, W). */
+/* srb_overlap_attention_infer  the OCAB core the inference forward (srb_forward) launches: same math, log2 domain.
+ *                            qkv: the q part must arrive scaled by head_dim^-0.5 * log2(e) (srb_forward packs the q rows of
+ *                            overlap_attn.qkv that way); bias_frag_log2e = srb_expand_rel_bias(table [361][6], index
+ *                            int64 [64*144], NK = 144, scale = log2(e)).  out bf16 [B,H,W,96]. */
+int srb_overlap_attention_infer(const void* qkv, const void* bias_frag_log2e, void* out, int B, int H, int W, void* stream);
 size_t srb_overlap_attention_bwd_scratch_bytes(int B, int H, int W);
 int srb_overlap_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, void* stream);
 int srb_overlap_attention_bwd(const void* qkv, const float* bias, const int* index, const void* dout, void* dqkv,

@@ -53,6 +53,7 @@ _PROTOS = {
     'srb_window_attention_bwd': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'srb_overlap_attention_bwd_scratch_bytes': (_sz, [_i, _i, _i]),
     'srb_overlap_attention': (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    'srb_overlap_attention_infer': (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     'srb_overlap_attention_bwd': (_i, [_vp] * 7 + [_i, _i, _i, _vp]),
     'srb_channel_attention_scratch_bytes': (_sz, [_i, _i]),
     'srb_channel_attention': (_i, [_vp] * 10 + [_i, _i, _vp]),

@@ -93,6 +93,7 @@ int srb_conv_nhwc_bf16(const void* in, int in_pitch, const void* w_packed, const
     a.alpha2 = alpha2; a.res2 = res2; a.res2_f32 = res2_f32; a.res2_pitch = res2_pitch; a.res2_cs = res2_cs;
     a.out = (bf16*)out_bf16; a.out_pitch = out_pitch; a.out32 = out_f32; a.out32_pitch = out32_pitch;
     a.pixel_shuffle = pixel_shuffle;
+    a.dyn_weights = 1;  // granular entry: the caller may have packed the weights just before on the same stream
     return conv_tc_launch(a, (cudaStream_t)stream);
 }
 
@@ -118,6 +119,7 @@ int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed,
     a.gelu_grad_of = (const bf16*)gelu_grad_of; a.gelu_grad_pitch = gelu_grad_pitch;
     a.alpha1_samples = alpha1_samples;
     a.res2 = res2; a.res2_f32 = 0; a.res2_pitch = res2_pitch; a.res2_cs = res2_cs;
+    a.dyn_weights = 1;
     return conv_tc_launch(a, (cudaStream_t)stream);
 }
 
@@ -311,6 +313,10 @@ int srb_window_attention_bwd(const void* qkv, const float* bias, const int* inde
                         (cudaStream_t)stream);
 }
 size_t srb_overlap_attention_bwd_scratch_bytes(int B, int H, int W) { return ocab_attn_bwd_scratch_bytes(B, H, W); }
+int srb_overlap_attention_infer(const void* qkv, const void* bias_frag_log2e, void* out, int B, int H, int W, void* stream) {
+    if (!qkv || !bias_frag_log2e || !out || B <= 0) { set_error("overlap_attention_infer: bad args"); return SRB_E_ARG; }
+    return ocab_attention((const bf16*)qkv, (const bf16*)bias_frag_log2e, (bf16*)out, B, H, W, (cudaStream_t)stream);
+}
 int srb_overlap_attention(const void* qkv, const float* bias, void* out, int B, int H, int W, void* stream) {
     if (!qkv || !bias || !out) { set_error("overlap_attention: bad args"); return SRB_E_ARG; }
     return ocab_attn_fwd((const bf16*)qkv, bias, (bf16*)out, B, H, W, (cudaStream_t)stream);

@@ -188,11 +188,8 @@ ocab_attn_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ bias_fra
 
 int ocab_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s) {
     if (H % 8 || W % 8) { set_error("attention: H=%d W=%d must be multiples of the window size 8", H, W); return SRB_E_SHAPE; }
-    static bool attr = false;
-    if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(ocab_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OCA_SMEM));
-        attr = true;
-    }
+    static std::atomic<unsigned long long> attr{0};
+    SRB_TRY(opt_in_dynamic_smem(ocab_attn_kernel, OCA_SMEM, attr));
     ocab_attn_kernel<<<B * (H / 8) * (W / 8), 192, OCA_SMEM, s>>>(qkv, bias_frag, out, H, W);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;

@@ -5,6 +5,8 @@
 #include <stdint.h>
 #include <stddef.h>
 
+#include <atomic>
+
 #include "../../include/srb.h"
 
 namespace srb {
@@ -56,12 +58,31 @@ struct ConvArgs {
     bf16* pre_out; int pre_pitch;
     const bf16* gelu_grad_of; int gelu_grad_pitch;
     const float* alpha1_samples;                      // optional [B]: per-image alpha1 (DropPath factor of the branch)
+    // 1: weights / bias were produced by a kernel enqueued just before this launch (training path: pack kernels run
+    // per step) -> every warp waits for the programmatic dependency before touching them.  0 (inference): weights are
+    // constants packed long before, the weight TMA and the bias prologue overlap the previous layer's tail.
+    int dyn_weights;
 };
 
 int conv_tc_launch(const ConvArgs& a, cudaStream_t stream);
 // chain of dependent 3x3 convs (Cout 32 / 64, common B/H/W) in one persistent kernel with grid barriers (conv_chain.cu)
 int conv_chain_launch(const ConvArgs* layers, int n, unsigned int* counters, cudaStream_t stream);
 int conv_chain_max_layers();
-int num_sms();  // SM count of the current device (cached)
+int num_sms();  // SM count of the current device (cached per device)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device property of a kernel: opt in once per (kernel, device).
+// `done` is the kernel's own bit mask of devices already configured (thread-safe; nn.DataParallel drives several
+// devices from one process, reference scripts/Modello_supporto.py:103-105).
+template <typename Kernel>
+inline int opt_in_dynamic_smem(Kernel* kernel, int bytes, std::atomic<unsigned long long>& done) {
+    int dev = 0;
+    SRB_CUDA(cudaGetDevice(&dev));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
+        SRB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        done.fetch_or(bit, std::memory_order_release);
+    }
+    return SRB_OK;
+}
 
 }  // namespace srb

@@ -349,11 +349,8 @@ int conv_chain_launch(const ConvArgs* layers, int n, unsigned int* counters, cud
             SRB_TRY(encode_bf16_map(&L.tmO, a.out, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B));
         }
     }
-    static bool attr = false;
-    if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(conv_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CHAIN_SMEM));
-        attr = true;
-    }
+    static std::atomic<unsigned long long> attr{0};
+    SRB_TRY(opt_in_dynamic_smem(conv_chain_kernel, CHAIN_SMEM, attr));
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     const int sms = num_sms();

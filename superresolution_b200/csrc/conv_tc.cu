@@ -122,6 +122,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 256); }
         fence_barrier_init();
     }
+    if (a.dyn_weights) pdl_wait();  // weights / bias written by the preceding kernel: no prologue overlap
     for (int i = threadIdx.x; i < a.Cout; i += kThreads) sbias[i] = a.bias ? __ldg(a.bias + i) : 0.f;  // constants
     if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmO); }
     if (warp == 3) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
@@ -440,17 +441,17 @@ int encode_bf16_map(CUtensorMap* m, const void* ptr, int rank, const cuuint64_t*
     return SRB_OK;
 }
 
-static int g_num_sms = 0;
 int num_sms() {
-    if (g_num_sms == 0) {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess &&
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-            g_num_sms = n;
-        else
-            g_num_sms = 148;
+    static std::atomic<int> cache[64];  // per device (zero-initialised)
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    std::atomic<int>& c = cache[dev & 63];
+    n = c.load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        c.store(n, std::memory_order_relaxed);
     }
-    return g_num_sms;
+    return n;
 }
 
 bool env_flag(const char* name, bool dflt) {
@@ -515,11 +516,8 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     } else {
         tmO = tmA;  // unused
     }
-    static int smem_set = 0;  // per template instantiation
-    if (smem_set < smem) {
-        SRB_CUDA(cudaFuncSetAttribute(conv_tc_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit));
-        smem_set = kSmemLimit;
-    }
+    static std::atomic<unsigned long long> smem_set{0};  // per template instantiation, one bit per device
+    SRB_TRY(opt_in_dynamic_smem(conv_tc_kernel<Cfg>, kSmemLimit, smem_set));
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3(t.n_spatial < num_sms() ? t.n_spatial : num_sms());

@@ -512,11 +512,8 @@ int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const 
                      const bf16* bias_frag_log2e, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
                      int W, int shift, cudaStream_t s) {
     if (H % 8 || W % 16) { set_error("hab_attention: H=%d must be a multiple of 8 and W=%d of 16", H, W); return SRB_E_SHAPE; }
-    static bool attr = false;
-    if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(hab_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HAB_TC_SMEM));
-        attr = true;
-    }
+    static std::atomic<unsigned long long> attr{0};
+    SRB_TRY(opt_in_dynamic_smem(hab_tc_kernel, HAB_TC_SMEM, attr));
     HabArgs a;
     a.x = x; a.ln_g = ln_g; a.ln_b = ln_b; a.wqkv = wqkv; a.bqkv = bqkv; a.bias_frag = bias_frag_log2e; a.wproj = wproj;
     a.bproj = bproj; a.xn = xn; a.t = t; a.B = B; a.H = H; a.W = W; a.shift = shift;

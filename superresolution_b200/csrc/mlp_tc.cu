@@ -451,12 +451,9 @@ int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, 
         return SRB_E_ARG;
     }
     if (xn2 && (!ln2_g || !ln2_b || ((uintptr_t)xn2 & 15))) { set_error("mlp_fused: xn2 needs ln2_g / ln2_b and 16-byte alignment"); return SRB_E_ARG; }
-    static bool attr = false;
-    if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(mlp_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MLP_TC_SMEM));
-        SRB_CUDA(cudaFuncSetAttribute(mlp_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MLP_TC_SMEM));
-        attr = true;
-    }
+    static std::atomic<unsigned long long> attr0{0}, attr1{0};
+    SRB_TRY(opt_in_dynamic_smem(mlp_tc_kernel<false>, MLP_TC_SMEM, attr0));
+    SRB_TRY(opt_in_dynamic_smem(mlp_tc_kernel<true>, MLP_TC_SMEM, attr1));
     const size_t nimg_total = ntok / tok_per_img;
     if (ntok % tok_per_img) { set_error("mlp_fused: ntok must be a multiple of tok_per_img"); return SRB_E_SHAPE; }
     const int sms = num_sms();

@@ -149,11 +149,8 @@ conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restric
 int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, float* out, int B, int H, int W,
                cudaStream_t s) {
     if (H % C1_TH || W % C1_TW) { set_error("conv_cout1: H=%d W=%d must be multiples of %dx%d", H, W, C1_TH, C1_TW); return SRB_E_SHAPE; }
-    static bool attr = false;
-    if (!attr) {
-        SRB_CUDA(cudaFuncSetAttribute(conv_cout1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C1_SMEM));
-        attr = true;
-    }
+    static std::atomic<unsigned long long> attr{0};
+    SRB_TRY(opt_in_dynamic_smem(conv_cout1_kernel, C1_SMEM, attr));
     const int ntiles = B * (H / C1_TH) * (W / C1_TW);
     int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;
     conv_cout1_kernel<<<grid, 256, C1_SMEM, s>>>(in, pitch, w, bias, out, B, H, W);

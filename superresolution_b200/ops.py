@@ -276,6 +276,16 @@ def overlap_attention(qkv, bias):
     return out
 
 
+def overlap_attention_infer(qkv_qscaled, bias_frag_log2e):
+    """The OCAB core of the inference forward (csrc/attn.cu).  qkv bf16 [B,H,W,288] whose q part is already scaled by
+    0.25 * log2(e); bias_frag_log2e = expand_rel_bias(table, index, 144, scale=log2(e)).  -> bf16 [B,H,W,96]."""
+    B, H, W, _ = qkv_qscaled.shape
+    out = torch.empty(B, H, W, 96, dtype=torch.bfloat16, device=qkv_qscaled.device)
+    L.check(L.lib().srb_overlap_attention_infer(L.ptr(qkv_qscaled), L.ptr(bias_frag_log2e), L.ptr(out), B, H, W,
+                                                L.current_stream()), 'overlap_attention_infer')
+    return out
+
+
 def overlap_attention_bwd(qkv, bias, index, dout, dtable=None):
     """Returns (dqkv bf16 [B,H,W,288], dtable fp32 [361,6]); dtable is accumulated into when given."""
     B, H, W, _ = qkv.shape

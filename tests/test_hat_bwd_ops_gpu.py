@@ -172,3 +172,30 @@ def test_overlap_attention_forward_backward(cuda, B, H, W):
     err = (dqkv.float() - qr.grad).abs()
     assert (err <= 2e-2 * qr.grad.abs() + 4e-2).all(), err.max().item()
     assert (dtab - tr.grad).abs().max().item() <= 2e-2 * tr.grad.abs().max().item() + 1e-2
+
+
+@pytest.mark.parametrize('B,H,W', [(1, 8, 8), (1, 16, 16), (2, 16, 32), (3, 24, 16), (1, 64, 64)])
+def test_overlap_attention_inference_kernel(cuda, B, H, W):
+    """The OCAB core every inference forward launches (csrc/attn.cu, C ABI srb_overlap_attention_infer) against the same
+    fp32 restatement of upstream OCAB.forward, with a sigma-0.5 bias table: border windows included (8x8 is all border),
+    so the zero-padded keys that stay in the softmax with logit = bias carry real weight."""
+    import math
+    from superresolution_b200 import ops
+    g = torch.Generator().manual_seed(7 * B * 1000 + H + W)
+    qkv = (torch.randn(B, H, W, 288, generator=g) * 1.2).to(cuda).bfloat16()
+    table = (torch.randn(361, 6, generator=g) * 0.5).to(cuda)
+    co = torch.stack(torch.meshgrid(torch.arange(8), torch.arange(8), indexing='ij')).flatten(1)
+    ce = torch.stack(torch.meshgrid(torch.arange(12), torch.arange(12), indexing='ij')).flatten(1)
+    rel = (ce[:, None, :] - co[:, :, None]).permute(1, 2, 0) + (8 - 12 + 1)
+    index = (rel[..., 0] * 19 + rel[..., 1]).to(cuda)
+    ref = _ref_overlap_attention(qkv.float(), table, index)
+    # the inference schedule folds head_dim^-0.5 * log2(e) into the q rows of the qkv linear: emulate on the bf16 tensor
+    qs = qkv.clone()
+    qs[..., :96] = (qkv[..., :96].float() * (0.25 * math.log2(math.e))).bfloat16()
+    bias = ops.expand_rel_bias(table, index, 144, scale=math.log2(math.e))
+    out = ops.overlap_attention_infer(qs, bias)
+    torch.cuda.synchronize()
+    err = (out.float() - ref).abs()
+    bad = (err > 2e-2 * ref.abs() + 3e-2).sum().item()
+    assert bad == 0, f'{bad} mismatches, max err {err.max().item():.4g}'
+    assert err.mean().item() < 6e-3, err.mean().item()
