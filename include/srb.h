@@ -95,7 +95,7 @@ int srb_conv_nhwc_bf16_train(const void* in, int in_pitch, const void* w_packed,
  * window 8, 6 heads, shift 0 or 4 (cyclic shift + the -100 region mask of calculate_mask); H % 8 == 0, W % 16 == 0.
  * wqkv_packed bf16 [288][96], wproj_packed bf16 [96][96] (srb_pack_conv_weight, taps = 1).
  * bias_frag_log2e = srb_expand_rel_bias(table [225][6] fp32, index int64 [64*64] (relative_position_index_SA),
- * NK = 64, scale = log2(e)): the gathered bias in tensor-core fragment order (NK = 144, scale 1 for OCAB). */
+ * NK = 64, scale = log2(e)): the gathered bias in the kernel-ready order of the consuming kernel (opaque to callers). */
 int srb_expand_rel_bias(const float* table, int T, const int64_t* index, int NK, void* out_bf16, float scale,
                         void* stream);
 int srb_hab_attention(const void* x, const float* ln_g, const float* ln_b, const void* wqkv_packed, const float* bqkv,

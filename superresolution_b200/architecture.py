@@ -17,6 +17,20 @@ _BINOMIAL = {3: [1, 2, 1], 5: [1, 4, 6, 4, 1], 7: [1, 6, 15, 20, 15, 6, 1]}
 _DIVISOR = {3: 16.0, 5: 256.0, 7: 1600.0}  # the reference's literal divisors (7x7 sums to 2.56, :13)
 
 
+def named_params(module):
+    """``module.named_parameters()`` that also works on ``nn.DataParallel`` replicas: ``replicate()`` empties
+    ``_parameters`` and keeps the broadcast copies (non-leaf, differentiable back to the originals) as plain attributes
+    listed in ``_former_parameters`` (reference scripts/Modello_supporto.py:103-105 wraps the model in DataParallel)."""
+    out = []
+    for mname, mod in module.named_modules():
+        replica = getattr(mod, '_is_replica', False) and hasattr(mod, '_former_parameters')
+        src = mod._former_parameters if replica else mod._parameters
+        for k, p in src.items():
+            if p is not None:
+                out.append(((mname + '.' if mname else '') + k, p))
+    return out
+
+
 def _conv(cin, cout, k=3):
     return nn.Conv2d(cin, cout, k, 1, k // 2)
 
@@ -238,20 +252,25 @@ class HybridSuperResolutionModel(nn.Module):
         else:
             self.s1 = self.s2 = self.sf = nn.Identity()
         self._smoothing = L.SMOOTHING[self.s1.mode] if smoothing != 'none' else L.SMOOTHING['none']
-        # engine state (never part of state_dict)
+        # engine state (never part of state_dict).  One entry per CUDA device: nn.DataParallel replicas share this dict
+        # (replicate() copies __dict__ shallowly) and each replica thread only touches its own device's entry.
         self._names = None
-        self._packed = None
-        self._packed_key = None
-        self._ws = {}
+        self._engine = {}
 
     # ---- engine --------------------------------------------------------------------------------------------
     def _param_list(self):
         lib = L.lib()
         if self._names is None:
             self._names = [lib.srb_param_name(i).decode() for i in range(lib.srb_param_count())]
-        sd = dict(self.named_parameters())
+        sd = dict(named_params(self))
         sd.update(dict(self.named_buffers()))
         return [sd[n] for n in self._names]
+
+    def _dev_state(self, dev):
+        st = self._engine.get(dev.index)
+        if st is None:
+            st = self._engine[dev.index] = {'packed': None, 'key': None, 'ws': {}}
+        return st
 
     def pack_weights(self, force=False):
         """(Re)build the kernel-ready bf16 / fp32 weight image when parameters changed (tracked by tensor version
@@ -259,32 +278,34 @@ class HybridSuperResolutionModel(nn.Module):
         lib = L.lib()
         tensors = self._param_list()
         key = tuple((t.data_ptr(), t._version) for t in tensors)
-        if force or self._packed is None or key != self._packed_key:
-            dev = tensors[0].device
-            if dev.type != 'cuda':
-                raise RuntimeError('HybridSuperResolutionModel (libsrb) needs its parameters on a CUDA device; '
-                                   'there is no CPU path. Call .to("cuda").')
+        dev = tensors[0].device
+        if dev.type != 'cuda':
+            raise RuntimeError('HybridSuperResolutionModel (libsrb) needs its parameters on a CUDA device; '
+                               'there is no CPU path. Call .to("cuda").')
+        st = self._dev_state(dev)
+        if force or st['packed'] is None or key != st['key']:
             srcs = []
             for n, t in zip(self._names, tensors):
                 want = torch.int64 if 'relative_position_index' in n else torch.float32
                 srcs.append(t.detach().to(want).contiguous())
             ptrs = (C.c_void_p * len(srcs))(*[t.data_ptr() for t in srcs])
-            if self._packed is None or self._packed.device != dev:
-                self._packed = torch.empty(lib.srb_packed_bytes(), dtype=torch.uint8, device=dev)
+            if st['packed'] is None:
+                st['packed'] = torch.empty(lib.srb_packed_bytes(), dtype=torch.uint8, device=dev)
             with torch.cuda.device(dev):
-                L.check(lib.srb_pack_weights(ptrs, len(srcs), L.ptr(self._packed), self._packed.numel(),
+                L.check(lib.srb_pack_weights(ptrs, len(srcs), L.ptr(st['packed']), st['packed'].numel(),
                                              L.current_stream()), 'pack_weights')
             # srcs must outlive the enqueued copies: same stream ordering + caching allocator make this safe
-            self._packed_key = key
-        return self._packed
+            st['key'] = key
+        return st['packed']
 
     def _workspace(self, B, H, W, dev):
-        k = (B, H, W, dev)
-        ws = self._ws.get(k)
+        k = (B, H, W)
+        cache = self._dev_state(dev)['ws']
+        ws = cache.get(k)
         if ws is None:
-            self._ws.clear()
+            cache.clear()
             ws = torch.empty(L.lib().srb_workspace_bytes(B, H, W), dtype=torch.uint8, device=dev)
-            self._ws[k] = ws
+            cache[k] = ws
         return ws
 
     def run(self, x, stage_mask=3, out_dtype=torch.float32):
@@ -342,7 +363,7 @@ class HybridSuperResolutionModel(nn.Module):
     def forward(self, x):
         """src/architecture.py:74-82.  Inference (eval() or no_grad): one srb_forward call.  Training (train() mode with
         grad enabled): the differentiable libsrb path of training.hybrid_forward."""
-        if torch.is_grad_enabled() and self.training and any(p.requires_grad for p in self.parameters()):
+        if torch.is_grad_enabled() and self.training and any(p.requires_grad for _, p in named_params(self)):
             from .training import hybrid_forward
             return hybrid_forward(self, x)
         if 4 * x.shape[-1] == self.output_size:

@@ -217,9 +217,27 @@ __global__ void expand_rel_bias_kernel(const float* __restrict__ table, int T, c
     }
 }
 
+// Operand-plane variant for the tcgen05 attention core of hab_tc.cu: out[h][r / 8][c][r % 8]
+__global__ void expand_rel_bias_rows_kernel(const float* __restrict__ table, int T, const int64_t* __restrict__ index,
+                                            int NK, bf16* __restrict__ out, float scale) {
+    const int n = 6 * 64 * NK;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int c = i % NK, r = (i / NK) % 64, h = i / (NK * 64);
+        long long idx = index[r * NK + c] % T;
+        if (idx < 0) idx += T;
+        // B operand of the bias MMA (S += I * Bias^T): K-major planes [query / 8][key][query % 8]
+        out[((h * 8 + (r >> 3)) * NK + c) * 8 + (r & 7)] = __float2bfloat16_rn(table[idx * 6 + h] * scale);
+    }
+}
+
 int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, float scale,
                          cudaStream_t s) {
     const int n = 6 * 64 * NK;
+    if (NK == 64) {  // HAB (hab_tc.cu): [6][8][64][8]
+        expand_rel_bias_rows_kernel<<<(n + 255) / 256, 256, 0, s>>>(table, T, index, NK, out, scale);
+        SRB_CUDA(cudaGetLastError());
+        return SRB_OK;
+    }
     expand_rel_bias_kernel<bf16><<<(n + 255) / 256, 256, 0, s>>>(table, T, index, NK, out, scale);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;

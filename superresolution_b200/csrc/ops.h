@@ -38,14 +38,16 @@ int cab_channel_scale(const float* pool, int nslab, float* cs, const float* w1, 
                       const float* b2, float conv_scale, int B, int HW, cudaStream_t s);
 
 // hab_tc.cu — fused HAB attention branch: xn = LN1(x); t = x + proj((S)W-MSA(xn)) + bproj (one pass over x), the qkv /
-// proj GEMMs on tcgen05 (TMEM accumulators) over 128-token tiles; bias_frag_log2e: expand_rel_bias_bf16(..., scale = log2(e))
+// proj GEMMs and the attention core on tcgen05 (TMEM accumulators) over 128-token tiles; bias_frag_log2e:
+// expand_rel_bias_bf16(..., NK = 64, scale = log2(e))
 int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const bf16* wqkv, const float* bqkv,
                      const bf16* bias_frag_log2e, const bf16* wproj, const float* bproj, bf16* xn, bf16* t, int B, int H,
                      int W, int shift, cudaStream_t s);
 // attn.cu — OCAB: 8x8 query windows x 12x12 zero-padded key/value windows (NK = 144), no shift, no mask.  Log2 domain:
 // the q part of qkv arrives scaled by head_dim^-0.5 * log2(e) (scale_rows at pack time), bias_frag holds bias * log2(e).
 int ocab_attention(const bf16* qkv, const bf16* bias_frag, bf16* out, int B, int H, int W, cudaStream_t s);
-// table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> fragment-ordered bias [6*64*NK]
+// table fp32 [T][6], index int64 [64*NK] (python-style negative wrap) -> kernel-ready bias [6*64*NK]: [6][8][64][8] operand planes
+// for NK = 64 (hab_tc.cu), mma.sync C-fragment order for NK = 144 (attn.cu)
 int expand_rel_bias_bf16(const float* table, int T, const int64_t* index, int NK, bf16* out, float scale,
                          cudaStream_t s);  // out = table[index] * scale
 int expand_rel_bias_f32(const float* table, int T, const int64_t* index, int NK, float* out, cudaStream_t s);

@@ -204,7 +204,8 @@ def rrdbnet_forward(stage1, x, accumulate_into_grad=False):
     ``accumulate_into_grad``: the weight-gradient kernels add straight into existing fp32 ``p.grad`` buffers (e.g. the
     flat-gradient views of ``FusedAdamW``) instead of returning tensors for autograd to add — same result, ~700 fewer
     element-wise launches per step; parameters without a ``.grad`` buffer take the autograd route."""
-    sd = dict(stage1.named_parameters())
+    from .architecture import named_params
+    sd = dict(named_params(stage1))  # also valid on nn.DataParallel replicas
     params = []
     direct = {}
     for n in CONV_NAMES:

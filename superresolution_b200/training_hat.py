@@ -330,7 +330,8 @@ def hat_forward(stage2, x, drop_path_rate=0.1, training=None, masks=None, debug=
     ``training`` defaults to ``stage2.training``)."""
     if training is None:
         training = stage2.training
-    named = list(stage2.named_parameters())
+    from .architecture import named_params
+    named = named_params(stage2)  # also valid on nn.DataParallel replicas
     names = [n for n, _ in named]
     B = x.shape[0]
     rates = torch.linspace(0, drop_path_rate, 24).tolist()

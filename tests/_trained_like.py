@@ -21,13 +21,13 @@ def make_trained_like(model, seed=1234, rdb_gain=6.0, bias_std=0.1, lin_gain=6.0
             if name.startswith('stage1.body.') and name.endswith('.weight'):
                 p.mul_(rdb_gain)
             elif 'relative_position_bias_table' in name:
-                p.copy_(rn(p, table_std))
+                p.copy_(rn(p, table_std * (2.5 if 'overlap_attn' in name else 1.0)))
             elif '.norm' in name and name.endswith('.weight'):
                 p.copy_(1.0 + rn(p, 0.2))
             elif '.norm' in name and name.endswith('.bias'):
                 p.copy_(rn(p, 0.1))
             elif 'cab.3.attention' in name and name.endswith('.weight'):
-                p.copy_(rn(p, 0.5))
+                p.copy_(rn(p, 1.0))
             elif ('cab.0.weight' in name) or ('cab.2.weight' in name):  # CAB enters the stream x conv_scale = 0.01
                 p.mul_(cab_gain)
             elif name == 'stage2.conv_last.weight':  # final signal sigma ~0.1 instead of ~0.01

@@ -65,7 +65,10 @@ def _ref(x, g, b, wqkv, bqkv, table, rpi, wproj, bproj, shift):
     return xn, x + o
 
 
-@pytest.mark.parametrize('B,H,W,shift', [(1, 16, 16, 0), (1, 16, 16, 4), (2, 32, 64, 4), (3, 64, 32, 0), (2, 64, 64, 4)])
+# the last two geometries give every persistent CTA several tiles (the cross-tile pipelining of the kernel) and an odd
+# number of windows (the last tile's second window is empty)
+@pytest.mark.parametrize('B,H,W,shift', [(1, 16, 16, 0), (1, 16, 16, 4), (2, 32, 64, 4), (3, 64, 32, 0), (2, 64, 64, 4),
+                                         (3, 256, 256, 4), (1, 24, 24, 4), (5, 72, 88, 0)])
 def test_hab_attention(cuda, B, H, W, shift):
     from superresolution_b200 import ops
     g = torch.Generator().manual_seed(B * 1000 + H + W + shift)

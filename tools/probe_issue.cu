@@ -5,12 +5,7 @@
 #include "ptx.cuh"
 using namespace srb;
 constexpr int PP = 128 * 16 + 16;
-__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
-}
-template <int N, bool TS, int SWZ>
+template <int N, bool TS, int SWZ, int M = 128>
 __global__ void __launch_bounds__(128, 1) k(int nw, int iters, long long* out) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar[4];
@@ -27,7 +22,7 @@ __global__ void __launch_bounds__(128, 1) k(int nw, int iters, long long* out) {
         const uint32_t a_u = smem_u32(smem) + warp * 8 * 1024, b_u = smem_u32(smem + 48 * 1024) + warp * 8 * 1024;
         const uint64_t ad = SWZ ? umma_smem_desc(a_u, 16, 1024, UMMA_SW_128B) : umma_smem_desc(a_u, PP, 128, UMMA_SW_NONE);
         const uint64_t bd = SWZ ? umma_smem_desc(b_u, 16, 1024, UMMA_SW_128B) : umma_smem_desc(b_u, PP, 128, UMMA_SW_NONE);
-        const uint32_t idesc = umma_idesc_bf16_f32(128, N);
+        const uint32_t idesc = umma_idesc_bf16_f32(M, N);
         const uint32_t d = tm + warp * 64;
         t0 = clock64();
         for (int i = 0; i < iters; i += 8) {
@@ -45,14 +40,14 @@ __global__ void __launch_bounds__(128, 1) k(int nw, int iters, long long* out) {
     tc_fence_before(); __syncthreads();
     if (warp == 0) tmem_dealloc(tm, 512);
 }
-template <int N, bool TS, int SWZ>
+template <int N, bool TS, int SWZ, int M = 128>
 void run(const char* what) {
     long long* d; cudaMalloc(&d, 32 * 148);
-    cudaFuncSetAttribute(k<N, TS, SWZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    cudaFuncSetAttribute(k<N, TS, SWZ, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     const int iters = 4000;
     for (int nw = 1; nw <= 4; ++nw) {
         cudaMemset(d, 0, 32 * 148);
-        for (int rep = 0; rep < 2; ++rep) k<N, TS, SWZ><<<148, 128, 96 * 1024>>>(nw, iters, d);
+        for (int rep = 0; rep < 2; ++rep) k<N, TS, SWZ, M><<<148, 128, 96 * 1024>>>(nw, iters, d);
         cudaDeviceSynchronize();
         long long h[148 * 4]; cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
         double c = 0; for (int i = 0; i < 148; ++i) { long long m = 0; for (int w = 0; w < nw; ++w) m = h[4 * i + w] > m ? h[4 * i + w] : m; c += m; }
@@ -67,5 +62,9 @@ int main() {
     run<32, false, 1>("SS M128 N32 sw128");
     run<64, false, 1>("SS M128 N64 sw128");
     run<96, false, 0>("SS M128 N96 planes");
+    run<64, true, 0>("TS M128 N64 (bias)");
+    run<32, true, 0>("TS M128 N32 (PV)");
+    run<64, false, 0, 64>("SS M64 N64 planes (QK)");
+    run<96, true, 0>("TS M128 N96");
     return 0;
 }
