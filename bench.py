@@ -97,9 +97,10 @@ def visible_gpu_index(local_rank):
     return local_rank
 
 
-def cpu_oracle_throughput(steps, warmup, size=64):
+def cpu_oracle_throughput(steps, warmup, size=PATCH):
     """Reference arm / cpu_baseline: the oracle port of the reference model (fp32, eager, no_grad) on all host cores,
-    on a bounded sample: ONE size x size patch per step (per-pixel cost is size-independent: convs + local windows)."""
+    on a bounded sample of the workload: ONE size x size patch per step instead of the batch of 16 (the reference's own
+    patch size, 128; ~3 s per patch on 16 cores, per-patch cost is batch-independent in eager fp32)."""
     from oracle.hybrid import HybridSuperResolutionModel as Oracle
     cores = len(os.sched_getaffinity(0))
     torch.set_num_threads(cores)
@@ -218,63 +219,105 @@ def run_gpu(args):
         # deltas then hold GPU time only, not host launch gaps.
         torch.cuda._sleep(20_000_000)
         prof = model.profile(x_dev)
+        launches_per_step = model.launch_count(BATCH, PATCH, PATCH)
+        graphed = graph is not None
+        del flush, graph
 
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = t.tolist()
+    # ---- secondary workloads (own clock samples): the sharded frame and the data-parallel train step run on every rank
+    extra = {}
+    if not args.no_extra:
+        import bench_extra as X
+        gi = visible_gpu_index(local_rank)
+        extra['config3'] = X.config3(model, dev, rank, world, ClockSampler, gi)
+        del model
+        torch.cuda.empty_cache()
+        extra['config4'] = X.config4(dev, rank, world, ClockSampler, gi)
+        if rank == 0 and world == 1:
+            extra['config5'] = X.config5(dev, ClockSampler, gi)
     if rank == 0:
-        peak_tf, peak_hbm, peak_src = load_peaks()
-        total_prof_ms = sum(v[0] for v in prof.values())
-        # tensor-core kernel families and the name of the kernel behind each
-        fam = {'conv3x3_tcgen05': 'conv_tc_kernel<*,*,9> + conv_chain_kernel (tcgen05 implicit-GEMM 3x3 conv)',
-               'linear_tcgen05': 'conv_tc_kernel<*,*,1> (tcgen05 linear)',
-               'hab_attention_tcgen05': 'hab_tc_kernel (LN1 + qkv + (S)W-MSA + proj; tcgen05 GEMMs, mma.sync 64x64 cores)',
-               'mlp_tcgen05': 'mlp_tc_kernel (LN2 + fc1 + GELU + fc2 + residual; tcgen05, TMEM)',
-               'ocab_attention': 'ocab_attn_kernel (mma.sync)'}
-        dom = max(fam, key=lambda k: prof[k][0])  # dominant kernel family of the step
-        d_ms, d_flops, d_n = prof[dom]
-        achieved = d_flops / (d_ms * 1e-3) / 1e12 if d_ms > 0 else 0.0
-        tc_ms = sum(prof[k][0] for k in fam)
-        tc_flops = sum(prof[k][1] for k in fam)
-        launches = model.launch_count(BATCH, PATCH, PATCH)
-        traffic, traffic_src = family_traffic(dom)
-        line = {
-            'metric': METRIC, 'value': world * out_mpix * args.steps / (dev_ms * 1e-3), 'unit': UNIT,
-            'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': dev_ms / args.steps,
-            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
-            'config': {'workload': WORKLOAD, 'batch_per_gpu': BATCH, 'patch': PATCH, 'smoothing': 'balanced',
-                       'weights': 'random-init seed 0', 'cuda_graph': graph is not None,
-                       'l2': 'flushed between timed steps (256 MiB write)', 'patches_per_s':
-                           world * BATCH * args.steps / (dev_ms * 1e-3),
-                       'model_tflops': world * BATCH * FLOP_PER_PATCH * args.steps / (dev_ms * 1e-3) / 1e12},
-            'clocks': clocks,
-            'e2e': {'value': world * out_mpix * args.steps / (e2e_ms * 1e-3), 'unit': UNIT,
-                    'h2d_bytes_per_step': x_host.numel() * 4, 'd2h_bytes_per_step': y_host.numel() * 4},
-            'gpu_launches': launches * args.steps,
-            'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s',
-                         'frac': achieved / peak_tf, 'traffic': traffic, 'traffic_source': traffic_src,
-                         'peak_source': peak_src,
-                         'kernel': fam[dom], 'launches_per_step': d_n, 'kernel_ms_per_step': d_ms,
-                         'share_of_step': d_ms / total_prof_ms if total_prof_ms else None,
-                         'all_tensor_kernels': {'achieved': tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms else 0.0,
-                                                'frac': tc_flops / (tc_ms * 1e-3) / 1e12 / peak_tf if tc_ms else 0.0,
-                                                'ms_per_step': tc_ms},
-                         'by_class_ms': {k: round(v[0], 4) for k, v in prof.items()},
-                         'by_class_tflops': {k: round(v[1] / (v[0] * 1e-3) / 1e12, 1) for k, v in prof.items()
-                                             if v[0] > 0 and v[1] > 0}},
-        }
+        line = report(args, world, dev_ms, e2e_ms, prof, clocks, launches_per_step, x_host, y_host, graphed)
+        if extra:
+            line['extra'] = extra
         if world == 1 and not args.no_cpu_baseline:
-            v, ms, cores, sample = cpu_oracle_throughput(2, 1)
-            line['cpu_baseline'] = {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample}
+            import bench_extra as X
+            cb = X.cpu_baselines()
+            full = cb['full_hybrid_fp32_128px']
+            line['cpu_baseline'] = {'value': full['output_mpix_per_s'], 'unit': UNIT, 'cores': cb['cores'], 'kind': 'port',
+                                    'sample': 'one full hybrid 128x128 patch (fp32 oracle port, torch eager, all host cores) '
+                                              'instead of the batch of 16', 'config1_rrdbnet_fp32_128px':
+                                        cb['config1_rrdbnet_fp32_128px'], 'full_hybrid_fp32_128px': full}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+# name of the kernel behind each tensor-core profile class of srb_forward_profile, algorithmic FLOPs counted per launch
+KERNELS = {'conv3x3_tcgen05': 'conv_tc_kernel<*,*,9> (tcgen05 implicit-GEMM 3x3 conv)',
+           'rrdb_chain_tcgen05': 'conv_chain_kernel (one RRDB = 15 dense-block convs per launch, tcgen05)',
+           'linear_tcgen05': 'conv_tc_kernel<*,*,1> (tcgen05 linear)',
+           'hab_attention_tcgen05': 'hab_tc_kernel (LN1 + qkv + (S)W-MSA + proj; every contraction on tcgen05 / TMEM)',
+           'mlp_tcgen05': 'mlp_tc_kernel (LN2 + fc1 + GELU + fc2 + residual; tcgen05, TMEM)',
+           'ocab_attention': 'ocab_attn_kernel (mma.sync)'}
+
+
+def report(args, world, dev_ms, e2e_ms, prof, clocks, launches, x_host, y_host, graphed):
+    peak_sus, peak_hbm, _ = load_peaks()
+    try:
+        peak_burst = float(json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['bf16_tflops'])
+        peak_src = 'measured (MEASURED_PEAKS.json)'
+    except Exception:
+        peak_burst, peak_src = 1590.0, 'fallback (B200_PROFILING.md)'
+    # the clock record decides the denominator: no power cap seen -> the burst figure, else the sustained one
+    capped = 'sw_power_cap' in (clocks.get('reasons') or [])
+    peak_tf = peak_sus if capped else peak_burst
+    out_mpix = BATCH * (4 * PATCH) ** 2 / 1e6
+    total_prof_ms = sum(v[0] for v in prof.values())
+    dom = max(KERNELS, key=lambda k: prof[k][0])  # dominant KERNEL of the step (largest sum of CUDA-event time)
+    d_ms, d_flops, d_n = prof[dom]
+    achieved = d_flops / (d_ms * 1e-3) / 1e12 if d_ms > 0 else 0.0
+    tc_ms = sum(prof[k][0] for k in KERNELS)
+    tc_flops = sum(prof[k][1] for k in KERNELS)
+    traffic, traffic_src = family_traffic(dom)
+    return {
+        'metric': METRIC, 'value': world * out_mpix * args.steps / (dev_ms * 1e-3), 'unit': UNIT,
+        'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': dev_ms / args.steps,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+        'config': {'workload': WORKLOAD, 'batch_per_gpu': BATCH, 'patch': PATCH, 'smoothing': 'balanced',
+                   'weights': 'random-init seed 0', 'cuda_graph': graphed,
+                   'l2': 'flushed between timed steps (256 MiB write)', 'patches_per_s':
+                       world * BATCH * args.steps / (dev_ms * 1e-3),
+                   'model_tflops': world * BATCH * FLOP_PER_PATCH * args.steps / (dev_ms * 1e-3) / 1e12},
+        'clocks': clocks,
+        'e2e': {'value': world * out_mpix * args.steps / (e2e_ms * 1e-3), 'unit': UNIT,
+                'h2d_bytes_per_step': x_host.numel() * 4, 'd2h_bytes_per_step': y_host.numel() * 4},
+        'gpu_launches': launches * args.steps,
+        'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s',
+                     'frac': achieved / peak_tf, 'frac_of_burst': achieved / peak_burst,
+                     'frac_of_sustained': achieved / peak_sus, 'traffic': traffic, 'traffic_source': traffic_src,
+                     'peak_source': peak_src + (': sustained (sw_power_cap seen)' if capped else ': burst (no power cap in '
+                                                                                              'the clock record)'),
+                     'kernel': KERNELS[dom], 'launches_per_step': d_n, 'kernel_ms_per_step': d_ms,
+                     'share_of_step': d_ms / total_prof_ms if total_prof_ms else None,
+                     'whole_step': {'achieved': BATCH * FLOP_PER_PATCH / (dev_ms / args.steps * 1e-3) / 1e12,
+                                    'frac': BATCH * FLOP_PER_PATCH / (dev_ms / args.steps * 1e-3) / 1e12 / peak_tf},
+                     'all_tensor_kernels': {'achieved': tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms else 0.0,
+                                            'frac': tc_flops / (tc_ms * 1e-3) / 1e12 / peak_tf if tc_ms else 0.0,
+                                            'ms_per_step': tc_ms},
+                     'by_kernel_ms': {k: round(v[0], 4) for k, v in prof.items()},
+                     'by_kernel_tflops': {k: round(v[1] / (v[0] * 1e-3) / 1e12, 1) for k, v in prof.items()
+                                          if v[0] > 0 and v[1] > 0},
+                     'by_kernel_frac': {k: round(v[1] / (v[0] * 1e-3) / 1e12 / peak_tf, 3) for k, v in prof.items()
+                                        if v[0] > 0 and v[1] > 0}},
+    }
+
+
 # kernel-name substrings of each tensor-core family in the committed ncu capture (profiles/r01_kernel_traffic.json)
-FAMILY_KERNELS = {'conv3x3_tcgen05': ('conv_chain_kernel', ', 9>>'), 'linear_tcgen05': (', 1>>',),
+FAMILY_KERNELS = {'conv3x3_tcgen05': (', 9>>',), 'rrdb_chain_tcgen05': ('conv_chain_kernel',), 'linear_tcgen05': (', 1>>',),
                   'hab_attention_tcgen05': ('hab_tc_kernel',), 'mlp_tcgen05': ('mlp_tc_kernel',),
                   'ocab_attention': ('ocab_attn_kernel',)}
 
@@ -304,6 +347,7 @@ def main():
     ap.add_argument('--impl', default='srb', choices=['srb', 'reference'])
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-extra', action='store_true', help='skip extra.config3 / config4 / config5 (config 2 only)')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

@@ -59,10 +59,11 @@ size_t srb_workspace_bytes(int B, int H, int W);
 int srb_forward(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                 void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream);
 /* Profiling variant (bench only): same work, but every launch is bracketed by CUDA events on `stream`; the call
- * synchronises the stream and returns per-class totals.  Classes: 0 conv3x3 (tcgen05 implicit GEMM, incl. the RRDB
- * chain kernel), 1 linear (tcgen05), 2 HAB attention branch (LN + qkv + W-MSA + proj, tcgen05 + mma.sync),
- * 3 layernorm, 4 other, 5 MLP branch (tcgen05), 6 OCAB attention core.  class_flops = algorithmic FLOPs (2*MACs). */
-#define SRB_PROF_CLASSES 7
+ * synchronises the stream and returns per-class totals.  Classes: 0 conv3x3 (conv_tc_kernel, tcgen05 implicit GEMM),
+ * 1 linear (tcgen05), 2 HAB attention branch (hab_tc_kernel: LN + qkv + W-MSA + proj, all tcgen05), 3 layernorm,
+ * 4 other, 5 MLP branch (tcgen05), 6 OCAB attention core, 7 RRDB chain kernel (conv_chain_kernel, tcgen05).
+ * class_flops = algorithmic FLOPs (2*MACs). */
+#define SRB_PROF_CLASSES 8
 int srb_forward_profile(const void* x, int x_dtype, void* y, int y_dtype, int B, int H, int W, const void* packed,
                         void* workspace, size_t workspace_bytes, int smoothing, int stage_mask, void* stream,
                         double* class_ms, double* class_flops, int* class_launches);
@@ -154,6 +155,10 @@ int srb_robust_hist(const float* x, size_t n, float thresh, int level, const uin
 int srb_blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int overlap, float* acc,
                     float* wsum, int FH, int FW, int row0, int row1, void* stream);
 int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, void* stream);
+/* srb_gather_tiles: out[t] = frame[iy[t] : iy[t]+tile, ix[t] : ix[t]+tile] (frame u16 or f32 [FH,FW]; iy/ix device int32):
+ *                   the tile batch of the whole-field driver in one launch. */
+int srb_gather_tiles(const void* frame, int dtype, int FH, int FW, const int* iy, const int* ix, int T, int tile, void* out,
+                     void* stream);
 
 
 /* ---- backward of the conv / linear layers (autograd of nn.Conv2d(..,3,1,1) / nn.Linear inside

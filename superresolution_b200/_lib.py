@@ -63,6 +63,7 @@ _PROTOS = {
     'srb_adamw_step': (_i, [_vp, _vp, _vp, _vp, _sz, _f, _f, _f, _f, _f, _i, _f, _f, _vp, _vp, _vp]),
     'srb_blend_tiles': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _vp]),
     'srb_blend_finalize': (_i, [_vp, _vp, _vp, _i, _sz, _vp]),
+    'srb_gather_tiles': (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _vp, _vp]),
     'srb_expand_rel_bias': (_i, [_vp, _i, _vp, _i, _vp, _f, _vp]),
     'srb_hab_attention': (_i, [_vp] * 10 + [_i, _i, _i, _i, _vp]),
     'srb_mlp_branch': (_i, [_vp] * 8 + [_sz, _sz, _vp]),

@@ -337,7 +337,7 @@ class HybridSuperResolutionModel(nn.Module):
         return y
 
     PROFILE_CLASSES = ('conv3x3_tcgen05', 'linear_tcgen05', 'hab_attention_tcgen05', 'layernorm', 'other',
-                       'mlp_tcgen05', 'ocab_attention')
+                       'mlp_tcgen05', 'ocab_attention', 'rrdb_chain_tcgen05')
 
     def profile(self, x, stage_mask=3):
         """bench helper: one forward with every launch bracketed by CUDA events on the launching stream.

@@ -369,6 +369,11 @@ int srb_blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int
     if (!tiles || !oy || !ox || !acc || !wsum || T <= 0) { set_error("blend_tiles: bad args"); return SRB_E_ARG; }
     return blend_tiles(tiles, oy, ox, T, th, tw, overlap, acc, wsum, FH, FW, row0, row1, (cudaStream_t)stream);
 }
+int srb_gather_tiles(const void* frame, int dtype, int FH, int FW, const int* iy, const int* ix, int T, int tile, void* out,
+                     void* stream) {
+    if (!frame || !iy || !ix || !out || T <= 0) { set_error("gather_tiles: bad args"); return SRB_E_ARG; }
+    return gather_tiles(frame, dtype, FH, FW, iy, ix, T, tile, out, (cudaStream_t)stream);
+}
 int srb_blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, void* stream) {
     if (!acc || !wsum || !out) { set_error("blend_finalize: null pointer"); return SRB_E_ARG; }
     return blend_finalize(acc, wsum, out, out_dtype, n, (cudaStream_t)stream);

@@ -54,6 +54,33 @@ int blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th,
     return SRB_OK;
 }
 
+// Tile gather: tiles[t] = frame[iy[t] : iy[t] + tile, ix[t] : ix[t] + tile] for T tiles whose origins live on the device
+// (one launch per batch instead of one slice copy per tile; the batch then feeds srb_forward directly).
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_tiles_kernel(const T* __restrict__ frame, int FW, const int* __restrict__ iy, const int* __restrict__ ix, int nt,
+                    int tile, T* __restrict__ out) {
+    const size_t per = (size_t)tile * tile;
+    const size_t n = per * nt;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int t = (int)(i / per), r = (int)(i % per);
+        out[i] = frame[(size_t)(iy[t] + r / tile) * FW + ix[t] + r % tile];
+    }
+}
+
+int gather_tiles(const void* frame, int dtype, int FH, int FW, const int* iy, const int* ix, int T, int tile, void* out,
+                 cudaStream_t s) {
+    if (tile <= 0 || tile > FH || tile > FW) { set_error("gather_tiles: tile %d does not fit the %dx%d frame", tile, FH, FW); return SRB_E_SHAPE; }
+    const size_t n = (size_t)T * tile * tile;
+    int grid = (int)((n + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    if (dtype == SRB_U16) gather_tiles_kernel<uint16_t><<<grid, 256, 0, s>>>((const uint16_t*)frame, FW, iy, ix, T, tile, (uint16_t*)out);
+    else if (dtype == SRB_F32) gather_tiles_kernel<float><<<grid, 256, 0, s>>>((const float*)frame, FW, iy, ix, T, tile, (float*)out);
+    else { set_error("gather_tiles: frame dtype must be U16 or F32"); return SRB_E_DTYPE; }
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
 int blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, cudaStream_t s) {
     int grid = (int)((n + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;

@@ -274,7 +274,7 @@ size_t model_workspace_bytes(int B, int H, int W) {
 // ------------------------------------------------------------------------------------------------------------------
 // forward schedule
 // ------------------------------------------------------------------------------------------------------------------
-enum ProfClass { PC_CONV3 = 0, PC_LINEAR = 1, PC_ATTN = 2, PC_LN = 3, PC_OTHER = 4, PC_MLP = 5, PC_OCAB = 6, PC_COUNT = 7 };
+enum ProfClass { PC_CONV3 = 0, PC_LINEAR = 1, PC_ATTN = 2, PC_LN = 3, PC_OTHER = 4, PC_MLP = 5, PC_OCAB = 6, PC_CHAIN = 7, PC_COUNT = 8 };
 static_assert(PC_COUNT == SRB_PROF_CLASSES, "profile classes");
 struct ProfRec {
     int cls;
@@ -395,7 +395,7 @@ static int run_stage1(Ctx& c, Workspace& w, const void* x, int x_dtype, int B, i
             if (!c.dry) {
                 double fl = 0;
                 for (int q = 0; q < nl; ++q) fl += layer_flops(la[q]);
-                prof_begin(c, PC_CONV3, fl);
+                prof_begin(c, PC_CHAIN, fl);
                 const int rc = conv_chain_launch(la, nl, w.chain_ctr + 16 * i, c.s);
                 prof_end(c);
                 if (rc != SRB_OK) return rc;

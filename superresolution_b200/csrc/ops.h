@@ -119,6 +119,8 @@ int adamw_step(float* p, const float* g, float* m, float* v, size_t n, float lr,
 int blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int ov, float* acc,
                 float* wsum, int FH, int FW, int row0, int row1, cudaStream_t s);
 int blend_finalize(const float* acc, const float* wsum, void* out, int out_dtype, size_t n, cudaStream_t s);
+int gather_tiles(const void* frame, int dtype, int FH, int FW, const int* iy, const int* ix, int T, int tile, void* out,
+                 cudaStream_t s);
 
 // forward.cu
 int model_param_count();

@@ -172,3 +172,74 @@ def test_seam_plan_partitions_rows_and_tiles():
         assert edges[0][0] == 0 and edges[-1][1] == 16384
         assert all(edges[i][1] == edges[i + 1][0] for i in range(len(edges) - 1))
         assert all(p[3] - p[2] <= 4 * 128 for p in pl)               # a strip is at most one tile high
+
+
+def _tile_worker(rank, world, port, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from superresolution_b200 import tiling
+    from oracle import tiling as otil
+    H, W = 128, 104
+    tile, stride, scale = 32, 24, 4
+    ov = scale * (tile - stride)
+    rng = np.random.default_rng(0)
+    origins = tiling.plan(H, W, tile, stride)
+    outs = {o: rng.random((scale * tile, scale * tile), dtype=np.float32) for o in origins}  # stand-in tile outputs
+    FH, FW = scale * H, scale * W
+    plan_all = tiling.tile_plan(H, W, tile, stride, scale, world)
+    me = plan_all[rank]
+    b0, b1 = me['buf']
+    sums = np.zeros((2, b1 - b0, FW), np.float32)
+    w = np.outer(otil.ramp(scale * tile, ov), otil.ramp(scale * tile, ov)).astype(np.float32)
+    for (y, x) in me['tiles']:
+        oy, ox = scale * y - b0, scale * x
+        sums[0, oy:oy + scale * tile, ox:ox + scale * tile] += w * outs[(y, x)]
+        sums[1, oy:oy + scale * tile, ox:ox + scale * tile] += w
+    own = tiling.exchange_tiles_planned(torch.from_numpy(sums), plan_all, rank).numpy()
+    mine = own[0] / np.maximum(own[1], 1e-30)
+    parts = [None] * world
+    dist.all_gather_object(parts, (me['own'][0], me['own'][1], mine))
+    if rank == 0:
+        ref = otil.blend(list(outs.values()), [(scale * y, scale * x) for (y, x) in outs], FH, FW, ov)
+        got = np.zeros_like(ref)
+        covered = np.zeros(FH, bool)
+        for a, b, m in parts:
+            got[a:b] = m
+            assert not covered[a:b].any()
+            covered[a:b] = True
+        q.put((bool(covered.all()), float(np.abs(got - ref).max()), [len(p['tiles']) for p in plan_all]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_three_rank_tile_count_sharding_matches_single_rank():
+    """seams='tiles': the tiles (not the tile rows) are dealt out by count; tile rows shared by two ranks are stitched
+    through the two-sided point-to-point exchange — the frame equals the single-rank blend."""
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = 33500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_tile_worker, args=(r, 3, port, q)) for r in range(3)]
+    for p in procs:
+        p.start()
+    covered, err, counts = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert covered and err < 1e-6
+    assert sum(counts) == 5 * 4 and max(counts) - min(counts) <= 1  # 20 tiles over 3 ranks: 6 / 7 / 7, rows are split
+
+
+def test_tile_plan_is_balanced_and_partitions_the_frame():
+    from superresolution_b200 import tiling
+    every = tiling.plan(4096, 4096)
+    for world in (1, 2, 3, 4, 8, 50):
+        pl = tiling.tile_plan(4096, 4096, 128, 96, 4, world)
+        assert [t for p in pl for t in p['tiles']] == every           # every tile exactly once, raster order
+        cnt = [len(p['tiles']) for p in pl]
+        assert max(cnt) - min(cnt) <= 1                               # SURVEY.md 8e: balance by tile COUNT
+        own = [p['own'] for p in pl]
+        assert own[0][0] == 0 and own[-1][1] == 16384 and all(own[i][1] == own[i + 1][0] for i in range(world - 1))
+        for p in pl:  # the local accumulator covers the rank's tiles and its own range
+            assert p['buf'][0] <= min(4 * p['tiles'][0][0], p['own'][0]) and p['buf'][1] >= max(4 * (p['tiles'][-1][0] + 128), p['own'][1])
+    assert [len(p['tiles']) for p in tiling.tile_plan(4096, 4096, 128, 96, 4, 8)].count(231) == 7
