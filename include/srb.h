@@ -137,6 +137,15 @@ int srb_weighted_l1(const float* pred, const float* target, size_t n, float* los
 size_t srb_psnr_ssim_scratch_bytes(int B, int H, int W);
 int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, void* scratch,
                   void* stream);
+/* srb_psnr_ssim_noalloc: srb_psnr_ssim for callers that may not allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same inputs, outputs and results as srb_psnr_ssim; the scratch is a static __device__ array of
+ * SRB_PSNR_SSIM_NOALLOC_MAX_BYTES inside the library (held by every GPU that loads it, until exit), so the call makes
+ * no cudaMalloc / cudaFree and takes no scratch pointer.  Shapes with srb_psnr_ssim_scratch_bytes(B,H,W) above the
+ * limit (e.g. more than 252 pairs of 512x512) are rejected with SRB_E_WORKSPACE.  All calls on one device share the
+ * array: calls that may overlap on the GPU (different streams without a dependency) race; serialise them. */
+#define SRB_PSNR_SSIM_NOALLOC_MAX_BYTES (256 * 1024)
+int srb_psnr_ssim_noalloc(const float* pred, const float* target, int B, int H, int W, float* out2, void* stream);
 int srb_log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, void* stream);
 /* srb_to_u16          save_as_tiff16's conversion (scripts/Modello_5.py:29-33): u16(clip(x, 0, 1) * 65535), truncating cast
  * srb_preview_strip   the [LR | SR | HR] comparison strip of scripts/Modello_5.py:83-85 / Modello_supporto.py:187-190:

@@ -30,6 +30,7 @@ _PROTOS = {
     'srb_weighted_l1': (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
     'srb_psnr_ssim_scratch_bytes': (_sz, [_i, _i, _i]),
     'srb_psnr_ssim': (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    'srb_psnr_ssim_noalloc': (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     'srb_log_normalize_u16': (_i, [_vp, _vp, _sz, _f, _f, _vp]),
     'srb_pack_conv_weight_dgrad': (_i, [_vp, _vp, _i, _i, _i, _vp]),
     'srb_conv_wgrad_scratch_bytes': (_sz, [_i] * 6),

@@ -217,6 +217,10 @@ int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, f
     if (!pred || !target || !out2 || !scratch || B <= 0) { set_error("psnr_ssim: bad args"); return SRB_E_ARG; }
     return psnr_ssim(pred, target, B, H, W, out2, (float*)scratch, (cudaStream_t)stream);
 }
+int srb_psnr_ssim_noalloc(const float* pred, const float* target, int B, int H, int W, float* out2, void* stream) {
+    if (!pred || !target || !out2) { set_error("psnr_ssim_noalloc: bad args"); return SRB_E_ARG; }
+    return psnr_ssim_noalloc(pred, target, B, H, W, out2, (cudaStream_t)stream);
+}
 int srb_pack_conv_weight_dgrad(const float* w, void* w_packed, int Cout, int Cin, int taps, void* stream) {
     if (!w || !w_packed || Cout <= 0 || Cin <= 0 || (taps != 9 && taps != 1)) { set_error("pack_conv_weight_dgrad: bad args"); return SRB_E_ARG; }
     return pack_conv_weight_dgrad(w, (bf16*)w_packed, Cout, Cin, taps, (cudaStream_t)stream);

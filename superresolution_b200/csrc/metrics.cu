@@ -296,6 +296,38 @@ int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// psnr_ssim without any allocation by the caller or by us (srb_psnr_ssim_noalloc; no counterpart in the reference,
+// added for callers that may not call cudaMalloc: graph capture, serving loops).
+// The scratch lives in a file-scope __device__ array that every GPU loading the library holds until exit.  Host code
+// may not use the array's name as a pointer (it is a host-side stand-in): the device address comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.  Every tile / image partial the kernels
+// read is rewritten by the same call, so stale contents of an earlier call never matter; two calls that overlap on
+// the GPU (different streams, no dependency) share the array and race.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr size_t kPsnrSsimStaticBytes = 256 * 1024;  // = SRB_PSNR_SSIM_NOALLOC_MAX_BYTES (include/srb.h)
+static __device__ __align__(256) unsigned char g_psnr_ssim_scratch[kPsnrSsimStaticBytes];
+
+int psnr_ssim_noalloc(const float* pred, const float* target, int B, int H, int W, float* out2, cudaStream_t s) {
+    if (B <= 0 || H <= 0 || W <= 0) { set_error("psnr_ssim_noalloc: bad shape"); return SRB_E_ARG; }
+    const size_t need = psnr_ssim_scratch_bytes(B, H, W);
+    if (need > kPsnrSsimStaticBytes) {
+        set_error("psnr_ssim_noalloc: [%d,%d,%d] needs %zu bytes of scratch, the static array holds %zu "
+                  "(use srb_psnr_ssim with caller scratch)", B, H, W, need, kPsnrSsimStaticBytes);
+        return SRB_E_WORKSPACE;
+    }
+    static std::atomic<void*> addr[64];
+    int dev = 0;
+    SRB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("psnr_ssim_noalloc: device index out of range"); return SRB_E_ARG; }
+    void* ptr = addr[dev].load(std::memory_order_acquire);
+    if (!ptr) {
+        SRB_CUDA(cudaGetSymbolAddress(&ptr, g_psnr_ssim_scratch));
+        addr[dev].store(ptr, std::memory_order_release);
+    }
+    return psnr_ssim(pred, target, B, H, W, out2, (float*)ptr, s);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // LOG normalisation: u16( clip((log1p(max(nan_to_num(x),0)) - gmin) / denom, 0, 1) * 65535 )   (truncating cast)
 // denom = float32(gmax - gmin + 1e-8) is formed by the caller exactly as numpy does.
 // ---------------------------------------------------------------------------------------------------------------

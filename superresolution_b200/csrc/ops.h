@@ -68,6 +68,7 @@ int weighted_l1(const float* pred, const float* target, size_t n, float* loss, f
 size_t psnr_ssim_scratch_bytes(int B, int H, int W);
 int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, float* scratch,
               cudaStream_t s);
+int psnr_ssim_noalloc(const float* pred, const float* target, int B, int H, int W, float* out2, cudaStream_t s);
 int log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float denom, cudaStream_t s);
 
 // conv_bwd.cu
