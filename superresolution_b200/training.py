@@ -251,11 +251,11 @@ def _head(model, x, accumulate_into_grad):
     return _BlurFn.apply(y, mode) if mode is not None else y
 
 
-def _tail(model, y, drop_path_rate):
+def _tail(model, y, drop_path_rate, masks=None, debug=None):
     """stage2 -> s2 -> bicubic resize when the shape differs -> sf (src/architecture.py:77-82)"""
     from .training_hat import hat_forward
     mode = getattr(model.s1, 'mode', None)
-    y = hat_forward(model.stage2, y, drop_path_rate=drop_path_rate, training=model.training)
+    y = hat_forward(model.stage2, y, drop_path_rate=drop_path_rate, training=model.training, masks=masks, debug=debug)
     if mode is not None:
         y = _BlurFn.apply(y, mode)
     if y.shape[-1] != model.output_size:
@@ -265,11 +265,12 @@ def _tail(model, y, drop_path_rate):
     return y
 
 
-def hybrid_forward(model, x, accumulate_into_grad=False, drop_path_rate=0.1):
+def hybrid_forward(model, x, accumulate_into_grad=False, drop_path_rate=0.1, masks=None, debug=None):
     """Differentiable ``HybridSuperResolutionModel.forward``: stage1 -> s1 -> stage2 -> s2 -> (bicubic resize to
     output_size when the shape differs) -> sf, exactly the order of src/architecture.py:74-82.  x: [B,1,H,W] float in
-    [0,1] with H % 32 == 0 and W % 64 == 0.  Returns fp32 [B,1,output_size,output_size] (or [B,1,4H,4W])."""
-    return _tail(model, _head(model, x, accumulate_into_grad), drop_path_rate)
+    [0,1] with H % 32 == 0 and W % 64 == 0.  Returns fp32 [B,1,output_size,output_size] (or [B,1,4H,4W]).
+    ``masks`` / ``debug``: see training_hat.hat_forward (given DropPath factors / captured intermediates; tests)."""
+    return _tail(model, _head(model, x, accumulate_into_grad), drop_path_rate, masks, debug)
 
 
 def train_step(model, optimizer, criterion, lr, hr, micro_batch=16, max_norm=1.0, world=1, group=None, grad_scale=1.0,

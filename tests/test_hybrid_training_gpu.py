@@ -96,7 +96,11 @@ def test_hybrid_forward_backward_matches_oracle_autograd(cuda, smoothing, output
     assert psnr >= 50.0
     (y * R.to(cuda)).sum().backward()
     ref = dict(o.named_parameters())
-    for stage, med_bar, cos_bar in (('stage2.', 0.12, 0.99), ('stage1.', 0.20, 0.99)):
+    # plain fp32 oracle, LeakyReLU sign flips included (HAT's LeakyReLU(0.01): a flipped element changes its gradient
+    # 100x): measured stage 2 median 2.6 / 7.3 %, p90 3.2 / 9.4 %, cosine 0.9998 / 0.9983; stage 1 median 8.0 / 11.6 %,
+    # p90 10.8 / 15.0 %, cosine 0.998 / 0.995 (balanced-192 / none-256).  Bars ~1.6-2x the worse case; the sign-matched
+    # test below is the tight one.
+    for stage, med_bar, p90_bar, cos_bar in (('stage2.', 0.12, 0.16, 0.997), ('stage1.', 0.20, 0.28, 0.99)):
         errs, a, b = [], [], []
         for n, p in m.named_parameters():
             if not n.startswith(stage):
@@ -110,8 +114,98 @@ def test_hybrid_forward_backward_matches_oracle_autograd(cuda, smoothing, output
         errs.sort()
         print(f'{stage} {len(errs)} tensors: median rel err {errs[len(errs) // 2]:.4f}  p90 {errs[int(len(errs) * .9)]:.4f} '
               f'max {errs[-1]:.4f}  cosine {cos:.5f}  |g| {a.norm():.4g} vs {b.norm():.4g}')
-        assert errs[len(errs) // 2] <= med_bar
+        assert errs[len(errs) // 2] <= med_bar and errs[int(len(errs) * .9)] <= p90_bar
         assert cos >= cos_bar
+
+
+def _grad_stats(tag, named_got, ref):
+    """per-tensor relative L2 error and cosine of every gradient tensor; cosines only for tensors whose reference norm
+    is above 1e-3 of the largest one (below that floor bf16 storage noise dominates a near-zero gradient)."""
+    errs, coss, norms = {}, {}, {}
+    for n, p in named_got:
+        assert p.grad is not None and p.grad.shape == ref[n].grad.shape, n
+        a, b = p.grad.cpu().double().flatten(), ref[n].grad.double().flatten()
+        errs[n] = ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+        coss[n] = (a @ b / (a.norm() * b.norm()).clamp_min(1e-30)).item()
+        norms[n] = b.norm().item()
+    floor = 1e-3 * max(norms.values())
+    v = sorted(errs.values())
+    live = {n: c for n, c in coss.items() if norms[n] >= floor}
+    worst = max(errs, key=errs.get)
+    low = min(live, key=live.get)
+    st = {'median': v[len(v) // 2], 'p90': v[int(len(v) * .9)], 'max': v[-1], 'min_cos': live[low],
+          'max_live': max(errs[n] for n in live)}
+    print(f'{tag}: {len(v)} tensors  median {st["median"]:.4f}  p90 {st["p90"]:.4f}  max {st["max"]:.4f} ({worst}, '
+          f'|g| {norms[worst]:.3g}; above the floor {st["max_live"]:.4f})  min cosine over {len(live)} tensors above the floor {st["min_cos"]:.5f} ({low})')
+    return st
+
+
+@pytest.mark.parametrize('drop,smoothing,output_size', [(False, 'balanced', 192), (True, 'none', 256)])
+def test_hybrid_gradients_match_rounding_matched_oracle(cuda, drop, smoothing, output_size, monkeypatch):
+    """the composition stage1 -> s1 -> stage2 -> s2 -> (resize) -> sf, forward and backward,
+    against autograd over the oracle with the kernels' rounding points in stage 1 (tests/_emulate.py) and the sign
+    pattern of HAT's one LeakyReLU taken from the libsrb forward — so the bars can sit at ~2x the measured errors instead
+    of absorbing sign flips.  drop=True: train mode with the SAME DropPath factors on both sides (rate 0.4 so that
+    branches really drop).  Bars (measured on B200, printed): see the asserts."""
+    import oracle.hat as ohat
+    from _emulate import _emulated_rrdbnet
+    from oracle.hybrid import HybridSuperResolutionModel as Oracle
+    from superresolution_b200.architecture import HybridSuperResolutionModel as Model
+    from superresolution_b200.training import hybrid_forward
+    from superresolution_b200.training_hat import drop_path_masks
+    torch.manual_seed(2)
+    o = Oracle(output_size=output_size, smoothing=smoothing)
+    m = Model(output_size=output_size, smoothing=smoothing)
+    m.load_state_dict(o.state_dict(), strict=True)
+    m = m.to(cuda).train()
+    B = 2 if drop else 1
+    g = torch.Generator().manual_seed(8)
+    x = torch.randint(0, 65536, (B, 1, 32, 64), generator=g).float() / 65535.0
+    masks = None
+    if drop:
+        o.train()
+        torch.manual_seed(3)
+        masks = [(None, None)] + [(drop_path_masks(B, 0.4, True, 'cpu'), drop_path_masks(B, 0.4, True, 'cpu'))
+                                  for _ in range(23)]
+        assert any(v == 0.0 for mm in masks[1:] for half in mm for v in half)
+        it = iter([half for mm in masks[1:] for half in mm])
+
+        def shared_drop_path(t, p=0.0, training=False):
+            return t * torch.as_tensor(next(it), dtype=t.dtype).view(-1, *([1] * (t.ndim - 1)))
+
+        monkeypatch.setattr(ohat, 'drop_path', shared_drop_path)
+    else:
+        o.eval()
+    dbg = {}
+    y = hybrid_forward(m, x.to(cuda), drop_path_rate=0.4 if drop else 0.0, masks=masks, debug=dbg)
+    pos = (dbg['u'].float() > 0).permute(0, 3, 1, 2).cpu()
+
+    class SignMatchedLeakyReLU(torch.nn.Module):
+        def forward(self, t):
+            return t * torch.where(pos, 1.0, 0.01)
+
+    o.stage2.conv_before_upsample[1] = SignMatchedLeakyReLU()
+    yo = o.stage2(o.s1(_emulated_rrdbnet(o.stage1, x)))
+    yo = o.s2(yo)
+    if yo.shape[-1] != output_size:
+        yo = F.interpolate(yo, size=(output_size, output_size), mode='bicubic', align_corners=False)
+    yo = o.sf(yo)
+    assert y.shape == yo.shape and y.requires_grad
+    fe = _rel(y.detach().cpu() - y.detach().cpu().mean(), yo.detach() - yo.detach().mean())
+    R = torch.randn(yo.shape, generator=g)
+    (yo * R).sum().backward()
+    (y * R.to(cuda)).sum().backward()
+    ref = dict(o.named_parameters())
+    s2 = _grad_stats('stage2', [(n, p) for n, p in m.named_parameters() if n.startswith('stage2.')], ref)
+    s1 = _grad_stats('stage1', [(n, p) for n, p in m.named_parameters() if n.startswith('stage1.')], ref)
+    print(f'forward rel err (mean removed) {fe:.4f}')
+    assert fe <= 0.03
+    # measured (B200): stage 2 median 0.7 / 1.1 %, p90 1.0 / 1.5 %, min cosine 0.9999; stage 1 median 2.4 / 3.1 %, p90 3.1 / 3.6 %,
+    # max 8.0 / 5.4 %, min cosine 0.9990 / 0.9995 (eval / shared-DropPath train mode).  Bars ~2x.  `max` over ALL tensors is
+    # dominated by near-zero gradients (|g| ~1e-5 of the largest: channel-attention 1x1 weights) and only sanity-bounded.
+    assert s2['median'] <= 0.025 and s2['p90'] <= 0.035 and s2['max_live'] <= 0.06 and s2['min_cos'] >= 0.999
+    assert s1['median'] <= 0.06 and s1['p90'] <= 0.075 and s1['max_live'] <= 0.16 and s1['min_cos'] >= 0.997
+    assert s2['max'] <= 0.7 and s1['max'] <= 0.2
 
 
 def test_train_step_micro_batches_equal_full_batch_and_reduce_loss(cuda):
