@@ -19,7 +19,7 @@ extern "C" {
 #endif
 
 #define SRB_OK 0
-#define SRB_E_SHAPE (-1)     /* unsupported geometry (H, W must be multiples of 16; stage-1 output of 8) */
+#define SRB_E_SHAPE (-1)     /* unsupported geometry (full model: H, W multiples of 4; stage 2 alone: of 8) */
 #define SRB_E_DTYPE (-2)
 #define SRB_E_WORKSPACE (-3) /* workspace / packed-weight buffer too small */
 #define SRB_E_CUDA (-4)      /* CUDA runtime / driver error, text in srb_last_error() */

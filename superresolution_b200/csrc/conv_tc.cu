@@ -292,7 +292,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const int mt = u / (N_TILE / 32), c0 = (u % (N_TILE / 32)) * 32;
                     const int y = ty * Cfg::TH + (row >> 3);
                     const int x = tx * Cfg::TW + 8 * mt + (row & 7);
-                    const size_t pix = ((size_t)b * a.H + y) * a.W + x;
+                    // ragged last tile row / column (H, W not multiples of the tile): rows beyond the image compute on
+                    // zero-filled input, read their residuals from a clamped (valid) pixel and are never stored
+                    const bool valid = (y < a.H) && (x < a.W);
+                    const size_t pix = ((size_t)b * a.H + (y < a.H ? y : a.H - 1)) * a.W + (x < a.W ? x : a.W - 1);
                     const int cb = nt * N_TILE + c0;  // first output channel of this 32-wide block
                     uint32_t acc[32];
                     PH_BEGIN();
@@ -306,7 +309,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     PH_BEGIN();
                     epilogue_math<Cfg::TRAIN>(v, a, pix, cb, b, sbias);
                     PH_END(ph_math);
-                    if (a.out32) {
+                    if (a.out32 && valid) {
                         float4* op = (float4*)(a.out32 + pix * a.out32_pitch + cb);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) op[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -340,6 +343,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                 bulk_commit_group();
                             }
                             ++it_s;
+                        } else if (!valid) {
+                            // nothing to store
                         } else if (!a.pixel_shuffle) {
                             uint4* op = (uint4*)(a.out + pix * a.out_pitch + cb);
 #pragma unroll
@@ -366,6 +371,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         }
                     }
                     if (a.colsum) {  // channel sums of this unit over the warp's 32 pixels (v is dead from here on)
+                        if (!valid) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] = 0.f;
+                        }
                         const float cs_ = warp_colsum32(v, lane);
                         scol[((it_a & 1) * 16 + mt * 4 + q) * N_TILE + c0 + lane] = cs_;
                     }
@@ -462,13 +471,15 @@ bool env_flag(const char* name, bool dflt) {
 
 template <class Cfg>
 static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
-    if (a.H % Cfg::TH || a.W % Cfg::TW) {
-        set_error("conv_tc: H=%d W=%d not divisible by tile %dx%d", a.H, a.W, Cfg::TH, Cfg::TW);
+    // Inference layers take any H, W: the last tile row / column is ragged (TMA zero-fills the loads and clips the
+    // stores, the epilogue masks the rest).  The training epilogue (pre_out) keeps whole tiles.
+    if (Cfg::TRAIN && (a.H % Cfg::TH || a.W % Cfg::TW)) {
+        set_error("conv_tc(train): H=%d W=%d not divisible by tile %dx%d", a.H, a.W, Cfg::TH, Cfg::TW);
         return SRB_E_SHAPE;
     }
     ConvLaunch t;
-    t.tiles_x = a.W / Cfg::TW;
-    t.tiles_y = a.H / Cfg::TH;
+    t.tiles_x = (a.W + Cfg::TW - 1) / Cfg::TW;
+    t.tiles_y = (a.H + Cfg::TH - 1) / Cfg::TH;
     t.n_tiles_n = a.Cout / Cfg::N_TILE;
     t.n_spatial = a.B * t.tiles_x * t.tiles_y;
     t.nchunks = (a.Cin + 63) / 64;

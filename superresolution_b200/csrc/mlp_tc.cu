@@ -64,7 +64,7 @@ struct MlpArgs {
     const float* ln2_g;  // optional second output xn2 = LayerNorm(y) * ln2_g + ln2_b (the next block's norm1,
     const float* ln2_b;  // fused into the copy-out: OCAB's norm1 after the last HAB of a group)
     bf16* xn2;
-    uint32_t ntiles, tiles_per_img;
+    uint32_t ntiles, tiles_per_img, tok_per_img;
     uint32_t nimg;  // images covered by this launch (cs table rows)
     long long* dbg;  // optional [grid][8] per-phase cycle totals of thread 0 (development aid)
 };
@@ -191,8 +191,18 @@ mlp_tc_kernel(const MlpArgs a) {
 #define SRB_PHASE(k) do { } while (0)
 #endif
 
+        // token row of this thread in `tile`: an image is ceil(tok_per_img / 128) tiles, the last one possibly ragged
+        // (HAT token counts are multiples of 64): rows beyond the image read a clamped (valid) row and are never stored
+        auto token_row = [&](uint32_t tile, bool& valid) -> size_t {
+            const uint32_t img = tile / a.tiles_per_img;
+            uint32_t r = (tile - img * a.tiles_per_img) * 128 + ln_row;
+            valid = r < a.tok_per_img;
+            if (!valid) r = a.tok_per_img - 1;
+            return (size_t)img * a.tok_per_img + r;
+        };
         auto issue_loads = [&](uint32_t tile) {
-            const size_t row = (size_t)tile * 128 + ln_row;
+            bool valid;
+            const size_t row = token_row(tile, valid);
             const uint4* tp = (const uint4*)(a.t + row * 96) + ln_j;
 #pragma unroll
             for (int m = 0; m < 3; ++m) pt[m] = tp[4 * m];  // plain loads: y may alias t (OCAB runs in place)
@@ -347,12 +357,14 @@ mlp_tc_kernel(const MlpArgs a) {
             // ---- (d) copy-out(i): 4 lanes per token, 64-byte row segments -> fully coalesced 16-byte stores ----
             {
                 const uint8_t* yp = sYP + (i & 1) * YP_BYTES + ln_row * 16;
-                uint4* gp = (uint4*)(a.y + ((size_t)tile * 128 + ln_row) * 96) + ln_j;
+                bool valid;
+                const size_t orow = token_row(tile, valid);
+                uint4* gp = (uint4*)(a.y + orow * 96) + ln_j;
                 uint4 o[3];
 #pragma unroll
                 for (int m = 0; m < 3; ++m) {
                     o[m] = *(const uint4*)(yp + (ln_j + 4 * m) * YP_PITCH);
-                    gp[4 * m] = o[m];
+                    if (valid) gp[4 * m] = o[m];
                 }
                 if (LN2) {  // xn2 = LayerNorm(y) of the bf16 row just written (4 lanes per token: two shuffles per sum)
                     float v[24];
@@ -384,7 +396,7 @@ mlp_tc_kernel(const MlpArgs a) {
                     qq += __shfl_xor_sync(0xffffffffu, qq, 1);
                     qq += __shfl_xor_sync(0xffffffffu, qq, 2);
                     const float rstd = rsqrtf(qq * (1.f / 96.f) + 1e-5f);
-                    uint4* xp = (uint4*)(a.xn2 + ((size_t)tile * 128 + ln_row) * 96) + ln_j;
+                    uint4* xp = (uint4*)(a.xn2 + orow * 96) + ln_j;
 #pragma unroll
                     for (int m = 0; m < 3; ++m) {
                         const float* gg = sLN2 + (ln_j + 4 * m) * 8;
@@ -394,7 +406,7 @@ mlp_tc_kernel(const MlpArgs a) {
                         for (int k = 0; k < 4; ++k)
                             xw[k] = packbf(fmaf((v[8 * m + 2 * k] - mean) * rstd, gg[2 * k], gg[96 + 2 * k]),
                                            fmaf((v[8 * m + 2 * k + 1] - mean) * rstd, gg[2 * k + 1], gg[96 + 2 * k + 1]));
-                        xp[4 * m] = x4;
+                        if (valid) xp[4 * m] = x4;
                     }
                 }
             }
@@ -445,7 +457,7 @@ int fold_ln_linear(const float* w, const float* b, const float* gamma, const flo
 int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, const float* b1f, const bf16* w2,
               const float* b2, bf16* y, size_t ntok, size_t tok_per_img, cudaStream_t s, const float* ln2_g,
               const float* ln2_b, bf16* xn2) {
-    if (ntok % 128 || tok_per_img % 128) { set_error("mlp_fused: token counts must be multiples of 128"); return SRB_E_SHAPE; }
+    if (ntok == 0 || tok_per_img == 0 || tok_per_img >= ((size_t)1 << 31)) { set_error("mlp_fused: bad token counts"); return SRB_E_SHAPE; }
     if (((uintptr_t)t | (uintptr_t)y | (uintptr_t)cab | (uintptr_t)w1f | (uintptr_t)w2) & 15) {
         set_error("mlp_fused: pointers must be 16-byte aligned");
         return SRB_E_ARG;
@@ -464,8 +476,9 @@ int mlp_fused(const bf16* t, const bf16* cab, const float* cs, const bf16* w1f, 
         a.t = t + tok0 * 96; a.cab = cab ? cab + tok0 * 96 : nullptr; a.cs = cs ? cs + img * 96 : nullptr;
         a.w1 = w1f; a.b1 = b1f; a.w2 = w2; a.b2 = b2; a.y = y + tok0 * 96;
         a.ln2_g = ln2_g; a.ln2_b = ln2_b; a.xn2 = xn2 ? xn2 + tok0 * 96 : nullptr;
-        a.ntiles = (uint32_t)(nimg * tok_per_img / 128);
-        a.tiles_per_img = (uint32_t)(tok_per_img / 128);
+        a.tiles_per_img = (uint32_t)((tok_per_img + 127) / 128);
+        a.ntiles = (uint32_t)(nimg * a.tiles_per_img);
+        a.tok_per_img = (uint32_t)tok_per_img;
         a.nimg = (uint32_t)nimg;
         a.dbg = g_fa_dbg;
         cudaLaunchConfig_t cfg;

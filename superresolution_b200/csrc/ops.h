@@ -33,7 +33,7 @@ int layernorm96(const bf16* in, const float* gamma, const float* beta, bf16* out
 int combine_ln96(const bf16* t, const bf16* cab, const float* cs, const float* gamma, const float* beta, bf16* y,
                  bf16* xn, size_t ntok, size_t tok_per_img, cudaStream_t s);
 int upsample2x(const bf16* in, int in_pitch, bf16* out, int B, int h, int w, cudaStream_t s);
-int cab_pool_slabs(int HW);  // pool scratch = B * slabs * 96 floats
+int cab_pool_slabs(int H, int W);  // pool scratch = B * slabs * 96 floats
 int cab_channel_scale(const float* pool, int nslab, float* cs, const float* w1, const float* b1, const float* w2,
                       const float* b2, float conv_scale, int B, int HW, cudaStream_t s);
 

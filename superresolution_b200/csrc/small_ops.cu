@@ -107,7 +107,7 @@ conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restric
 #pragma unroll
         for (int j = 0; j < 8; ++j) wr[t * 8 + j] = __ldg(w + (sub * 8 + j) * 9 + t);
     const float b0 = bias[0];
-    const int tiles_x = W / C1_TW, tiles_y = H / C1_TH;
+    const int tiles_x = (W + C1_TW - 1) / C1_TW, tiles_y = (H + C1_TH - 1) / C1_TH;  // ragged last tiles are masked
     const int ntiles = B * tiles_x * tiles_y;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, b = tile / (tiles_x * tiles_y);
@@ -141,17 +141,17 @@ conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restric
             s += __shfl_xor_sync(0xffffffffu, s, 1);
             s += __shfl_xor_sync(0xffffffffu, s, 2);
             s += __shfl_xor_sync(0xffffffffu, s, 4);
-            if (sub == 0) out[((size_t)b * H + ty * C1_TH + oy) * W + tx * C1_TW + ox] = s + b0;
+            if (sub == 0 && ty * C1_TH + oy < H && tx * C1_TW + ox < W)
+                out[((size_t)b * H + ty * C1_TH + oy) * W + tx * C1_TW + ox] = s + b0;
         }
     }
 }
 
 int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, float* out, int B, int H, int W,
                cudaStream_t s) {
-    if (H % C1_TH || W % C1_TW) { set_error("conv_cout1: H=%d W=%d must be multiples of %dx%d", H, W, C1_TH, C1_TW); return SRB_E_SHAPE; }
     static std::atomic<unsigned long long> attr{0};
     SRB_TRY(opt_in_dynamic_smem(conv_cout1_kernel, C1_SMEM, attr));
-    const int ntiles = B * (H / C1_TH) * (W / C1_TW);
+    const int ntiles = B * ((H + C1_TH - 1) / C1_TH) * ((W + C1_TW - 1) / C1_TW);
     int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;
     conv_cout1_kernel<<<grid, 256, C1_SMEM, s>>>(in, pitch, w, bias, out, B, H, W);
     SRB_CUDA(cudaGetLastError());

@@ -334,7 +334,8 @@ cab_finish_kernel(const float* __restrict__ partial, int nslab, float inv_hw, co
 }
 
 // One slab = one 16 x 16 output tile of the cab.2 conv (conv_tc <96,2,9>), which writes the per-tile sums itself.
-int cab_pool_slabs(int HW) { return (HW + 255) / 256; }
+// = the 16 x 16 spatial tiles of conv_tc<96, 2, 9> (cab.2), whose epilogue leaves one channel-sum row per tile
+int cab_pool_slabs(int H, int W) { return ((H + 15) / 16) * ((W + 15) / 16); }
 
 int cab_channel_scale(const float* pool, int nslab, float* cs, const float* w1, const float* b1, const float* w2,
                       const float* b2, float conv_scale, int B, int HW, cudaStream_t s) {

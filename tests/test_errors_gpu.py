@@ -15,7 +15,7 @@ def test_model_refuses_cpu_tensors_bad_ranks_and_bad_geometry(cuda):
     with pytest.raises(ValueError, match=r'\[B,1,H,W\]'):
         m(torch.rand(1, 3, 32, 32, device=cuda))
     with pytest.raises(RuntimeError, match='libsrb forward failed'):
-        m(torch.rand(1, 1, 40, 40, device=cuda))            # H, W must be multiples of 32
+        m(torch.rand(1, 1, 42, 40, device=cuda))            # H, W must be multiples of 4 (pixel_unshuffle(2) + 8x8 windows)
     m.train()
     with pytest.raises(ValueError, match='multiple of 32'):
         hybrid_forward(m, torch.rand(1, 1, 32, 32, device=cuda))   # training path: W % 64
