@@ -32,11 +32,13 @@
 // pitch, SBO = 128 B); V: [head][window][dim/8][key][8 dims] (MN-major core matrices: LBO = 128 B over keys, SBO = 1 KB
 // over the four 8-dim groups); bias: [head][query/8][key][8 queries].  All forms validated on B200 by
 // tools/probe_umma.cu / tools/probe_attn.cu.
+#include <cuda.h>
 #include <cstring>
 
 #include "common.h"
 #include "ops.h"
 #include "ptx.cuh"
+#include "tmap.h"
 
 namespace srb {
 
@@ -50,6 +52,9 @@ constexpr int kIssuerWarp0 = kComputeWarps + 1;     // warps 13, 14, 15: MMA iss
 constexpr int kHabThreads = (kComputeWarps + 4) * 32;
 constexpr int PP = 128 * 16 + 16;        // activation plane pitch (bytes): 128 token rows x 16 B + a 16-byte skew that
                                          // spreads the 6-lanes-per-token global I/O pattern over the banks
+constexpr int A1_WROW = 12 * 128;        // A1 (x -> xn, the qkv A operand): [window row 16][k-group 12][8 tokens][16 B]: one TMA
+                                         // box per window row (8 tokens x 96 channels = 1536 contiguous bytes in HBM); a
+                                         // (window row, k-group) block IS a core matrix: LBO = 128 B, SBO = 1536 B
 constexpr int WQ_PITCH = 288 * 16;       // qkv weight plane pitch
 constexpr int WP_PITCH = 96 * 16;        // proj weight plane pitch
 constexpr int VG = 64 * 16;              // V: one (head, window, 8-dim group) block = 64 keys x 16 B
@@ -89,6 +94,18 @@ struct HabArgs {
     int ntiles;           // window pairs
     long long* dbg;       // optional [grid][8] per-phase cycle totals of thread 0 (development aid)
 };
+
+// Development aid (-DSRB_HAB_TRACE): clock64 time stamps of CTA 0 on its tiles 3 and 4, [tile][warp][32 slots] behind the
+// phase totals (tools/hab_trace.py prints the timeline).
+#ifndef SRB_HAB_EXP
+#define SRB_HAB_EXP 0
+#endif
+#ifdef SRB_HAB_TRACE
+#define TR(k) do { if (a.dbg && blockIdx.x == 0 && (i == 3 || i == 4) && (threadIdx.x & 31) == 0) \
+    a.dbg[2 * 148 * 8 + ((i - 3) * 16 + (threadIdx.x >> 5)) * 32 + (k)] = clock64(); } while (0)
+#else
+#define TR(k) do { } while (0)
+#endif
 
 __device__ __forceinline__ uint32_t packbf(float lo, float hi) {
     __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
@@ -142,7 +159,7 @@ __device__ __forceinline__ float softmax_row(uint32_t tm_s, bool masked, const i
 }
 
 __global__ void __launch_bounds__(kHabThreads, 1)
-hab_tc_kernel(const HabArgs a) {
+hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmXN, const HabArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sWq = smem + OFF_WQ;
     uint8_t* sWp = smem + OFF_WP;
@@ -169,6 +186,7 @@ hab_tc_kernel(const HabArgs a) {
     uint64_t* bar_t = bars + 24;    // proj accumulated                         tcgen05.commit (issuer 0)
     uint64_t* bar_x = bars + 25;    // x(i) landed in A1, region ids written    count kIoThreads
     uint32_t* tmem_slot = (uint32_t*)(bars + 26);
+    int* sMsk = (int*)(bars + 28);  // [2][2]: does window w of the tile in buffer b touch the shift-mask border?
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int H = a.H, W = a.W, shift = a.shift;
@@ -185,6 +203,7 @@ hab_tc_kernel(const HabArgs a) {
         fence_barrier_init();
     }
     if (warp == kIssuerWarp0) { tmem_alloc(tmem_slot, HAB_TMEM_COLS); tmem_relinquish(); }
+    if (warp == kIoWarp && lane == 0) { tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmXN); }
     // constants of the launch
     for (int i = tid; i < 12 * 288; i += kHabThreads) {
         const int kg = i / 288, n = i % 288;
@@ -230,7 +249,7 @@ hab_tc_kernel(const HabArgs a) {
         auto issue_qkv_part = [&]() {
 #pragma unroll
             for (int ks = 0; ks < 6; ++ks)
-                umma_bf16_ss(tmem_base + 96 * g, umma_smem_desc(a1_u + ks * 2 * PP, PP, 128, UMMA_SW_NONE),
+                umma_bf16_ss(tmem_base + 96 * g, umma_smem_desc(a1_u + ks * 2 * 128, 128, A1_WROW, UMMA_SW_NONE),
                              umma_smem_desc(wq_u + g * 96 * 16 + ks * 2 * WQ_PITCH, WQ_PITCH, 128, UMMA_SW_NONE), idesc,
                              ks > 0);
             umma_commit(bar_qkv + g);
@@ -244,29 +263,36 @@ hab_tc_kernel(const HabArgs a) {
         for (int i = 0; i < n_my; ++i) {
             mbar_wait(bar_qkvw, i & 1);  // Q / K / V planes of tile i written, qkv accumulators read out
             tc_fence_after();
+            TR(0);
             if (elect_one()) {
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     const int h = g + 3 * hh;
+#if SRB_HAB_EXP != 2
 #pragma unroll
                     for (int w = 0; w < 2; ++w)  // S_h(window w) = Q K^T: M = 64 rows at lane offset 16 w
                         umma_bf16_ss(tmem_base + ((uint32_t)(16 * w) << 16) + 64 * h,
                                      umma_smem_desc(q_u + 2 * h * PP + 64 * w * 16, PP, 128, UMMA_SW_NONE),
                                      umma_smem_desc(k_u + 2 * h * PP + 64 * w * 16, PP, 128, UMMA_SW_NONE), idesc_s, 0);
+#endif
+#if SRB_HAB_EXP != 1
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)  // S_h += E * Bias_h^T for both windows at once: M = 128, lane L reads
                         umma_bf16_ts(tmem_base + 64 * h, tmem_base + COL_E + 8 * ks,  // its own one-hot row of E
                                      umma_smem_desc(bias_u + h * 8192 + ks * 2 * 1024, 1024, 128, UMMA_SW_NONE),
-                                     idesc_b, 1);
+                                     idesc_b, (SRB_HAB_EXP == 2) ? (ks > 0) : 1);
+#endif
                     umma_commit(bar_s + h);
                 }
             }
             __syncwarp();
+            TR(1);
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
                 const int h = g + 3 * hh;
                 mbar_wait(bar_p + h, i & 1);  // P_h of all 128 rows is in TMEM
                 tc_fence_after();
+                TR(2 + 2 * hh);
                 if (elect_one()) {
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)
@@ -276,9 +302,11 @@ hab_tc_kernel(const HabArgs a) {
                     umma_commit(bar_o + h);
                 }
                 __syncwarp();
+                TR(3 + 2 * hh);
             }
             mbar_wait(bar_ao, i & 1);  // normalised O(i) in the Q planes; every TMEM read of tile i's S / P / O is done
             tc_fence_after();
+            TR(6);
             if (g == 0) {
                 if (elect_one()) {
 #pragma unroll
@@ -289,77 +317,111 @@ hab_tc_kernel(const HabArgs a) {
                 }
                 __syncwarp();
             }
+            TR(7);
             if (i + 1 < n_my) {
                 mbar_wait(bar_a1, (i + 1) & 1);  // LN(i+1) precedes the O read-out of tile i: already complete
                 tc_fence_after();
+                TR(8);
                 if (elect_one()) issue_qkv_part();
                 __syncwarp();
+                TR(9);
             }
         }
     } else if (warp == kIoWarp) {
-        // ===================== I/O warp: x rows HBM -> A1 planes one tile ahead, xn rows A1 planes -> HBM =====================
-        // 4 lanes per token, lane j moves the 16-byte units j, j + 4, j + 8 -> every request covers 64 contiguous bytes
-        // per token (two full sectors); 16 passes of 8 tokens.
-        const int row0 = lane >> 2, uj = lane & 3;
-        uint32_t gp_c[16], gp_n[16];  // pixel index of this thread's rows: current / next tile (0xffffffff: no such window)
-        auto token_pix = [&](int tile, int row, int& rid) -> uint32_t {  // cyclic shift = index math; shift-mask region id
-            const int win = 2 * tile + (row >> 6), n = row & 63;
-            const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
-            const int ys = wy * 8 + (n >> 3), xs = wx * 8 + (n & 7);  // rolled-image coordinates
-            int y = ys + shift, x = xs + shift;                       // torch.roll(-shift): rolled[i] = orig[i + shift]
-            if (y >= H) y -= H;
-            if (x >= W) x -= W;
-            const int rh = ys < H - 8 ? 0 : (ys < H - 4 ? 1 : 2);
-            const int rw = xs < W - 8 ? 0 : (xs < W - 4 ? 1 : 2);
-            rid = rh * 3 + rw;
-            return win < nwin ? (uint32_t)((b * H + y) * W + x) : 0xffffffffu;
-        };
-        auto fetch_x = [&](int tile, int j) {  // x of this CTA's j-th tile: HBM -> A1 planes (cp.async); ids -> sRid / sGp
+        // ===================== I/O warp: x rows HBM -> A1 one tile ahead, xn rows A1 -> HBM, both by TMA =====================
+        // Lane p < 16 owns window row p of the tile (window p >> 3, row p & 7): 8 tokens x 96 channels = 1536 contiguous
+        // bytes in HBM = one 4-D box {8 ch, 8 tokens, 12 k-groups, 1 image row} that lands as 12 core matrices.  Only window
+        // rows whose 8 tokens wrap around the image edge under the cyclic shift (last window column, shift > 0) go
+        // through per-lane 16-byte copies.  cyclic shift = index math: rolled[i] = orig[i + shift] (torch.roll(-shift)).
+        int x0_c = 0, gr_c = 0, x0_n = 0, gr_n = 0;
+        bool tma_c = false, tma_n = false;
+        uint32_t wrap_c = 0, wrap_n = 0;  // bit p: window row p is copied by the lanes
+        auto plan = [&](int tile, int j) {  // index bookkeeping of the CTA's j-th tile: region ids / pixel indices / mask flags
             const int buf = j & 1, gbuf = j % 3;
+            bool have = false, wrapx = false;
+            tma_n = false;
+            if (lane < 16) {
+                const int wi = lane >> 3, pr = lane & 7;
+                const int win = 2 * tile + wi;
+                have = win < nwin;  // an odd window count leaves the last tile's second window empty
+                const int wx = win % nwx, wq = win / nwx;
+                const int wy = wq % nwy, b = wq / nwy;
+                const int ys = wy * 8 + pr;  // rolled-image coordinates
+                int y = ys + shift;
+                if (y >= H) y -= H;
+                const int rh = ys < H - 8 ? 0 : (ys < H - 4 ? 1 : 2);
+                wrapx = shift > 0 && wx == nwx - 1;
+                x0_n = wx * 8 + shift;
+                gr_n = b * H + y;
+                if (pr == 0) sMsk[buf * 2 + wi] = (shift > 0 && (wx == nwx - 1 || wy == nwy - 1)) ? 1 : 0;
 #pragma unroll
-            for (int p = 0; p < 16; ++p) {
-                const int row = 8 * p + row0;
-                int rid;
-                gp_n[p] = token_pix(tile, row, rid);
-                if (gp_n[p] != 0xffffffffu) {
-                    const uint4* xp = (const uint4*)(a.x + (size_t)gp_n[p] * 96) + uj;
-#pragma unroll
-                    for (int m = 0; m < 3; ++m) cp_async_16(sA1 + (uj + 4 * m) * PP + row * 16, xp + 4 * m);
+                for (int k = 0; k < 8; ++k) {
+                    const int xs = wx * 8 + k;
+                    int x = xs + shift;
+                    if (x >= W) x -= W;
+                    const int rw = xs < W - 8 ? 0 : (xs < W - 4 ? 1 : 2);
+                    sRid[buf * 128 + 8 * lane + k] = rh * 3 + rw;
+                    sGp[gbuf * 128 + 8 * lane + k] = have ? (uint32_t)(gr_n * W + x) : 0xffffffffu;
                 }
-                if (uj == 0) { sRid[buf * 128 + row] = rid; sGp[gbuf * 128 + row] = gp_n[p]; }
+                tma_n = have && !wrapx;
+            }
+            wrap_n = __ballot_sync(0xffffffffu, have && wrapx);
+        };
+        auto fetch = [&](int j) {  // x of the planned tile -> A1; completes bar_x (32 arrivals + the TMA bytes)
+            const int gbuf = j % 3;
+            const uint32_t ntma = __popc(__ballot_sync(0xffffffffu, tma_n));
+            if (lane == 0) mbar_arrive_expect_tx(bar_x, ntma * A1_WROW);
+            if (tma_n) tma_load_4d(sA1 + lane * A1_WROW, &tmX, bar_x, 0, x0_n, 0, gr_n);
+            for (uint32_t m = wrap_n; m; m &= m - 1) {
+                const int p = __ffs(m) - 1;
+#pragma unroll
+                for (int c = lane; c < 96; c += 32) {
+                    const int tok = c / 12, kg = c % 12;
+                    const uint32_t gp = sGp[gbuf * 128 + 8 * p + tok];
+                    cp_async_16(sA1 + p * A1_WROW + kg * 128 + tok * 16, (const uint4*)(a.x + (size_t)gp * 96) + kg);
+                }
             }
             cp_async_commit_group();
-        };
-        auto copy_out = [&](const uint8_t* planes, bf16* dst) {  // planes -> HBM
-#pragma unroll
-            for (int p = 0; p < 16; ++p) {
-                const int row = 8 * p + row0;
-                if (gp_c[p] != 0xffffffffu) {
-                    uint4* op = (uint4*)(dst + (size_t)gp_c[p] * 96) + uj;
-#pragma unroll
-                    for (int m = 0; m < 3; ++m) op[4 * m] = *(const uint4*)(planes + (uj + 4 * m) * PP + row * 16);
-                }
-            }
+            cp_async_wait_group<0>();
+            if (lane != 0) mbar_arrive(bar_x);
         };
         if (n_my > 0) {
-            fetch_x(first, 0);
-            cp_async_wait_group<0>();
-            mbar_arrive(bar_x);
+            plan(first, 0);
+            __syncwarp();
+            fetch(0);
         }
         for (int i = 0; i < n_my; ++i) {
             const int tile = first + i * step;
-#pragma unroll
-            for (int p = 0; p < 16; ++p) gp_c[p] = gp_n[p];
+            x0_c = x0_n; gr_c = gr_n; tma_c = tma_n; wrap_c = wrap_n;
             // xn(i) -> HBM for the CAB branch
             mbar_wait(bar_a1, i & 1);
-            copy_out(sA1, a.xn);
+            TR(0);
+            if (tma_c) {
+                tma_store_4d(&tmXN, sA1 + lane * A1_WROW, 0, x0_c, 0, gr_c);
+                bulk_commit_group();
+            }
+            for (uint32_t m = wrap_c; m; m &= m - 1) {
+                const int p = __ffs(m) - 1;
+#pragma unroll
+                for (int c = lane; c < 96; c += 32) {
+                    const int tok = c / 12, kg = c % 12;
+                    const uint32_t gp = sGp[(i % 3) * 128 + 8 * p + tok];
+                    *((uint4*)(a.xn + (size_t)gp * 96) + kg) = *(const uint4*)(sA1 + p * A1_WROW + kg * 128 + tok * 16);
+                }
+            }
+            TR(1);
             if (i + 1 < n_my) {  // x(i+1) -> A1, free once all three qkv parts of tile i have been accumulated
                 for (int part = 0; part < 3; ++part) mbar_wait(bar_qkv + part, i & 1);
-                fetch_x(tile + step, i + 1);
-                cp_async_wait_group<0>();
-                mbar_arrive(bar_x);
+                TR(2);
+                // (not earlier: sRid / sMsk[(i + 1) & 1] are read by the softmax of tile i - 1, which precedes qkv(i))
+                plan(tile + step, i + 1);
+                bulk_wait_group_read<0>();  // the xn stores have read A1
+                __syncwarp();
+                fetch(i + 1);
+                TR(4);
             }
         }
+        bulk_wait_group<0>();
     } else {
         // ===================== 12 compute warps =====================
         const int q = warp & 3, g = warp >> 2;
@@ -368,6 +430,7 @@ hab_tc_kernel(const HabArgs a) {
         const int am = 16 * q + (lane & 15);      // ... and query row inside it (M = 64 accumulator layout)
         const int ar = 64 * aw + am;              // the same query as a tile row
         const uint32_t tm_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+        uint8_t* a1_row = sA1 + (r >> 3) * A1_WROW + (r & 7) * 16;  // token row r of A1 (k-group kg at + kg * 128)
 
         if (g == 0) {  // identity rows for the bias MMAs: E[m][k] = (k == m) as bf16 pairs, one row per TMEM lane
             uint32_t e[32];
@@ -377,17 +440,17 @@ hab_tc_kernel(const HabArgs a) {
             tmem_st_wait();
         }
 
-        uint4 xc[4];             // this tile's 32 channels of x of row r (bf16): the shortcut of the proj epilogue
 #ifdef SRB_HAB_PHASES
         long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
 #define SRB_PHASE(k) do { if (a.dbg && (tid & 31) == 0 && tid < 64) { const long long tn = clock64(); ph[k] += tn - tprev; tprev = tn; } } while (0)
 #else
 #define SRB_PHASE(k) do { } while (0)
 #endif
-        // LayerNorm of the x parked in A1, in place (A1 becomes xn = the A operand of qkv); keeps x in `xk`
-        auto layer_norm = [&](uint4 (&xk)[4]) {
+        // LayerNorm of the x parked in A1, in place (A1 becomes xn = the A operand of qkv)
+        auto layer_norm = [&]() {
+            uint4 xk[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) xk[u] = *(const uint4*)(sA1 + (4 * g + u) * PP + r * 16);
+            for (int u = 0; u < 4; ++u) xk[u] = *(const uint4*)(a1_row + (4 * g + u) * 128);
             float v[32];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -425,7 +488,7 @@ hab_tc_kernel(const HabArgs a) {
                 for (int k = 0; k < 4; ++k)
                     ow[k] = packbf(fmaf((v[8 * u + 2 * k] - mean) * rs, gg[2 * k], bb[2 * k]),
                                    fmaf((v[8 * u + 2 * k + 1] - mean) * rs, gg[2 * k + 1], bb[2 * k + 1]));
-                *(uint4*)(sA1 + (4 * g + u) * PP + r * 16) = o4;
+                *(uint4*)(a1_row + (4 * g + u) * 128) = o4;
             }
             fence_proxy_async_smem();
             tc_fence_before();
@@ -436,9 +499,19 @@ hab_tc_kernel(const HabArgs a) {
         // GROUP'S OWN operand buffer (Q / K / V region: proj, S and PV of tile j are complete; the group itself is the
         // next writer of that buffer), then the group copies its 64 bytes per token out, 4 lanes per token.
         uint8_t* stage = (g == 0) ? sQ : (g == 1) ? sK : sV;
-        auto proj_epilogue = [&](int j, const uint4 (&xk)[4]) {
+        auto proj_epilogue = [&](int j) {
+            // the shortcut x (this thread's row, 32 channels = 64 bytes) comes back from L2 under the proj MMAs: holding
+            // it in registers since the LayerNorm cost 16 registers across the softmax and a local-memory spill
+            uint4 xk[4];
+            {
+                const uint32_t gpr = sGp[(j % 3) * 128 + r];
+                const uint4* xp = (const uint4*)(a.x + (size_t)(gpr != 0xffffffffu ? gpr : 0u) * 96 + 32 * g);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) xk[u] = xp[u];  // plain loads: t may alias x (each tile reads its rows first)
+            }
             mbar_wait(bar_t, j & 1);
             tc_fence_after();
+            { const int i = j; TR(12); }
             uint32_t acc[32];
             tmem_ld_32x32b_x32(tm_lane + COL_T + 32 * g, acc);
             tmem_ld_wait();
@@ -459,6 +532,7 @@ hab_tc_kernel(const HabArgs a) {
                 *(uint4*)(stage + u * PP + r * 16) = o4;
             }
             named_bar_sync(2 + g, 128);  // the group's 128 rows x 64 bytes are staged
+            { const int i = j; TR(13); }
             const int gt = tid & 127, cu = gt & 3;
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
@@ -472,14 +546,16 @@ hab_tc_kernel(const HabArgs a) {
 
         if (n_my > 0) {
             mbar_wait(bar_x, 0);
-            layer_norm(xc);
+            layer_norm();
         }
         for (int i = 0; i < n_my; ++i) {
             const int tile = first + i * step;
             const bool have_next = (i + 1 < n_my);
             // ---- qkv epilogue: this warp's 32 rows x the 96 columns of part g -> Q / K / V ----
+            TR(0);
             mbar_wait(bar_qkv + g, i & 1);
             tc_fence_after();
+            TR(1);
             SRB_PHASE(0);
             {
                 uint32_t acc[2][32];
@@ -516,31 +592,34 @@ hab_tc_kernel(const HabArgs a) {
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(bar_qkvw);
+            TR(2);
             SRB_PHASE(1);
             // ---- LN(i+1) in place on A1 while the issuers put S + bias of tile i on the tensor pipe (x(i+1) was fetched
-            //      as soon as qkv(i) had been accumulated); x(i+1) stays in registers for its proj epilogue ----
-            uint4 xnext[4];
+            //      as soon as qkv(i) had been accumulated) ----
             if (have_next) {
                 mbar_wait(bar_x, (i + 1) & 1);  // the I/O warp's cp.async of x(i+1) have landed
-                layer_norm(xnext);
+                TR(3);
+                layer_norm();
             }
+            TR(4);
             SRB_PHASE(4);
             // ---- softmax numerators of this group's two heads (S + bias arrives from the tensor pipe) ----
             float rowsum[2];
             {
-                const int win = 2 * tile + aw;
-                const int wxx = win % nwx, wyy = (win / nwx) % nwy;
-                const bool masked = shift > 0 && (wxx == nwx - 1 || wyy == nwy - 1);
+                const bool masked = sMsk[(i & 1) * 2 + aw] != 0;  // (written by the I/O warp with the region ids)
                 const int* rid_w = sRid + (i & 1) * 128 + 64 * aw;
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     const int h = g + 3 * hh;
+                    if (hh == 0) TR(14);
                     mbar_wait(bar_s + h, i & 1);
                     tc_fence_after();
+                    TR(5 + 2 * hh);
                     rowsum[hh] = softmax_row(tm_lane + 64 * h, masked, rid_w, am);
                     tmem_st_wait();
                     tc_fence_before();
                     mbar_arrive(bar_p + h);
+                    TR(6 + 2 * hh);
                     if (hh == 0) SRB_PHASE(2);
                 }
             }
@@ -551,6 +630,7 @@ hab_tc_kernel(const HabArgs a) {
                 const int h = g + 3 * hh;
                 mbar_wait(bar_o + h, i & 1);
                 tc_fence_after();
+                TR(9 + hh);
                 uint32_t o2[32];  // [window 0 dims | window 1 dims]: the TMEM address must be warp-uniform, so both
                 tmem_ld_32x32b_x32(tm_lane + 64 * h + 32, o2);  // halves are loaded and each lane keeps its window's
                 tmem_ld_wait();
@@ -570,13 +650,11 @@ hab_tc_kernel(const HabArgs a) {
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(bar_ao);
+            TR(11);
             SRB_PHASE(5);
             // ---- proj epilogue(i) (direct 64-byte row-segment stores) while the tensor pipe runs qkv(i+1) ----
-            proj_epilogue(i, xc);
-            if (have_next) {
-#pragma unroll
-                for (int u = 0; u < 4; ++u) xc[u] = xnext[u];
-            }
+            proj_epilogue(i);
+            TR(15);
             SRB_PHASE(6);
         }
 #ifdef SRB_HAB_PHASES
@@ -619,7 +697,18 @@ int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const 
     attrs[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attrs;
     cfg.numAttrs = 1;
-    SRB_CUDA(cudaLaunchKernelEx(&cfg, hab_tc_kernel, a));
+    // x / xn as 4-D tensors {8 channels (16 B), W tokens, 12 channel groups, B * H image rows}: the box {8, 8, 12, 1} is
+    // one window row (8 tokens x 96 channels, contiguous in HBM) and lands in shared memory k-group-major
+    CUtensorMap tmX, tmXN;
+    {
+        if ((((uintptr_t)x | (uintptr_t)xn | (uintptr_t)t) & 15)) { set_error("hab_attention: x / xn / t must be 16-byte aligned"); return SRB_E_ARG; }
+        cuuint64_t dims[4] = {8, (cuuint64_t)W, 12, (cuuint64_t)B * H};
+        cuuint64_t str[3] = {192, 16, (cuuint64_t)W * 192};
+        cuuint32_t box[4] = {8, 8, 12, 1};
+        SRB_TRY(encode_bf16_map(&tmX, x, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE));
+        SRB_TRY(encode_bf16_map(&tmXN, xn, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE));
+    }
+    SRB_CUDA(cudaLaunchKernelEx(&cfg, hab_tc_kernel, tmX, tmXN, a));
     return SRB_OK;
 }
 
