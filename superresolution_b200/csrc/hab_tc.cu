@@ -52,9 +52,14 @@ constexpr int kIssuerWarp0 = kComputeWarps + 1;     // warps 13, 14, 15: MMA iss
 constexpr int kHabThreads = (kComputeWarps + 4) * 32;
 constexpr int PP = 128 * 16 + 16;        // activation plane pitch (bytes): 128 token rows x 16 B + a 16-byte skew that
                                          // spreads the 6-lanes-per-token global I/O pattern over the banks
-constexpr int A1_WROW = 12 * 128;        // A1 (x -> xn, the qkv A operand): [window row 16][k-group 12][8 tokens][16 B]: one TMA
-                                         // box per window row (8 tokens x 96 channels = 1536 contiguous bytes in HBM); a
-                                         // (window row, k-group) block IS a core matrix: LBO = 128 B, SBO = 1536 B
+// A1 (x -> xn, the A operand of qkv) in the canonical swizzled K-major layouts the TMA writes at full speed: channels
+// [0, 64) as 128 rows x 128 B (SWIZZLE_128B), channels [64, 96) as 128 rows x 64 B (SWIZZLE_64B).  One window row (8 tokens
+// = 8 consecutive tile rows, 1536 contiguous bytes in HBM) = two boxes {64 ch, 8 tokens} + {32 ch, 8 tokens}.
+constexpr int A1_C1 = 128 * 128;         // byte offset of the second channel chunk
+__device__ __forceinline__ uint32_t a1_off(int row, int kg) {  // 16-byte unit kg (8 channels) of token row `row`
+    return kg < 8 ? (uint32_t)(row * 128 + ((kg ^ (row & 7)) << 4))
+                  : (uint32_t)(A1_C1 + row * 64 + (((kg - 8) ^ ((row >> 1) & 3)) << 4));
+}
 constexpr int WQ_PITCH = 288 * 16;       // qkv weight plane pitch
 constexpr int WP_PITCH = 96 * 16;        // proj weight plane pitch
 constexpr int VG = 64 * 16;              // V: one (head, window, 8-dim group) block = 64 keys x 16 B
@@ -76,6 +81,7 @@ constexpr int HAB_TC_SMEM = OFF_BAR + 32 * 8;
 constexpr uint32_t COL_T = 384, COL_E = 480, HAB_TMEM_COLS = 512;  // qkv: cols [0, 288); S/P/O of head h: cols [64h, 64h + 64);
                                                                    // E: 64 x 64 identity (bf16 pairs), cols [480, 512)
 static_assert(HAB_TC_SMEM <= 227 * 1024, "shared memory budget");
+static_assert(OFF_A1 % 1024 == 0 && A1_C1 % 1024 == 0, "the swizzled A1 chunks need 1024-byte alignment");
 static_assert(OFF_A1 % 16 == 0 && OFF_Q % 16 == 0 && OFF_K % 16 == 0 && OFF_V % 16 == 0 && OFF_BIAS % 16 == 0 &&
               OFF_BAR % 8 == 0, "alignment");
 
@@ -159,7 +165,8 @@ __device__ __forceinline__ float softmax_row(uint32_t tm_s, bool masked, const i
 }
 
 __global__ void __launch_bounds__(kHabThreads, 1)
-hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmXN, const HabArgs a) {
+hab_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
+              const __grid_constant__ CUtensorMap tmN0, const __grid_constant__ CUtensorMap tmN1, const HabArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sWq = smem + OFF_WQ;
     uint8_t* sWp = smem + OFF_WP;
@@ -193,6 +200,7 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
     const int nwx = W / 8, nwy = H / 8;
 
     if (tid == 0) {
+        if (smem_u32(sA1) & 1023u) __trap();  // swizzle pattern = address bits: the dynamic smem base must be 1 KB aligned
         mbar_init(bar_a1, kComputeThreads);
         for (int i = 0; i < 3; ++i) mbar_init(bar_qkv + i, 1);
         mbar_init(bar_qkvw, kComputeThreads);
@@ -203,7 +211,9 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         fence_barrier_init();
     }
     if (warp == kIssuerWarp0) { tmem_alloc(tmem_slot, HAB_TMEM_COLS); tmem_relinquish(); }
-    if (warp == kIoWarp && lane == 0) { tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmXN); }
+    if (warp == kIoWarp && lane == 0) {
+        tma_prefetch_desc(&tmX0); tma_prefetch_desc(&tmX1); tma_prefetch_desc(&tmN0); tma_prefetch_desc(&tmN1);
+    }
     // constants of the launch
     for (int i = tid; i < 12 * 288; i += kHabThreads) {
         const int kg = i / 288, n = i % 288;
@@ -248,8 +258,10 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         const uint32_t idesc_pv = umma_idesc_bf16_f32_major(128, 32, 0, 1);
         auto issue_qkv_part = [&]() {
 #pragma unroll
-            for (int ks = 0; ks < 6; ++ks)
-                umma_bf16_ss(tmem_base + 96 * g, umma_smem_desc(a1_u + ks * 2 * 128, 128, A1_WROW, UMMA_SW_NONE),
+            for (int ks = 0; ks < 6; ++ks)  // k-steps 0-3: the 128B-swizzled chunk (32 bytes per step), 4-5: the 64B one
+                umma_bf16_ss(tmem_base + 96 * g,
+                             ks < 4 ? umma_smem_desc(a1_u + ks * 32, 16, 1024, UMMA_SW_128B)
+                                    : umma_smem_desc(a1_u + A1_C1 + (ks - 4) * 32, 16, 512, UMMA_SW_64B),
                              umma_smem_desc(wq_u + g * 96 * 16 + ks * 2 * WQ_PITCH, WQ_PITCH, 128, UMMA_SW_NONE), idesc,
                              ks > 0);
             umma_commit(bar_qkv + g);
@@ -329,65 +341,85 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         }
     } else if (warp == kIoWarp) {
         // ===================== I/O warp: x rows HBM -> A1 one tile ahead, xn rows A1 -> HBM, both by TMA =====================
-        // Lane p < 16 owns window row p of the tile (window p >> 3, row p & 7): 8 tokens x 96 channels = 1536 contiguous
-        // bytes in HBM = one 4-D box {8 ch, 8 tokens, 12 k-groups, 1 image row} that lands as 12 core matrices.  Only window
-        // rows whose 8 tokens wrap around the image edge under the cyclic shift (last window column, shift > 0) go
-        // through per-lane 16-byte copies.  cyclic shift = index math: rolled[i] = orig[i + shift] (torch.roll(-shift)).
-        int x0_c = 0, gr_c = 0, x0_n = 0, gr_n = 0;
+        // Lane p < 16 does the index math of window row p of the tile (window p >> 3, row p & 7); a window row is 8 tokens
+        // x 96 channels = 1536 contiguous bytes in HBM and 8 consecutive rows of the swizzled A1 chunks, so half a window
+        // (4 window rows) moves as two 3-D boxes {64 ch, 8 tokens, 4 rows} + {32 ch, 8 tokens, 4 rows}.  Only window rows
+        // whose 8 tokens wrap around the image edge under the cyclic shift (last window column, shift > 0) go through
+        // per-lane 16-byte copies.  cyclic shift = index math: rolled[i] = orig[i + shift] (torch.roll(-shift)).
+        int x0_c = 0, gr_c = 0, x0_n = 0, gr_n = 0;  // lanes 0-3: TMA box (window lane >> 1, half lane & 1) of the current / next tile
         bool tma_c = false, tma_n = false;
         uint32_t wrap_c = 0, wrap_n = 0;  // bit p: window row p is copied by the lanes
-        auto plan = [&](int tile, int j) {  // index bookkeeping of the CTA's j-th tile: region ids / pixel indices / mask flags
-            const int buf = j & 1, gbuf = j % 3;
-            bool have = false, wrapx = false;
-            tma_n = false;
+        int r_wx = 0, r_wy = 0, r_gr = 0;  // lanes 0-15: window row 'lane' of the planned tile
+        bool r_have = false;
+        // index math of the CTA's next tile, registers only (runs before A1 is free)
+        auto plan_regs = [&](int tile) {
+            bool wrapx = false;
+            r_have = false;
             if (lane < 16) {
                 const int wi = lane >> 3, pr = lane & 7;
                 const int win = 2 * tile + wi;
-                have = win < nwin;  // an odd window count leaves the last tile's second window empty
-                const int wx = win % nwx, wq = win / nwx;
-                const int wy = wq % nwy, b = wq / nwy;
-                const int ys = wy * 8 + pr;  // rolled-image coordinates
-                int y = ys + shift;
+                r_have = win < nwin;  // an odd window count leaves the last tile's second window empty
+                r_wx = win % nwx;
+                const int wq = win / nwx;
+                r_wy = wq % nwy;
+                int y = r_wy * 8 + pr + shift;  // rolled-image row pr of the window -> image row
                 if (y >= H) y -= H;
+                r_gr = (wq / nwy) * H + y;
+                wrapx = shift > 0 && r_wx == nwx - 1;
+            }
+            wrap_n = __ballot_sync(0xffffffffu, r_have && wrapx);
+            // one TMA box = 4 window rows (half a window: 8-aligned windows shifted by 4 never wrap inside a half); lane
+            // L < 4 issues the boxes of window L >> 1, half L & 1 (a TMA instruction costs its issuing warp ~90 cycles)
+            const int src = lane < 4 ? 8 * (lane >> 1) + 4 * (lane & 1) : 0;
+            x0_n = __shfl_sync(0xffffffffu, r_wx * 8 + shift, src);
+            gr_n = __shfl_sync(0xffffffffu, r_gr, src);
+            tma_n = __shfl_sync(0xffffffffu, (int)(r_have && !wrapx), src) != 0 && lane < 4;
+        };
+        // region ids / pixel indices / mask flags of the planned tile -> smem (buffers of tile j: see OFF_RID / OFF_GP)
+        auto plan_smem = [&](int j) {
+            const int buf = j & 1, gbuf = j % 3;
+            if (lane < 16) {
+                const int ys = r_wy * 8 + (lane & 7);
                 const int rh = ys < H - 8 ? 0 : (ys < H - 4 ? 1 : 2);
-                wrapx = shift > 0 && wx == nwx - 1;
-                x0_n = wx * 8 + shift;
-                gr_n = b * H + y;
-                if (pr == 0) sMsk[buf * 2 + wi] = (shift > 0 && (wx == nwx - 1 || wy == nwy - 1)) ? 1 : 0;
+                if ((lane & 7) == 0) sMsk[buf * 2 + (lane >> 3)] = (shift > 0 && (r_wx == nwx - 1 || r_wy == nwy - 1)) ? 1 : 0;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    const int xs = wx * 8 + k;
+                    const int xs = r_wx * 8 + k;
                     int x = xs + shift;
                     if (x >= W) x -= W;
                     const int rw = xs < W - 8 ? 0 : (xs < W - 4 ? 1 : 2);
                     sRid[buf * 128 + 8 * lane + k] = rh * 3 + rw;
-                    sGp[gbuf * 128 + 8 * lane + k] = have ? (uint32_t)(gr_n * W + x) : 0xffffffffu;
+                    sGp[gbuf * 128 + 8 * lane + k] = r_have ? (uint32_t)(r_gr * W + x) : 0xffffffffu;
                 }
-                tma_n = have && !wrapx;
             }
-            wrap_n = __ballot_sync(0xffffffffu, have && wrapx);
+            __syncwarp();
         };
-        auto fetch = [&](int j) {  // x of the planned tile -> A1; completes bar_x (32 arrivals + the TMA bytes)
+        // x of the planned tile -> A1 (TMA boxes first, then the bookkeeping, then the wrapped rows); completes bar_x
+        auto fetch = [&](int j) {
             const int gbuf = j % 3;
             const uint32_t ntma = __popc(__ballot_sync(0xffffffffu, tma_n));
-            if (lane == 0) mbar_arrive_expect_tx(bar_x, ntma * A1_WROW);
-            if (tma_n) tma_load_4d(sA1 + lane * A1_WROW, &tmX, bar_x, 0, x0_n, 0, gr_n);
+            if (lane == 0) mbar_expect_tx(bar_x, ntma * 4 * 1536);
+            __syncwarp();
+            if (tma_n) {
+                tma_load_3d(sA1 + lane * 4 * 1024, &tmX0, bar_x, 0, x0_n, gr_n);
+                tma_load_3d(sA1 + A1_C1 + lane * 4 * 512, &tmX1, bar_x, 0, x0_n, gr_n);
+            }
+            plan_smem(j);
             for (uint32_t m = wrap_n; m; m &= m - 1) {
                 const int p = __ffs(m) - 1;
 #pragma unroll
                 for (int c = lane; c < 96; c += 32) {
                     const int tok = c / 12, kg = c % 12;
                     const uint32_t gp = sGp[gbuf * 128 + 8 * p + tok];
-                    cp_async_16(sA1 + p * A1_WROW + kg * 128 + tok * 16, (const uint4*)(a.x + (size_t)gp * 96) + kg);
+                    cp_async_16(sA1 + a1_off(8 * p + tok, kg), (const uint4*)(a.x + (size_t)gp * 96) + kg);
                 }
             }
             cp_async_commit_group();
             cp_async_wait_group<0>();
-            if (lane != 0) mbar_arrive(bar_x);
+            mbar_arrive(bar_x);
         };
         if (n_my > 0) {
-            plan(first, 0);
-            __syncwarp();
+            plan_regs(first);
             fetch(0);
         }
         for (int i = 0; i < n_my; ++i) {
@@ -397,7 +429,8 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             mbar_wait(bar_a1, i & 1);
             TR(0);
             if (tma_c) {
-                tma_store_4d(&tmXN, sA1 + lane * A1_WROW, 0, x0_c, 0, gr_c);
+                tma_store_3d(&tmN0, sA1 + lane * 4 * 1024, 0, x0_c, gr_c);
+                tma_store_3d(&tmN1, sA1 + A1_C1 + lane * 4 * 512, 0, x0_c, gr_c);
                 bulk_commit_group();
             }
             for (uint32_t m = wrap_c; m; m &= m - 1) {
@@ -406,17 +439,17 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 for (int c = lane; c < 96; c += 32) {
                     const int tok = c / 12, kg = c % 12;
                     const uint32_t gp = sGp[(i % 3) * 128 + 8 * p + tok];
-                    *((uint4*)(a.xn + (size_t)gp * 96) + kg) = *(const uint4*)(sA1 + p * A1_WROW + kg * 128 + tok * 16);
+                    *((uint4*)(a.xn + (size_t)gp * 96) + kg) = *(const uint4*)(sA1 + a1_off(8 * p + tok, kg));
                 }
             }
             TR(1);
             if (i + 1 < n_my) {  // x(i+1) -> A1, free once all three qkv parts of tile i have been accumulated
+                plan_regs(tile + step);
+                bulk_wait_group_read<0>();  // the xn stores have read A1
                 for (int part = 0; part < 3; ++part) mbar_wait(bar_qkv + part, i & 1);
                 TR(2);
-                // (not earlier: sRid / sMsk[(i + 1) & 1] are read by the softmax of tile i - 1, which precedes qkv(i))
-                plan(tile + step, i + 1);
-                bulk_wait_group_read<0>();  // the xn stores have read A1
-                __syncwarp();
+                // (the smem bookkeeping inside fetch() may not run earlier: sRid / sMsk[(i + 1) & 1] are read by the softmax
+                // of tile i - 1, which precedes qkv(i))
                 fetch(i + 1);
                 TR(4);
             }
@@ -430,7 +463,6 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         const int am = 16 * q + (lane & 15);      // ... and query row inside it (M = 64 accumulator layout)
         const int ar = 64 * aw + am;              // the same query as a tile row
         const uint32_t tm_lane = tmem_base + ((uint32_t)(q * 32) << 16);
-        uint8_t* a1_row = sA1 + (r >> 3) * A1_WROW + (r & 7) * 16;  // token row r of A1 (k-group kg at + kg * 128)
 
         if (g == 0) {  // identity rows for the bias MMAs: E[m][k] = (k == m) as bf16 pairs, one row per TMEM lane
             uint32_t e[32];
@@ -450,7 +482,7 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
         auto layer_norm = [&]() {
             uint4 xk[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) xk[u] = *(const uint4*)(a1_row + (4 * g + u) * 128);
+            for (int u = 0; u < 4; ++u) xk[u] = *(const uint4*)(sA1 + a1_off(r, 4 * g + u));
             float v[32];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
@@ -488,7 +520,7 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
                 for (int k = 0; k < 4; ++k)
                     ow[k] = packbf(fmaf((v[8 * u + 2 * k] - mean) * rs, gg[2 * k], bb[2 * k]),
                                    fmaf((v[8 * u + 2 * k + 1] - mean) * rs, gg[2 * k + 1], bb[2 * k + 1]));
-                *(uint4*)(a1_row + (4 * g + u) * 128) = o4;
+                *(uint4*)(sA1 + a1_off(r, 4 * g + u)) = o4;
             }
             fence_proxy_async_smem();
             tc_fence_before();
@@ -560,31 +592,45 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ C
             {
                 uint32_t acc[2][32];
                 tmem_ld_32x32b_x32(tm_lane + 96 * g, acc[0]);
+                if (g == 0) {  // q = (acc + bq) * head_dim^-0.5 * log2(e); the chunk's 32 biases are fetched under the TMEM load
 #pragma unroll
-                for (int j = 0; j < 3; ++j) {
-                    tmem_ld_wait();  // chunk j is in registers; fetch chunk j+1 while it is converted
-                    if (j < 2) tmem_ld_32x32b_x32(tm_lane + 96 * g + 32 * (j + 1), acc[(j + 1) & 1]);
+                    for (int j = 0; j < 3; ++j) {
+                        float4 bb[8];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        uint4 o4;
-                        uint32_t* ow = (uint32_t*)&o4;
-                        const int dgi = 4 * j + u;  // 8-channel group of this part: head dgi >> 1, half dgi & 1
-                        if (g == 0) {  // q = (acc + bq) * head_dim^-0.5 * log2(e)
-                            const float4 b0 = *(const float4*)(sbq + 8 * dgi), b1 = *(const float4*)(sbq + 8 * dgi + 4);
-                            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                        for (int u = 0; u < 8; ++u) bb[u] = *(const float4*)(sbq + 32 * j + 4 * u);
+                        tmem_ld_wait();  // chunk j is in registers; fetch chunk j+1 while it is converted
+                        if (j < 2) tmem_ld_32x32b_x32(tm_lane + 32 * (j + 1), acc[(j + 1) & 1]);
 #pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                ow[k] = packbf(fmaf(__uint_as_float(acc[j & 1][8 * u + 2 * k]), 0.25f * kLog2e, bb[2 * k]),
-                                               fmaf(__uint_as_float(acc[j & 1][8 * u + 2 * k + 1]), 0.25f * kLog2e, bb[2 * k + 1]));
-                            *(uint4*)(sQ + dgi * PP + r * 16) = o4;
-                        } else {       // k, v: no bias (see the prologue)
+                        for (int u = 0; u < 4; ++u) {
+                            const uint32_t* ac = acc[j & 1] + 8 * u;
+                            const float4 b0 = bb[2 * u], b1 = bb[2 * u + 1];
+                            uint4 o4;
+                            o4.x = packbf(fmaf(__uint_as_float(ac[0]), 0.25f * kLog2e, b0.x), fmaf(__uint_as_float(ac[1]), 0.25f * kLog2e, b0.y));
+                            o4.y = packbf(fmaf(__uint_as_float(ac[2]), 0.25f * kLog2e, b0.z), fmaf(__uint_as_float(ac[3]), 0.25f * kLog2e, b0.w));
+                            o4.z = packbf(fmaf(__uint_as_float(ac[4]), 0.25f * kLog2e, b1.x), fmaf(__uint_as_float(ac[5]), 0.25f * kLog2e, b1.y));
+                            o4.w = packbf(fmaf(__uint_as_float(ac[6]), 0.25f * kLog2e, b1.z), fmaf(__uint_as_float(ac[7]), 0.25f * kLog2e, b1.w));
+                            *(uint4*)(sQ + (4 * j + u) * PP + r * 16) = o4;
+                        }
+                    }
+                } else {       // k, v: no bias (see the prologue)
+                    // V[head][window][half][key]: MN-major operand of the PV MMAs; K: planes like Q
+                    uint8_t* dst0 = (g == 2) ? sV + ((r >> 6) * 2) * VG + (r & 63) * 16 : sK + r * 16;
+                    const int pitch = (g == 2) ? VG : PP;  // 8-channel group dgi -> V block (dgi >> 1) * 4 + (dgi & 1) / K plane dgi
 #pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                ow[k] = packbf(__uint_as_float(acc[j & 1][8 * u + 2 * k]), __uint_as_float(acc[j & 1][8 * u + 2 * k + 1]));
-                            if (g == 2)  // V[head][window][half][key]: MN-major operand of the PV MMAs
-                                *(uint4*)(sV + (((dgi >> 1) * 4 + (r >> 6) * 2 + (dgi & 1)) * VG) + (r & 63) * 16) = o4;
-                            else
-                                *(uint4*)(sK + dgi * PP + r * 16) = o4;
+                    for (int j = 0; j < 3; ++j) {
+                        tmem_ld_wait();
+                        if (j < 2) tmem_ld_32x32b_x32(tm_lane + 96 * g + 32 * (j + 1), acc[(j + 1) & 1]);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const uint32_t* ac = acc[j & 1] + 8 * u;
+                            const int dgi = 4 * j + u;
+                            const int blk = (g == 2) ? (dgi >> 1) * 4 + (dgi & 1) : dgi;
+                            uint4 o4;
+                            o4.x = packbf(__uint_as_float(ac[0]), __uint_as_float(ac[1]));
+                            o4.y = packbf(__uint_as_float(ac[2]), __uint_as_float(ac[3]));
+                            o4.z = packbf(__uint_as_float(ac[4]), __uint_as_float(ac[5]));
+                            o4.w = packbf(__uint_as_float(ac[6]), __uint_as_float(ac[7]));
+                            *(uint4*)(dst0 + blk * pitch) = o4;
                         }
                     }
                 }
@@ -697,18 +743,20 @@ int hab_attention_tc(const bf16* x, const float* ln_g, const float* ln_b, const 
     attrs[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attrs;
     cfg.numAttrs = 1;
-    // x / xn as 4-D tensors {8 channels (16 B), W tokens, 12 channel groups, B * H image rows}: the box {8, 8, 12, 1} is
-    // one window row (8 tokens x 96 channels, contiguous in HBM) and lands in shared memory k-group-major
-    CUtensorMap tmX, tmXN;
+    // x / xn as 3-D tensors {channels, W tokens, B * H image rows}, one map per channel chunk: box {64, 8, 4} (half a window) with
+    // SWIZZLE_128B over channels [0, 64) and box {32, 8, 4} with SWIZZLE_64B over channels [64, 96)
+    CUtensorMap tmX0, tmX1, tmN0, tmN1;
     {
         if ((((uintptr_t)x | (uintptr_t)xn | (uintptr_t)t) & 15)) { set_error("hab_attention: x / xn / t must be 16-byte aligned"); return SRB_E_ARG; }
-        cuuint64_t dims[4] = {8, (cuuint64_t)W, 12, (cuuint64_t)B * H};
-        cuuint64_t str[3] = {192, 16, (cuuint64_t)W * 192};
-        cuuint32_t box[4] = {8, 8, 12, 1};
-        SRB_TRY(encode_bf16_map(&tmX, x, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE));
-        SRB_TRY(encode_bf16_map(&tmXN, xn, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE));
+        cuuint64_t d0[3] = {64, (cuuint64_t)W, (cuuint64_t)B * H}, d1[3] = {32, (cuuint64_t)W, (cuuint64_t)B * H};
+        cuuint64_t str[2] = {192, (cuuint64_t)W * 192};
+        cuuint32_t b0[3] = {64, 8, 4}, b1[3] = {32, 8, 4};
+        SRB_TRY(encode_bf16_map(&tmX0, x, 3, d0, str, b0, CU_TENSOR_MAP_SWIZZLE_128B));
+        SRB_TRY(encode_bf16_map(&tmX1, x + 64, 3, d1, str, b1, CU_TENSOR_MAP_SWIZZLE_64B));
+        SRB_TRY(encode_bf16_map(&tmN0, xn, 3, d0, str, b0, CU_TENSOR_MAP_SWIZZLE_128B));
+        SRB_TRY(encode_bf16_map(&tmN1, xn + 64, 3, d1, str, b1, CU_TENSOR_MAP_SWIZZLE_64B));
     }
-    SRB_CUDA(cudaLaunchKernelEx(&cfg, hab_tc_kernel, tmX, tmXN, a));
+    SRB_CUDA(cudaLaunchKernelEx(&cfg, hab_tc_kernel, tmX0, tmX1, tmN0, tmN1, a));
     return SRB_OK;
 }
 
