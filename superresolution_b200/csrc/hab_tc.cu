@@ -50,8 +50,8 @@ constexpr int kIoWarp = kComputeWarps;              // warp 12
 constexpr int kIoThreads = 32;
 constexpr int kIssuerWarp0 = kComputeWarps + 1;     // warps 13, 14, 15: MMA issuers of group 0, 1, 2
 constexpr int kHabThreads = (kComputeWarps + 4) * 32;
-constexpr int PP = 128 * 16 + 16;        // activation plane pitch (bytes): 128 token rows x 16 B + a 16-byte skew that
-                                         // spreads the 6-lanes-per-token global I/O pattern over the banks
+constexpr int PP = 128 * 16 + 32;        // Q / K / staging plane pitch (bytes): 128 token rows x 16 B + a 32-byte skew that
+                                         // makes the 4-lanes-per-token copy-out of the proj epilogue bank-conflict free
 // A1 (x -> xn, the A operand of qkv) in the canonical swizzled K-major layouts the TMA writes at full speed: channels
 // [0, 64) as 128 rows x 128 B (SWIZZLE_128B), channels [64, 96) as 128 rows x 64 B (SWIZZLE_64B).  One window row (8 tokens
 // = 8 consecutive tile rows, 1536 contiguous bytes in HBM) = two boxes {64 ch, 8 tokens} + {32 ch, 8 tokens}.
@@ -66,7 +66,7 @@ constexpr int VG = 64 * 16;              // V: one (head, window, 8-dim group) b
 constexpr int OFF_WQ = 0;
 constexpr int OFF_WP = OFF_WQ + 12 * WQ_PITCH;
 constexpr int OFF_A1 = OFF_WP + 12 * WP_PITCH;
-constexpr int OFF_Q = OFF_A1 + 12 * PP;
+constexpr int OFF_Q = OFF_A1 + 128 * 192;   // A1: 128 rows x 96 channels (two swizzled chunks)
 constexpr int OFF_K = OFF_Q + 12 * PP;
 constexpr int OFF_V = OFF_K + 12 * PP;
 constexpr int OFF_BIAS = OFF_V + 24 * VG;               // bf16 [6][8][64][8] * log2(e): B operand planes [query/8][key][8 queries]

@@ -81,6 +81,15 @@ __device__ __forceinline__ uint4 bias_split(float b) {
     return make_uint4((uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(lo) << 16), 0u, 0u, 0u);
 }
 
+// Development aid (-DSRB_MLP_TRACE): clock64 stamps of CTA 0 on its tiles 3 and 4, [tile][warp 0..17][16 slots] behind
+// the phase totals (tools/mlp_trace.py prints the timeline).
+#ifdef SRB_MLP_TRACE
+#define TR(k) do { if (a.dbg && blockIdx.x == 0 && (i == 3 || i == 4) && (threadIdx.x & 31) == 0) \
+    a.dbg[148 * 8 + ((i - 3) * 18 + (threadIdx.x >> 5)) * 16 + (k)] = clock64(); } while (0)
+#else
+#define TR(k) do { } while (0)
+#endif
+
 template <bool LN2>
 __global__ void __launch_bounds__(kMlpThreads, 1)
 mlp_tc_kernel(const MlpArgs a) {
@@ -150,6 +159,7 @@ mlp_tc_kernel(const MlpArgs a) {
         for (uint32_t i = 0; i < n_my; ++i) {
             mbar_wait(bar_a1, i & 1);
             tc_fence_after();
+            TR(0);
             if (elect_one()) {
 #pragma unroll
                 for (int ks = 0; ks < A1_PLANES / 2; ++ks)
@@ -159,8 +169,10 @@ mlp_tc_kernel(const MlpArgs a) {
                 umma_commit(bar_d1);
             }
             __syncwarp();
+            TR(1);
             mbar_wait(bar_a2, i & 1);
             tc_fence_after();
+            TR(2);
             if (elect_one()) {
 #pragma unroll
                 for (int ks = 0; ks < A2_PLANES / 2; ++ks)
@@ -170,6 +182,7 @@ mlp_tc_kernel(const MlpArgs a) {
                 umma_commit(bar_d2);
             }
             __syncwarp();
+            TR(3);
         }
     } else if (warp < kAluWarps) {
         // ===================== ALU warps =====================
@@ -288,8 +301,10 @@ mlp_tc_kernel(const MlpArgs a) {
             const uint32_t tile = first + i * step;
             // ---- (a) GELU(i): D1 -> A2 ----
             SRB_PHASE(7);
+            TR(0);
             mbar_wait(bar_d1, i & 1);
             tc_fence_after();
+            TR(1);
             SRB_PHASE(0);
             {
                 uint32_t acc[48];
@@ -317,18 +332,22 @@ mlp_tc_kernel(const MlpArgs a) {
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(bar_a2);
+            TR(2);
             SRB_PHASE(1);
             // ---- (b) LN(i+1) -> A1 (fc1(i) has completed: bar_d1 was waited), prefetch tile i+2 ----
             // the barrier orders copy-out(i-1) (last readers of YP[(i+1)&1]) before the y0(i+1) stores
             named_bar_sync(1, kAluThreads);
+            TR(3);
             SRB_PHASE(1);
             if (i + 1 < n_my) {
                 layer_norm(tile + step, i + 1);
             }
+            TR(4);
             SRB_PHASE(5);
             // ---- (c) EPI(i): D2 + y0 -> YP[i&1] in place (row per lane: conflict free) ----
             mbar_wait(bar_d2, i & 1);
             tc_fence_after();
+            TR(5);
             {
                 uint32_t lo[16], hi[8];
                 tmem_ld_32x32b_x16(tm_lane + D2_COL + 24 * h4, lo);
@@ -352,8 +371,10 @@ mlp_tc_kernel(const MlpArgs a) {
                 }
             }
             tc_fence_before();
+            TR(6);
             SRB_PHASE(6);
             named_bar_sync(2, kAluThreads);
+            TR(7);
             // ---- (d) copy-out(i): 4 lanes per token, 64-byte row segments -> fully coalesced 16-byte stores ----
             {
                 const uint8_t* yp = sYP + (i & 1) * YP_BYTES + ln_row * 16;
@@ -410,7 +431,9 @@ mlp_tc_kernel(const MlpArgs a) {
                     }
                 }
             }
+            TR(8);
             if (i + 2 < n_my) issue_loads(tile + 2 * step);
+            TR(9);
         }
 #ifdef SRB_MLP_PHASES
         if (a.dbg && tid == 0)

@@ -1,10 +1,11 @@
 """Digest of one `ncu --set full` report: headline metrics, stall reasons, hottest SASS lines.
-usage: python tools/ncu_digest.py report.ncu-rep [n_hot_lines]"""
+usage: python tools/ncu_digest.py report.ncu-rep [n_hot_lines] [kernel-name regex when the report holds several kernels]"""
 import csv, io, subprocess, sys
 
 rep = sys.argv[1]
 nhot = int(sys.argv[2]) if len(sys.argv) > 2 else 30
-raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+ksel = ['-k', 'regex:' + sys.argv[3]] if len(sys.argv) > 3 else []
+raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'] + ksel, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rows[0], rows[1], rows[-1]
 d = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
@@ -32,7 +33,7 @@ for h, (v, u) in d.items():
             pass
 tot = sum(v for v, _ in st) or 1
 print('stalls:', ', '.join(f'{h} {100 * v / tot:.1f}%' for v, h in sorted(st, reverse=True)[:8]))
-src = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'], capture_output=True, text=True).stdout
+src = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'] + ksel, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
 hi = next(i for i, r in enumerate(rows) if 'Source' in r and 'Address' in r)
 hdr = rows[hi]; data = rows[hi + 1:]
