@@ -208,6 +208,23 @@ def config5(dev, sampler_cls, gpu_index, pairs=10000):
                 _psnr_ssim(p[i:i + 250], t[i:i + 250])
     ms = _timed(metrics, 1, 3)
     res['psnr_ssim'] = dict(roof(ms, nchunks * t.numel() * 8), pairs=nchunks * chunk, bytes_per_px=8)
+    # weighted-L1 loss + gradient kernel (srb_weighted_l1 through the C ABI, caller-owned buffers): 250 pairs = 786 MB of
+    # traffic per call, larger than L2; and the same loss through the autograd module (torch allocations + the
+    # grad_output scaling kernel inside the timed region) on the training batch shape
+    from superresolution_b200 import _lib as L
+    lib = L.lib()
+    pk, tk = p[:250].contiguous(), t[:250].contiguous()
+    gk = torch.empty_like(pk)
+    lossbuf = torch.zeros(1, device=dev)
+    scr = torch.empty(lib.srb_loss_scratch_bytes(), dtype=torch.uint8, device=dev)
+
+    def l1_kernel():
+        L.check(lib.srb_weighted_l1(L.ptr(pk), L.ptr(tk), pk.numel(), L.ptr(lossbuf), L.ptr(gk), L.ptr(scr),
+                                    L.current_stream()), 'weighted_l1')
+    ms = _timed(l1_kernel, 2, 7)
+    res['weighted_l1_kernel'] = dict(roof(ms, pk.numel() * 12), pairs=250, bytes_per_px=12,
+                                     note='loss + dLoss/dpred in one pass: read pred, target; write grad')
+    del pk, tk, gk
     crit = CombinedLoss()
     pred = p[:32].clone().requires_grad_(True)
     big = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -219,7 +236,8 @@ def config5(dev, sampler_cls, gpu_index, pairs=10000):
         l.backward()
     ms = _timed(loss, 2, 7) - _timed(big.zero_, 2, 7)
     res['weighted_l1_fwd_bwd'] = dict(roof(ms, pred.numel() * 12), shape=[32, 1, 512, 512], bytes_per_px=12,
-                                      note='L2 flushed, flush time subtracted')
+                                      note='autograd module path (allocations, grad_output scaling kernel); L2 flushed, '
+                                           'flush time subtracted')
     res['clocks'] = sampler.stop()
     del t, p, big
     torch.cuda.empty_cache()
