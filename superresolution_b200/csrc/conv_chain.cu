@@ -45,6 +45,7 @@ struct alignas(64) ChainLayer {
 struct ChainParams {
     ChainLayer L[kMaxChain];
     int nlayers;
+    int dep_chunk[kMaxChain];  // first 64-channel input chunk of layer l that holds outputs of layer l - 1 (see the producer)
     int tiles_x, tiles_y, n_spatial;
     unsigned int* counters;  // [nlayers] zeroed before the launch
     long long* dbg;          // optional [grid][16] cycle totals per role / phase (development aid)
@@ -109,23 +110,30 @@ conv_chain_kernel(const __grid_constant__ ChainParams P) {
         for (int l = 0; l < P.nlayers; ++l) {
             const ChainLayer& Ly = P.L[l];
             if (lane == 0) tma_prefetch_desc(&Ly.tmA);
-            if (l > 0) {
-                if (lane == 0) {
-                    const long long tb0 = clock64();
-                    uint32_t spins = 0;
-                    while (ld_acquire_gpu(&P.counters[l - 1]) < ncta) {
-                        if (++spins > (1u << 24)) __trap();  // a protocol bug fails the launch instead of hanging
-                    }
-                    fence_proxy_async_global();  // order the acquire before this thread's async-proxy (TMA) reads
-                    dbg_bar += clock64() - tb0;
-                }
-                __syncwarp();
-            }
+            // Dense-block inputs are [x | x1 | ... | x_{k-1}]: only the chunk that holds the previous layer's 32 new channels
+            // (and every chunk of an RDB's conv1) depends on the grid barrier.  The older chunks were made visible by
+            // earlier barriers, so their patch loads - and the MMAs that consume them - run ahead of the barrier, under the
+            // previous layer's epilogue: 60 % of an RDB's MMA work leaves the serial load -> MMA -> epilogue -> barrier chain.
+            const int dep = (l > 0) ? P.dep_chunk[l] : 0;
+            bool synced = (l == 0);
             const int nchunks = (Ly.a.Cin + 63) / 64;
             for (int st = blockIdx.x; st < P.n_spatial; st += gridDim.x) {
                 const int b = st / per_img, r = st % per_img;
                 const int ty = r / P.tiles_x, tx = r % P.tiles_x;
                 for (int ch = 0; ch < nchunks; ++ch, ++it) {
+                    if (!synced && ch >= dep) {
+                        if (lane == 0) {
+                            const long long tb0 = clock64();
+                            uint32_t spins = 0;
+                            while (ld_acquire_gpu(&P.counters[l - 1]) < ncta) {
+                                if (++spins > (1u << 24)) __trap();  // a protocol bug fails the launch instead of hanging
+                            }
+                            fence_proxy_async_global();  // order the acquire before this thread's async-proxy (TMA) reads
+                            dbg_bar += clock64() - tb0;
+                        }
+                        __syncwarp();
+                        synced = true;
+                    }
                     const uint32_t s = it % PS;
                     mbar_wait(&empty_p[s], ((it / PS) & 1) ^ 1);
                     if (lane == 0) {
@@ -330,6 +338,23 @@ int conv_chain_launch(const ConvArgs* layers, int n, unsigned int* counters, cud
         }
         ChainLayer& L = P.L[i];
         L.a = a;
+        // first input chunk that overlaps what layer i - 1 wrote (bf16 `out` slice or, conservatively, everything when the
+        // layers do not share a channel pitch); chunks before it may be loaded ahead of the grid barrier
+        P.dep_chunk[i] = 0;
+        if (i > 0) {
+            const ConvArgs& pv = layers[i - 1];
+            const int nchunks = (a.Cin + 63) / 64;
+            int dep = nchunks;  // no overlap at all: still synchronise before the last chunk (keeps the layers ordered)
+            if (pv.out_pitch != a.in_pitch) dep = 0;
+            else {
+                const ptrdiff_t d = pv.out - a.in;  // elements; same buffer <=> |d| < pitch
+                for (int c = nchunks - 1; c >= 0; --c) {
+                    const ptrdiff_t lo = 64 * c, hi = (64 * c + 64 < a.Cin) ? 64 * c + 64 : a.Cin;
+                    if (d < hi && d + pv.Cout > lo && d > -(ptrdiff_t)a.in_pitch && d < (ptrdiff_t)a.in_pitch) dep = c;
+                }
+            }
+            P.dep_chunk[i] = dep < nchunks ? dep : nchunks - 1;
+        }
         {
             cuuint64_t dims[4] = {(cuuint64_t)a.Cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
             cuuint64_t str[3] = {(cuuint64_t)a.in_pitch * 2, (cuuint64_t)W * a.in_pitch * 2, (cuuint64_t)H * W * a.in_pitch * 2};
