@@ -15,7 +15,7 @@
 //    across them (activations are read from L2 once per layer).
 //  * Accumulators live in TMEM (MT tiles x N_TILE fp32 columns, double buffered when they fit) so the epilogue of
 //    tile i overlaps the MMAs of tile i+1.  Persistent CTAs, warp-specialised (384 threads):
-//      warp 0 patch TMA | warp 1 MMA issue | warp 2 weight TMA | warp 3 TMEM alloc | warps 4-11 epilogue (2 groups
+//      warp 0 patch TMA | warp 1 MMA issue | warp 2 weight TMA | warp 3 TMEM alloc | warps 4+ epilogue (2 or 3 groups
 //      of 4 warps, each group covering the 128 TMEM lanes and taking every other 128x32 accumulator block).
 //  * Epilogue (TMEM -> registers): bias, LeakyReLU / exact GELU, two scaled residuals (fp32 or bf16), then bf16 tiles
 //    are staged in 64B-swizzled shared memory and written with TMA stores into a channel slice of a wider NHWC buffer
@@ -53,15 +53,18 @@ struct ConvCfg {
     static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128
                                      : ACC_COLS <= 256 ? 256 : 512;
     static constexpr int UNITS = MT * (N_TILE / 32);  // 128x32 accumulator blocks per tile
+    // epilogue groups of 4 warps (each group covers the 128 TMEM lanes).  The N = 96 layers (cab.2, the 1x1 linears) are
+    // epilogue-bound and have 3 n-blocks per m-tile: three groups; the others keep two (their patches need the smem).
+    static constexpr int EG = (N_TILE % 96 == 0) ? 3 : 2;
+    static constexpr int THREADS = 128 + EG * 128;
+    static constexpr int STAGING = EG * 2 * 8192;  // per group: two 128 x 32 bf16 staging blocks
     static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
     static_assert(N_TILE % 32 == 0 && N_TILE >= 32 && N_TILE <= 256, "N_TILE");
     static_assert(W_BYTES % 1024 == 0, "weight tile must keep 1024B alignment");
-    static_assert(UNITS % 2 == 0, "two epilogue groups split the units evenly");
 };
 
-constexpr int kThreads = 384;
+
 constexpr int kStageBytes = 8192;               // one 128 x 32 bf16 block, 64B-swizzled
-constexpr int kStagingBytes = 4 * kStageBytes;  // 2 epilogue groups x 2 buffers
 constexpr int kBarrierBytes = 512;
 constexpr int kBiasBytes = 2048;   // the layer's bias in shared memory (Cout <= 512 floats)
 constexpr int kColsumBytes = 2 * 16 * 128 * 4;  // [2 tiles][MT * 4 row groups <= 16][N_TILE <= 128] fp32 partial channel sums
@@ -94,7 +97,7 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
 }
 
 template <class Cfg>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(Cfg::THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                const __grid_constant__ CUtensorMap tmO, const ConvArgs a, const ConvLaunch t) {
     constexpr int N_TILE = Cfg::N_TILE, MT = Cfg::MT, TAPS = Cfg::TAPS, AS = Cfg::ACC_STAGES;
@@ -103,9 +106,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t* patch0 = smem;
     uint8_t* wt0 = patch0 + t.ps * Cfg::PATCH_STRIDE;
     uint8_t* stg0 = wt0 + t.wslots * Cfg::W_BYTES;
-    float* scol = (float*)(stg0 + kStagingBytes);  // only carved when a.colsum (t.colsum_bytes)
-    float* sbias = (float*)(stg0 + kStagingBytes + t.colsum_bytes);
-    uint64_t* bars = (uint64_t*)(stg0 + kStagingBytes + t.colsum_bytes + kBiasBytes);
+    float* scol = (float*)(stg0 + Cfg::STAGING);  // only carved when a.colsum (t.colsum_bytes)
+    float* sbias = (float*)(stg0 + Cfg::STAGING + t.colsum_bytes);
+    uint64_t* bars = (uint64_t*)(stg0 + Cfg::STAGING + t.colsum_bytes + kBiasBytes);
     uint64_t* full_p = bars;                 // [kMaxPS]
     uint64_t* empty_p = full_p + kMaxPS;     // [kMaxPS]
     uint64_t* full_w = empty_p + kMaxPS;     // [W_RING]  (3x3: ring; 1x1: full_w[0] = all resident tiles landed)
@@ -119,11 +122,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kMaxPS; ++i) { mbar_init(&full_p[i], 1); mbar_init(&empty_p[i], 1); }
         for (int i = 0; i < Cfg::W_RING; ++i) { mbar_init(&full_w[i], 1); mbar_init(&empty_w[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 256); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], Cfg::EG * 128); }
         fence_barrier_init();
     }
     if (a.dyn_weights) pdl_wait();  // weights / bias written by the preceding kernel: no prologue overlap
-    for (int i = threadIdx.x; i < a.Cout; i += kThreads) sbias[i] = a.bias ? __ldg(a.bias + i) : 0.f;  // constants
+    for (int i = threadIdx.x; i < a.Cout; i += Cfg::THREADS) sbias[i] = a.bias ? __ldg(a.bias + i) : 0.f;  // constants
     if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW); tma_prefetch_desc(&tmO); }
     if (warp == 3) { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
     tc_fence_before();
@@ -267,7 +270,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
 #endif
     } else if (warp >= 4) {
-        // ===================== epilogue: 2 groups x 4 warps, each group = all 128 TMEM lanes =====================
+        // ===================== epilogue: EG groups x 4 warps, each group = all 128 TMEM lanes =====================
         pdl_wait();  // residual reads / output writes must not overtake the previous kernel
         const int eg = (warp - 4) >> 2;
         const int q = warp & 3;
@@ -288,7 +291,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 PH_END(ph_full);
                 tc_fence_after();
 #pragma unroll 1
-                for (int u = eg; u < Cfg::UNITS; u += 2) {
+                for (int u = eg; u < Cfg::UNITS; u += Cfg::EG) {
                     const int mt = u / (N_TILE / 32), c0 = (u % (N_TILE / 32)) * 32;
                     const int y = ty * Cfg::TH + (row >> 3);
                     const int x = tx * Cfg::TW + 8 * mt + (row & 7);
@@ -320,7 +323,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             uint8_t* sb = stg + (it_s & 1) * kStageBytes;
                             PH_BEGIN();
                             if (issuer) bulk_wait_group_read<1>();  // the store that last used this buffer has read it
-                            named_bar_sync(1 + eg, 128);
+                            named_bar_sync(2 + eg, 128);
                             PH_END(ph_b1);
                             PH_BEGIN();
                             const uint32_t sw = (row >> 1) & 3;
@@ -336,7 +339,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             fence_proxy_async_smem();
                             PH_END(ph_st);
                             PH_BEGIN();
-                            named_bar_sync(1 + eg, 128);
+                            named_bar_sync(2 + eg, 128);
                             PH_END(ph_b2);
                             if (issuer) {
                                 tma_store_4d(&tmO, sb, cb, tx * Cfg::TW + 8 * mt, ty * Cfg::TH, b);
@@ -381,8 +384,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 tc_fence_before();
                 mbar_arrive(&acc_empty[as]);
-                if (a.colsum) {  // both epilogue groups: fixed-order sum of the MT*4 row-group partials -> colsum[st][c]
-                    named_bar_sync(3, 256);
+                if (a.colsum) {  // all epilogue groups: fixed-order sum of the MT*4 row-group partials -> colsum[st][c]
+                    named_bar_sync(1, Cfg::EG * 128);
                     const int c = threadIdx.x - 128;
                     if (c < N_TILE) {
                         float tot = 0.f;
@@ -489,7 +492,7 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
         set_error("conv_tc: colsum needs Cout == N tile (Cout=%d)", a.Cout);
         return SRB_E_ARG;
     }
-    const int fixed = t.wslots * Cfg::W_BYTES + kStagingBytes + t.colsum_bytes + kBiasBytes + kBarrierBytes + 1024;
+    const int fixed = t.wslots * Cfg::W_BYTES + Cfg::STAGING + t.colsum_bytes + kBiasBytes + kBarrierBytes + 1024;
     t.ps = (kSmemLimit - fixed) / Cfg::PATCH_STRIDE;
     if (t.ps > kMaxPS) t.ps = kMaxPS;
     if (t.ps < 2) {
@@ -532,7 +535,7 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3(t.n_spatial < num_sms() ? t.n_spatial : num_sms());
-    cfg.blockDim = dim3(kThreads);
+    cfg.blockDim = dim3(Cfg::THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];

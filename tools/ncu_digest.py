@@ -4,7 +4,9 @@ import csv, io, subprocess, sys
 
 rep = sys.argv[1]
 nhot = int(sys.argv[2]) if len(sys.argv) > 2 else 30
-ksel = ['-k', 'regex:' + sys.argv[3]] if len(sys.argv) > 3 else []
+ksel = []
+if len(sys.argv) > 3:  # a kernel-name regex, or '#N' = the N-th launch of the report
+    ksel = ['--launch-skip', sys.argv[3][1:], '--launch-count', '1'] if sys.argv[3].startswith('#') else ['-k', 'regex:' + sys.argv[3]]
 raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'] + ksel, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rows[0], rows[1], rows[-1]
@@ -35,8 +37,11 @@ tot = sum(v for v, _ in st) or 1
 print('stalls:', ', '.join(f'{h} {100 * v / tot:.1f}%' for v, h in sorted(st, reverse=True)[:8]))
 src = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv'] + ksel, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
-hi = next(i for i, r in enumerate(rows) if 'Source' in r and 'Address' in r)
-hdr = rows[hi]; data = rows[hi + 1:]
+his = [i for i, r in enumerate(rows) if 'Source' in r and 'Address' in r]  # one header row per kernel of the report
+sec = int(sys.argv[3][1:]) if len(sys.argv) > 3 and sys.argv[3].startswith('#') and len(his) > 1 else 0
+hi = his[sec]
+hdr = rows[hi]; data = rows[hi + 1:his[sec + 1] if sec + 1 < len(his) else len(rows)]
+data = [r for r in data if len(r) == len(hdr)]
 ia, isamp = hdr.index('Source'), hdr.index('Warp Stall Sampling (All Samples)')
 tot = sum(int(r[isamp]) for r in data if r[isamp].isdigit()) or 1
 idx = sorted(range(len(data)), key=lambda i: -int(data[i][isamp] or 0))[:nhot]
