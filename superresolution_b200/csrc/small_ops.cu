@@ -113,36 +113,66 @@ conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restric
         const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, b = tile / (tiles_x * tiles_y);
         const int y0 = ty * C1_TH - 1, x0 = tx * C1_TW - 1;
         __syncthreads();  // previous tile fully consumed
-        for (int i = threadIdx.x; i < C1_PH * C1_PW * 8; i += 256) {
-            const int ck = i & 7, p = i >> 3;
-            const int py = p / C1_PW, px = p % C1_PW;
-            const int y = y0 + py, x = x0 + px;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (y >= 0 && y < H && x >= 0 && x < W)
-                v = __ldg((const uint4*)(in + (((size_t)b * H + y) * W + x) * pitch) + ck);
-            *(uint4*)(c1_smem + p * 128 + ck * 16) = v;
+        {   // all of a thread's patch loads in flight at once (11 independent 16-byte loads), then the stores
+            constexpr int kIt = (C1_PH * C1_PW * 8 + 255) / 256;
+            uint4 v[kIt];
+#pragma unroll
+            for (int k = 0; k < kIt; ++k) {
+                const int i = threadIdx.x + 256 * k;
+                const int ck = i & 7, p = i >> 3;
+                const int py = p / C1_PW, px = p % C1_PW;
+                const int y = y0 + py, x = x0 + px;
+                v[k] = make_uint4(0, 0, 0, 0);
+                if (i < C1_PH * C1_PW * 8 && y >= 0 && y < H && x >= 0 && x < W)
+                    v[k] = __ldg((const uint4*)(in + (((size_t)b * H + y) * W + x) * pitch) + ck);
+            }
+#pragma unroll
+            for (int k = 0; k < kIt; ++k) {
+                const int i = threadIdx.x + 256 * k;
+                if (i < C1_PH * C1_PW * 8) *(uint4*)(c1_smem + (i >> 3) * 128 + (i & 7) * 16) = v[k];
+            }
         }
         __syncthreads();
-#pragma unroll 1
-        for (int pass = 0; pass < C1_TH; ++pass) {  // 32 pixels (one tile row) per pass
-            const int oy = pass, ox = threadIdx.x >> 3;
-            float s = 0.f;
+        // Vertical sliding window: the three 16-byte units (x - 1, x, x + 1) of input row py feed output rows py - 2, py - 1
+        // and py (taps ky = 2, 1, 0), so every output costs 3 shared-memory loads per lane instead of 9 (the 9-load form
+        // was bound by shared-memory bandwidth: 0.44 ms for the 512 x 512 stage-2 image against an 82 us HBM floor).
+        {
+            const int ox = threadIdx.x >> 3;
+            float acc[3] = {0.f, 0.f, 0.f};  // acc[oy % 3] of the output rows in flight
 #pragma unroll
-            for (int t = 0; t < 9; ++t) {
-                const uint4 v = *(const uint4*)(c1_smem + ((oy + t / 3) * C1_PW + ox + t % 3) * 128 + sub * 16);
-                const __nv_bfloat162* h2 = (const __nv_bfloat162*)&v;
+            for (int py = 0; py < C1_PH; ++py) {
+                uint4 v[3];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float2 f = __bfloat1622float2(h2[k]);
-                    s = fmaf(f.x, wr[t * 8 + 2 * k], s);
-                    s = fmaf(f.y, wr[t * 8 + 2 * k + 1], s);
+                for (int kx = 0; kx < 3; ++kx) v[kx] = *(const uint4*)(c1_smem + (py * C1_PW + ox + kx) * 128 + sub * 16);
+#pragma unroll
+                for (int ky = 0; ky < 3; ++ky) {
+                    const int oy = py - ky;  // compile-time after unrolling
+                    if (oy < 0 || oy >= C1_TH) continue;
+                    float a = acc[oy % 3];
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) {
+                        const __nv_bfloat162* h2 = (const __nv_bfloat162*)&v[kx];
+                        const int t = ky * 3 + kx;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 f = __bfloat1622float2(h2[k]);
+                            a = fmaf(f.x, wr[t * 8 + 2 * k], a);
+                            a = fmaf(f.y, wr[t * 8 + 2 * k + 1], a);
+                        }
+                    }
+                    acc[oy % 3] = a;
+                }
+                const int done = py - 2;  // output row whose last tap row (ky = 2) was just added
+                if (done >= 0) {
+                    float s = acc[done % 3];
+                    acc[done % 3] = 0.f;
+                    s += __shfl_xor_sync(0xffffffffu, s, 1);
+                    s += __shfl_xor_sync(0xffffffffu, s, 2);
+                    s += __shfl_xor_sync(0xffffffffu, s, 4);
+                    if (sub == 0 && ty * C1_TH + done < H && tx * C1_TW + ox < W)
+                        out[((size_t)b * H + ty * C1_TH + done) * W + tx * C1_TW + ox] = s + b0;
                 }
             }
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            s += __shfl_xor_sync(0xffffffffu, s, 4);
-            if (sub == 0 && ty * C1_TH + oy < H && tx * C1_TW + ox < W)
-                out[((size_t)b * H + ty * C1_TH + oy) * W + tx * C1_TW + ox] = s + b0;
         }
     }
 }
