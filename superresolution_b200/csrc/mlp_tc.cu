@@ -310,8 +310,12 @@ mlp_tc_kernel(const MlpArgs a) {
                 uint32_t acc[48];
                 {
                     uint32_t lo[32], hi[16];
-                    tmem_ld_32x32b_x32(tm_lane + D1_COL + 48 * h4, lo);
-                    tmem_ld_32x32b_x16(tm_lane + D1_COL + 48 * h4 + 32, hi);
+                    // (h4 laundered: hoisted out of the tile loop, the two TMEM addresses are spilled in the LN2 variant and
+                    // reloaded from local memory right behind the accumulator wait)
+                    int h4v = h4;
+                    if (LN2) asm volatile("" : "+r"(h4v));
+                    tmem_ld_32x32b_x32(tm_lane + D1_COL + 48 * h4v, lo);
+                    tmem_ld_32x32b_x16(tm_lane + D1_COL + 48 * h4v + 32, hi);
                     tmem_ld_wait();
 #pragma unroll
                     for (int k = 0; k < 32; ++k) acc[k] = lo[k];
@@ -350,8 +354,10 @@ mlp_tc_kernel(const MlpArgs a) {
             TR(5);
             {
                 uint32_t lo[16], hi[8];
-                tmem_ld_32x32b_x16(tm_lane + D2_COL + 24 * h4, lo);
-                tmem_ld_32x32b_x8(tm_lane + D2_COL + 24 * h4 + 16, hi);
+                int h4v = h4;
+                if (LN2) asm volatile("" : "+r"(h4v));
+                tmem_ld_32x32b_x16(tm_lane + D2_COL + 24 * h4v, lo);
+                tmem_ld_32x32b_x8(tm_lane + D2_COL + 24 * h4v + 16, hi);
                 tmem_ld_wait();
                 uint8_t* yp = sYP + (i & 1) * YP_BYTES + (3 * h4) * YP_PITCH + r * 16;
 #pragma unroll
@@ -388,32 +394,29 @@ mlp_tc_kernel(const MlpArgs a) {
                     if (valid) gp[4 * m] = o[m];
                 }
                 if (LN2) {  // xn2 = LayerNorm(y) of the bf16 row just written (4 lanes per token: two shuffles per sum)
-                    float v[24];
+                    // the row stays packed (12 registers) and is unpacked in each of the three passes: holding 24 floats
+                    // next to the prefetched tiles spilled, which cost this variant 110 us per launch
+                    float sm = 0.f;
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) {
+                        const uint32_t* w = (const uint32_t*)&o[m];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) { const float2 f = unpackbf(w[k]); sm += f.x + f.y; }
+                    }
+                    sm += __shfl_xor_sync(0xffffffffu, sm, 1);
+                    sm += __shfl_xor_sync(0xffffffffu, sm, 2);
+                    const float mean = sm * (1.f / 96.f);
+                    float qq = 0.f;
 #pragma unroll
                     for (int m = 0; m < 3; ++m) {
                         const uint32_t* w = (const uint32_t*)&o[m];
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
                             const float2 f = unpackbf(w[k]);
-                            v[8 * m + 2 * k] = f.x;
-                            v[8 * m + 2 * k + 1] = f.y;
+                            qq = fmaf(f.x - mean, f.x - mean, qq);
+                            qq = fmaf(f.y - mean, f.y - mean, qq);
                         }
                     }
-                    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) { s0 += v[k]; s1 += v[8 + k]; s2 += v[16 + k]; }
-                    float sm = (s0 + s1) + s2;
-                    sm += __shfl_xor_sync(0xffffffffu, sm, 1);
-                    sm += __shfl_xor_sync(0xffffffffu, sm, 2);
-                    const float mean = sm * (1.f / 96.f);
-                    float q0 = 0.f, q1 = 0.f, q2 = 0.f;
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        q0 = fmaf(v[k] - mean, v[k] - mean, q0);
-                        q1 = fmaf(v[8 + k] - mean, v[8 + k] - mean, q1);
-                        q2 = fmaf(v[16 + k] - mean, v[16 + k] - mean, q2);
-                    }
-                    float qq = (q0 + q1) + q2;
                     qq += __shfl_xor_sync(0xffffffffu, qq, 1);
                     qq += __shfl_xor_sync(0xffffffffu, qq, 2);
                     const float rstd = rsqrtf(qq * (1.f / 96.f) + 1e-5f);
@@ -421,12 +424,15 @@ mlp_tc_kernel(const MlpArgs a) {
 #pragma unroll
                     for (int m = 0; m < 3; ++m) {
                         const float* gg = sLN2 + (ln_j + 4 * m) * 8;
+                        const uint32_t* w = (const uint32_t*)&o[m];
                         uint4 x4;
                         uint32_t* xw = (uint32_t*)&x4;
 #pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            xw[k] = packbf(fmaf((v[8 * m + 2 * k] - mean) * rstd, gg[2 * k], gg[96 + 2 * k]),
-                                           fmaf((v[8 * m + 2 * k + 1] - mean) * rstd, gg[2 * k + 1], gg[96 + 2 * k + 1]));
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 f = unpackbf(w[k]);
+                            xw[k] = packbf(fmaf((f.x - mean) * rstd, gg[2 * k], gg[96 + 2 * k]),
+                                           fmaf((f.y - mean) * rstd, gg[2 * k + 1], gg[96 + 2 * k + 1]));
+                        }
                         if (valid) xp[4 * m] = x4;
                     }
                 }
