@@ -37,16 +37,24 @@ namespace srb {
 
 // TRAIN_: the epilogue also honours ConvArgs::pre_out / gelu_grad_of (training path).  A compile-time flag: the two
 // extra run-time tests in the inference epilogue cost 0.4 ms per batch-16 forward when they were unconditional.
-template <int N_TILE_, int MT_, int TAPS_, bool TRAIN_ = false>
+// KC_: channels per K chunk = bytes / 2 of one patch row (pixel) and one weight row in shared memory: 64 (128-byte rows,
+// SWIZZLE_128B) or 32 (64-byte rows, SWIZZLE_64B; for Cin = 32 layers: cab.2).  With KC = 32 the layer's whole 3x3 weight
+// image (9 x N_TILE x 64 B) stays RESIDENT in shared memory: re-streaming 108 KB of (zero-padded) weight tiles per 256-px
+// tile was cab.2's bottleneck (the MMA warp waited on the weight ring a third of the time).
+template <int N_TILE_, int MT_, int TAPS_, bool TRAIN_ = false, int KC_ = 64>
 struct ConvCfg {
-    static constexpr int N_TILE = N_TILE_, MT = MT_, TAPS = TAPS_;
+    static constexpr int N_TILE = N_TILE_, MT = MT_, TAPS = TAPS_, KC = KC_;
     static constexpr bool TRAIN = TRAIN_;
+    static constexpr bool W_RESIDENT = (TAPS == 9 && KC == 32);  // all tap tiles of the layer loaded once per CTA
+    static constexpr int ROW_BYTES = KC * 2;
+    static constexpr uint32_t SWZ = (KC == 64) ? UMMA_SW_128B : UMMA_SW_64B;
     static constexpr int HALO = (TAPS == 9) ? 1 : 0;
     static constexpr int TH = 16, TW = 8 * MT;
     static constexpr int PH = TH + 2 * HALO, PW = TW + 2 * HALO;
-    static constexpr int PATCH_BYTES = PH * PW * 128;
+    static constexpr int PATCH_BYTES = PH * PW * ROW_BYTES;
     static constexpr int PATCH_STRIDE = (PATCH_BYTES + 1023) / 1024 * 1024;
-    static constexpr int W_BYTES = N_TILE * 128;
+    static constexpr int W_BYTES = N_TILE * ROW_BYTES;
+    static_assert(KC == 64 || KC == 32, "KC");
     static constexpr int W_RING = 4;
     static constexpr int ACC_STAGES = (2 * MT * N_TILE <= 512) ? 2 : 1;
     static constexpr int ACC_COLS = ACC_STAGES * MT * N_TILE;
@@ -151,7 +159,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     mbar_wait(&empty_p[s], ((it / t.ps) & 1) ^ 1);
                     if (elect_one()) {
                         mbar_arrive_expect_tx(&full_p[s], Cfg::PATCH_BYTES);
-                        tma_load_4d(patch0 + s * Cfg::PATCH_STRIDE, &tmA, &full_p[s], ch * 64,
+                        tma_load_4d(patch0 + s * Cfg::PATCH_STRIDE, &tmA, &full_p[s], ch * Cfg::KC,
                                     tx * Cfg::TW - Cfg::HALO, ty * Cfg::TH - Cfg::HALO, b);
                     }
                     __syncwarp();
@@ -160,13 +168,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
     } else if (warp == 2) {
         // ===================== weight TMA producer (weights are constants: no dependency wait) =====================
-        if (TAPS == 1) {
+        if (TAPS == 1 || Cfg::W_RESIDENT) {  // every weight tile of the layer, once: slot (nt * nchunks + ch) * TAPS + tap
             if (elect_one()) {
                 mbar_arrive_expect_tx(&full_w[0], (uint32_t)(t.wslots * Cfg::W_BYTES));
                 for (int nt = 0; nt < t.n_tiles_n; ++nt)
                     for (int ch = 0; ch < t.nchunks; ++ch)
-                        tma_load_3d(wt0 + (nt * t.nchunks + ch) * Cfg::W_BYTES, &tmW, &full_w[0], ch * 64,
-                                    nt * N_TILE, 0);
+                        for (int tap = 0; tap < TAPS; ++tap)
+                            tma_load_3d(wt0 + ((nt * t.nchunks + ch) * TAPS + tap) * Cfg::W_BYTES, &tmW, &full_w[0],
+                                        ch * Cfg::KC, nt * N_TILE, tap);
             }
             __syncwarp();
         } else {
@@ -179,7 +188,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             mbar_wait(&empty_w[s], ((it / Cfg::W_RING) & 1) ^ 1);
                             if (elect_one()) {
                                 mbar_arrive_expect_tx(&full_w[s], Cfg::W_BYTES);
-                                tma_load_3d(wt0 + s * Cfg::W_BYTES, &tmW, &full_w[s], ch * 64, nt * N_TILE, tap);
+                                tma_load_3d(wt0 + s * Cfg::W_BYTES, &tmW, &full_w[s], ch * Cfg::KC, nt * N_TILE, tap);
                             }
                             __syncwarp();
                         }
@@ -199,7 +208,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #define PH_BEGIN()
 #define PH_END(x)
 #endif
-        if (TAPS == 1) { mbar_wait(&full_w[0], 0); tc_fence_after(); }
+        if (TAPS == 1 || Cfg::W_RESIDENT) { mbar_wait(&full_w[0], 0); tc_fence_after(); }
         for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
             for (int nt = 0; nt < t.n_tiles_n; ++nt, ++it_a) {
                 const uint32_t as = it_a % AS;
@@ -215,15 +224,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     mbar_wait(&full_p[ps], (pi / t.ps) & 1);  // immediate when the chunk is already resident
                     PH_END(ph_patch);
                     tc_fence_after();
-                    const uint64_t ad0 = umma_smem_desc(p_u32 + ps * Cfg::PATCH_STRIDE, 16, Cfg::PW * 128, UMMA_SW_128B);
-                    const bool full_chunk = (a.Cin - ch * 64) >= 64;  // else 32 valid channels (2 k-steps)
+                    const uint64_t ad0 = umma_smem_desc(p_u32 + ps * Cfg::PATCH_STRIDE, 16, Cfg::PW * Cfg::ROW_BYTES, Cfg::SWZ);
+                    const bool full_chunk = (a.Cin - ch * Cfg::KC) >= 64;  // else 32 valid channels (2 k-steps)
                     const uint32_t acc0 = (ch != 0);
 #pragma unroll
                     for (int tap = 0; tap < TAPS; ++tap) {
                         uint32_t wbase;
                         uint32_t ws = 0;
-                        if (TAPS == 1) {
-                            wbase = w_u32 + (nt * t.nchunks + ch) * Cfg::W_BYTES;
+                        if (TAPS == 1 || Cfg::W_RESIDENT) {
+                            wbase = w_u32 + ((nt * t.nchunks + ch) * TAPS + tap) * Cfg::W_BYTES;
                         } else {
                             ws = it_w % Cfg::W_RING;
                             PH_BEGIN();
@@ -232,8 +241,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             tc_fence_after();
                             wbase = w_u32 + ws * Cfg::W_BYTES;
                         }
-                        const uint64_t bd0 = umma_smem_desc(wbase, 16, 1024, UMMA_SW_128B);
-                        constexpr int kRowStep = 128 >> 4;  // one patch row in descriptor address units
+                        const uint64_t bd0 = umma_smem_desc(wbase, 16, 8 * Cfg::ROW_BYTES, Cfg::SWZ);
+                        constexpr int kRowStep = Cfg::ROW_BYTES >> 4;  // one patch row (pixel) in descriptor address units
                         const int arow = (TAPS == 9) ? ((tap / 3) * Cfg::PW + (tap % 3)) : 0;
                         const uint64_t ad_tap = ad0 + (uint64_t)(arow * kRowStep);
                         const bool leader = elect_one();
@@ -246,7 +255,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                                  bd0 + (uint64_t)(ks * 2), idesc, (tap == 0 && ks == 0) ? acc0 : 1u);
                             }
                         }
-                        if (TAPS != 1) {
+                        if (TAPS != 1 && !Cfg::W_RESIDENT) {
                             if (leader) umma_commit(&empty_w[ws]);
                             ++it_w;
                         }
@@ -485,8 +494,8 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     t.tiles_y = (a.H + Cfg::TH - 1) / Cfg::TH;
     t.n_tiles_n = a.Cout / Cfg::N_TILE;
     t.n_spatial = a.B * t.tiles_x * t.tiles_y;
-    t.nchunks = (a.Cin + 63) / 64;
-    t.wslots = (Cfg::TAPS == 1) ? t.n_tiles_n * t.nchunks : Cfg::W_RING;
+    t.nchunks = (a.Cin + Cfg::KC - 1) / Cfg::KC;
+    t.wslots = (Cfg::TAPS == 1 || Cfg::W_RESIDENT) ? t.n_tiles_n * t.nchunks * Cfg::TAPS : Cfg::W_RING;
     t.colsum_bytes = a.colsum ? kColsumBytes : 0;
     if (a.colsum && (t.n_tiles_n != 1 || Cfg::MT * 4 > 16 || Cfg::N_TILE > 128)) {
         set_error("conv_tc: colsum needs Cout == N tile (Cout=%d)", a.Cout);
@@ -512,14 +521,14 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
         cuuint64_t dims[4] = {(cuuint64_t)a.Cin, (cuuint64_t)a.W, (cuuint64_t)a.H, (cuuint64_t)a.B};
         cuuint64_t str[3] = {(cuuint64_t)a.in_pitch * 2, (cuuint64_t)a.W * a.in_pitch * 2,
                              (cuuint64_t)a.H * a.W * a.in_pitch * 2};
-        cuuint32_t box[4] = {64, (cuuint32_t)Cfg::PW, (cuuint32_t)Cfg::PH, 1};
-        SRB_TRY(encode_bf16_map(&tmA, a.in, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B));
+        cuuint32_t box[4] = {(cuuint32_t)Cfg::KC, (cuuint32_t)Cfg::PW, (cuuint32_t)Cfg::PH, 1};
+        SRB_TRY(encode_bf16_map(&tmA, a.in, 4, dims, str, box, Cfg::KC == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
     }
     {
         cuuint64_t dims[3] = {(cuuint64_t)a.Cin, (cuuint64_t)a.Cout, (cuuint64_t)Cfg::TAPS};
         cuuint64_t str[2] = {(cuuint64_t)a.Cin * 2, (cuuint64_t)a.Cout * a.Cin * 2};
-        cuuint32_t box[3] = {64, (cuuint32_t)Cfg::N_TILE, 1};
-        SRB_TRY(encode_bf16_map(&tmW, a.w, 3, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B));
+        cuuint32_t box[3] = {(cuuint32_t)Cfg::KC, (cuuint32_t)Cfg::N_TILE, 1};
+        SRB_TRY(encode_bf16_map(&tmW, a.w, 3, dims, str, box, Cfg::KC == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
     }
     if (t.tma_store) {
         cuuint64_t dims[4] = {(cuuint64_t)a.Cout, (cuuint64_t)a.W, (cuuint64_t)a.H, (cuuint64_t)a.B};
@@ -567,6 +576,7 @@ int conv_tc_launch(const ConvArgs& a_in, cudaStream_t stream) {
         if (a.Cout == 32) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<32, 4, 9>>(a, stream) : launch_cfg<ConvCfg<32, 2, 9>>(a, stream);
         if (a.Cout == 64) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<64, 4, 9>>(a, stream) : launch_cfg<ConvCfg<64, 2, 9>>(a, stream);
         if (a.Cout % 128 == 0) return launch_cfg<ConvCfg<128, 2, 9>>(a, stream);
+        if (a.Cout % 96 == 0 && a.Cin == 32 && a.Cout == 96) return launch_cfg<ConvCfg<96, 2, 9, false, 32>>(a, stream);  // cab.2
         if (a.Cout % 96 == 0) return launch_cfg<ConvCfg<96, 2, 9>>(a, stream);
         // any other multiple of 32 (e.g. the 160-channel data gradient of a dense-block conv4): N tiles of 32
         return (a.W % 32 == 0) ? launch_cfg<ConvCfg<32, 4, 9>>(a, stream) : launch_cfg<ConvCfg<32, 2, 9>>(a, stream);
