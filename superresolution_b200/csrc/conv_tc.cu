@@ -225,7 +225,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     PH_END(ph_patch);
                     tc_fence_after();
                     const uint64_t ad0 = umma_smem_desc(p_u32 + ps * Cfg::PATCH_STRIDE, 16, Cfg::PW * Cfg::ROW_BYTES, Cfg::SWZ);
-                    const bool full_chunk = (a.Cin - ch * Cfg::KC) >= 64;  // else 32 valid channels (2 k-steps)
+                    const bool full_chunk = Cfg::KC == 64 && (a.Cin - ch * 64) >= 64;  // else 32 valid channels (2 k-steps)
                     const uint32_t acc0 = (ch != 0);
 #pragma unroll
                     for (int tap = 0; tap < TAPS; ++tap) {
@@ -573,6 +573,7 @@ int conv_tc_launch(const ConvArgs& a_in, cudaStream_t stream) {
         return SRB_E_SHAPE;
     }
     if (a.taps == 9) {
+        if (a.Cout == 32 && a.Cin == 96 && a.W % 32 == 0) return launch_cfg<ConvCfg<32, 4, 9, false, 32>>(a, stream);  // cab.0
         if (a.Cout == 32) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<32, 4, 9>>(a, stream) : launch_cfg<ConvCfg<32, 2, 9>>(a, stream);
         if (a.Cout == 64) return (a.W % 32 == 0) ? launch_cfg<ConvCfg<64, 4, 9>>(a, stream) : launch_cfg<ConvCfg<64, 2, 9>>(a, stream);
         if (a.Cout % 128 == 0) return launch_cfg<ConvCfg<128, 2, 9>>(a, stream);
