@@ -384,6 +384,23 @@ int conv_chain_launch(const ConvArgs* layers, int n, unsigned int* counters, cud
     cfg.dynamicSmemBytes = CHAIN_SMEM;
     cfg.stream = stream;
     static const bool use_pdl = env_flag("SRB_PDL", true);
+    // The software grid barrier needs every CTA co-resident.  grid <= SM count and 1 CTA / SM make that true on a whole
+    // GPU; under MPS / green-context SM limits or MIG it may not be, so the launch first asks the occupancy calculator
+    // (which honours those limits through the device's reported SM count) and refuses instead of spinning into the trap.
+    {
+        static std::atomic<int> cached[64];  // per device, 0 = not asked yet
+        int dev = 0;
+        SRB_CUDA(cudaGetDevice(&dev));
+        int per_sm = cached[dev & 63].load(std::memory_order_relaxed);
+        if (per_sm == 0) {
+            SRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv_chain_kernel, kChainThreads, CHAIN_SMEM));
+            cached[dev & 63].store(per_sm > 0 ? per_sm : -1, std::memory_order_relaxed);
+        }
+        if (per_sm < 1 || (int)cfg.gridDim.x > per_sm * sms) {
+            set_error("conv_chain: %d CTAs cannot be co-resident (%d per SM x %d SMs)", (int)cfg.gridDim.x, per_sm, sms);
+            return SRB_E_SHAPE;
+        }
+    }
     cudaLaunchAttribute attrs[1];
     attrs[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attrs[0].val.programmaticStreamSerializationAllowed = 1;

@@ -28,6 +28,12 @@ def ssim_torch(img1, img2, window_size=11):
     already-clamped single-channel inputs (window_size fixed at 11)."""
     if window_size != 11:
         raise NotImplementedError('libsrb implements the 11x11 window of src/metrics.py')
+    # the kernel saturates its inputs to [0,1] (what Metrics.update feeds it); the reference function itself does not
+    # clamp, so anything else would silently differ: refuse it (one device->host sync; not on the Metrics path)
+    for name, img in (('img1', img1), ('img2', img2)):
+        if not bool(((img >= 0) & (img <= 1)).all()):
+            raise ValueError(f'ssim_torch (libsrb): {name} has values outside [0,1] or NaN; clamp first '
+                             f'(Metrics.update does) - the fused kernel saturates its inputs')
     return _psnr_ssim(img1, img2)[1] / img1.shape[0]
 
 

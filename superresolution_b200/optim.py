@@ -63,12 +63,30 @@ class FusedAdamW(torch.optim.Optimizer):
             if p.grad is None or p.grad.data_ptr() != self.flat_grad.data_ptr() + 4 * o:
                 p.grad = self.flat_grad[o:o + p.numel()].view_as(p)
 
+    def _gather_stray_grads(self):
+        """``model.zero_grad()`` (set_to_none is torch's default) or ``p.grad = None`` drops the views; autograd then
+        allocates fresh ``.grad`` tensors and the flat buffer would go stale.  Before the flat buffer is read, every
+        gradient that no longer aliases it is copied in and re-pointed (a missing gradient counts as zero, like
+        torch.optim.AdamW skipping a parameter without ``.grad`` does for that step's gradient)."""
+        base = self.flat_grad.data_ptr()
+        for p, o in zip(self.param_groups[0]['params'], self._offsets):
+            gr = p.grad
+            if gr is not None and gr.data_ptr() == base + 4 * o:
+                continue
+            view = self.flat_grad[o:o + p.numel()].view_as(p)
+            if gr is None:
+                view.zero_()
+            else:
+                view.copy_(gr)
+            p.grad = view
+
     def grad_norm(self, grad_scale=1.0, world=1):
         """L2 norm of the (unscaled, rank-averaged) gradient as a 0-dim CUDA tensor (no sync)."""
         self._sumsq()
         return self._info[0].sqrt() / (float(grad_scale) * world)
 
     def _sumsq(self):
+        self._gather_stray_grads()
         with torch.cuda.device(self.flat_grad.device):
             L.check(L.lib().srb_grad_sumsq(L.ptr(self.flat_grad), self.numel, L.ptr(self._info), L.ptr(self._scratch),
                                            L.current_stream()), 'grad_sumsq')
@@ -84,6 +102,8 @@ class FusedAdamW(torch.optim.Optimizer):
         inv_scale = 1.0 / (float(grad_scale if grad_scale is not None else 1.0) * world)
         if fused:
             self._sumsq()
+        else:
+            self._gather_stray_grads()
         self._step += 1
         with torch.cuda.device(self.flat_param.device):
             L.check(L.lib().srb_adamw_step(

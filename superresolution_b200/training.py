@@ -302,6 +302,7 @@ def train_step(model, optimizer, criterion, lr, hr, micro_batch=16, max_norm=1.0
         total = loss.detach() * ((e - s) / B) if total is None else total + loss.detach() * ((e - s) / B)
     y1.backward(g1)
     if world > 1:
+        optimizer._gather_stray_grads()  # (no-op on this path: the autograd functions accumulate into the flat views)
         allreduce_gradients(optimizer.flat_grad, group)
     optimizer.step(grad_scale=grad_scale, max_norm=max_norm, world=world)
     return total

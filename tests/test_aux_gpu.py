@@ -63,6 +63,20 @@ def test_psnr_ssim(cuda):
     assert abs(r['ssim'] - 1.0) < 1e-5 and abs(r['psnr'] - 80.0) < 1e-3
 
 
+def test_ssim_torch_drop_in_and_range_check(cuda):
+    """ssim_torch mirrors src/metrics.py:5-19 for inputs in [0,1]; out-of-range inputs are refused (the reference
+    function does not clamp, the fused kernel does: ADVICE r01)."""
+    from oracle import aux
+    from superresolution_b200.metrics import ssim_torch
+    gen = torch.Generator().manual_seed(8)
+    t2 = torch.rand(2, 1, 96, 80, generator=gen)
+    p2 = (t2 + 0.05 * torch.randn(2, 1, 96, 80, generator=gen)).clamp(0, 1)
+    got = ssim_torch(p2.to(cuda), t2.to(cuda)).item()
+    assert abs(got - aux.ssim_torch(p2, t2).item()) < 1e-4
+    with pytest.raises(ValueError, match='outside'):
+        ssim_torch((p2 * 1.5).to(cuda), t2.to(cuda))
+
+
 def test_log_normalize(cuda):
     from oracle import aux
     from superresolution_b200.normalization import log_normalize_u16

@@ -37,6 +37,33 @@ def test_plain_step_matches_torch_adamw(cuda):
         assert q.grad is not None and q.grad.abs().max().item() == 0.0  # views survive zero_grad
 
 
+def test_step_survives_dropped_gradient_views(cuda):
+    """after ``p.grad = None`` (what ``model.zero_grad()`` does by default) autograd allocates fresh .grad
+    tensors that no longer alias the flat buffer: the step must use THEM, not the stale buffer, in the plain and in the
+    fused form; a parameter left without a gradient contributes a zero gradient."""
+    from superresolution_b200.optim import FusedAdamW
+    for fused in (False, True):
+        a, b = _make(cuda, 1), _make(cuda, 1)
+        ref = torch.optim.AdamW(a, lr=5e-4, weight_decay=0.0)
+        opt = FusedAdamW(b, lr=5e-4, weight_decay=0.0)
+        for it in range(4):
+            for k, (p, q, g) in enumerate(zip(a, b, _grads(30 + it))):
+                q.grad = None                      # drop the view ...
+                if k == 2 and it == 1:
+                    p.grad = torch.zeros_like(p)   # ... and leave one parameter without a gradient for one step
+                    continue
+                p.grad = g.to(cuda)
+                q.grad = g.to(cuda).clone()        # ... a fresh tensor, as autograd would allocate
+            ref.step()
+            if fused:
+                opt.step(grad_scale=1.0, max_norm=1e9, world=1)
+            else:
+                opt.step()
+        for p, q in zip(a, b):
+            assert torch.allclose(p, q, rtol=0, atol=2e-6), (fused, (p - q).abs().max().item())
+            assert q.grad.data_ptr() >= opt.flat_grad.data_ptr()  # re-pointed into the flat buffer
+
+
 def test_fused_unscale_clip_step_matches_reference_sequence(cuda):
     from superresolution_b200.optim import FusedAdamW
     a, b = _make(cuda, 1), _make(cuda, 1)
