@@ -144,7 +144,8 @@ def test_abi_argument_errors_need_no_gpu():
     from superresolution_b200 import _lib as L
     lib = L.lib()
     assert lib.srb_forward_launch_count(16, 128, 128, 2, 3) > 100
-    assert lib.srb_forward_launch_count(16, 100, 128, 2, 3) < 0 and lib.srb_last_error()      # H % 32
+    assert lib.srb_forward_launch_count(16, 100, 128, 2, 3) > 100                              # H % 4 == 0: accepted (ragged tiles)
+    assert lib.srb_forward_launch_count(16, 102, 128, 2, 3) < 0 and b'multiples of 4' in lib.srb_last_error()
     assert lib.srb_forward_launch_count(16, 128, 128, 2, 5) < 0 and b'stage_mask' in lib.srb_last_error()
     assert lib.srb_forward_launch_count(16, 128, 128, 9, 3) < 0 and b'smoothing' in lib.srb_last_error()
     rc = lib.srb_forward(None, L.SRB_F32, None, L.SRB_F32, 1, 32, 32, None, None, 0, 2, 3, None)
