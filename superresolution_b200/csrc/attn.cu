@@ -158,21 +158,38 @@ ocab_attn_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ bias_fra
     const int win = blockIdx.x;
     const int wx = win % nwx, wy = (win / nwx) % nwy, b = win / (nwx * nwy);
     const size_t img = (size_t)b * H * W;
-    // every 16-byte chunk of the window is one cp.async: all loads of the CTA are in flight at once
-    for (int i = threadIdx.x; i < 64 * 12; i += 192) {
-        const int n = i / 12, ck = i % 12;
-        const size_t pix = img + (size_t)(wy * 8 + (n >> 3)) * W + wx * 8 + (n & 7);
-        cp_async16(sQ + n * AP + ck * 8, (const uint4*)(qkv + pix * 288) + ck);
-        if (ck == 0) spix[n] = (int)(pix - img);
+    // every 16-byte chunk of the window is one cp.async: all loads of the CTA are in flight at once.  192 threads = 16
+    // rows x 12 chunks (Q) = 8 rows x 24 chunks (K | V): a thread keeps its chunk column and steps through the rows with
+    // increments (the div / mod form of this index math was a fifth of the kernel's instructions).
+    {
+        const int ck = threadIdx.x % 12;
+        const bf16* src = qkv + (img + (size_t)(wy * 8) * W + wx * 8) * 288 + ck * 8;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int n = threadIdx.x / 12 + 16 * it;  // window token: row n >> 3, column n & 7
+            const int off = (n >> 3) * W + (n & 7);
+            cp_async16(sQ + n * AP + ck * 8, src + (size_t)off * 288);
+            if (ck == 0) spix[n] = (wy * 8) * W + wx * 8 + off;
+        }
     }
-    for (int i = threadIdx.x; i < 144 * 24; i += 192) {
-        const int m = i / 24, ck = i % 24;
-        const int y = wy * 8 - 2 + m / 12, x = wx * 8 - 2 + m % 12;
-        bf16* dst = (ck < 12) ? (sK + m * AP + ck * 8) : (sV + m * AP + (ck - 12) * 8);
-        if (y >= 0 && y < H && x >= 0 && x < W)
-            cp_async16(dst, (const uint4*)(qkv + (img + (size_t)y * W + x) * 288 + 96) + ck);
-        else
-            *(uint4*)dst = make_uint4(0, 0, 0, 0);  // nn.Unfold zero padding of the projected K / V maps
+    {
+        const int ck = threadIdx.x % 24;
+        bf16* dst0 = (ck < 12) ? (sK + ck * 8) : (sV + (ck - 12) * 8);
+        const bf16* src = qkv + img * 288 + 96 + ck * 8;
+        int my = (threadIdx.x / 24) / 12, mx = (threadIdx.x / 24) % 12;  // key (my, mx) of the 12 x 12 neighbourhood
+        int m = threadIdx.x / 24;
+#pragma unroll 3
+        for (int it = 0; it < 18; ++it) {
+            const int y = wy * 8 - 2 + my, x = wx * 8 - 2 + mx;
+            bf16* dst = dst0 + m * AP;
+            if (y >= 0 && y < H && x >= 0 && x < W)
+                cp_async16(dst, src + ((size_t)y * W + x) * 288);
+            else
+                *(uint4*)dst = make_uint4(0, 0, 0, 0);  // nn.Unfold zero padding of the projected K / V maps
+            m += 8;
+            mx += 8;
+            if (mx >= 12) { mx -= 12; ++my; }
+        }
     }
     cp_async_commit();
     cp_async_wait<0>();
