@@ -101,7 +101,9 @@ __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16
         m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
         m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1));
         m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
-        float l0 = 0.f, l1 = 0.f;
+        // row sums on the tensor cores: P x ones (the sum of the bf16-rounded probabilities the PV product really uses;
+        // no FADD per element, no shuffles)
+        float lsum[4] = {0.f, 0.f, 0.f, 0.f};
         float o[2][4];
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
@@ -115,8 +117,6 @@ __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16
                 e[jj][1] = ex2f(s[j][1] - m0);
                 e[jj][2] = ex2f(s[j][2] - m1);
                 e[jj][3] = ex2f(s[j][3] - m1);
-                l0 += e[jj][0] + e[jj][1];
-                l1 += e[jj][2] + e[jj][3];
             }
             const uint32_t p0 = pack_bf16(e[0][0], e[0][1]), p1 = pack_bf16(e[0][2], e[0][3]);
             const uint32_t p2 = pack_bf16(e[1][0], e[1][1]), p3 = pack_bf16(e[1][2], e[1][3]);
@@ -125,12 +125,9 @@ __device__ __forceinline__ void attend_head(bf16* sQ, const bf16* sK, const bf16
             ldsm_x4_trans(vb, sV + (16 * kt + (lane & 7) + ((lane >> 3) & 1) * 8) * AP + h * 16 + (lane >> 4) * 8);
             mma_bf16_16816(o[0], p0, p1, p2, p3, vb[0], vb[1]);
             mma_bf16_16816(o[1], p0, p1, p2, p3, vb[2], vb[3]);
+            mma_bf16_16816(lsum, p0, p1, p2, p3, 0x3F803F80u, 0x3F803F80u);  // B = ones: every column = the row sum
         }
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-        const float i0 = __fdividef(1.f, l0), i1 = __fdividef(1.f, l1);
+        const float i0 = __fdividef(1.f, lsum[0]), i1 = __fdividef(1.f, lsum[2]);
         __syncwarp();  // every lane has read its Q fragments of this m-tile before they are overwritten
 #pragma unroll
         for (int nt = 0; nt < 2; ++nt) {
