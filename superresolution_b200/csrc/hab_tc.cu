@@ -21,15 +21,18 @@
 //
 // 16 warps.  Warps 0-11 compute = 3 groups of 4 (TMEM lane quadrant = warp & 3): group g owns channel third g of the
 // token-wise phases (LayerNorm, qkv epilogue part g = q | k | v, proj epilogue) and heads g, g+3 of the attention;
-// they never issue an MMA, never touch global memory and meet only at mbarriers (+ one named barrier inside the
-// LayerNorm).  Warp 12 moves the token rows between HBM and the operand planes (4 lanes per token; x in by cp.async
-// one tile ahead, xn / t out).  Warps 13-15 issue the MMAs of group 0 / 1 / 2: qkv part g, S + bias and PV of heads
-// g, g+3 (warp 13 also proj).  Per tile i the compute warps run
+// they never issue an MMA and meet only at mbarriers (+ one named barrier inside the LayerNorm); their only global
+// traffic is the proj epilogue (shortcut re-read from L2, t out).  Warp 12 is the I/O warp: x in one tile ahead and xn
+// out as TMA tensor boxes (half a window = 4 rows x 8 tokens per box, straight into / out of the swizzled A1 chunks),
+// plus the per-tile index bookkeeping (window coordinates, shift-mask region ids, pixel indices).  Warps 13-15 issue the
+// MMAs of group 0 / 1 / 2: qkv part g, S + bias and PV of heads g, g+3 (warp 13 also proj).  Per tile i the compute
+// warps run
 //   qkv epilogue(i) -> Q/K/V planes | LN(i+1) in place on A1 | softmax(g), softmax(g+3) | O/rowsum -> Q planes |
 //   proj epilogue(i) + x -> the group's own plane buffer -> HBM,   with S(i) + bias under LN(i+1), PV(g) under
 //   softmax(g+3) and qkv(i+1) under the proj epilogue of tile i.
-// Operand layout: un-swizzled K-major planes [k/8][row][8 bf16] (core matrix = 8 rows x 16 B contiguous, LBO = plane
-// pitch, SBO = 128 B); V: [head][window][dim/8][key][8 dims] (MN-major core matrices: LBO = 128 B over keys, SBO = 1 KB
+// Operand layouts: A1 (x -> xn, A of qkv) = the TMA-native swizzled K-major tiles (64 channels x 128 B rows SWIZZLE_128B
+// + 32 channels x 64 B rows SWIZZLE_64B); Q / K / weights: un-swizzled K-major planes [k/8][row][8 bf16] (core matrix =
+// 8 rows x 16 B contiguous, LBO = plane pitch, SBO = 128 B); V: [head][window][dim/8][key][8 dims] (MN-major core matrices: LBO = 128 B over keys, SBO = 1 KB
 // over the four 8-dim groups); bias: [head][query/8][key][8 queries].  All forms validated on B200 by
 // tools/probe_umma.cu / tools/probe_attn.cu.
 #include <cuda.h>
@@ -103,9 +106,6 @@ struct HabArgs {
 
 // Development aid (-DSRB_HAB_TRACE): clock64 time stamps of CTA 0 on its tiles 3 and 4, [tile][warp][32 slots] behind the
 // phase totals (tools/hab_trace.py prints the timeline).
-#ifndef SRB_HAB_EXP
-#define SRB_HAB_EXP 0
-#endif
 #ifdef SRB_HAB_TRACE
 #define TR(k) do { if (a.dbg && blockIdx.x == 0 && (i == 3 || i == 4) && (threadIdx.x & 31) == 0) \
     a.dbg[2 * 148 * 8 + ((i - 3) * 16 + (threadIdx.x >> 5)) * 32 + (k)] = clock64(); } while (0)
@@ -280,20 +280,16 @@ hab_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ 
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     const int h = g + 3 * hh;
-#if SRB_HAB_EXP != 2
 #pragma unroll
                     for (int w = 0; w < 2; ++w)  // S_h(window w) = Q K^T: M = 64 rows at lane offset 16 w
                         umma_bf16_ss(tmem_base + ((uint32_t)(16 * w) << 16) + 64 * h,
                                      umma_smem_desc(q_u + 2 * h * PP + 64 * w * 16, PP, 128, UMMA_SW_NONE),
                                      umma_smem_desc(k_u + 2 * h * PP + 64 * w * 16, PP, 128, UMMA_SW_NONE), idesc_s, 0);
-#endif
-#if SRB_HAB_EXP != 1
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)  // S_h += E * Bias_h^T for both windows at once: M = 128, lane L reads
                         umma_bf16_ts(tmem_base + 64 * h, tmem_base + COL_E + 8 * ks,  // its own one-hot row of E
                                      umma_smem_desc(bias_u + h * 8192 + ks * 2 * 1024, 1024, 128, UMMA_SW_NONE),
-                                     idesc_b, (SRB_HAB_EXP == 2) ? (ks > 0) : 1);
-#endif
+                                     idesc_b, 1);
                     umma_commit(bar_s + h);
                 }
             }
