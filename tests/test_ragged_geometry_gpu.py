@@ -95,3 +95,32 @@ def test_random_init_ragged_frame_psnr(cuda):
         got = m(x.to(cuda)).cpu()
     assert got.shape == ref.shape == (1, 1, 400, 400)
     assert psnr(got, ref) >= 50.0
+
+
+@pytest.mark.parametrize('B,H,W', [(1, 36, 44), (2, 20, 68), (1, 100, 100), (2, 64, 64)])
+def test_forward_stays_inside_its_buffers(pair, cuda, B, H, W):
+    """Guard bands around the workspace, the input and the output of srb_forward (C ABI, caller-owned buffers): the
+    ragged-tile paths (TMA-clipped stores, masked epilogues, clamped MLP rows) and the whole-tile ones must not write a
+    byte outside what srb_workspace_bytes / the output shape promise, and the result equals the module's."""
+    from superresolution_b200 import _lib as L
+    _, m = pair
+    lib = L.lib()
+    G = 1 << 16  # guard bytes on either side
+    x = _input(B, H, W, seed=7).to(cuda)
+    m.output_size = 4 * W
+    with torch.no_grad():
+        want = m.run(x, stage_mask=3)
+    packed = m.pack_weights()
+    nws = lib.srb_workspace_bytes(B, H, W)
+    nout = B * 16 * H * W * 4
+    arena = torch.full((G + nws + G + nout + G,), 0xA5, dtype=torch.uint8, device=cuda)
+    ws = arena[G:G + nws]
+    y = arena[G + nws + G:G + nws + G + nout]
+    assert ws.data_ptr() % 256 == 0 and y.data_ptr() % 16 == 0
+    L.check(lib.srb_forward(L.ptr(x), L.SRB_F32, L.ptr(y), L.SRB_F32, B, H, W, L.ptr(packed), L.ptr(ws), nws, m._smoothing,
+                            3, L.current_stream()), 'forward')
+    torch.cuda.synchronize()
+    for lo, hi in ((0, G), (G + nws, G + nws + G), (G + nws + G + nout, G + nws + G + nout + G)):
+        assert bool((arena[lo:hi] == 0xA5).all()), (lo, hi)
+    got = y.view(torch.float32).view(B, 1, 4 * H, 4 * W)
+    assert torch.equal(got, want)
