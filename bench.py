@@ -316,7 +316,7 @@ def report(args, world, dev_ms, e2e_ms, prof, clocks, launches, x_host, y_host, 
     }
 
 
-# kernel-name substrings of each tensor-core family in the committed ncu capture (profiles/r01_kernel_traffic.json)
+# kernel-name substrings of each tensor-core family in the committed ncu capture (profiles/r02_kernel_traffic.json)
 FAMILY_KERNELS = {'conv3x3_tcgen05': (', 9>>',), 'rrdb_chain_tcgen05': ('conv_chain_kernel',), 'linear_tcgen05': (', 1>>',),
                   'hab_attention_tcgen05': ('hab_tc_kernel',), 'mlp_tcgen05': ('mlp_tc_kernel',),
                   'ocab_attention': ('ocab_attn_kernel',)}
@@ -326,7 +326,7 @@ def family_traffic(family):
     """DRAM bytes (read + write) per launch of the family's kernels, averaged over its launches in one forward, from
     the committed ncu capture of tools/run_forward_once.py (dram__bytes_read.sum + dram__bytes_write.sum per launch;
     tools/ncu_metrics_table.py --json).  None when the file is absent."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r01_kernel_traffic.json')
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r02_kernel_traffic.json')
     try:
         tab = json.load(open(path))
     except Exception:
@@ -336,7 +336,7 @@ def family_traffic(family):
         if any(k in name for k in FAMILY_KERNELS.get(family, ())):
             tot += row['dram_bytes_per_launch'] * row['launches']
             n += row['launches']
-    return (tot / n if n else None), 'profiles/r01_kernel_traffic.json (ncu dram__bytes_read+write per launch, one forward)'
+    return (tot / n if n else None), 'profiles/r02_kernel_traffic.json (ncu dram__bytes_read+write per launch, one forward)'
 
 
 def main():
