@@ -317,7 +317,7 @@ def report(args, world, dev_ms, e2e_ms, prof, clocks, launches, x_host, y_host, 
 
 
 # kernel-name substrings of each tensor-core family in the committed ncu capture (profiles/r02_kernel_traffic.json)
-FAMILY_KERNELS = {'conv3x3_tcgen05': (', 9>>',), 'rrdb_chain_tcgen05': ('conv_chain_kernel',), 'linear_tcgen05': (', 1>>',),
+FAMILY_KERNELS = {'conv3x3_tcgen05': (', 9, 0',), 'rrdb_chain_tcgen05': ('conv_chain_kernel',), 'linear_tcgen05': (', 1, 0',),
                   'hab_attention_tcgen05': ('hab_tc_kernel',), 'mlp_tcgen05': ('mlp_tc_kernel',),
                   'ocab_attention': ('ocab_attn_kernel',)}
 
