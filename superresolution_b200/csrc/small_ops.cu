@@ -93,7 +93,7 @@ constexpr int C1_TH = 8, C1_TW = 32;                          // output tile
 constexpr int C1_PH = C1_TH + 2, C1_PW = C1_TW + 2;           // input patch with halo
 constexpr int C1_SMEM = C1_PH * C1_PW * 128;                  // 64 bf16 channels per pixel
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restrict__ w /*[1][64][3][3]*/,
                   const float* __restrict__ bias, float* __restrict__ out, int B, int H, int W) {
     // The 3x3 x 64-channel dot product re-reads every input pixel 9 times: stage the haloed patch in shared memory once
@@ -113,23 +113,28 @@ conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restric
         const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, b = tile / (tiles_x * tiles_y);
         const int y0 = ty * C1_TH - 1, x0 = tx * C1_TW - 1;
         __syncthreads();  // previous tile fully consumed
-        {   // all of a thread's patch loads in flight at once (11 independent 16-byte loads), then the stores
-            constexpr int kIt = (C1_PH * C1_PW * 8 + 255) / 256;
-            uint4 v[kIt];
+        {   // a thread's patch loads in flight in two batches (6 + 5 independent 16-byte loads), then the stores: the 72
+            // weight registers leave room for 24 staging registers at two blocks per SM (one block per SM - what the
+            // unbatched form compiled to at 163 registers - left the loads' latency exposed)
+            constexpr int kIt = (C1_PH * C1_PW * 8 + 255) / 256, kHalf = (kIt + 1) / 2;
 #pragma unroll
-            for (int k = 0; k < kIt; ++k) {
-                const int i = threadIdx.x + 256 * k;
-                const int ck = i & 7, p = i >> 3;
-                const int py = p / C1_PW, px = p % C1_PW;
-                const int y = y0 + py, x = x0 + px;
-                v[k] = make_uint4(0, 0, 0, 0);
-                if (i < C1_PH * C1_PW * 8 && y >= 0 && y < H && x >= 0 && x < W)
-                    v[k] = __ldg((const uint4*)(in + (((size_t)b * H + y) * W + x) * pitch) + ck);
-            }
+            for (int k0 = 0; k0 < kIt; k0 += kHalf) {
+                uint4 v[kHalf];
 #pragma unroll
-            for (int k = 0; k < kIt; ++k) {
-                const int i = threadIdx.x + 256 * k;
-                if (i < C1_PH * C1_PW * 8) *(uint4*)(c1_smem + (i >> 3) * 128 + (i & 7) * 16) = v[k];
+                for (int k = 0; k < kHalf; ++k) {
+                    const int i = threadIdx.x + 256 * (k0 + k);
+                    const int ck = i & 7, p = i >> 3;
+                    const int py = p / C1_PW, px = p % C1_PW;
+                    const int y = y0 + py, x = x0 + px;
+                    v[k] = make_uint4(0, 0, 0, 0);
+                    if (k0 + k < kIt && i < C1_PH * C1_PW * 8 && y >= 0 && y < H && x >= 0 && x < W)
+                        v[k] = __ldg((const uint4*)(in + (((size_t)b * H + y) * W + x) * pitch) + ck);
+                }
+#pragma unroll
+                for (int k = 0; k < kHalf; ++k) {
+                    const int i = threadIdx.x + 256 * (k0 + k);
+                    if (k0 + k < kIt && i < C1_PH * C1_PW * 8) *(uint4*)(c1_smem + (i >> 3) * 128 + (i & 7) * 16) = v[k];
+                }
             }
         }
         __syncthreads();
@@ -182,7 +187,7 @@ int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, flo
     static std::atomic<unsigned long long> attr{0};
     SRB_TRY(opt_in_dynamic_smem(conv_cout1_kernel, C1_SMEM, attr));
     const int ntiles = B * ((H + C1_TH - 1) / C1_TH) * ((W + C1_TW - 1) / C1_TW);
-    int grid = ntiles < 148 * 4 ? ntiles : 148 * 4;
+    int grid = ntiles < num_sms() * 2 ? ntiles : num_sms() * 2;  // two resident blocks per SM (registers)
     conv_cout1_kernel<<<grid, 256, C1_SMEM, s>>>(in, pitch, w, bias, out, B, H, W);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
