@@ -107,15 +107,16 @@ int weighted_l1(const float* pred, const float* target, size_t n, float* loss, f
 // PSNR + SSIM (11x11 Gaussian sigma 1.5, *valid* convolution, C1 = 0.01^2, C2 = 0.03^2; inputs clamped to [0,1]).
 // One block = 64 x 32 output tile.  Pass A (horizontal): each thread filters 4 adjacent outputs of one input row from
 // 16 clamped inputs read straight from global (float4, L1 absorbs the overlap), forms a^2, c^2, ac once per input and
-// leaves the 5 filtered rows in shared memory; the squared error of the tile's own pixels rides along.  Pass B
+// leaves the 4 filtered rows (a, c, a^2 + c^2, ac: SSIM needs the two variances only as a sum) in shared memory; the squared error of the tile's own pixels rides along.  Pass B
 // (vertical): each thread owns one column and 8 consecutive output rows, so every shared-memory value feeds up to 8
 // accumulators from registers (statically unrolled taps), then evaluates the SSIM map entry.  FP32-FMA bound
-// (~113 FMA per pixel), not HBM bound.
+// (~95 FMA per pixel), not HBM bound.
 // ---------------------------------------------------------------------------------------------------------------
 struct GaussWin { float g[11]; };
 
 constexpr int kSsimTX = 64, kSsimTY = 32, kSsimRows = kSsimTY + 10;
-constexpr int kSsimSmem = 5 * kSsimRows * kSsimTX * (int)sizeof(float);
+constexpr int kSsimQ = 4;  // filtered quantities: a, c, a^2 + c^2, a c (SSIM needs var(a) + var(c) only as a sum)
+constexpr int kSsimSmem = kSsimQ * kSsimRows * kSsimTX * (int)sizeof(float);
 
 // four clamped pixels of one row starting at column x (x % 4 == 0); zeros beyond the image
 __device__ __forceinline__ float4 load4_sat(const float* __restrict__ row, int x, int W, bool row_ok, bool vec_ok) {
@@ -133,10 +134,10 @@ __device__ __forceinline__ float4 load4_sat(const float* __restrict__ row, int x
     return make_float4(__saturatef(v.x), __saturatef(v.y), __saturatef(v.z), __saturatef(v.w));
 }
 
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, 4)
 psnr_ssim_tile_kernel(const float* __restrict__ p, const float* __restrict__ t, int H, int W, GaussWin win,
                       float* __restrict__ part_se, float* __restrict__ part_ssim) {
-    extern __shared__ float hz[];  // [5][kSsimRows][kSsimTX]
+    extern __shared__ float hz[];  // [kSsimQ][kSsimRows][kSsimTX]
     __shared__ float sh[32];
     const int bx = blockIdx.x * kSsimTX, by = blockIdx.y * kSsimTY, b = blockIdx.z;
     const float* pb = p + (size_t)b * H * W;
@@ -162,50 +163,49 @@ psnr_ssim_tile_kernel(const float* __restrict__ p, const float* __restrict__ t, 
 #pragma unroll
             for (int j = 0; j < 4; ++j) se = fmaf(a[j] - c[j], a[j] - c[j], se);
         }
-        float o[5][4];
+        float o[kSsimQ][4];
 #pragma unroll
-        for (int q = 0; q < 5; ++q)
+        for (int q = 0; q < kSsimQ; ++q)
 #pragma unroll
             for (int j = 0; j < 4; ++j) o[q][j] = 0.f;
 #pragma unroll
         for (int k = 0; k < 14; ++k) {
-            const float aa = a[k] * a[k], cc = c[k] * c[k], ac = a[k] * c[k];
+            const float sq = fmaf(a[k], a[k], c[k] * c[k]), ac = a[k] * c[k];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 if (k - j >= 0 && k - j < 11) {
                     const float g = win.g[k - j];
                     o[0][j] = fmaf(g, a[k], o[0][j]);
                     o[1][j] = fmaf(g, c[k], o[1][j]);
-                    o[2][j] = fmaf(g, aa, o[2][j]);
-                    o[3][j] = fmaf(g, cc, o[3][j]);
-                    o[4][j] = fmaf(g, ac, o[4][j]);
+                    o[2][j] = fmaf(g, sq, o[2][j]);
+                    o[3][j] = fmaf(g, ac, o[3][j]);
                 }
             }
         }
 #pragma unroll
-        for (int q = 0; q < 5; ++q)
+        for (int q = 0; q < kSsimQ; ++q)
             *(float4*)(hz + (q * kSsimRows + ly) * kSsimTX + gx) = make_float4(o[q][0], o[q][1], o[q][2], o[q][3]);
     }
     __syncthreads();
     // ---- pass B: column ox, output rows oy0 .. oy0 + 7
     const int ox = threadIdx.x & 63, oy0 = (threadIdx.x >> 6) * 8;
     const int OH = H - 10, OW = W - 10;
-    float acc[8][5];
+    float acc[8][kSsimQ];
 #pragma unroll
     for (int j = 0; j < 8; ++j)
 #pragma unroll
-        for (int q = 0; q < 5; ++q) acc[j][q] = 0.f;
+        for (int q = 0; q < kSsimQ; ++q) acc[j][q] = 0.f;
 #pragma unroll
     for (int r = 0; r < 18; ++r) {
-        float v[5];
+        float v[kSsimQ];
 #pragma unroll
-        for (int q = 0; q < 5; ++q) v[q] = hz[(q * kSsimRows + oy0 + r) * kSsimTX + ox];
+        for (int q = 0; q < kSsimQ; ++q) v[q] = hz[(q * kSsimRows + oy0 + r) * kSsimTX + ox];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             if (r - j >= 0 && r - j < 11) {
                 const float g = win.g[r - j];
 #pragma unroll
-                for (int q = 0; q < 5; ++q) acc[j][q] = fmaf(g, v[q], acc[j][q]);
+                for (int q = 0; q < kSsimQ; ++q) acc[j][q] = fmaf(g, v[q], acc[j][q]);
             }
         }
     }
@@ -215,9 +215,10 @@ psnr_ssim_tile_kernel(const float* __restrict__ p, const float* __restrict__ t, 
         for (int j = 0; j < 8; ++j) {
             if (by + oy0 + j < OH) {
                 const float m1 = acc[j][0], m2 = acc[j][1];
-                const float v1 = acc[j][2] - m1 * m1, v2 = acc[j][3] - m2 * m2, cv = acc[j][4] - m1 * m2;
+                const float mm = m1 * m1 + m2 * m2;
+                const float vsum = acc[j][2] - mm, cv = acc[j][3] - m1 * m2;  // var(a) + var(c), cov(a, c)
                 const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-                ss += __fdividef((2.f * m1 * m2 + C1) * (2.f * cv + C2), (m1 * m1 + m2 * m2 + C1) * (v1 + v2 + C2));
+                ss += __fdividef((2.f * m1 * m2 + C1) * (2.f * cv + C2), (mm + C1) * (vsum + C2));
             }
         }
     }
