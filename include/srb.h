@@ -134,6 +134,11 @@ int srb_pack_conv_weight(const float* w, void* w_packed, int Cout, int Cin, int 
 size_t srb_loss_scratch_bytes(void);
 int srb_weighted_l1(const float* pred, const float* target, size_t n, float* loss, float* grad, void* scratch,
                     void* stream);
+/* srb_charbonnier_astro  the non-VGG terms of the stale loss variant (Backup/src/losses.py:6-15,37-48) in one
+ *                   pass: out3 = {char = mean sqrt(d^2 + 1e-6), l1_raw = mean |d|, astro = mean sqrt(d^2 + 1e-6)(1 + 5 t)};
+ *                   grad (optional) = d(l1_w char + astro_w astro)/dpred.  scratch: srb_loss_scratch_bytes(). */
+int srb_charbonnier_astro(const float* pred, const float* target, size_t n, float l1_w, float astro_w, float* out3,
+                          float* grad, void* scratch, void* stream);
 size_t srb_psnr_ssim_scratch_bytes(int B, int H, int W);
 int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, void* scratch,
                   void* stream);

@@ -23,6 +23,23 @@ def combined_loss(pred, target):
     return torch.mean(diff * weight)
 
 
+def charbonnier_loss(x, y, eps=1e-6):
+    """CharbonnierLoss.forward of the stale variant, reference Backup/src/losses.py:6-15."""
+    diff = x - y
+    return torch.mean(torch.sqrt(diff * diff + eps))
+
+
+def astro_loss_terms(pred, target):
+    """The non-VGG terms of the stale CombinedLoss, reference Backup/src/losses.py:37-48: (char, l1_raw, astro).
+    The perceptual (VGG19) term needs downloaded ImageNet weights and stays out."""
+    char = charbonnier_loss(pred, target)
+    l1_raw = F.l1_loss(pred, target)
+    diff = torch.abs(pred - target)
+    weight_map = 1.0 + 5.0 * target
+    astro = torch.mean(torch.sqrt(diff * diff + 1e-6) * weight_map)
+    return char, l1_raw, astro
+
+
 def ssim_torch(img1, img2, window_size=11):
     c = img1.size(1)
     g = torch.Tensor([exp(-(x - window_size // 2) ** 2 / float(2 * 1.5 ** 2)) for x in range(window_size)])

@@ -28,6 +28,7 @@ _PROTOS = {
     'srb_forward_launch_count': (_i, [_i, _i, _i, _i, _i]),
     'srb_loss_scratch_bytes': (_sz, []),
     'srb_weighted_l1': (_i, [_vp, _vp, _sz, _vp, _vp, _vp, _vp]),
+    'srb_charbonnier_astro': (_i, [_vp, _vp, _sz, C.c_float, C.c_float, _vp, _vp, _vp, _vp]),
     'srb_psnr_ssim_scratch_bytes': (_sz, [_i, _i, _i]),
     'srb_psnr_ssim': (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     'srb_psnr_ssim_noalloc': (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),

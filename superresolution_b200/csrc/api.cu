@@ -211,6 +211,11 @@ int srb_weighted_l1(const float* pred, const float* target, size_t n, float* los
     if (!pred || !target || !loss || !scratch || n == 0) { set_error("weighted_l1: bad args"); return SRB_E_ARG; }
     return weighted_l1(pred, target, n, loss, grad, (float*)scratch, (cudaStream_t)stream);
 }
+int srb_charbonnier_astro(const float* pred, const float* target, size_t n, float l1_w, float astro_w, float* out3,
+                          float* grad, void* scratch, void* stream) {
+    if (!pred || !target || !out3 || !scratch || n == 0) { set_error("charbonnier_astro: bad args"); return SRB_E_ARG; }
+    return charbonnier_astro(pred, target, n, l1_w, astro_w, out3, grad, (float*)scratch, (cudaStream_t)stream);
+}
 size_t srb_psnr_ssim_scratch_bytes(int B, int H, int W) { return psnr_ssim_scratch_bytes(B, H, W); }
 int srb_psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, void* scratch,
                   void* stream) {

@@ -88,6 +88,60 @@ final_mean_kernel(const float* __restrict__ partial, int nb, double inv_n, float
     if (threadIdx.x == 0) out[0] = (float)(sh[0] * inv_n);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Stale-variant loss terms (reference Backup/src/losses.py:6-15,37-48), one pass:
+//   char = mean(sqrt(d^2 + 1e-6)),  l1_raw = mean(|d|),  astro = mean(sqrt(d^2 + 1e-6) * (1 + 5 t)),  d = p - t
+//   grad (optional) = d(l1_w * char + astro_w * astro)/dp = (l1_w + astro_w (1 + 5 t)) * d / sqrt(d^2 + 1e-6) / n
+// (the VGG19 perceptual term of that file needs downloaded ImageNet weights and is not built)
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+charbonnier_astro_kernel(const float* __restrict__ p, const float* __restrict__ t, float* __restrict__ grad, size_t n,
+                         float inv_n, float l1_w, float astro_w, float* __restrict__ partial /*[3][gridDim.x]*/) {
+    __shared__ float sh[32];
+    float a_char = 0.f, a_l1 = 0.f, a_astro = 0.f;
+    auto one = [&](float pv, float tv) -> float {
+        const float d = pv - tv;
+        const float c = sqrtf(fmaf(d, d, 1e-6f));
+        const float w = fmaf(5.f, tv, 1.f);
+        a_char += c;
+        a_l1 += fabsf(d);
+        a_astro = fmaf(c, w, a_astro);
+        return (l1_w + astro_w * w) * __fdividef(d, c) * inv_n;
+    };
+    const size_t n4 = n / 4, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 a = __ldcs((const float4*)p + i), b = __ldcs((const float4*)t + i);
+        const float4 g = make_float4(one(a.x, b.x), one(a.y, b.y), one(a.z, b.z), one(a.w, b.w));
+        if (grad) __stcs((float4*)grad + i, g);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {  // tail
+        const size_t i = n4 * 4 + threadIdx.x;
+        const float g = one(p[i], t[i]);
+        if (grad) grad[i] = g;
+    }
+    const float s0 = block_sum(a_char, sh), s1 = block_sum(a_l1, sh), s2 = block_sum(a_astro, sh);
+    if (threadIdx.x == 0) {
+        partial[blockIdx.x] = s0;
+        partial[gridDim.x + blockIdx.x] = s1;
+        partial[2 * gridDim.x + blockIdx.x] = s2;
+    }
+}
+
+int charbonnier_astro(const float* pred, const float* target, size_t n, float l1_w, float astro_w, float* out3, float* grad,
+                      float* scratch, cudaStream_t s) {
+    if (((uintptr_t)pred | (uintptr_t)target | (uintptr_t)grad) & 15) { set_error("charbonnier_astro: pointers must be 16-byte aligned"); return SRB_E_ARG; }
+    int grid = (int)((n / 4 + 255) / 256);
+    if (grid > 148 * 8) grid = 148 * 8;
+    if (grid < 1) grid = 1;
+    charbonnier_astro_kernel<<<grid, 256, 0, s>>>(pred, target, grad, n, 1.f / (float)n, l1_w, astro_w, scratch);
+    SRB_CUDA(cudaGetLastError());
+    for (int k = 0; k < 3; ++k) {  // fixed-order final sums (deterministic)
+        final_mean_kernel<<<1, 256, 0, s>>>(scratch + (size_t)k * grid, grid, 1.0 / (double)n, out3 + k);
+        SRB_CUDA(cudaGetLastError());
+    }
+    return SRB_OK;
+}
+
 size_t reduce_scratch_bytes() { return 148 * 8 * sizeof(float) * 4; }
 
 int weighted_l1(const float* pred, const float* target, size_t n, float* loss, float* grad, float* scratch,

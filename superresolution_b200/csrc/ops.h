@@ -65,6 +65,8 @@ int fold_ln_linear(const float* w, const float* b, const float* gamma, const flo
 size_t reduce_scratch_bytes();
 int weighted_l1(const float* pred, const float* target, size_t n, float* loss, float* grad, float* scratch,
                 cudaStream_t s);
+int charbonnier_astro(const float* pred, const float* target, size_t n, float l1_w, float astro_w, float* out3, float* grad,
+                      float* scratch, cudaStream_t s);
 size_t psnr_ssim_scratch_bytes(int B, int H, int W);
 int psnr_ssim(const float* pred, const float* target, int B, int H, int W, float* out2, float* scratch,
               cudaStream_t s);

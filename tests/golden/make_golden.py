@@ -8,6 +8,7 @@
 * aux.npz    — outputs of the REFERENCE's own src/losses.py, src/metrics.py (imported from /root/reference) and of
   the normalisation lines of scripts/Dataset_step4_normalization.py:167-179 (exec'd from the reference file), on
   seeded inputs.  The oracle restatements (oracle/aux.py) are asserted equal to them here and again in the CPU tests.
+* backup_loss.npz — the Charbonnier and astro terms of the stale Backup/src/losses.py on the same seeded inputs (f4).
 """
 import hashlib
 import importlib.util
@@ -96,6 +97,17 @@ def main():
     assert np.array_equal(ref_u16, aux.log_normalize_u16(raw, gmin, gmax)), 'oracle log_normalize != reference'
     np.savez_compressed(os.path.join(HERE, 'aux.npz'), loss=loss.numpy(), psnr=np.float64(mm['psnr']),
                         ssim=np.float64(mm['ssim']), lognorm_u16=ref_u16, gmin=gmin, gmax=gmax)
+    # ---- stale-variant loss terms: Backup/src/losses.py CharbonnierLoss imported, the astro lines exec'd ----
+    bl = load_ref('Backup/src/losses.py', 'ref_backup_losses')   # (needs torchvision importable; no weights are fetched)
+    char = bl.CharbonnierLoss()(p, t)
+    lines = open(os.path.join(REF, 'Backup/src/losses.py')).read().split('\n')
+    body = '\n'.join(l.strip() for l in lines[45:48])            # diff / weight_map / astro_loss (:46-48)
+    env = {'torch': torch, 'pred': p, 'target': t}
+    exec(body, env)
+    oc, ol1, oa = aux.astro_loss_terms(p, t)
+    assert torch.equal(char, oc) and torch.equal(env['astro_loss'], oa)
+    np.savez_compressed(os.path.join(HERE, 'backup_loss.npz'), char=char.numpy(), astro=env['astro_loss'].numpy(),
+                        l1_raw=ol1.numpy())
     print('golden written: stage1', s1.shape, 'stage2', s2.shape, 'full', full.shape, 'loss', float(loss), mm)
 
 

@@ -153,3 +153,16 @@ def test_abi_argument_errors_need_no_gpu():
     assert lib.srb_blur(None, None, L.SRB_F32, 2, 1, 8, 8, None) < 0
     assert lib.srb_robust_hist(None, 0, C.c_float(1e-5), 0, None, 0, None, None) < 0
     assert lib.srb_workspace_bytes(16, 128, 128) > (1 << 30)
+
+
+def test_backup_loss_terms_match_reference_golden():
+    """the oracle restatement of the stale Charbonnier / astro terms equals the values produced by the
+    reference's own Backup/src/losses.py (tests/golden/make_golden.py) on the seeded aux inputs."""
+    import numpy as np
+    import torch
+    from _inputs import aux_inputs
+    from oracle import aux
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'backup_loss.npz'))
+    p, t, _ = aux_inputs()
+    char, l1_raw, astro = aux.astro_loss_terms(p, t)
+    assert char.item() == float(g['char']) and astro.item() == float(g['astro']) and l1_raw.item() == float(g['l1_raw'])
