@@ -1,4 +1,6 @@
 """Granular operator wrappers over the C ABI (used by the parity tests; the model forward uses srb_forward)."""
+import math
+
 import torch
 
 from . import _lib as L
@@ -367,6 +369,39 @@ def _cubic_taps(n_in, n_out):
     return idx, w
 
 
+def _cubic_taps_aa(n_in, n_out):
+    """tap tables of ATen's anti-aliased bicubic (F.interpolate(..., mode='bicubic', antialias=True), the call of the
+    stale Backup/src/architecture.py:91-92): Keys filter with A = -0.5 stretched by max(scale, 1), taps
+    [int(center - support + 0.5), int(center + support + 0.5)) clipped to the image and renormalised."""
+    A = -0.5
+    scale = n_in / n_out
+    support = 2.0 * max(scale, 1.0)
+    inv = 1.0 / max(scale, 1.0)
+    K = int(math.ceil(support)) * 2 + 1
+
+    def filt(x):
+        x = abs(x)
+        if x < 1.0:
+            return ((A + 2.0) * x - (A + 3.0)) * x * x + 1.0
+        if x < 2.0:
+            return (((x - 5.0) * x + 8.0) * x - 4.0) * A
+        return 0.0
+
+    idx = torch.zeros(n_out, K, dtype=torch.int32)
+    w = torch.zeros(n_out, K, dtype=torch.float32)
+    for o in range(n_out):
+        center = scale * (o + 0.5)
+        xmin = max(0, int(center - support + 0.5))
+        xsize = min(n_in, int(center + support + 0.5)) - xmin
+        ws = [filt((j + xmin - center + 0.5) * inv) for j in range(xsize)]
+        tot = sum(ws)
+        for j in range(xsize):
+            idx[o, j] = xmin + j
+            w[o, j] = ws[j] / tot
+        idx[o, xsize:] = xmin  # padding taps: weight 0 on a valid index
+    return idx, w
+
+
 def _transpose_taps(idx, w, n_in):
     """tables of the transposed operator: for every input position, the outputs it feeds and their weights (padded)"""
     n_out, K = idx.shape
@@ -383,10 +418,10 @@ def _transpose_taps(idx, w, n_in):
     return it, wt
 
 
-def bicubic_tables(n_in, n_out, device, transpose=False):
-    key = (n_in, n_out, str(device), transpose)
+def bicubic_tables(n_in, n_out, device, transpose=False, antialias=False):
+    key = (n_in, n_out, str(device), transpose, antialias)
     if key not in _BICUBIC_TABLES:
-        idx, w = _cubic_taps(n_in, n_out)
+        idx, w = _cubic_taps_aa(n_in, n_out) if antialias else _cubic_taps(n_in, n_out)
         if transpose:
             idx, w = _transpose_taps(idx, w, n_in)
             if idx.shape[1] > 64:
@@ -407,10 +442,14 @@ def resample_separable(x, Ho, Wo, ty, tx):
     return out
 
 
-def bicubic_resize(x, Ho, Wo):
-    """F.interpolate(x, size=(Ho, Wo), mode='bicubic', align_corners=False) on fp32 [B,1,H,W] (src/architecture.py:80-81)."""
+def bicubic_resize(x, Ho, Wo, antialias=False):
+    """F.interpolate(x, size=(Ho, Wo), mode='bicubic', align_corners=False) on fp32 [B,1,H,W] (src/architecture.py:80-81);
+    ``antialias=True`` = the stale variant's call (Backup/src/architecture.py:91-92)."""
     Hi, Wi = x.shape[-2:]
-    return resample_separable(x, Ho, Wo, bicubic_tables(Hi, Ho, x.device), bicubic_tables(Wi, Wo, x.device))
+    ty, tx = bicubic_tables(Hi, Ho, x.device, False, antialias), bicubic_tables(Wi, Wo, x.device, False, antialias)
+    K = max(ty[0].shape[1], tx[0].shape[1])
+    pad = lambda t: tuple(torch.nn.functional.pad(a, (0, K - a.shape[1])).contiguous() for a in t)
+    return resample_separable(x, Ho, Wo, pad(ty), pad(tx))
 
 
 def bicubic_resize_bwd(g, Hi, Wi):

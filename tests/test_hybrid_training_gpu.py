@@ -54,6 +54,18 @@ def test_bicubic_resize_forward_backward_match_aten(cuda, hw_in, hw_out):
     assert (gx.cpu() - x.grad).abs().max().item() <= 1e-4 * max(1.0, x.grad.abs().max().item())
 
 
+@pytest.mark.parametrize('hw_in,hw_out', [((128, 256), (48, 96)), ((512, 512), (192, 192)), ((64, 64), (256, 256))])
+def test_antialiased_bicubic_resize_matches_aten(cuda, hw_in, hw_out):
+    """F.interpolate(..., mode='bicubic', antialias=True) of the stale Backup/src/architecture.py:91-92."""
+    from superresolution_b200 import ops
+    g = torch.Generator().manual_seed(13)
+    x = torch.rand(2, 1, *hw_in, generator=g)
+    ref = F.interpolate(x, size=hw_out, mode='bicubic', align_corners=False, antialias=True)
+    got = ops.bicubic_resize(x.to(cuda), *hw_out, antialias=True)
+    assert got.shape == ref.shape
+    assert (got.cpu() - ref).abs().max().item() <= 2e-5
+
+
 def test_inference_resize_branch_matches_oracle(cuda):
     """output_size != 4W: stage1 -> s1 -> stage2 -> s2 -> bicubic -> sf (src/architecture.py:74-82), bf16 bar 50 dB."""
     from oracle.hybrid import HybridSuperResolutionModel as Oracle

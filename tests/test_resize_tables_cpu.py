@@ -83,3 +83,19 @@ def test_tiff16_codec_round_trips_with_pil(tmp_path, shape):
     Image.fromarray(a).save(tmp_path / 'pil.tiff')                          # what Modello_5.save_as_tiff16 writes
     assert np.array_equal(io16.read_tiff16(tmp_path / 'pil.tiff'), a)
     assert np.array_equal(io16.read_tiff16(tmp_path / 'ours.tiff'), a)
+
+
+def test_antialiased_bicubic_tables_match_aten():
+    """the stale variant resizes with antialias=True (Backup/src/architecture.py:91-92); the tap tables fed to
+    srb_resample_separable reproduce ATen's anti-aliased bicubic per axis (checked densely on the CPU, 1e-5)."""
+    import torch
+    import torch.nn.functional as F
+    from superresolution_b200 import ops
+    torch.manual_seed(0)
+    for n_in, n_out in ((128, 48), (512, 192), (96, 37), (64, 512), (100, 100), (53, 128)):
+        idx, w = ops._cubic_taps_aa(n_in, n_out)
+        assert idx.min() >= 0 and idx.max() < n_in and torch.allclose(w.sum(1), torch.ones(n_out), atol=1e-6)
+        x = torch.rand(1, 1, 1, n_in)
+        ref = F.interpolate(x, size=(1, n_out), mode='bicubic', align_corners=False, antialias=True)[0, 0, 0]
+        got = (x[0, 0, 0][idx.long()] * w).sum(1)
+        assert (got - ref).abs().max().item() <= 1e-5, (n_in, n_out)
