@@ -3,6 +3,7 @@
 // Each cites the reference call site it replaces.
 #include "common.h"
 #include "ops.h"
+#include "ptx.cuh"
 
 namespace srb {
 
@@ -87,108 +88,133 @@ int rrdb_conv_first(const void* x, int x_dtype, const float* w, const float* bia
 
 // ---------------------------------------------------------------------------------------------------------------
 // K7/K17: 3x3 conv with ONE output channel (conv_last of both stages), NHWC bf16 [B,H,W,64] -> fp32 [B,H,W].
-// 8 lanes per pixel, each owning 8 input channels (16-byte loads, 4 pixels = 512 contiguous bytes per warp load).
+// The haloed patch of an 8 x 32 output tile is staged in shared memory once (coalesced 16-byte chunks, zero fill = conv
+// padding, 144-byte pixel pitch = conflict-free ldmatrix); the 576-term dot products then run as an implicit GEMM on
+// mma.sync.m16n8k16: M = 16 consecutive output pixels of a row, K = 9 taps x 64 channels (36 k-steps), N = 8 of which
+// column 0 carries the bf16-rounded weights and column 1 their fp32 residual (hi + lo = the fp32 weight to ~16 bits), so
+// out = D[:,0] + D[:,1] + bias.  The CUDA-core form spent ~1300 instructions per thread and tile (576 FMA + as many
+// bf16 unpack operations per output) and was instruction-bound at 3.6x the HBM time; this one issues 72 MMAs + 72
+// ldmatrix per warp and tile.
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int C1_TH = 8, C1_TW = 32;                          // output tile
+constexpr int C1_TH = 8, C1_TW = 32;                          // output tile: warp w = output row w, two m-tiles of 16 px
 constexpr int C1_PH = C1_TH + 2, C1_PW = C1_TW + 2;           // input patch with halo
-constexpr int C1_SMEM = C1_PH * C1_PW * 128;                  // 64 bf16 channels per pixel
+constexpr int C1_PIX = 144;                                   // bytes per staged pixel (64 bf16 + 16 B skew)
+constexpr int C1_SMEM = C1_PH * C1_PW * C1_PIX;
 
 __global__ void __launch_bounds__(256, 2)
 conv_cout1_kernel(const bf16* __restrict__ in, int pitch, const float* __restrict__ w /*[1][64][3][3]*/,
                   const float* __restrict__ bias, float* __restrict__ out, int B, int H, int W) {
-    // The 3x3 x 64-channel dot product re-reads every input pixel 9 times: stage the haloed patch in shared memory once
-    // (coalesced 16-byte chunks, zero fill = conv padding) and let 8 lanes per output pixel (8 channels each) read it
-    // back conflict-free (4 pixels x 128 contiguous bytes per warp load).
     extern __shared__ __align__(16) uint8_t c1_smem[];
-    const int sub = threadIdx.x & 7;
-    float wr[72];  // [tap][8 channels of this lane]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // B fragments of the 36 k-steps (tap t, channel chunk c): b0 = B[k = 2 (lane % 4) + {0, 1}][n = lane / 4],
+    // b1 = the same with k + 8; n = 0: bf16(w), n = 1: bf16(w - bf16(w)), n >= 2: 0
+    uint32_t bf[36][2];
+    {
+        const int n = lane >> 2, kq = 2 * (lane & 3);
 #pragma unroll
-    for (int t = 0; t < 9; ++t)
+        for (int t = 0; t < 9; ++t)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) wr[t * 8 + j] = __ldg(w + (sub * 8 + j) * 9 + t);
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float v[2];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float wv = __ldg(w + (16 * c + kq + 8 * h + e) * 9 + t);
+                        const float hi = __bfloat162float(__float2bfloat16_rn(wv));
+                        v[e] = n == 0 ? hi : (n == 1 ? wv - hi : 0.f);
+                    }
+                    __nv_bfloat162 pk = __floats2bfloat162_rn(v[0], v[1]);
+                    bf[t * 4 + c][h] = *(uint32_t*)&pk;
+                }
+    }
     const float b0 = bias[0];
     const int tiles_x = (W + C1_TW - 1) / C1_TW, tiles_y = (H + C1_TH - 1) / C1_TH;  // ragged last tiles are masked
     const int ntiles = B * tiles_x * tiles_y;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    // patch of `tile` -> buffer `buf` by cp.async (zero fill = conv padding by plain stores): the next tile's patch is in
+    // flight while the current one is multiplied (two 48 KB buffers, two blocks per SM)
+    auto stage = [&](int tile, int buf) {
         const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, b = tile / (tiles_x * tiles_y);
         const int y0 = ty * C1_TH - 1, x0 = tx * C1_TW - 1;
-        __syncthreads();  // previous tile fully consumed
-        {   // a thread's patch loads in flight in two batches (6 + 5 independent 16-byte loads), then the stores: the 72
-            // weight registers leave room for 24 staging registers at two blocks per SM (one block per SM - what the
-            // unbatched form compiled to at 163 registers - left the loads' latency exposed)
-            constexpr int kIt = (C1_PH * C1_PW * 8 + 255) / 256, kHalf = (kIt + 1) / 2;
+        uint8_t* dst0 = c1_smem + buf * C1_SMEM;
+        constexpr int kIt = (C1_PH * C1_PW * 8 + 255) / 256;
 #pragma unroll
-            for (int k0 = 0; k0 < kIt; k0 += kHalf) {
-                uint4 v[kHalf];
-#pragma unroll
-                for (int k = 0; k < kHalf; ++k) {
-                    const int i = threadIdx.x + 256 * (k0 + k);
-                    const int ck = i & 7, p = i >> 3;
-                    const int py = p / C1_PW, px = p % C1_PW;
-                    const int y = y0 + py, x = x0 + px;
-                    v[k] = make_uint4(0, 0, 0, 0);
-                    if (k0 + k < kIt && i < C1_PH * C1_PW * 8 && y >= 0 && y < H && x >= 0 && x < W)
-                        v[k] = __ldg((const uint4*)(in + (((size_t)b * H + y) * W + x) * pitch) + ck);
-                }
-#pragma unroll
-                for (int k = 0; k < kHalf; ++k) {
-                    const int i = threadIdx.x + 256 * (k0 + k);
-                    if (k0 + k < kIt && i < C1_PH * C1_PW * 8) *(uint4*)(c1_smem + (i >> 3) * 128 + (i & 7) * 16) = v[k];
-                }
-            }
+        for (int k = 0; k < kIt; ++k) {
+            const int i = threadIdx.x + 256 * k;
+            if (i >= C1_PH * C1_PW * 8) break;
+            const int ck = i & 7, p = i >> 3;
+            const int py = p / C1_PW, px = p % C1_PW;
+            const int y = y0 + py, x = x0 + px;
+            uint8_t* dst = dst0 + p * C1_PIX + ck * 16;
+            if (y >= 0 && y < H && x >= 0 && x < W)
+                cp_async_16(dst, (const uint4*)(in + (((size_t)b * H + y) * W + x) * pitch) + ck);
+            else
+                *(uint4*)dst = make_uint4(0, 0, 0, 0);
+        }
+        cp_async_commit_group();
+    };
+    if ((int)blockIdx.x < ntiles) stage(blockIdx.x, 0);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int tx = tile % tiles_x, ty = (tile / tiles_x) % tiles_y, b = tile / (tiles_x * tiles_y);
+        const int nxt = tile + gridDim.x;
+        if (nxt < ntiles) {
+            stage(nxt, (it + 1) & 1);  // (that buffer was read in iteration it - 1: the barrier at its end protects it)
+            cp_async_wait_group<1>();
+        } else {
+            cp_async_wait_group<0>();
         }
         __syncthreads();
-        // Vertical sliding window: the three 16-byte units (x - 1, x, x + 1) of input row py feed output rows py - 2, py - 1
-        // and py (taps ky = 2, 1, 0), so every output costs 3 shared-memory loads per lane instead of 9 (the 9-load form
-        // was bound by shared-memory bandwidth: 0.44 ms for the 512 x 512 stage-2 image against an 82 us HBM floor).
-        {
-            const int ox = threadIdx.x >> 3;
-            float acc[3] = {0.f, 0.f, 0.f};  // acc[oy % 3] of the output rows in flight
+        const uint8_t* patch = c1_smem + (it & 1) * C1_SMEM;
+        // warp = output row `warp`; m-tile mt = output pixels [16 mt, 16 mt + 16); A fragment of (tap, chunk): ldmatrix.x4
+        // over rows = pixels (pitch C1_PIX), the four 8x8 matrices = (rows 0-7 | 8-15) x (k 0-7 | 8-15)
+        float acc[2][4];
 #pragma unroll
-            for (int py = 0; py < C1_PH; ++py) {
-                uint4 v[3];
+        for (int mt = 0; mt < 2; ++mt) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0.f;
+        const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(patch);
+        const uint32_t lane_off = (uint32_t)(((lane & 7) + ((lane >> 3) & 1) * 8) * C1_PIX + (lane >> 4) * 16);
 #pragma unroll
-                for (int kx = 0; kx < 3; ++kx) v[kx] = *(const uint4*)(c1_smem + (py * C1_PW + ox + kx) * 128 + sub * 16);
+        for (int t = 0; t < 9; ++t) {
+            const uint32_t row_base = smem_base + (uint32_t)(((warp + t / 3) * C1_PW + t % 3) * C1_PIX) + lane_off;
 #pragma unroll
-                for (int ky = 0; ky < 3; ++ky) {
-                    const int oy = py - ky;  // compile-time after unrolling
-                    if (oy < 0 || oy >= C1_TH) continue;
-                    float a = acc[oy % 3];
+            for (int c = 0; c < 4; ++c) {
 #pragma unroll
-                    for (int kx = 0; kx < 3; ++kx) {
-                        const __nv_bfloat162* h2 = (const __nv_bfloat162*)&v[kx];
-                        const int t = ky * 3 + kx;
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const float2 f = __bfloat1622float2(h2[k]);
-                            a = fmaf(f.x, wr[t * 8 + 2 * k], a);
-                            a = fmaf(f.y, wr[t * 8 + 2 * k + 1], a);
-                        }
-                    }
-                    acc[oy % 3] = a;
-                }
-                const int done = py - 2;  // output row whose last tap row (ky = 2) was just added
-                if (done >= 0) {
-                    float s = acc[done % 3];
-                    acc[done % 3] = 0.f;
-                    s += __shfl_xor_sync(0xffffffffu, s, 1);
-                    s += __shfl_xor_sync(0xffffffffu, s, 2);
-                    s += __shfl_xor_sync(0xffffffffu, s, 4);
-                    if (sub == 0 && ty * C1_TH + done < H && tx * C1_TW + ox < W)
-                        out[((size_t)b * H + ty * C1_TH + done) * W + tx * C1_TW + ox] = s + b0;
+                for (int mt = 0; mt < 2; ++mt) {
+                    uint32_t a0, a1, a2, a3;
+                    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3)
+                                 : "r"(row_base + (uint32_t)(16 * mt * C1_PIX + 32 * c)));
+                    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+                                 "{%0,%1,%2,%3};"
+                                 : "+f"(acc[mt][0]), "+f"(acc[mt][1]), "+f"(acc[mt][2]), "+f"(acc[mt][3])
+                                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(bf[t * 4 + c][0]), "r"(bf[t * 4 + c][1]));
                 }
             }
         }
+        // D fragment: lanes with lane % 4 == 0 hold columns 0, 1 of rows lane / 4 (acc[.][0..1]) and lane / 4 + 8 ([2..3])
+        if ((lane & 3) == 0) {
+            const int oy = ty * C1_TH + warp;
+            if (oy < H) {
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) {
+                    const int ox = tx * C1_TW + 16 * mt + (lane >> 2);
+                    float* op = out + ((size_t)b * H + oy) * W;
+                    if (ox < W) op[ox] = acc[mt][0] + acc[mt][1] + b0;
+                    if (ox + 8 < W) op[ox + 8] = acc[mt][2] + acc[mt][3] + b0;
+                }
+            }
+        }
+        __syncthreads();  // every warp has read this buffer before the next iteration refills it
     }
 }
 
 int conv_cout1(const bf16* in, int pitch, const float* w, const float* bias, float* out, int B, int H, int W,
                cudaStream_t s) {
     static std::atomic<unsigned long long> attr{0};
-    SRB_TRY(opt_in_dynamic_smem(conv_cout1_kernel, C1_SMEM, attr));
+    SRB_TRY(opt_in_dynamic_smem(conv_cout1_kernel, 2 * C1_SMEM, attr));
     const int ntiles = B * ((H + C1_TH - 1) / C1_TH) * ((W + C1_TW - 1) / C1_TW);
     int grid = ntiles < num_sms() * 2 ? ntiles : num_sms() * 2;  // two resident blocks per SM (registers)
-    conv_cout1_kernel<<<grid, 256, C1_SMEM, s>>>(in, pitch, w, bias, out, B, H, W);
+    conv_cout1_kernel<<<grid, 256, 2 * C1_SMEM, s>>>(in, pitch, w, bias, out, B, H, W);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
