@@ -251,13 +251,15 @@ int srb_overlap_attention_bwd(const void* qkv, const float* bias, const int* ind
 /* srb_channel_attention      ChannelAttention of CAB: out = y * sigmoid(W2 relu(W1 mean_px(y) + b1) + b2), y bf16 [B,HW,96],
  *                            w1 fp32 [3,96], w2 fp32 [96,3]; saves pooled [B,96], hid [B,3], scale [B,96] for the backward.
  * srb_channel_attention_bwd  dy (direct + pooled term) and dw1/db1/dw2/db2 (+= when accumulate); dpooled [B,96] scratch out.
+ *                            g_scale multiplies the incoming gradient g (HAB's conv_scale 0.01 without a pass over g).
  *                            scratch: srb_channel_attention_scratch_bytes(B, HW).  Deterministic. */
 size_t srb_channel_attention_scratch_bytes(int B, int HW);
 int srb_channel_attention(const void* y, const float* w1, const float* b1, const float* w2, const float* b2, void* out,
                           float* pooled, float* hid, float* scale, void* scratch, int B, int HW, void* stream);
 int srb_channel_attention_bwd(const void* y, const void* g, const float* w1, const float* w2, const float* pooled,
                               const float* hid, const float* scale, void* dy, float* dw1, float* db1, float* dw2,
-                              float* db2, float* dpooled, void* scratch, int B, int HW, int accumulate, void* stream);
+                              float* db2, float* dpooled, void* scratch, int B, int HW, int accumulate, float g_scale,
+                              void* stream);
 size_t srb_layernorm96_bwd_scratch_bytes(void);
 int srb_layernorm96(const void* x, const float* gamma, const float* beta, void* y, size_t ntok, void* stream);
 int srb_layernorm96_bwd(const void* x, const void* g, const float* gamma, const void* res, int res_f32, void* dx,

@@ -59,7 +59,7 @@ _PROTOS = {
     'srb_overlap_attention_bwd': (_i, [_vp] * 7 + [_i, _i, _i, _vp]),
     'srb_channel_attention_scratch_bytes': (_sz, [_i, _i]),
     'srb_channel_attention': (_i, [_vp] * 10 + [_i, _i, _vp]),
-    'srb_channel_attention_bwd': (_i, [_vp] * 14 + [_i, _i, _i, _vp]),
+    'srb_channel_attention_bwd': (_i, [_vp] * 14 + [_i, _i, _i, _f, _vp]),
     'srb_grad_norm_scratch_bytes': (_sz, []),
     'srb_grad_sumsq': (_i, [_vp, _sz, _vp, _vp, _vp]),
     'srb_adamw_step': (_i, [_vp, _vp, _vp, _vp, _sz, _f, _f, _f, _f, _f, _i, _f, _f, _vp, _vp, _vp]),

@@ -347,14 +347,15 @@ int srb_channel_attention(const void* y, const float* w1, const float* b1, const
 }
 int srb_channel_attention_bwd(const void* y, const void* g, const float* w1, const float* w2, const float* pooled,
                               const float* hid, const float* scale, void* dy, float* dw1, float* db1, float* dw2,
-                              float* db2, float* dpooled, void* scratch, int B, int HW, int accumulate, void* stream) {
+                              float* db2, float* dpooled, void* scratch, int B, int HW, int accumulate, float g_scale,
+                              void* stream) {
     if (!y || !g || !w1 || !w2 || !pooled || !hid || !scale || !dy || !dw1 || !db1 || !dw2 || !db2 || !dpooled ||
         !scratch || B <= 0 || HW <= 0) {
         set_error("channel_attention_bwd: bad args");
         return SRB_E_ARG;
     }
     return chan_attn_bwd((const bf16*)y, (const bf16*)g, w1, w2, pooled, hid, scale, (bf16*)dy, dw1, db1, dw2, db2, dpooled,
-                         scratch, B, HW, accumulate, (cudaStream_t)stream);
+                         scratch, B, HW, accumulate, g_scale, (cudaStream_t)stream);
 }
 size_t srb_grad_norm_scratch_bytes(void) { return grad_norm_scratch_bytes(); }
 int srb_grad_sumsq(const float* grad, size_t n, float* info2, void* scratch, void* stream) {

@@ -84,7 +84,7 @@ ca_fwd_kernel(const float* __restrict__ partial, int nblk, float inv_hw, const f
 
 // out[b][px][c] = a * y[b][px][c] * s[b][c] (+ add[b][px][c] / HW-broadcast term dp[b][c] * inv_hw when given)
 __global__ void __launch_bounds__(256)
-ca_scale_kernel(bf16* __restrict__ out, const bf16* __restrict__ y, const float* __restrict__ s,
+ca_scale_kernel(bf16* __restrict__ out, const bf16* __restrict__ y, const float* __restrict__ s, float a,
                 const float* __restrict__ dp, float inv_hw, int HW, size_t ntok) {
     const size_t n = ntok * 12;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
@@ -94,7 +94,7 @@ ca_scale_kernel(bf16* __restrict__ out, const bf16* __restrict__ y, const float*
         const uint4 raw = __ldg((const uint4*)(y + tok * CA_C + c));
         const __nv_bfloat162* h = (const __nv_bfloat162*)&raw;
         const float4 s0 = *(const float4*)(s + b * CA_C + c), s1 = *(const float4*)(s + b * CA_C + c + 4);
-        const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+        const float sv[8] = {a * s0.x, a * s0.y, a * s0.z, a * s0.w, a * s1.x, a * s1.y, a * s1.z, a * s1.w};
         float add[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (dp) {
             const float4 d0 = *(const float4*)(dp + b * CA_C + c), d1 = *(const float4*)(dp + b * CA_C + c + 4);
@@ -112,10 +112,29 @@ ca_scale_kernel(bf16* __restrict__ out, const bf16* __restrict__ y, const float*
     }
 }
 
-// single block: for every image ds[b][c] = sum_px g*y -> dz = ds * s(1-s) -> dhid -> dpooled[b][c]; parameter gradients
+// ds[b][c] = sum_blk partial[b][blk][c], written over partial[b][0][c]: eight block slices per (image, channel) folded
+// in a fixed order (the single-block kernel below walked all B * nblk partials serially: 250 us at 16 x 256 blocks)
+__global__ void __launch_bounds__(CA_C * 8)
+ca_fold_kernel(float* __restrict__ partial, int nblk) {
+    __shared__ float sm[8][CA_C];
+    const int c = threadIdx.x % CA_C, j = threadIdx.x / CA_C, b = blockIdx.x;
+    float* pb = partial + (size_t)b * nblk * CA_C;
+    float t = 0.f;
+    for (int i = j; i < nblk; i += 8) t += pb[(size_t)i * CA_C + c];
+    sm[j][c] = t;
+    __syncthreads();  // every partial of this image has been read
+    if (j == 0) {
+        float v = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v += sm[k][c];
+        pb[c] = v;
+    }
+}
+
+// single block: for every image ds[b][c] = g_scale * sum_px g*y (folded by ca_fold_kernel) -> dz = ds * s(1-s) -> dhid -> dpooled[b][c]; parameter gradients
 // summed over the images in order (deterministic).
 __global__ void __launch_bounds__(CA_C)
-ca_bwd_kernel(const float* __restrict__ partial, int nblk, int B, const float* __restrict__ w1,
+ca_bwd_kernel(const float* __restrict__ partial, int nblk, float g_scale, int B, const float* __restrict__ w1,
               const float* __restrict__ w2, const float* __restrict__ pooled, const float* __restrict__ hid,
               const float* __restrict__ s, float* __restrict__ dpooled, float* __restrict__ dw1, float* __restrict__ db1,
               float* __restrict__ dw2, float* __restrict__ db2, int accumulate) {
@@ -125,8 +144,7 @@ ca_bwd_kernel(const float* __restrict__ partial, int nblk, int B, const float* _
     float gw1[CA_HID] = {0.f, 0.f, 0.f};  // dW1[k][c] for k = 0..2 (this thread's column c)
     float gb1 = 0.f;                       // db1[c] for c < 3
     for (int b = 0; b < B; ++b) {
-        float ds = 0.f;
-        for (int i = 0; i < nblk; ++i) ds += partial[((size_t)b * nblk + i) * CA_C + c];
+        const float ds = g_scale * partial[(size_t)b * nblk * CA_C + c];
         const float sv = s[b * CA_C + c];
         const float dz = ds * sv * (1.f - sv);
         sdz[c] = dz;
@@ -181,21 +199,23 @@ int chan_attn_fwd(const bf16* y, const float* w1, const float* b1, const float* 
     SRB_CUDA(cudaGetLastError());
     ca_fwd_kernel<<<B, CA_C, 0, st>>>((const float*)scratch, nblk, 1.f / (float)HW, w1, b1, w2, b2, pooled, hid, s);
     SRB_CUDA(cudaGetLastError());
-    ca_scale_kernel<<<ca_grid((size_t)B * HW * 12), 256, 0, st>>>(out, y, s, nullptr, 0.f, HW, (size_t)B * HW);
+    ca_scale_kernel<<<ca_grid((size_t)B * HW * 12), 256, 0, st>>>(out, y, s, 1.f, nullptr, 0.f, HW, (size_t)B * HW);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
 
 int chan_attn_bwd(const bf16* y, const bf16* g, const float* w1, const float* w2, const float* pooled, const float* hid,
                   const float* s, bf16* dy, float* dw1, float* db1, float* dw2, float* db2, float* dpooled,
-                  void* scratch, int B, int HW, int accumulate, cudaStream_t st) {
+                  void* scratch, int B, int HW, int accumulate, float g_scale, cudaStream_t st) {
     const int nblk = ca_blocks(HW);
     ca_colsum_kernel<<<dim3(nblk, B), 192, 0, st>>>(g, y, HW, (float*)scratch);
     SRB_CUDA(cudaGetLastError());
-    ca_bwd_kernel<<<1, CA_C, 0, st>>>((const float*)scratch, nblk, B, w1, w2, pooled, hid, s, dpooled, dw1, db1, dw2, db2,
-                                      accumulate);
+    ca_fold_kernel<<<B, CA_C * 8, 0, st>>>((float*)scratch, nblk);
     SRB_CUDA(cudaGetLastError());
-    ca_scale_kernel<<<ca_grid((size_t)B * HW * 12), 256, 0, st>>>(dy, g, s, dpooled, 1.f / (float)HW, HW, (size_t)B * HW);
+    ca_bwd_kernel<<<1, CA_C, 0, st>>>((const float*)scratch, nblk, g_scale, B, w1, w2, pooled, hid, s, dpooled, dw1, db1, dw2,
+                                      db2, accumulate);
+    SRB_CUDA(cudaGetLastError());
+    ca_scale_kernel<<<ca_grid((size_t)B * HW * 12), 256, 0, st>>>(dy, g, s, g_scale, dpooled, 1.f / (float)HW, HW, (size_t)B * HW);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -436,6 +436,8 @@ int pack_conv_weight_dgrad(const float* w, bf16* o, int Cout, int Cin, int taps,
 }
 
 size_t conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps) {
+    if (const int ks = wgrad_tc_splits(B, H, W, Cin, Cout, taps))
+        return (size_t)ks * ((size_t)taps * Cout * Cin + Cout) * sizeof(float);
     if (W % WG_KC) return 0;
     const int nchunks = B * H * (W / WG_KC);
     const size_t npx = (size_t)B * H * W;
@@ -449,12 +451,26 @@ size_t conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps
 int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
                int H, int W, int Cin, int Cout, int taps, int accumulate, cudaStream_t s) {
     if (taps != 9 && taps != 1) { set_error("conv_wgrad: taps must be 9 or 1"); return SRB_E_ARG; }
-    if (W % WG_KC) { set_error("conv_wgrad: W=%d must be a multiple of %d", W, WG_KC); return SRB_E_SHAPE; }
     if (Cin % 8 || Cout % 8 || Cout > 512) { set_error("conv_wgrad: Cin=%d Cout=%d must be multiples of 8 (Cout <= 512)", Cin, Cout); return SRB_E_SHAPE; }
     if (x_pitch % 8 || dy_pitch % 8 || (((uintptr_t)x | (uintptr_t)dy) & 15) || ((uintptr_t)scratch & 15)) {
         set_error("conv_wgrad: pitches / pointers must be 16-byte aligned");
         return SRB_E_ARG;
     }
+    if (const int ks = (x_pitch >= Cin && dy_pitch >= Cout) ? wgrad_tc_splits(B, H, W, Cin, Cout, taps) : 0) {
+        // tcgen05 path (wgrad_tc.cu): same partial layouts, same fixed-order reductions
+        const int n = taps * Cout * Cin;
+        float* partial = (float*)scratch;
+        float* bpartial = db ? partial + (size_t)ks * n : nullptr;
+        SRB_TRY(wgrad_tc_launch(x, x_pitch, dy, dy_pitch, partial, bpartial, ks, B, H, W, Cin, Cout, taps, s));
+        wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(partial, dw, ks, taps, Cout, Cin, accumulate);
+        SRB_CUDA(cudaGetLastError());
+        if (db) {
+            bias_grad_final_kernel<<<Cout, 128, 0, s>>>(bpartial, ks, Cout, db, accumulate);
+            SRB_CUDA(cudaGetLastError());
+        }
+        return SRB_OK;
+    }
+    if (W % WG_KC) { set_error("conv_wgrad: W=%d must be a multiple of %d", W, WG_KC); return SRB_E_SHAPE; }
     WgradArgs a;
     a.x = x; a.dy = dy; a.partial = (float*)scratch; a.bpartial = nullptr;
     a.x_pitch = x_pitch; a.dy_pitch = dy_pitch; a.B = B; a.H = H; a.W = W; a.Cin = Cin; a.Cout = Cout; a.taps = taps;

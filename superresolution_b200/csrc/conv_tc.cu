@@ -568,6 +568,7 @@ int conv_tc_launch(const ConvArgs& a_in, cudaStream_t stream) {
     if (a.pixel_shuffle && (a.Cout % 128 || !a.out)) { set_error("conv_tc: pixel_shuffle needs Cout%%128==0"); return SRB_E_ARG; }
     if (a.pre_out || a.gelu_grad_of || a.alpha1_samples) {  // training-path epilogue: instantiated for the two shapes that use it
         if (a.taps == 1 && a.Cout % 96 == 0) return launch_cfg<ConvCfg<96, 2, 1, true>>(a, stream);
+        if (a.taps == 9 && a.Cout == 32 && a.Cin == 96 && a.W % 32 == 0) return launch_cfg<ConvCfg<32, 4, 9, true, 32>>(a, stream);  // cab.0 / cab.2 data gradient: resident weights
         if (a.taps == 9 && a.Cout == 32 && a.W % 32 == 0) return launch_cfg<ConvCfg<32, 4, 9, true>>(a, stream);
         set_error("conv_tc: pre_out / gelu_grad_of / alpha1_samples need a linear with Cout %% 96 == 0 or a 3x3 conv with Cout == 32, W %% 32 == 0");
         return SRB_E_SHAPE;

@@ -75,6 +75,10 @@ int log_normalize_u16(const float* x, uint16_t* out, size_t n, float gmin, float
 
 // conv_bwd.cu
 int pack_conv_weight_dgrad(const float* w, bf16* o, int Cout, int Cin, int taps, cudaStream_t s);
+// wgrad_tc.cu: the tcgen05 weight-gradient kernel behind conv_wgrad (0 splits = shape not covered)
+int wgrad_tc_splits(int B, int H, int W, int Cin, int Cout, int taps);
+int wgrad_tc_launch(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* partial, float* bpartial, int ksplit,
+                    int B, int H, int W, int Cin, int Cout, int taps, cudaStream_t s);
 size_t conv_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps);
 int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* dw, float* db, void* scratch, int B,
                int H, int W, int Cin, int Cout, int taps, int accumulate, cudaStream_t s);
@@ -109,7 +113,7 @@ int chan_attn_fwd(const bf16* y, const float* w1, const float* b1, const float* 
                   float* pooled, float* hid, float* s, void* scratch, int B, int HW, cudaStream_t st);
 int chan_attn_bwd(const bf16* y, const bf16* g, const float* w1, const float* w2, const float* pooled, const float* hid,
                   const float* s, bf16* dy, float* dw1, float* db1, float* dw2, float* db2, float* dpooled,
-                  void* scratch, int B, int HW, int accumulate, cudaStream_t st);
+                  void* scratch, int B, int HW, int accumulate, float g_scale, cudaStream_t st);
 
 // optim.cu
 size_t grad_norm_scratch_bytes();

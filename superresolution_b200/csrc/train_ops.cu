@@ -185,62 +185,86 @@ layernorm96_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ g, c
 #pragma unroll
     for (int j = 0; j < 8; ++j) { gam[j] = __ldg(gamma + c0 + j); dg[j] = 0.f; db[j] = 0.f; }
     const size_t stride = ((size_t)gridDim.x * blockDim.x) >> 4;
-    for (size_t tok = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 4; tok < ntok; tok += stride) {
-        float xv[8], gv[8];
-        {
-            const uint4 xr = __ldg((const uint4*)(x + tok * 96 + c0)), gr = __ldg((const uint4*)(g + tok * 96 + c0));
-            const __nv_bfloat162* xh = (const __nv_bfloat162*)&xr;
-            const __nv_bfloat162* gh = (const __nv_bfloat162*)&gr;
+    constexpr int U = 2;  // tokens in flight per 16-lane group: x, g and res of both are requested before either is used
+    for (size_t t0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 4; t0 < ntok; t0 += U * stride) {
+        uint4 xr[U], gr[U], rr0[U], rr1[U];
+        bool valid[U];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float2 a = __bfloat1622float2(xh[k]), b = __bfloat1622float2(gh[k]);
-                xv[2 * k] = a.x; xv[2 * k + 1] = a.y; gv[2 * k] = b.x; gv[2 * k + 1] = b.y;
-            }
-        }
-        float s = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s += xv[j];
-        const float mean = half16_sum(act ? s : 0.f) * (1.f / 96.f);
-        float q = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) q += (xv[j] - mean) * (xv[j] - mean);
-        const float rstd = rsqrtf(half16_sum(act ? q : 0.f) * (1.f / 96.f) + 1e-5f);
-        float m1 = 0.f, m2 = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            xv[j] = (xv[j] - mean) * rstd;  // xhat
-            const float gg = gv[j] * gam[j];
-            m1 += gg;
-            m2 = fmaf(gg, xv[j], m2);
-            dg[j] = fmaf(gv[j], xv[j], dg[j]);
-            db[j] += gv[j];
-        }
-        m1 = half16_sum(act ? m1 : 0.f) * (1.f / 96.f);
-        m2 = half16_sum(act ? m2 : 0.f) * (1.f / 96.f);
-        if (act) {
-            float o[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = (gv[j] * gam[j] - m1 - xv[j] * m2) * rstd;
-            if (res) {
+        for (int u = 0; u < U; ++u) {
+            const size_t tok = t0 + u * stride;
+            valid[u] = tok < ntok;
+            const size_t off = (valid[u] ? tok : t0) * 96 + c0;
+            xr[u] = __ldcs((const uint4*)(x + off));
+            gr[u] = __ldcs((const uint4*)(g + off));
+            rr0[u] = rr1[u] = make_uint4(0, 0, 0, 0);
+            if (res && act) {
                 if (res_f32) {
-                    const float4 r0 = *(const float4*)((const float*)res + tok * 96 + c0);
-                    const float4 r1 = *(const float4*)((const float*)res + tok * 96 + c0 + 4);
-                    o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w; o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+                    rr0[u] = __ldcs((const uint4*)((const float*)res + off));
+                    rr1[u] = __ldcs((const uint4*)((const float*)res + off + 4));
                 } else {
-                    const uint4 rr = *(const uint4*)((const bf16*)res + tok * 96 + c0);
-                    const __nv_bfloat162* rh = (const __nv_bfloat162*)&rr;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const float2 f = __bfloat1622float2(rh[k]);
-                        o[2 * k] += f.x; o[2 * k + 1] += f.y;
-                    }
+                    rr0[u] = __ldcs((const uint4*)((const bf16*)res + off));
                 }
             }
-            uint4 ov;
-            __nv_bfloat162* oh = (__nv_bfloat162*)&ov;
+        }
 #pragma unroll
-            for (int k = 0; k < 4; ++k) oh[k] = __floats2bfloat162_rn(o[2 * k], o[2 * k + 1]);
-            *(uint4*)(dx + tok * 96 + c0) = ov;
+        for (int u = 0; u < U; ++u) {
+            if (!valid[u]) continue;  // uniform over the 16-lane group (the shuffles below name the half-warp)
+            const size_t tok = t0 + u * stride;
+            float xv[8], gv[8];
+            {
+                const __nv_bfloat162* xh = (const __nv_bfloat162*)&xr[u];
+                const __nv_bfloat162* gh = (const __nv_bfloat162*)&gr[u];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 a = __bfloat1622float2(xh[k]), b = __bfloat1622float2(gh[k]);
+                    xv[2 * k] = a.x; xv[2 * k + 1] = a.y; gv[2 * k] = b.x; gv[2 * k + 1] = b.y;
+                }
+            }
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s += xv[j];
+            const float mean = half16_sum(act ? s : 0.f) * (1.f / 96.f);
+            float q = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) q += (xv[j] - mean) * (xv[j] - mean);
+            const float rstd = rsqrtf(half16_sum(act ? q : 0.f) * (1.f / 96.f) + 1e-5f);
+            float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                xv[j] = (xv[j] - mean) * rstd;  // xhat
+                const float gg = gv[j] * gam[j];
+                m1 += gg;
+                m2 = fmaf(gg, xv[j], m2);
+                if (act) {
+                    dg[j] = fmaf(gv[j], xv[j], dg[j]);
+                    db[j] += gv[j];
+                }
+            }
+            m1 = half16_sum(act ? m1 : 0.f) * (1.f / 96.f);
+            m2 = half16_sum(act ? m2 : 0.f) * (1.f / 96.f);
+            if (act) {
+                float o[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = (gv[j] * gam[j] - m1 - xv[j] * m2) * rstd;
+                if (res) {
+                    if (res_f32) {
+                        const float4 r0 = *(const float4*)&rr0[u], r1 = *(const float4*)&rr1[u];
+                        o[0] += r0.x; o[1] += r0.y; o[2] += r0.z; o[3] += r0.w; o[4] += r1.x; o[5] += r1.y; o[6] += r1.z; o[7] += r1.w;
+                    } else {
+                        const __nv_bfloat162* rh = (const __nv_bfloat162*)&rr0[u];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 f = __bfloat1622float2(rh[k]);
+                            o[2 * k] += f.x; o[2 * k + 1] += f.y;
+                        }
+                    }
+                }
+                uint4 ov;
+                __nv_bfloat162* oh = (__nv_bfloat162*)&ov;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) oh[k] = __floats2bfloat162_rn(o[2 * k], o[2 * k + 1]);
+                __stcs((uint4*)(dx + tok * 96 + c0), ov);
+            }
         }
     }
     if (act) {

@@ -320,8 +320,8 @@ def channel_attention(y, w1, b1, w2, b2):
     return out, (pooled, hid, scale)
 
 
-def channel_attention_bwd(y, g, w1, w2, saved):
-    """Returns (dy bf16 [B,HW,96], dw1 [3,96], db1 [3], dw2 [96,3], db2 [96])."""
+def channel_attention_bwd(y, g, w1, w2, saved, g_scale=1.0):
+    """Returns (dy bf16 [B,HW,96], dw1 [3,96], db1 [3], dw2 [96,3], db2 [96]) for the incoming gradient g_scale * g."""
     B, HW, _ = y.shape
     dev = y.device
     pooled, hid, scale = saved
@@ -333,7 +333,7 @@ def channel_attention_bwd(y, g, w1, w2, saved):
     f = lambda t: t.detach().float().contiguous()
     L.check(lib.srb_channel_attention_bwd(L.ptr(y), L.ptr(g), L.ptr(f(w1)), L.ptr(f(w2)), L.ptr(pooled), L.ptr(hid),
                                           L.ptr(scale), L.ptr(dy), L.ptr(dw1), L.ptr(db1), L.ptr(dw2), L.ptr(db2),
-                                          L.ptr(dpooled), L.ptr(scratch), B, HW, 0, L.current_stream()),
+                                          L.ptr(dpooled), L.ptr(scratch), B, HW, 0, float(g_scale), L.current_stream()),
             'channel_attention_bwd')
     return dy, dw1, db1, dw2, db2
 

@@ -181,10 +181,9 @@ def _hab_bwd(G, pre, saved, shift, rpi, m1, m2, g2):
     dxn = G.dgrad(pre + 'attn.qkv', dqkv)
     # ---- CAB branch (scaled by conv_scale)
     ca_pre = pre + 'conv_block.cab.3.attention.'
-    gs = ops.axpby(torch.empty_like(g1), _CONV_SCALE, g1)
-    dc2, dw1, db1, dw2, db2 = ops.channel_attention_bwd(c2.view(B, H * W, 96), gs.view(B, H * W, 96),
+    dc2, dw1, db1, dw2, db2 = ops.channel_attention_bwd(c2.view(B, H * W, 96), g1.view(B, H * W, 96),
                                                         P[ca_pre + '1.weight'].view(3, 96),
-                                                        P[ca_pre + '3.weight'].view(96, 3), ca_saved)
+                                                        P[ca_pre + '3.weight'].view(96, 3), ca_saved, g_scale=_CONV_SCALE)
     G.g[ca_pre + '1.weight'] = dw1.view(3, 96, 1, 1)
     G.g[ca_pre + '1.bias'] = db1
     G.g[ca_pre + '3.weight'] = dw2.view(96, 3, 1, 1)

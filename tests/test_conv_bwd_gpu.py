@@ -12,6 +12,10 @@ CASES = [(1, 32, 32, 64, 32, 9), (2, 32, 64, 96, 32, 9), (1, 64, 64, 160, 32, 9)
          (1, 32, 32, 32, 96, 9), (2, 64, 32, 96, 96, 9), (1, 64, 64, 64, 256, 9), (2, 32, 32, 96, 288, 1),
          (1, 64, 64, 192, 96, 1), (3, 32, 32, 64, 64, 9), (1, 32, 64, 96, 192, 1), (2, 64, 64, 96, 96, 1),
          (1, 16, 32, 96, 288, 1), (1, 32, 32, 64, 96, 1)]
+# the tcgen05 weight-gradient kernel takes ragged chunks (TMA zero fill) and a full 128-channel M chunk; the last two
+# shapes (Cin 16, Cout 8: conv_first / the padded conv_last) stay on the mma.sync kernels
+WGRAD_EXTRA = [(1, 6, 40, 64, 32, 9), (2, 10, 24, 32, 96, 9), (1, 5, 7, 96, 96, 1), (1, 32, 32, 128, 32, 9),
+               (1, 32, 32, 16, 96, 9), (1, 32, 32, 64, 8, 9)]
 
 
 def _mk(B, H, W, Cin, Cout, taps, cuda, seed):
@@ -44,7 +48,7 @@ def test_conv_dgrad(cuda, B, H, W, Cin, Cout, taps):
     assert torch.equal(G[..., Cin:], G0[..., Cin:])
 
 
-@pytest.mark.parametrize('B,H,W,Cin,Cout,taps', CASES)
+@pytest.mark.parametrize('B,H,W,Cin,Cout,taps', CASES + WGRAD_EXTRA)
 def test_conv_wgrad_and_bias_grad(cuda, B, H, W, Cin, Cout, taps):
     from superresolution_b200 import ops
     x, dy, w, k = _mk(B, H, W, Cin, Cout, taps, cuda, 2)

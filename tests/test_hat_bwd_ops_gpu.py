@@ -122,11 +122,14 @@ def test_channel_attention_forward_backward(cuda, B, HW):
     out, saved = ops.channel_attention(y, w1, b1, w2, b2)
     err = (out.float() - ref.detach()).abs()
     assert (err <= 1e-2 * ref.detach().abs() + 1e-2).all(), err.max().item()
-    dy, dw1, db1, dw2, db2 = ops.channel_attention_bwd(y, gy, w1, w2, saved)
-    err = (dy.float() - yr.grad).abs()
-    assert (err <= 1e-2 * yr.grad.abs() + 1e-2).all(), err.max().item()
-    for got, want in ((dw1, P[0].grad), (db1, P[1].grad), (dw2, P[2].grad), (db2, P[3].grad)):
-        assert (got - want).abs().max().item() <= 1e-2 * want.abs().max().item() + 1e-3, (got - want).abs().max().item()
+    for sc_g in (1.0, 0.25):  # g_scale: the gradient of sc_g * out without a scaling pass over gy (HAB's conv_scale)
+        dy, dw1, db1, dw2, db2 = ops.channel_attention_bwd(y, gy, w1, w2, saved, g_scale=sc_g)
+        want_dy = sc_g * yr.grad
+        err = (dy.float() - want_dy).abs()
+        assert (err <= 1e-2 * want_dy.abs() + 1e-2 * sc_g).all(), err.max().item()
+        for got, want in ((dw1, P[0].grad), (db1, P[1].grad), (dw2, P[2].grad), (db2, P[3].grad)):
+            want = sc_g * want
+            assert (got - want).abs().max().item() <= 1e-2 * want.abs().max().item() + 1e-3 * sc_g, (got - want).abs().max().item()
 
 
 def _ref_overlap_attention(qkv, table, index):
