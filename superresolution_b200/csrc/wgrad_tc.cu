@@ -11,14 +11,22 @@
 // the shared-memory address, so a shifted view reads what TMA wrote).
 //
 // One CTA owns a split of the pixels for the whole launch and accumulates in TMEM (fp32); three operand roles:
-//   mode L   (linear, 1 tap)   M = dY (Cout in tiles of 128 rows), N = X (Cin <= 256);     D tile t at columns t * Cin
-//   mode C1  (3x3, Cout <= 64) M = X chunk of 128 channels (shifted), N = 32 channels of dY; D tap at columns 32 * tap
-//   mode C2  (3x3, Cout > 64)  M = dY chunk of 128 channels, N = 32 channels of X (shifted);  D tap at columns 32 * tap
+//   mode L   (linear, 1 tap)   M = dY (Cout in tiles of 128 rows), N = X (Cin <= 256);  D tile t at columns t * Cin
+//   mode C1  (3x3, Cout <= 64) M = X chunk of 128 channels, N = 32 channels of dY, dY shifted:
+//                              dW[co][ci][tap] = sum_q X[q][ci] dY[q - tap][co]
+//   mode C2  (3x3, Cout > 64)  M = dY chunk of 128 channels, N = 32 channels of X, X shifted
+// In the 3x3 modes the shifted (narrow) operand is a haloed patch of 32-channel rows (64 bytes, SWIZZLE_64B), and ONE MMA
+// covers the three horizontal taps of a kernel row: its N = 96 is three 32-channel atoms whose leading-dimension
+// offset is 64 bytes = one pixel, i.e. three overlapping views of the patch one pixel apart.  Three N = 96 MMAs per
+// k-step instead of nine N = 32 ones (which are issue-bound at ~45 cycles each).  D block b = 3 * row + atom at
+// columns 32 b holds tap b (C2) or tap 8 - b (C1: the shift is on dY, so the view order is mirrored).
 // The bias gradient is one more MMA per k-step against an all-ones operand (any layout: every element is 1.0) into 16
 // or 32 spare TMEM columns.  Split-K partials go to the same [split][tap][co][ci] / [split][co] scratch layout as the
 // mma.sync kernels of conv_bwd.cu, so wgrad_reduce / bias_grad_final (fixed order, deterministic) finish both.
 //
-// Warps: 0 = TMA producer, 1 = MMA issuer (+ TMEM allocation), 2-5 = epilogue (TMEM lane quadrant = warp & 3).
+// Warps: 0 = TMA producer, 1 = MMA issuer (+ TMEM allocation), 2-5 = epilogue (TMEM lane quadrant = warp & 3), 6 = second
+// MMA issuer of the 3x3 modes (their N = 32 MMAs are issue-bound at ~45 cycles per instruction and thread: the two
+// issuers take alternate taps).
 #include <cuda.h>
 
 #include <cstring>
@@ -32,14 +40,14 @@ namespace srb {
 
 namespace {
 
-constexpr int WT_THREADS = 192;
+constexpr int WT_THREADS = 224;  // 7 warps
 constexpr int WT_TW = 32, WT_TH = 4;                 // 3x3 chunk: 4 image rows x 32 pixels (8 k-steps of 16 pixels)
 constexpr int WT_PW = WT_TW + 2, WT_PH = WT_TH + 2;  // haloed X patch of the chunk
 constexpr int WT_KP = 64;                            // linear chunk: 64 consecutive pixels (4 k-steps)
-constexpr int WT_FLAT_ATOM = WT_KP * 128;            // bytes of one 64-channel atom: flat chunk,
-constexpr int WT_TILE_ATOM = WT_TW * WT_TH * 128;    //   unshifted 3x3 chunk,
-constexpr int WT_PATCH_ATOM = (WT_PW * WT_PH * 128 + 1023) / 1024 * 1024;  // haloed patch (rounded to the swizzle atom)
-constexpr int WT_PATCH_BYTES = WT_PW * WT_PH * 128;
+constexpr int WT_FLAT_ATOM = WT_KP * 128;            // bytes of one 64-channel atom (128-byte rows): flat chunk,
+constexpr int WT_TILE_ATOM = WT_TW * WT_TH * 128;    //   3x3 chunk of the un-shifted operand
+constexpr int WT_NPATCH_BYTES = WT_PW * WT_PH * 64;  // haloed patch of the shifted operand: 32-channel rows of 64 bytes
+constexpr int WT_NPATCH_ATOM = (WT_NPATCH_BYTES + 1023) / 1024 * 1024;
 constexpr int WT_ONES_BYTES = 4096;
 constexpr int WT_MAX_STAGES = 4;
 constexpr int WT_SMEM_LIMIT = 227 * 1024;
@@ -78,8 +86,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
     const int c_end = min(a.nchunks, c_begin + a.chunks_per_split);
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < WT_MAX_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        mbar_init(acc_full, 1);
+        const uint32_t n_iss = MODE == WT_L ? 1 : 2;  // MMA issuer warps that release a stage / publish the accumulators
+        for (int i = 0; i < WT_MAX_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], n_iss); }
+        mbar_init(acc_full, n_iss);
         fence_barrier_init();
         tma_prefetch_desc(&tmM);
         tma_prefetch_desc(&tmN);
@@ -96,9 +105,8 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        const uint32_t tx_bytes = MODE == WT_L    ? (uint32_t)(m_loaded + a.n_atoms) * WT_FLAT_ATOM
-                                  : MODE == WT_C1 ? (uint32_t)m_loaded * WT_PATCH_BYTES + WT_TILE_ATOM
-                                                  : (uint32_t)m_loaded * WT_TILE_ATOM + WT_PATCH_BYTES;
+        const uint32_t tx_bytes = MODE == WT_L ? (uint32_t)(m_loaded + a.n_atoms) * WT_FLAT_ATOM
+                                               : (uint32_t)m_loaded * WT_TILE_ATOM + WT_NPATCH_BYTES;
         uint32_t it = 0;
         for (int c = c_begin; c < c_end; ++c, ++it) {
             const uint32_t s = it % a.nstages;
@@ -114,16 +122,16 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
                     const int per_img = a.tiles_x * a.tiles_y;
                     const int b = c / per_img, r = c % per_img;
                     const int y0 = (r / a.tiles_x) * WT_TH, x0 = (r % a.tiles_x) * WT_TW;
-                    const int hm = MODE == WT_C1 ? 1 : 0, hn = MODE == WT_C2 ? 1 : 0;  // which side carries the halo
                     for (int k = 0; k < m_loaded; ++k)
-                        tma_load_4d(sm_m + k * a.m_atom_bytes, &tmM, &full[s], m_c0 + 64 * k, x0 - hm, y0 - hm, b);
-                    tma_load_4d(sm_n, &tmN, &full[s], 64 * (n_chunk >> 1), x0 - hn, y0 - hn, b);
+                        tma_load_4d(sm_m + k * a.m_atom_bytes, &tmM, &full[s], m_c0 + 64 * k, x0, y0, b);
+                    tma_load_4d(sm_n, &tmN, &full[s], 32 * n_chunk, x0 - 1, y0 - 1, b);  // haloed: origin (-1, -1)
                 }
             }
             __syncwarp();
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer =====================
+    } else if (warp == 1 || (warp == 6 && MODE != WT_L)) {
+        // ===================== MMA issuer(s) =====================
+        const int iss = warp == 1 ? 0 : 1;
         const uint32_t ones_u = smem_u32(ones);
         const uint64_t ones_desc = umma_smem_desc(ones_u, 2048, 128, UMMA_SW_NONE);  // K-major planes, all 1.0
         uint32_t it = 0;
@@ -132,7 +140,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
             mbar_wait(&full[s], (it / a.nstages) & 1);
             tc_fence_after();
             const uint32_t m_u = smem_u32(smem + s * a.stage_bytes);
-            const uint32_t n_u = m_u + a.m_atoms * a.m_atom_bytes + (MODE == WT_L ? 0 : (n_chunk & 1) * 64);
+            const uint32_t n_u = m_u + a.m_atoms * a.m_atom_bytes;
             const bool leader = elect_one();
             if (MODE == WT_L) {
                 const uint32_t idesc = umma_idesc_bf16_f32_major(128, a.Cin, 1, 1);
@@ -150,8 +158,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
                     }
                 }
             } else {
-                const uint32_t idesc = umma_idesc_bf16_f32_major(128, 32, 1, 1);
-                // bias: C1 = ones (A, K-major) x dY (B);  C2 = dY (A) x ones (B, K-major); only one CTA column adds it
+                const uint32_t idesc = umma_idesc_bf16_f32_major(128, 96, 1, 1);
+                // bias: C1 = ones (A, K-major) x the un-shifted view of dY (B);  C2 = dY (A) x ones (B, K-major); one CTA
+                // column of the grid adds it
                 const bool bias = a.bpartial && (MODE == WT_C1 ? m_chunk == 0 : n_chunk == 0);
                 const uint32_t idesc_b = MODE == WT_C1 ? umma_idesc_bf16_f32_major(128, 32, 0, 1)
                                                        : umma_idesc_bf16_f32_major(128, 16, 1, 0);
@@ -159,19 +168,16 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
                 for (int ks = 0; ks < WT_TW * WT_TH / 16; ++ks) {
                     const int yy = ks >> 1, xs = (ks & 1) * 16;
                     const uint32_t acc = (c > c_begin || ks > 0);
-                    const uint32_t flat_row = yy * WT_TW + xs;  // row of the un-shifted operand
-                    const uint64_t md0 = umma_smem_desc(m_u + (MODE == WT_C1 ? 0 : flat_row * 128), a.m_atom_bytes, 1024, UMMA_SW_128B);
-                    const uint64_t nd0 = umma_smem_desc(n_u + (MODE == WT_C2 ? 0 : flat_row * 128), a.n_atom_bytes, 1024, UMMA_SW_128B);
+                    const uint64_t md = umma_smem_desc(m_u + (yy * WT_TW + xs) * 128, a.m_atom_bytes, 1024, UMMA_SW_128B);
+                    // patch rows yy + j (j = 0..2), pixels xs + atom (atom = 0..2 through LBO = 64 bytes)
+                    const uint64_t nd0 = umma_smem_desc(n_u + (yy * WT_PW + xs) * 64, 64, 512, UMMA_SW_64B);
 #pragma unroll
-                    for (int tap = 0; tap < 9; ++tap) {
-                        const uint64_t sh = (uint64_t)((((yy + tap / 3) * WT_PW + xs + tap % 3) * 128) >> 4);  // patch row
-                        if (leader)
-                            umma_bf16_ss(tmem_base + 32 * tap, MODE == WT_C1 ? md0 + sh : md0, MODE == WT_C2 ? nd0 + sh : nd0,
-                                         idesc, acc);
-                    }
-                    if (bias && leader) {
-                        if (MODE == WT_C1) umma_bf16_ss(tmem_base + 288, ones_desc, nd0, idesc_b, acc);
-                        else umma_bf16_ss(tmem_base + 288, md0, ones_desc, idesc_b, acc);
+                    for (int j = 0; j < 3; ++j)
+                        if (leader && (j >> 1) == iss)  // issuer 0: kernel rows 0, 1; issuer 1: row 2 + the bias
+                            umma_bf16_ss(tmem_base + 96 * j, md, nd0 + (uint64_t)((j * WT_PW * 64) >> 4), idesc, acc);
+                    if (bias && leader && iss == 1) {
+                        if (MODE == WT_C1) umma_bf16_ss(tmem_base + 288, ones_desc, nd0 + (uint64_t)(((WT_PW + 1) * 64) >> 4), idesc_b, acc);
+                        else umma_bf16_ss(tmem_base + 288, md, ones_desc, idesc_b, acc);
                     }
                 }
             }
@@ -180,7 +186,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
         }
         if (elect_one()) umma_commit(acc_full);
         __syncwarp();
-    } else {
+    } else if (warp >= 2 && warp < 6) {
         // ===================== epilogue: TMEM -> split-K partials =====================
         mbar_wait(acc_full, 0);
         tc_fence_after();
@@ -214,8 +220,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__
         } else {
             float* dst = a.partial + (size_t)blockIdx.x * 9 * a.Cout * a.Cin;
             const int mc = m_c0 + row;  // C1: input channel, C2: output channel
-            for (int tap = 0; tap < 9; ++tap) {
-                tmem_ld_32x32b_x32(tm_lane + 32 * tap, v);
+            for (int blk = 0; blk < 9; ++blk) {
+                const int tap = MODE == WT_C1 ? 8 - blk : blk;
+                tmem_ld_32x32b_x32(tm_lane + 32 * blk, v);
                 tmem_ld_wait();
                 if (MODE == WT_C1) {
                     if (mc < a.Cin) {
@@ -333,17 +340,17 @@ int wgrad_tc_launch(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, fl
         a.nchunks = B * a.tiles_x * a.tiles_y;
         a.m_tiles = 1;
         a.m_atoms = 2; a.n_atoms = 1;
-        a.m_atom_bytes = a.mode == WT_C1 ? WT_PATCH_ATOM : WT_TILE_ATOM;
-        a.n_atom_bytes = a.mode == WT_C1 ? WT_TILE_ATOM : WT_PATCH_ATOM;
+        a.m_atom_bytes = WT_TILE_ATOM;
+        a.n_atom_bytes = WT_NPATCH_ATOM;
         a.n_n_chunks = Cn / 32;
         tiles = ((Cm + 127) / 128) * a.n_n_chunks;
-        cuuint32_t box_halo[4] = {64, (cuuint32_t)WT_PW, (cuuint32_t)WT_PH, 1}, box_flat[4] = {64, (cuuint32_t)WT_TW, (cuuint32_t)WT_TH, 1};
+        cuuint32_t box_m[4] = {64, (cuuint32_t)WT_TW, (cuuint32_t)WT_TH, 1}, box_n[4] = {32, (cuuint32_t)WT_PW, (cuuint32_t)WT_PH, 1};
         cuuint64_t dm[4] = {(cuuint64_t)Cm, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
         cuuint64_t sm[3] = {(cuuint64_t)m_pitch * 2, (cuuint64_t)W * m_pitch * 2, (cuuint64_t)H * W * m_pitch * 2};
         cuuint64_t dn[4] = {(cuuint64_t)Cn, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
         cuuint64_t sn[3] = {(cuuint64_t)n_pitch * 2, (cuuint64_t)W * n_pitch * 2, (cuuint64_t)H * W * n_pitch * 2};
-        SRB_TRY(encode_bf16_map(&tmM, m_ptr, 4, dm, sm, a.mode == WT_C1 ? box_halo : box_flat, CU_TENSOR_MAP_SWIZZLE_128B));
-        SRB_TRY(encode_bf16_map(&tmN, n_ptr, 4, dn, sn, a.mode == WT_C1 ? box_flat : box_halo, CU_TENSOR_MAP_SWIZZLE_128B));
+        SRB_TRY(encode_bf16_map(&tmM, m_ptr, 4, dm, sm, box_m, CU_TENSOR_MAP_SWIZZLE_128B));
+        SRB_TRY(encode_bf16_map(&tmN, n_ptr, 4, dn, sn, box_n, CU_TENSOR_MAP_SWIZZLE_64B));
     }
     a.stage_bytes = a.m_atoms * a.m_atom_bytes + a.n_atoms * a.n_atom_bytes;
     a.nstages = (WT_SMEM_LIMIT - 1024 - WT_ONES_BYTES - 256) / a.stage_bytes;
