@@ -5,6 +5,7 @@
 
 #include "common.h"
 #include "ops.h"
+#include "ptx.cuh"
 
 namespace srb {
 
@@ -281,6 +282,133 @@ layernorm96_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ g, c
     }
 }
 
+// The same backward as a bulk-copy pipeline (bf16 or no residual): a producer warp streams 64-token tiles of x, g and
+// res (12 KB each, contiguous) into a ring of shared-memory stages with cp.async.bulk; eight consumer warps take 8 tokens
+// each.  The register-resident kernel above cannot keep more than one token per 16-lane group in flight at 64 registers
+// (3.5 TB/s at 1 M tokens); here the bytes in flight are the ring (2 CTAs x 108 KB per SM).
+constexpr int LNQ_TOK = 64, LNQ_STAGES = 3, LNQ_TILE_BYTES = LNQ_TOK * 192, LNQ_STAGE_BYTES = 3 * LNQ_TILE_BYTES;
+constexpr int LNQ_SMEM = LNQ_STAGES * LNQ_STAGE_BYTES + 2 * LNQ_STAGES * 8 + 128;
+
+__global__ void __launch_bounds__(288, 2)
+layernorm96_bwd_pipe_kernel(const bf16* __restrict__ x, const bf16* __restrict__ g, const float* __restrict__ gamma,
+                            const bf16* __restrict__ res, bf16* __restrict__ dx, size_t ntok, float* __restrict__ partial) {
+    extern __shared__ uint8_t lnq_raw[];
+    uint8_t* stages = (uint8_t*)(((uintptr_t)lnq_raw + 127) & ~(uintptr_t)127);
+    uint64_t* full = (uint64_t*)(stages + LNQ_STAGES * LNQ_STAGE_BYTES);
+    uint64_t* empty = full + LNQ_STAGES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < LNQ_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 8); }
+        fence_barrier_init();
+    }
+    __syncthreads();
+    const size_t ntiles = (ntok + LNQ_TOK - 1) / LNQ_TOK;
+    const int sub = lane & 15, half = lane >> 4;
+    const bool act = sub < 12;
+    const int c0 = (act ? sub : 0) * 8;
+    float gam[8], dg[8], db[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { gam[j] = __ldg(gamma + c0 + j); dg[j] = 0.f; db[j] = 0.f; }
+    if (warp == 8) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+                const uint32_t s = it % LNQ_STAGES;
+                mbar_wait(&empty[s], ((it / LNQ_STAGES) & 1) ^ 1);
+                const size_t t0 = tile * LNQ_TOK;
+                const uint32_t bytes = (uint32_t)(min((size_t)LNQ_TOK, ntok - t0) * 192);
+                uint8_t* st = stages + s * LNQ_STAGE_BYTES;
+                mbar_arrive_expect_tx(&full[s], bytes * (res ? 3 : 2));
+                bulk_load_1d(st, x + t0 * 96, bytes, &full[s]);
+                bulk_load_1d(st + LNQ_TILE_BYTES, g + t0 * 96, bytes, &full[s]);
+                if (res) bulk_load_1d(st + 2 * LNQ_TILE_BYTES, res + t0 * 96, bytes, &full[s]);
+            }
+        }
+    } else {
+        uint32_t it = 0;
+        for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+            const uint32_t s = it % LNQ_STAGES;
+            mbar_wait(&full[s], (it / LNQ_STAGES) & 1);
+            const uint8_t* st = stages + s * LNQ_STAGE_BYTES;
+            const size_t t0 = tile * LNQ_TOK;
+#pragma unroll 2
+            for (int k = 0; k < 4; ++k) {
+                const size_t tok = t0 + warp * 8 + 2 * k + half;
+                const bool valid = tok < ntok;  // uniform over the 16-lane group
+                const int off = (warp * 8 + 2 * k + half) * 192 + c0 * 2;
+                const uint4 xr = *(const uint4*)(st + off), gr = *(const uint4*)(st + LNQ_TILE_BYTES + off);
+                const uint4 rr = res ? *(const uint4*)(st + 2 * LNQ_TILE_BYTES + off) : make_uint4(0, 0, 0, 0);
+                float xv[8], gv[8];
+                {
+                    const __nv_bfloat162* xh = (const __nv_bfloat162*)&xr;
+                    const __nv_bfloat162* gh = (const __nv_bfloat162*)&gr;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float2 a2 = __bfloat1622float2(xh[q]), b2 = __bfloat1622float2(gh[q]);
+                        xv[2 * q] = a2.x; xv[2 * q + 1] = a2.y; gv[2 * q] = b2.x; gv[2 * q + 1] = b2.y;
+                    }
+                }
+                float sum = 0.f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sum += xv[j];
+                const float mean = half16_sum(act ? sum : 0.f) * (1.f / 96.f);
+                float q2 = 0.f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) q2 += (xv[j] - mean) * (xv[j] - mean);
+                const float rstd = rsqrtf(half16_sum(act ? q2 : 0.f) * (1.f / 96.f) + 1e-5f);
+                float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    xv[j] = (xv[j] - mean) * rstd;  // xhat
+                    const float gg = gv[j] * gam[j];
+                    m1 += gg;
+                    m2 = fmaf(gg, xv[j], m2);
+                    if (act && valid) {
+                        dg[j] = fmaf(gv[j], xv[j], dg[j]);
+                        db[j] += gv[j];
+                    }
+                }
+                m1 = half16_sum(act ? m1 : 0.f) * (1.f / 96.f);
+                m2 = half16_sum(act ? m2 : 0.f) * (1.f / 96.f);
+                if (act && valid) {
+                    float o[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) o[j] = (gv[j] * gam[j] - m1 - xv[j] * m2) * rstd;
+                    const __nv_bfloat162* rh = (const __nv_bfloat162*)&rr;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float2 f = __bfloat1622float2(rh[q]);
+                        o[2 * q] += f.x; o[2 * q + 1] += f.y;
+                    }
+                    uint4 ov;
+                    __nv_bfloat162* oh = (__nv_bfloat162*)&ov;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) oh[q] = __floats2bfloat162_rn(o[2 * q], o[2 * q + 1]);
+                    __stcs((uint4*)(dx + tok * 96 + c0), ov);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);  // this warp has read its 8 tokens: the stage may be refilled
+        }
+    }
+    // per-block dgamma / dbeta: the ring is idle now (every issued copy has been consumed) and takes the fold
+    __syncthreads();
+    float* red = (float*)stages;  // [16 groups][2][96]
+    if (warp < 8 && act) {
+        const int grp = warp * 2 + half;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { red[(grp * 2 + 0) * 96 + c0 + j] = dg[j]; red[(grp * 2 + 1) * 96 + c0 + j] = db[j]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 192) {
+        const int w = threadIdx.x / 96, c = threadIdx.x % 96;
+        float s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) s2 += red[(k * 2 + w) * 96 + c];
+        partial[((size_t)blockIdx.x * 2 + w) * 96 + c] = s2;
+    }
+}
+
 __global__ void __launch_bounds__(128)
 layernorm96_bwd_final_kernel(const float* __restrict__ partial, int nblk, float* __restrict__ dgamma,
                              float* __restrict__ dbeta, int accumulate) {
@@ -346,8 +474,17 @@ int layernorm96_bwd(const bf16* x, const bf16* g, const float* gamma, const void
         return SRB_E_ARG;
     }
     size_t want = (ntok * 16 + 255) / 256;
-    const int grid = (int)(want < 1 ? 1 : (want > LNB_BLOCKS ? LNB_BLOCKS : want));
-    layernorm96_bwd_kernel<<<grid, 256, 0, s>>>(x, g, gamma, res, res_f32, dx, ntok, (float*)scratch);
+    int grid = (int)(want < 1 ? 1 : (want > LNB_BLOCKS ? LNB_BLOCKS : want));
+    if (ntok >= 16384 && !(res && res_f32)) {
+        static std::atomic<unsigned long long> smem_set{0};
+        SRB_TRY(opt_in_dynamic_smem(layernorm96_bwd_pipe_kernel, LNQ_SMEM, smem_set));
+        const size_t ntiles = (ntok + LNQ_TOK - 1) / LNQ_TOK;
+        const size_t cap = (size_t)num_sms() * 2 < (size_t)LNB_BLOCKS ? (size_t)num_sms() * 2 : (size_t)LNB_BLOCKS;
+        grid = (int)(ntiles < cap ? ntiles : cap);
+        layernorm96_bwd_pipe_kernel<<<grid, 288, LNQ_SMEM, s>>>(x, g, gamma, (const bf16*)res, dx, ntok, (float*)scratch);
+    } else {
+        layernorm96_bwd_kernel<<<grid, 256, 0, s>>>(x, g, gamma, res, res_f32, dx, ntok, (float*)scratch);
+    }
     SRB_CUDA(cudaGetLastError());
     layernorm96_bwd_final_kernel<<<192, 128, 0, s>>>((const float*)scratch, grid, dgamma, dbeta, accumulate);
     SRB_CUDA(cudaGetLastError());

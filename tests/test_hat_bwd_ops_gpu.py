@@ -8,7 +8,9 @@ import torch.nn.functional as F
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize('ntok,with_res', [(64, None), (4096 + 37, 'bf16'), (148 * 4 * 16 * 3 + 5, 'f32')])
+# >= 16384 tokens with a bf16 / no residual take the bulk-copy pipeline kernel of the backward (ragged last tile included)
+@pytest.mark.parametrize('ntok,with_res', [(64, None), (4096 + 37, 'bf16'), (148 * 4 * 16 * 3 + 5, 'f32'),
+                                           (16384 + 128 * 37 + 19, 'bf16'), (300 * 128 * 3 + 77, None)])
 def test_layernorm96_forward_backward(cuda, ntok, with_res):
     from superresolution_b200 import ops
     g = torch.Generator().manual_seed(ntok)
@@ -25,7 +27,8 @@ def test_layernorm96_forward_backward(cuda, ntok, with_res):
     y_ref = F.layer_norm(xr, (96,), gr, br, 1e-5)
     y_ref.backward(gy.float())
     y = ops.layernorm96(x, gamma, beta)
-    assert (y.float() - y_ref.detach()).abs().max().item() <= 3e-2
+    err = (y.float() - y_ref.detach()).abs()  # bf16 output: half an ulp is 2^-9 relative
+    assert (err <= 4e-3 * y_ref.detach().abs() + 1e-2).all(), err.max().item()
     dx, dg, db = ops.layernorm96_bwd(x, gy, gamma, res=res)
     want = xr.grad + (res.float() if res is not None else 0)
     err = (dx.float() - want).abs()
