@@ -105,12 +105,13 @@ def config4(dev, rank, world, sampler_cls, gpu_index, batch=32, micro=16, steps=
     import torch.distributed as dist
     from superresolution_b200.architecture import HybridSuperResolutionModel
     from superresolution_b200.losses import CombinedLoss
-    from superresolution_b200.optim import FusedAdamW, allreduce_gradients
-    from superresolution_b200.training import _head, _tail
+    from superresolution_b200.optim import FusedAdamW, allreduce_gradients_start, allreduce_gradients_wait
+    from superresolution_b200.training import _head, _tail, stage2_offset
     torch.manual_seed(0)
     model = HybridSuperResolutionModel(smoothing='none').to(dev).train()
     opt = FusedAdamW(model.parameters(), lr=5e-4, weight_decay=0.0)
     crit = CombinedLoss()
+    cut = stage2_offset(model, opt)
     g = torch.Generator(device=dev).manual_seed(10 + rank)
     x = torch.rand(batch, 1, 128, 128, device=dev, generator=g)
     t = torch.rand(batch, 1, 512, 512, device=dev, generator=g) * 0.02
@@ -127,11 +128,13 @@ def config4(dev, rank, world, sampler_cls, gpu_index, batch=32, micro=16, steps=
             loss, _ = crit(_tail(model, ys, 0.1), t[s:s + micro])
             (loss * (ys.shape[0] / batch)).backward()
             g1[s:s + micro] = ys.grad
-        y1.backward(g1)
+        works = allreduce_gradients_start(opt.flat_grad, lo=cut) if world > 1 else []  # stage 2 is final: reduce it
+        y1.backward(g1)                                                                # under the stage-1 backward
         e0, e1 = _ev(), _ev()
         e0.record()
         if world > 1:
-            allreduce_gradients(opt.flat_grad)
+            works += allreduce_gradients_start(opt.flat_grad, hi=cut)
+            allreduce_gradients_wait(works)
         e1.record()
         opt.step(grad_scale=1.0, max_norm=1.0, world=world)
         if record:

@@ -63,6 +63,14 @@ class FusedAdamW(torch.optim.Optimizer):
             if p.grad is None or p.grad.data_ptr() != self.flat_grad.data_ptr() + 4 * o:
                 p.grad = self.flat_grad[o:o + p.numel()].view_as(p)
 
+    def offset_of(self, param):
+        """first element of ``param`` in the flat buffers (the all-reduce of a parameter range can start as soon as the
+        last gradient of that range is final)"""
+        for p, o in zip(self.param_groups[0]['params'], self._offsets):
+            if p is param:
+                return o
+        raise KeyError('FusedAdamW.offset_of: not a parameter of this optimizer')
+
     def _gather_stray_grads(self):
         """``model.zero_grad()`` (set_to_none is torch's default) or ``p.grad = None`` drops the views; autograd then
         allocates fresh ``.grad`` tensors and the flat buffer would go stale.  Before the flat buffer is read, every
@@ -128,17 +136,29 @@ def bucket_ranges(numel, bucket_elems):
     return [(s, min(s + bucket_elems, numel)) for s in range(0, numel, bucket_elems)]
 
 
+def allreduce_gradients_start(flat_grad, group=None, bucket_bytes=25 << 20, lo=0, hi=None):
+    """Launch the SUM all-reduce of flat_grad[lo:hi] in ~25 MB buckets and return the pending work handles: the
+    collectives run on the backend's own stream, so whatever the caller enqueues next (the stage-1 backward, which does
+    not touch this range) overlaps them.  Finish with ``allreduce_gradients_wait``."""
+    if not dist.is_available() or not dist.is_initialized():
+        raise RuntimeError('allreduce_gradients: torch.distributed is not initialised')
+    if dist.get_world_size(group) == 1:
+        return []
+    hi = flat_grad.numel() if hi is None else hi
+    per = max(1, bucket_bytes // flat_grad.element_size())
+    return [dist.all_reduce(flat_grad[lo + s:lo + e], op=dist.ReduceOp.SUM, group=group, async_op=True)
+            for s, e in bucket_ranges(hi - lo, per)]
+
+
+def allreduce_gradients_wait(works):
+    for w in works:
+        w.wait()
+
+
 def allreduce_gradients(flat_grad, group=None, bucket_bytes=25 << 20):
     """SUM all-reduce of the flat gradient in ~25 MB buckets (all launched asynchronously, then waited), the
     replacement for nn.DataParallel's reduce-add (Modello_supporto.py:103-105).  The 1/world mean is NOT applied
     here: pass ``world=`` to FusedAdamW.step, which folds it into the update.  Backend: NCCL on CUDA tensors (NVLink /
     NVSwitch), gloo on CPU tensors (tests)."""
-    if not dist.is_available() or not dist.is_initialized():
-        raise RuntimeError('allreduce_gradients: torch.distributed is not initialised')
-    if dist.get_world_size(group) == 1:
-        return flat_grad
-    works = [dist.all_reduce(flat_grad[s:e], op=dist.ReduceOp.SUM, group=group, async_op=True)
-             for s, e in bucket_ranges(flat_grad.numel(), max(1, bucket_bytes // flat_grad.element_size()))]
-    for w in works:
-        w.wait()
+    allreduce_gradients_wait(allreduce_gradients_start(flat_grad, group, bucket_bytes))
     return flat_grad

@@ -286,7 +286,7 @@ def train_step(model, optimizer, criterion, lr, hr, micro_batch=16, max_norm=1.0
     of the slice gradients IS the batch gradient; parameter gradients accumulate in the optimizer's flat fp32 buffer.
     ``model`` must be in train() mode, on CUDA; ``optimizer`` a ``FusedAdamW`` over ``model.parameters()``.
     Returns the batch loss (0-d tensor, no sync)."""
-    from .optim import allreduce_gradients
+    from .optim import allreduce_gradients_start, allreduce_gradients_wait
     B = lr.shape[0]
     mb = micro_batch or B
     optimizer.zero_grad()
@@ -300,9 +300,30 @@ def train_step(model, optimizer, criterion, lr, hr, micro_batch=16, max_norm=1.0
         (loss * (grad_scale * (e - s) / B)).backward()  # mean over the whole batch = weighted sum of slice means
         g1[s:e] = ys.grad
         total = loss.detach() * ((e - s) / B) if total is None else total + loss.detach() * ((e - s) / B)
+    works, cut = [], 0
+    if world > 1:
+        # every stage-2 gradient is final here (the stage-1 backward below does not touch them): their all-reduce
+        # starts now and runs under the stage-1 backward.  model.parameters() lists stage 1 first, so stage 2 is the
+        # tail of the flat buffer.
+        optimizer._gather_stray_grads()  # (no-op on this path: the autograd functions accumulate into the flat views)
+        cut = stage2_offset(model, optimizer)
+        works = allreduce_gradients_start(optimizer.flat_grad, group, lo=cut)
     y1.backward(g1)
     if world > 1:
-        optimizer._gather_stray_grads()  # (no-op on this path: the autograd functions accumulate into the flat views)
-        allreduce_gradients(optimizer.flat_grad, group)
+        optimizer._gather_stray_grads()
+        works += allreduce_gradients_start(optimizer.flat_grad, group, hi=cut)
+        allreduce_gradients_wait(works)
     optimizer.step(grad_scale=grad_scale, max_norm=max_norm, world=world)
     return total
+
+
+def stage2_offset(model, optimizer):
+    """flat-buffer offset of the first stage-2 parameter when stage 2 forms the tail of the optimizer's parameter list
+    (the order of ``HybridSuperResolutionModel.parameters()``); otherwise the buffer's length = nothing is reduced early"""
+    m = getattr(model, 'module', model)
+    s2 = {id(p) for p in m.stage2.parameters()}
+    ps = optimizer.param_groups[0]['params']
+    first = next((i for i, p in enumerate(ps) if id(p) in s2), None)
+    if first is None or any(id(p) not in s2 for p in ps[first:]):
+        return optimizer.numel
+    return optimizer.offset_of(ps[first])

@@ -128,3 +128,22 @@ def test_drives_model_parameters_and_repack(cuda):
         y1 = m(x)
     assert not torch.equal(y0, y1)  # repacked with the updated bias
     assert (m.stage2.conv_last.bias - sd0['stage2.conv_last.bias']).abs().max().item() > 0
+
+
+def test_stage2_gradient_range_is_the_tail_of_the_flat_buffer(cuda):
+    """train_step all-reduces flat_grad[cut:] (stage 2) under the stage-1 backward: the cut must separate the stages."""
+    from superresolution_b200.architecture import HybridSuperResolutionModel
+    from superresolution_b200.optim import FusedAdamW
+    from superresolution_b200.training import stage2_offset
+    m = HybridSuperResolutionModel(smoothing='none').to(cuda)
+    opt = FusedAdamW(m.parameters(), lr=1e-3)
+    cut = stage2_offset(m, opt)
+    base = opt.flat_grad.data_ptr()
+    assert 0 < cut < opt.numel
+    for n, p in m.named_parameters():
+        off = (p.grad.data_ptr() - base) // 4
+        assert (off >= cut) == n.startswith('stage2.'), n
+    # a parameter list that interleaves the stages cannot be split: nothing is reduced early
+    mixed = list(m.stage2.parameters())[:3] + list(m.stage1.parameters())[:3]
+    opt2 = FusedAdamW(mixed, lr=1e-3)
+    assert stage2_offset(m, opt2) == opt2.numel

@@ -80,6 +80,16 @@ def _allreduce_worker(rank, world, port, q):
     g = torch.Generator().manual_seed(100 + rank)
     flat = torch.randn(100_003, generator=g)
     allreduce_gradients(flat, bucket_bytes=64 << 10)  # 7 buckets, the last one ragged
+    # the overlapped form of train_step: the tail range (stage 2) first, other work in between, then the head range
+    from superresolution_b200.optim import allreduce_gradients_start, allreduce_gradients_wait
+    flat2 = torch.randn(100_003, generator=torch.Generator().manual_seed(100 + rank))
+    works = allreduce_gradients_start(flat2, bucket_bytes=64 << 10, lo=60_001)
+    head = flat2[:10].clone()
+    flat2[:10] = 0.0   # "stage-1 backward" still writes the head range while the tail is in flight
+    flat2[:10] = head
+    works += allreduce_gradients_start(flat2, bucket_bytes=64 << 10, hi=60_001)
+    allreduce_gradients_wait(works)
+    assert torch.equal(flat2, flat), (flat2 - flat).abs().max()
     q.put((rank, flat[:5].tolist(), float(flat.double().sum())))
     dist.destroy_process_group()
 
