@@ -107,6 +107,7 @@ def config4(dev, rank, world, sampler_cls, gpu_index, batch=32, micro=16, steps=
     from superresolution_b200.losses import CombinedLoss
     from superresolution_b200.optim import FusedAdamW, allreduce_gradients_start, allreduce_gradients_wait
     from superresolution_b200.training import _head, _tail, stage2_offset
+    from superresolution_b200 import ops
     torch.manual_seed(0)
     model = HybridSuperResolutionModel(smoothing='none').to(dev).train()
     opt = FusedAdamW(model.parameters(), lr=5e-4, weight_decay=0.0)
@@ -123,11 +124,12 @@ def config4(dev, rank, world, sampler_cls, gpu_index, batch=32, micro=16, steps=
         y1 = _head(model, x, True)
         g1 = torch.empty_like(y1)
         loss = None
-        for s in range(0, batch, micro):
-            ys = y1[s:s + micro].detach().requires_grad_(True)
-            loss, _ = crit(_tail(model, ys, 0.1), t[s:s + micro])
-            (loss * (ys.shape[0] / batch)).backward()
-            g1[s:s + micro] = ys.grad
+        with ops.weight_pack_cache():  # as train_step: one pack per weight and step
+            for s in range(0, batch, micro):
+                ys = y1[s:s + micro].detach().requires_grad_(True)
+                loss, _ = crit(_tail(model, ys, 0.1), t[s:s + micro])
+                (loss * (ys.shape[0] / batch)).backward()
+                g1[s:s + micro] = ys.grad
         works = allreduce_gradients_start(opt.flat_grad, lo=cut) if world > 1 else []  # stage 2 is final: reduce it
         y1.backward(g1)                                                                # under the stage-1 backward
         e0, e1 = _ev(), _ev()

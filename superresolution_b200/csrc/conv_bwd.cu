@@ -378,36 +378,52 @@ bool wgrad_full_shape(int Cin, int Cout, int taps) {
                          (Cout == 96 && Cin == 96));
 }
 
-// dW[co][ci][tap] (PyTorch layout) = (accumulate ? dW : 0) + sum_split partial[split][tap][co][ci], fixed order
-__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int ksplit, int taps,
-                                    int Cout, int Cin, int accumulate) {
-    const int n = taps * Cout * Cin;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+// dW[co][ci][tap] (PyTorch layout) = (accumulate ? dW : 0) + sum_split partial[split][tap][co][ci];
+// db[c] = (accumulate ? db[c] : 0) + sum_split bpartial[split][c].
+// Both reductions of a weight-gradient launch in ONE kernel (the step makes ~1000 of these pairs): blocks [0, gw) sum the
+// weight partials, 64 outputs x 4 split slices per block (the serial walk over 148 splits by one thread per output was
+// latency-bound: 9 us per call), the rest the bias partials.  Fixed order: deterministic.
+__global__ void __launch_bounds__(256)
+wgrad_finish_kernel(const float* __restrict__ partial, float* __restrict__ dw, const float* __restrict__ bpartial,
+                    float* __restrict__ db, int ksplit, int taps, int Cout, int Cin, int accumulate, int gw) {
+    __shared__ double sh[4][64];
+    const int o = threadIdx.x & 63, sl = threadIdx.x >> 6;
+    if ((int)blockIdx.x < gw) {
+        const int n = taps * Cout * Cin, i = blockIdx.x * 64 + o;
         float s = 0.f;
-        for (int k = 0; k < ksplit; ++k) s += partial[(size_t)k * n + i];
-        const int ci = i % Cin, co = (i / Cin) % Cout, tap = i / (Cin * Cout);
-        float* o = dw + ((size_t)co * Cin + ci) * taps + tap;
-        *o = accumulate ? *o + s : s;
+        if (i < n)
+            for (int k = sl; k < ksplit; k += 4) s += partial[(size_t)k * n + i];
+        sh[sl][o] = (double)s;
+        __syncthreads();
+        if (sl == 0 && i < n) {
+            const float tot = (float)sh[0][o] + (float)sh[1][o] + (float)sh[2][o] + (float)sh[3][o];
+            const int ci = i % Cin, co = (i / Cin) % Cout, tap = i / (Cin * Cout);
+            float* d = dw + ((size_t)co * Cin + ci) * taps + tap;
+            *d = accumulate ? *d + tot : tot;
+        }
+    } else {
+        const int c = (blockIdx.x - gw) * 64 + o;
+        double s = 0.0;
+        if (c < Cout)
+            for (int k = sl; k < ksplit; k += 4) s += (double)bpartial[(size_t)k * Cout + c];
+        sh[sl][o] = s;
+        __syncthreads();
+        if (sl == 0 && c < Cout) {
+            const float tot = (float)(sh[0][o] + sh[1][o] + sh[2][o] + sh[3][o]);
+            db[c] = accumulate ? db[c] + tot : tot;
+        }
     }
+}
+
+int wgrad_finish(const float* partial, float* dw, const float* bpartial, float* db, int ksplit, int taps, int Cout, int Cin,
+                 int accumulate, cudaStream_t s) {
+    const int gw = (taps * Cout * Cin + 63) / 64, gb = db ? (Cout + 63) / 64 : 0;
+    wgrad_finish_kernel<<<gw + gb, 256, 0, s>>>(partial, dw, bpartial, db, ksplit, taps, Cout, Cin, accumulate, gw);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
 }
 
 constexpr int BG_ROWS = 256;  // (scratch sizing only: the column sums now come from the weight-gradient kernels)
-
-// db[c] = (accumulate ? db[c] : 0) + sum_blk partial[blk][c]; one block per channel, fixed-order tree (deterministic)
-__global__ void __launch_bounds__(128)
-bias_grad_final_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ db, int accumulate) {
-    __shared__ double sh[128];
-    const int c = blockIdx.x;
-    double s = 0.0;
-    for (int i = threadIdx.x; i < nblk; i += 128) s += (double)partial[(size_t)i * C + c];
-    sh[threadIdx.x] = s;
-    __syncthreads();
-    for (int k = 64; k > 0; k >>= 1) {
-        if (threadIdx.x < k) sh[threadIdx.x] += sh[threadIdx.x + k];
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) db[c] = accumulate ? db[c] + (float)sh[0] : (float)sh[0];
-}
 
 int wgrad_tiles(int Cin, int Cout) {
     const int bm = Cout <= 32 ? 32 : 64, bn = Cout <= 32 ? 64 : 32;
@@ -462,13 +478,7 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
         float* partial = (float*)scratch;
         float* bpartial = db ? partial + (size_t)ks * n : nullptr;
         SRB_TRY(wgrad_tc_launch(x, x_pitch, dy, dy_pitch, partial, bpartial, ks, B, H, W, Cin, Cout, taps, s));
-        wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(partial, dw, ks, taps, Cout, Cin, accumulate);
-        SRB_CUDA(cudaGetLastError());
-        if (db) {
-            bias_grad_final_kernel<<<Cout, 128, 0, s>>>(bpartial, ks, Cout, db, accumulate);
-            SRB_CUDA(cudaGetLastError());
-        }
-        return SRB_OK;
+        return wgrad_finish(partial, dw, bpartial, db, ks, taps, Cout, Cin, accumulate, s);
     }
     if (W % WG_KC) { set_error("conv_wgrad: W=%d must be a multiple of %d", W, WG_KC); return SRB_E_SHAPE; }
     WgradArgs a;
@@ -489,13 +499,7 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
     } else if (taps == 9) rc = Cout <= 32 ? launch_wgrad<1, 9>(a, tiles, ksplit, s) : launch_wgrad<2, 9>(a, tiles, ksplit, s);
     else rc = Cout <= 32 ? launch_wgrad<1, 1>(a, tiles, ksplit, s) : launch_wgrad<2, 1>(a, tiles, ksplit, s);
     if (rc != SRB_OK) return rc;
-    wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(a.partial, dw, ksplit, taps, Cout, Cin, accumulate);
-    SRB_CUDA(cudaGetLastError());
-    if (db) {
-        bias_grad_final_kernel<<<Cout, 128, 0, s>>>(a.bpartial, ksplit, Cout, db, accumulate);
-        SRB_CUDA(cudaGetLastError());
-    }
-    return SRB_OK;
+    return wgrad_finish(a.partial, dw, a.bpartial, db, ksplit, taps, Cout, Cin, accumulate, s);
 }
 
 }  // namespace srb

@@ -6,6 +6,44 @@ import torch
 from . import _lib as L
 
 
+_PACK_SCOPE = 0  # id of the active weight_pack_cache() scope, 0 = none: every call packs afresh
+
+
+class weight_pack_cache:
+    """``with ops.weight_pack_cache():`` — inside the scope ``packed_weight`` keeps each parameter's packed bf16 image
+    on the parameter object, so that the micro-batches of ONE training step (forward and backward) pack every weight
+    once.  The caller guarantees that no parameter changes inside the scope (train_step: the optimizer runs after it);
+    outside a scope nothing is cached, so a parameter edited between two forwards can never meet a stale image."""
+    _next = 1
+
+    def __enter__(self):
+        global _PACK_SCOPE
+        self._prev = _PACK_SCOPE
+        _PACK_SCOPE = weight_pack_cache._next
+        weight_pack_cache._next += 1
+        return self
+
+    def __exit__(self, *exc):
+        global _PACK_SCOPE
+        _PACK_SCOPE = self._prev
+        return False
+
+
+def packed_weight(param, w, dgrad=False):
+    """pack_conv_weight / pack_conv_weight_dgrad of ``w`` (the fp32 view of ``param``); cached on the parameter object
+    for the lifetime of the enclosing ``weight_pack_cache`` scope."""
+    if _PACK_SCOPE == 0:
+        return pack_conv_weight_dgrad(w) if dgrad else pack_conv_weight(w)
+    key = (_PACK_SCOPE, w.data_ptr(), tuple(w.shape))
+    c = getattr(param, '_srb_packs', None)
+    if c is None or c[0] != key:
+        c = (key, {})
+        param._srb_packs = c
+    if dgrad not in c[1]:
+        c[1][dgrad] = pack_conv_weight_dgrad(w) if dgrad else pack_conv_weight(w)
+    return c[1][dgrad]
+
+
 def pack_conv_weight(w):
     """fp32 [Cout,Cin,kh,kw] (or Linear [Cout,Cin]) CUDA tensor -> bf16 [taps][Cout][Cin]."""
     w = w.detach().float().contiguous()

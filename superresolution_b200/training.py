@@ -293,13 +293,14 @@ def train_step(model, optimizer, criterion, lr, hr, micro_batch=16, max_norm=1.0
     y1 = _head(model, lr, True)
     g1 = torch.empty_like(y1)
     total = None
-    for s in range(0, B, mb):
-        e = min(B, s + mb)
-        ys = y1[s:e].detach().requires_grad_(True)
-        loss, _ = criterion(_tail(model, ys, drop_path_rate), hr[s:e])
-        (loss * (grad_scale * (e - s) / B)).backward()  # mean over the whole batch = weighted sum of slice means
-        g1[s:e] = ys.grad
-        total = loss.detach() * ((e - s) / B) if total is None else total + loss.detach() * ((e - s) / B)
+    with ops.weight_pack_cache():  # the parameters do not change before optimizer.step: pack each weight once
+        for s in range(0, B, mb):
+            e = min(B, s + mb)
+            ys = y1[s:e].detach().requires_grad_(True)
+            loss, _ = criterion(_tail(model, ys, drop_path_rate), hr[s:e])
+            (loss * (grad_scale * (e - s) / B)).backward()  # mean over the whole batch = weighted sum of slice means
+            g1[s:e] = ys.grad
+            total = loss.detach() * ((e - s) / B) if total is None else total + loss.detach() * ((e - s) / B)
     works, cut = [], 0
     if world > 1:
         # every stage-2 gradient is final here (the stage-1 backward below does not touch them): their all-reduce

@@ -50,15 +50,19 @@ def _scale_samples(t, m, plus=None):
 class _Tape:
     """forward helpers that remember nothing themselves: the caller stores what its backward needs"""
 
-    def __init__(self, P):
+    def __init__(self, P, params):
         self.P = P
+        self.params = params  # name -> the nn.Parameter object (carries the packed-weight cache)
+
+    def packed(self, name):
+        return ops.packed_weight(self.params[name + '.weight'], self.P[name + '.weight'])
 
     def conv(self, x, cin, name, out=None, **kw):
         w, b = self.P[name + '.weight'], self.P[name + '.bias']
         if out is None:
             B, H, W = x.shape[:3]
             out = torch.empty(B, H, W, w.shape[0], dtype=torch.bfloat16, device=x.device)
-        ops.conv_nhwc(x, cin, ops.pack_conv_weight(w), b, out=out, **kw)
+        ops.conv_nhwc(x, cin, self.packed(name), b, out=out, **kw)
         return out
 
 
@@ -67,7 +71,7 @@ class _Tape:
         w, b = self.P[name + '.weight'], self.P[name + '.bias']
         B, H, W = x.shape[:3]
         pre = torch.empty(B, H, W, w.shape[0], dtype=torch.bfloat16, device=x.device)
-        act = ops.conv_nhwc_train(x, cin, ops.pack_conv_weight(w), b, act=L.ACT_GELU, pre_out=pre)
+        act = ops.conv_nhwc_train(x, cin, self.packed(name), b, act=L.ACT_GELU, pre_out=pre)
         return act, pre
 
 
@@ -79,12 +83,13 @@ class _Tape:
         cs = None
         if res2 is not None:
             cs = torch.full((x.shape[0], w.shape[0]), float(res2_scale), dtype=torch.float32, device=x.device)
-        return ops.conv_nhwc_train(x, cin, ops.pack_conv_weight(w), b, res1=res, alpha1_samples=a, res2=res2, res2_cs=cs)
+        return ops.conv_nhwc_train(x, cin, self.packed(name), b, res1=res, alpha1_samples=a, res2=res2, res2_cs=cs)
 
 
 class _Grads:
-    def __init__(self, P):
+    def __init__(self, P, params):
         self.P = P
+        self.params = params
         self.g = {}
 
     def wgrad(self, name, x, cin, dy, cout, taps):
@@ -96,14 +101,15 @@ class _Grads:
         """out (+)= conv^T(dy) through the weights of `name` (3x3 conv or Linear); with ``gelu_grad_of`` (the saved
         pre-activation that fed a GELU producing this layer's input) the result is multiplied by GELU' of it"""
         w = self.P[name + '.weight']
+        wd = ops.packed_weight(self.params[name + '.weight'], w, dgrad=True)
         cout, cin = w.shape[0], w.shape[1]
         if out is None:
             B, H, W = dy.shape[:3]
             out = torch.empty(B, H, W, cin, dtype=torch.bfloat16, device=dy.device)
         if gelu_grad_of is not None:
             assert not acc
-            return ops.conv_nhwc_train(dy, cout, ops.pack_conv_weight_dgrad(w), None, out=out, gelu_grad_of=gelu_grad_of)
-        ops.conv_nhwc(dy, cout, ops.pack_conv_weight_dgrad(w), None, out=out, res1=out if acc else None)
+            return ops.conv_nhwc_train(dy, cout, wd, None, out=out, gelu_grad_of=gelu_grad_of)
+        ops.conv_nhwc(dy, cout, wd, None, out=out, res1=out if acc else None)
         return out
 
     def ln_bwd(self, name, x, g, res=None):
@@ -239,7 +245,8 @@ class _HATFn(torch.autograd.Function):
         if H % 16 or W % 32:
             raise ValueError('hat_forward: H must be a multiple of 16 and W of 32 (tile and weight-gradient chunking)')
         dev = x.device
-        T = _Tape(P)
+        PO = dict(zip(names, params))
+        T = _Tape(P, PO)
         x16 = torch.zeros(B, H, W, 16, dtype=torch.bfloat16, device=dev)
         x16[..., 0] = x.detach()[:, 0]
         wf = _pad_w(P['conv_first.weight'], cin=16)
@@ -264,10 +271,11 @@ class _HATFn(torch.autograd.Function):
         r = T.conv(tn, 96, 'conv_after_body', res1=f)
         u = T.conv(r, 96, 'conv_before_upsample.0', act=L.ACT_LRELU, slope=_LRELU)
         s = torch.empty(B, 2 * H, 2 * W, 64, dtype=torch.bfloat16, device=dev)
-        ops.conv_nhwc(u, 64, ops.pack_conv_weight(P['upsample.0.weight']), P['upsample.0.bias'], out=s, pixel_shuffle=True)
+        ops.conv_nhwc(u, 64, T.packed('upsample.0'), P['upsample.0.bias'], out=s, pixel_shuffle=True)
         y = ops.conv3x3_cout1(s, P['conv_last.weight'], P['conv_last.bias'])  # fp32 [B,2H,2W]
         if debug is not None:  # test hook: the stored LeakyReLU output (its sign pattern decides the backward)
             debug['u'] = u
+        ctx.params = PO
         ctx.saved = (P, names, rpi_sa, rpi_oca, masks, x16, f, saved_layers, tN, tn, r, u, s)
         ctx.geom = (B, H, W)
         ctx.need_dx = ctx.needs_input_grad[0]
@@ -279,7 +287,7 @@ class _HATFn(torch.autograd.Function):
         B, H, W = ctx.geom
         dev = gy.device
         bf = dict(dtype=torch.bfloat16, device=dev)
-        G = _Grads(P)
+        G = _Grads(P, ctx.params)
         # ---- conv_last (64 -> 1): gradient padded to 16 channels so that the tensor-core kernels apply
         g16 = torch.zeros(B, 2 * H, 2 * W, 16, **bf)
         g16[..., 0] = gy.detach()[:, 0]

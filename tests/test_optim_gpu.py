@@ -147,3 +147,23 @@ def test_stage2_gradient_range_is_the_tail_of_the_flat_buffer(cuda):
     mixed = list(m.stage2.parameters())[:3] + list(m.stage1.parameters())[:3]
     opt2 = FusedAdamW(mixed, lr=1e-3)
     assert stage2_offset(m, opt2) == opt2.numel
+
+
+def test_packed_weight_cache_lives_only_inside_its_scope(cuda):
+    """train_step packs every stage-2 weight once per step (ops.weight_pack_cache); outside a scope nothing is cached,
+    so a parameter edited between two forwards never meets a stale packed image."""
+    from superresolution_b200 import ops
+    p = torch.nn.Parameter(torch.randn(96, 32, 3, 3, device=cuda))
+    w = p.detach()
+    a = ops.packed_weight(p, w)
+    with torch.no_grad():
+        p.data.mul_(2.0)  # an edit torch's version counter does not see
+    b = ops.packed_weight(p, w)
+    assert a.data_ptr() != b.data_ptr() and torch.equal(b.float(), (2 * a.float()).bfloat16().float())
+    with ops.weight_pack_cache():
+        c1, d1 = ops.packed_weight(p, w), ops.packed_weight(p, w, dgrad=True)
+        c2, d2 = ops.packed_weight(p, w), ops.packed_weight(p, w, dgrad=True)
+        assert c1 is c2 and d1 is d2 and torch.equal(c1, b)
+        assert torch.equal(d1, ops.pack_conv_weight_dgrad(w))
+    with ops.weight_pack_cache():
+        assert ops.packed_weight(p, w) is not c1  # a new scope (= a new step) packs again
