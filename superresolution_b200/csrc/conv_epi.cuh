@@ -21,9 +21,12 @@ __device__ __forceinline__ float gelu_fast_grad(float x) {
 // bias + activation + residuals on one 32-channel slice of one pixel (all indices compile-time after unrolling)
 // sbias: the layer's bias staged in shared memory by the kernel prologue (zeros when the layer has none); a global
 // __ldg per unit sat on the epilogue's critical path (~500 cycles per 128 x 32 block).
+// g_row (TRAIN) / r1_row: this thread's 64-byte row of the saved GELU pre-activation / of the bf16 res1 operand, already
+// staged in shared memory by TMA (16-byte chunk j at row + ((j ^ sw) << 4)); null = read it from global memory here
 template <bool TRAIN = false>
 __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a, size_t pix, int cb, int b,
-                                              const float* sbias = nullptr) {
+                                              const float* sbias = nullptr, const uint8_t* g_row = nullptr,
+                                              const uint8_t* r1_row = nullptr, uint32_t g_sw = 0) {
     if (sbias) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
@@ -59,7 +62,7 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
         const uint4* gp = (const uint4*)(a.gelu_grad_of + pix * a.gelu_grad_pitch + cb);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const uint4 rr = __ldg(gp + j);
+            const uint4 rr = g_row ? *(const uint4*)(g_row + ((j ^ g_sw) << 4)) : __ldg(gp + j);
             const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
@@ -85,7 +88,7 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
             const uint4* rp = (const uint4*)((const bf16*)a.res1 + pix * a.res1_pitch + cb);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const uint4 rr = rp[j];
+                const uint4 rr = r1_row ? *(const uint4*)(r1_row + ((j ^ g_sw) << 4)) : rp[j];
                 const __nv_bfloat162* h = (const __nv_bfloat162*)&rr;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {

@@ -65,7 +65,7 @@ struct ConvCfg {
     // epilogue-bound and have 3 n-blocks per m-tile: three groups; the others keep two (their patches need the smem).
     static constexpr int EG = (N_TILE % 96 == 0) ? 3 : 2;
     static constexpr int THREADS = 128 + EG * 128;
-    static constexpr int STAGING = EG * 2 * 8192;  // per group: two 128 x 32 bf16 staging blocks
+    // output staging: ConvLaunch::nstg blocks of 128 x 32 bf16 per epilogue group (2; 3 when an operand is staged in them)
     static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
     static_assert(N_TILE % 32 == 0 && N_TILE >= 32 && N_TILE <= 256, "N_TILE");
     static_assert(W_BYTES % 1024 == 0, "weight tile must keep 1024B alignment");
@@ -85,6 +85,9 @@ struct ConvLaunch {
     int wslots;     // weight slots (ring depth for 3x3, resident tile count for 1x1)
     int reuse;      // patch chunks stay resident across the N tiles of one spatial tile
     int tma_store;  // bf16 output through smem staging + TMA store
+    int stage_g;    // tiles of one epilogue operand arrive by TMA in the output staging blocks (tmG):
+                    // 1 = gelu_grad_of (TRAIN), 2 = res1 (bf16), 0 = none
+    int nstg;       // staging blocks per epilogue group: 2, or 3 when stage_g
     int colsum_bytes;  // shared-memory bytes of the per-tile channel-sum scratch (0 unless a.colsum)
     long long* dbg;    // development aid (-DSRB_CONV_PHASES): [grid][16] cycle totals of the MMA / epilogue warps
 };
@@ -107,16 +110,18 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
 template <class Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-               const __grid_constant__ CUtensorMap tmO, const ConvArgs a, const ConvLaunch t) {
+               const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmG, const ConvArgs a,
+               const ConvLaunch t) {
     constexpr int N_TILE = Cfg::N_TILE, MT = Cfg::MT, TAPS = Cfg::TAPS, AS = Cfg::ACC_STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* patch0 = smem;
     uint8_t* wt0 = patch0 + t.ps * Cfg::PATCH_STRIDE;
     uint8_t* stg0 = wt0 + t.wslots * Cfg::W_BYTES;
-    float* scol = (float*)(stg0 + Cfg::STAGING);  // only carved when a.colsum (t.colsum_bytes)
-    float* sbias = (float*)(stg0 + Cfg::STAGING + t.colsum_bytes);
-    uint64_t* bars = (uint64_t*)(stg0 + Cfg::STAGING + t.colsum_bytes + kBiasBytes);
+    const int staging = Cfg::EG * t.nstg * kStageBytes;
+    float* scol = (float*)(stg0 + staging);  // only carved when a.colsum (t.colsum_bytes)
+    float* sbias = (float*)(stg0 + staging + t.colsum_bytes);
+    uint64_t* bars = (uint64_t*)(stg0 + staging + t.colsum_bytes + kBiasBytes);
     uint64_t* full_p = bars;                 // [kMaxPS]
     uint64_t* empty_p = full_p + kMaxPS;     // [kMaxPS]
     uint64_t* full_w = empty_p + kMaxPS;     // [W_RING]  (3x3: ring; 1x1: full_w[0] = all resident tiles landed)
@@ -124,6 +129,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t* acc_full = empty_w + Cfg::W_RING;  // [2]
     uint64_t* acc_empty = acc_full + 2;          // [2]
     uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
+    uint64_t* g_bar = acc_empty + 3;             // [EG][3] staged epilogue operand landed (TRAIN)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -131,6 +137,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < kMaxPS; ++i) { mbar_init(&full_p[i], 1); mbar_init(&empty_p[i], 1); }
         for (int i = 0; i < Cfg::W_RING; ++i) { mbar_init(&full_w[i], 1); mbar_init(&empty_w[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], Cfg::EG * 128); }
+        for (int i = 0; i < Cfg::EG * 3; ++i) mbar_init(&g_bar[i], 1);
         fence_barrier_init();
     }
     if (a.dyn_weights) pdl_wait();  // weights / bias written by the preceding kernel: no prologue overlap
@@ -285,11 +292,27 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int q = warp & 3;
         const int row = q * 32 + lane;  // M row inside the 128-row UMMA tile
         const bool issuer = (q == 0 && lane == 0);
-        uint8_t* stg = stg0 + eg * 2 * kStageBytes;
+        uint8_t* stg = stg0 + eg * t.nstg * kStageBytes;
         uint32_t it_a = 0, it_s = 0;
 #ifdef SRB_CONV_PHASES
         long long ph_full = 0, ph_e0 = clock64(), ph_c, ph_ld = 0, ph_math = 0, ph_b1 = 0, ph_st = 0, ph_b2 = 0;
 #endif
+        // TRAIN, GELU' epilogue: the saved pre-activation tile of a unit (128 pixels x 32 channels) is fetched by TMA
+        // into the staging block the unit's output will leave from, one unit ahead; each thread then multiplies its
+        // 64-byte row in place.  Read by the threads themselves (LDG or cp.async: 16 bytes per lane at a 384-byte
+        // stride = one L1 wavefront per lane) those operands cost ~1.4k cycles of LSU time per unit whether or not their
+        // latency was hidden; the TMA tile costs none.
+        const bool stage_g = t.stage_g != 0;
+        const uint32_t sw_row = (row >> 1) & 3;
+        uint64_t* gb = g_bar + eg * 3;
+        auto issue_g = [&](int st_, int nt_, int u_, uint32_t buf) {  // issuer thread only
+            const int b_ = st_ / per_img, r_ = st_ % per_img;
+            const int ty_ = r_ / t.tiles_x, tx_ = r_ % t.tiles_x;
+            const int mt_ = u_ / (N_TILE / 32), c0_ = (u_ % (N_TILE / 32)) * 32;
+            mbar_arrive_expect_tx(&gb[buf], kStageBytes);
+            tma_load_4d(stg + buf * kStageBytes, &tmG, &gb[buf], nt_ * N_TILE + c0_, tx_ * Cfg::TW + 8 * mt_, ty_ * Cfg::TH, b_);
+        };
+        if (stage_g && issuer && (int)blockIdx.x < t.n_spatial) issue_g(blockIdx.x, 0, eg, 0);
         for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
             const int b = st / per_img, r = st % per_img;
             const int ty = r / t.tiles_x, tx = r % t.tiles_x;
@@ -318,8 +341,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
+                    const uint8_t* g_row = nullptr;  // this thread's row of the staged operand
+                    if (stage_g) {
+                        // three blocks in rotation: the block the next unit's operand goes to was last stored from two
+                        // units ago (waiting for the store issued a moment ago would expose its shared-memory read)
+                        if (issuer) {
+                            bulk_wait_group_read<1>();
+                            int st2 = st, nt2 = nt, u2 = u + Cfg::EG;
+                            bool more = true;
+                            if (u2 >= Cfg::UNITS) {
+                                u2 = eg;
+                                if (++nt2 >= t.n_tiles_n) { nt2 = 0; st2 += gridDim.x; more = st2 < t.n_spatial; }
+                            }
+                            if (more) issue_g(st2, nt2, u2, (it_s + 1) % 3);
+                        }
+                        mbar_wait(&gb[it_s % 3], (it_s / 3) & 1);  // this unit's tile (requested one unit ago) has landed
+                        g_row = stg + (it_s % 3) * kStageBytes + row * 64;
+                    }
                     PH_BEGIN();
-                    epilogue_math<Cfg::TRAIN>(v, a, pix, cb, b, sbias);
+                    epilogue_math<Cfg::TRAIN>(v, a, pix, cb, b, sbias, (Cfg::TRAIN && t.stage_g == 1) ? g_row : nullptr,
+                                              t.stage_g == 2 ? g_row : nullptr, sw_row);
                     PH_END(ph_math);
                     if (a.out32 && valid) {
                         float4* op = (float4*)(a.out32 + pix * a.out32_pitch + cb);
@@ -329,10 +370,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     if (a.out) {
                         if (t.tma_store) {
                             // stage the 128 x 32 bf16 block (64-byte rows, SWIZZLE_64B) and hand it to TMA
-                            uint8_t* sb = stg + (it_s & 1) * kStageBytes;
+                            uint8_t* sb = stg + (stage_g ? it_s % 3 : (it_s & 1)) * kStageBytes;
                             PH_BEGIN();
-                            if (issuer) bulk_wait_group_read<1>();  // the store that last used this buffer has read it
-                            named_bar_sync(2 + eg, 128);
+                            if (!stage_g) {  // (the staged-operand path has waited above)
+                                if (issuer) bulk_wait_group_read<1>();  // the store that last used this buffer has read it
+                                named_bar_sync(2 + eg, 128);
+                            }
                             PH_END(ph_b1);
                             PH_BEGIN();
                             const uint32_t sw = (row >> 1) & 3;
@@ -501,7 +544,27 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
         set_error("conv_tc: colsum needs Cout == N tile (Cout=%d)", a.Cout);
         return SRB_E_ARG;
     }
-    const int fixed = t.wslots * Cfg::W_BYTES + Cfg::STAGING + t.colsum_bytes + kBiasBytes + kBarrierBytes + 1024;
+    static const bool use_tma_store = env_flag("SRB_TMA_STORE", true);
+    static const bool use_pdl = env_flag("SRB_PDL", true);
+    static const bool use_stage = env_flag("SRB_STAGE_OPERAND", true);
+    t.tma_store = (a.out && !a.pixel_shuffle && use_tma_store && (((uintptr_t)a.out & 15) == 0) &&
+                   (a.out_pitch % 8 == 0)) ? 1 : 0;
+    // one per-pixel epilogue operand can ride the staging blocks (TMA tile in, multiply / add in place, TMA tile out)
+    const bf16* st_op = nullptr;
+    int st_pitch = 0;
+    t.stage_g = 0;
+    if (t.tma_store && use_stage) {
+        if (Cfg::TRAIN && a.gelu_grad_of) { st_op = a.gelu_grad_of; st_pitch = a.gelu_grad_pitch; t.stage_g = 1; }
+        else if (a.res1 && !a.res1_f32) { st_op = (const bf16*)a.res1; st_pitch = a.res1_pitch; t.stage_g = 2; }
+        if (st_op && ((((uintptr_t)st_op & 15) != 0) || st_pitch % 8 != 0)) t.stage_g = 0;
+    }
+    t.nstg = t.stage_g ? 3 : 2;
+    int fixed = t.wslots * Cfg::W_BYTES + Cfg::EG * t.nstg * kStageBytes + t.colsum_bytes + kBiasBytes + kBarrierBytes + 1024;
+    if (t.stage_g && (kSmemLimit - fixed) / Cfg::PATCH_STRIDE < (t.nchunks < 2 ? 2 : t.nchunks)) {
+        t.stage_g = 0;  // the third block would cost a patch stage the layer needs
+        t.nstg = 2;
+        fixed -= Cfg::EG * kStageBytes;
+    }
     t.ps = (kSmemLimit - fixed) / Cfg::PATCH_STRIDE;
     if (t.ps > kMaxPS) t.ps = kMaxPS;
     if (t.ps < 2) {
@@ -509,10 +572,6 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
         return SRB_E_SHAPE;
     }
     t.reuse = (t.n_tiles_n > 1 && t.nchunks <= t.ps) ? 1 : 0;
-    static const bool use_tma_store = env_flag("SRB_TMA_STORE", true);
-    static const bool use_pdl = env_flag("SRB_PDL", true);
-    t.tma_store = (a.out && !a.pixel_shuffle && use_tma_store && (((uintptr_t)a.out & 15) == 0) &&
-                   (a.out_pitch % 8 == 0)) ? 1 : 0;
     const int smem = t.ps * Cfg::PATCH_STRIDE + fixed;
     t.dbg = g_fa_dbg;
 
@@ -539,6 +598,13 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     } else {
         tmO = tmA;  // unused
     }
+    CUtensorMap tmG = tmA;  // unused unless an epilogue operand is staged
+    if (t.stage_g) {
+        cuuint64_t dims[4] = {(cuuint64_t)a.Cout, (cuuint64_t)a.W, (cuuint64_t)a.H, (cuuint64_t)a.B};
+        cuuint64_t str[3] = {(cuuint64_t)st_pitch * 2, (cuuint64_t)a.W * st_pitch * 2, (cuuint64_t)a.H * a.W * st_pitch * 2};
+        cuuint32_t box[4] = {32, 8, 16, 1};
+        SRB_TRY(encode_bf16_map(&tmG, st_op, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_64B));
+    }
     static std::atomic<unsigned long long> smem_set{0};  // per template instantiation, one bit per device
     SRB_TRY(opt_in_dynamic_smem(conv_tc_kernel<Cfg>, kSmemLimit, smem_set));
     cudaLaunchConfig_t cfg;
@@ -552,7 +618,7 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = use_pdl ? 1 : 0;
-    SRB_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<Cfg>, tmA, tmW, tmO, a, t));
+    SRB_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<Cfg>, tmA, tmW, tmO, tmG, a, t));
     return SRB_OK;
 }
 
