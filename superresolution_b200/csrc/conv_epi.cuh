@@ -26,8 +26,10 @@ __device__ __forceinline__ float gelu_fast_grad(float x) {
 template <bool TRAIN = false>
 __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a, size_t pix, int cb, int b,
                                               const float* sbias = nullptr, const uint8_t* g_row = nullptr,
-                                              const uint8_t* r1_row = nullptr, uint32_t g_sw = 0) {
-    if (sbias) {
+                                              const uint8_t* r1_row = nullptr, uint32_t g_sw = 0, bool pre_done = false) {
+    // pre_done (TRAIN): the caller has added the bias and sent the pre-activation out already (TMA store)
+    if (TRAIN && pre_done) {
+    } else if (sbias) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
             const float4 bb = *(const float4*)(sbias + cb + j);
@@ -40,7 +42,7 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const ConvArgs& a,
             v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
         }
     }
-    if (TRAIN && a.pre_out) {
+    if (TRAIN && a.pre_out && !pre_done) {
         uint4* pp = (uint4*)(a.pre_out + pix * a.pre_pitch + cb);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {

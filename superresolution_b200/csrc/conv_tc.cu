@@ -86,7 +86,8 @@ struct ConvLaunch {
     int reuse;      // patch chunks stay resident across the N tiles of one spatial tile
     int tma_store;  // bf16 output through smem staging + TMA store
     int stage_g;    // tiles of one epilogue operand arrive by TMA in the output staging blocks (tmG):
-                    // 1 = gelu_grad_of (TRAIN), 2 = res1 (bf16), 0 = none
+                    // 1 = gelu_grad_of (TRAIN), 2 = res1 (bf16), 0 = none;
+                    // 3 (TRAIN) = no operand, but pre_out LEAVES through the staging blocks as a second TMA store (tmG)
     int nstg;       // staging blocks per epilogue group: 2, or 3 when stage_g
     int colsum_bytes;  // shared-memory bytes of the per-tile channel-sum scratch (0 unless a.colsum)
     long long* dbg;    // development aid (-DSRB_CONV_PHASES): [grid][16] cycle totals of the MMA / epilogue warps
@@ -302,7 +303,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // 64-byte row in place.  Read by the threads themselves (LDG or cp.async: 16 bytes per lane at a 384-byte
         // stride = one L1 wavefront per lane) those operands cost ~1.4k cycles of LSU time per unit whether or not their
         // latency was hidden; the TMA tile costs none.
-        const bool stage_g = t.stage_g != 0;
+        const bool stage_g = t.stage_g == 1 || t.stage_g == 2;
+        const bool pre_tma = Cfg::TRAIN && t.stage_g == 3;
         const uint32_t sw_row = (row >> 1) & 3;
         uint64_t* gb = g_bar + eg * 3;
         auto issue_g = [&](int st_, int nt_, int u_, uint32_t buf) {  // issuer thread only
@@ -313,6 +315,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tma_load_4d(stg + buf * kStageBytes, &tmG, &gb[buf], nt_ * N_TILE + c0_, tx_ * Cfg::TW + 8 * mt_, ty_ * Cfg::TH, b_);
         };
         if (stage_g && issuer && (int)blockIdx.x < t.n_spatial) issue_g(blockIdx.x, 0, eg, 0);
+        // stores of one staging block: wait for the store `depth` stores back to have read it, fill, hand to TMA
+        auto stage_store = [&](const CUtensorMap* tm, const float (&vv)[32], uint8_t* sb, int cb_, int x_, int y_, int b_) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                uint4 o;
+                __nv_bfloat162* h = (__nv_bfloat162*)&o;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(vv[8 * j + 2 * k], vv[8 * j + 2 * k + 1]);
+                *(uint4*)(sb + row * 64 + ((j ^ sw_row) << 4)) = o;
+            }
+            fence_proxy_async_smem();
+            named_bar_sync(2 + eg, 128);
+            if (issuer) {
+                tma_store_4d(tm, sb, cb_, x_, y_, b_);
+                bulk_commit_group();
+            }
+        };
         for (int st = blockIdx.x; st < t.n_spatial; st += gridDim.x) {
             const int b = st / per_img, r = st % per_img;
             const int ty = r / t.tiles_x, tx = r % t.tiles_x;
@@ -358,9 +377,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         mbar_wait(&gb[it_s % 3], (it_s / 3) & 1);  // this unit's tile (requested one unit ago) has landed
                         g_row = stg + (it_s % 3) * kStageBytes + row * 64;
                     }
+                    if (Cfg::TRAIN && pre_tma) {
+                        // the bf16 pre-activation (acc + bias) leaves as a TMA tile of its own: blocks rotate per STORE, the
+                        // block of store s was last read by store s - 3
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            const float4 bb = *(const float4*)(sbias + cb + j);
+                            v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+                        }
+                        if (issuer) bulk_wait_group_read<2>();
+                        named_bar_sync(2 + eg, 128);
+                        stage_store(&tmG, v, stg + (it_s % 3) * kStageBytes, cb, tx * Cfg::TW + 8 * mt, ty * Cfg::TH, b);
+                        ++it_s;
+                    }
                     PH_BEGIN();
                     epilogue_math<Cfg::TRAIN>(v, a, pix, cb, b, sbias, (Cfg::TRAIN && t.stage_g == 1) ? g_row : nullptr,
-                                              t.stage_g == 2 ? g_row : nullptr, sw_row);
+                                              t.stage_g == 2 ? g_row : nullptr, sw_row, Cfg::TRAIN && pre_tma);
                     PH_END(ph_math);
                     if (a.out32 && valid) {
                         float4* op = (float4*)(a.out32 + pix * a.out32_pitch + cb);
@@ -370,10 +402,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     if (a.out) {
                         if (t.tma_store) {
                             // stage the 128 x 32 bf16 block (64-byte rows, SWIZZLE_64B) and hand it to TMA
-                            uint8_t* sb = stg + (stage_g ? it_s % 3 : (it_s & 1)) * kStageBytes;
+                            uint8_t* sb = stg + ((stage_g || pre_tma) ? it_s % 3 : (it_s & 1)) * kStageBytes;
                             PH_BEGIN();
                             if (!stage_g) {  // (the staged-operand path has waited above)
-                                if (issuer) bulk_wait_group_read<1>();  // the store that last used this buffer has read it
+                                if (issuer) {  // the store that last used this buffer has read it
+                                    if (pre_tma) bulk_wait_group_read<2>(); else bulk_wait_group_read<1>();
+                                }
                                 named_bar_sync(2 + eg, 128);
                             }
                             PH_END(ph_b1);
@@ -556,6 +590,7 @@ static int launch_cfg(const ConvArgs& a, cudaStream_t stream) {
     if (t.tma_store && use_stage) {
         if (Cfg::TRAIN && a.gelu_grad_of) { st_op = a.gelu_grad_of; st_pitch = a.gelu_grad_pitch; t.stage_g = 1; }
         else if (a.res1 && !a.res1_f32) { st_op = (const bf16*)a.res1; st_pitch = a.res1_pitch; t.stage_g = 2; }
+        else if (Cfg::TRAIN && a.pre_out) { st_op = a.pre_out; st_pitch = a.pre_pitch; t.stage_g = 3; }
         if (st_op && ((((uintptr_t)st_op & 15) != 0) || st_pitch % 8 != 0)) t.stage_g = 0;
     }
     t.nstg = t.stage_g ? 3 : 2;
