@@ -308,9 +308,10 @@ class HybridSuperResolutionModel(nn.Module):
             cache[k] = ws
         return ws
 
-    def run(self, x, stage_mask=3, out_dtype=torch.float32):
+    def run(self, x, stage_mask=3, out_dtype=torch.float32, out=None):
         """x: [B,1,H,W] float32 in [0,1] (or uint16 counts, divided by 65535 like src/dataset.py:34).
-        stage_mask 1: RRDBNet only -> [B,1,2H,2W]; 2: HAT only -> [B,1,2H,2W]; 3: full model -> [B,1,4H,4W]."""
+        stage_mask 1: RRDBNet only -> [B,1,2H,2W]; 2: HAT only -> [B,1,2H,2W]; 3: full model -> [B,1,4H,4W].
+        out: optional preallocated result tensor (contiguous, right shape / dtype / device) instead of a fresh one."""
         lib = L.lib()
         if x.dim() != 4 or x.shape[1] != 1:
             raise ValueError(f'expected [B,1,H,W], got {tuple(x.shape)}')
@@ -330,8 +331,15 @@ class HybridSuperResolutionModel(nn.Module):
         with torch.cuda.device(x.device):
             packed = self.pack_weights()
             ws = self._workspace(B, H, W, x.device)
-            y = torch.empty(B, 1, scale * H, scale * W, dtype=torch.uint16 if yd == L.SRB_U16 else torch.float32,
-                            device=x.device)
+            ydt = torch.uint16 if yd == L.SRB_U16 else torch.float32
+            if out is None:
+                y = torch.empty(B, 1, scale * H, scale * W, dtype=ydt, device=x.device)
+            else:
+                if (tuple(out.shape) != (B, 1, scale * H, scale * W) or out.dtype != ydt or out.device != x.device
+                        or not out.is_contiguous()):
+                    raise ValueError('run(out=): expected a contiguous %s tensor of shape %s on %s'
+                                     % (ydt, (B, 1, scale * H, scale * W), x.device))
+                y = out
             L.check(lib.srb_forward(L.ptr(x), xd, L.ptr(y), yd, B, H, W, L.ptr(packed), L.ptr(ws), ws.numel(),
                                     self._smoothing, stage_mask, L.current_stream()), 'forward')
         return y
