@@ -144,7 +144,7 @@ __device__ __forceinline__ void probs(const WinArgs& a, const bf16* sT, const ui
 
 constexpr int FWD_SMEM = 64 * RP * 2 + 64 * 4 + 64;
 
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(32, 20)  // 94 registers: 20 single-warp CTAs per SM (the kernel is latency-bound)
 win_attn_fwd_kernel(const WinArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
     bf16* sT = (bf16*)smem;
@@ -330,7 +330,7 @@ int win_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, in
     WinArgs a;
     a.qkv = qkv; a.bias = bias; a.index = nullptr; a.dout = nullptr; a.out = out; a.dtable = nullptr;
     a.B = B; a.H = H; a.W = W; a.shift = shift; a.nwin = B * (H / 8) * (W / 8);
-    const int items = a.nwin * 6, cap = num_sms() * 16;
+    const int items = a.nwin * 6, cap = num_sms() * 20;
     win_attn_fwd_kernel<<<items < cap ? items : cap, 32, FWD_SMEM, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
