@@ -100,7 +100,7 @@ def config3(model, dev, rank, world, sampler_cls, gpu_index, size=4096):
                       'after 1 warm-up; max over ranks', 'clocks': clocks}
 
 
-def config4(dev, rank, world, sampler_cls, gpu_index, batch=32, micro=16, steps=2):
+def config4(dev, rank, world, sampler_cls, gpu_index, batch=32, micro=16, steps=3):
     """Hybrid training step (scripts/Modello_supporto.py:125-141 on libsrb) with the gradient all-reduce over the ranks."""
     import torch.distributed as dist
     from superresolution_b200.architecture import HybridSuperResolutionModel
@@ -143,7 +143,8 @@ def config4(dev, rank, world, sampler_cls, gpu_index, batch=32, micro=16, steps=
             ar_evs.append((e0, e1))
         return loss
 
-    step(False)
+    step(False)  # two untimed steps: the second one runs with the caching allocator already grown (at 8 ranks the
+    step(False)  # first timed step otherwise waits in the all-reduce for the rank that is still allocating)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
