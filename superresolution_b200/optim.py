@@ -10,8 +10,11 @@ stands, works with ``CosineAnnealingLR`` (reads ``param_groups[0]['lr']`` every 
 form.  Parameters, gradients and both moments are flat fp32 buffers; every ``p.data`` / ``p.grad`` is a view into
 them, and ``zero_grad`` zeroes the flat gradient instead of dropping the views.
 
-The backward pass through the model is NOT part of libsrb yet: this file is the part of row a12 that
-exists — gradients produced by any autograd graph over the parameters (e.g. the loss kernels) flow through it.
+The gradients come from the libsrb backward of both stages (training.py / training_hat.py) or from any other autograd
+graph over the parameters; ``state_dict()`` carries the step count and both moment buffers (flat), so a run resumes
+where ``torch.optim.AdamW`` would.  One deviation from ``GradScaler``: a fused step that the kernel skips because of an
+inf/nan gradient still advances the bias-correction count (the skip is decided on the device, without a host
+synchronisation); ``settle_skipped_step()`` reads the flag (one sync) and takes the count back.
 """
 import torch
 import torch.distributed as dist
@@ -123,6 +126,32 @@ class FusedAdamW(torch.optim.Optimizer):
         # packed-weight cache, autograd's saved-tensor checks) see the update
         torch.autograd.graph.increment_version(g['params'])
         return loss
+
+    def settle_skipped_step(self):
+        """GradScaler parity for the bias correction: if the last fused step was skipped (inf/nan gradient), take the
+        step count back.  Reads the device flag (one host synchronisation); returns True when a step was skipped."""
+        skipped = bool(self._info[1].item() != 0.0)
+        if skipped:
+            self._step = max(0, self._step - 1)
+            self._info[1].zero_()  # settled: a second call does not take another step back
+        return skipped
+
+    def state_dict(self):
+        """torch layout ('state' / 'param_groups') with ONE state entry: the flat moment buffers and the step count."""
+        sd = super().state_dict()
+        sd['state'] = {0: {'step': self._step, 'exp_avg': self.exp_avg.clone(), 'exp_avg_sq': self.exp_avg_sq.clone()}}
+        return sd
+
+    def load_state_dict(self, state_dict):
+        st = state_dict['state'][0] if 0 in state_dict['state'] else state_dict['state']['0']
+        if st['exp_avg'].numel() != self.numel or st['exp_avg_sq'].numel() != self.numel:
+            raise ValueError('FusedAdamW.load_state_dict: moment buffers of %d elements expected' % self.numel)
+        for k, v in state_dict['param_groups'][0].items():
+            if k != 'params':
+                self.param_groups[0][k] = v
+        self._step = int(st['step'])
+        self.exp_avg.copy_(st['exp_avg'])
+        self.exp_avg_sq.copy_(st['exp_avg_sq'])
 
     def found_inf(self):
         """1.0 if the last fused step saw an inf/nan gradient and was skipped (0-dim CUDA tensor; feed to the scaler)."""

@@ -167,3 +167,29 @@ def test_packed_weight_cache_lives_only_inside_its_scope(cuda):
         assert torch.equal(d1, ops.pack_conv_weight_dgrad(w))
     with ops.weight_pack_cache():
         assert ops.packed_weight(p, w) is not c1  # a new scope (= a new step) packs again
+
+
+def test_state_dict_round_trip_and_skipped_step_count(cuda):
+    """state_dict carries step + both moments (a resumed run continues like torch.optim.AdamW would); a skipped fused step
+    can be taken back out of the bias-correction count."""
+    from superresolution_b200.optim import FusedAdamW
+    a, b = _make(cuda, 4), _make(cuda, 4)
+    oa, ob = FusedAdamW(a, lr=2e-3, weight_decay=0.01), FusedAdamW(b, lr=1e-4, weight_decay=0.0)
+    for step in range(3):
+        for q, g in zip(a, _grads(40 + step)):
+            q.grad.copy_(g.to(cuda))
+        oa.step()
+    sd = oa.state_dict()
+    assert sd['state'][0]['step'] == 3 and sd['param_groups'][0]['lr'] == 2e-3
+    ob.load_state_dict(sd)
+    ob.flat_param.copy_(oa.flat_param)
+    for o, ps in ((oa, a), (ob, b)):
+        for q, g in zip(ps, _grads(50)):
+            q.grad.copy_(g.to(cuda))
+        o.step()
+    assert torch.equal(oa.flat_param, ob.flat_param) and torch.equal(oa.exp_avg_sq, ob.exp_avg_sq)
+    # skipped step: the count is taken back, so the next update uses the bias correction of step 5, not 6
+    a[0].grad[0, 0] = float('inf')
+    oa.step(grad_scale=1.0, max_norm=1.0)
+    assert oa.settle_skipped_step() is True and oa._step == 4
+    assert oa.settle_skipped_step() is False and oa._step == 4  # settled once
