@@ -1,7 +1,8 @@
 // Halo-blend stitch for tiled whole-field inference (BASELINE config 3).  The reference only iterates
 // pre-cut patches (scripts/Modello_5.py:72-85), so the tile/blend semantics are defined here and restated in
 // oracle/tiling.py: every tile output is weighted by a separable ramp w(i) = min(i+1, n-i, ov)/ov, accumulated into
-// fp32 (sum w*y, sum w) planes, then normalised, clipped and cast like scripts/Modello_5.py:29-33.
+// fp32 (sum w*y, sum w) planes in a fixed order (deterministic), then normalised, clipped and cast like
+// scripts/Modello_5.py:29-33.
 // Tiles are independent: a rank blends only the rows of its band -> no collective on the data path.
 #include "common.h"
 #include "ops.h"
@@ -13,22 +14,24 @@ __device__ __forceinline__ float ramp(int i, int n, int ov) {
     return (float)m / (float)ov;
 }
 
+// ONE tile per launch: its pixels are distinct output pixels, so the accumulation is a plain read-add-write, and the
+// order in which overlapping tiles reach a pixel is the launch order (the stream's), i.e. the plan's raster order:
+// the stitched frame is bit-reproducible run to run.  (One launch over a whole batch of tiles needed float atomics,
+// whose order varies.)
 __global__ void __launch_bounds__(256)
-blend_tiles_kernel(const float* __restrict__ tiles, const int* __restrict__ oy, const int* __restrict__ ox, int T,
-                   int th, int tw, int ov, float* __restrict__ acc, float* __restrict__ wsum, int FH, int FW,
-                   int row0, int row1) {
-    const size_t per = (size_t)th * tw;
-    const size_t n = per * T;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const int t = (int)(i / per);
-        const int r = (int)(i % per);
+blend_tile_kernel(const float* __restrict__ tile, const int* __restrict__ oy, const int* __restrict__ ox, int t,
+                  int th, int tw, int ov, float* __restrict__ acc, float* __restrict__ wsum, int FH, int FW,
+                  int row0, int row1) {
+    const int n = th * tw;
+    const int y0 = oy[t], x0 = ox[t];
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x) {
         const int ty = r / tw, tx = r % tw;
-        const int y = oy[t] + ty, x = ox[t] + tx;
+        const int y = y0 + ty, x = x0 + tx;
         if (y < row0 || y >= row1 || y >= FH || x >= FW || x < 0) continue;
         const float w = ramp(ty, th, ov) * ramp(tx, tw, ov);
         const size_t o = (size_t)(y - row0) * FW + x;
-        atomicAdd(acc + o, w * tiles[i]);
-        atomicAdd(wsum + o, w);
+        acc[o] = fmaf(w, tile[r], acc[o]);
+        wsum[o] += w;
     }
 }
 
@@ -46,11 +49,14 @@ blend_finalize_kernel(const float* __restrict__ acc, const float* __restrict__ w
 int blend_tiles(const float* tiles, const int* oy, const int* ox, int T, int th, int tw, int ov, float* acc,
                 float* wsum, int FH, int FW, int row0, int row1, cudaStream_t s) {
     if (ov <= 0 || ov > th || ov > tw) { set_error("blend_tiles: bad overlap %d", ov); return SRB_E_ARG; }
-    const size_t n = (size_t)T * th * tw;
-    int grid = (int)((n + 255) / 256);
+    const size_t per = (size_t)th * tw;
+    if (per > 0x7fffffff) { set_error("blend_tiles: tile too large"); return SRB_E_SHAPE; }
+    int grid = (int)((per + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;
-    blend_tiles_kernel<<<grid, 256, 0, s>>>(tiles, oy, ox, T, th, tw, ov, acc, wsum, FH, FW, row0, row1);
-    SRB_CUDA(cudaGetLastError());
+    for (int t = 0; t < T; ++t) {
+        blend_tile_kernel<<<grid, 256, 0, s>>>(tiles + (size_t)t * per, oy, ox, t, th, tw, ov, acc, wsum, FH, FW, row0, row1);
+        SRB_CUDA(cudaGetLastError());
+    }
     return SRB_OK;
 }
 

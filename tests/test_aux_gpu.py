@@ -164,6 +164,10 @@ def test_tiled_frame_matches_oracle_blend(cuda):
                  for (y, x) in origins]
     ref = otil.blend(tiles, [(scale * y, scale * x) for (y, x) in origins], 320, 224, scale * (tile - stride))
     assert np.abs(out.cpu().numpy() - ref).max() < 1e-5
+    # overlapping tiles reach a pixel in the plan's raster order (one tile per blend launch, no atomics): bit-reproducible
+    for batch in (4, 3):
+        again, _ = tiling.infer_frame(m, frame, tile, stride, batch=batch, out_dtype=torch.float32)
+        assert torch.equal(again, out)
     bands = [tiling.infer_frame(m, frame, tile, stride, batch=4, rank=r, world=2, out_dtype=torch.float32,
                                 seams='recompute')[0]
              for r in range(2)]
