@@ -49,7 +49,7 @@ constexpr int WT_TILE_ATOM = WT_TW * WT_TH * 128;    //   3x3 chunk of the un-sh
 constexpr int WT_NPATCH_BYTES = WT_PW * WT_PH * 64;  // haloed patch of the shifted operand: 32-channel rows of 64 bytes
 constexpr int WT_NPATCH_ATOM = (WT_NPATCH_BYTES + 1023) / 1024 * 1024;
 constexpr int WT_ONES_BYTES = 4096;
-constexpr int WT_MAX_STAGES = 4;
+constexpr int WT_MAX_STAGES = 6;
 constexpr int WT_SMEM_LIMIT = 227 * 1024;
 enum { WT_L = 0, WT_C1 = 1, WT_C2 = 2 };
 
