@@ -250,6 +250,8 @@ int srb_overlap_attention_bwd(const void* qkv, const float* bias, const int* ind
                               float* dtable, void* scratch, int B, int H, int W, void* stream);
 /* srb_channel_attention      ChannelAttention of CAB: out = y * sigmoid(W2 relu(W1 mean_px(y) + b1) + b2), y bf16 [B,HW,96],
  *                            w1 fp32 [3,96], w2 fp32 [96,3]; saves pooled [B,96], hid [B,3], scale [B,96] for the backward.
+ *                            out may be NULL: only the statistics are produced (the caller applies scale[b][c] in a later
+ *                            epilogue, e.g. res2_cs of srb_conv_nhwc_bf16_train).
  * srb_channel_attention_bwd  dy (direct + pooled term) and dw1/db1/dw2/db2 (+= when accumulate); dpooled [B,96] scratch out.
  *                            g_scale multiplies the incoming gradient g (HAB's conv_scale 0.01 without a pass over g).
  *                            scratch: srb_channel_attention_scratch_bytes(B, HW).  Deterministic. */

@@ -339,7 +339,7 @@ int srb_overlap_attention_bwd(const void* qkv, const float* bias, const int* ind
 size_t srb_channel_attention_scratch_bytes(int B, int HW) { return chan_attn_scratch_bytes(B, HW); }
 int srb_channel_attention(const void* y, const float* w1, const float* b1, const float* w2, const float* b2, void* out,
                           float* pooled, float* hid, float* scale, void* scratch, int B, int HW, void* stream) {
-    if (!y || !w1 || !b1 || !w2 || !b2 || !out || !pooled || !hid || !scale || !scratch || B <= 0 || HW <= 0) {
+    if (!y || !w1 || !b1 || !w2 || !b2 || !pooled || !hid || !scale || !scratch || B <= 0 || HW <= 0) {  // out may be NULL
         set_error("channel_attention: bad args");
         return SRB_E_ARG;
     }

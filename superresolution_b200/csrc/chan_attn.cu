@@ -199,8 +199,10 @@ int chan_attn_fwd(const bf16* y, const float* w1, const float* b1, const float* 
     SRB_CUDA(cudaGetLastError());
     ca_fwd_kernel<<<B, CA_C, 0, st>>>((const float*)scratch, nblk, 1.f / (float)HW, w1, b1, w2, b2, pooled, hid, s);
     SRB_CUDA(cudaGetLastError());
-    ca_scale_kernel<<<ca_grid((size_t)B * HW * 12), 256, 0, st>>>(out, y, s, 1.f, nullptr, 0.f, HW, (size_t)B * HW);
-    SRB_CUDA(cudaGetLastError());
+    if (out) {  // null: the caller folds s[b][c] into a later epilogue (res2_cs of the proj conv) instead of a pass over y
+        ca_scale_kernel<<<ca_grid((size_t)B * HW * 12), 256, 0, st>>>(out, y, s, 1.f, nullptr, 0.f, HW, (size_t)B * HW);
+        SRB_CUDA(cudaGetLastError());
+    }
     return SRB_OK;
 }
 

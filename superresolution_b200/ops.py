@@ -341,11 +341,12 @@ def overlap_attention_bwd(qkv, bias, index, dout, dtable=None):
     return dqkv, dtable
 
 
-def channel_attention(y, w1, b1, w2, b2):
-    """y bf16 [B,HW,96]; w1 [3,96(,1,1)], w2 [96,3(,1,1)] fp32.  Returns (out bf16, saved = (pooled, hid, scale))."""
+def channel_attention(y, w1, b1, w2, b2, want_out=True):
+    """y bf16 [B,HW,96]; w1 [3,96(,1,1)], w2 [96,3(,1,1)] fp32.  Returns (out bf16, saved = (pooled, hid, scale));
+    want_out=False: out is None and only the statistics are computed (scale [B,96] is applied by the caller)."""
     B, HW, _ = y.shape
     dev = y.device
-    out = torch.empty_like(y)
+    out = torch.empty_like(y) if want_out else None
     pooled = torch.empty(B, 96, dtype=torch.float32, device=dev)
     hid = torch.empty(B, 3, dtype=torch.float32, device=dev)
     scale = torch.empty(B, 96, dtype=torch.float32, device=dev)

@@ -75,13 +75,13 @@ class _Tape:
         return act, pre
 
 
-    def conv_droppath(self, x, cin, name, m, res, res2=None, res2_scale=None):
+    def conv_droppath(self, x, cin, name, m, res, res2=None, res2_scale=None, res2_cs=None):
         """res + m[image] * conv(x) (+ res2_scale * res2): the DropPath-scaled residual branch, and HAB's conv_scale * CAB
         term, in the conv epilogue (no extra pass); m = None: factor 1"""
         w, b = self.P[name + '.weight'], self.P[name + '.bias']
         a = None if m is None else torch.as_tensor(m, dtype=torch.float32).to(x.device)
-        cs = None
-        if res2 is not None:
+        cs = res2_cs  # fp32 [B, Cout] per-image channel factors of res2
+        if res2 is not None and cs is None:
             cs = torch.full((x.shape[0], w.shape[0]), float(res2_scale), dtype=torch.float32, device=x.device)
         return ops.conv_nhwc_train(x, cin, self.packed(name), b, res1=res, alpha1_samples=a, res2=res2, res2_cs=cs)
 
@@ -164,10 +164,11 @@ def _hab_fwd(T, pre, x, shift, rpi, m1, m2):
     c1, c1p = T.conv_gelu(xn, 96, pre + 'conv_block.cab.0')
     c2 = T.conv(c1, 32, pre + 'conv_block.cab.2')
     ca_pre = pre + 'conv_block.cab.3.attention.'
-    ca, ca_saved = ops.channel_attention(c2.view(B, H * W, 96), P[ca_pre + '1.weight'].view(3, 96), P[ca_pre + '1.bias'],
-                                         P[ca_pre + '3.weight'].view(96, 3), P[ca_pre + '3.bias'])
-    # x1 = shortcut + DropPath(proj(attention)) + conv_scale * CAB: all three terms in the proj epilogue
-    x1 = T.conv_droppath(ao, 96, pre + 'attn.proj', m1, x, res2=ca.view(B, H, W, 96), res2_scale=_CONV_SCALE)
+    _, ca_saved = ops.channel_attention(c2.view(B, H * W, 96), P[ca_pre + '1.weight'].view(3, 96), P[ca_pre + '1.bias'],
+                                        P[ca_pre + '3.weight'].view(96, 3), P[ca_pre + '3.bias'], want_out=False)
+    # x1 = shortcut + DropPath(proj(attention)) + conv_scale * CAB: all three terms in the proj epilogue; the channel
+    # attention scale s[b][c] rides in the per-image channel factor of res2 (no scaled copy of c2 is ever written)
+    x1 = T.conv_droppath(ao, 96, pre + 'attn.proj', m1, x, res2=c2, res2_cs=ca_saved[2] * _CONV_SCALE)
     x2, mlp_saved = _mlp_fwd(T, pre, x1, m2)
     return x2, (x, xn, qkv, bias, ao, c1p, c1, c2, ca_saved, x1, mlp_saved)
 
