@@ -472,7 +472,8 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
         set_error("conv_wgrad: pitches / pointers must be 16-byte aligned");
         return SRB_E_ARG;
     }
-    if (const int ks = (x_pitch >= Cin && dy_pitch >= Cout) ? wgrad_tc_splits(B, H, W, Cin, Cout, taps) : 0) {
+    if (x_pitch < Cin || dy_pitch < Cout) { set_error("conv_wgrad: pitches (%d, %d) smaller than the channel counts (%d, %d)", x_pitch, dy_pitch, Cin, Cout); return SRB_E_ARG; }
+    if (const int ks = wgrad_tc_splits(B, H, W, Cin, Cout, taps)) {
         // tcgen05 path (wgrad_tc.cu): same partial layouts, same fixed-order reductions
         const int n = taps * Cout * Cin;
         float* partial = (float*)scratch;
@@ -491,7 +492,7 @@ int conv_wgrad(const bf16* x, int x_pitch, const bf16* dy, int dy_pitch, float* 
     const int n = taps * Cout * Cin;
     if (db) a.bpartial = a.partial + (size_t)ksplit * n;  // [ksplit][Cout], written by the weight-gradient kernel
     int rc;
-    if (wgrad_full_shape(Cin, Cout, taps) && x_pitch >= Cin && dy_pitch >= Cout) {
+    if (wgrad_full_shape(Cin, Cout, taps)) {
         rc = Cout == 288 ? launch_wgrad_full<9, 3>(a, ksplit, s)
            : Cout == 192 ? launch_wgrad_full<6, 3>(a, ksplit, s)
            : Cin == 192  ? launch_wgrad_full<3, 6>(a, ksplit, s)

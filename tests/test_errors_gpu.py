@@ -44,6 +44,9 @@ def test_operator_wrappers_raise_with_the_library_message(cuda):
     w64 = ops.pack_conv_weight(torch.zeros(64, 96, 1, 1, device=cuda))
     with pytest.raises(RuntimeError, match='pre_out'):
         ops.conv_nhwc_train(x96, 96, w64, None, pre_out=torch.empty(1, 16, 32, 64, dtype=torch.bfloat16, device=cuda))
+    with pytest.raises(RuntimeError, match='pitches'):  # a 32-channel buffer cannot hold 64 input channels
+        ops.conv_wgrad(torch.zeros(1, 16, 32, 32, dtype=torch.bfloat16, device=cuda), 64,
+                       torch.zeros(1, 16, 32, 32, dtype=torch.bfloat16, device=cuda), 32, 9)
     with pytest.raises(RuntimeError, match='wgrad'):
         ops.conv_wgrad(torch.zeros(1, 16, 24, 32, dtype=torch.bfloat16, device=cuda), 32,
                        torch.zeros(1, 16, 24, 32, dtype=torch.bfloat16, device=cuda), 32, 9)   # W % 32
