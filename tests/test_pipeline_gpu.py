@@ -24,5 +24,13 @@ def test_host_batches_match_plain_forwards(cuda):
     out = infer_host_batches(m, xs, out=[buf] * 5)
     assert out[-1] is buf and torch.equal(buf, want[-1])
     assert infer_host_batches(m, []) == []
+    # eager forwards instead of graph replays, and a weight update between calls (the cached graphs must not go stale)
+    eager = infer_host_batches(m, xs[:2], use_graphs=False)
+    assert torch.equal(eager[0], want[0]) and torch.equal(eager[1], want[1])
+    with torch.no_grad():
+        m.stage1.conv_first.weight.mul_(1.5)
+        want2 = m(xs[0].to(cuda)).cpu()
+    assert not torch.equal(want2, want[0])
+    assert torch.equal(infer_host_batches(m, xs[:1])[0], want2)
     with pytest.raises(ValueError, match='len'):
         infer_host_batches(m, xs, out=[buf])
