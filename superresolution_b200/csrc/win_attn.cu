@@ -29,6 +29,9 @@ using namespace amma;
 
 constexpr int RP = 56;  // bf16 pitch of a staged token row: q16 | k16 | v16 | 8 pad = 112 B = 7 chunks (odd)
 constexpr int GP = 24;  // bf16 pitch of a staged dO row: 16 | 8 pad = 48 B = 3 chunks (odd)
+constexpr int BP = 72;  // bf16 pitch of the CTA's [64][64] bias tile: word address 36 r + 4 j + t -> bank 4 g + t
+constexpr int BIAS_TILE = 64 * BP * 2;
+constexpr int FWD_WARPS = 4, BWD_WARPS = 8;  // warps per CTA, all on one head (they share its bias tile)
 
 struct WinArgs {
     const bf16* qkv;    // [B,H,W,288]
@@ -84,17 +87,21 @@ __device__ __forceinline__ bool stage(const WinArgs& a, int win, int h, bf16* sT
 }
 
 // softmax probabilities of the 16 query rows of block mt (fp32, accumulator layout: s[j][0..1] row g, s[j][2..3] row g+8)
-__device__ __forceinline__ void probs(const WinArgs& a, const bf16* sT, const uint8_t* sRid, bool mixed, int h, int mt,
+__device__ __forceinline__ void probs(const bf16* sB, const bf16* sT, const uint8_t* sRid, bool mixed, int mt,
                                       int lane, float (&s)[8][4]) {
     const int g = lane >> 2, t = lane & 3;
-    // the bias rows come from L2 (the shared-memory carve-out leaves almost no L1): issue the loads first so that the
-    // ldmatrix + MMA sequence below covers their latency
+    // bias of this CTA's head from its shared-memory tile (bf16, pitch BP: the 32 lanes of a request hit 32 banks).
+    // Read from global memory these were 64 float2 loads per item whose 8 row segments are 8 L1 wavefronts each -
+    // two thirds of the kernel's LSU time.
     const int r0 = 16 * mt + g, r1 = r0 + 8;
-    const float* b0 = a.bias + ((size_t)h * 64 + r0) * 64 + 2 * t;
-    const float* b1 = b0 + 8 * 64;
+    const bf16* b0 = sB + r0 * BP + 2 * t;
+    const bf16* b1 = b0 + 8 * BP;
     float2 bu[8], bv[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { bu[j] = __ldg((const float2*)(b0 + 8 * j)); bv[j] = __ldg((const float2*)(b1 + 8 * j)); }
+    for (int j = 0; j < 8; ++j) {
+        bu[j] = __bfloat1622float2(*(const __nv_bfloat162*)(b0 + 8 * j));
+        bv[j] = __bfloat1622float2(*(const __nv_bfloat162*)(b1 + 8 * j));
+    }
     uint32_t qa[4];
     frag_a(qa, sT, RP, 16 * mt, 0, lane);
 #pragma unroll
@@ -142,22 +149,37 @@ __device__ __forceinline__ void probs(const WinArgs& a, const bf16* sT, const ui
     for (int j = 0; j < 8; ++j) { s[j][0] *= i0; s[j][1] *= i0; s[j][2] *= i1; s[j][3] *= i1; }
 }
 
-constexpr int FWD_SMEM = 64 * RP * 2 + 64 * 4 + 64;
+constexpr int FWD_SMEM = 64 * RP * 2 + 64 * 4 + 64;  // per warp
 
-__global__ void __launch_bounds__(32, 20)  // 94 registers: 20 single-warp CTAs per SM (the kernel is latency-bound)
+// CTA prologue: head of this CTA, its bf16 bias tile in shared memory (the only CTA-wide barrier of the kernels)
+__device__ __forceinline__ void load_bias_tile(const WinArgs& a, int h, bf16* sB) {
+    const float4* src = (const float4*)(a.bias + (size_t)h * 4096);
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) {
+        const float4 v = __ldg(src + i);
+        const int r = i >> 4, c = (i & 15) * 4;
+        *(__nv_bfloat162*)(sB + r * BP + c) = __floats2bfloat162_rn(v.x, v.y);
+        *(__nv_bfloat162*)(sB + r * BP + c + 2) = __floats2bfloat162_rn(v.z, v.w);
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(32 * FWD_WARPS, 4)
 win_attn_fwd_kernel(const WinArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    bf16* sT = (bf16*)smem;
-    int* sPix = (int*)(smem + 64 * RP * 2);
+    bf16* sB = (bf16*)smem;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    uint8_t* mine = smem + BIAS_TILE + warp * FWD_SMEM;
+    bf16* sT = (bf16*)mine;
+    int* sPix = (int*)(mine + 64 * RP * 2);
     uint8_t* sRid = (uint8_t*)(sPix + 64);
-    const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
-    for (int item = blockIdx.x; item < a.nwin * 6; item += gridDim.x) {
-        const int win = item / 6, h = item % 6;
+    const int h = blockIdx.x % 6, nh = (gridDim.x - h + 5) / 6;  // this CTA's head, CTAs on that head
+    load_bias_tile(a, h, sB);
+    for (int win = (blockIdx.x / 6) * FWD_WARPS + warp; win < a.nwin; win += nh * FWD_WARPS) {
         const bool mixed = stage<false>(a, win, h, sT, nullptr, sPix, sRid, lane);
 #pragma unroll 1
         for (int mt = 0; mt < 4; ++mt) {
             float s[8][4];
-            probs(a, sT, sRid, mixed, h, mt, lane, s);
+            probs(sB, sT, sRid, mixed, mt, lane, s);
             float o[2][4];
 #pragma unroll
             for (int nt = 0; nt < 2; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
@@ -188,22 +210,26 @@ win_attn_fwd_kernel(const WinArgs a) {
     }
 }
 
-constexpr int BWD_SMEM = 64 * RP * 2 + 64 * GP * 2 + 64 * 64 * 4 + 64 * 4 + 64;
+constexpr int BWD_SMEM = 64 * RP * 2 + 64 * GP * 2 + 64 * 64 * 4 + 64 * 4 + 64;  // per warp
 
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(32 * BWD_WARPS, 1)
 win_attn_bwd_kernel(const WinArgs a) {
     extern __shared__ __align__(16) uint8_t smem[];
-    bf16* sT = (bf16*)smem;
+    bf16* sB = (bf16*)smem;
+    const int warp = threadIdx.x >> 5;
+    uint8_t* mine = smem + BIAS_TILE + warp * BWD_SMEM;
+    bf16* sT = (bf16*)mine;
     bf16* sG = sT + 64 * RP;
     float* sAcc = (float*)(sG + 64 * GP);            // [64][64] sum over this warp's windows of dS (one head)
     int* sPix = (int*)(sAcc + 64 * 64);
     uint8_t* sRid = (uint8_t*)(sPix + 64);
-    const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
-    // a warp keeps ONE head for all its items (grid is a multiple of 6): its sAcc tile is a single-head sum
-    const int h = blockIdx.x % 6;
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    // a CTA (and so each of its warps) keeps ONE head for all its items: every sAcc tile is a single-head sum
+    const int h = blockIdx.x % 6, nh = (gridDim.x - h + 5) / 6;
+    load_bias_tile(a, h, sB);
     for (int i = lane; i < 64 * 64; i += 32) sAcc[i] = 0.f;
     __syncwarp();
-    for (int win = blockIdx.x / 6; win < a.nwin; win += gridDim.x / 6) {
+    for (int win = (blockIdx.x / 6) * BWD_WARPS + warp; win < a.nwin; win += nh * BWD_WARPS) {
         const bool mixed = stage<true>(a, win, h, sT, sG, sPix, sRid, lane);
         float dk[4][2][4], dv[4][2][4];
 #pragma unroll
@@ -215,7 +241,7 @@ win_attn_bwd_kernel(const WinArgs a) {
 #pragma unroll 1
         for (int mt = 0; mt < 4; ++mt) {
             float p[8][4], ds[8][4];
-            probs(a, sT, sRid, mixed, h, mt, lane, p);
+            probs(sB, sT, sRid, mixed, mt, lane, p);
             // dP = dO V^T
             uint32_t ga[4];
             frag_a(ga, sG, GP, 16 * mt, 0, lane);
@@ -330,8 +356,13 @@ int win_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, in
     WinArgs a;
     a.qkv = qkv; a.bias = bias; a.index = nullptr; a.dout = nullptr; a.out = out; a.dtable = nullptr;
     a.B = B; a.H = H; a.W = W; a.shift = shift; a.nwin = B * (H / 8) * (W / 8);
-    const int items = a.nwin * 6, cap = num_sms() * 20;
-    win_attn_fwd_kernel<<<items < cap ? items : cap, 32, FWD_SMEM, s>>>(a);
+    static std::atomic<unsigned long long> smem_set{0};
+    constexpr int smem = BIAS_TILE + FWD_WARPS * FWD_SMEM;
+    SRB_TRY(opt_in_dynamic_smem(win_attn_fwd_kernel, smem, smem_set));
+    int grid = num_sms() * 4;  // 4 CTAs of 4 warps per SM
+    const int need = ((a.nwin + FWD_WARPS - 1) / FWD_WARPS) * 6;
+    if (grid > need) grid = need;
+    win_attn_fwd_kernel<<<grid, 32 * FWD_WARPS, smem, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
@@ -342,9 +373,14 @@ int win_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf1
     WinArgs a;
     a.qkv = qkv; a.bias = bias; a.index = index; a.dout = dout; a.out = dqkv; a.dtable = dtable;
     a.B = B; a.H = H; a.W = W; a.shift = shift; a.nwin = B * (H / 8) * (W / 8);
-    int warps_per_head = (num_sms() * 8) / 6;  // 8 resident single-warp CTAs per SM (registers and shared memory)
-    if (warps_per_head > a.nwin) warps_per_head = a.nwin;
-    win_attn_bwd_kernel<<<warps_per_head * 6, 32, BWD_SMEM, s>>>(a);
+    static std::atomic<unsigned long long> smem_set{0};
+    constexpr int smem = BIAS_TILE + BWD_WARPS * BWD_SMEM;
+    static_assert(smem <= 227 * 1024, "win_attn_bwd: shared memory");
+    SRB_TRY(opt_in_dynamic_smem(win_attn_bwd_kernel, smem, smem_set));
+    int grid = num_sms();  // one CTA of 8 warps per SM (255 registers per thread, 26 KB of shared memory per warp)
+    const int need = ((a.nwin + BWD_WARPS - 1) / BWD_WARPS) * 6;
+    if (grid > need) grid = need;
+    win_attn_bwd_kernel<<<grid, 32 * BWD_WARPS, smem, s>>>(a);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -217,7 +217,9 @@ def test_hybrid_gradients_match_rounding_matched_oracle(cuda, drop, smoothing, o
     # dominated by near-zero gradients (|g| ~1e-5 of the largest: channel-attention 1x1 weights) and only sanity-bounded.
     assert s2['median'] <= 0.025 and s2['p90'] <= 0.035 and s2['max_live'] <= 0.06 and s2['min_cos'] >= 0.999
     assert s1['median'] <= 0.06 and s1['p90'] <= 0.075 and s1['max_live'] <= 0.16 and s1['min_cos'] >= 0.997
-    assert s2['max'] <= 0.7 and s1['max'] <= 0.2
+    # (the stage-2 maximum sits on a channel-attention 1x1 weight with |g| ~6e-6, five orders below the largest tensors:
+    # bf16 noise of everything upstream decides its direction; 0.3 - 1.4 across kernel revisions)
+    assert s2['max'] <= 2.5 and s1['max'] <= 0.2
 
 
 def test_train_step_micro_batches_equal_full_batch_and_reduce_loss(cuda):
