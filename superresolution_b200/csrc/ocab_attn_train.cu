@@ -37,6 +37,7 @@ constexpr int KP = 40;  // bf16 pitch of a staged key row: k16 | v16 | 8 pad = 8
 struct OcaArgs {
     const bf16* qkv;    // [B,H,W,288]
     const float* bias;  // [6][64][144]
+    const float* bias_frag;  // optional: the same values in MMA-fragment order [6][4 mt][18 j][32 lanes][4] (backward)
     const int* index;   // [64][144]  (backward)
     const bf16* dout;   // [B,H,W,96] (backward)
     bf16* out;          // forward: [B,H,W,96];  backward: dqkv [B,H,W,288] (q part written here, k/v part by the fold)
@@ -100,12 +101,24 @@ template <int NT>
 __device__ __forceinline__ void oa_logits(const OcaArgs& a, const bf16* sQ, const bf16* sKV, int h, int mt, int key0, int lane,
                                           float (&s)[NT][4]) {
     const int g = lane >> 2, t = lane & 3;
-    // bias rows come from L2: issue the loads before the ldmatrix + MMA sequence that covers their latency
-    const float* b0 = a.bias + ((size_t)h * 64 + 16 * mt + g) * OA_NK + key0 + 2 * t;
-    const float* b1 = b0 + 8 * OA_NK;
+    // bias rows come from L2: issue the loads before the ldmatrix + MMA sequence that covers their latency.  Row-major,
+    // the two float2 a lane needs per n-tile are 8 row segments = 8 L1 wavefronts per load; in fragment order one
+    // float4 per lane is 512 contiguous bytes per warp = 4 wavefronts for both.
     float2 bu[NT], bv[NT];
+    if (a.bias_frag) {
+        const float4* bf = (const float4*)a.bias_frag + ((size_t)(h * 4 + mt) * 18 + (key0 >> 3)) * 32 + lane;
 #pragma unroll
-    for (int j = 0; j < NT; ++j) { bu[j] = __ldg((const float2*)(b0 + 8 * j)); bv[j] = __ldg((const float2*)(b1 + 8 * j)); }
+        for (int j = 0; j < NT; ++j) {
+            const float4 b4 = __ldg(bf + j * 32);
+            bu[j] = make_float2(b4.x, b4.y);
+            bv[j] = make_float2(b4.z, b4.w);
+        }
+    } else {
+        const float* b0 = a.bias + ((size_t)h * 64 + 16 * mt + g) * OA_NK + key0 + 2 * t;
+        const float* b1 = b0 + 8 * OA_NK;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) { bu[j] = __ldg((const float2*)(b0 + 8 * j)); bv[j] = __ldg((const float2*)(b1 + 8 * j)); }
+    }
     uint32_t qa[4];
     frag_a(qa, sQ, QP, 16 * mt, 0, lane);
 #pragma unroll
@@ -160,6 +173,17 @@ __device__ __forceinline__ void oa_rows(const OcaArgs& a, const bf16* sQ, const 
     i0 = 1.f / quad_sum(l0); i1 = 1.f / quad_sum(l1);
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) { o[nt][0] *= i0; o[nt][1] *= i0; o[nt][2] *= i1; o[nt][3] *= i1; }
+}
+
+// frag[h][mt][j][lane = 4 g + t] = (bias[h][16 mt + g][8 j + 2 t], [..][8 j + 2 t + 1], bias[h][16 mt + g + 8][8 j + 2 t], [.. + 1])
+__global__ void __launch_bounds__(256)
+oa_bias_frag_kernel(const float* __restrict__ bias, float4* __restrict__ frag) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;  // (h, mt, j, lane)
+    if (i >= 6 * 4 * 18 * 32) return;
+    const int lane = i & 31, j = (i >> 5) % 18, mt = (i / (32 * 18)) & 3, h = i / (32 * 18 * 4);
+    const int g = lane >> 2, t = lane & 3;
+    const float* b0 = bias + ((size_t)h * 64 + 16 * mt + g) * OA_NK + 8 * j + 2 * t;
+    frag[i] = make_float4(b0[0], b0[1], b0[8 * OA_NK], b0[8 * OA_NK + 1]);
 }
 
 constexpr int OA_FWD_SMEM = 64 * QP * 2 + OA_NK * KP * 2 + 64 * 4;
@@ -395,7 +419,10 @@ int oa_check(int B, int H, int W) {
 
 }  // namespace
 
-size_t ocab_attn_bwd_scratch_bytes(int B, int H, int W) { return (size_t)B * (H / 8) * (W / 8) * OA_NK * 192 * sizeof(bf16); }
+constexpr size_t OA_FRAG_BYTES = (size_t)6 * 64 * OA_NK * sizeof(float);
+static size_t oa_dkv_bytes(int B, int H, int W) { return (size_t)B * (H / 8) * (W / 8) * OA_NK * 192 * sizeof(bf16); }
+// per-window dK | dV rows, then the bias in fragment order
+size_t ocab_attn_bwd_scratch_bytes(int B, int H, int W) { return oa_dkv_bytes(B, H, W) + OA_FRAG_BYTES; }
 
 int ocab_attn_fwd(const bf16* qkv, const float* bias, bf16* out, int B, int H, int W, cudaStream_t s) {
     SRB_TRY(oa_check(B, H, W));
@@ -412,6 +439,12 @@ int ocab_attn_bwd(const bf16* qkv, const float* bias, const int* index, const bf
     SRB_TRY(oa_check(B, H, W));
     OcaArgs a{};
     a.qkv = qkv; a.bias = bias; a.index = index; a.dout = dout; a.out = dqkv; a.dkv_win = (bf16*)scratch; a.dtable = dtable;
+    float4* frag = (float4*)((uint8_t*)scratch + oa_dkv_bytes(B, H, W));
+    if (((uintptr_t)frag & 15) == 0) {  // (a scratch base off 16 bytes keeps the row-major loads)
+        oa_bias_frag_kernel<<<(6 * 4 * 18 * 32 + 255) / 256, 256, 0, s>>>(bias, frag);
+        SRB_CUDA(cudaGetLastError());
+        a.bias_frag = (const float*)frag;
+    }
     a.B = B; a.H = H; a.W = W; a.nwin = B * (H / 8) * (W / 8);
     SRB_CUDA(cudaFuncSetAttribute(ocab_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OA_BWD_SMEM));
     int warps_per_head = (num_sms() * 4) / 6;  // 4 resident single-warp CTAs per SM (56 KB of shared memory each)
