@@ -56,3 +56,11 @@ for name, xx, ci, dd, co, taps in [('qkv', x96, 96, x288, 288, 1), ('proj', x96,
 timed('layernorm96', lambda: ops.layernorm96(x96.view(-1, 96), alpha.new_ones(96), alpha.new_zeros(96)), 192)
 timed('layernorm96_bwd (+res)', lambda: ops.layernorm96_bwd(x96.view(-1, 96), y96.view(-1, 96), alpha.new_ones(96), z96.view(-1, 96)), 384)
 qkv = x288
+# window attention of one HAB (all 16384 windows x 6 heads), forward and backward
+table = torch.randn(225, 6, device=dev) * 0.5
+coords = torch.stack(torch.meshgrid(torch.arange(8), torch.arange(8), indexing='ij')).flatten(1)
+rel = (coords[:, :, None] - coords[:, None, :]).permute(1, 2, 0) + 7
+index = (rel[..., 0] * 15 + rel[..., 1]).to(dev)
+wbias = ops.gather_rel_bias(table, index)
+timed('window attention fwd (shift 4)', lambda: ops.window_attention(qkv, wbias, 4), 288 + 96)
+timed('window attention bwd (shift 4)', lambda: ops.window_attention_bwd(qkv, wbias, index, y96, 4), 288 + 96 + 288)
